@@ -1,0 +1,607 @@
+// libsgnn C ABI (include/sgnn.h): model description, buffers, kernel dispatch.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "sgnn_allpairs.cuh"
+#include "sgnn_common.cuh"
+#include "sgnn_rank.cuh"
+#include "sgnn_small.cuh"
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct HostWs {  // device staging for the *_host entry points (sized by sgnn_reserve)
+  int64_t cap_graphs = 0, cap_nodes = 0, cap_nnz = 0, cap_pairs = 0, cap_q = 0, cap_db = 0;
+  int32_t *node_off[2] = {nullptr, nullptr}, *labels[2] = {nullptr, nullptr};
+  int32_t *rowptr[2] = {nullptr, nullptr}, *col[2] = {nullptr, nullptr};
+  float* val[2] = {nullptr, nullptr};
+  int32_t *g1 = nullptr, *g2 = nullptr;
+  float *target = nullptr, *raw = nullptr, *sim_pairs = nullptr, *emb = nullptr;
+  float *emb_q = nullptr, *emb_db = nullptr, *sim = nullptr, *topk_vals = nullptr;
+  int32_t* topk_ids = nullptr;
+  int64_t cap_topk = 0;
+};
+
+}  // namespace
+
+struct SgnnHandle_t {
+  SgnnConfig cfg;
+  ModelDev M;
+  int device = 0, sm_count = 148, smem_optin = 0;
+  std::string err;
+  std::vector<SgnnParamInfo> table;
+  float *d_params = nullptr, *d_grads = nullptr, *d_m = nullptr, *d_v = nullptr, *d_loss = nullptr;
+  int64_t adam_t = 0;
+  float *d_P = nullptr, *d_C = nullptr;  // all-pairs query tables
+  int64_t cap_P = 0;
+  int dep = 16;                           // padded embedding width of the all-pairs scorer
+  cudaStream_t stream = nullptr;          // used by *_host entry points
+  HostWs ws;
+  // launch geometry decided at create
+  int embed_wpb[2] = {8, 8}, train_wpb[2] = {4, 4};
+  size_t embed_smem[2] = {0, 0}, train_smem[2] = {0, 0}, pair_smem = 0;
+};
+
+namespace {
+
+int fail(SgnnHandle h, const std::string& msg) {
+  if (h) h->err = msg; else g_create_error = msg;
+  return 1;
+}
+
+#define CUDA_OK(h, expr)                                                                  \
+  do {                                                                                    \
+    cudaError_t e_ = (expr);                                                              \
+    if (e_ != cudaSuccess)                                                                \
+      return fail(h, std::string(#expr) + ": " + cudaGetErrorString(e_));                 \
+  } while (0)
+
+BatchDev to_dev(const SgnnGraphBatch* b) {
+  BatchDev d;
+  d.n_graphs = b->n_graphs; d.node_off = b->node_off; d.labels = b->labels;
+  d.rowptr = b->rowptr; d.col = b->col; d.val = b->val;
+  return d;
+}
+
+const char* kind_name(int k) {
+  static const char* names[] = {"GraphConvolution", "Dense", "Padding", "Average", "Attention", "NTN", "Dot"};
+  return (k >= 0 && k <= 6) ? names[k] : "?";
+}
+
+// Validate the layer chain and lay the flat parameter blob out in the reference's variable
+// creation order (layers.py:67-73, 146-151, 172-177, 268-277).
+int build_model(const SgnnConfig& c, ModelDev& M, std::vector<SgnnParamInfo>& table, std::string& err) {
+  memset(&M, 0, sizeof(M));
+  if (c.abi_version != SGNN_ABI_VERSION) { err = "SgnnConfig.abi_version mismatch"; return 1; }
+  if (c.num_layers < 2 || c.num_layers > SGNN_MAX_LAYERS) { err = "num_layers must be in [2, 12]"; return 1; }
+  if (c.input_dim < 1) { err = "input_dim must be >= 1"; return 1; }
+  if (c.dropout != 0.f) { err = "dropout > 0 is not implemented on the device path yet (run with --dropout=0)"; return 1; }
+  int64_t off = 0;
+  int cur = c.input_dim, stage = 0, act_cols = 0, dmax = 4, aux = 0;
+  auto add = [&](int layer, const char* name, int nd, int s0, int s1, int s2) {
+    SgnnParamInfo p; memset(&p, 0, sizeof(p));
+    p.layer = layer; strncpy(p.name, name, sizeof(p.name) - 1); p.ndim = nd;
+    p.shape[0] = s0; p.shape[1] = s1; p.shape[2] = s2; p.offset = off;
+    int64_t cnt = (int64_t)s0 * (nd > 1 ? s1 : 1) * (nd > 2 ? s2 : 1);
+    table.push_back(p); off += cnt; return (int)p.offset;
+  };
+  M.pool_kind = -1; M.pair_kind = -1;
+  for (int i = 0; i < c.num_layers; ++i) {
+    const SgnnLayerDesc& d = c.layers[i];
+    if (d.kind == SGNN_LAYER_GCN || d.kind == SGNN_LAYER_DENSE) {
+      if (stage != 0) { err = std::string(kind_name(d.kind)) + " after the pooling layer is not supported"; return 1; }
+      if (i == 0 && d.kind != SGNN_LAYER_GCN) { err = "layer_0 must be GraphConvolution (model_mse.py:97)"; return 1; }
+      if (d.input_dim != cur) { err = "layer " + std::to_string(i) + ": input_dim does not match the previous width"; return 1; }
+      if (d.output_dim < 1 || d.output_dim > 128) { err = "output_dim must be in [1, 128]"; return 1; }
+      LayerDev& L = M.L[M.n_node];
+      L.kind = d.kind; L.din = d.input_dim; L.dout = d.output_dim; L.act = d.act; L.bias = d.bias;
+      L.w_off = add(i, d.kind == SGNN_LAYER_GCN ? "weights_0" : "weights", 2, L.din, L.dout, 1);
+      L.b_off = d.bias ? add(i, "bias", 1, L.dout, 1, 1) : 0;
+      L.out_off = act_cols; act_cols += round_up(L.dout, 4);
+      if (M.n_node > 0) { L.wt_off = aux; aux += round_up(L.din * L.dout, 4); }
+      dmax = std::max(dmax, L.dout);
+      cur = L.dout; ++M.n_node;
+    } else if (d.kind == SGNN_LAYER_PADDING || d.kind == SGNN_LAYER_AVERAGE || d.kind == SGNN_LAYER_ATTENTION) {
+      if (stage != 0 || M.n_node == 0) { err = "exactly one pooling layer must follow the node layers"; return 1; }
+      M.pool_kind = d.kind; M.node_dim = cur; stage = 1;
+      if (d.kind == SGNN_LAYER_PADDING) {
+        if (d.aux < 1) { err = "Padding: max_in_dims must be >= 1"; return 1; }
+        M.pool_aux = d.aux; M.pool_fparam = d.fparam; M.emb_dim = d.aux * cur;
+      } else {
+        M.emb_dim = cur;
+        if (d.kind == SGNN_LAYER_ATTENTION) {
+          if (d.input_dim != cur) { err = "Attention: input_dim does not match the node width"; return 1; }
+          M.pool_w_off = add(i, "weights", 2, cur, cur, 1);
+          M.pool_wt_off = aux; aux += round_up(cur * cur, 4);
+        }
+      }
+    } else if (d.kind == SGNN_LAYER_NTN || d.kind == SGNN_LAYER_DOT) {
+      if (stage != 1 || i != c.num_layers - 1) { err = "the pair layer (NTN/Dot) must be last and follow a pooling layer"; return 1; }
+      M.pair_kind = d.kind; M.D = M.emb_dim; stage = 2;
+      if (d.kind == SGNN_LAYER_NTN) {
+        if (d.input_dim != M.emb_dim) { err = "NTN: input_dim must equal the flattened representation width"; return 1; }
+        M.K = d.aux; M.pair_act = d.act; M.pair_bias = d.bias;
+        if (M.K < 1 || M.K > 64) { err = "NTN: feature_map_dim must be in [1, 64]"; return 1; }
+        if ((int64_t)M.D * M.D * M.K > 32768) { err = "NTN: input_dim^2 * feature_map_dim must be <= 32768"; return 1; }
+        M.w_off = add(i, "weights_W", 3, M.D, M.D, M.K);
+        M.v_off = add(i, "weights_V", 2, M.K, 2 * M.D, 1);
+        M.u_off = add(i, "weights_U", 2, M.K, 1, 1);
+        M.b_off = d.bias ? add(i, "bias", 1, M.K, 1, 1) : 0;
+      } else {
+        M.K = 1; M.pair_act = SGNN_ACT_IDENTITY;
+      }
+    } else {
+      err = "Unknown layer kind " + std::to_string(d.kind); return 1;
+    }
+  }
+  if (stage != 2) { err = "the layer chain must end with NTN or Dot"; return 1; }
+  if (M.emb_dim > 64) { err = "flattened representation wider than 64 is not supported"; return 1; }
+  M.final_act = c.final_act; M.yeta = c.yeta; M.ntn_mode = c.ntn_mode; M.loss_mode = c.loss_mode;
+  M.n_params = (int)off; M.input_dim = c.input_dim;
+  M.ld = round_up(dmax, 4) + 4;
+  M.act_ld = act_cols + 4;
+  M.aux_floats = aux;
+  return 0;
+}
+
+template <typename Kern>
+int set_smem(SgnnHandle h, Kern k, size_t bytes) {
+  CUDA_OK(h, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  return 0;
+}
+
+int plan_launches(SgnnHandle h) {
+  const ModelDev& M = h->M;
+  const size_t wfl = round_up(M.n_params, 4);
+  const size_t budget = (size_t)h->smem_optin;
+  const int DK = M.D * M.K;
+  const size_t wpfl = M.pair_kind == SGNN_LAYER_NTN ? round_up(M.D * DK, 4) : 0;
+  for (int v = 0; v < 2; ++v) {
+    const int nmax = v == 0 ? 16 : 32;
+    const int csr = v == 0 ? SmallGeom<16>::CSR_WORDS : SmallGeom<32>::CSR_WORDS;
+    int wpb = 8;
+    size_t need;
+    while (true) {
+      need = (wfl + (size_t)wpb * embed_warp_floats(M, nmax, csr)) * sizeof(float);
+      if (need <= budget || wpb == 1) break;
+      wpb >>= 1;
+    }
+    if (need > budget) return fail(h, "model too large for the small-graph embed kernel's shared memory");
+    h->embed_wpb[v] = wpb; h->embed_smem[v] = need;
+    const TrainLayout TL = train_layout(M, nmax, csr);
+    wpb = 4;
+    while (true) {
+      need = (2 * wfl + wpfl + round_up(M.aux_floats, 4) + (size_t)wpb * TL.total) * sizeof(float);
+      if (need <= budget || wpb == 1) break;
+      wpb >>= 1;
+    }
+    if (need > budget) return fail(h, "model too large for the fused training kernel's shared memory");
+    h->train_wpb[v] = wpb; h->train_smem[v] = need;
+  }
+  {
+    const int Dp = round_up(M.D, 4), Kp = round_up(M.K, 4);
+    h->pair_smem = (wfl + wpfl + 8 * (size_t)(2 * Dp + round_up(DK, 4) + 2 * Kp)) * sizeof(float);
+    if (h->pair_smem > budget) return fail(h, "pair layer too large for shared memory");
+  }
+  if (set_smem(h, embed_kernel<16>, h->embed_smem[0])) return 1;
+  if (set_smem(h, embed_kernel<32>, h->embed_smem[1])) return 1;
+  if (set_smem(h, train_pairs_kernel<16>, h->train_smem[0])) return 1;
+  if (set_smem(h, train_pairs_kernel<32>, h->train_smem[1])) return 1;
+  if (set_smem(h, pair_score_kernel, h->pair_smem)) return 1;
+  return 0;
+}
+
+uint64_t splitmix64(uint64_t& s) {
+  uint64_t z = (s += 0x9E3779B97F4A7C15ull);
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+
+template <typename T>
+int dev_alloc(SgnnHandle h, T** p, int64_t count) {
+  if (*p) { cudaFree(*p); *p = nullptr; }
+  if (count <= 0) return 0;
+  CUDA_OK(h, cudaMalloc(reinterpret_cast<void**>(p), (size_t)count * sizeof(T)));
+  return 0;
+}
+
+int ensure_query_tables(SgnnHandle h, int64_t m) {
+  if (m <= h->cap_P) return 0;
+  return fail(h, "query table workspace too small: call sgnn_reserve(max_queries >= m) first");
+}
+
+}  // namespace
+
+extern "C" {
+
+int sgnn_abi_version(void) { return SGNN_ABI_VERSION; }
+
+const char* sgnn_last_error(SgnnHandle h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+int sgnn_create(const SgnnConfig* cfg, SgnnHandle* out) {
+  if (!cfg || !out) return fail(nullptr, "sgnn_create: null argument");
+  *out = nullptr;
+  SgnnHandle h = new SgnnHandle_t();
+  h->cfg = *cfg;
+  std::string err;
+  if (build_model(*cfg, h->M, h->table, err)) { delete h; return fail(nullptr, err); }
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    delete h;
+    return fail(nullptr, std::string("no CUDA device: the sm_100a path has no CPU fallback (") +
+                             cudaGetErrorString(e) + ")");
+  }
+  h->device = cfg->device;
+  if (cudaSetDevice(h->device) != cudaSuccess) { delete h; return fail(nullptr, "cudaSetDevice failed"); }
+  cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, h->device);
+  cudaDeviceGetAttribute(&h->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device);
+  const int64_t np = h->M.n_params;
+  auto bail = [&](const char* what) {
+    g_create_error = std::string(what) + ": " + h->err;
+    sgnn_destroy(h);
+    return 1;
+  };
+  if (dev_alloc(h, &h->d_params, np) || dev_alloc(h, &h->d_grads, np) || dev_alloc(h, &h->d_m, np) ||
+      dev_alloc(h, &h->d_v, np) || dev_alloc(h, &h->d_loss, 4))
+    return bail("allocating parameter buffers");
+  cudaMemset(h->d_params, 0, np * sizeof(float));
+  cudaMemset(h->d_grads, 0, np * sizeof(float));
+  cudaMemset(h->d_m, 0, np * sizeof(float));
+  cudaMemset(h->d_v, 0, np * sizeof(float));
+  cudaMemset(h->d_loss, 0, 4 * sizeof(float));
+  if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess)
+    return bail("cudaStreamCreate");
+  h->dep = h->M.emb_dim <= 16 ? 16 : (h->M.emb_dim <= 32 ? 32 : 64);
+  if (plan_launches(h)) return bail("planning launches");
+  *out = h;
+  return 0;
+}
+
+int sgnn_destroy(SgnnHandle h) {
+  if (!h) return 0;
+  cudaSetDevice(h->device);
+  cudaFree(h->d_params); cudaFree(h->d_grads); cudaFree(h->d_m); cudaFree(h->d_v); cudaFree(h->d_loss);
+  cudaFree(h->d_P); cudaFree(h->d_C);
+  HostWs& w = h->ws;
+  for (int s = 0; s < 2; ++s) {
+    cudaFree(w.node_off[s]); cudaFree(w.labels[s]); cudaFree(w.rowptr[s]); cudaFree(w.col[s]); cudaFree(w.val[s]);
+  }
+  cudaFree(w.g1); cudaFree(w.g2); cudaFree(w.target); cudaFree(w.raw); cudaFree(w.sim_pairs); cudaFree(w.emb);
+  cudaFree(w.emb_q); cudaFree(w.emb_db); cudaFree(w.sim); cudaFree(w.topk_vals); cudaFree(w.topk_ids);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+  return 0;
+}
+
+int64_t sgnn_param_count(SgnnHandle h) { return h ? h->M.n_params : -1; }
+
+int sgnn_param_table(SgnnHandle h, SgnnParamInfo* out, int32_t capacity) {
+  if (!h) return -1;
+  const int n = (int)h->table.size();
+  if (out) for (int i = 0; i < n && i < capacity; ++i) out[i] = h->table[i];
+  return n;
+}
+
+int sgnn_embed_dim(SgnnHandle h) { return h ? h->M.emb_dim : -1; }
+
+int sgnn_set_params(SgnnHandle h, const float* host_params) {
+  if (!h || !host_params) return fail(h, "sgnn_set_params: null argument");
+  CUDA_OK(h, cudaSetDevice(h->device));
+  const size_t bytes = (size_t)h->M.n_params * sizeof(float);
+  CUDA_OK(h, cudaMemcpy(h->d_params, host_params, bytes, cudaMemcpyHostToDevice));
+  CUDA_OK(h, cudaMemset(h->d_m, 0, bytes));
+  CUDA_OK(h, cudaMemset(h->d_v, 0, bytes));
+  CUDA_OK(h, cudaMemset(h->d_grads, 0, bytes));
+  h->adam_t = 0;
+  return 0;
+}
+
+int sgnn_get_params(SgnnHandle h, float* host_params) {
+  if (!h || !host_params) return fail(h, "sgnn_get_params: null argument");
+  CUDA_OK(h, cudaSetDevice(h->device));
+  CUDA_OK(h, cudaDeviceSynchronize());
+  CUDA_OK(h, cudaMemcpy(host_params, h->d_params, (size_t)h->M.n_params * sizeof(float), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int sgnn_init_params(SgnnHandle h, uint64_t seed) {
+  if (!h) return 1;
+  std::vector<float> p(h->M.n_params, 0.f);
+  uint64_t s = seed;
+  for (const SgnnParamInfo& t : h->table) {
+    if (strcmp(t.name, "bias") == 0) continue;                       // zeros, inits.py:18-21
+    const double r = std::sqrt(6.0 / (t.shape[0] + t.shape[1]));      // glorot, inits.py:11-15
+    int64_t cnt = (int64_t)t.shape[0] * (t.ndim > 1 ? t.shape[1] : 1) * (t.ndim > 2 ? t.shape[2] : 1);
+    for (int64_t i = 0; i < cnt; ++i) {
+      const double u = (double)(splitmix64(s) >> 11) * (1.0 / 9007199254740992.0);
+      p[t.offset + i] = (float)((2.0 * u - 1.0) * r);
+    }
+  }
+  return sgnn_set_params(h, p.data());
+}
+
+int sgnn_device_buffers(SgnnHandle h, float** params, float** grads, float** adam_m, float** adam_v) {
+  if (!h) return 1;
+  if (params) *params = h->d_params;
+  if (grads) *grads = h->d_grads;
+  if (adam_m) *adam_m = h->d_m;
+  if (adam_v) *adam_v = h->d_v;
+  return 0;
+}
+
+int sgnn_reserve(SgnnHandle h, int64_t max_graphs, int64_t max_nodes, int64_t max_nnz, int64_t max_pairs,
+                 int64_t max_queries, int64_t max_db) {
+  if (!h) return 1;
+  CUDA_OK(h, cudaSetDevice(h->device));
+  CUDA_OK(h, cudaDeviceSynchronize());
+  HostWs& w = h->ws;
+  const int E = h->M.emb_dim;
+  if (max_graphs > w.cap_graphs || max_nodes > w.cap_nodes || max_nnz > w.cap_nnz) {
+    w.cap_graphs = std::max(w.cap_graphs, max_graphs);
+    w.cap_nodes = std::max(w.cap_nodes, max_nodes);
+    w.cap_nnz = std::max(w.cap_nnz, max_nnz);
+    for (int s = 0; s < 2; ++s) {
+      if (dev_alloc(h, &w.node_off[s], w.cap_graphs + 1) || dev_alloc(h, &w.labels[s], w.cap_nodes) ||
+          dev_alloc(h, &w.rowptr[s], w.cap_nodes + 1) || dev_alloc(h, &w.col[s], w.cap_nnz) ||
+          dev_alloc(h, &w.val[s], w.cap_nnz))
+        return 1;
+    }
+    if (dev_alloc(h, &w.emb, w.cap_graphs * E) || dev_alloc(h, &w.emb_q, w.cap_graphs * E) ||
+        dev_alloc(h, &w.emb_db, w.cap_graphs * E))
+      return 1;
+  }
+  if (max_pairs > w.cap_pairs) {
+    w.cap_pairs = max_pairs;
+    if (dev_alloc(h, &w.g1, max_pairs) || dev_alloc(h, &w.g2, max_pairs) || dev_alloc(h, &w.target, max_pairs) ||
+        dev_alloc(h, &w.raw, max_pairs) || dev_alloc(h, &w.sim_pairs, max_pairs))
+      return 1;
+  }
+  if (max_queries > h->cap_P) {
+    h->cap_P = max_queries;
+    const int K = h->M.pair_kind == SGNN_LAYER_NTN ? h->M.K : 1;
+    if (dev_alloc(h, &h->d_P, max_queries * K * 64) || dev_alloc(h, &h->d_C, max_queries * K)) return 1;
+  }
+  if (max_queries * max_db > w.cap_q * w.cap_db || max_queries > w.cap_q) {
+    w.cap_q = std::max(w.cap_q, max_queries);
+    w.cap_db = std::max(w.cap_db, max_db);
+    if (dev_alloc(h, &w.sim, w.cap_q * w.cap_db)) return 1;
+    w.cap_topk = w.cap_q * 64;
+    if (dev_alloc(h, &w.topk_ids, w.cap_topk) || dev_alloc(h, &w.topk_vals, w.cap_topk)) return 1;
+  }
+  return 0;
+}
+
+int sgnn_embed_graphs(SgnnHandle h, const SgnnGraphBatch* b, float* emb_dev, void* stream) {
+  if (!h || !b || !emb_dev) return fail(h, "sgnn_embed_graphs: null argument");
+  if (b->n_graphs == 0) return 0;
+  if (b->max_nodes > 32)
+    return fail(h, "graphs with more than 32 nodes need the large-graph path (not built yet)");
+  const int v = b->max_nodes <= 16 ? 0 : 1;
+  const int wpb = h->embed_wpb[v];
+  const int blocks = std::min((b->n_graphs + wpb - 1) / wpb, h->sm_count * 4);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (v == 0)
+    embed_kernel<16><<<blocks, wpb * 32, h->embed_smem[0], st>>>(h->M, to_dev(b), h->d_params, emb_dev);
+  else
+    embed_kernel<32><<<blocks, wpb * 32, h->embed_smem[1], st>>>(h->M, to_dev(b), h->d_params, emb_dev);
+  CUDA_OK(h, cudaGetLastError());
+  return 0;
+}
+
+int sgnn_score_pairs(SgnnHandle h, const float* emb_dev, const int32_t* g1, const int32_t* g2, int32_t n_pairs,
+                     float* raw_dev, float* sim_dev, void* stream) {
+  if (!h || !emb_dev || !g1 || !g2) return fail(h, "sgnn_score_pairs: null argument");
+  if (n_pairs == 0) return 0;
+  const int blocks = std::min((n_pairs + 7) / 8, h->sm_count * 4);
+  pair_score_kernel<<<blocks, 256, h->pair_smem, (cudaStream_t)stream>>>(h->M, h->d_params, emb_dev, g1, g2,
+                                                                        n_pairs, raw_dev, sim_dev);
+  CUDA_OK(h, cudaGetLastError());
+  return 0;
+}
+
+int sgnn_forward_pairs(SgnnHandle h, const SgnnGraphBatch* b, const int32_t* g1, const int32_t* g2,
+                       int32_t n_pairs, float* emb_ws_dev, float* raw_dev, float* sim_dev, void* stream) {
+  if (sgnn_embed_graphs(h, b, emb_ws_dev, stream)) return 1;
+  return sgnn_score_pairs(h, emb_ws_dev, g1, g2, n_pairs, raw_dev, sim_dev, stream);
+}
+
+int sgnn_score_all_pairs(SgnnHandle h, const float* emb_q, int32_t m, const float* emb_db, int32_t n,
+                         float* sim_dev, int64_t ld, void* stream) {
+  if (!h || !emb_q || !emb_db || !sim_dev) return fail(h, "sgnn_score_all_pairs: null argument");
+  if (m == 0 || n == 0) return 0;
+  if (ld < n) return fail(h, "sgnn_score_all_pairs: ld < n");
+  if (ensure_query_tables(h, m)) return 1;
+  cudaStream_t st = (cudaStream_t)stream;
+  const ModelDev& M = h->M;
+  const int K = M.pair_kind == SGNN_LAYER_NTN ? M.K : 1;
+  const int DEP = h->dep;
+  allpairs_prep_kernel<<<(m + 3) / 4, 128, 0, st>>>(M, h->d_params, emb_q, m, DEP, h->d_P, h->d_C);
+  CUDA_OK(h, cudaGetLastError());
+  constexpr int QC = 8;
+  const int gx = (n + 127) / 128;
+  // enough query blocks to fill the machine a few times over
+  int gy = std::max(1, std::min((m + QC - 1) / QC, (h->sm_count * 8 + gx - 1) / gx));
+  const int qpb = ((m + gy - 1) / gy + QC - 1) / QC * QC;
+  gy = (m + qpb - 1) / qpb;
+  const size_t smem = ((size_t)QC * K * DEP + QC * K + K) * sizeof(float);
+  dim3 grid(gx, gy);
+  if (DEP == 16)
+    allpairs_fp32_kernel<16, QC><<<grid, 128, smem, st>>>(M, h->d_params, h->d_P, h->d_C, emb_db, m, n, qpb, sim_dev, ld);
+  else if (DEP == 32)
+    allpairs_fp32_kernel<32, QC><<<grid, 128, smem, st>>>(M, h->d_params, h->d_P, h->d_C, emb_db, m, n, qpb, sim_dev, ld);
+  else
+    allpairs_fp32_kernel<64, QC><<<grid, 128, smem, st>>>(M, h->d_params, h->d_P, h->d_C, emb_db, m, n, qpb, sim_dev, ld);
+  CUDA_OK(h, cudaGetLastError());
+  return 0;
+}
+
+int sgnn_topk(SgnnHandle h, const float* sim_dev, int32_t m, int32_t n, int64_t ld, int32_t k, int32_t* ids_dev,
+              float* vals_dev, void* stream) {
+  if (!h || !sim_dev || !ids_dev) return fail(h, "sgnn_topk: null argument");
+  if (k < 0 || k > n) return fail(h, "Invalid k " + std::to_string(k));  // results.py:68-69
+  if (m == 0 || k == 0) return 0;
+  const size_t row_bytes = (size_t)n * sizeof(float);
+  const int in_smem = row_bytes <= 48 * 1024;
+  topk_kernel<<<m, 256, in_smem ? row_bytes : 0, (cudaStream_t)stream>>>(sim_dev, n, ld, k, in_smem, ids_dev, vals_dev);
+  CUDA_OK(h, cudaGetLastError());
+  return 0;
+}
+
+int sgnn_sort_rows(SgnnHandle h, const float* sim_dev, int32_t m, int32_t n, int64_t ld, int32_t* ids_dev,
+                   void* stream) {
+  if (!h || !sim_dev || !ids_dev) return fail(h, "sgnn_sort_rows: null argument");
+  if (m == 0 || n == 0) return 0;
+  int n_pad = 2;
+  while (n_pad < n) n_pad <<= 1;
+  const size_t bytes = (size_t)n_pad * sizeof(unsigned long long);
+  if (bytes > (size_t)h->smem_optin) return fail(h, "sgnn_sort_rows: row too long for the shared-memory sorter");
+  if (set_smem(h, sort_rows_kernel, bytes)) return 1;
+  sort_rows_kernel<<<m, 1024, bytes, (cudaStream_t)stream>>>(sim_dev, n, n_pad, ld, ids_dev);
+  CUDA_OK(h, cudaGetLastError());
+  return 0;
+}
+
+int sgnn_train_step(SgnnHandle h, const SgnnGraphBatch* b, const int32_t* g1, const int32_t* g2,
+                    const float* target_sim, int32_t n_pairs, int32_t global_batch, double target_sum,
+                    double target_sqsum, float* loss_dev, void* stream) {
+  if (!h || !b || !g1 || !g2 || !target_sim) return fail(h, "sgnn_train_step: null argument");
+  if (n_pairs == 0) return 0;
+  if (global_batch < n_pairs) return fail(h, "sgnn_train_step: global_batch < n_pairs");
+  if (b->max_nodes > 32) return fail(h, "graphs with more than 32 nodes need the large-graph path (not built yet)");
+  const int v = b->max_nodes <= 16 ? 0 : 1;
+  const int wpb = h->train_wpb[v];
+  const int blocks = std::min((n_pairs + wpb - 1) / wpb, h->sm_count * 2);
+  cudaStream_t st = (cudaStream_t)stream;
+  float* loss = loss_dev ? loss_dev : h->d_loss;
+  const float invB = 1.0f / (float)global_batch;
+  if (v == 0)
+    train_pairs_kernel<16><<<blocks, wpb * 32, h->train_smem[0], st>>>(
+        h->M, to_dev(b), h->d_params, g1, g2, target_sim, n_pairs, invB, (float)target_sum, (float)target_sqsum,
+        h->d_grads, loss, nullptr);
+  else
+    train_pairs_kernel<32><<<blocks, wpb * 32, h->train_smem[1], st>>>(
+        h->M, to_dev(b), h->d_params, g1, g2, target_sim, n_pairs, invB, (float)target_sum, (float)target_sqsum,
+        h->d_grads, loss, nullptr);
+  CUDA_OK(h, cudaGetLastError());
+  return 0;
+}
+
+int sgnn_apply_adam(SgnnHandle h, float grad_scale, float* loss_dev, void* stream) {
+  if (!h) return 1;
+  h->adam_t += 1;
+  const SgnnConfig& c = h->cfg;
+  const double t = (double)h->adam_t;
+  const double lr_t = (double)c.learning_rate * std::sqrt(1.0 - std::pow((double)c.beta2, t)) /
+                      (1.0 - std::pow((double)c.beta1, t));
+  const int n = h->M.n_params;
+  const int blocks = std::min((n + 255) / 256, h->sm_count);
+  adam_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(n, h->d_params, h->d_grads, h->d_m, h->d_v, grad_scale,
+                                                       c.weight_decay, (float)lr_t, c.beta1, c.beta2, c.epsilon,
+                                                       loss_dev);
+  CUDA_OK(h, cudaGetLastError());
+  return 0;
+}
+
+int sgnn_zero_grads(SgnnHandle h, void* stream) {
+  if (!h) return 1;
+  CUDA_OK(h, cudaMemsetAsync(h->d_grads, 0, (size_t)h->M.n_params * sizeof(float), (cudaStream_t)stream));
+  return 0;
+}
+
+int sgnn_precision_at_k(SgnnHandle h, const float*, const float*, int32_t, int32_t, const int32_t*, int32_t,
+                        double*, void*) {
+  return fail(h, "sgnn_precision_at_k: not built yet");
+}
+
+int sgnn_kendall_tau(SgnnHandle h, const float*, const float*, int32_t, int32_t, int64_t*, double*, void*) {
+  return fail(h, "sgnn_kendall_tau: not built yet");
+}
+
+// ---- host-buffer entry points ---------------------------------------------------------
+static int upload_batch(SgnnHandle h, const SgnnGraphBatch* b, int slot, SgnnGraphBatch* dev) {
+  HostWs& w = h->ws;
+  if (b->n_graphs > w.cap_graphs || b->total_nodes > w.cap_nodes || b->nnz > w.cap_nnz)
+    return fail(h, "host workspace too small: call sgnn_reserve first");
+  cudaStream_t st = h->stream;
+  CUDA_OK(h, cudaMemcpyAsync(w.node_off[slot], b->node_off, (size_t)(b->n_graphs + 1) * 4, cudaMemcpyHostToDevice, st));
+  CUDA_OK(h, cudaMemcpyAsync(w.labels[slot], b->labels, (size_t)b->total_nodes * 4, cudaMemcpyHostToDevice, st));
+  CUDA_OK(h, cudaMemcpyAsync(w.rowptr[slot], b->rowptr, (size_t)(b->total_nodes + 1) * 4, cudaMemcpyHostToDevice, st));
+  CUDA_OK(h, cudaMemcpyAsync(w.col[slot], b->col, (size_t)b->nnz * 4, cudaMemcpyHostToDevice, st));
+  CUDA_OK(h, cudaMemcpyAsync(w.val[slot], b->val, (size_t)b->nnz * 4, cudaMemcpyHostToDevice, st));
+  *dev = *b;
+  dev->node_off = w.node_off[slot]; dev->labels = w.labels[slot]; dev->rowptr = w.rowptr[slot];
+  dev->col = w.col[slot]; dev->val = w.val[slot];
+  return 0;
+}
+
+int sgnn_forward_pairs_host(SgnnHandle h, const SgnnGraphBatch* b, const int32_t* g1, const int32_t* g2,
+                            int32_t n_pairs, float* raw_host, float* sim_host) {
+  if (!h || !b) return fail(h, "sgnn_forward_pairs_host: null argument");
+  CUDA_OK(h, cudaSetDevice(h->device));
+  HostWs& w = h->ws;
+  if (n_pairs > w.cap_pairs) return fail(h, "host workspace too small: call sgnn_reserve first");
+  SgnnGraphBatch d;
+  if (upload_batch(h, b, 0, &d)) return 1;
+  cudaStream_t st = h->stream;
+  CUDA_OK(h, cudaMemcpyAsync(w.g1, g1, (size_t)n_pairs * 4, cudaMemcpyHostToDevice, st));
+  CUDA_OK(h, cudaMemcpyAsync(w.g2, g2, (size_t)n_pairs * 4, cudaMemcpyHostToDevice, st));
+  if (sgnn_forward_pairs(h, &d, w.g1, w.g2, n_pairs, w.emb, w.raw, w.sim_pairs, st)) return 1;
+  if (raw_host) CUDA_OK(h, cudaMemcpyAsync(raw_host, w.raw, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, st));
+  if (sim_host) CUDA_OK(h, cudaMemcpyAsync(sim_host, w.sim_pairs, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, st));
+  CUDA_OK(h, cudaStreamSynchronize(st));
+  return 0;
+}
+
+int sgnn_rank_host(SgnnHandle h, const SgnnGraphBatch* q, const SgnnGraphBatch* db, int32_t k,
+                   int32_t* topk_ids_host, float* topk_vals_host, float* sim_host) {
+  if (!h || !q || !db) return fail(h, "sgnn_rank_host: null argument");
+  CUDA_OK(h, cudaSetDevice(h->device));
+  HostWs& w = h->ws;
+  const int64_t m = q->n_graphs, n = db->n_graphs;
+  if (m * n > w.cap_q * w.cap_db || m > w.cap_q || (int64_t)m * k > w.cap_topk)
+    return fail(h, "host workspace too small: call sgnn_reserve first");
+  SgnnGraphBatch dq, ddb;
+  if (upload_batch(h, q, 0, &dq) || upload_batch(h, db, 1, &ddb)) return 1;
+  cudaStream_t st = h->stream;
+  if (sgnn_embed_graphs(h, &dq, w.emb_q, st) || sgnn_embed_graphs(h, &ddb, w.emb_db, st)) return 1;
+  if (sgnn_score_all_pairs(h, w.emb_q, (int)m, w.emb_db, (int)n, w.sim, n, st)) return 1;
+  if (k > 0 && topk_ids_host) {
+    if (sgnn_topk(h, w.sim, (int)m, (int)n, n, k, w.topk_ids, w.topk_vals, st)) return 1;
+    CUDA_OK(h, cudaMemcpyAsync(topk_ids_host, w.topk_ids, (size_t)m * k * 4, cudaMemcpyDeviceToHost, st));
+    if (topk_vals_host)
+      CUDA_OK(h, cudaMemcpyAsync(topk_vals_host, w.topk_vals, (size_t)m * k * 4, cudaMemcpyDeviceToHost, st));
+  }
+  if (sim_host) CUDA_OK(h, cudaMemcpyAsync(sim_host, w.sim, (size_t)m * n * 4, cudaMemcpyDeviceToHost, st));
+  CUDA_OK(h, cudaStreamSynchronize(st));
+  return 0;
+}
+
+int sgnn_train_step_host(SgnnHandle h, const SgnnGraphBatch* b, const int32_t* g1, const int32_t* g2,
+                         const float* target_sim, int32_t n_pairs, float* loss_host) {
+  if (!h || !b) return fail(h, "sgnn_train_step_host: null argument");
+  CUDA_OK(h, cudaSetDevice(h->device));
+  HostWs& w = h->ws;
+  if (n_pairs > w.cap_pairs) return fail(h, "host workspace too small: call sgnn_reserve first");
+  double s1 = 0.0, s2 = 0.0;
+  for (int i = 0; i < n_pairs; ++i) { s1 += target_sim[i]; s2 += (double)target_sim[i] * target_sim[i]; }
+  SgnnGraphBatch d;
+  if (upload_batch(h, b, 0, &d)) return 1;
+  cudaStream_t st = h->stream;
+  CUDA_OK(h, cudaMemcpyAsync(w.g1, g1, (size_t)n_pairs * 4, cudaMemcpyHostToDevice, st));
+  CUDA_OK(h, cudaMemcpyAsync(w.g2, g2, (size_t)n_pairs * 4, cudaMemcpyHostToDevice, st));
+  CUDA_OK(h, cudaMemcpyAsync(w.target, target_sim, (size_t)n_pairs * 4, cudaMemcpyHostToDevice, st));
+  CUDA_OK(h, cudaMemsetAsync(h->d_loss, 0, 4 * sizeof(float), st));
+  if (sgnn_train_step(h, &d, w.g1, w.g2, w.target, n_pairs, n_pairs, s1, s2, h->d_loss, st)) return 1;
+  if (sgnn_apply_adam(h, 1.0f, h->d_loss, st)) return 1;
+  if (loss_host) CUDA_OK(h, cudaMemcpyAsync(loss_host, h->d_loss, 2 * sizeof(float), cudaMemcpyDeviceToHost, st));
+  CUDA_OK(h, cudaStreamSynchronize(st));
+  return 0;
+}
+
+}  // extern "C"

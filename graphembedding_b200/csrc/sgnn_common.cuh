@@ -1,0 +1,70 @@
+// Shared device/host definitions for libsgnn (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/sgnn.h"
+
+#define SGNN_WARP 32
+
+struct LayerDev {
+  int kind, din, dout, act, bias, w_off, b_off, aux;
+  float fparam;
+  int out_off;   // column offset of this layer's output inside a saved-activation row (train)
+  int wt_off;    // offset of the transposed copy inside the "aux weights" smem region
+};
+
+// Flattened description of one model (SgnnConfig after validation).  Passed by value as a
+// __grid_constant__ kernel parameter.
+struct ModelDev {
+  int n_node;                    // node-level layers (GCN / Dense) before the pooling layer
+  LayerDev L[SGNN_MAX_LAYERS];
+  int pool_kind, pool_aux, pool_w_off, pool_wt_off;
+  float pool_fparam;
+  int node_dim;                  // width of the last node-level output
+  int emb_dim;                   // flattened representation consumed by the pair layer
+  int pair_kind, D, K, w_off, v_off, u_off, b_off, pair_bias, pair_act, wp_off;
+  int final_act, ntn_mode, loss_mode;
+  float yeta;
+  int n_params, input_dim;
+  int ld;                        // row stride (floats) of per-warp activation buffers
+  int act_ld;                    // row stride of the saved-activation rows (train)
+  int aux_floats;                // size of the transposed/permuted weight region (train)
+};
+
+struct BatchDev {
+  int n_graphs;
+  const int32_t* node_off;
+  const int32_t* labels;
+  const int32_t* rowptr;
+  const int32_t* col;
+  const float* val;
+};
+
+__device__ __forceinline__ float sgnn_act(float x, int act, float yeta) {
+  switch (act) {
+    case SGNN_ACT_RELU: return fmaxf(x, 0.f);
+    case SGNN_ACT_SIGMOID: return 1.f / (1.f + expf(-x));
+    case SGNN_ACT_TANH: return tanhf(x);
+    case SGNN_ACT_SIM_KERNEL: return expf(-yeta * x * x);
+    default: return x;
+  }
+}
+
+// derivative of the activation expressed with its OUTPUT y (and input x for sim_kernel)
+__device__ __forceinline__ float sgnn_act_grad(float y, float x, int act, float yeta) {
+  switch (act) {
+    case SGNN_ACT_RELU: return y > 0.f ? 1.f : 0.f;
+    case SGNN_ACT_SIGMOID: return y * (1.f - y);
+    case SGNN_ACT_TANH: return 1.f - y * y;
+    case SGNN_ACT_SIM_KERNEL: return -2.f * yeta * x * y;
+    default: return 1.f;
+  }
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+static inline int round_up(int x, int m) { return (x + m - 1) / m * m; }

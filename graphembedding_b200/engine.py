@@ -1,0 +1,192 @@
+"""Thin object wrapper over the libsgnn handle.  PyTorch is used for device memory and
+streams only; every computation is a C-ABI call into the hand-written CUDA kernels."""
+import ctypes as C
+
+import numpy as np
+
+from . import native
+from .native import PackedBatch, check, lib, _ptr
+
+
+def _stream_ptr(stream):
+    if stream is None:
+        import torch
+        return torch.cuda.current_stream().cuda_stream
+    return stream if isinstance(stream, int) else stream.cuda_stream
+
+
+class SgnnEngine(object):
+    def __init__(self, layers, input_dim, **kw):
+        import torch
+        if not torch.cuda.is_available():
+            raise native.SgnnError('no CUDA device: the sm_100a path has no CPU fallback')
+        self.layers = layers
+        self.cfg = native.make_config(layers, input_dim, **kw)
+        self.device = torch.device('cuda', self.cfg.device)
+        h = C.c_void_p()
+        rc = lib().sgnn_create(C.byref(self.cfg), C.byref(h))
+        if rc != 0:
+            raise native.SgnnError(lib().sgnn_last_error(None).decode())
+        self.h = h
+        self.n_params = int(lib().sgnn_param_count(h))
+        self.emb_dim = int(lib().sgnn_embed_dim(h))
+        self.launches = 0  # kernels launched through this object (bench.py's gpu_launches)
+
+    def close(self):
+        if getattr(self, 'h', None):
+            lib().sgnn_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- parameters ----------------------------------------------------------------
+    def param_table(self):
+        n = lib().sgnn_param_table(self.h, None, 0)
+        arr = (native.ParamInfo * n)()
+        lib().sgnn_param_table(self.h, arr, n)
+        return [dict(layer=p.layer, name=p.name.decode(), shape=tuple(p.shape[:p.ndim]),
+                     offset=int(p.offset)) for p in arr]
+
+    def set_params(self, flat):
+        flat = np.ascontiguousarray(flat, np.float32)
+        assert flat.size == self.n_params
+        check(self.h, lib().sgnn_set_params(self.h, _ptr(flat)))
+
+    def get_params(self):
+        out = np.empty(self.n_params, np.float32)
+        check(self.h, lib().sgnn_get_params(self.h, _ptr(out)))
+        return out
+
+    def init_params(self, seed):
+        check(self.h, lib().sgnn_init_params(self.h, int(seed)))
+
+    def device_buffers(self):
+        """(params, grads, adam_m, adam_v) as torch views of the handle-owned buffers."""
+        import torch
+        ptrs = [C.c_void_p() for _ in range(4)]
+        check(self.h, lib().sgnn_device_buffers(self.h, *[C.byref(p) for p in ptrs]))
+        out = []
+        for p in ptrs:
+            class _Arr(object):
+                pass
+            a = _Arr()
+            a.__cuda_array_interface__ = {'shape': (self.n_params,), 'typestr': '<f4',
+                                          'data': (p.value, False), 'version': 2}
+            out.append(torch.as_tensor(a, device=self.device))
+        return out
+
+    def reserve(self, max_graphs=0, max_nodes=0, max_nnz=0, max_pairs=0, max_queries=0, max_db=0):
+        check(self.h, lib().sgnn_reserve(self.h, max_graphs, max_nodes, max_nnz, max_pairs,
+                                         max_queries, max_db))
+
+    # ---- device-resident compute -----------------------------------------------------
+    def embed(self, batch, out=None, stream=None):
+        import torch
+        if out is None:
+            out = torch.empty((batch.n_graphs, self.emb_dim), dtype=torch.float32, device=self.device)
+        s = batch.struct()
+        check(self.h, lib().sgnn_embed_graphs(self.h, C.byref(s), _ptr(out), _stream_ptr(stream)))
+        self.launches += 1
+        return out
+
+    def score_pairs(self, emb, g1, g2, stream=None):
+        import torch
+        n = int(g1.numel())
+        raw = torch.empty(n, dtype=torch.float32, device=self.device)
+        sim = torch.empty(n, dtype=torch.float32, device=self.device)
+        check(self.h, lib().sgnn_score_pairs(self.h, _ptr(emb), _ptr(g1), _ptr(g2), n, _ptr(raw),
+                                             _ptr(sim), _stream_ptr(stream)))
+        self.launches += 1
+        return raw, sim
+
+    def forward_pairs(self, batch, g1, g2, stream=None):
+        emb = self.embed(batch, stream=stream)
+        return self.score_pairs(emb, g1, g2, stream=stream)
+
+    def score_all_pairs(self, emb_q, emb_db, out=None, stream=None):
+        import torch
+        m, n = emb_q.shape[0], emb_db.shape[0]
+        if out is None:
+            out = torch.empty((m, n), dtype=torch.float32, device=self.device)
+        check(self.h, lib().sgnn_score_all_pairs(self.h, _ptr(emb_q), m, _ptr(emb_db), n, _ptr(out),
+                                                 out.stride(0), _stream_ptr(stream)))
+        self.launches += 2
+        return out
+
+    def topk(self, sim, k, stream=None):
+        import torch
+        m, n = sim.shape
+        ids = torch.empty((m, k), dtype=torch.int32, device=self.device)
+        vals = torch.empty((m, k), dtype=torch.float32, device=self.device)
+        check(self.h, lib().sgnn_topk(self.h, _ptr(sim), m, n, sim.stride(0), k, _ptr(ids), _ptr(vals),
+                                      _stream_ptr(stream)))
+        self.launches += 1
+        return ids, vals
+
+    def sort_rows(self, sim, stream=None):
+        import torch
+        m, n = sim.shape
+        ids = torch.empty((m, n), dtype=torch.int32, device=self.device)
+        check(self.h, lib().sgnn_sort_rows(self.h, _ptr(sim), m, n, sim.stride(0), _ptr(ids),
+                                           _stream_ptr(stream)))
+        self.launches += 1
+        return ids
+
+    def train_step(self, batch, g1, g2, target_sim, global_batch=None, target_sum=None,
+                   target_sqsum=None, loss=None, stream=None):
+        """Adds the MSE-part gradient of these pairs into the grad buffer; loss[0] += mse part."""
+        import torch
+        n = int(g1.numel())
+        if global_batch is None:
+            global_batch = n
+        if target_sum is None:
+            t = target_sim.double()
+            target_sum, target_sqsum = float(t.sum()), float((t * t).sum())
+        if loss is None:
+            loss = torch.zeros(4, dtype=torch.float32, device=self.device)
+        s = batch.struct()
+        check(self.h, lib().sgnn_train_step(self.h, C.byref(s), _ptr(g1), _ptr(g2), _ptr(target_sim), n,
+                                            int(global_batch), float(target_sum), float(target_sqsum),
+                                            _ptr(loss), _stream_ptr(stream)))
+        self.launches += 1
+        return loss
+
+    def apply_adam(self, grad_scale=1.0, loss=None, stream=None):
+        check(self.h, lib().sgnn_apply_adam(self.h, float(grad_scale), _ptr(loss), _stream_ptr(stream)))
+        self.launches += 1
+
+    def zero_grads(self, stream=None):
+        check(self.h, lib().sgnn_zero_grads(self.h, _stream_ptr(stream)))
+
+    # ---- host-buffer entry points ----------------------------------------------------
+    def forward_pairs_host(self, batch, g1, g2, raw=None, sim=None):
+        n = len(g1)
+        raw = np.empty(n, np.float32) if raw is None else raw
+        sim = np.empty(n, np.float32) if sim is None else sim
+        s = batch.struct()
+        check(self.h, lib().sgnn_forward_pairs_host(self.h, C.byref(s), _ptr(g1), _ptr(g2), n,
+                                                    _ptr(raw), _ptr(sim)))
+        self.launches += 2
+        return raw, sim
+
+    def rank_host(self, queries, db, k, ids=None, vals=None, sim=None):
+        m = queries.n_graphs
+        ids = np.empty((m, k), np.int32) if ids is None else ids
+        vals = np.empty((m, k), np.float32) if vals is None else vals
+        sq, sd = queries.struct(), db.struct()
+        check(self.h, lib().sgnn_rank_host(self.h, C.byref(sq), C.byref(sd), k, _ptr(ids), _ptr(vals),
+                                           _ptr(sim)))
+        self.launches += 5
+        return ids, vals
+
+    def train_step_host(self, batch, g1, g2, target_sim, loss=None):
+        loss = np.zeros(2, np.float32) if loss is None else loss
+        s = batch.struct()
+        check(self.h, lib().sgnn_train_step_host(self.h, C.byref(s), _ptr(g1), _ptr(g2), _ptr(target_sim),
+                                                 len(g1), _ptr(loss)))
+        self.launches += 2
+        return loss

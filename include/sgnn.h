@@ -1,0 +1,197 @@
+/*
+ * sgnn.h -- C ABI of libsgnn.so: the B200 (sm_100a) Siamese graph-pair similarity path.
+ *
+ * The reference (kangzf/GraphEmbedding, pure Python/TensorFlow-1) has no FFI or operator
+ * registry; the seams this library sits behind are Python-level.
+ * Each entry point cites the reference code it replaces (paths relative to the reference
+ * root).  Conventions:
+ *   - every call returns 0 on success, non-zero on error; sgnn_last_error() gives the text
+ *     (no exception crosses the ABI; Python raises RuntimeError from it, like
+ *     model/Siamese/layers_factory.py:33 / train.py:88 do);
+ *   - plain pointers and sizes only, no torch / numpy types;
+ *   - a handle is bound to one GPU; not thread-safe per handle, thread-safe across handles;
+ *   - "device" pointers are CUDA device pointers owned by the caller; `stream` is a
+ *     cudaStream_t passed as void* (NULL = legacy default stream);
+ *   - all device memory the library itself needs is allocated in sgnn_create / sgnn_reserve,
+ *     never inside a compute call.
+ */
+#ifndef SGNN_H_
+#define SGNN_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SGNN_MAX_LAYERS 12
+#define SGNN_ABI_VERSION 1
+
+typedef struct SgnnHandle_t* SgnnHandle;
+
+/* layer kinds: model/Siamese/layers_factory.py:20-33 (+ Attention, layers.py:143-160) */
+enum {
+  SGNN_LAYER_GCN = 0,       /* layers.py:52-118  */
+  SGNN_LAYER_DENSE = 1,     /* layers.py:163-205 */
+  SGNN_LAYER_PADDING = 2,   /* layers.py:208-227 */
+  SGNN_LAYER_AVERAGE = 3,   /* layers.py:121-140 */
+  SGNN_LAYER_ATTENTION = 4, /* layers.py:143-160 */
+  SGNN_LAYER_NTN = 5,       /* layers.py:255-310 */
+  SGNN_LAYER_DOT = 6        /* layers.py:230-252 */
+};
+
+/* activations: layers_factory.py:101-114 */
+enum { SGNN_ACT_RELU = 0, SGNN_ACT_IDENTITY = 1, SGNN_ACT_SIGMOID = 2, SGNN_ACT_TANH = 3,
+       SGNN_ACT_SIM_KERNEL = 4 /* exp(-yeta x^2), src/similarity.py:58-60 */ };
+
+enum { SGNN_NTN_REFERENCE = 0 /* (sum U)(sum act(m)), layers.py:305-308 */, SGNN_NTN_PAPER = 1 };
+enum { SGNN_LOSS_REFERENCE = 0 /* (B,1)-(B,) broadcast, model_mse.py:145-151 */, SGNN_LOSS_PAIRED = 1 };
+enum { SGNN_PREC_FP32 = 0, SGNN_PREC_BF16X3 = 1, SGNN_PREC_BF16 = 2 };
+
+typedef struct {
+  int32_t kind;          /* SGNN_LAYER_* */
+  int32_t input_dim;     /* GCN/Dense/Attention/NTN */
+  int32_t output_dim;    /* GCN/Dense */
+  int32_t act;           /* GCN/Dense act, NTN inneract */
+  int32_t bias;          /* 0/1 */
+  int32_t dropout;       /* 0/1: layer spec `dropout=True` (layers.py:45-49) */
+  int32_t sparse_inputs; /* GCN */
+  int32_t aux;           /* Padding: max_in_dims; NTN: feature_map_dim */
+  float fparam;          /* Padding: padding_value */
+} SgnnLayerDesc;
+
+/* model/Siamese/config.py flags that reach the device path */
+typedef struct {
+  int32_t abi_version;   /* SGNN_ABI_VERSION */
+  int32_t num_layers;
+  SgnnLayerDesc layers[SGNN_MAX_LAYERS];
+  int32_t input_dim;     /* one-hot width, graphs.py:113-114 */
+  int32_t final_act;     /* config.py:82-83 */
+  float yeta;            /* config.py:81 */
+  int32_t ntn_mode;      /* SGNN_NTN_* */
+  int32_t loss_mode;     /* SGNN_LOSS_* */
+  float weight_decay;    /* config.py:104-105 */
+  float learning_rate;   /* config.py:107 */
+  float beta1, beta2, epsilon; /* tf.train.AdamOptimizer defaults, models.py:28-29 */
+  float dropout;         /* config.py:103 (0 for parity runs) */
+  int32_t precision;     /* SGNN_PREC_* for the all-pairs scorer */
+  int32_t device;        /* CUDA ordinal */
+} SgnnConfig;
+
+typedef struct {
+  int32_t layer;         /* index into SgnnConfig.layers */
+  char name[16];         /* weights_0 | bias | weights | weights_W | weights_V | weights_U */
+  int32_t ndim;
+  int32_t shape[3];
+  int64_t offset;        /* in floats, into the flat parameter blob */
+} SgnnParamInfo;
+
+/* A batch of graphs as one block-diagonal CSR (what graphs.py:34-95 produces per graph,
+ * concatenated).  All arrays live where the call says (host for *_host calls, device
+ * otherwise).  Algorithmic bytes per graph: 4N + 4(N+1) + 8 nnz. */
+typedef struct {
+  int32_t n_graphs;
+  int32_t total_nodes;
+  int64_t nnz;
+  int32_t max_nodes;        /* largest N in the batch */
+  const int32_t* node_off;  /* [n_graphs+1] */
+  const int32_t* labels;    /* [total_nodes] one-hot column of each node (graphs.py:108-111) */
+  const int32_t* rowptr;    /* [total_nodes+1] offsets into col/val */
+  const int32_t* col;       /* [nnz] node index local to its graph */
+  const float* val;         /* [nnz] A_hat = D^-1/2 (A+I) D^-1/2 (graphs.py:64-76) */
+} SgnnGraphBatch;
+
+/* ---- host-side packer (no GPU needed) ------------------------------------------------
+ * Replaces ModelGraph._preprocess_adj/_normalize_adj/_sparse_to_tuple (graphs.py:64-95)
+ * for a whole list of graphs at once.  edges are undirected pairs of local node indices,
+ * edge_off[g]..edge_off[g+1] index pairs of graph g.  Outputs are (row,col)-sorted CSR
+ * with float32 values bit-identical to float32(reference float64 value).
+ * col/val must have room for total_nodes + 2*num_edges entries. */
+int sgnn_pack_graphs(int32_t n_graphs, const int32_t* node_counts, const int64_t* edge_off,
+                     const int32_t* edges, int32_t* node_off, int32_t* rowptr, int32_t* col,
+                     float* val, int64_t* nnz_out, int32_t* max_nodes_out);
+
+/* ---- lifecycle ----------------------------------------------------------------------- */
+/* create_model + Model.__init__ (models_factory.py:5-11, models.py:7-37). */
+int sgnn_create(const SgnnConfig* cfg, SgnnHandle* out);
+int sgnn_destroy(SgnnHandle h);
+/* h may be NULL: returns the last error of a failed sgnn_create on this thread. */
+const char* sgnn_last_error(SgnnHandle h);
+int sgnn_abi_version(void);
+
+/* layer.vars (layers.py:29, 70-73, 174-177, 269-277) as one flat fp32 blob */
+int64_t sgnn_param_count(SgnnHandle h);
+int sgnn_param_table(SgnnHandle h, SgnnParamInfo* out, int32_t capacity); /* returns #entries or <0 */
+int sgnn_embed_dim(SgnnHandle h);
+int sgnn_set_params(SgnnHandle h, const float* host_params);   /* also resets Adam state */
+int sgnn_get_params(SgnnHandle h, float* host_params);
+/* glorot / zeros (inits.py:11-21), counter-based RNG seeded by `seed` */
+int sgnn_init_params(SgnnHandle h, uint64_t seed);
+/* device pointers of the handle-owned flat buffers (params, grads, adam m, adam v), each
+ * sgnn_param_count floats; for torch.distributed all-reduce on grads. */
+int sgnn_device_buffers(SgnnHandle h, float** params, float** grads, float** adam_m, float** adam_v);
+/* size the internal workspaces used by the *_host entry points */
+int sgnn_reserve(SgnnHandle h, int64_t max_graphs, int64_t max_nodes, int64_t max_nnz,
+                 int64_t max_pairs, int64_t max_queries, int64_t max_db);
+
+/* ---- device-resident compute --------------------------------------------------------- */
+/* GCN/Dense/pooling stack of every graph in the batch -> emb[n_graphs][embed_dim]
+ * (layers.py:91-118, 136-140, 154-160, 192-205, 223-227). */
+int sgnn_embed_graphs(SgnnHandle h, const SgnnGraphBatch* batch_dev, float* emb_dev, void* stream);
+/* NTN/Dot + final_act on listed pairs (layers.py:249-252, 282-310; model_mse.py:39-45).
+ * raw_dev / sim_dev may be NULL. */
+int sgnn_score_pairs(SgnnHandle h, const float* emb_dev, const int32_t* g1_dev, const int32_t* g2_dev,
+                     int32_t n_pairs, float* raw_dev, float* sim_dev, void* stream);
+/* one sess.run of test_output / train_val_outputs (train.py:77-102) for n_pairs pairs */
+int sgnn_forward_pairs(SgnnHandle h, const SgnnGraphBatch* batch_dev, const int32_t* g1_dev,
+                       const int32_t* g2_dev, int32_t n_pairs, float* emb_ws_dev, float* raw_dev,
+                       float* sim_dev, void* stream);
+/* the m x n loop of test() (train.py:57-61) as one call: sim[i*ld + j] for every
+ * (query i, database j). */
+int sgnn_score_all_pairs(SgnnHandle h, const float* emb_q_dev, int32_t m, const float* emb_db_dev,
+                         int32_t n, float* sim_dev, int64_t ld, void* stream);
+/* descending top-k per row with the reference's tie order (results.py:221-224: stable
+ * ascending mergesort reversed => equal scores come out higher index first). */
+int sgnn_topk(SgnnHandle h, const float* sim_dev, int32_t m, int32_t n, int64_t ld, int32_t k,
+              int32_t* ids_dev, float* vals_dev, void* stream);
+/* full descending ranking per row (sort_id_mat, results.py:221-224) */
+int sgnn_sort_rows(SgnnHandle h, const float* sim_dev, int32_t m, int32_t n, int64_t ld,
+                   int32_t* ids_dev, void* stream);
+
+/* loss + gradient of the MSE part for the listed pairs, ADDED into the handle's grad
+ * buffer; loss_dev[0] += mse part (models.py:67-88, model_mse.py:145-151).  targets are
+ * similarities exp(-yeta d^2).  global_batch / target_sum / target_sqsum describe the whole
+ * (all-rank) batch, needed by the reference-mode loss (F6). */
+int sgnn_train_step(SgnnHandle h, const SgnnGraphBatch* batch_dev, const int32_t* g1_dev,
+                    const int32_t* g2_dev, const float* target_sim_dev, int32_t n_pairs,
+                    int32_t global_batch, double target_sum, double target_sqsum, float* loss_dev,
+                    void* stream);
+/* weight-decay gradient + TF-1 Adam update on every variable (models.py:28-29, 67-74),
+ * then zeroes the grad buffer.  grad_scale multiplies the summed gradient first.
+ * loss_dev[1] = weight-decay loss term if loss_dev != NULL. */
+int sgnn_apply_adam(SgnnHandle h, float grad_scale, float* loss_dev, void* stream);
+int sgnn_zero_grads(SgnnHandle h, void* stream);
+
+/* ranking metrics on device (src/metrics.py:14-82, results.py:51-109; Kendall tau-b is
+ * build-defined, pinned to scipy.stats.kendalltau).  true_sim/pred_sim are m x n. */
+int sgnn_precision_at_k(SgnnHandle h, const float* true_sim_dev, const float* pred_sim_dev, int32_t m,
+                        int32_t n, const int32_t* ks_dev, int32_t n_ks, double* prec_dev, void* stream);
+int sgnn_kendall_tau(SgnnHandle h, const float* true_sim_dev, const float* pred_sim_dev, int32_t m,
+                     int32_t n, int64_t* counts_dev /* [m][5] */, double* tau_dev /* [m] */, void* stream);
+
+/* ---- host-buffer entry points (what a Python caller with numpy arrays uses; H2D / D2H
+ * inside).  These are the `e2e` path of bench.py. ---------------------------------------- */
+int sgnn_forward_pairs_host(SgnnHandle h, const SgnnGraphBatch* batch_host, const int32_t* g1,
+                            const int32_t* g2, int32_t n_pairs, float* raw_host, float* sim_host);
+/* embeds queries + database, scores all pairs, returns top-k ids/values per query; the
+ * full m x n matrix is copied back only if sim_host != NULL. */
+int sgnn_rank_host(SgnnHandle h, const SgnnGraphBatch* queries_host, const SgnnGraphBatch* db_host,
+                   int32_t k, int32_t* topk_ids_host, float* topk_vals_host, float* sim_host);
+/* one optimizer step: forward + backward + Adam; returns [mse_part, wd_part] */
+int sgnn_train_step_host(SgnnHandle h, const SgnnGraphBatch* batch_host, const int32_t* g1,
+                         const int32_t* g2, const float* target_sim, int32_t n_pairs, float* loss_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SGNN_H_ */

@@ -1,0 +1,178 @@
+"""GPU parity tests: CUDA path (through the C ABI) vs the CPU oracle on the same seeded inputs.
+
+Tolerances: fp32 device math vs the fp64 oracle, 1e-4 relative (BASELINE.json north_star);
+integer / index outputs bit-exact."""
+import numpy as np
+import pytest
+
+from util import CONFIGS, O, corpus, encoder_for, oracle_graphs, rel_err
+
+torch = pytest.importorskip('torch')
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-4
+
+
+def _setup(cfg_name, num_graphs, n_hi=10, seed=3, **kw):
+    from graphembedding_b200.engine import SgnnEngine
+    from graphembedding_b200.graphs import pack_nx_graphs
+    from graphembedding_b200.layers_factory import parse_layers
+    gs = corpus(num_graphs, 2, n_hi, seed)
+    enc = encoder_for(gs)
+    layers = parse_layers(CONFIGS[cfg_name], enc.input_dim())
+    eng = SgnnEngine(layers, enc.input_dim(), **kw)
+    flat = O.init_params(O.parse_layer_specs(CONFIGS[cfg_name], enc.input_dim()), seed=11)
+    # non-zero biases so that bias paths are exercised
+    rng = np.random.default_rng(5)
+    for li, name, shape in O.param_table(layers):
+        pass
+    flat = flat + (rng.standard_normal(flat.shape) * 0.01).astype(np.float32)
+    eng.set_params(flat)
+    batch = pack_nx_graphs(gs, enc)
+    return eng, layers, flat, gs, enc, batch
+
+
+@pytest.mark.parametrize('cfg', ['default', 'avg_ntn', 'att3', 'dense_dot'])
+def test_embed_matches_oracle(cfg):
+    eng, layers, flat, gs, enc, batch = _setup(cfg, 40)
+    emb = eng.embed(batch.to(eng.device)).cpu().numpy()
+    P = O.unflatten(layers, flat, torch.float64)
+    og = oracle_graphs(gs, enc)
+    for i, g in enumerate(og):
+        ref = O.graph_forward(layers, P, g, enc.input_dim(), torch.float64).numpy()
+        assert emb[i].shape == ref.shape
+        assert np.max(np.abs(emb[i] - ref)) <= RTOL * max(1.0, np.max(np.abs(ref))), (cfg, i)
+
+
+@pytest.mark.parametrize('cfg', ['default', 'avg_ntn', 'att3', 'dense_dot'])
+@pytest.mark.parametrize('ntn_mode', ['reference', 'paper'])
+def test_forward_pairs_matches_oracle(cfg, ntn_mode):
+    eng, layers, flat, gs, enc, batch = _setup(cfg, 64, ntn_mode=ntn_mode)
+    B = 32
+    g1 = torch.arange(0, B, dtype=torch.int32, device=eng.device)
+    g2 = torch.arange(B, 2 * B, dtype=torch.int32, device=eng.device)  # arm i <-> arm i+B (model_mse.py:117-126)
+    raw, sim = eng.forward_pairs(batch.to(eng.device), g1, g2)
+    P = O.unflatten(layers, flat, torch.float64)
+    og = oracle_graphs(gs, enc)
+    ref_raw = O.forward_pairs(layers, P, og[:B], og[B:2 * B], enc.input_dim(), torch.float64, ntn_mode).numpy()
+    ref_sim = np.exp(-0.6 * ref_raw ** 2)
+    scale = max(1.0, np.max(np.abs(ref_raw)))
+    assert np.max(np.abs(raw.cpu().numpy() - ref_raw)) <= RTOL * scale
+    assert rel_err(sim.cpu().numpy(), ref_sim, floor=1e-3) <= 5 * RTOL
+
+
+def test_aids10k_shaped_graphs_up_to_30_nodes():
+    eng, layers, flat, gs, enc, batch = _setup('avg_ntn', 48, n_hi=30)
+    assert batch.max_nodes > 16
+    B = 24
+    g1 = torch.arange(0, B, dtype=torch.int32, device=eng.device)
+    g2 = torch.arange(B, 2 * B, dtype=torch.int32, device=eng.device)
+    raw, _ = eng.forward_pairs(batch.to(eng.device), g1, g2)
+    P = O.unflatten(layers, flat, torch.float64)
+    og = oracle_graphs(gs, enc)
+    ref = O.forward_pairs(layers, P, og[:B], og[B:2 * B], enc.input_dim(), torch.float64).numpy()
+    assert np.max(np.abs(raw.cpu().numpy() - ref)) <= RTOL * max(1.0, np.max(np.abs(ref)))
+
+
+@pytest.mark.parametrize('cfg', ['default', 'avg_ntn', 'dense_dot'])
+def test_all_pairs_equals_pairwise_and_oracle(cfg):
+    eng, layers, flat, gs, enc, batch = _setup(cfg, 150)
+    m, n = 21, 129
+    eng.reserve(max_queries=m, max_db=n)
+    dev = batch.to(eng.device)
+    emb = eng.embed(dev)
+    sim = eng.score_all_pairs(emb[:m].contiguous(), emb[m:m + n].contiguous())
+    # against the pair-list kernel
+    qi, dj = np.meshgrid(np.arange(m), np.arange(m, m + n), indexing='ij')
+    g1 = torch.as_tensor(qi.ravel().astype(np.int32), device=eng.device)
+    g2 = torch.as_tensor(dj.ravel().astype(np.int32), device=eng.device)
+    _, sim_pairs = eng.score_pairs(emb, g1, g2)
+    a, b = sim.cpu().numpy(), sim_pairs.cpu().numpy().reshape(m, n)
+    assert rel_err(a, b, floor=1e-3) <= 5 * RTOL
+    # against the oracle on a sample of cells
+    P = O.unflatten(layers, flat, torch.float64)
+    og = oracle_graphs(gs, enc)
+    rng = np.random.default_rng(0)
+    for _ in range(40):
+        i, j = int(rng.integers(m)), int(rng.integers(n))
+        x1 = O.graph_forward(layers, P, og[i], enc.input_dim())
+        x2 = O.graph_forward(layers, P, og[m + j], enc.input_dim())
+        r = float(O.pair_forward(layers, P, x1, x2))
+        ref = np.exp(-0.6 * r * r)
+        assert abs(a[i, j] - ref) <= 5 * RTOL * max(ref, 1e-3)
+
+
+def test_topk_and_sort_tie_order_is_reference_order():
+    eng, *_ = _setup('default', 8)
+    rng = np.random.default_rng(1)
+    m, n, k = 37, 1000, 10
+    # heavy ties: few distinct values
+    sim = rng.integers(0, 12, size=(m, n)).astype(np.float32) / 11.0
+    sim[3, :] = 0.5  # a fully tied row
+    d = torch.as_tensor(sim, device=eng.device)
+    ids, vals = eng.topk(d, k)
+    ref = O.sort_id_mat_sim(sim)  # results.py:221-224
+    assert np.array_equal(ids.cpu().numpy(), ref[:, :k])
+    assert np.array_equal(vals.cpu().numpy(), np.take_along_axis(sim, ref[:, :k], 1))
+    full = eng.sort_rows(d).cpu().numpy()
+    assert np.array_equal(full, ref)
+
+
+@pytest.mark.parametrize('cfg', ['default', 'avg_ntn', 'att3', 'dense_dot'])
+@pytest.mark.parametrize('modes', [('reference', 'reference'), ('paired', 'paper')])
+def test_loss_and_gradients_match_fp64_autograd(cfg, modes):
+    loss_mode, ntn_mode = modes
+    eng, layers, flat, gs, enc, batch = _setup(cfg, 40, loss_mode=loss_mode, ntn_mode=ntn_mode)
+    B = 20
+    rng = np.random.default_rng(2)
+    tgt = rng.uniform(0.05, 1.0, size=B).astype(np.float32)
+    g1 = torch.arange(0, B, dtype=torch.int32, device=eng.device)
+    g2 = torch.arange(B, 2 * B, dtype=torch.int32, device=eng.device)
+    loss = eng.train_step(batch.to(eng.device), g1, g2, torch.as_tensor(tgt, device=eng.device))
+    grads = eng.device_buffers()[1].cpu().numpy().astype(np.float64)
+    og = oracle_graphs(gs, enc)
+    l, mse, pred, ref_g, raw = O.loss_and_grads(layers, flat, og[:B], og[B:2 * B], tgt, enc.input_dim(),
+                                                weight_decay=0.0, loss_mode=loss_mode, ntn_mode=ntn_mode)
+    assert abs(float(loss[0]) - mse) <= RTOL * max(abs(mse), 1e-3)
+    gscale = np.max(np.abs(ref_g))
+    assert gscale > 0
+    assert np.max(np.abs(grads - ref_g)) <= 2e-4 * gscale, (cfg, modes)
+
+
+def test_adam_steps_match_oracle_restatement():
+    eng, layers, flat, gs, enc, batch = _setup('default', 40)
+    B = 20
+    rng = np.random.default_rng(4)
+    tgt = rng.uniform(0.05, 1.0, size=B).astype(np.float32)
+    dev = batch.to(eng.device)
+    g1 = torch.arange(0, B, dtype=torch.int32, device=eng.device)
+    g2 = torch.arange(B, 2 * B, dtype=torch.int32, device=eng.device)
+    t = torch.as_tensor(tgt, device=eng.device)
+    og = oracle_graphs(gs, enc)
+    adam = O.TFAdam(flat.size, lr=0.01)
+    p = flat.astype(np.float64)
+    for step in range(5):
+        loss = eng.train_step(dev, g1, g2, t)
+        eng.apply_adam(1.0, loss)
+        l, mse, _, g, _ = O.loss_and_grads(layers, p, og[:B], og[B:2 * B], tgt, enc.input_dim())
+        assert abs(float(loss[0] + loss[1]) - l) <= 2e-4 * abs(l)
+        p = adam.step(p, g)
+        got = eng.get_params().astype(np.float64)
+        # Adam normalises the step to ~lr, so compare against lr-scaled tolerance
+        assert np.max(np.abs(got - p)) <= 2e-3 * 0.01 * (step + 1) + 1e-6, step
+
+
+def test_host_entry_points_round_trip():
+    eng, layers, flat, gs, enc, batch = _setup('default', 96)
+    eng.reserve(max_graphs=128, max_nodes=2048, max_nnz=8192, max_pairs=64, max_queries=32, max_db=64)
+    B = 48
+    g1 = np.arange(0, B, dtype=np.int32)
+    g2 = np.arange(B, 2 * B, dtype=np.int32)
+    raw_h, sim_h = eng.forward_pairs_host(batch, g1, g2)
+    raw_d, sim_d = eng.forward_pairs(batch.to(eng.device), torch.as_tensor(g1, device=eng.device),
+                                     torch.as_tensor(g2, device=eng.device))
+    assert np.array_equal(raw_h, raw_d.cpu().numpy())
+    q, db = batch.select(np.arange(0, 32)), batch.select(np.arange(32, 96))
+    sim = np.empty((32, 64), np.float32)
+    ids, vals = eng.rank_host(q, db, 10, sim=sim)
+    assert np.array_equal(ids, O.sort_id_mat_sim(sim)[:, :10])

@@ -1,0 +1,396 @@
+#!/usr/bin/env python3
+"""bench.py -- graph-pairs/s of the Siamese graph-pair similarity hot path on B200.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --steps K --warmup W    # CPU baseline arm (oracle port)
+
+Headline workload (config.workload): BASELINE.json configs[3] -- all-pairs similarity ranking,
+1 000 query x 10 000 database AIDS-shaped graphs (<= 10 nodes, 29 labels), the reference's default
+flag model (config.py:44-66), top-10 per query.  One "step" = embed every query and database
+graph, score every (query, database) pair, select the top-10 ids per query -- what the reference's
+test() does with m x n sess.run calls (train.py:57-61).  Nothing is cached across steps.
+With N GPUs every rank holds its own 10 000-graph database shard (weak scaling), queries are
+replicated, and the per-shard top-10 are all-gathered and merged.
+
+Also measured and reported inside the same JSON line: "train" (configs[2]: data-parallel training,
+128 pairs/GPU/step on AIDS10knef-shaped graphs, fwd+bwd+allreduce+Adam).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+DEFAULT_LAYERS = [
+    'GraphConvolution:output_dim=32,act=relu,dropout=True,bias=True,sparse_inputs=True',
+    'GraphConvolution:input_dim=32,output_dim=16,act=identity,dropout=True,bias=True,sparse_inputs=False',
+    'Dense:input_dim=16,output_dim=1,dropout=True,act=relu,bias=True',
+    'Padding:max_in_dims=10,padding_value=0',
+    'NTN:input_dim=10,feature_map_dim=10,inneract=relu,dropout=True,bias=True',
+]
+TRAIN_LAYERS = DEFAULT_LAYERS[:2] + [  # tuning.py:74-93 (Average pooling: AIDS10k graphs exceed Padding's 10)
+    'Average', 'NTN:input_dim=16,feature_map_dim=10,inneract=relu,dropout=True,bias=True']
+M_QUERIES, N_DB, TOPK = 1000, 10000, 10
+TRAIN_BATCH, TRAIN_GRAPHS = 128, 4096
+
+
+def peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return d.get('hbm_gbs', 6650.0), 'measured (MEASURED_PEAKS.json)'
+    return 6650.0, 'fallback (B200_PROFILING.md)'
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks + throttle reasons while the timed region runs."""
+    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
+                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(',')])
+
+    def stop(self):
+        if not self.proc:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace('.', '').isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace('.', '').isdigit()]
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i] == 'Active'})
+        return {'sm_mhz': float(np.median(sm)) if sm else None, 'sm_max_mhz': max(mx) if mx else None,
+                'reasons': reasons, 'samples': len(sm)}
+
+
+def make_rank_data(rank):
+    from graphembedding_b200 import data as D
+    from graphembedding_b200.graphs import NodeFeatureOneHotEncoder, pack_nx_graphs
+    enc = NodeFeatureOneHotEncoder([], 'type', feat_idx_dic={l: i for i, l in enumerate(D.AIDS_LABELS)})
+    q = pack_nx_graphs(D.synthetic_corpus(M_QUERIES, 2, 10, seed=124, gid_base=10 ** 6), enc)
+    db = pack_nx_graphs(D.synthetic_corpus(N_DB, 2, 10, seed=123 + 1000 * rank, gid_base=rank * N_DB), enc)
+    return enc, q, db
+
+
+def make_train_data(rank, world, n_batches=8):
+    """AIDS10knef-shaped graphs (<= 30 nodes) and n_batches mini-batches of TRAIN_BATCH pairs with
+    proxy-GED targets exp(-yeta nGED^2); rank r takes pairs r, r+world, ... of the global stream."""
+    from graphembedding_b200 import data as D
+    from graphembedding_b200.dist_calculator import proxy_ged
+    from graphembedding_b200.graphs import NodeFeatureOneHotEncoder, pack_nx_graphs
+    enc = NodeFeatureOneHotEncoder([], 'type', feat_idx_dic={l: i for i, l in enumerate(D.AIDS_LABELS)})
+    gs = D.synthetic_corpus(TRAIN_GRAPHS, 2, 30, seed=223, size_skew=False)
+    batch = pack_nx_graphs(gs, enc)
+    rng = np.random.default_rng(99)
+    out = []
+    for _ in range(n_batches):
+        glob = rng.integers(0, TRAIN_GRAPHS, size=(TRAIN_BATCH * world, 2))
+        d = np.array([2.0 * proxy_ged(gs[a], gs[b]) / (gs[a].number_of_nodes() + gs[b].number_of_nodes())
+                      for a, b in glob])
+        t = np.exp(-0.6 * d * d).astype(np.float32)
+        mine = slice(rank, None, world)
+        out.append((glob[mine, 0].astype(np.int32), glob[mine, 1].astype(np.int32), t[mine],
+                    float(t.astype(np.float64).sum()), float((t.astype(np.float64) ** 2).sum())))
+    return enc, batch, out
+
+
+def cpu_rank_baseline(layers_spec, q, db, seconds_budget=15.0, threads=None):
+    """Oracle port on the host cores: batched torch-CPU all-pairs ranking step on a bounded
+    sample of queries against the full database (embedding of the sampled queries + all database
+    graphs + scoring + top-k).  Returns (pairs/s, cores, sample text)."""
+    import torch
+    from oracle import batched as OB
+    from oracle import siamese_oracle as O
+    threads = threads or os.cpu_count()
+    torch.set_num_threads(threads)
+    layers = O.parse_layer_specs(layers_spec, 29)
+    P = O.unflatten(layers, O.init_params(layers, 123), torch.float32)
+    pq, pd = OB.pad_from_packed(q), OB.pad_from_packed(db)
+    t0 = time.perf_counter()
+    reps = 0
+    while True:
+        xq = OB.embed(layers, P, *pq)
+        xd = OB.embed(layers, P, *pd)
+        for c in range(0, q.n_graphs, 100):           # chunked so that the [Q,K,M] tensor stays in cache
+            sim = OB.score_all_pairs(layers, P, xq[c:c + 100], xd)
+            torch.topk(sim, TOPK, dim=1)
+        reps += 1
+        if time.perf_counter() - t0 > seconds_budget or reps >= 50:
+            break
+    dt = time.perf_counter() - t0
+    return q.n_graphs * db.n_graphs * reps / dt, threads, \
+        '{} full steps of {} queries x {} database graphs (embed + score + top-{}), batched torch-CPU fp32, ' \
+        'inputs pre-padded'.format(reps, q.n_graphs, db.n_graphs, TOPK)
+
+
+def cpu_per_pair_rate(layers_spec, q, db, n_pairs=200):
+    """The reference's own control flow: one un-batched forward per (query, database) pair
+    (train.py:57-61), single thread."""
+    import torch
+    from oracle import siamese_oracle as O
+    torch.set_num_threads(1)
+    layers = O.parse_layer_specs(layers_spec, 29)
+    P = O.unflatten(layers, O.init_params(layers, 123), torch.float32)
+
+    def graph(b, g):
+        lo, hi = b.node_off[g], b.node_off[g + 1]
+        rp = np.asarray(b.rowptr[lo:hi + 1])
+        rows = np.repeat(np.arange(hi - lo), np.diff(rp))
+        return O.Graph(b.labels[lo:hi], rows, b.col[rp[0]:rp[-1]], b.val[rp[0]:rp[-1]])
+    t0 = time.perf_counter()
+    for i in range(n_pairs):
+        g1, g2 = graph(q, i % q.n_graphs), graph(db, (7 * i) % db.n_graphs)
+        x1 = O.graph_forward(layers, P, g1, 29, torch.float32)
+        x2 = O.graph_forward(layers, P, g2, 29, torch.float32)
+        O.pair_forward(layers, P, x1, x2)
+    torch.set_num_threads(os.cpu_count())
+    return n_pairs / (time.perf_counter() - t0)
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path restated (TensorFlow is not installed, so the
+    reference's own TF graph cannot run on this box; the oracle port stands in)."""
+    rank = int(os.environ.get('RANK', 0))
+    if rank != 0:
+        return
+    enc, q, db = make_rank_data(0)
+    vals = []
+    for s in range(args.warmup + args.steps):
+        v, cores, sample = cpu_rank_baseline(DEFAULT_LAYERS, q, db, seconds_budget=6.0)
+        if s >= args.warmup:
+            vals.append(v)
+    value = float(np.mean(vals))
+    pp = cpu_per_pair_rate(DEFAULT_LAYERS, q, db)
+    ms = 1000.0 * M_QUERIES * N_DB / value
+    print(json.dumps({
+        'impl': 'reference', 'metric': 'graph-pairs/sec (all-pairs ranking inference)', 'value': value,
+        'unit': 'pairs/s', 'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms,
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': workload_config(),
+        'cpu_baseline': {'value': value, 'unit': 'pairs/s', 'cores': cores, 'kind': 'port', 'sample': sample,
+                         'per_pair_reference_structure_pairs_per_s': pp},
+        'e2e': {'value': value, 'unit': 'pairs/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}))
+
+
+def workload_config():
+    return {'workload': 'all-pairs ranking, BASELINE configs[3]: {} queries x {} database graphs per GPU, '
+                        'AIDS-shaped (2..10 nodes, 29 labels), reference default flags model '
+                        '(GCN32-GCN16-Dense1-Pad10-NTN(10,10)), top-{}'.format(M_QUERIES, N_DB, TOPK),
+            'queries': M_QUERIES, 'db_per_gpu': N_DB, 'topk': TOPK, 'l2': 'flushed between timed steps (256 MiB write)',
+            'ntn_mode': 'reference', 'dropout': 0.0}
+
+
+def timed_steps(torch, fn, steps, flush):
+    """K device-timed calls of fn with an L2 flush before each; returns total ms."""
+    evs = []
+    for _ in range(steps):
+        flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        evs.append((a, b))
+    torch.cuda.synchronize()
+    return sum(a.elapsed_time(b) for a, b in evs)
+
+
+def run_cuda(args):
+    import torch
+    import torch.distributed as dist
+    from graphembedding_b200.engine import SgnnEngine
+    from graphembedding_b200.layers_factory import parse_layers
+    world = int(os.environ.get('WORLD_SIZE', 1))
+    rank = int(os.environ.get('RANK', 0))
+    local = int(os.environ.get('LOCAL_RANK', 0))
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py: no CUDA device (the product path has no CPU fallback)')
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    enc, q, db = make_rank_data(rank)
+    eng = SgnnEngine(parse_layers(DEFAULT_LAYERS, 29), 29, device=local, precision=args.precision)
+    eng.init_params(123)
+    eng.reserve(max_graphs=N_DB, max_nodes=db.total_nodes, max_nnz=db.nnz, max_queries=M_QUERIES, max_db=N_DB)
+    qd, dbd = q.to(dev), db.to(dev)
+    emb_q = torch.empty((M_QUERIES, eng.emb_dim), dtype=torch.float32, device=dev)
+    emb_db = torch.empty((N_DB, eng.emb_dim), dtype=torch.float32, device=dev)
+    sim = torch.empty((M_QUERIES, N_DB), dtype=torch.float32, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    gath_v = torch.empty((world, M_QUERIES, TOPK), dtype=torch.float32, device=dev)
+    gath_i = torch.empty((world, M_QUERIES, TOPK), dtype=torch.int32, device=dev)
+    out = {}
+
+    def step():
+        eng.embed(qd, out=emb_q)
+        eng.embed(dbd, out=emb_db)
+        eng.score_all_pairs(emb_q, emb_db, out=sim)
+        ids, vals = eng.topk(sim, TOPK)
+        if world > 1:  # database sharded over ranks: all-gather the per-shard top-k, merge with global ids
+            ids = ids + rank * N_DB
+            dist.all_gather_into_tensor(gath_v, vals)
+            dist.all_gather_into_tensor(gath_i, ids)
+            cv = gath_v.permute(1, 0, 2).reshape(M_QUERIES, world * TOPK).contiguous()
+            ci = gath_i.permute(1, 0, 2).reshape(M_QUERIES, world * TOPK).contiguous()
+            ids, vals = eng.topk_merge(cv, ci, TOPK)
+        out['ids'], out['vals'] = ids, vals
+
+    for _ in range(args.warmup):
+        step()
+    launches0 = eng.launches
+    clocks = ClockSampler(local)
+    barrier()
+    clocks.start()
+    total_ms = timed_steps(torch, step, args.steps, flush)
+    barrier()
+    clk = clocks.stop()
+    launches = eng.launches - launches0
+    total_ms = max_over_ranks(total_ms)
+    ms_per_step = total_ms / args.steps
+    value = M_QUERIES * N_DB * world / (ms_per_step * 1e-3)
+
+    # ---- dominant kernel: the all-pairs scorer, timed alone on its launching stream ----
+    for _ in range(3):
+        eng.score_all_pairs(emb_q, emb_db, out=sim)
+    k_ms = timed_steps(torch, lambda: eng.score_all_pairs(emb_q, emb_db, out=sim), args.steps, flush) / args.steps
+    e_ms = timed_steps(torch, lambda: (eng.embed(qd, out=emb_q), eng.embed(dbd, out=emb_db)), args.steps, flush) / args.steps
+    t_ms = timed_steps(torch, lambda: eng.topk(sim, TOPK), args.steps, flush) / args.steps
+    peak, peak_src = peaks()
+    alg_bytes = 4.0 * M_QUERIES * N_DB + 4.0 * (M_QUERIES + N_DB) * eng.emb_dim
+    achieved = alg_bytes / (k_ms * 1e-3) / 1e9
+    roofline = {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
+                'traffic': None, 'kernel': 'allpairs_prep_kernel + allpairs scorer (sgnn_score_all_pairs)',
+                'kernel_ms': k_ms, 'peak_source': peak_src,
+                'algorithmic_bytes_per_launch': alg_bytes,
+                'stage_ms': {'embed_q_plus_db': e_ms, 'score_all_pairs': k_ms, 'topk': t_ms}}
+
+    # ---- e2e: host buffers in, top-k out, through the host C-ABI entry point ----
+    qp, dbp = q.pin(), db.pin()
+    ids_h = torch.empty((M_QUERIES, TOPK), dtype=torch.int32).pin_memory()
+    vals_h = torch.empty((M_QUERIES, TOPK), dtype=torch.float32).pin_memory()
+    for _ in range(args.warmup):
+        eng.rank_host(qp, dbp, TOPK, ids=ids_h, vals=vals_h)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        eng.rank_host(qp, dbp, TOPK, ids=ids_h, vals=vals_h)
+    barrier()
+    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / args.steps
+    if world == 1:
+        assert torch.equal(ids_h.to(dev), out['ids']), 'host entry point and device path disagree'
+    e2e = {'value': M_QUERIES * N_DB * world / (e2e_ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': e2e_ms,
+           'h2d_bytes_per_step': q.nbytes() + db.nbytes(), 'd2h_bytes_per_step': 2 * 4 * M_QUERIES * TOPK}
+
+    train = run_train(torch, dist, dev, rank, world, local, args, barrier, max_over_ranks)
+
+    if rank != 0:
+        return
+    line = {'metric': 'graph-pairs/sec (all-pairs ranking inference)', 'value': value, 'unit': 'pairs/s',
+            'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms_per_step,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+            'dtype': 'f32' if args.precision == 'fp32' else args.precision, 'data': 'synthetic',
+            'config': workload_config(), 'clocks': clk, 'e2e': e2e, 'gpu_launches': launches,
+            'roofline': roofline, 'train': train}
+    if world == 1 and not args.no_cpu_baseline:
+        v, cores, sample = cpu_rank_baseline(DEFAULT_LAYERS, q, db)
+        line['cpu_baseline'] = {'value': v, 'unit': 'pairs/s', 'cores': cores, 'kind': 'port', 'sample': sample,
+                                'per_pair_reference_structure_pairs_per_s': cpu_per_pair_rate(DEFAULT_LAYERS, q, db)}
+    print(json.dumps(line))
+
+
+def run_train(torch, dist, dev, rank, world, local, args, barrier, max_over_ranks):
+    """BASELINE configs[2]: data-parallel training, TRAIN_BATCH pairs per GPU per step."""
+    from graphembedding_b200.engine import SgnnEngine
+    from graphembedding_b200.layers_factory import parse_layers
+    enc, batch, batches = make_train_data(rank, world)
+    eng = SgnnEngine(parse_layers(TRAIN_LAYERS, 29), 29, device=local, loss_mode='paired', ntn_mode='reference')
+    eng.init_params(123)
+    bd = batch.to(dev)
+    feeds = [(torch.as_tensor(a, device=dev), torch.as_tensor(b, device=dev), torch.as_tensor(t, device=dev), s1, s2)
+             for a, b, t, s1, s2 in batches]
+    loss = torch.zeros(4, dtype=torch.float32, device=dev)
+    grads = eng.device_buffers()[1]
+    gb = TRAIN_BATCH * world
+
+    def step(i):
+        g1, g2, t, s1, s2 = feeds[i % len(feeds)]
+        loss.zero_()
+        eng.train_step(bd, g1, g2, t, gb, s1, s2, loss=loss)
+        if world > 1:
+            dist.all_reduce(grads)      # one bucket: the whole flat gradient blob
+        eng.apply_adam(1.0, loss)
+
+    n = max(args.steps * 10, 100)
+    for i in range(10):
+        step(i)
+    l0 = eng.launches
+    barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for i in range(n):
+        step(i)
+    b.record()
+    barrier()
+    ms = max_over_ranks(a.elapsed_time(b)) / n
+    return {'workload': 'BASELINE configs[2]: DP training, {} pairs/GPU/step, {} AIDS10knef-shaped graphs (2..30 nodes), '
+                        'GCN32-GCN16-Average-NTN(16,10), fwd+bwd+allreduce+Adam, fp32'.format(TRAIN_BATCH, TRAIN_GRAPHS),
+            'value': TRAIN_BATCH * world / (ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': ms, 'steps': n,
+            'gpu_launches': eng.launches - l0, 'final_loss': float(loss[0] + loss[1])}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='cuda', choices=['cuda', 'reference'])
+    ap.add_argument('--precision', default='fp32', choices=['fp32', 'bf16x3', 'bf16'])
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_cuda(args)
+
+
+if __name__ == '__main__':
+    main()

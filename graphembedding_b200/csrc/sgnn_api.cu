@@ -189,8 +189,10 @@ int plan_launches(SgnnHandle h) {
   }
   if (set_smem(h, embed_kernel<16>, h->embed_smem[0])) return 1;
   if (set_smem(h, embed_kernel<32>, h->embed_smem[1])) return 1;
-  if (set_smem(h, train_pairs_kernel<16>, h->train_smem[0])) return 1;
-  if (set_smem(h, train_pairs_kernel<32>, h->train_smem[1])) return 1;
+  if (set_smem(h, train_pairs_kernel<16, true>, h->train_smem[0])) return 1;
+  if (set_smem(h, train_pairs_kernel<32, true>, h->train_smem[1])) return 1;
+  if (set_smem(h, train_pairs_kernel<16, false>, h->train_smem[0])) return 1;
+  if (set_smem(h, train_pairs_kernel<32, false>, h->train_smem[1])) return 1;
   if (set_smem(h, pair_score_kernel, h->pair_smem)) return 1;
   return 0;
 }
@@ -448,7 +450,20 @@ int sgnn_topk(SgnnHandle h, const float* sim_dev, int32_t m, int32_t n, int64_t 
   if (m == 0 || k == 0) return 0;
   const size_t row_bytes = (size_t)n * sizeof(float);
   const int in_smem = row_bytes <= 48 * 1024;
-  topk_kernel<<<m, 256, in_smem ? row_bytes : 0, (cudaStream_t)stream>>>(sim_dev, n, ld, k, in_smem, ids_dev, vals_dev);
+  topk_kernel<<<m, 256, in_smem ? row_bytes : 0, (cudaStream_t)stream>>>(sim_dev, nullptr, n, ld, k, in_smem, ids_dev, vals_dev);
+  CUDA_OK(h, cudaGetLastError());
+  return 0;
+}
+
+int sgnn_topk_merge(SgnnHandle h, const float* cand_vals_dev, const int32_t* cand_ids_dev, int32_t m, int32_t c,
+                    int32_t k, int32_t* ids_dev, float* vals_dev, void* stream) {
+  if (!h || !cand_vals_dev || !cand_ids_dev || !ids_dev) return fail(h, "sgnn_topk_merge: null argument");
+  if (k < 0 || k > c) return fail(h, "Invalid k " + std::to_string(k));
+  if (m == 0 || k == 0) return 0;
+  const size_t row_bytes = (size_t)c * sizeof(float);
+  const int in_smem = row_bytes <= 48 * 1024;
+  topk_kernel<<<m, 256, in_smem ? row_bytes : 0, (cudaStream_t)stream>>>(cand_vals_dev, cand_ids_dev, c, c, k, in_smem,
+                                                                         ids_dev, vals_dev);
   CUDA_OK(h, cudaGetLastError());
   return 0;
 }
@@ -467,29 +482,43 @@ int sgnn_sort_rows(SgnnHandle h, const float* sim_dev, int32_t m, int32_t n, int
   return 0;
 }
 
-int sgnn_train_step(SgnnHandle h, const SgnnGraphBatch* b, const int32_t* g1, const int32_t* g2,
-                    const float* target_sim, int32_t n_pairs, int32_t global_batch, double target_sum,
-                    double target_sqsum, float* loss_dev, void* stream) {
-  if (!h || !b || !g1 || !g2 || !target_sim) return fail(h, "sgnn_train_step: null argument");
+static int launch_pairs(SgnnHandle h, bool bwd, const SgnnGraphBatch* b, const int32_t* g1, const int32_t* g2,
+                        const float* target_sim, int32_t n_pairs, int32_t global_batch, double target_sum,
+                        double target_sqsum, float* loss, float* raw, float* sim, void* stream) {
   if (n_pairs == 0) return 0;
-  if (global_batch < n_pairs) return fail(h, "sgnn_train_step: global_batch < n_pairs");
+  if (global_batch < n_pairs) return fail(h, "global_batch < n_pairs");
   if (b->max_nodes > 32) return fail(h, "graphs with more than 32 nodes need the large-graph path (not built yet)");
   const int v = b->max_nodes <= 16 ? 0 : 1;
   const int wpb = h->train_wpb[v];
   const int blocks = std::min((n_pairs + wpb - 1) / wpb, h->sm_count * 2);
   cudaStream_t st = (cudaStream_t)stream;
-  float* loss = loss_dev ? loss_dev : h->d_loss;
   const float invB = 1.0f / (float)global_batch;
-  if (v == 0)
-    train_pairs_kernel<16><<<blocks, wpb * 32, h->train_smem[0], st>>>(
-        h->M, to_dev(b), h->d_params, g1, g2, target_sim, n_pairs, invB, (float)target_sum, (float)target_sqsum,
-        h->d_grads, loss, nullptr);
-  else
-    train_pairs_kernel<32><<<blocks, wpb * 32, h->train_smem[1], st>>>(
-        h->M, to_dev(b), h->d_params, g1, g2, target_sim, n_pairs, invB, (float)target_sum, (float)target_sqsum,
-        h->d_grads, loss, nullptr);
+  const float s1 = (float)target_sum, s2 = (float)target_sqsum;
+#define SGNN_LAUNCH_PAIRS(NM, BW)                                                                        \
+  train_pairs_kernel<NM, BW><<<blocks, wpb * 32, h->train_smem[v], st>>>(                                \
+      h->M, to_dev(b), h->d_params, g1, g2, target_sim, n_pairs, invB, s1, s2, h->d_grads, loss, raw, sim)
+  if (v == 0) { if (bwd) SGNN_LAUNCH_PAIRS(16, true); else SGNN_LAUNCH_PAIRS(16, false); }
+  else { if (bwd) SGNN_LAUNCH_PAIRS(32, true); else SGNN_LAUNCH_PAIRS(32, false); }
+#undef SGNN_LAUNCH_PAIRS
   CUDA_OK(h, cudaGetLastError());
   return 0;
+}
+
+int sgnn_train_step(SgnnHandle h, const SgnnGraphBatch* b, const int32_t* g1, const int32_t* g2,
+                    const float* target_sim, int32_t n_pairs, int32_t global_batch, double target_sum,
+                    double target_sqsum, float* loss_dev, void* stream) {
+  if (!h || !b || !g1 || !g2 || !target_sim) return fail(h, "sgnn_train_step: null argument");
+  return launch_pairs(h, true, b, g1, g2, target_sim, n_pairs, global_batch, target_sum, target_sqsum,
+                      loss_dev ? loss_dev : h->d_loss, nullptr, nullptr, stream);
+}
+
+int sgnn_eval_pairs(SgnnHandle h, const SgnnGraphBatch* b, const int32_t* g1, const int32_t* g2,
+                    const float* target_sim, int32_t n_pairs, int32_t global_batch, double target_sum,
+                    double target_sqsum, float* loss_dev, float* raw_dev, float* sim_dev, void* stream) {
+  if (!h || !b || !g1 || !g2) return fail(h, "sgnn_eval_pairs: null argument");
+  if (!target_sim && loss_dev) return fail(h, "sgnn_eval_pairs: a loss needs targets");
+  return launch_pairs(h, false, b, g1, g2, target_sim, n_pairs, global_batch, target_sum, target_sqsum,
+                      target_sim ? loss_dev : nullptr, raw_dev, sim_dev, stream);
 }
 
 int sgnn_apply_adam(SgnnHandle h, float grad_scale, float* loss_dev, void* stream) {

@@ -36,11 +36,13 @@ __device__ __forceinline__ unsigned long long block_max_u64(unsigned long long v
 // One CTA per row.  k selection rounds; round r returns the largest key strictly below
 // the previous winner (keys are unique because the index is part of the key).
 __global__ void __launch_bounds__(256)
-topk_kernel(const float* __restrict__ sim, int n, int64_t ld, int k, int row_in_smem,
-            int32_t* __restrict__ ids, float* __restrict__ vals) {
+topk_kernel(const float* __restrict__ sim, const int32_t* __restrict__ col_ids, int n, int64_t ld, int k,
+            int row_in_smem, int32_t* __restrict__ ids, float* __restrict__ vals) {
   extern __shared__ __align__(16) float s_row[];
   __shared__ unsigned long long s_red[32];
   const float* r = sim + (size_t)blockIdx.x * ld;
+  // merge mode: candidate i carries an explicit (global) id; ties still break on that id
+  const int32_t* cid = col_ids ? col_ids + (size_t)blockIdx.x * ld : nullptr;
   if (row_in_smem) {
     for (int i = threadIdx.x; i < n; i += blockDim.x) s_row[i] = r[i];
     __syncthreads();
@@ -49,15 +51,16 @@ topk_kernel(const float* __restrict__ sim, int n, int64_t ld, int k, int row_in_
   unsigned long long prev = ~0ull;
   for (int round = 0; round < k; ++round) {
     unsigned long long best = 0ull;
+    int best_i = 0;
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
-      const unsigned long long key = rank_key(r[i], i);
-      if (key < prev && key > best) best = key;
+      const unsigned long long key = rank_key(r[i], cid ? cid[i] : i);
+      if (key < prev && key > best) { best = key; best_i = i; }
     }
+    const unsigned long long mine = best;
     best = block_max_u64(best, s_red);
-    if (threadIdx.x == 0) {
-      const int idx = (int)(best & 0xffffffffull);
-      ids[(size_t)blockIdx.x * k + round] = idx;
-      if (vals) vals[(size_t)blockIdx.x * k + round] = r[idx];
+    if (mine == best && best != 0ull) {  // keys are unique: exactly one owner
+      ids[(size_t)blockIdx.x * k + round] = (int)(best & 0xffffffffull);
+      if (vals) vals[(size_t)blockIdx.x * k + round] = r[best_i];
     }
     prev = best;
   }

@@ -491,13 +491,14 @@ __device__ __forceinline__ void graph_bwd(const ModelDev& M, const GraphS& G, co
   }
 }
 
-template <int NMAX>
+template <int NMAX, bool BWD>
 __global__ void __launch_bounds__(128)
 train_pairs_kernel(const __grid_constant__ ModelDev M, const BatchDev B,
                    const float* __restrict__ params, const int32_t* __restrict__ g1,
                    const int32_t* __restrict__ g2, const float* __restrict__ target_sim, int n_pairs,
                    float inv_global_batch, float tsum, float tsqsum, float* __restrict__ grads,
-                   float* __restrict__ loss, float* __restrict__ sim_out) {
+                   float* __restrict__ loss, float* __restrict__ raw_out,
+                   float* __restrict__ sim_out) {
   extern __shared__ __align__(16) float smem[];
   using Geo = SmallGeom<NMAX>;
   const int wfl = (M.n_params + 3) / 4 * 4;
@@ -539,7 +540,7 @@ train_pairs_kernel(const __grid_constant__ ModelDev M, const BatchDev B,
     const float* x1 = embs[0]; const float* x2 = embs[1];
     const float raw = pair_fwd(M, s_w, s_wp, x1, x2, ub, mb, tb, lane, &st, &su);
     const float pr = sgnn_act(raw, M.final_act, M.yeta);
-    const float tgt = target_sim[p];
+    const float tgt = target_sim ? target_sim[p] : 0.f;
     float dp, lc;
     if (M.loss_mode == SGNN_LOSS_REFERENCE) {
       // (1/2B) sum_i (s_i - p)^2 summed over the B targets (F6, model_mse.py:145-151)
@@ -550,7 +551,11 @@ train_pairs_kernel(const __grid_constant__ ModelDev M, const BatchDev B,
       lc = 0.5f * (pr - tgt) * (pr - tgt) * inv_global_batch;
     }
     loss_acc += lc;
-    if (sim_out && lane == 0) sim_out[p] = pr;
+    if (lane == 0) {
+      if (sim_out) sim_out[p] = pr;
+      if (raw_out) raw_out[p] = raw;
+    }
+    if (!BWD) { __syncwarp(); continue; }
     const float graw = dp * sgnn_act_grad(pr, raw, M.final_act, M.yeta);
 
     // ---- pair layer backward -> dx1, dx2 (length emb_dim) ----
@@ -606,7 +611,8 @@ train_pairs_kernel(const __grid_constant__ ModelDev M, const BatchDev B,
     }
     __syncwarp();
   }
-  if (lane == 0 && loss_acc != 0.f) atomicAdd(loss, loss_acc);
+  if (lane == 0 && loss && loss_acc != 0.f) atomicAdd(loss, loss_acc);
+  if (!BWD) return;
   __syncthreads();
   for (int i = threadIdx.x; i < M.n_params; i += blockDim.x) {
     const float v = s_g[i];

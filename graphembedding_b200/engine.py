@@ -127,6 +127,16 @@ class SgnnEngine(object):
         self.launches += 1
         return ids, vals
 
+    def topk_merge(self, cand_vals, cand_ids, k, stream=None):
+        import torch
+        m, c = cand_vals.shape
+        ids = torch.empty((m, k), dtype=torch.int32, device=self.device)
+        vals = torch.empty((m, k), dtype=torch.float32, device=self.device)
+        check(self.h, lib().sgnn_topk_merge(self.h, _ptr(cand_vals), _ptr(cand_ids), m, c, k, _ptr(ids),
+                                            _ptr(vals), _stream_ptr(stream)))
+        self.launches += 1
+        return ids, vals
+
     def sort_rows(self, sim, stream=None):
         import torch
         m, n = sim.shape
@@ -154,6 +164,24 @@ class SgnnEngine(object):
                                             _ptr(loss), _stream_ptr(stream)))
         self.launches += 1
         return loss
+
+    def eval_pairs(self, batch, g1, g2, target_sim=None, global_batch=None, stream=None):
+        """Forward only on the listed pairs -> (loss[4] or None, raw, sim)."""
+        import torch
+        n = int(g1.numel())
+        raw = torch.empty(n, dtype=torch.float32, device=self.device)
+        sim = torch.empty(n, dtype=torch.float32, device=self.device)
+        loss, s1, s2 = None, 0.0, 0.0
+        if target_sim is not None:
+            loss = torch.zeros(4, dtype=torch.float32, device=self.device)
+            t = target_sim.double()
+            s1, s2 = float(t.sum()), float((t * t).sum())
+        s = batch.struct()
+        check(self.h, lib().sgnn_eval_pairs(self.h, C.byref(s), _ptr(g1), _ptr(g2), _ptr(target_sim), n,
+                                            int(global_batch or n), s1, s2, _ptr(loss), _ptr(raw), _ptr(sim),
+                                            _stream_ptr(stream)))
+        self.launches += 1
+        return loss, raw, sim
 
     def apply_adam(self, grad_scale=1.0, loss=None, stream=None):
         check(self.h, lib().sgnn_apply_adam(self.h, float(grad_scale), _ptr(loss), _stream_ptr(stream)))

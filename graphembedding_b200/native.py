@@ -70,8 +70,10 @@ SIGNATURES = {
     'sgnn_forward_pairs': (C.c_int, [_P, _BP, _P, _P, _I32, _P, _P, _P, _P]),
     'sgnn_score_all_pairs': (C.c_int, [_P, _P, _I32, _P, _I32, _P, _I64, _P]),
     'sgnn_topk': (C.c_int, [_P, _P, _I32, _I32, _I64, _I32, _P, _P, _P]),
+    'sgnn_topk_merge': (C.c_int, [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P]),
     'sgnn_sort_rows': (C.c_int, [_P, _P, _I32, _I32, _I64, _P, _P]),
     'sgnn_train_step': (C.c_int, [_P, _BP, _P, _P, _P, _I32, _I32, _D, _D, _P, _P]),
+    'sgnn_eval_pairs': (C.c_int, [_P, _BP, _P, _P, _P, _I32, _I32, _D, _D, _P, _P, _P, _P]),
     'sgnn_apply_adam': (C.c_int, [_P, _F, _P, _P]),
     'sgnn_zero_grads': (C.c_int, [_P, _P]),
     'sgnn_precision_at_k': (C.c_int, [_P, _P, _P, _I32, _I32, _P, _I32, _P, _P]),

@@ -154,6 +154,10 @@ int sgnn_score_all_pairs(SgnnHandle h, const float* emb_q_dev, int32_t m, const 
  * ascending mergesort reversed => equal scores come out higher index first). */
 int sgnn_topk(SgnnHandle h, const float* sim_dev, int32_t m, int32_t n, int64_t ld, int32_t k,
               int32_t* ids_dev, float* vals_dev, void* stream);
+/* merge of per-shard top-k candidates (database sharded over GPUs): cand_vals/cand_ids are
+ * m x c (c = shards * k), ids are GLOBAL database indices; same tie order as sgnn_topk. */
+int sgnn_topk_merge(SgnnHandle h, const float* cand_vals_dev, const int32_t* cand_ids_dev, int32_t m,
+                    int32_t c, int32_t k, int32_t* ids_dev, float* vals_dev, void* stream);
 /* full descending ranking per row (sort_id_mat, results.py:221-224) */
 int sgnn_sort_rows(SgnnHandle h, const float* sim_dev, int32_t m, int32_t n, int64_t ld,
                    int32_t* ids_dev, void* stream);
@@ -166,6 +170,13 @@ int sgnn_train_step(SgnnHandle h, const SgnnGraphBatch* batch_dev, const int32_t
                     const int32_t* g2_dev, const float* target_sim_dev, int32_t n_pairs,
                     int32_t global_batch, double target_sum, double target_sqsum, float* loss_dev,
                     void* stream);
+/* forward only on the listed pairs (no full-batch embedding pass): the 'val' and 'test'
+ * branches of run_tf (train.py:84-87).  target_sim/loss_dev may be NULL (no loss wanted);
+ * raw_dev = pre-final_act score (pred_sim_without_act, models.py:90-91), sim_dev = after. */
+int sgnn_eval_pairs(SgnnHandle h, const SgnnGraphBatch* batch_dev, const int32_t* g1_dev,
+                    const int32_t* g2_dev, const float* target_sim_dev, int32_t n_pairs,
+                    int32_t global_batch, double target_sum, double target_sqsum, float* loss_dev,
+                    float* raw_dev, float* sim_dev, void* stream);
 /* weight-decay gradient + TF-1 Adam update on every variable (models.py:28-29, 67-74),
  * then zeroes the grad buffer.  grad_scale multiplies the summed gradient first.
  * loss_dev[1] = weight-decay loss term if loss_dev != NULL. */

@@ -1,0 +1,50 @@
+"""The batched CPU baseline (oracle/batched.py) must agree with the per-graph restatement."""
+import numpy as np
+import pytest
+
+from util import CONFIGS, O, corpus, encoder_for, oracle_graphs
+from oracle import batched as OB
+from graphembedding_b200.graphs import pack_nx_graphs
+
+torch = pytest.importorskip('torch')
+
+
+@pytest.mark.parametrize('cfg', ['default', 'avg_ntn', 'att3', 'dense_dot'])
+def test_batched_equals_per_graph(cfg):
+    gs = corpus(30, 2, 10, seed=9)
+    enc = encoder_for(gs)
+    layers = O.parse_layer_specs(CONFIGS[cfg], enc.input_dim())
+    flat = O.init_params(layers, 3)
+    P = O.unflatten(layers, flat, torch.float64)
+    og = oracle_graphs(gs, enc)
+    lab, A, mask, n = OB.pad_graphs(og, enc.input_dim(), torch.float64)
+    lab2, A2, mask2, n2 = OB.pad_from_packed(pack_nx_graphs(gs, enc), torch.float64)
+    assert torch.equal(lab, lab2) and torch.equal(n, n2)
+    assert torch.allclose(A, A2, rtol=0, atol=1e-7)          # packed values are float32
+    emb = OB.embed(layers, P, lab, A, mask, n, torch.float64)
+    for i, g in enumerate(og):
+        ref = O.graph_forward(layers, P, g, enc.input_dim())
+        assert torch.allclose(emb[i], ref, rtol=1e-10, atol=1e-12)
+    raw = OB.score_pairs(layers, P, emb[:15], emb[15:])
+    ref = O.forward_pairs(layers, P, og[:15], og[15:], enc.input_dim())
+    assert torch.allclose(raw, ref, rtol=1e-10, atol=1e-12)
+    sim = OB.score_all_pairs(layers, P, emb[:7], emb[7:])
+    for i in range(7):
+        for j in (0, 5, 22):
+            r = O.pair_forward(layers, P, emb[i], emb[7 + j])
+            assert abs(float(sim[i, j]) - float(torch.exp(-0.6 * r * r))) < 1e-10
+
+
+def test_batched_train_step_equals_oracle():
+    gs = corpus(20, 2, 10, seed=10)
+    enc = encoder_for(gs)
+    layers = O.parse_layer_specs(CONFIGS['default'], enc.input_dim())
+    flat = O.init_params(layers, 4).astype(np.float64)
+    og = oracle_graphs(gs, enc)
+    lab, A, mask, n = OB.pad_graphs(og, enc.input_dim(), torch.float64)
+    tgt = np.linspace(0.1, 0.9, 10)
+    a1, a2 = O.TFAdam(flat.size), O.TFAdam(flat.size)
+    g1, g2 = torch.arange(0, 10), torch.arange(10, 20)
+    new, loss = OB.train_step(layers, flat, a1, lab, A, mask, n, g1, g2, tgt, dtype=torch.float64)
+    l, _, _, g, _ = O.loss_and_grads(layers, flat, og[:10], og[10:], tgt, enc.input_dim())
+    assert abs(l - loss) < 1e-12 and np.allclose(new, a2.step(flat, g), rtol=0, atol=1e-12)

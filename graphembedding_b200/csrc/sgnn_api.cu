@@ -6,6 +6,7 @@
 #include <vector>
 
 #include "sgnn_allpairs.cuh"
+#include "sgnn_allpairs_tc.cuh"
 #include "sgnn_common.cuh"
 #include "sgnn_rank.cuh"
 #include "sgnn_small.cuh"
@@ -38,6 +39,8 @@ struct SgnnHandle_t {
   int64_t adam_t = 0;
   float *d_P = nullptr, *d_C = nullptr;  // all-pairs query tables
   int64_t cap_P = 0;
+  __nv_bfloat16 *d_Atc = nullptr, *d_Btc = nullptr;  // tensor-core operands in UMMA tile order
+  int64_t cap_Atc = 0, cap_Btc = 0;                   // in elements
   int dep = 16;                           // padded embedding width of the all-pairs scorer
   cudaStream_t stream = nullptr;          // used by *_host entry points
   HostWs ws;
@@ -217,6 +220,61 @@ int ensure_query_tables(SgnnHandle h, int64_t m) {
   return fail(h, "query table workspace too small: call sgnn_reserve(max_queries >= m) first");
 }
 
+
+template <int KT, bool RELU, bool REF>
+int launch_tc(SgnnHandle h, const TcGeom& G, int grid, size_t smem, float* sim, int64_t ld, cudaStream_t st) {
+  auto kern = allpairs_tc_kernel<KT, RELU, REF>;
+  CUDA_OK(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<grid, TC_THREADS, smem, st>>>(h->M, G, h->d_params, h->d_Atc, h->d_Btc, sim, ld);
+  CUDA_OK(h, cudaGetLastError());
+  return 0;
+}
+
+// tcgen05 path of sgnn_score_all_pairs (SGNN_PREC_BF16X3 / SGNN_PREC_BF16)
+int score_all_pairs_tc(SgnnHandle h, const float* emb_q, int m, const float* emb_db, int n, float* sim,
+                       int64_t ld, cudaStream_t st) {
+  const ModelDev& M = h->M;
+  const bool ntn = M.pair_kind == SGNN_LAYER_NTN;
+  TcGeom G;
+  G.m = m; G.n = n; G.D = M.emb_dim; G.K = ntn ? M.K : 1;
+  G.QH = 128 / G.K;
+  G.KCH = round_up(G.D + 1, 16) / 8;
+  G.parts = h->cfg.precision == SGNN_PREC_BF16 ? 1 : 2;
+  G.n_gtiles = (n + 127) / 128;
+  G.n_qblocks = (m + 2 * G.QH - 1) / (2 * G.QH);
+  const int64_t items = (int64_t)G.n_gtiles * G.n_qblocks;
+  G.GA = (int)std::max<int64_t>(1, std::min<int64_t>(TC_GA_MAX, items / ((int64_t)h->sm_count * 4)));
+  G.GA = std::min(G.GA, G.n_gtiles);
+  const int g_groups = (G.n_gtiles + G.GA - 1) / G.GA;
+  int q_groups = std::max(1, std::min(G.n_qblocks, h->sm_count / g_groups));
+  G.qb_per_group = (G.n_qblocks + q_groups - 1) / q_groups;
+  q_groups = (G.n_qblocks + G.qb_per_group - 1) / G.qb_per_group;
+  G.q_groups = q_groups;
+  const int64_t need_a = (int64_t)G.n_gtiles * G.parts * G.KCH * 1024;
+  const int64_t need_b = (int64_t)G.n_qblocks * G.parts * G.KCH * (TC_NPAD * 8);
+  if (need_a > h->cap_Atc || need_b > h->cap_Btc)
+    return fail(h, "tensor-core operand workspace too small: call sgnn_reserve(max_queries, max_db) first");
+  tc_prep_db_kernel<<<(G.n_gtiles * 128 * G.KCH + 255) / 256, 256, 0, st>>>(G, emb_db, h->d_Atc);
+  CUDA_OK(h, cudaGetLastError());
+  tc_prep_q_kernel<<<(m + 3) / 4, 128, 0, st>>>(M, G, h->d_params, emb_q, h->d_Btc);
+  CUDA_OK(h, cudaGetLastError());
+  size_t smem = (size_t)TC_GA_MAX * tc_a_bytes(G) + (size_t)TC_STAGES * tc_b_bytes(G) + 256 + 4 * G.K;
+  smem = std::max<size_t>(smem, 120 * 1024);  // one CTA per SM: each CTA owns all 512 TMEM columns
+  if (smem > (size_t)h->smem_optin) return fail(h, "embedding too wide for the tensor-core all-pairs tiles");
+  const int grid = g_groups * q_groups;
+  const bool relu = ntn && M.pair_act == SGNN_ACT_RELU;
+  const bool ref = ntn && M.ntn_mode == SGNN_NTN_REFERENCE;
+#define SGNN_TC(KT)                                                                                  \
+  (relu ? (ref ? launch_tc<KT, true, true>(h, G, grid, smem, sim, ld, st)                            \
+               : launch_tc<KT, true, false>(h, G, grid, smem, sim, ld, st))                          \
+        : (ref ? launch_tc<KT, false, true>(h, G, grid, smem, sim, ld, st)                           \
+               : launch_tc<KT, false, false>(h, G, grid, smem, sim, ld, st)))
+  if (G.K == 10) return SGNN_TC(10);
+  if (G.K == 16) return SGNN_TC(16);
+  return SGNN_TC(0);
+#undef SGNN_TC
+}
+
 }  // namespace
 
 extern "C" {
@@ -269,7 +327,7 @@ int sgnn_destroy(SgnnHandle h) {
   if (!h) return 0;
   cudaSetDevice(h->device);
   cudaFree(h->d_params); cudaFree(h->d_grads); cudaFree(h->d_m); cudaFree(h->d_v); cudaFree(h->d_loss);
-  cudaFree(h->d_P); cudaFree(h->d_C);
+  cudaFree(h->d_P); cudaFree(h->d_C); cudaFree(h->d_Atc); cudaFree(h->d_Btc);
   HostWs& w = h->ws;
   for (int s = 0; s < 2; ++s) {
     cudaFree(w.node_off[s]); cudaFree(w.labels[s]); cudaFree(w.rowptr[s]); cudaFree(w.col[s]); cudaFree(w.val[s]);
@@ -369,6 +427,23 @@ int sgnn_reserve(SgnnHandle h, int64_t max_graphs, int64_t max_nodes, int64_t ma
     const int K = h->M.pair_kind == SGNN_LAYER_NTN ? h->M.K : 1;
     if (dev_alloc(h, &h->d_P, max_queries * K * 64) || dev_alloc(h, &h->d_C, max_queries * K)) return 1;
   }
+  {
+    const ModelDev& M = h->M;
+    const int K = M.pair_kind == SGNN_LAYER_NTN ? M.K : 1;
+    const int64_t kch = round_up(M.emb_dim + 1, 16) / 8, qt = 2 * (128 / K);
+    const int64_t need_a = ((max_db + 127) / 128) * 2 * kch * 1024;
+    const int64_t need_b = ((max_queries + qt - 1) / qt) * 2 * kch * (TC_NPAD * 8);
+    if (need_a > h->cap_Atc) {
+      if (dev_alloc(h, &h->d_Atc, need_a)) return 1;
+      CUDA_OK(h, cudaMemset(h->d_Atc, 0, need_a * sizeof(__nv_bfloat16)));
+      h->cap_Atc = need_a;
+    }
+    if (need_b > h->cap_Btc) {
+      if (dev_alloc(h, &h->d_Btc, need_b)) return 1;
+      CUDA_OK(h, cudaMemset(h->d_Btc, 0, need_b * sizeof(__nv_bfloat16)));
+      h->cap_Btc = need_b;
+    }
+  }
   if (max_queries * max_db > w.cap_q * w.cap_db || max_queries > w.cap_q) {
     w.cap_q = std::max(w.cap_q, max_queries);
     w.cap_db = std::max(w.cap_db, max_db);
@@ -422,6 +497,7 @@ int sgnn_score_all_pairs(SgnnHandle h, const float* emb_q, int32_t m, const floa
   cudaStream_t st = (cudaStream_t)stream;
   const ModelDev& M = h->M;
   const int K = M.pair_kind == SGNN_LAYER_NTN ? M.K : 1;
+  if (h->cfg.precision != SGNN_PREC_FP32) return score_all_pairs_tc(h, emb_q, m, emb_db, n, sim_dev, ld, st);
   const int DEP = h->dep;
   allpairs_prep_kernel<<<(m + 3) / 4, 128, 0, st>>>(M, h->d_params, emb_q, m, DEP, h->d_P, h->d_C);
   CUDA_OK(h, cudaGetLastError());

@@ -176,3 +176,21 @@ def test_host_entry_points_round_trip():
     sim = np.empty((32, 64), np.float32)
     ids, vals = eng.rank_host(q, db, 10, sim=sim)
     assert np.array_equal(ids, O.sort_id_mat_sim(sim)[:, :10])
+
+
+@pytest.mark.parametrize('cfg', ['default', 'avg_ntn', 'att3', 'dense_dot'])
+@pytest.mark.parametrize('ntn_mode', ['reference', 'paper'])
+def test_tensor_core_all_pairs_matches_fp32_path(cfg, ntn_mode):
+    """tcgen05 scorer (bf16x3 split, fp32 accumulate in TMEM) vs the fp32 CUDA-core scorer and the
+    1e-4 parity gate; plain bf16 (one hi.hi product) at its stated tolerance: 0.1 relative, floor 1e-2
+    (the final exp(-yeta s^2) amplifies the ~2^-8 operand rounding)."""
+    out = {}
+    for prec in ('fp32', 'bf16x3', 'bf16'):
+        eng, layers, flat, gs, enc, batch = _setup(cfg, 700, ntn_mode=ntn_mode, precision=prec)
+        m, n = 77, 600
+        eng.reserve(max_queries=m, max_db=n)
+        emb = eng.embed(batch.to(eng.device))
+        out[prec] = eng.score_all_pairs(emb[:m].contiguous(), emb[m:m + n].contiguous()).cpu().numpy()
+    ref = out['fp32']
+    assert np.max(np.abs(out['bf16x3'] - ref) / np.maximum(np.abs(ref), 1e-3)) <= 2e-4
+    assert np.max(np.abs(out['bf16'] - ref) / np.maximum(np.abs(ref), 1e-2)) <= 1e-1

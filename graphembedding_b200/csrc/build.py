@@ -1,42 +1,61 @@
-"""Build libsgnn.so in-tree with nvcc for sm_100a (cross-compiles without a GPU)."""
+"""Build libsgnn.so in-tree with nvcc for sm_100a (cross-compiles without a GPU).  Every .cu/.cpp
+in this directory is one translation unit; units compile in parallel and are linked into one
+shared library."""
 import os
 import subprocess
 import sys
+from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB = os.path.join(HERE, 'libsgnn.so')
-SOURCES = ['sgnn_api.cu', 'sgnn_pack.cpp']
-HEADERS = ['sgnn_common.cuh', 'sgnn_small.cuh', 'sgnn_allpairs.cuh', 'sgnn_rank.cuh',
-           os.path.join('..', '..', 'include', 'sgnn.h')]
-EXTRA_GLOB_SUFFIX = ('.cuh', '.cu', '.cpp', '.h')
+OBJ = os.path.join(HERE, 'build')
+DEP_SUFFIX = ('.cuh', '.cu', '.cpp', '.h')
+FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
+         '--expt-relaxed-constexpr', '--extended-lambda', '-Xcompiler', '-fPIC']
 
 
-def _stale():
-    if not os.path.exists(LIB):
-        return True
-    t = os.path.getmtime(LIB)
-    deps = [os.path.join(HERE, f) for f in os.listdir(HERE) if f.endswith(EXTRA_GLOB_SUFFIX)]
+def _deps():
+    deps = [os.path.join(HERE, f) for f in os.listdir(HERE) if f.endswith(DEP_SUFFIX)]
     deps.append(os.path.join(HERE, '..', '..', 'include', 'sgnn.h'))
-    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+    return [d for d in deps if os.path.exists(d)]
+
+
+def _stale(target, deps):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps)
 
 
 def build(force=False, verbose=False):
-    if not force and not _stale():
+    headers = [d for d in _deps() if d.endswith(('.cuh', '.h'))]
+    srcs = sorted(f for f in os.listdir(HERE) if f.endswith(('.cu', '.cpp')))
+    if not force and not _stale(LIB, _deps()):
         return LIB
     nvcc = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
-    srcs = [f for f in os.listdir(HERE) if f.endswith('.cu') or f.endswith('.cpp')]
-    cmd = [nvcc, '-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
-           '--expt-relaxed-constexpr', '--extended-lambda', '-Xcompiler', '-fPIC', '-shared',
-           '-o', LIB] + sorted(srcs) + ['-lcuda']
+    os.makedirs(OBJ, exist_ok=True)
+
+    def compile_one(src):
+        obj = os.path.join(OBJ, src + '.o')
+        if not force and not _stale(obj, headers + [os.path.join(HERE, src)]):
+            return obj, ''
+        cmd = [nvcc] + FLAGS + (['-Xptxas', '-v'] if verbose else []) + ['-c', src, '-o', obj]
+        r = subprocess.run(cmd, cwd=HERE, capture_output=True, text=True)
+        if r.returncode != 0:
+            sys.stderr.write(r.stdout + r.stderr)
+            raise RuntimeError('nvcc failed on ' + src)
+        return obj, r.stderr
+
+    with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
+        results = list(ex.map(compile_one, srcs))
     if verbose:
-        cmd.insert(1, '-Xptxas')
-        cmd.insert(2, '-v')
+        for _, log in results:
+            sys.stderr.write(log)
+    cmd = [nvcc, '-shared', '-o', LIB] + [o for o, _ in results] + ['-lcuda']
     r = subprocess.run(cmd, cwd=HERE, capture_output=True, text=True)
     if r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)
-        raise RuntimeError('nvcc failed building libsgnn.so')
-    if verbose:
-        sys.stderr.write(r.stderr)
+        raise RuntimeError('nvcc failed linking libsgnn.so')
     return LIB
 
 

@@ -20,24 +20,7 @@
 #pragma once
 #include "sgnn_common.cuh"
 #include "sgnn_tc.cuh"
-
-struct TcGeom {
-  int m, n, D, K;
-  int QH;          // queries per column half (= floor(128 / K)); a q-block holds 2*QH queries
-  int KCH;         // 16-byte K chunks per part (= round_up(D+1,16)/8)
-  int parts;       // 1 = bf16, 2 = bf16x3 (hi + lo)
-  int n_gtiles, n_qblocks;
-  int GA;          // database tiles kept resident per CTA
-  int q_groups, qb_per_group;
-};
-
-constexpr int TC_NPAD = 256;     // MMA N: half h of the queries lives in columns [128h, 128h + QH*K)
-constexpr int TC_STAGES = 3;
-constexpr int TC_GA_MAX = 4;
-constexpr int TC_THREADS = 320;
-
-__host__ __device__ inline int tc_a_bytes(const TcGeom& G) { return G.parts * G.KCH * 128 * 16; }
-__host__ __device__ inline int tc_b_bytes(const TcGeom& G) { return G.parts * G.KCH * TC_NPAD * 16; }
+#include "sgnn_tc_geom.h"
 
 __device__ __forceinline__ void split_bf16(float x, __nv_bfloat16& hi, __nv_bfloat16& lo) {
   hi = __float2bfloat16_rn(x);
@@ -66,7 +49,10 @@ tc_prep_db_kernel(const TcGeom G, const float* __restrict__ emb_db, __nv_bfloat1
     *reinterpret_cast<uint4*>(A + base + (size_t)G.KCH * 1024) = *reinterpret_cast<const uint4*>(lo);
 }
 
-// B operand: one warp per query; lanes over (k, kk)
+// B operand: one warp per query; lanes over (k, kk).  With KC == K + 1 (relu inner activation) row K
+// of the query holds sum_k w_k * row_k (w = 1 in reference mode, U in paper mode): the tensor core
+// then also delivers sum_k w_k m_k, and  sum_k w_k relu(m_k) = (sum_k w_k m_k + sum_k w_k |m_k|) / 2
+// costs ONE add-with-|x|-modifier per accumulator element in the epilogue instead of max + add.
 __global__ void __launch_bounds__(128)
 tc_prep_q_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const float* __restrict__ params,
                  const float* __restrict__ emb_q, __nv_bfloat16* __restrict__ B) {
@@ -76,13 +62,12 @@ tc_prep_q_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const float
   const int D = G.D, K = G.K, DK16 = G.KCH * 8, DK = D * K;
   const int QT = 2 * G.QH;
   const int qb = q / QT, ql = q - qb * QT, h = ql / G.QH, qq = ql - h * G.QH;
-  const int row0 = h * 128 + qq * K;
+  const int row0 = h * 128 + qq * G.KC;
   const float* x = emb_q + (size_t)q * D;
   const bool dot = M.pair_kind == SGNN_LAYER_DOT;
   const float* W = params + M.w_off;
   const float* V = params + M.v_off;
-  for (int i = lane; i < K * DK16; i += 32) {
-    const int k = i / DK16, kk = i - k * DK16;
+  auto value = [&](int k, int kk) {
     float v = 0.f;
     if (dot) {
       v = kk < D ? x[kk] : 0.f;
@@ -93,64 +78,103 @@ tc_prep_q_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const float
       v = M.pair_bias ? params[M.b_off + k] : 0.f;
       for (int a = 0; a < D; ++a) v = fmaf(V[k * 2 * D + a], x[a], v);
     }
+    return v;
+  };
+  auto put = [&](int row, int kk, float v) {
     __nv_bfloat16 hi, lo;
     split_bf16(v, hi, lo);
-    const size_t off = ((size_t)(qb * G.parts) * G.KCH + (kk >> 3)) * (TC_NPAD * 8) + (size_t)(row0 + k) * 8 + (kk & 7);
+    const size_t off = ((size_t)(qb * G.parts) * G.KCH + (kk >> 3)) * (TC_NPAD * 8) + (size_t)row * 8 + (kk & 7);
     B[off] = hi;
     if (G.parts == 2) B[off + (size_t)G.KCH * TC_NPAD * 8] = lo;
+  };
+  for (int i = lane; i < K * DK16; i += 32) {
+    const int k = i / DK16, kk = i - k * DK16;
+    put(row0 + k, kk, value(k, kk));
+  }
+  if (G.KC > K) {
+    const bool ref = M.ntn_mode == SGNN_NTN_REFERENCE;
+    for (int kk = lane; kk < DK16; kk += 32) {
+      float s = 0.f;
+      for (int k = 0; k < K; ++k) s = fmaf(ref ? 1.f : params[M.u_off + k], value(k, kk), s);
+      put(row0 + K, kk, s);
+    }
   }
 }
 
 struct TcEpi {
   const float* sU;   // [K] in shared memory
   float su, yeta;
+  float c2;          // relu + sim_kernel fast path: sim = 2^(c2 * (sum + abs_sum)^2)
   int final_act, pair_act;
   float* sim;
   int64_t ld;
   int m, n;
 };
 
-__device__ __forceinline__ void tc_emit(const TcEpi& E, bool ref, float st, int qrow, int g) {
-  const float score = ref ? E.su * st : st;
-  float s;
-  if (E.final_act == SGNN_ACT_SIM_KERNEL) s = __expf(-E.yeta * score * score);
-  else s = sgnn_act(score, E.final_act, E.yeta);
-  if (qrow < E.m && g < E.n) E.sim[(size_t)qrow * E.ld + g] = s;
+__device__ __forceinline__ float tc_ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// score of one (query, database graph) from the reduced accumulator value
+template <bool RELU, bool REF, bool SIMK>
+__device__ __forceinline__ float tc_finish(const TcEpi& E, float st) {
+  if constexpr (RELU && SIMK) {
+    return tc_ex2(st * st * E.c2);
+  } else {
+    float score = RELU ? 0.5f * st : st;
+    if (REF) score *= E.su;
+    if constexpr (SIMK) return __expf(-E.yeta * score * score);
+    return sgnn_act(score, E.final_act, E.yeta);
+  }
 }
 
 // Epilogue of one accumulator half: this thread owns TMEM lane (database graph) g and walks the
-// columns of QH queries x K feature maps.  KT > 0: K known at compile time, everything unrolled.
-template <int KT, bool RELU, bool REF>
-__device__ __forceinline__ void tc_epilogue_half(const TcEpi& E, uint32_t taddr, int K, int QH, int qrow0, int g) {
+// columns of QH queries x KC accumulator columns.  KT > 0: K known at compile time; the whole half
+// is pulled into registers, the TMEM buffer is handed back to the MMA warp at once, and the
+// arithmetic + stores run from registers while the next tile's MMAs execute.
+template <int KT, bool RELU, bool REF, bool SIMK>
+__device__ __forceinline__ void tc_epilogue_half(const TcEpi& E, uint32_t taddr, int K, int KCr, int QH, int qrow0,
+                                                 int g, uint64_t* t_empty, int lane) {
+  const bool g_ok = g < E.n;
+  const int qmax = min(QH, E.m - qrow0);
+  float* p = E.sim + (size_t)qrow0 * E.ld + g;
   if constexpr (KT > 0) {
-    constexpr int QHC = 128 / KT, COLS = QHC * KT;
+    constexpr int KC = RELU ? KT + 1 : KT;
+    constexpr int QHC = 128 / KC, COLS = QHC * KC, NCH = (COLS + 31) / 32;
+    float v[NCH * 32];
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) tc::tmem_ld32(taddr + c * 32, v + c * 32);
+    tc::tmem_ld_wait();
+    tc::tc_fence_before();
+    __syncwarp();
+    if (lane == 0) tc::mbar_arrive(t_empty);
     float u[KT];
     if constexpr (!REF) {
 #pragma unroll
       for (int k = 0; k < KT; ++k) u[k] = E.sU[k];
     }
-    float st = 0.f;
 #pragma unroll
-    for (int c = 0; c < (COLS + 31) / 32; ++c) {
-      float v[32];
-      tc::tmem_ld32(taddr + c * 32, v);
-      tc::tmem_ld_wait();
+    for (int q = 0; q < QHC; ++q) {
+      float st;
+      if constexpr (RELU) {
+        st = v[q * KC + KT];   // sum_k w_k m_k from the tensor core
 #pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        const int col = c * 32 + i;
-        if (col < COLS) {
-          const int kk = col % KT;
-          const float t = RELU ? fmaxf(v[i], 0.f) : sgnn_act(v[i], E.pair_act, E.yeta);
-          st = REF ? st + t : fmaf(u[kk], t, st);
-          if (kk == KT - 1) {
-            tc_emit(E, REF, st, qrow0 + col / KT, g);
-            st = 0.f;
-          }
+        for (int k = 0; k < KT; ++k) st = REF ? st + fabsf(v[q * KC + k]) : fmaf(fabsf(v[q * KC + k]), u[k], st);
+      } else {
+        st = 0.f;
+#pragma unroll
+        for (int k = 0; k < KT; ++k) {
+          const float t = sgnn_act(v[q * KC + k], E.pair_act, E.yeta);
+          st = REF ? st + t : fmaf(u[k], t, st);
         }
       }
+      const float s = tc_finish<RELU, REF, SIMK>(E, st);
+      if (g_ok && q < qmax) p[(size_t)q * E.ld] = s;
     }
   } else {
-    const int cols = QH * K;
+    const int cols = QH * KCr;
     float st = 0.f;
     int kk = 0, qq = 0;
     for (int c0 = 0; c0 < cols; c0 += 8) {
@@ -160,19 +184,28 @@ __device__ __forceinline__ void tc_epilogue_half(const TcEpi& E, uint32_t taddr,
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         if (c0 + i < cols) {
-          const float t = RELU ? fmaxf(v[i], 0.f) : sgnn_act(v[i], E.pair_act, E.yeta);
-          st = REF ? st + t : fmaf(E.sU[kk], t, st);
-          if (++kk == K) {
-            tc_emit(E, REF, st, qrow0 + qq, g);
+          if (kk < K) {
+            const float w = REF ? 1.f : E.sU[kk];
+            const float t = RELU ? fabsf(v[i]) : sgnn_act(v[i], E.pair_act, E.yeta);
+            st = fmaf(w, t, st);
+          } else {
+            st += v[i];  // the sum column (RELU only: KCr == K + 1)
+          }
+          if (++kk == KCr) {
+            const float s = tc_finish<RELU, REF, SIMK>(E, st);
+            if (g_ok && qq < qmax) p[(size_t)qq * E.ld] = s;
             st = 0.f; kk = 0; ++qq;
           }
         }
       }
     }
+    tc::tc_fence_before();
+    __syncwarp();
+    if (lane == 0) tc::mbar_arrive(t_empty);
   }
 }
 
-template <int KT, bool RELU, bool REF>
+template <int KT, bool RELU, bool REF, bool SIMK>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 allpairs_tc_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const float* __restrict__ params,
                    const __nv_bfloat16* __restrict__ Ag, const __nv_bfloat16* __restrict__ Bg,
@@ -271,6 +304,10 @@ allpairs_tc_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const flo
     float su = 0.f;
     for (int k = 0; k < G.K; ++k) su += sU[k];
     E.su = su;
+    {
+      const float hs = REF ? 0.5f * su : 0.5f;
+      E.c2 = -M.yeta * hs * hs * 1.4426950408889634f;
+    }
     const int lg = warp & 3, half = warp >> 2;
     const int QT = 2 * G.QH;
     int it = 0;
@@ -282,10 +319,7 @@ allpairs_tc_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const flo
         tc::tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + buf * TC_NPAD + half * 128;
         const int g = (gt0 + ga) * 128 + lg * 32 + lane;
-        tc_epilogue_half<KT, RELU, REF>(E, taddr, G.K, G.QH, qrow0, g);
-        tc::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) tc::mbar_arrive(t_empty + buf);
+        tc_epilogue_half<KT, RELU, REF, SIMK>(E, taddr, G.K, G.KC, G.QH, qrow0, g, t_empty + buf, lane);
       }
     }
   }

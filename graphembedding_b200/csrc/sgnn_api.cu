@@ -6,9 +6,9 @@
 #include <vector>
 
 #include "sgnn_allpairs.cuh"
-#include "sgnn_allpairs_tc.cuh"
+#include "sgnn_tc_geom.h"
 #include "sgnn_common.cuh"
-#include "sgnn_rank.cuh"
+#include "sgnn_internal.h"
 #include "sgnn_small.cuh"
 
 namespace {
@@ -221,23 +221,18 @@ int ensure_query_tables(SgnnHandle h, int64_t m) {
 }
 
 
-template <int KT, bool RELU, bool REF>
-int launch_tc(SgnnHandle h, const TcGeom& G, int grid, size_t smem, float* sim, int64_t ld, cudaStream_t st) {
-  auto kern = allpairs_tc_kernel<KT, RELU, REF>;
-  CUDA_OK(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<grid, TC_THREADS, smem, st>>>(h->M, G, h->d_params, h->d_Atc, h->d_Btc, sim, ld);
-  CUDA_OK(h, cudaGetLastError());
-  return 0;
-}
-
 // tcgen05 path of sgnn_score_all_pairs (SGNN_PREC_BF16X3 / SGNN_PREC_BF16)
 int score_all_pairs_tc(SgnnHandle h, const float* emb_q, int m, const float* emb_db, int n, float* sim,
                        int64_t ld, cudaStream_t st) {
   const ModelDev& M = h->M;
   const bool ntn = M.pair_kind == SGNN_LAYER_NTN;
   TcGeom G;
+  const bool relu = ntn && M.pair_act == SGNN_ACT_RELU;
+  const bool ref = ntn && M.ntn_mode == SGNN_NTN_REFERENCE;
+  const bool simk = M.final_act == SGNN_ACT_SIM_KERNEL;
   G.m = m; G.n = n; G.D = M.emb_dim; G.K = ntn ? M.K : 1;
-  G.QH = 128 / G.K;
+  G.KC = tc_cols_per_query(G.K, relu);
+  G.QH = 128 / G.KC;
   G.KCH = round_up(G.D + 1, 16) / 8;
   G.parts = h->cfg.precision == SGNN_PREC_BF16 ? 1 : 2;
   G.n_gtiles = (n + 127) / 128;
@@ -254,25 +249,14 @@ int score_all_pairs_tc(SgnnHandle h, const float* emb_q, int m, const float* emb
   const int64_t need_b = (int64_t)G.n_qblocks * G.parts * G.KCH * (TC_NPAD * 8);
   if (need_a > h->cap_Atc || need_b > h->cap_Btc)
     return fail(h, "tensor-core operand workspace too small: call sgnn_reserve(max_queries, max_db) first");
-  tc_prep_db_kernel<<<(G.n_gtiles * 128 * G.KCH + 255) / 256, 256, 0, st>>>(G, emb_db, h->d_Atc);
-  CUDA_OK(h, cudaGetLastError());
-  tc_prep_q_kernel<<<(m + 3) / 4, 128, 0, st>>>(M, G, h->d_params, emb_q, h->d_Btc);
-  CUDA_OK(h, cudaGetLastError());
   size_t smem = (size_t)TC_GA_MAX * tc_a_bytes(G) + (size_t)TC_STAGES * tc_b_bytes(G) + 256 + 4 * G.K;
   smem = std::max<size_t>(smem, 120 * 1024);  // one CTA per SM: each CTA owns all 512 TMEM columns
   if (smem > (size_t)h->smem_optin) return fail(h, "embedding too wide for the tensor-core all-pairs tiles");
   const int grid = g_groups * q_groups;
-  const bool relu = ntn && M.pair_act == SGNN_ACT_RELU;
-  const bool ref = ntn && M.ntn_mode == SGNN_NTN_REFERENCE;
-#define SGNN_TC(KT)                                                                                  \
-  (relu ? (ref ? launch_tc<KT, true, true>(h, G, grid, smem, sim, ld, st)                            \
-               : launch_tc<KT, true, false>(h, G, grid, smem, sim, ld, st))                          \
-        : (ref ? launch_tc<KT, false, true>(h, G, grid, smem, sim, ld, st)                           \
-               : launch_tc<KT, false, false>(h, G, grid, smem, sim, ld, st)))
-  if (G.K == 10) return SGNN_TC(10);
-  if (G.K == 16) return SGNN_TC(16);
-  return SGNN_TC(0);
-#undef SGNN_TC
+  const cudaError_t e = sgnn_tc_launch(M, G, relu, ref, simk, grid, smem, h->d_params, emb_q, emb_db, h->d_Atc,
+                                       h->d_Btc, sim, ld, st);
+  if (e != cudaSuccess) return fail(h, std::string("tensor-core all-pairs launch: ") + cudaGetErrorString(e));
+  return 0;
 }
 
 }  // namespace
@@ -430,7 +414,8 @@ int sgnn_reserve(SgnnHandle h, int64_t max_graphs, int64_t max_nodes, int64_t ma
   {
     const ModelDev& M = h->M;
     const int K = M.pair_kind == SGNN_LAYER_NTN ? M.K : 1;
-    const int64_t kch = round_up(M.emb_dim + 1, 16) / 8, qt = 2 * (128 / K);
+    const bool relu = M.pair_kind == SGNN_LAYER_NTN && M.pair_act == SGNN_ACT_RELU;
+    const int64_t kch = round_up(M.emb_dim + 1, 16) / 8, qt = 2 * (128 / tc_cols_per_query(K, relu));
     const int64_t need_a = ((max_db + 127) / 128) * 2 * kch * 1024;
     const int64_t need_b = ((max_queries + qt - 1) / qt) * 2 * kch * (TC_NPAD * 8);
     if (need_a > h->cap_Atc) {
@@ -519,15 +504,19 @@ int sgnn_score_all_pairs(SgnnHandle h, const float* emb_q, int32_t m, const floa
   return 0;
 }
 
+#define LAUNCH_OK(h, what, expr)                                                              \
+  do {                                                                                        \
+    cudaError_t e_ = (expr);                                                                  \
+    if (e_ == cudaErrorInvalidValue) return fail(h, std::string(what) + ": row too long for the shared-memory sorter"); \
+    if (e_ != cudaSuccess) return fail(h, std::string(what) + ": " + cudaGetErrorString(e_)); \
+  } while (0)
+
 int sgnn_topk(SgnnHandle h, const float* sim_dev, int32_t m, int32_t n, int64_t ld, int32_t k, int32_t* ids_dev,
               float* vals_dev, void* stream) {
   if (!h || !sim_dev || !ids_dev) return fail(h, "sgnn_topk: null argument");
   if (k < 0 || k > n) return fail(h, "Invalid k " + std::to_string(k));  // results.py:68-69
   if (m == 0 || k == 0) return 0;
-  const size_t row_bytes = (size_t)n * sizeof(float);
-  const int in_smem = row_bytes <= 48 * 1024;
-  topk_kernel<<<m, 256, in_smem ? row_bytes : 0, (cudaStream_t)stream>>>(sim_dev, nullptr, n, ld, k, in_smem, ids_dev, vals_dev);
-  CUDA_OK(h, cudaGetLastError());
+  LAUNCH_OK(h, "sgnn_topk", sgnn_launch_topk(sim_dev, nullptr, m, n, ld, k, ids_dev, vals_dev, (cudaStream_t)stream));
   return 0;
 }
 
@@ -536,11 +525,8 @@ int sgnn_topk_merge(SgnnHandle h, const float* cand_vals_dev, const int32_t* can
   if (!h || !cand_vals_dev || !cand_ids_dev || !ids_dev) return fail(h, "sgnn_topk_merge: null argument");
   if (k < 0 || k > c) return fail(h, "Invalid k " + std::to_string(k));
   if (m == 0 || k == 0) return 0;
-  const size_t row_bytes = (size_t)c * sizeof(float);
-  const int in_smem = row_bytes <= 48 * 1024;
-  topk_kernel<<<m, 256, in_smem ? row_bytes : 0, (cudaStream_t)stream>>>(cand_vals_dev, cand_ids_dev, c, c, k, in_smem,
-                                                                         ids_dev, vals_dev);
-  CUDA_OK(h, cudaGetLastError());
+  LAUNCH_OK(h, "sgnn_topk_merge",
+            sgnn_launch_topk(cand_vals_dev, cand_ids_dev, m, c, c, k, ids_dev, vals_dev, (cudaStream_t)stream));
   return 0;
 }
 
@@ -548,13 +534,7 @@ int sgnn_sort_rows(SgnnHandle h, const float* sim_dev, int32_t m, int32_t n, int
                    void* stream) {
   if (!h || !sim_dev || !ids_dev) return fail(h, "sgnn_sort_rows: null argument");
   if (m == 0 || n == 0) return 0;
-  int n_pad = 2;
-  while (n_pad < n) n_pad <<= 1;
-  const size_t bytes = (size_t)n_pad * sizeof(unsigned long long);
-  if (bytes > (size_t)h->smem_optin) return fail(h, "sgnn_sort_rows: row too long for the shared-memory sorter");
-  if (set_smem(h, sort_rows_kernel, bytes)) return 1;
-  sort_rows_kernel<<<m, 1024, bytes, (cudaStream_t)stream>>>(sim_dev, n, n_pad, ld, ids_dev);
-  CUDA_OK(h, cudaGetLastError());
+  LAUNCH_OK(h, "sgnn_sort_rows", sgnn_launch_sort_rows(sim_dev, m, n, ld, ids_dev, h->smem_optin, (cudaStream_t)stream));
   return 0;
 }
 
@@ -619,13 +599,23 @@ int sgnn_zero_grads(SgnnHandle h, void* stream) {
   return 0;
 }
 
-int sgnn_precision_at_k(SgnnHandle h, const float*, const float*, int32_t, int32_t, const int32_t*, int32_t,
-                        double*, void*) {
-  return fail(h, "sgnn_precision_at_k: not built yet");
+int sgnn_precision_at_k(SgnnHandle h, const float* true_sim_dev, const float* pred_sim_dev, int32_t m, int32_t n,
+                        const int32_t* ks_dev, int32_t n_ks, double* prec_dev, void* stream) {
+  if (!h || !true_sim_dev || !pred_sim_dev || !ks_dev || !prec_dev) return fail(h, "sgnn_precision_at_k: null argument");
+  if (m <= 0 || n <= 1 || n_ks <= 0) return fail(h, "sgnn_precision_at_k: empty problem");
+  LAUNCH_OK(h, "sgnn_precision_at_k", sgnn_launch_prec_at_k(true_sim_dev, pred_sim_dev, m, n, ks_dev, n_ks, prec_dev,
+                                                            h->smem_optin, (cudaStream_t)stream));
+  return 0;
 }
 
-int sgnn_kendall_tau(SgnnHandle h, const float*, const float*, int32_t, int32_t, int64_t*, double*, void*) {
-  return fail(h, "sgnn_kendall_tau: not built yet");
+int sgnn_kendall_tau(SgnnHandle h, const float* true_sim_dev, const float* pred_sim_dev, int32_t m, int32_t n,
+                     int64_t* counts_dev, double* tau_dev, void* stream) {
+  if (!h || !true_sim_dev || !pred_sim_dev || !counts_dev) return fail(h, "sgnn_kendall_tau: null argument");
+  if (m <= 0 || n <= 1) return fail(h, "sgnn_kendall_tau: empty problem");
+  LAUNCH_OK(h, "sgnn_kendall_tau", sgnn_launch_kendall(true_sim_dev, pred_sim_dev, m, n,
+                                                       reinterpret_cast<long long*>(counts_dev), tau_dev,
+                                                       h->smem_optin, (cudaStream_t)stream));
+  return 0;
 }
 
 // ---- host-buffer entry points ---------------------------------------------------------

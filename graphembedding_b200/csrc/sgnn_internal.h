@@ -1,0 +1,15 @@
+// Launch wrappers defined in the kernel translation units (sgnn_rank.cu, ...), called from the C ABI
+// in sgnn_api.cu.  Each returns a cudaError_t or, for argument problems, a message through *err.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+cudaError_t sgnn_launch_topk(const float* sim, const int32_t* col_ids, int m, int n, int64_t ld, int k,
+                             int32_t* ids, float* vals, cudaStream_t st);
+// returns cudaErrorInvalidValue if a row does not fit the shared-memory sorter
+cudaError_t sgnn_launch_sort_rows(const float* sim, int m, int n, int64_t ld, int32_t* ids, int smem_optin,
+                                  cudaStream_t st);
+cudaError_t sgnn_launch_prec_at_k(const float* true_sim, const float* pred_sim, int m, int n, const int32_t* ks,
+                                  int n_ks, double* prec, int smem_optin, cudaStream_t st);
+cudaError_t sgnn_launch_kendall(const float* true_sim, const float* pred_sim, int m, int n, long long* counts,
+                                double* tau, int smem_optin, cudaStream_t st);

@@ -1,0 +1,58 @@
+// Translation unit of the ranking / metric kernels (sgnn_rank.cuh).
+#include "sgnn_rank.cuh"
+#include "sgnn_internal.h"
+
+static int pad_pow2(int n) {
+  int p = 2;
+  while (p < n) p <<= 1;
+  return p;
+}
+
+cudaError_t sgnn_launch_topk(const float* sim, const int32_t* col_ids, int m, int n, int64_t ld, int k,
+                             int32_t* ids, float* vals, cudaStream_t st) {
+  if (k <= 256) {
+    topk_select_kernel<<<m, 256, 0, st>>>(sim, col_ids, n, ld, k, ids, vals);
+  } else {
+    const size_t row_bytes = (size_t)n * sizeof(float);
+    const int in_smem = row_bytes <= 48 * 1024;
+    topk_kernel<<<m, 256, in_smem ? row_bytes : 0, st>>>(sim, col_ids, n, ld, k, in_smem, ids, vals);
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t sgnn_launch_sort_rows(const float* sim, int m, int n, int64_t ld, int32_t* ids, int smem_optin,
+                                  cudaStream_t st) {
+  const int n_pad = pad_pow2(n);
+  const size_t bytes = (size_t)n_pad * sizeof(unsigned long long);
+  if (bytes > (size_t)smem_optin) return cudaErrorInvalidValue;
+  cudaError_t e = cudaFuncSetAttribute(sort_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  if (e != cudaSuccess) return e;
+  sort_rows_kernel<<<m, 1024, bytes, st>>>(sim, n, n_pad, ld, ids);
+  return cudaGetLastError();
+}
+
+cudaError_t sgnn_launch_prec_at_k(const float* true_sim, const float* pred_sim, int m, int n, const int32_t* ks,
+                                  int n_ks, double* prec, int smem_optin, cudaStream_t st) {
+  const int n_pad = pad_pow2(n);
+  const size_t bytes = (size_t)n_pad * 8 + (size_t)(2 * n + 2) * 4;
+  if (bytes > (size_t)smem_optin) return cudaErrorInvalidValue;
+  cudaError_t e = cudaFuncSetAttribute(prec_at_k_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  if (e != cudaSuccess) return e;
+  e = cudaMemsetAsync(prec, 0, (size_t)n_ks * sizeof(double), st);
+  if (e != cudaSuccess) return e;
+  prec_at_k_kernel<<<m, 1024, bytes, st>>>(true_sim, pred_sim, n, n_pad, ks, n_ks,
+                                          reinterpret_cast<unsigned long long*>(prec));
+  prec_finish_kernel<<<(n_ks + 255) / 256, 256, 0, st>>>(ks, n_ks, m, prec);
+  return cudaGetLastError();
+}
+
+cudaError_t sgnn_launch_kendall(const float* true_sim, const float* pred_sim, int m, int n, long long* counts,
+                                double* tau, int smem_optin, cudaStream_t st) {
+  const int n_pad = pad_pow2(n);
+  const size_t bytes = (size_t)n_pad * 8;
+  if (n_pad > 16384 || bytes > (size_t)smem_optin) return cudaErrorInvalidValue;
+  cudaError_t e = cudaFuncSetAttribute(kendall_tau_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  if (e != cudaSuccess) return e;
+  kendall_tau_kernel<<<m, 1024, bytes, st>>>(true_sim, pred_sim, n, n_pad, counts, tau);
+  return cudaGetLastError();
+}

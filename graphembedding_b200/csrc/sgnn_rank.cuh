@@ -66,6 +66,87 @@ topk_kernel(const float* __restrict__ sim, const int32_t* __restrict__ col_ids, 
   }
 }
 
+__device__ __forceinline__ float rank_key_score(unsigned long long key) {
+  unsigned int u = (unsigned int)(key >> 32);
+  u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+  return __uint_as_float(u);
+}
+
+// Top-k for k <= 256, two streaming passes over the row instead of k.  Pass 1: every thread
+// keeps the largest key of its strided slice; the k-th largest of those 256 slice maxima is a
+// lower bound of the k-th largest key of the row (k distinct elements are >= it).  Pass 2 gathers
+// the (few) keys >= that bound into shared memory, where each candidate finds its rank by
+// counting.  Falls back to the k-round selection when more than TOPK_CAND keys survive.
+constexpr int TOPK_CAND = 1024;
+
+__global__ void __launch_bounds__(256)
+topk_select_kernel(const float* __restrict__ sim, const int32_t* __restrict__ col_ids, int n, int64_t ld,
+                   int k, int32_t* __restrict__ ids, float* __restrict__ vals) {
+  __shared__ unsigned long long s_max[256];
+  __shared__ unsigned long long s_cand[TOPK_CAND];
+  __shared__ unsigned long long s_red[32];
+  __shared__ unsigned long long s_thr;
+  __shared__ int s_cnt;
+  const float* r = sim + (size_t)blockIdx.x * ld;
+  const int32_t* cid = col_ids ? col_ids + (size_t)blockIdx.x * ld : nullptr;
+  const int tid = threadIdx.x;
+  unsigned long long best = 0ull;
+#pragma unroll 8
+  for (int i = tid; i < n; i += 256) {
+    const unsigned long long key = rank_key(r[i], cid ? cid[i] : i);
+    best = key > best ? key : best;
+  }
+  s_max[tid] = best;
+  if (tid == 0) s_cnt = 0;
+  __syncthreads();
+  if (best != 0ull) {
+    int above = 0;
+#pragma unroll 8
+    for (int j = 0; j < 256; ++j) above += s_max[j] > best ? 1 : 0;
+    if (above == k - 1) s_thr = best;   // keys are unique: exactly one thread
+  }
+  __syncthreads();
+  const unsigned long long thr = s_thr;
+#pragma unroll 8
+  for (int i = tid; i < n; i += 256) {
+    const unsigned long long key = rank_key(r[i], cid ? cid[i] : i);
+    if (key >= thr) {
+      const int pos = atomicAdd(&s_cnt, 1);
+      if (pos < TOPK_CAND) s_cand[pos] = key;
+    }
+  }
+  __syncthreads();
+  const int c = s_cnt;
+  int32_t* out_i = ids + (size_t)blockIdx.x * k;
+  float* out_v = vals ? vals + (size_t)blockIdx.x * k : nullptr;
+  if (c <= TOPK_CAND) {
+    for (int j = tid; j < c; j += 256) {
+      const unsigned long long key = s_cand[j];
+      int rank = 0;
+      for (int t = 0; t < c; ++t) rank += s_cand[t] > key ? 1 : 0;
+      if (rank < k) {
+        out_i[rank] = (int)(key & 0xffffffffull);
+        if (out_v) out_v[rank] = rank_key_score(key);
+      }
+    }
+    return;
+  }
+  unsigned long long prev = ~0ull;   // pathological rows: k selection rounds over keys >= thr
+  for (int round = 0; round < k; ++round) {
+    unsigned long long bk = 0ull;
+    for (int i = tid; i < n; i += 256) {
+      const unsigned long long key = rank_key(r[i], cid ? cid[i] : i);
+      if (key < prev && key > bk) bk = key;
+    }
+    bk = block_max_u64(bk, s_red);
+    if (tid == 0) {
+      out_i[round] = (int)(bk & 0xffffffffull);
+      if (out_v) out_v[round] = rank_key_score(bk);
+    }
+    prev = bk;
+  }
+}
+
 // Full descending ranking of one row per CTA: bitonic sort of 64-bit keys in shared memory.
 __global__ void __launch_bounds__(1024)
 sort_rows_kernel(const float* __restrict__ sim, int n, int n_pad, int64_t ld,
@@ -88,4 +169,205 @@ sort_rows_kernel(const float* __restrict__ sim, int n, int n_pad, int64_t ld,
   }
   for (int i = threadIdx.x; i < n; i += blockDim.x)
     ids[(size_t)blockIdx.x * n + i] = (int)(s_keys[i] & 0xffffffffull);
+}
+
+// ---------------------------------------------------------------------------------------
+// Ranking metrics, one CTA (1024 threads) per query row, everything in shared memory.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned int orderable_u32(float f) {
+  f += 0.f;
+  const unsigned int u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+// in-place bitonic sort of n_pad (power of two) 64-bit keys; DESC selects the direction
+template <bool DESC>
+__device__ __forceinline__ void block_bitonic_u64(unsigned long long* s_keys, int n_pad) {
+  for (int size = 2; size <= n_pad; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      for (int t = threadIdx.x; t < (n_pad >> 1); t += blockDim.x) {
+        const int lo = 2 * t - (t & (stride - 1));
+        const int hi = lo + stride;
+        const bool first = (lo & size) == 0;
+        const unsigned long long a = s_keys[lo], b = s_keys[hi];
+        if (((a < b) == first) == DESC) { s_keys[lo] = b; s_keys[hi] = a; }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// precision@k (src/metrics.py:14-35 with results.py:51-82 top-k semantics): the true top-k is
+// tie-inclusive, the predicted top-k is the first k of the descending ranking.  Item j is in
+// both sets iff k >= need_j = max(tie-inclusive true position, predicted position), so ONE pass
+// gives |true_topk(k) & pred_topk(k)| for every k.  hit_sum[i] (u64) += hits of this row at ks[i].
+// smem: keys[n_pad] u64 | pos[n] i32 | hist[n + 2] i32
+__global__ void __launch_bounds__(1024)
+prec_at_k_kernel(const float* __restrict__ true_sim, const float* __restrict__ pred_sim, int n, int n_pad,
+                 const int32_t* __restrict__ ks, int n_ks, unsigned long long* __restrict__ hit_sum) {
+  extern __shared__ __align__(16) unsigned long long s_keys[];
+  int* s_pos = reinterpret_cast<int*>(s_keys + n_pad);
+  int* s_hist = s_pos + n;
+  __shared__ int s_warp[32];
+  const float* t = true_sim + (size_t)blockIdx.x * n;
+  const float* p = pred_sim + (size_t)blockIdx.x * n;
+  const int tid = threadIdx.x;
+  for (int i = tid; i < n_pad; i += blockDim.x) s_keys[i] = i < n ? rank_key(t[i], i) : 0ull;
+  for (int i = tid; i < n + 2; i += blockDim.x) s_hist[i] = 0;
+  __syncthreads();
+  block_bitonic_u64<true>(s_keys, n_pad);
+  // tie-inclusive position = 1 + start of the run of equal scores: lower bound by binary search
+  for (int i = tid; i < n; i += blockDim.x) {
+    const unsigned int sc = (unsigned int)(s_keys[i] >> 32);
+    int lo = 0, hi = i;   // first index whose score == sc (scores descending)
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if ((unsigned int)(s_keys[mid] >> 32) > sc) lo = mid + 1; else hi = mid;
+    }
+    s_pos[(int)(s_keys[i] & 0xffffffffull)] = lo + 1;
+  }
+  __syncthreads();
+  for (int i = tid; i < n_pad; i += blockDim.x) s_keys[i] = i < n ? rank_key(p[i], i) : 0ull;
+  __syncthreads();
+  block_bitonic_u64<true>(s_keys, n_pad);
+  for (int i = tid; i < n; i += blockDim.x) {
+    const int j = (int)(s_keys[i] & 0xffffffffull);
+    atomicAdd(&s_hist[max(s_pos[j], i + 1)], 1);
+  }
+  __syncthreads();
+  // inclusive prefix sum of hist[0..n] in place (chunk per thread + block scan of chunk sums)
+  const int per = (n + 1 + blockDim.x - 1) / blockDim.x;
+  const int b0 = tid * per, b1 = min(n + 1, b0 + per);
+  int sum = 0;
+  for (int i = b0; i < b1; ++i) sum += s_hist[i];
+  int incl = sum;
+  const int lane = tid & 31, warp = tid >> 5;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    int w = s_warp[lane];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, w, o);
+      if (lane >= o) w += v;
+    }
+    s_warp[lane] = w;
+  }
+  __syncthreads();
+  int run = incl - sum + (warp > 0 ? s_warp[warp - 1] : 0);
+  for (int i = b0; i < b1; ++i) { run += s_hist[i]; s_hist[i] = run; }
+  __syncthreads();
+  for (int i = tid; i < n_ks; i += blockDim.x) atomicAdd(&hit_sum[i], (unsigned long long)s_hist[ks[i]]);
+}
+
+// prec[i] = hit_sum[i] / (ks[i] * m), in place over the u64 counters
+__global__ void prec_finish_kernel(const int32_t* __restrict__ ks, int n_ks, int m, double* prec) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_ks) return;
+  const unsigned long long h = reinterpret_cast<unsigned long long*>(prec)[i];
+  prec[i] = (double)h / ((double)ks[i] * (double)m);
+}
+
+__device__ __forceinline__ long long block_sum_i64(long long v, long long* s_red) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  __syncthreads();
+  if (lane == 0) s_red[warp] = v;
+  __syncthreads();
+  v = lane < nw ? s_red[lane] : 0ll;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Kendall tau-b of (true row, predicted row), exact integer pair counts (Knight's algorithm):
+// sort by (x, y); tie pairs from run lengths; discordant pairs = strict inversions of the y
+// sequence, counted by a bottom-up merge sort whose merges are rank computations by binary
+// search.  counts = {concordant, discordant, ties only in x, ties only in y, joint ties}.
+// smem: keys[n_pad] u64, later re-used as two u32 ping-pong arrays of n_pad entries each.
+__global__ void __launch_bounds__(1024)
+kendall_tau_kernel(const float* __restrict__ true_sim, const float* __restrict__ pred_sim, int n, int n_pad,
+                   long long* __restrict__ counts, double* __restrict__ tau) {
+  extern __shared__ __align__(16) unsigned long long s_keys[];
+  __shared__ long long s_red[32];
+  const float* x = true_sim + (size_t)blockIdx.x * n;
+  const float* y = pred_sim + (size_t)blockIdx.x * n;
+  const int tid = threadIdx.x;
+  for (int i = tid; i < n_pad; i += blockDim.x)
+    s_keys[i] = i < n ? (((unsigned long long)orderable_u32(x[i]) << 32) | orderable_u32(y[i])) : ~0ull;
+  __syncthreads();
+  block_bitonic_u64<false>(s_keys, n_pad);   // ascending; padding (all ones) goes last
+  // tie pairs: sum_i (#elements after i inside i's run) = sum_i (upper_bound(key_i) - 1 - i)
+  long long nx = 0, nxy = 0;
+  for (int i = tid; i < n; i += blockDim.x) {
+    const unsigned long long k = s_keys[i];
+    const unsigned int kx = (unsigned int)(k >> 32);
+    int lo = i + 1, hi = n;
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if ((unsigned int)(s_keys[mid] >> 32) > kx) hi = mid; else lo = mid + 1; }
+    nx += lo - 1 - i;
+    lo = i + 1; hi = n;
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (s_keys[mid] > k) hi = mid; else lo = mid + 1; }
+    nxy += lo - 1 - i;
+  }
+  nx = block_sum_i64(nx, s_red);
+  nxy = block_sum_i64(nxy, s_red);
+  // compact the y keys (low words) of the sorted sequence into a u32 array over the same memory
+  unsigned int* bufA = reinterpret_cast<unsigned int*>(s_keys);
+  unsigned int* bufB = bufA + n_pad;
+  {
+    unsigned int tmp[16];   // n_pad <= 16384 = 16 * 1024
+    int c = 0;
+    for (int i = tid; i < n_pad; i += blockDim.x) tmp[c++] = (unsigned int)(s_keys[i] & 0xffffffffull);
+    __syncthreads();
+    c = 0;
+    for (int i = tid; i < n_pad; i += blockDim.x) bufA[i] = tmp[c++];
+    __syncthreads();
+  }
+  long long dis = 0;
+  unsigned int* src = bufA;
+  unsigned int* dst = bufB;
+  for (int w = 1; w < n; w <<= 1) {
+    for (int i = tid; i < n; i += blockDim.x) {
+      const int blk = i / (2 * w) * (2 * w);
+      const int mid = min(blk + w, n), end = min(blk + 2 * w, n);
+      const unsigned int v = src[i];
+      if (i < mid) {              // left element: goes after the right elements strictly below it
+        int lo = mid, hi = end;
+        while (lo < hi) { const int md = (lo + hi) >> 1; if (src[md] < v) lo = md + 1; else hi = md; }
+        dst[i + (lo - mid)] = v;
+      } else {                    // right element: goes after the left elements <= it (stable)
+        int lo = blk, hi = mid;
+        while (lo < hi) { const int md = (lo + hi) >> 1; if (src[md] <= v) lo = md + 1; else hi = md; }
+        dst[(i - mid) + lo] = v;
+        dis += mid - lo;          // left elements strictly greater: inversions
+      }
+    }
+    __syncthreads();
+    unsigned int* sw = src; src = dst; dst = sw;
+  }
+  dis = block_sum_i64(dis, s_red);
+  long long ny = 0;
+  for (int i = tid; i < n; i += blockDim.x) {
+    const unsigned int v = src[i];
+    int lo = i + 1, hi = n;
+    while (lo < hi) { const int md = (lo + hi) >> 1; if (src[md] > v) hi = md; else lo = md + 1; }
+    ny += lo - 1 - i;
+  }
+  ny = block_sum_i64(ny, s_red);
+  if (tid == 0) {
+    const long long tot = (long long)n * (n - 1) / 2;
+    const long long con = tot - nx - ny + nxy - dis;
+    long long* c = counts + (size_t)blockIdx.x * 5;
+    c[0] = con; c[1] = dis; c[2] = nx - nxy; c[3] = ny - nxy; c[4] = nxy;
+    if (tau) {
+      const double den = sqrt((double)(con + dis + (nx - nxy))) * sqrt((double)(con + dis + (ny - nxy)));
+      tau[blockIdx.x] = den > 0.0 ? (double)(con - dis) / den : nan("");
+    }
+  }
 }

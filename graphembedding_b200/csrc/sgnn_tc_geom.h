@@ -1,0 +1,33 @@
+// Tile geometry of the tensor-core all-pairs scorer, shared by the API translation unit (sizes the
+// operand workspaces, plans the grid) and sgnn_tc.cu (the kernels).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "sgnn_common.cuh"
+
+struct TcGeom {
+  int m, n, D, K;
+  int KC;          // accumulator columns per query: K, or K+1 with the |x| form of relu (see below)
+  int QH;          // queries per column half (= floor(128 / KC)); a q-block holds 2*QH queries
+  int KCH;         // 16-byte K chunks per part (= round_up(D+1,16)/8)
+  int parts;       // 1 = bf16, 2 = bf16x3 (hi + lo)
+  int n_gtiles, n_qblocks;
+  int GA;          // database tiles kept resident per CTA
+  int q_groups, qb_per_group;
+};
+
+constexpr int TC_NPAD = 256;     // MMA N: half h of the queries lives in columns [128h, 128h + QH*K)
+constexpr int TC_STAGES = 3;
+constexpr int TC_GA_MAX = 4;
+constexpr int TC_THREADS = 320;
+
+__host__ __device__ inline int tc_cols_per_query(int K, bool relu) { return relu ? K + 1 : K; }
+__host__ __device__ inline int tc_a_bytes(const TcGeom& G) { return G.parts * G.KCH * 128 * 16; }
+__host__ __device__ inline int tc_b_bytes(const TcGeom& G) { return G.parts * G.KCH * TC_NPAD * 16; }
+
+
+// prep kernels + allpairs_tc_kernel on `st` (defined in sgnn_tc.cu)
+cudaError_t sgnn_tc_launch(const ModelDev& M, const TcGeom& G, bool relu, bool ref, bool simk, int grid, size_t smem,
+                           const float* params, const float* emb_q, const float* emb_db, void* A_ws, void* B_ws,
+                           float* sim, int64_t ld, cudaStream_t st);

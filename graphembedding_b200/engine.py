@@ -146,6 +146,33 @@ class SgnnEngine(object):
         self.launches += 1
         return ids
 
+    def precision_at_ks(self, true_sim, pred_sim, ks, stream=None):
+        """Mean over queries of |true_topk_incl(k) & pred_topk(k)| / k for every k in ks
+        (src/metrics.py:14-35); true_sim / pred_sim: [m, n] float32 device tensors, higher =
+        more similar."""
+        import torch
+        m, n = pred_sim.shape
+        assert tuple(true_sim.shape) == (m, n) and true_sim.is_contiguous() and pred_sim.is_contiguous()
+        ks_d = torch.as_tensor(np.asarray(ks, np.int32), device=self.device)
+        out = torch.empty(len(ks), dtype=torch.float64, device=self.device)
+        check(self.h, lib().sgnn_precision_at_k(self.h, _ptr(true_sim), _ptr(pred_sim), m, n, _ptr(ks_d),
+                                                len(ks), _ptr(out), _stream_ptr(stream)))
+        self.launches += 2
+        return out
+
+    def kendall_tau(self, true_sim, pred_sim, stream=None):
+        """Per-query Kendall tau-b and the exact pair counts [m, 5] = (concordant, discordant,
+        ties only in true, ties only in pred, joint ties)."""
+        import torch
+        m, n = pred_sim.shape
+        assert tuple(true_sim.shape) == (m, n) and true_sim.is_contiguous() and pred_sim.is_contiguous()
+        counts = torch.empty((m, 5), dtype=torch.int64, device=self.device)
+        tau = torch.empty(m, dtype=torch.float64, device=self.device)
+        check(self.h, lib().sgnn_kendall_tau(self.h, _ptr(true_sim), _ptr(pred_sim), m, n, _ptr(counts),
+                                             _ptr(tau), _stream_ptr(stream)))
+        self.launches += 1
+        return tau, counts
+
     def train_step(self, batch, g1, g2, target_sim, global_batch=None, target_sum=None,
                    target_sqsum=None, loss=None, stream=None):
         """Adds the MSE-part gradient of these pairs into the grad buffer; loss[0] += mse part."""

@@ -194,3 +194,56 @@ def test_tensor_core_all_pairs_matches_fp32_path(cfg, ntn_mode):
     ref = out['fp32']
     assert np.max(np.abs(out['bf16x3'] - ref) / np.maximum(np.abs(ref), 1e-3)) <= 2e-4
     assert np.max(np.abs(out['bf16'] - ref) / np.maximum(np.abs(ref), 1e-2)) <= 1e-1
+
+
+def test_topk_large_rows_random_and_pathological():
+    """Two-pass select path (k <= 256) on long rows, incl. a row whose large values all sit in one
+    thread's strided slice (forces the k-round fallback) and k > 256 (selection-round kernel)."""
+    eng, *_ = _setup('default', 8)
+    rng = np.random.default_rng(2)
+    m, n = 5, 256 * 1100
+    sim = rng.random((m, n)).astype(np.float32) * 0.5
+    sim[1, ::256] = 0.9 + 0.05 * rng.random(1100).astype(np.float32)
+    sim[2, :] = 0.25
+    d = torch.as_tensor(sim, device=eng.device)
+    ref = np.argsort(sim, kind='mergesort', axis=1)[:, ::-1]
+    for k in (1, 2, 10, 64, 256, 300):
+        ids, vals = eng.topk(d, k)
+        assert np.array_equal(ids.cpu().numpy(), ref[:, :k]), k
+        assert np.array_equal(vals.cpu().numpy(), np.take_along_axis(sim, ref[:, :k], 1)), k
+
+
+@pytest.mark.parametrize('n', [2, 37, 1000, 10000])
+def test_precision_at_k_and_kendall_tau_on_device(n):
+    """prec@k hit counts and Kendall concordance counts are integers: bit-exact vs the oracle
+    (metrics.py:14-35 / results.py:51-82 restated; tau-b pinned to scipy.stats.kendalltau --
+    build-defined, parity unpinned by the reference)."""
+    from scipy.stats import kendalltau
+    eng, *_ = _setup('default', 8)
+    rng = np.random.default_rng(n)
+    m = 6
+    true = (rng.integers(0, max(2, n // 3), size=(m, n)) / 7.0).astype(np.float32)   # many ties
+    pred = rng.random((m, n)).astype(np.float32)
+    pred[:, : n // 2] = np.round(pred[:, : n // 2], 2)                               # some ties
+    if m > 2:
+        true[2, :] = 0.5     # fully tied truth
+        pred[3, :] = pred[3, 0]
+    ks = list(range(1, n)) if n <= 1000 else [1, 2, 5, 10, 100, n - 1]
+    td, pd_ = torch.as_tensor(true, device=eng.device), torch.as_tensor(pred, device=eng.device)
+    if n > 1:
+        if ks:
+            got = eng.precision_at_ks(td, pd_, ks).cpu().numpy()
+            ts, ps = O.sort_id_mat_sim(true), O.sort_id_mat_sim(pred)
+            ref = O.precision_at_ks(ts, true, ps, pred, ks)
+            assert np.allclose(got, ref, rtol=0, atol=1e-12)
+        tau, counts = eng.kendall_tau(td, pd_)
+        counts = counts.cpu().numpy()
+        for i in range(m):
+            if n <= 1000:      # the O(n^2) oracle count
+                assert tuple(counts[i]) == tuple(O.kendall_tau_counts(true[i], pred[i])), i
+            assert counts[i].sum() == n * (n - 1) // 2
+            ref_tau = kendalltau(true[i], pred[i]).statistic
+            if np.isnan(ref_tau):
+                assert np.isnan(tau[i].item())
+            else:
+                assert abs(tau[i].item() - ref_tau) <= 1e-12

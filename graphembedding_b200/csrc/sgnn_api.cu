@@ -444,10 +444,17 @@ int sgnn_embed_graphs(SgnnHandle h, const SgnnGraphBatch* b, float* emb_dev, voi
   if (b->n_graphs == 0) return 0;
   if (b->max_nodes > 32)
     return fail(h, "graphs with more than 32 nodes need the large-graph path (not built yet)");
+  cudaStream_t st = (cudaStream_t)stream;
+  {
+    const cudaError_t e = sgnn_launch_embed_tile(h->M, to_dev(b), b->max_nodes, h->d_params, emb_dev, h->sm_count,
+                                                 h->smem_optin, st);
+    if (e == cudaSuccess) return 0;
+    if (e != cudaErrorInvalidValue) return fail(h, std::string("sgnn_embed_graphs: ") + cudaGetErrorString(e));
+    cudaGetLastError();   // model too wide for the tile kernel: warp-per-graph kernel below
+  }
   const int v = b->max_nodes <= 16 ? 0 : 1;
   const int wpb = h->embed_wpb[v];
   const int blocks = std::min((b->n_graphs + wpb - 1) / wpb, h->sm_count * 4);
-  cudaStream_t st = (cudaStream_t)stream;
   if (v == 0)
     embed_kernel<16><<<blocks, wpb * 32, h->embed_smem[0], st>>>(h->M, to_dev(b), h->d_params, emb_dev);
   else

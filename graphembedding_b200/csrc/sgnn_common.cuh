@@ -68,3 +68,4 @@ __device__ __forceinline__ float warp_sum(float v) {
 }
 
 static inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
+__host__ __device__ __forceinline__ int round_up4(int x) { return (x + 3) & ~3; }

@@ -3,6 +3,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include "sgnn_common.cuh"
 
 cudaError_t sgnn_launch_topk(const float* sim, const int32_t* col_ids, int m, int n, int64_t ld, int k,
                              int32_t* ids, float* vals, cudaStream_t st);
@@ -13,3 +14,8 @@ cudaError_t sgnn_launch_prec_at_k(const float* true_sim, const float* pred_sim, 
                                   int n_ks, double* prec, int smem_optin, cudaStream_t st);
 cudaError_t sgnn_launch_kendall(const float* true_sim, const float* pred_sim, int m, int n, long long* counts,
                                 double* tau, int smem_optin, cudaStream_t st);
+
+// node-per-thread embedding of small graphs (max_nodes <= 32); cudaErrorInvalidValue if the model
+// does not fit this kernel's shared memory (the caller then uses the warp-per-graph kernel)
+cudaError_t sgnn_launch_embed_tile(const ModelDev& M, const BatchDev& B, int max_nodes, const float* params,
+                                   float* emb, int sm_count, int smem_optin, cudaStream_t st);

@@ -1,0 +1,300 @@
+// Node-per-thread embedding kernel for small graphs (N <= 32).
+//
+// A warp owns a TILE of up to 32 consecutive node rows = `gpw` whole graphs of the block-diagonal
+// batch (gpw = floor(32 / max_nodes)); lane l is node l of the tile.  Every thread carries its
+// node's output row in registers (JT accumulators at a time):
+//   layer 0 (one-hot X, graphs.py:55-62):  out_i = act(sum_e A_hat[i,e] * W0[label(e), :] + b)   -- a row gather of W0
+//   GCN l>0 (layers.py:91-118):            T_i = H_i . W  (own row x broadcast weight rows), then
+//                                          out_i = act(sum_e A_hat[i,e] * T_e + b) through shared memory
+//   Dense (layers.py:192-205):             out_i = act(H_i . W + b)
+// so the feature x weight products run at full lane utilisation with no per-row predication, and
+// the only cross-lane traffic is the neighbour gather (warp-synchronous shared memory).  Weights
+// are re-staged once per CTA in a padded, 16-byte aligned layout (EmbPlan) so that weight rows are
+// read as broadcast float4.  Pooling (Padding / Average / Attention, layers.py:136-160, 223-227)
+// is done per graph by the same warp.
+#pragma once
+#include "sgnn_common.cuh"
+
+constexpr int TILE_CSR_CAP = 320;   // staged nnz per tile (falls back to global reads beyond)
+constexpr int TILE_WARPS = 8;
+
+struct EmbPlan {
+  int w_s[SGNN_MAX_LAYERS];    // offset (floats) of layer l's padded weight matrix in shared memory
+  int b_s[SGNN_MAX_LAYERS];    // offset of the padded bias (zeros when the layer has none)
+  int ldw[SGNN_MAX_LAYERS];    // padded row stride of the weight matrix
+  int att_s;                   // attention weights [d][d] (row stride d), -1 if unused
+  int w_floats;                // total staged floats (multiple of 4)
+  int ldh;                     // row stride of the per-warp activation buffers (ldh % 8 == 4)
+  int gpw;                     // graphs per warp tile
+  int warp_floats;             // per-warp shared memory (floats)
+};
+
+inline EmbPlan make_emb_plan(const ModelDev& M, int max_nodes) {
+  EmbPlan P;
+  int o = 0, dmax = 4;
+  for (int l = 0; l < M.n_node; ++l) {
+    const LayerDev& L = M.L[l];
+    int ldw = round_up(L.dout, 4);
+    if (l == 0 && ldw % 8 == 0) ldw += 4;   // gathered rows: spread consecutive labels over the banks
+    const int rows = l == 0 ? L.din : round_up(L.din, 4);
+    P.ldw[l] = ldw; P.w_s[l] = o; o += rows * ldw;
+    P.b_s[l] = o; o += round_up(L.dout, 4);
+    dmax = dmax > L.dout ? dmax : L.dout;
+  }
+  P.att_s = -1;
+  if (M.pool_kind == SGNN_LAYER_ATTENTION) { P.att_s = o; o += round_up(M.node_dim * M.node_dim, 4); }
+  P.w_floats = round_up(o, 4);
+  P.ldh = round_up(dmax, 4);
+  if (P.ldh % 8 == 0) P.ldh += 4;
+  int gpw = max_nodes > 0 ? 32 / max_nodes : 1;
+  P.gpw = gpw < 1 ? 1 : (gpw > 16 ? 16 : gpw);
+  P.warp_floats = 2 * 32 * P.ldh + 2 * TILE_CSR_CAP + 32 + 32;
+  return P;
+}
+
+__device__ __forceinline__ void tile_stage_weights(const ModelDev& M, const EmbPlan& P, const float* __restrict__ params,
+                                                   float* s_w) {
+  for (int i = threadIdx.x; i < P.w_floats; i += blockDim.x) s_w[i] = 0.f;
+  __syncthreads();
+  for (int l = 0; l < M.n_node; ++l) {
+    const LayerDev& L = M.L[l];
+    for (int i = threadIdx.x; i < L.din * L.dout; i += blockDim.x) {
+      const int k = i / L.dout, j = i - k * L.dout;
+      s_w[P.w_s[l] + k * P.ldw[l] + j] = params[L.w_off + i];
+    }
+    if (L.bias)
+      for (int j = threadIdx.x; j < L.dout; j += blockDim.x) s_w[P.b_s[l] + j] = params[L.b_off + j];
+  }
+  if (P.att_s >= 0)
+    for (int i = threadIdx.x; i < M.node_dim * M.node_dim; i += blockDim.x) s_w[P.att_s + i] = params[M.pool_w_off + i];
+  __syncthreads();
+}
+
+struct TileCtx {
+  int n_rows;          // node rows in this tile (<= 32)
+  bool on;             // this lane owns a node
+  int g_off;           // lane of the first node of my graph
+  int e0, e1;          // my row's entries, relative to the tile's first entry
+  const int* col;      // staged (shared) or global, indexed relative to the tile's first entry
+  const float* val;
+  const int* lab;      // [32] labels of the tile's nodes (shared)
+};
+
+template <int JT>
+__device__ __forceinline__ void tile_store_row(float* dst, const float (&acc)[JT], const float* bias, int j0, int dout,
+                                               int act) {
+#pragma unroll
+  for (int jj = 0; jj < JT; jj += 4) {
+    if (j0 + jj < dout) {   // warp-uniform
+      float4 o;
+      float* op = reinterpret_cast<float*>(&o);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const int j = j0 + jj + c;
+        op[c] = j < dout ? sgnn_act(acc[jj + c] + (bias ? bias[j] : 0.f), act, 0.f) : 0.f;
+      }
+      *reinterpret_cast<float4*>(dst + j0 + jj) = o;
+    }
+  }
+}
+
+// acc[jj] += sum_e val[e] * Src[row(e)][j0 + jj]; rows are weight rows (by label) or neighbour rows
+template <int JT, bool BY_LABEL>
+__device__ __forceinline__ void tile_gather(const TileCtx& T, const float* Src, int ld, int j0, int dout,
+                                            float (&acc)[JT]) {
+  for (int e = T.e0; e < T.e1; ++e) {
+    const int nb = T.g_off + T.col[e];
+    const float v = T.val[e];
+    const float* row = Src + (BY_LABEL ? T.lab[nb] : nb) * ld + j0;
+#pragma unroll
+    for (int jj = 0; jj < JT; jj += 4) {
+      if (j0 + jj < dout) {
+        const float4 w = *reinterpret_cast<const float4*>(row + jj);
+        acc[jj + 0] = fmaf(v, w.x, acc[jj + 0]);
+        acc[jj + 1] = fmaf(v, w.y, acc[jj + 1]);
+        acc[jj + 2] = fmaf(v, w.z, acc[jj + 2]);
+        acc[jj + 3] = fmaf(v, w.w, acc[jj + 3]);
+      }
+    }
+  }
+}
+
+// acc[jj] = sum_k hrow[k] * W[k][j0 + jj]   (own row x broadcast weight rows)
+template <int JT>
+__device__ __forceinline__ void tile_row_gemm(const float* hrow, int din, const float* W, int ldw, int j0, int dout,
+                                              float (&acc)[JT]) {
+  for (int k = 0; k < din; k += 4) {
+    const float4 h4 = *reinterpret_cast<const float4*>(hrow + k);
+    const float hk[4] = {h4.x, h4.y, h4.z, h4.w};
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk) {
+      const float* wr = W + (k + kk) * ldw + j0;
+#pragma unroll
+      for (int jj = 0; jj < JT; jj += 4) {
+        if (j0 + jj < dout) {
+          const float4 w = *reinterpret_cast<const float4*>(wr + jj);
+          acc[jj + 0] = fmaf(hk[kk], w.x, acc[jj + 0]);
+          acc[jj + 1] = fmaf(hk[kk], w.y, acc[jj + 1]);
+          acc[jj + 2] = fmaf(hk[kk], w.z, acc[jj + 2]);
+          acc[jj + 3] = fmaf(hk[kk], w.w, acc[jj + 3]);
+        }
+      }
+    }
+  }
+}
+
+// all node layers of one tile; returns the buffer holding the last layer's output rows
+template <int JT>
+__device__ __forceinline__ float* tile_node_layers(const ModelDev& M, const EmbPlan& P, const TileCtx& T,
+                                                   const float* s_w, float* bufA, float* bufB, int lane) {
+  const int ldh = P.ldh;
+  float* cur = bufA;   // holds H (input of the layer); other = scratch / output
+  float* oth = bufB;
+  for (int l = 0; l < M.n_node; ++l) {
+    const LayerDev& L = M.L[l];
+    const float* W = s_w + P.w_s[l];
+    const float* b = s_w + P.b_s[l];
+    if (l == 0) {
+      if (T.on)
+        for (int j0 = 0; j0 < L.dout; j0 += JT) {
+          float acc[JT];
+#pragma unroll
+          for (int jj = 0; jj < JT; ++jj) acc[jj] = 0.f;
+          tile_gather<JT, true>(T, W, P.ldw[0], j0, L.dout, acc);
+          tile_store_row<JT>(cur + lane * ldh, acc, b, j0, L.dout, L.act);
+        }
+      __syncwarp();
+      continue;
+    }
+    const bool gcn = L.kind == SGNN_LAYER_GCN;
+    if (T.on)
+      for (int j0 = 0; j0 < L.dout; j0 += JT) {
+        float acc[JT];
+#pragma unroll
+        for (int jj = 0; jj < JT; ++jj) acc[jj] = 0.f;
+        tile_row_gemm<JT>(cur + lane * ldh, round_up4(L.din), W, P.ldw[l], j0, L.dout, acc);
+        if (gcn) tile_store_row<JT>(oth + lane * ldh, acc, nullptr, j0, L.dout, SGNN_ACT_IDENTITY);
+        else tile_store_row<JT>(oth + lane * ldh, acc, b, j0, L.dout, L.act);
+      }
+    __syncwarp();
+    if (gcn) {   // cur (the layer input) is dead: aggregate oth -> cur
+      if (T.on)
+        for (int j0 = 0; j0 < L.dout; j0 += JT) {
+          float acc[JT];
+#pragma unroll
+          for (int jj = 0; jj < JT; ++jj) acc[jj] = 0.f;
+          tile_gather<JT, false>(T, oth, ldh, j0, L.dout, acc);
+          tile_store_row<JT>(cur + lane * ldh, acc, b, j0, L.dout, L.act);
+        }
+      __syncwarp();
+    } else {
+      float* sw = cur; cur = oth; oth = sw;
+    }
+  }
+  return cur;
+}
+
+template <int JT>
+__global__ void __launch_bounds__(TILE_WARPS * 32)
+embed_tile_kernel(const __grid_constant__ ModelDev M, const __grid_constant__ EmbPlan P, const BatchDev B,
+                  const float* __restrict__ params, float* __restrict__ emb) {
+  extern __shared__ __align__(16) float smem[];
+  float* s_w = smem;
+  tile_stage_weights(M, P, params, s_w);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float* my = smem + P.w_floats + warp * P.warp_floats;
+  float* bufA = my;
+  float* bufB = bufA + 32 * P.ldh;
+  int* s_col = reinterpret_cast<int*>(bufB + 32 * P.ldh);
+  float* s_val = reinterpret_cast<float*>(s_col + TILE_CSR_CAP);
+  int* s_lab = reinterpret_cast<int*>(s_val + TILE_CSR_CAP);
+  float* s_att = reinterpret_cast<float*>(s_lab + 32);
+  const int gpw = P.gpw;
+  const int n_tiles = (B.n_graphs + gpw - 1) / gpw;
+  const int E = M.emb_dim, d = M.node_dim;
+  for (int t = blockIdx.x * TILE_WARPS + warp; t < n_tiles; t += gridDim.x * TILE_WARPS) {
+    const int g0 = t * gpw, g1 = min(B.n_graphs, g0 + gpw);
+    // lanes 0..gpw hold the node offsets of the tile's graphs
+    const int my_no = B.node_off[min(g0 + lane, g1)];
+    const int base = __shfl_sync(0xffffffffu, my_no, 0);
+    const int n_rows = __shfl_sync(0xffffffffu, my_no, g1 - g0) - base;
+    TileCtx T;
+    T.n_rows = n_rows; T.on = lane < n_rows;
+    int gi = 0;   // my graph inside the tile
+    T.g_off = 0;
+    for (int k = 1; k <= g1 - g0; ++k) {
+      const int off = __shfl_sync(0xffffffffu, my_no, k) - base;
+      if (k < g1 - g0 && lane >= off) { gi = k; T.g_off = off; }
+    }
+    const int rp_lo = B.rowptr[base + min(lane, n_rows)];
+    const int rp_hi = B.rowptr[base + min(lane + 1, n_rows)];
+    const int tile_e0 = __shfl_sync(0xffffffffu, rp_lo, 0);
+    const int tile_nnz = B.rowptr[base + n_rows] - tile_e0;
+    T.e0 = rp_lo - tile_e0; T.e1 = T.on ? rp_hi - tile_e0 : T.e0;
+    s_lab[lane] = T.on ? B.labels[base + lane] : 0;
+    if (tile_nnz <= TILE_CSR_CAP) {
+      for (int e = lane; e < tile_nnz; e += 32) { s_col[e] = B.col[tile_e0 + e]; s_val[e] = B.val[tile_e0 + e]; }
+      T.col = s_col; T.val = s_val;
+    } else {
+      T.col = B.col + tile_e0; T.val = B.val + tile_e0;
+    }
+    T.lab = s_lab;
+    __syncwarp();
+    float* H = tile_node_layers<JT>(M, P, T, s_w, bufA, bufB, lane);
+    float* scratch = H == bufA ? bufB : bufA;
+    const int ldh = P.ldh;
+    // ---- pooling, per graph of the tile ----
+    if (M.pool_kind == SGNN_LAYER_PADDING) {
+      for (int k = 0; k < g1 - g0; ++k) {
+        const int off = __shfl_sync(0xffffffffu, my_no, k) - base;
+        const int n = __shfl_sync(0xffffffffu, my_no, k + 1) - base - off;
+        float* out = emb + (size_t)(g0 + k) * E;
+        for (int idx = lane; idx < E; idx += 32) {
+          const int p = idx / d, c = idx - p * d;
+          out[idx] = p < n ? H[(off + p) * ldh + c] : M.pool_fparam;
+        }
+      }
+    } else if (M.pool_kind == SGNN_LAYER_AVERAGE) {
+      for (int idx = lane; idx < (g1 - g0) * d; idx += 32) {
+        const int k = idx / d, j = idx - k * d;
+        const int off = B.node_off[g0 + k] - base, n = B.node_off[g0 + k + 1] - base - off;
+        float s = 0.f;
+        for (int i = 0; i < n; ++i) s += H[(off + i) * ldh + j];
+        emb[(size_t)(g0 + k) * E + j] = s / (float)n;
+      }
+    } else {   // Attention (layers.py:154-160)
+      float* s_mean = scratch;                 // [gpw][d]
+      float* s_c = scratch + (g1 - g0) * d;    // [gpw][d]
+      const float* Wa = s_w + P.att_s;
+      for (int idx = lane; idx < (g1 - g0) * d; idx += 32) {
+        const int k = idx / d, j = idx - k * d;
+        const int off = B.node_off[g0 + k] - base, n = B.node_off[g0 + k + 1] - base - off;
+        float s = 0.f;
+        for (int i = 0; i < n; ++i) s += H[(off + i) * ldh + j];
+        s_mean[idx] = s / (float)n;
+      }
+      __syncwarp();
+      for (int idx = lane; idx < (g1 - g0) * d; idx += 32) {
+        const int k = idx / d, j = idx - k * d;
+        float s = 0.f;
+        for (int kk = 0; kk < d; ++kk) s = fmaf(s_mean[k * d + kk], Wa[kk * d + j], s);
+        s_c[idx] = tanhf(s);
+      }
+      __syncwarp();
+      if (T.on) {
+        float s = 0.f;
+        for (int kk = 0; kk < d; ++kk) s = fmaf(H[lane * ldh + kk], s_c[gi * d + kk], s);
+        s_att[lane] = 1.f / (1.f + expf(-s));
+      }
+      __syncwarp();
+      for (int idx = lane; idx < (g1 - g0) * d; idx += 32) {
+        const int k = idx / d, j = idx - k * d;
+        const int off = B.node_off[g0 + k] - base, n = B.node_off[g0 + k + 1] - base - off;
+        float s = 0.f;
+        for (int i = 0; i < n; ++i) s = fmaf(s_att[off + i], H[(off + i) * ldh + j], s);
+        emb[(size_t)(g0 + k) * E + j] = s;
+      }
+    }
+    __syncwarp();
+  }
+}

@@ -52,21 +52,24 @@ inline EmbPlan make_emb_plan(const ModelDev& M, int max_nodes) {
   return P;
 }
 
+// raw: a scratch area of >= n_params floats (the per-warp buffers, unused before the tile loop)
 __device__ __forceinline__ void tile_stage_weights(const ModelDev& M, const EmbPlan& P, const float* __restrict__ params,
-                                                   float* s_w) {
+                                                   float* s_w, float* raw) {
   for (int i = threadIdx.x; i < P.w_floats; i += blockDim.x) s_w[i] = 0.f;
+#pragma unroll 4
+  for (int i = threadIdx.x; i < M.n_params; i += blockDim.x) raw[i] = params[i];   // coalesced, loads in flight together
   __syncthreads();
   for (int l = 0; l < M.n_node; ++l) {
     const LayerDev& L = M.L[l];
     for (int i = threadIdx.x; i < L.din * L.dout; i += blockDim.x) {
       const int k = i / L.dout, j = i - k * L.dout;
-      s_w[P.w_s[l] + k * P.ldw[l] + j] = params[L.w_off + i];
+      s_w[P.w_s[l] + k * P.ldw[l] + j] = raw[L.w_off + i];
     }
     if (L.bias)
-      for (int j = threadIdx.x; j < L.dout; j += blockDim.x) s_w[P.b_s[l] + j] = params[L.b_off + j];
+      for (int j = threadIdx.x; j < L.dout; j += blockDim.x) s_w[P.b_s[l] + j] = raw[L.b_off + j];
   }
   if (P.att_s >= 0)
-    for (int i = threadIdx.x; i < M.node_dim * M.node_dim; i += blockDim.x) s_w[P.att_s + i] = params[M.pool_w_off + i];
+    for (int i = threadIdx.x; i < M.node_dim * M.node_dim; i += blockDim.x) s_w[P.att_s + i] = raw[M.pool_w_off + i];
   __syncthreads();
 }
 
@@ -80,19 +83,37 @@ struct TileCtx {
   const int* lab;      // [32] labels of the tile's nodes (shared)
 };
 
+// sigmoid / tanh / sim_kernel are rare on node layers: keep their (large) code out of line, once
+__device__ __noinline__ float tile_act_slow(float x, int act) { return sgnn_act(x, act, 0.f); }
+
 template <int JT>
-__device__ __forceinline__ void tile_store_row(float* dst, const float (&acc)[JT], const float* bias, int j0, int dout,
+__device__ __forceinline__ void tile_store_row(float* dst, float (&acc)[JT], const float* bias, int j0, int dout,
                                                int act) {
+  if (bias) {
+#pragma unroll
+    for (int jj = 0; jj < JT; jj += 4) {
+      if (j0 + jj < dout) {   // warp-uniform
+        const float4 b4 = *reinterpret_cast<const float4*>(bias + j0 + jj);   // padded with zeros
+        acc[jj] += b4.x; acc[jj + 1] += b4.y; acc[jj + 2] += b4.z; acc[jj + 3] += b4.w;
+      }
+    }
+  }
+  if (act == SGNN_ACT_RELU) {
+#pragma unroll
+    for (int jj = 0; jj < JT; ++jj) acc[jj] = fmaxf(acc[jj], 0.f);
+  } else if (act != SGNN_ACT_IDENTITY) {
+#pragma unroll
+    for (int jj = 0; jj < JT; ++jj)
+      if (j0 + jj < dout) acc[jj] = tile_act_slow(acc[jj], act);
+  }
 #pragma unroll
   for (int jj = 0; jj < JT; jj += 4) {
-    if (j0 + jj < dout) {   // warp-uniform
+    if (j0 + jj < dout) {
       float4 o;
-      float* op = reinterpret_cast<float*>(&o);
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        const int j = j0 + jj + c;
-        op[c] = j < dout ? sgnn_act(acc[jj + c] + (bias ? bias[j] : 0.f), act, 0.f) : 0.f;
-      }
+      o.x = acc[jj];
+      o.y = j0 + jj + 1 < dout ? acc[jj + 1] : 0.f;   // padded columns stay exactly zero
+      o.z = j0 + jj + 2 < dout ? acc[jj + 2] : 0.f;
+      o.w = j0 + jj + 3 < dout ? acc[jj + 3] : 0.f;
       *reinterpret_cast<float4*>(dst + j0 + jj) = o;
     }
   }
@@ -143,64 +164,68 @@ __device__ __forceinline__ void tile_row_gemm(const float* hrow, int din, const 
   }
 }
 
-// all node layers of one tile; returns the buffer holding the last layer's output rows
+// One node layer of one tile with JT accumulators per pass.  first: gather of W rows by label into
+// cur.  GCN: cur -> (gemm) oth -> (aggregate) cur.  Dense: cur -> oth (caller swaps).
 template <int JT>
-__device__ __forceinline__ float* tile_node_layers(const ModelDev& M, const EmbPlan& P, const TileCtx& T,
-                                                   const float* s_w, float* bufA, float* bufB, int lane) {
-  const int ldh = P.ldh;
-  float* cur = bufA;   // holds H (input of the layer); other = scratch / output
-  float* oth = bufB;
-  for (int l = 0; l < M.n_node; ++l) {
-    const LayerDev& L = M.L[l];
-    const float* W = s_w + P.w_s[l];
-    const float* b = s_w + P.b_s[l];
-    if (l == 0) {
-      if (T.on)
-        for (int j0 = 0; j0 < L.dout; j0 += JT) {
-          float acc[JT];
-#pragma unroll
-          for (int jj = 0; jj < JT; ++jj) acc[jj] = 0.f;
-          tile_gather<JT, true>(T, W, P.ldw[0], j0, L.dout, acc);
-          tile_store_row<JT>(cur + lane * ldh, acc, b, j0, L.dout, L.act);
-        }
-      __syncwarp();
-      continue;
-    }
-    const bool gcn = L.kind == SGNN_LAYER_GCN;
+__device__ __noinline__ void tile_layer(const LayerDev& L, bool first, const TileCtx& T, const float* W, int ldw,
+                                        const float* b, float* cur, float* oth, int ldh, int lane) {
+  const bool gcn = L.kind == SGNN_LAYER_GCN;
+  if (first) {
     if (T.on)
       for (int j0 = 0; j0 < L.dout; j0 += JT) {
         float acc[JT];
 #pragma unroll
         for (int jj = 0; jj < JT; ++jj) acc[jj] = 0.f;
-        tile_row_gemm<JT>(cur + lane * ldh, round_up4(L.din), W, P.ldw[l], j0, L.dout, acc);
-        if (gcn) tile_store_row<JT>(oth + lane * ldh, acc, nullptr, j0, L.dout, SGNN_ACT_IDENTITY);
-        else tile_store_row<JT>(oth + lane * ldh, acc, b, j0, L.dout, L.act);
+        tile_gather<JT, true>(T, W, ldw, j0, L.dout, acc);
+        tile_store_row<JT>(cur + lane * ldh, acc, b, j0, L.dout, L.act);
       }
     __syncwarp();
-    if (gcn) {   // cur (the layer input) is dead: aggregate oth -> cur
-      if (T.on)
-        for (int j0 = 0; j0 < L.dout; j0 += JT) {
-          float acc[JT];
+    return;
+  }
+  if (T.on)
+    for (int j0 = 0; j0 < L.dout; j0 += JT) {
+      float acc[JT];
 #pragma unroll
-          for (int jj = 0; jj < JT; ++jj) acc[jj] = 0.f;
-          tile_gather<JT, false>(T, oth, ldh, j0, L.dout, acc);
-          tile_store_row<JT>(cur + lane * ldh, acc, b, j0, L.dout, L.act);
-        }
-      __syncwarp();
-    } else {
-      float* sw = cur; cur = oth; oth = sw;
+      for (int jj = 0; jj < JT; ++jj) acc[jj] = 0.f;
+      tile_row_gemm<JT>(cur + lane * ldh, round_up4(L.din), W, ldw, j0, L.dout, acc);
+      tile_store_row<JT>(oth + lane * ldh, acc, gcn ? nullptr : b, j0, L.dout, gcn ? (int)SGNN_ACT_IDENTITY : L.act);
     }
+  __syncwarp();
+  if (!gcn) return;
+  if (T.on)
+    for (int j0 = 0; j0 < L.dout; j0 += JT) {
+      float acc[JT];
+#pragma unroll
+      for (int jj = 0; jj < JT; ++jj) acc[jj] = 0.f;
+      tile_gather<JT, false>(T, oth, ldh, j0, L.dout, acc);
+      tile_store_row<JT>(cur + lane * ldh, acc, b, j0, L.dout, L.act);
+    }
+  __syncwarp();
+}
+
+// all node layers of one tile; returns the buffer holding the last layer's output rows
+__device__ __forceinline__ float* tile_node_layers(const ModelDev& M, const EmbPlan& P, const TileCtx& T,
+                                                   const float* s_w, float* bufA, float* bufB, int lane) {
+  float* cur = bufA;
+  float* oth = bufB;
+  for (int l = 0; l < M.n_node; ++l) {
+    const LayerDev& L = M.L[l];
+    const float* W = s_w + P.w_s[l];
+    const float* b = L.bias ? s_w + P.b_s[l] : nullptr;
+    if (L.dout > 16) tile_layer<32>(L, l == 0, T, W, P.ldw[l], b, cur, oth, P.ldh, lane);
+    else if (L.dout > 4) tile_layer<16>(L, l == 0, T, W, P.ldw[l], b, cur, oth, P.ldh, lane);
+    else tile_layer<4>(L, l == 0, T, W, P.ldw[l], b, cur, oth, P.ldh, lane);
+    if (l > 0 && L.kind != SGNN_LAYER_GCN) { float* sw = cur; cur = oth; oth = sw; }
   }
   return cur;
 }
 
-template <int JT>
 __global__ void __launch_bounds__(TILE_WARPS * 32)
 embed_tile_kernel(const __grid_constant__ ModelDev M, const __grid_constant__ EmbPlan P, const BatchDev B,
                   const float* __restrict__ params, float* __restrict__ emb) {
   extern __shared__ __align__(16) float smem[];
   float* s_w = smem;
-  tile_stage_weights(M, P, params, s_w);
+  tile_stage_weights(M, P, params, s_w, smem + P.w_floats);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float* my = smem + P.w_floats + warp * P.warp_floats;
   float* bufA = my;
@@ -240,7 +265,7 @@ embed_tile_kernel(const __grid_constant__ ModelDev M, const __grid_constant__ Em
     }
     T.lab = s_lab;
     __syncwarp();
-    float* H = tile_node_layers<JT>(M, P, T, s_w, bufA, bufB, lane);
+    float* H = tile_node_layers(M, P, T, s_w, bufA, bufB, lane);
     float* scratch = H == bufA ? bufB : bufA;
     const int ldh = P.ldh;
     // ---- pooling, per graph of the tile ----

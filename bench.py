@@ -51,41 +51,76 @@ def peaks():
 
 
 class ClockSampler(object):
-    """nvidia-smi clocks + throttle reasons while the timed region runs."""
-    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
-         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+    """SM clock + throttle reasons sampled through NVML every 5 ms while the timed legs run (the timed
+    region of K steps lasts only a few ms, too short for `nvidia-smi -lms`); falls back to nvidia-smi."""
+    BITS = {'hw_slowdown': 0x8, 'hw_thermal_slowdown': 0x40, 'sw_thermal_slowdown': 0x20, 'sw_power_cap': 0x4}
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.marks, self.stop_flag, self.thread = index, [], {}, False, None
+        self.max_mhz = None
+
+    def _loop_nvml(self, nv, h):
+        while not self.stop_flag:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                try:
+                    rs = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.rows.append((time.perf_counter(), float(sm), int(rs)))
+            except Exception:
+                pass
+            time.sleep(0.005)
+
+    def _loop_smi(self):
+        q = 'clocks.sm,clocks.max.sm,clocks_event_reasons.active'
+        while not self.stop_flag:
+            try:
+                o = subprocess.run(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + q,
+                                    '--format=csv,noheader,nounits'], capture_output=True, text=True, timeout=5).stdout
+                c = [x.strip() for x in o.strip().split(',')]
+                self.max_mhz = float(c[1])
+                self.rows.append((time.perf_counter(), float(c[0]), int(c[2], 16)))
+            except Exception:
+                time.sleep(0.05)
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
-                                          '--format=csv,noheader,nounits', '-lms', '100'],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
-            self.thread.start()
+            import pynvml as nv
+            nv.nvmlInit()
+            # NVML enumerates physical devices: honour CUDA_VISIBLE_DEVICES when it is a plain index list
+            vis = os.environ.get('CUDA_VISIBLE_DEVICES', '')
+            idx = self.index
+            if vis and all(v.strip().isdigit() for v in vis.split(',')):
+                idx = int(vis.split(',')[self.index])
+            h = nv.nvmlDeviceGetHandleByIndex(idx)
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            self.thread = threading.Thread(target=self._loop_nvml, args=(nv, h), daemon=True)
         except Exception:
-            self.proc = None
+            self.thread = threading.Thread(target=self._loop_smi, daemon=True)
+        self.thread.start()
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(',')])
+    def mark(self, name):
+        self.marks[name] = time.perf_counter()
 
     def stop(self):
-        if not self.proc:
-            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
-        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace('.', '').isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace('.', '').isdigit()]
-        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
-        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i] == 'Active'})
-        return {'sm_mhz': float(np.median(sm)) if sm else None, 'sm_max_mhz': max(mx) if mx else None,
-                'reasons': reasons, 'samples': len(sm)}
+        self.stop_flag = True
+        if self.thread:
+            self.thread.join(timeout=6)
+        t0, t1 = self.marks.get('timed_begin', 0.0), self.marks.get('timed_end', float('inf'))
+        l0, l1 = self.marks.get('load_begin', 0.0), self.marks.get('load_end', float('inf'))
+        timed = [r for r in self.rows if t0 <= r[0] <= t1]
+        load = [r for r in self.rows if l0 <= r[0] <= l1]
+        use = load or self.rows
+        if not use:
+            return {'sm_mhz': None, 'sm_max_mhz': self.max_mhz, 'reasons': ['no clock samples']}
+        mask = 0
+        for r in use:
+            mask |= r[2]
+        return {'sm_mhz': float(np.median([r[1] for r in use])), 'sm_max_mhz': self.max_mhz,
+                'reasons': sorted(n for n, b in self.BITS.items() if mask & b), 'samples': len(use),
+                'samples_in_timed_region': len(timed),
+                'window': 'pre-load + timed steps + per-stage timings (GPU continuously busy), 5 ms NVML polling'}
 
 
 def make_rank_data(rank):
@@ -273,15 +308,23 @@ def run_cuda(args):
             ids, vals = eng.topk_merge(cv, ci, TOPK)
         out['ids'], out['vals'] = ids, vals
 
+    clocks = ClockSampler(local)
+    clocks.start()
     for _ in range(args.warmup):
         step()
+    torch.cuda.synchronize()
+    clocks.mark('load_begin')
+    t_pre = time.perf_counter()           # untimed pre-load: ~0.3 s of back-to-back steps so that the
+    while time.perf_counter() - t_pre < 0.3:   # clocks are in their loaded state and get sampled
+        for _ in range(20):
+            step()
+        torch.cuda.synchronize()
     launches0 = eng.launches
-    clocks = ClockSampler(local)
     barrier()
-    clocks.start()
+    clocks.mark('timed_begin')
     total_ms = timed_steps(torch, step, args.steps, flush)
     barrier()
-    clk = clocks.stop()
+    clocks.mark('timed_end')
     launches = eng.launches - launches0
     total_ms = max_over_ranks(total_ms)
     ms_per_step = total_ms / args.steps
@@ -293,6 +336,8 @@ def run_cuda(args):
     k_ms = timed_steps(torch, lambda: eng.score_all_pairs(emb_q, emb_db, out=sim), args.steps, flush) / args.steps
     e_ms = timed_steps(torch, lambda: (eng.embed(qd, out=emb_q), eng.embed(dbd, out=emb_db)), args.steps, flush) / args.steps
     t_ms = timed_steps(torch, lambda: eng.topk(sim, TOPK), args.steps, flush) / args.steps
+    clocks.mark('load_end')
+    clk = clocks.stop()
     peak, peak_src = peaks()
     alg_bytes = 4.0 * M_QUERIES * N_DB + 4.0 * (M_QUERIES + N_DB) * eng.emb_dim
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9

@@ -15,8 +15,10 @@
 // i.e. 16-byte rows, 8-row core matrices contiguous (SBO = 128 B), K chunks R*16 B apart (LBO).
 // The prep kernels write global memory in exactly this order, so a tile is ONE bulk async copy.
 //
-// Roles (320 threads): warps 0-7 epilogue (warp w: TMEM lanes 32(w%4).., column half w/4),
-// warp 8 bulk-copy producer, warp 9 MMA issuer.  TMEM: 2 accumulator buffers x 256 columns.
+// Roles (320 threads): warps 0-7 epilogue in two groups of four (group = w/4 takes every other tile,
+// warp w reads TMEM lanes 32(w%4)..), warp 8 bulk-copy producer, warp 9 MMA issuer.  TMEM: 4
+// accumulator buffers x 128 columns; the two groups are half a tile out of phase, so one group's
+// TMEM loads overlap the other's arithmetic on every scheduler.
 #pragma once
 #include "sgnn_common.cuh"
 #include "sgnn_tc.cuh"
@@ -27,78 +29,75 @@ __device__ __forceinline__ void split_bf16(float x, __nv_bfloat16& hi, __nv_bflo
   lo = __float2bfloat16_rn(x - __bfloat162float(hi));
 }
 
-// A operand: one thread per (database graph, K chunk)
-__global__ void __launch_bounds__(256)
-tc_prep_db_kernel(const TcGeom G, const float* __restrict__ emb_db, __nv_bfloat16* __restrict__ A) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  const int total = G.n_gtiles * 128 * G.KCH;
-  if (idx >= total) return;
-  const int kc = idx % G.KCH, g = idx / G.KCH;
-  const int T = g >> 7, r = g & 127;
-  __align__(16) __nv_bfloat16 hi[8], lo[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const int b = kc * 8 + j;
-    float v = 0.f;
-    if (g < G.n) v = b < G.D ? emb_db[(size_t)g * G.D + b] : (b == G.D ? 1.f : 0.f);
-    split_bf16(v, hi[j], lo[j]);
-  }
-  const size_t base = ((size_t)(T * G.parts) * G.KCH + kc) * 1024 + r * 8;
-  *reinterpret_cast<uint4*>(A + base) = *reinterpret_cast<const uint4*>(hi);
-  if (G.parts == 2)
-    *reinterpret_cast<uint4*>(A + base + (size_t)G.KCH * 1024) = *reinterpret_cast<const uint4*>(lo);
-}
-
-// B operand: one warp per query; lanes over (k, kk).  With KC == K + 1 (relu inner activation) row K
-// of the query holds sum_k w_k * row_k (w = 1 in reference mode, U in paper mode): the tensor core
-// then also delivers sum_k w_k m_k, and  sum_k w_k relu(m_k) = (sum_k w_k m_k + sum_k w_k |m_k|) / 2
+// Operand preparation, ONE launch: blocks [0, q_blocks) build the B tiles (queries), the rest the A
+// tiles (database graphs).
+//
+// B: thread = (query, kk); it walks the K feature maps of its column kk of P' / C.  With
+// KC == K + 1 (relu inner activation) row K of the query holds sum_k w_k * row_k (w = 1 in reference
+// mode, U in paper mode): the tensor core then also delivers sum_k w_k m_k, and
+//   sum_k w_k relu(m_k) = (sum_k w_k m_k + sum_k w_k |m_k|) / 2
 // costs ONE add-with-|x|-modifier per accumulator element in the epilogue instead of max + add.
+// A: one thread per (database graph, K chunk).
 __global__ void __launch_bounds__(128)
-tc_prep_q_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const float* __restrict__ params,
-                 const float* __restrict__ emb_q, __nv_bfloat16* __restrict__ B) {
-  const int lane = threadIdx.x & 31;
-  const int q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (q >= G.m) return;
+tc_prep_kernel(const __grid_constant__ ModelDev M, const TcGeom G, int q_blocks, const float* __restrict__ params,
+               const float* __restrict__ emb_q, const float* __restrict__ emb_db, __nv_bfloat16* __restrict__ A,
+               __nv_bfloat16* __restrict__ B) {
+  if ((int)blockIdx.x >= q_blocks) {
+    const int idx = (blockIdx.x - q_blocks) * blockDim.x + threadIdx.x;
+    const int total = G.n_gtiles * 128 * G.KCH;
+    if (idx >= total) return;
+    const int kc = idx % G.KCH, g = idx / G.KCH;
+    const int T = g >> 7, r = g & 127;
+    __align__(16) __nv_bfloat16 hi[8], lo[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int b = kc * 8 + j;
+      float v = 0.f;
+      if (g < G.n) v = b < G.D ? emb_db[(size_t)g * G.D + b] : (b == G.D ? 1.f : 0.f);
+      split_bf16(v, hi[j], lo[j]);
+    }
+    const size_t base = ((size_t)(T * G.parts) * G.KCH + kc) * 1024 + r * 8;
+    *reinterpret_cast<uint4*>(A + base) = *reinterpret_cast<const uint4*>(hi);
+    if (G.parts == 2)
+      *reinterpret_cast<uint4*>(A + base + (size_t)G.KCH * 1024) = *reinterpret_cast<const uint4*>(lo);
+    return;
+  }
   const int D = G.D, K = G.K, DK16 = G.KCH * 8, DK = D * K;
-  const int QT = 2 * G.QH;
-  const int qb = q / QT, ql = q - qb * QT, h = ql / G.QH, qq = ql - h * G.QH;
-  const int row0 = h * 128 + qq * G.KC;
+  const int qpb = blockDim.x / DK16;
+  const int ql = threadIdx.x / DK16, kk = threadIdx.x - ql * DK16;
+  const int q = blockIdx.x * qpb + ql;
+  if (ql >= qpb || q >= G.m) return;
+  const int qb = q / G.QH, qq = q - qb * G.QH;
+  const int row0 = qq * G.KC;
   const float* x = emb_q + (size_t)q * D;
   const bool dot = M.pair_kind == SGNN_LAYER_DOT;
+  const bool ref = M.ntn_mode == SGNN_NTN_REFERENCE;
   const float* W = params + M.w_off;
   const float* V = params + M.v_off;
-  auto value = [&](int k, int kk) {
+  __nv_bfloat16* Bq = B + ((size_t)(qb * G.parts) * G.KCH + (kk >> 3)) * (TC_NPAD * 8) + (kk & 7);
+  const size_t lo_off = (size_t)G.KCH * TC_NPAD * 8;
+  auto put = [&](int row, float v) {
+    __nv_bfloat16 hi, lo;
+    split_bf16(v, hi, lo);
+    Bq[(size_t)row * 8] = hi;
+    if (G.parts == 2) Bq[(size_t)row * 8 + lo_off] = lo;
+  };
+  float sum = 0.f;
+  for (int k = 0; k < K; ++k) {
     float v = 0.f;
     if (dot) {
       v = kk < D ? x[kk] : 0.f;
-    } else if (kk < D) {
+    } else if (kk < D) {          // P'[q][k][kk] = V[k][D + kk] + sum_a x[a] W[a][kk][k]
       v = V[k * 2 * D + D + kk];
       for (int a = 0; a < D; ++a) v = fmaf(x[a], W[a * DK + kk * K + k], v);
-    } else if (kk == D) {
+    } else if (kk == D) {         // C[q][k] = b[k] + V[k][0:D] . x
       v = M.pair_bias ? params[M.b_off + k] : 0.f;
       for (int a = 0; a < D; ++a) v = fmaf(V[k * 2 * D + a], x[a], v);
     }
-    return v;
-  };
-  auto put = [&](int row, int kk, float v) {
-    __nv_bfloat16 hi, lo;
-    split_bf16(v, hi, lo);
-    const size_t off = ((size_t)(qb * G.parts) * G.KCH + (kk >> 3)) * (TC_NPAD * 8) + (size_t)row * 8 + (kk & 7);
-    B[off] = hi;
-    if (G.parts == 2) B[off + (size_t)G.KCH * TC_NPAD * 8] = lo;
-  };
-  for (int i = lane; i < K * DK16; i += 32) {
-    const int k = i / DK16, kk = i - k * DK16;
-    put(row0 + k, kk, value(k, kk));
+    put(row0 + k, v);
+    sum = fmaf(dot || ref ? 1.f : params[M.u_off + k], v, sum);
   }
-  if (G.KC > K) {
-    const bool ref = M.ntn_mode == SGNN_NTN_REFERENCE;
-    for (int kk = lane; kk < DK16; kk += 32) {
-      float s = 0.f;
-      for (int k = 0; k < K; ++k) s = fmaf(ref ? 1.f : params[M.u_off + k], value(k, kk), s);
-      put(row0 + K, kk, s);
-    }
-  }
+  if (G.KC > K) put(row0 + K, sum);
 }
 
 struct TcEpi {
@@ -137,9 +136,9 @@ __device__ __forceinline__ float tc_finish(const TcEpi& E, float st) {
 template <int KT, bool RELU, bool REF, bool SIMK>
 __device__ __forceinline__ void tc_epilogue_half(const TcEpi& E, uint32_t taddr, int K, int KCr, int QH, int qrow0,
                                                  int g, uint64_t* t_empty, int lane) {
-  const bool g_ok = g < E.n;
-  const int qmax = min(QH, E.m - qrow0);
+  const int qmax = g < E.n ? min(QH, E.m - qrow0) : 0;   // queries this thread may store
   float* p = E.sim + (size_t)qrow0 * E.ld + g;
+  const int64_t ld = E.ld;
   if constexpr (KT > 0) {
     constexpr int KC = RELU ? KT + 1 : KT;
     constexpr int QHC = 128 / KC, COLS = QHC * KC, NCH = (COLS + 31) / 32;
@@ -171,7 +170,8 @@ __device__ __forceinline__ void tc_epilogue_half(const TcEpi& E, uint32_t taddr,
         }
       }
       const float s = tc_finish<RELU, REF, SIMK>(E, st);
-      if (g_ok && q < qmax) p[(size_t)q * E.ld] = s;
+      if (q < qmax) *p = s;
+      p += ld;
     }
   } else {
     const int cols = QH * KCr;
@@ -193,7 +193,7 @@ __device__ __forceinline__ void tc_epilogue_half(const TcEpi& E, uint32_t taddr,
           }
           if (++kk == KCr) {
             const float s = tc_finish<RELU, REF, SIMK>(E, st);
-            if (g_ok && qq < qmax) p[(size_t)qq * E.ld] = s;
+            if (qq < qmax) p[(size_t)qq * ld] = s;
             st = 0.f; kk = 0; ++qq;
           }
         }
@@ -219,9 +219,9 @@ allpairs_tc_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const flo
   uint64_t* a_full = bars;                 // [1]
   uint64_t* b_full = bars + 1;             // [TC_STAGES]
   uint64_t* b_empty = b_full + TC_STAGES;  // [TC_STAGES]
-  uint64_t* t_full = b_empty + TC_STAGES;  // [2]
-  uint64_t* t_empty = t_full + 2;          // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
+  uint64_t* t_full = b_empty + TC_STAGES;  // [TC_BUFS]
+  uint64_t* t_empty = t_full + TC_BUFS;    // [TC_BUFS]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + TC_BUFS);
   float* sU = reinterpret_cast<float*>(tmem_slot + 4);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -235,7 +235,7 @@ allpairs_tc_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const flo
   if (threadIdx.x == 0) {
     tc::mbar_init(a_full, 1);
     for (int s = 0; s < TC_STAGES; ++s) { tc::mbar_init(b_full + s, 1); tc::mbar_init(b_empty + s, 1); }
-    for (int b = 0; b < 2; ++b) { tc::mbar_init(t_full + b, 1); tc::mbar_init(t_empty + b, 8); }
+    for (int b = 0; b < TC_BUFS; ++b) { tc::mbar_init(t_full + b, 1); tc::mbar_init(t_empty + b, 4); }
     tc::fence_barrier_init();
   }
   const bool dot = M.pair_kind == SGNN_LAYER_DOT;
@@ -274,8 +274,8 @@ allpairs_tc_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const flo
         tc::tc_fence_after();
         const uint32_t b_addr = tc::smem_u32(sB + s * b_bytes);
         for (int ga = 0; ga < ga_count; ++ga, ++it) {
-          const int buf = it & 1;
-          if (it >= 2) tc::mbar_wait(t_empty + buf, ((it >> 1) - 1) & 1);
+          const int buf = it & (TC_BUFS - 1);
+          if (it >= TC_BUFS) tc::mbar_wait(t_empty + buf, ((it / TC_BUFS) - 1) & 1);
           tc::tc_fence_after();
           const uint32_t a_addr = tc::smem_u32(sA + ga * a_bytes);
           const uint32_t d_addr = tmem_base + buf * TC_NPAD;
@@ -308,19 +308,17 @@ allpairs_tc_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const flo
       const float hs = REF ? 0.5f * su : 0.5f;
       E.c2 = -M.yeta * hs * hs * 1.4426950408889634f;
     }
-    const int lg = warp & 3, half = warp >> 2;
-    const int QT = 2 * G.QH;
-    int it = 0;
-    for (int i = 0; i < nq; ++i) {
-      const int qrow0 = (qb0 + i) * QT + half * G.QH;
-      for (int ga = 0; ga < ga_count; ++ga, ++it) {
-        const int buf = it & 1;
-        tc::mbar_wait(t_full + buf, (it >> 1) & 1);
-        tc::tc_fence_after();
-        const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + buf * TC_NPAD + half * 128;
-        const int g = (gt0 + ga) * 128 + lg * 32 + lane;
-        tc_epilogue_half<KT, RELU, REF, SIMK>(E, taddr, G.K, G.KC, G.QH, qrow0, g, t_empty + buf, lane);
-      }
+    // group `grp` takes tiles it = grp, grp + 2, ...; tile it lives in TMEM buffer it % 4
+    const int lg = warp & 3, grp = warp >> 2;
+    const int total = nq * ga_count;
+    for (int it = grp; it < total; it += 2) {
+      const int i = it / ga_count, ga = it - i * ga_count;
+      const int buf = it & (TC_BUFS - 1);
+      tc::mbar_wait(t_full + buf, (it / TC_BUFS) & 1);
+      tc::tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + buf * TC_NPAD;
+      const int g = (gt0 + ga) * 128 + lg * 32 + lane;
+      tc_epilogue_half<KT, RELU, REF, SIMK>(E, taddr, G.K, G.KC, G.QH, (qb0 + i) * G.QH, g, t_empty + buf, lane);
     }
   }
   tc::tc_fence_before();

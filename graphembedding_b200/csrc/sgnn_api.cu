@@ -236,7 +236,7 @@ int score_all_pairs_tc(SgnnHandle h, const float* emb_q, int m, const float* emb
   G.KCH = round_up(G.D + 1, 16) / 8;
   G.parts = h->cfg.precision == SGNN_PREC_BF16 ? 1 : 2;
   G.n_gtiles = (n + 127) / 128;
-  G.n_qblocks = (m + 2 * G.QH - 1) / (2 * G.QH);
+  G.n_qblocks = (m + G.QH - 1) / G.QH;
   const int64_t items = (int64_t)G.n_gtiles * G.n_qblocks;
   G.GA = (int)std::max<int64_t>(1, std::min<int64_t>(TC_GA_MAX, items / ((int64_t)h->sm_count * 4)));
   G.GA = std::min(G.GA, G.n_gtiles);
@@ -415,7 +415,7 @@ int sgnn_reserve(SgnnHandle h, int64_t max_graphs, int64_t max_nodes, int64_t ma
     const ModelDev& M = h->M;
     const int K = M.pair_kind == SGNN_LAYER_NTN ? M.K : 1;
     const bool relu = M.pair_kind == SGNN_LAYER_NTN && M.pair_act == SGNN_ACT_RELU;
-    const int64_t kch = round_up(M.emb_dim + 1, 16) / 8, qt = 2 * (128 / tc_cols_per_query(K, relu));
+    const int64_t kch = round_up(M.emb_dim + 1, 16) / 8, qt = 128 / tc_cols_per_query(K, relu);
     const int64_t need_a = ((max_db + 127) / 128) * 2 * kch * 1024;
     const int64_t need_b = ((max_queries + qt - 1) / qt) * 2 * kch * (TC_NPAD * 8);
     if (need_a > h->cap_Atc) {

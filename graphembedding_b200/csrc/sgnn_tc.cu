@@ -32,11 +32,13 @@ cudaError_t sgnn_tc_launch(const ModelDev& M, const TcGeom& G, bool relu, bool r
                            float* sim, int64_t ld, cudaStream_t st) {
   __nv_bfloat16* A = static_cast<__nv_bfloat16*>(A_ws);
   __nv_bfloat16* B = static_cast<__nv_bfloat16*>(B_ws);
-  tc_prep_db_kernel<<<(G.n_gtiles * 128 * G.KCH + 255) / 256, 256, 0, st>>>(G, emb_db, A);
+  const int dk16 = G.KCH * 8;
+  if (dk16 > 128) return cudaErrorInvalidValue;
+  const int qpb = 128 / dk16;
+  const int q_blocks = (G.m + qpb - 1) / qpb;
+  const int db_blocks = (G.n_gtiles * 128 * G.KCH + 127) / 128;
+  tc_prep_kernel<<<q_blocks + db_blocks, 128, 0, st>>>(M, G, q_blocks, params, emb_q, emb_db, A, B);
   cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) return e;
-  tc_prep_q_kernel<<<(G.m + 3) / 4, 128, 0, st>>>(M, G, params, emb_q, B);
-  e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   if (G.K == 10) return dispatch<10>(relu, ref, simk, M, G, grid, smem, params, A, B, sim, ld, st);
   if (G.K == 16) return dispatch<16>(relu, ref, simk, M, G, grid, smem, params, A, B, sim, ld, st);

@@ -8,8 +8,8 @@
 
 struct TcGeom {
   int m, n, D, K;
-  int KC;          // accumulator columns per query: K, or K+1 with the |x| form of relu (see below)
-  int QH;          // queries per column half (= floor(128 / KC)); a q-block holds 2*QH queries
+  int KC;          // accumulator columns per query: K, or K+1 with the |x| form of relu
+  int QH;          // queries per q-block (= floor(128 / KC)): one q-block = one 128-row B tile
   int KCH;         // 16-byte K chunks per part (= round_up(D+1,16)/8)
   int parts;       // 1 = bf16, 2 = bf16x3 (hi + lo)
   int n_gtiles, n_qblocks;
@@ -17,15 +17,15 @@ struct TcGeom {
   int q_groups, qb_per_group;
 };
 
-constexpr int TC_NPAD = 256;     // MMA N: half h of the queries lives in columns [128h, 128h + QH*K)
-constexpr int TC_STAGES = 3;
+constexpr int TC_NPAD = 128;     // MMA N = accumulator columns of one tile (QH * KC of them used)
+constexpr int TC_BUFS = 4;       // TMEM accumulator buffers (4 x 128 columns = all 512)
+constexpr int TC_STAGES = 4;     // B-tile ring
 constexpr int TC_GA_MAX = 4;
 constexpr int TC_THREADS = 320;
 
 __host__ __device__ inline int tc_cols_per_query(int K, bool relu) { return relu ? K + 1 : K; }
 __host__ __device__ inline int tc_a_bytes(const TcGeom& G) { return G.parts * G.KCH * 128 * 16; }
 __host__ __device__ inline int tc_b_bytes(const TcGeom& G) { return G.parts * G.KCH * TC_NPAD * 16; }
-
 
 // prep kernels + allpairs_tc_kernel on `st` (defined in sgnn_tc.cu)
 cudaError_t sgnn_tc_launch(const ModelDev& M, const TcGeom& G, bool relu, bool ref, bool simk, int grid, size_t smem,

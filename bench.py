@@ -431,6 +431,9 @@ def main():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    # a hung kernel must not eat the GPU lease: dump every thread's stack and exit after the watchdog
+    import faulthandler
+    faulthandler.dump_traceback_later(int(os.environ.get('BENCH_WATCHDOG_S', '900')), exit=True)
     if args.impl == 'reference':
         run_reference(args)
     else:

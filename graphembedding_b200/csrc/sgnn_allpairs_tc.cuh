@@ -15,7 +15,7 @@
 // i.e. 16-byte rows, 8-row core matrices contiguous (SBO = 128 B), K chunks R*16 B apart (LBO).
 // The prep kernels write global memory in exactly this order, so a tile is ONE bulk async copy.
 //
-// Roles (320 threads): warps 0-7 epilogue in two groups of four (group = w/4 takes every other tile,
+// Roles (416 threads): warps 0-7 epilogue in two groups of four (group = w/4 takes every other tile,
 // warp w reads TMEM lanes 32(w%4)..), warp 8 bulk-copy producer, warp 9 MMA issuer.  TMEM: 4
 // accumulator buffers x 128 columns; the two groups are half a tile out of phase, so one group's
 // TMEM loads overlap the other's arithmetic on every scheduler.
@@ -108,7 +108,15 @@ struct TcEpi {
   float* sim;
   int64_t ld;
   int m, n;
+#ifdef SGNN_TC_TRACE
+  long long* trace; int tile;
+#endif
 };
+#ifdef SGNN_TC_TRACE
+#define TC_ESTAMP(slot) do { if (blockIdx.x == 0 && (threadIdx.x & 127) == 0 && (threadIdx.x >> 7) % 2 == 0) E.trace[E.tile * 8 + (slot)] = clock64(); } while (0)
+#else
+#define TC_ESTAMP(slot) do { } while (0)
+#endif
 
 __device__ __forceinline__ float tc_ex2(float x) {
   float y;
@@ -129,23 +137,26 @@ __device__ __forceinline__ float tc_finish(const TcEpi& E, float st) {
   }
 }
 
-// Epilogue of one accumulator half: this thread owns TMEM lane (database graph) g and walks the
-// columns of QH queries x KC accumulator columns.  KT > 0: K known at compile time; the whole half
-// is pulled into registers, the TMEM buffer is handed back to the MMA warp at once, and the
-// arithmetic + stores run from registers while the next tile's MMAs execute.
-template <int KT, bool RELU, bool REF, bool SIMK>
-__device__ __forceinline__ void tc_epilogue_half(const TcEpi& E, uint32_t taddr, int K, int KCr, int QH, int qrow0,
+// Epilogue of one tile part: this thread owns TMEM lane (database graph) g and the accumulator
+// columns of queries [Q0, Q0 + NQ) of the tile (PART 0: the first ceil(QH/2) queries, PART 1: the
+// rest).  KT > 0: K known at compile time; the part is pulled into registers with one wait, the
+// warp signals the buffer's MMA issuer at once (8 warps share a buffer), and the arithmetic + stores
+// run from registers while the other warps of the scheduler cover the TMEM load latency.
+template <int KT, bool RELU, bool REF, bool SIMK, int PART>
+__device__ __forceinline__ void tc_epilogue_part(const TcEpi& E, uint32_t taddr, int K, int KCr, int QH, int qrow0,
                                                  int g, uint64_t* t_empty, int lane) {
-  const int qmax = g < E.n ? min(QH, E.m - qrow0) : 0;   // queries this thread may store
-  float* p = E.sim + (size_t)qrow0 * E.ld + g;
   const int64_t ld = E.ld;
   if constexpr (KT > 0) {
     constexpr int KC = RELU ? KT + 1 : KT;
-    constexpr int QHC = 128 / KC, COLS = QHC * KC, NCH = (COLS + 31) / 32;
-    float v[NCH * 32];
-#pragma unroll
-    for (int c = 0; c < NCH; ++c) tc::tmem_ld32(taddr + c * 32, v + c * 32);
+    constexpr int QHC = 128 / KC, QA = (QHC + 1) / 2;
+    constexpr int Q0 = PART ? QA : 0, NQ = PART ? QHC - QA : QA, NC = NQ * KC;
+    const int qmax = g < E.n ? min(NQ, E.m - (qrow0 + Q0)) : 0;   // queries this thread may store
+    float* p = E.sim + (size_t)(qrow0 + Q0) * ld + g;
+    float v[NC > 0 ? NC : 1];
+    tc::tmem_ld_n<NC>(taddr + Q0 * KC, v);
+    TC_ESTAMP(5);
     tc::tmem_ld_wait();
+    TC_ESTAMP(7);
     tc::tc_fence_before();
     __syncwarp();
     if (lane == 0) tc::mbar_arrive(t_empty);
@@ -155,7 +166,7 @@ __device__ __forceinline__ void tc_epilogue_half(const TcEpi& E, uint32_t taddr,
       for (int k = 0; k < KT; ++k) u[k] = E.sU[k];
     }
 #pragma unroll
-    for (int q = 0; q < QHC; ++q) {
+    for (int q = 0; q < NQ; ++q) {
       float st;
       if constexpr (RELU) {
         st = v[q * KC + KT];   // sum_k w_k m_k from the tensor core
@@ -169,17 +180,22 @@ __device__ __forceinline__ void tc_epilogue_half(const TcEpi& E, uint32_t taddr,
           st = REF ? st + t : fmaf(u[k], t, st);
         }
       }
-      const float s = tc_finish<RELU, REF, SIMK>(E, st);
-      if (q < qmax) *p = s;
+      const float sv = tc_finish<RELU, REF, SIMK>(E, st);
+      if (q < qmax) *p = sv;
       p += ld;
     }
   } else {
-    const int cols = QH * KCr;
+    const int QA = (QH + 1) / 2;
+    const int q0 = PART ? QA : 0, nq = PART ? QH - QA : QA;
+    const int qmax = g < E.n ? min(nq, E.m - (qrow0 + q0)) : 0;
+    float* p = E.sim + (size_t)(qrow0 + q0) * ld + g;
+    const int cols = nq * KCr;
+    const uint32_t t0 = taddr + q0 * KCr;
     float st = 0.f;
     int kk = 0, qq = 0;
     for (int c0 = 0; c0 < cols; c0 += 8) {
       float v[8];
-      tc::tmem_ld8(taddr + c0, v);
+      tc::tmem_ld8(t0 + c0, v);   // may read past this part's columns, never past the 128-column tile + 7
       tc::tmem_ld_wait();
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
@@ -192,8 +208,8 @@ __device__ __forceinline__ void tc_epilogue_half(const TcEpi& E, uint32_t taddr,
             st += v[i];  // the sum column (RELU only: KCr == K + 1)
           }
           if (++kk == KCr) {
-            const float s = tc_finish<RELU, REF, SIMK>(E, st);
-            if (qq < qmax) p[(size_t)qq * ld] = s;
+            const float sv = tc_finish<RELU, REF, SIMK>(E, st);
+            if (qq < qmax) p[(size_t)qq * ld] = sv;
             st = 0.f; kk = 0; ++qq;
           }
         }
@@ -209,17 +225,26 @@ template <int KT, bool RELU, bool REF, bool SIMK>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 allpairs_tc_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const float* __restrict__ params,
                    const __nv_bfloat16* __restrict__ Ag, const __nv_bfloat16* __restrict__ Bg,
-                   float* __restrict__ sim, int64_t ld) {
+                   float* __restrict__ sim, int64_t ld
+#ifdef SGNN_TC_TRACE
+                   , long long* __restrict__ trace   // [tile][8] clock64 stamps of CTA 0 (tools/tc_trace.cu)
+#endif
+                   ) {
+#ifdef SGNN_TC_TRACE
+#define TC_STAMP(tile, slot) do { if (blockIdx.x == 0) trace[(tile) * 8 + (slot)] = clock64(); } while (0)
+#else
+#define TC_STAMP(tile, slot) do { } while (0)
+#endif
   extern __shared__ __align__(1024) uint8_t tc_smem[];
   uint8_t* smem = tc_smem;
   const int a_bytes = tc_a_bytes(G), b_bytes = tc_b_bytes(G);
   uint8_t* sA = smem;
   uint8_t* sB = sA + TC_GA_MAX * a_bytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + TC_STAGES * b_bytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + G.stages * b_bytes);
   uint64_t* a_full = bars;                 // [1]
-  uint64_t* b_full = bars + 1;             // [TC_STAGES]
-  uint64_t* b_empty = b_full + TC_STAGES;  // [TC_STAGES]
-  uint64_t* t_full = b_empty + TC_STAGES;  // [TC_BUFS]
+  uint64_t* b_full = bars + 1;             // [G.stages]
+  uint64_t* b_empty = b_full + G.stages;  // [G.stages]
+  uint64_t* t_full = b_empty + G.stages;  // [TC_BUFS]
   uint64_t* t_empty = t_full + TC_BUFS;    // [TC_BUFS]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + TC_BUFS);
   float* sU = reinterpret_cast<float*>(tmem_slot + 4);
@@ -234,19 +259,19 @@ allpairs_tc_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const flo
 
   if (threadIdx.x == 0) {
     tc::mbar_init(a_full, 1);
-    for (int s = 0; s < TC_STAGES; ++s) { tc::mbar_init(b_full + s, 1); tc::mbar_init(b_empty + s, 1); }
-    for (int b = 0; b < TC_BUFS; ++b) { tc::mbar_init(t_full + b, 1); tc::mbar_init(t_empty + b, 4); }
+    for (int s = 0; s < G.stages; ++s) { tc::mbar_init(b_full + s, 1); tc::mbar_init(b_empty + s, TC_BUFS); }
+    for (int b = 0; b < TC_BUFS; ++b) { tc::mbar_init(t_full + b, 1); tc::mbar_init(t_empty + b, 8); }
     tc::fence_barrier_init();
   }
   const bool dot = M.pair_kind == SGNN_LAYER_DOT;
   for (int k = threadIdx.x; k < G.K; k += blockDim.x) sU[k] = dot ? 1.f : params[M.u_off + k];
-  if (warp == 8) tc::tmem_alloc(tmem_slot, 512);
+  if (warp == TC_PROD_WARP) tc::tmem_alloc(tmem_slot, 512);
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 8) {
+  if (warp == TC_PROD_WARP) {
     // ===== producer: A tiles once, then the stream of query-block B tiles =====
     if (lane == 0 && nq > 0) {
       tc::mbar_arrive_expect_tx(a_full, ga_count * a_bytes);
@@ -254,46 +279,75 @@ allpairs_tc_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const flo
         tc::bulk_g2s(sA + ga * a_bytes, reinterpret_cast<const uint8_t*>(Ag) + (size_t)(gt0 + ga) * a_bytes,
                      a_bytes, a_full);
       for (int i = 0; i < nq; ++i) {
-        const int s = i % TC_STAGES;
-        if (i >= TC_STAGES) tc::mbar_wait(b_empty + s, ((i / TC_STAGES) - 1) & 1);
+        const int s = i % G.stages;
+        if (i >= G.stages) tc::mbar_wait(b_empty + s, ((i / G.stages) - 1) & 1);
         tc::mbar_arrive_expect_tx(b_full + s, b_bytes);
         tc::bulk_g2s(sB + s * b_bytes, reinterpret_cast<const uint8_t*>(Bg) + (size_t)(qb0 + i) * b_bytes, b_bytes,
                      b_full + s);
       }
     }
-  } else if (warp == 9) {
-    // ===== MMA issuer (one thread) =====
+  } else if (warp > TC_PROD_WARP) {
+    // ===== MMA issuers: warp 9 + w owns TMEM buffer w and the tiles it = w, w + 4, ... (one thread each).
+    // Measured with tools/tc_trace.cu: back-to-back tcgen05.mma into the SAME accumulator serialise at
+    // ~250 cycles each (the three bf16x3 products of a tile are such a chain) while chains on different
+    // accumulators overlap, and every scalar instruction of a lone issuing thread costs ~8 cycles.  So
+    // there is one short chain per buffer in flight, and the loop carries running descriptors instead of
+    // recomputing tile coordinates. =====
     if (lane == 0 && nq > 0) {
+      const int w = warp - TC_MMA_WARP0;
       const uint32_t idesc = tc::umma_idesc_bf16(128, TC_NPAD);
-      const uint32_t a_part = G.KCH * 128 * 16, b_part = G.KCH * TC_NPAD * 16;
+      const uint32_t a_part = (G.KCH * 128 * 16) >> 4, b_part = (G.KCH * TC_NPAD * 16) >> 4;   // in 16-byte units
+      const uint32_t a_ks = (2 * 128 * 16) >> 4, b_ks = (2 * TC_NPAD * 16) >> 4;
+      const uint64_t a_desc0 = tc::umma_desc(tc::smem_u32(sA), 128 * 16, 128);
+      const uint64_t b_desc0 = tc::umma_desc(tc::smem_u32(sB), TC_NPAD * 16, 128);
+      const uint32_t a_tile = (uint32_t)a_bytes >> 4, b_tile = (uint32_t)b_bytes >> 4;
+      const int combos = G.parts == 2 ? 3 : 1;
+      const int ksteps = G.KCH / 2;
+      const bool recycle = nq > G.stages;
+      const uint32_t d_addr = tmem_base + w * TC_NPAD;
+      const int total = nq * ga_count;
       tc::mbar_wait(a_full, 0);
-      int it = 0;
-      for (int i = 0; i < nq; ++i) {
-        const int s = i % TC_STAGES;
-        tc::mbar_wait(b_full + s, (i / TC_STAGES) & 1);
-        tc::tc_fence_after();
-        const uint32_t b_addr = tc::smem_u32(sB + s * b_bytes);
-        for (int ga = 0; ga < ga_count; ++ga, ++it) {
-          const int buf = it & (TC_BUFS - 1);
-          if (it >= TC_BUFS) tc::mbar_wait(t_empty + buf, ((it / TC_BUFS) - 1) & 1);
-          tc::tc_fence_after();
-          const uint32_t a_addr = tc::smem_u32(sA + ga * a_bytes);
-          const uint32_t d_addr = tmem_base + buf * TC_NPAD;
-          uint32_t acc = 0;
-          const int combos = G.parts == 2 ? 3 : 1;
-          for (int c = 0; c < combos; ++c) {
-            // (hi,hi) (hi,lo) (lo,hi)
-            const uint32_t ao = (c == 2) ? a_part : 0, bo = (c == 1) ? b_part : 0;
-            for (int ks = 0; ks < G.KCH / 2; ++ks) {
-              const uint64_t ad = tc::umma_desc(a_addr + ao + ks * 2 * (128 * 16), 128 * 16, 128);
-              const uint64_t bd = tc::umma_desc(b_addr + bo + ks * 2 * (TC_NPAD * 16), TC_NPAD * 16, 128);
-              tc::umma_bf16(d_addr, ad, bd, idesc, acc);
-              acc = 1;
-            }
-          }
-          tc::umma_commit(t_full + buf);
+      // running tile coordinates of it: (i, ga), B stage slot of i, parities
+      int i = w / ga_count, ga = w - i * ga_count;
+      int waited = 0, released = 0, slot_w = 0, par_w = 0, slot_r = 0;
+      int slot_i = i % G.stages;
+      uint32_t par_e = 1;   // parity of the previous phase of t_empty[w] (first wait is skipped)
+      for (int it = w; it < total; it += TC_BUFS) {
+        while (waited <= i) {   // B tiles arrive in order
+          tc::mbar_wait(b_full + slot_w, par_w);
+          ++waited;
+          if (++slot_w == G.stages) { slot_w = 0; par_w ^= 1; }
         }
-        tc::umma_commit(b_empty + s);
+        TC_STAMP(it, 0);
+        if (it >= TC_BUFS) tc::mbar_wait(t_empty + w, par_e);
+        par_e ^= 1;
+        tc::tc_fence_after();
+        TC_STAMP(it, 1);
+        const uint64_t ad0 = a_desc0 + (uint64_t)(ga * a_tile);
+        const uint64_t bd0 = b_desc0 + (uint64_t)(slot_i * b_tile);
+        uint32_t acc = 0;
+        for (int c = 0; c < combos; ++c) {   // (hi,hi) (hi,lo) (lo,hi)
+          const uint32_t ao = c == 2 ? a_part : 0u, bo = c == 1 ? b_part : 0u;
+          for (int ks = 0; ks < ksteps; ++ks) {
+            tc::umma_bf16(d_addr, ad0 + ao + (uint64_t)(ks * a_ks), bd0 + bo + (uint64_t)(ks * b_ks), idesc, acc);
+            acc = 1;
+          }
+        }
+        tc::umma_commit(t_full + w);
+        TC_STAMP(it, 2);
+        // advance (i, ga) by TC_BUFS tiles
+        ga += TC_BUFS;
+        while (ga >= ga_count) {
+          ga -= ga_count; ++i;
+          if (++slot_i == G.stages) slot_i = 0;
+        }
+        if (recycle) {   // hand back the B stages all of this warp's MMAs are done with (4 issuers: count 4)
+          const int upto = it + TC_BUFS < total ? i : nq;
+          for (; released < upto; ++released) {
+            tc::umma_commit(b_empty + slot_r);
+            if (++slot_r == G.stages) slot_r = 0;
+          }
+        }
       }
     }
   } else {
@@ -308,20 +362,34 @@ allpairs_tc_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const flo
       const float hs = REF ? 0.5f * su : 0.5f;
       E.c2 = -M.yeta * hs * hs * 1.4426950408889634f;
     }
-    // group `grp` takes tiles it = grp, grp + 2, ...; tile it lives in TMEM buffer it % 4
-    const int lg = warp & 3, grp = warp >> 2;
+    // group `grp` takes tiles it = grp, grp + 2, ...; tile it lives in TMEM buffer it % 4, so a buffer
+    // is only ever read by ONE group (TC_BUFS is a multiple of TC_EPI_GROUPS).  That matters: mbarrier
+    // waits are by phase parity, and a group that skipped a buffer's phase (because another group
+    // consumed it) can be two phases behind, where the parity wait aliases and returns at once.
+    const int lg = warp & 3, part = (warp >> 2) & 1, grp = warp >> 3;
     const int total = nq * ga_count;
-    for (int it = grp; it < total; it += 2) {
-      const int i = it / ga_count, ga = it - i * ga_count;
+    int i = grp / ga_count, ga = grp - i * ga_count;
+    for (int it = grp; it < total; it += TC_EPI_GROUPS) {
       const int buf = it & (TC_BUFS - 1);
+      if (lg == 0 && lane == 0) TC_STAMP(it, 3);
       tc::mbar_wait(t_full + buf, (it / TC_BUFS) & 1);
       tc::tc_fence_after();
+      if (lg == 0 && lane == 0) TC_STAMP(it, 4);
       const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + buf * TC_NPAD;
       const int g = (gt0 + ga) * 128 + lg * 32 + lane;
-      tc_epilogue_half<KT, RELU, REF, SIMK>(E, taddr, G.K, G.KC, G.QH, (qb0 + i) * G.QH, g, t_empty + buf, lane);
+#ifdef SGNN_TC_TRACE
+      E.trace = trace; E.tile = it;
+#endif
+      if (part == 0)
+        tc_epilogue_part<KT, RELU, REF, SIMK, 0>(E, taddr, G.K, G.KC, G.QH, (qb0 + i) * G.QH, g, t_empty + buf, lane);
+      else
+        tc_epilogue_part<KT, RELU, REF, SIMK, 1>(E, taddr, G.K, G.KC, G.QH, (qb0 + i) * G.QH, g, t_empty + buf, lane);
+      if (lg == 0 && lane == 0) TC_STAMP(it, 6);
+      ga += TC_EPI_GROUPS;
+      while (ga >= ga_count) { ga -= ga_count; ++i; }
     }
   }
   tc::tc_fence_before();
   __syncthreads();
-  if (warp == 8) tc::tmem_dealloc(tmem_base, 512);
+  if (warp == TC_PROD_WARP) tc::tmem_dealloc(tmem_base, 512);
 }

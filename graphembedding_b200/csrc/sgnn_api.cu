@@ -249,9 +249,12 @@ int score_all_pairs_tc(SgnnHandle h, const float* emb_q, int m, const float* emb
   const int64_t need_b = (int64_t)G.n_qblocks * G.parts * G.KCH * (TC_NPAD * 8);
   if (need_a > h->cap_Atc || need_b > h->cap_Btc)
     return fail(h, "tensor-core operand workspace too small: call sgnn_reserve(max_queries, max_db) first");
-  size_t smem = (size_t)TC_GA_MAX * tc_a_bytes(G) + (size_t)TC_STAGES * tc_b_bytes(G) + 256 + 4 * G.K;
+  const size_t fixed = (size_t)TC_GA_MAX * tc_a_bytes(G) + TC_TAIL_BYTES + 1024;
+  if (fixed + 2 * (size_t)tc_b_bytes(G) > (size_t)h->smem_optin)
+    return fail(h, "embedding too wide for the tensor-core all-pairs tiles");
+  G.stages = (int)std::min<size_t>(std::min(G.qb_per_group, TC_MAX_STAGES), ((size_t)h->smem_optin - fixed) / tc_b_bytes(G));
+  size_t smem = fixed + (size_t)G.stages * tc_b_bytes(G);
   smem = std::max<size_t>(smem, 120 * 1024);  // one CTA per SM: each CTA owns all 512 TMEM columns
-  if (smem > (size_t)h->smem_optin) return fail(h, "embedding too wide for the tensor-core all-pairs tiles");
   const int grid = g_groups * q_groups;
   const cudaError_t e = sgnn_tc_launch(M, G, relu, ref, simk, grid, smem, h->d_params, emb_q, emb_db, h->d_Atc,
                                        h->d_Btc, sim, ld, st);

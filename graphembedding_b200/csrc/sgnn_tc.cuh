@@ -3,6 +3,7 @@
 #pragma once
 #include <cuda_bf16.h>
 #include <stdint.h>
+#include <cstdio>
 
 namespace tc {
 
@@ -24,6 +25,24 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t by
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                : "memory");
 }
+#ifdef SGNN_TC_WATCHDOG
+// debug build (tools/tc_trace.cu): a wait that never completes reports who waits on what, then traps
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  for (long long spin = 0;; ++spin) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    if (ok) return;
+    if (spin == (1ll << 21) && (threadIdx.x & 31) == 0)
+      printf("mbar_wait stuck: block %d warp %d bar#%d parity %u\n", blockIdx.x, threadIdx.x >> 5,
+             (int)((smem_u32(bar) & 1023) / 8), parity);
+    if (spin > (1ll << 23)) __trap();
+  }
+}
+#else
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   asm volatile(
       "{\n\t"
@@ -37,6 +56,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "r"(parity)
       : "memory");
 }
+#endif
 
 // ---- bulk async copy global -> shared (TMA engine, no tensor map) ------------------------
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
@@ -116,6 +136,40 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
         "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
         "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
       : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld1(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];"
+               : "=r"(r[0])
+               : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld2(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0,%1}, [%2];"
+               : "=r"(r[0]), "=r"(r[1])
+               : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+               : "r"(taddr));
+}
+// N consecutive columns (any N <= 128) as a greedy sequence of power-of-two loads
+template <int N>
+__device__ __forceinline__ void tmem_ld_n(uint32_t taddr, float* v) {
+  if constexpr (N >= 32) { tmem_ld32(taddr, v); tmem_ld_n<N - 32>(taddr + 32, v + 32); }
+  else if constexpr (N >= 16) { tmem_ld16(taddr, v); tmem_ld_n<N - 16>(taddr + 16, v + 16); }
+  else if constexpr (N >= 8) { tmem_ld8(taddr, v); tmem_ld_n<N - 8>(taddr + 8, v + 8); }
+  else if constexpr (N >= 4) { tmem_ld4(taddr, v); tmem_ld_n<N - 4>(taddr + 4, v + 4); }
+  else if constexpr (N >= 2) { tmem_ld2(taddr, v); tmem_ld_n<N - 2>(taddr + 2, v + 2); }
+  else if constexpr (N == 1) { tmem_ld1(taddr, v); }
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 

@@ -15,17 +15,23 @@ struct TcGeom {
   int n_gtiles, n_qblocks;
   int GA;          // database tiles kept resident per CTA
   int q_groups, qb_per_group;
+  int stages;      // B-tile ring depth; == qb_per_group when all of a CTA's query blocks fit (no recycling)
 };
 
 constexpr int TC_NPAD = 128;     // MMA N = accumulator columns of one tile (QH * KC of them used)
 constexpr int TC_BUFS = 4;       // TMEM accumulator buffers (4 x 128 columns = all 512)
-constexpr int TC_STAGES = 4;     // B-tile ring
+constexpr int TC_MAX_STAGES = 24; // upper bound of the B-tile ring depth (barrier storage)
 constexpr int TC_GA_MAX = 4;
-constexpr int TC_THREADS = 320;
+constexpr int TC_EPI_GROUPS = 2;  // epilogue groups (must divide TC_BUFS); a group = 4 TMEM lane quadrants x 2 column parts
+constexpr int TC_EPI_WARPS = 8 * TC_EPI_GROUPS;
+constexpr int TC_PROD_WARP = TC_EPI_WARPS;        // bulk-copy producer
+constexpr int TC_MMA_WARP0 = TC_EPI_WARPS + 1;    // first of TC_BUFS MMA issuer warps
+constexpr int TC_THREADS = 32 * (TC_EPI_WARPS + 1 + TC_BUFS);
 
 __host__ __device__ inline int tc_cols_per_query(int K, bool relu) { return relu ? K + 1 : K; }
 __host__ __device__ inline int tc_a_bytes(const TcGeom& G) { return G.parts * G.KCH * 128 * 16; }
 __host__ __device__ inline int tc_b_bytes(const TcGeom& G) { return G.parts * G.KCH * TC_NPAD * 16; }
+constexpr int TC_TAIL_BYTES = (1 + 2 * TC_MAX_STAGES + 2 * TC_BUFS) * 8 + 16 + 4 * 64;   // barriers, TMEM slot, U
 
 // prep kernels + allpairs_tc_kernel on `st` (defined in sgnn_tc.cu)
 cudaError_t sgnn_tc_launch(const ModelDev& M, const TcGeom& G, bool relu, bool ref, bool simk, int grid, size_t smem,

@@ -290,23 +290,13 @@ def run_cuda(args):
     emb_db = torch.empty((N_DB, eng.emb_dim), dtype=torch.float32, device=dev)
     sim = torch.empty((M_QUERIES, N_DB), dtype=torch.float32, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    gath_v = torch.empty((world, M_QUERIES, TOPK), dtype=torch.float32, device=dev)
-    gath_i = torch.empty((world, M_QUERIES, TOPK), dtype=torch.int32, device=dev)
     out = {}
 
-    def step():
-        eng.embed(qd, out=emb_q)
-        eng.embed(dbd, out=emb_db)
-        eng.score_all_pairs(emb_q, emb_db, out=sim)
-        ids, vals = eng.topk(sim, TOPK)
-        if world > 1:  # database sharded over ranks: all-gather the per-shard top-k, merge with global ids
-            ids = ids + rank * N_DB
-            dist.all_gather_into_tensor(gath_v, vals)
-            dist.all_gather_into_tensor(gath_i, ids)
-            cv = gath_v.permute(1, 0, 2).reshape(M_QUERIES, world * TOPK).contiguous()
-            ci = gath_i.permute(1, 0, 2).reshape(M_QUERIES, world * TOPK).contiguous()
-            ids, vals = eng.topk_merge(cv, ci, TOPK)
-        out['ids'], out['vals'] = ids, vals
+    from graphembedding_b200 import distributed as DS
+
+    def step():   # database sharded over ranks: local top-k, all-gather of the candidates, merge (global ids)
+        out['ids'], out['vals'] = DS.sharded_rank(eng, qd, dbd, rank * N_DB, TOPK, dist if world > 1 else None,
+                                                  emb_q=emb_q, emb_db=emb_db, sim=sim)
 
     clocks = ClockSampler(local)
     clocks.start()
@@ -383,6 +373,7 @@ def run_cuda(args):
 
 def run_train(torch, dist, dev, rank, world, local, args, barrier, max_over_ranks):
     """BASELINE configs[2]: data-parallel training, TRAIN_BATCH pairs per GPU per step."""
+    from graphembedding_b200 import distributed as DS
     from graphembedding_b200.engine import SgnnEngine
     from graphembedding_b200.layers_factory import parse_layers
     enc, batch, batches = make_train_data(rank, world)
@@ -398,10 +389,7 @@ def run_train(torch, dist, dev, rank, world, local, args, barrier, max_over_rank
     def step(i):
         g1, g2, t, s1, s2 = feeds[i % len(feeds)]
         loss.zero_()
-        eng.train_step(bd, g1, g2, t, gb, s1, s2, loss=loss)
-        if world > 1:
-            dist.all_reduce(grads)      # one bucket: the whole flat gradient blob
-        eng.apply_adam(1.0, loss)
+        DS.data_parallel_step(eng, bd, g1, g2, t, gb, s1, s2, loss, dist if world > 1 else None, grads=grads)
 
     n = max(args.steps * 10, 100)
     for i in range(10):

@@ -1,0 +1,98 @@
+"""Multi-GPU plumbing of the two places the path shards; one process per GPU,
+``torch.distributed`` (NCCL on the GPUs, gloo in the CPU tests) for the collectives.
+
+* Training is data-parallel over the pair stream: pair ``t`` of the global mini-batch goes to rank
+  ``t mod R`` (so R = 1 and R = 8 see the same global batch), every rank runs ``sgnn_train_step`` on
+  its slice, ONE all-reduce sums the flat gradient blob (a single bucket: 11-40 KB), and every rank
+  applies the identical ``sgnn_apply_adam``.  The reference-mode loss (model_mse.py:145-151, SURVEY
+  F6) needs the target sum / square sum of the GLOBAL batch: targets are host data, so they are
+  computed on the host from the global batch -- no extra collective.
+* All-pairs ranking shards the DATABASE contiguously; queries are replicated.  Each rank scores its
+  m x n_r tile and keeps a local top-k with GLOBAL ids; the (score, id) candidates are all-gathered
+  (m x k x 8 bytes per rank) and merged with the reference's tie order (results.py:221-224: equal
+  scores -> higher index first), which ``sgnn_topk_merge`` reproduces on device.
+
+Nothing here touches the reference's semantics; the functions are written against plain tensors so
+that the world_size-2 gloo tests (tests/test_dist_gloo.py) exercise exactly the code the GPU path
+runs."""
+import numpy as np
+
+
+def shard_range(n, rank, world):
+    """Contiguous database shard [lo, hi) of rank ``rank``: sizes differ by at most one."""
+    base, rem = divmod(int(n), int(world))
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def pair_slice(global_batch, rank, world):
+    """Indices of the global mini-batch that rank ``rank`` trains on (t mod R == rank)."""
+    return np.arange(rank, int(global_batch), int(world))
+
+
+def global_target_stats(target_sim_global):
+    """(sum, sum of squares) of the global batch's target similarities in float64, the two
+    scalars ``sgnn_train_step`` needs for the reference-mode loss on a shard of the batch."""
+    t = np.asarray(target_sim_global, np.float64)
+    return float(t.sum()), float((t * t).sum())
+
+
+def allreduce_gradients(grads, dist=None, group=None):
+    """Sum the flat gradient blob over ranks in place (one bucket)."""
+    if dist is not None and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(grads, op=dist.ReduceOp.SUM, group=group)
+    return grads
+
+
+def gather_topk_candidates(local_vals, local_ids, id_offset, dist=None, group=None):
+    """All-gather the per-shard top-k and lay the candidates out as [m, world * k] with GLOBAL
+    database ids (local id + the shard's offset).  Returns (cand_vals, cand_ids)."""
+    import torch
+    ids = local_ids + int(id_offset)
+    world = dist.get_world_size(group) if dist is not None and dist.is_initialized() else 1
+    if world == 1:
+        return local_vals, ids
+    m, k = local_vals.shape
+    gv = torch.empty((world * m, k), dtype=local_vals.dtype, device=local_vals.device)   # rank-major concat
+    gi = torch.empty((world * m, k), dtype=ids.dtype, device=ids.device)
+    dist.all_gather_into_tensor(gv, local_vals.contiguous(), group=group)
+    dist.all_gather_into_tensor(gi, ids.contiguous(), group=group)
+    cv = gv.view(world, m, k).permute(1, 0, 2).reshape(m, world * k).contiguous()
+    ci = gi.view(world, m, k).permute(1, 0, 2).reshape(m, world * k).contiguous()
+    return cv, ci
+
+
+def merge_topk_host(cand_vals, cand_ids, k):
+    """Host statement of the merge ``sgnn_topk_merge`` performs on device: descending score, ties
+    -> higher GLOBAL id first (a stable ascending mergesort on (score, id) reversed,
+    results.py:221-224).  Used by the CPU tests; the GPU path calls the kernel."""
+    v = np.asarray(cand_vals)
+    i = np.asarray(cand_ids)
+    order = np.lexsort((i, v), axis=1)[:, ::-1][:, :k]
+    return np.take_along_axis(i, order, 1), np.take_along_axis(v, order, 1)
+
+
+def sharded_rank(engine, queries_dev, db_shard_dev, id_offset, k, dist=None, group=None, emb_q=None,
+                 emb_db=None, sim=None):
+    """One database-sharded ranking step on this rank: embed, score the local tile, local top-k,
+    all-gather, merge.  Returns (ids, vals) of the global top-k (identical on every rank)."""
+    emb_q = engine.embed(queries_dev, out=emb_q)
+    emb_db = engine.embed(db_shard_dev, out=emb_db)
+    sim = engine.score_all_pairs(emb_q, emb_db, out=sim)
+    ids, vals = engine.topk(sim, k)
+    world = dist.get_world_size(group) if dist is not None and dist.is_initialized() else 1
+    if world == 1 and id_offset == 0:
+        return ids, vals
+    cv, ci = gather_topk_candidates(vals, ids, id_offset, dist, group)
+    return engine.topk_merge(cv, ci, k)
+
+
+def data_parallel_step(engine, batch_dev, g1, g2, target_sim, global_batch, target_sum, target_sqsum, loss,
+                       dist=None, group=None, grads=None):
+    """One DP optimiser step: local fwd+bwd, gradient all-reduce, identical Adam on every rank."""
+    engine.train_step(batch_dev, g1, g2, target_sim, global_batch, target_sum, target_sqsum, loss=loss)
+    if grads is None:
+        grads = engine.device_buffers()[1]
+    allreduce_gradients(grads, dist, group)
+    engine.apply_adam(1.0, loss)
+    return loss

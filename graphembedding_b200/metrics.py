@@ -8,6 +8,39 @@ The reference evaluates O(m n^2) Python set intersections when ks = 1..n-1
 counts towards p@k once k >= max(its predicted position, its tie-inclusive true position)."""
 import numpy as np
 
+_ENGINE = None   # SgnnEngine whose device kernels evaluate precision@k / Kendall tau (set by use_engine)
+DEVICE_MAX_N = 10000   # row length the shared-memory metric kernels accept (sgnn_rank.cuh)
+
+
+def use_engine(engine):
+    """Route precision_at_ks / kendall_tau through the device kernels of ``engine``
+    (sgnn_precision_at_k / sgnn_kendall_tau); ``None`` restores the host (numpy) mirror of the
+    reference's own host implementation."""
+    global _ENGINE
+    _ENGINE = engine
+
+
+def _score_rows_f32(r, norm):
+    """Row scores where higher = more similar, as float32 (distances are negated).  Ties and
+    strict orderings of the float64 rows survive the cast: distances are small-integer ratios
+    2d/(n1+n2) and similarities come from the float32 device path."""
+    s = np.asarray(r.dist_sim_mat(norm), np.float64)
+    if hasattr(r, 'dist_mat'):
+        s = -s
+    return np.ascontiguousarray(s, np.float32)
+
+
+def _on_device(true_r, pred_r, norm):
+    if _ENGINE is None:
+        return None
+    m, n = true_r.m_n()
+    if n > DEVICE_MAX_N or n < 2:
+        return None
+    import torch
+    t = torch.as_tensor(_score_rows_f32(true_r, norm), device=_ENGINE.device)
+    p = torch.as_tensor(_score_rows_f32(pred_r, norm), device=_ENGINE.device)
+    return t, p
+
 
 class Metric(object):
     def __init__(self, name, ylabel):
@@ -37,6 +70,9 @@ def precision_at_ks(true_r, pred_r, norm, ks, print_ids=[]):
     ks = list(ks)
     for k in ks:
         assert type(k) is int and 0 < k < n
+    dev = _on_device(true_r, pred_r, norm)
+    if dev is not None and not print_ids:
+        return _ENGINE.precision_at_ks(dev[0], dev[1], ks).cpu().numpy()
     t_pos = _tie_inclusive_position(true_r.sort_id_mat(norm), true_r.dist_sim_mat(norm))
     p_ids = pred_r.sort_id_mat(norm)
     p_pos = np.empty((m, n), np.int64)
@@ -126,10 +162,16 @@ def _count_inversions(a):
 def kendall_tau(true_r, pred_r, norm):
     """Mean over queries of tau-b between the true and predicted SIMILARITY rows (a distance
     ground truth is negated so that higher = more similar on both sides)."""
+    dev = _on_device(true_r, pred_r, norm)
+    if dev is not None:
+        taus = _ENGINE.kendall_tau(dev[0], dev[1])[0].cpu().numpy()
+        return float(np.nanmean(taus)), taus
     t = true_r.dist_sim_mat(norm)
     if hasattr(true_r, 'dist_mat'):
         t = -t
     p = pred_r.dist_sim_mat(norm)
+    if hasattr(pred_r, 'dist_mat'):
+        p = -p
     taus = []
     for i in range(t.shape[0]):
         con, dis, tx, ty, txy = kendall_tau_counts(t[i], p[i])

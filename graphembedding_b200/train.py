@@ -124,8 +124,11 @@ def test(data, dist_calculator, model, saver, sess, eval_obj=None):
         from .eval import Eval
         eval_obj = Eval.from_data(data, dist_calculator, model)
     print('Evaluating...')
+    from . import metrics
+    metrics.use_engine(model.engine)          # precision@k / Kendall tau on the device
     results = eval_obj.eval_test(model.__class__.__name__.lower().replace('gcntnmse', '_gcntn_mse'),
                                  test_sim_mat, test_time_mat)
+    metrics.use_engine(None)
     print('Results generated with {} metrics'.format(len(results)))
     return results
 

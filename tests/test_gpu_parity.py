@@ -247,3 +247,30 @@ def test_precision_at_k_and_kendall_tau_on_device(n):
                 assert np.isnan(tau[i].item())
             else:
                 assert abs(tau[i].item() - ref_tau) <= 1e-12
+
+
+def test_metrics_module_routes_through_device_kernels():
+    """metrics.precision_at_ks / kendall_tau with an engine registered (device kernels) equal the
+    host mirror of the reference's src/metrics.py on a GED-style ground truth."""
+    from graphembedding_b200 import metrics
+    from graphembedding_b200.results import PairwiseGEDModelResult, SiameseModelResult
+    eng, *_ = _setup('default', 8)
+    rng = np.random.default_rng(4)
+    m, n = 9, 300
+    dist = rng.integers(0, 9, size=(m, n)).astype(np.float64)
+    qn, dn = rng.integers(2, 11, size=m), rng.integers(2, 11, size=n)
+    true_r = PairwiseGEDModelResult('syn', 'astar', dist, qn, dn, time_mat=np.zeros((m, n)))
+    pred = np.round(rng.random((m, n)), 2).astype(np.float32).astype(np.float64)
+    pred_r = SiameseModelResult('syn', 'siamese_gcntn_mse', sim_mat=pred, time_mat=np.zeros((m, n)))
+    ks = list(range(1, n))
+    for norm in (True, False):
+        host_p = metrics.precision_at_ks(true_r, pred_r, norm, ks)
+        host_t = metrics.kendall_tau(true_r, pred_r, norm)
+        metrics.use_engine(eng)
+        try:
+            dev_p = metrics.precision_at_ks(true_r, pred_r, norm, ks)
+            dev_t = metrics.kendall_tau(true_r, pred_r, norm)
+        finally:
+            metrics.use_engine(None)
+        assert np.allclose(dev_p, host_p, rtol=0, atol=1e-12)
+        assert np.allclose(dev_t[1], host_t[1], rtol=0, atol=1e-12, equal_nan=True)

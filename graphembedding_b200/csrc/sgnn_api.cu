@@ -37,6 +37,7 @@ struct SgnnHandle_t {
   std::vector<SgnnParamInfo> table;
   float *d_params = nullptr, *d_grads = nullptr, *d_m = nullptr, *d_v = nullptr, *d_loss = nullptr;
   int64_t adam_t = 0;
+  uint64_t drop_seed = 0, drop_counter = 0;   // dropout stream: one counter value per train/eval call
   float *d_P = nullptr, *d_C = nullptr;  // all-pairs query tables
   int64_t cap_P = 0;
   __nv_bfloat16 *d_Atc = nullptr, *d_Btc = nullptr;  // tensor-core operands in UMMA tile order
@@ -82,7 +83,7 @@ int build_model(const SgnnConfig& c, ModelDev& M, std::vector<SgnnParamInfo>& ta
   if (c.abi_version != SGNN_ABI_VERSION) { err = "SgnnConfig.abi_version mismatch"; return 1; }
   if (c.num_layers < 2 || c.num_layers > SGNN_MAX_LAYERS) { err = "num_layers must be in [2, 12]"; return 1; }
   if (c.input_dim < 1) { err = "input_dim must be >= 1"; return 1; }
-  if (c.dropout != 0.f) { err = "dropout > 0 is not implemented on the device path yet (run with --dropout=0)"; return 1; }
+  if (!(c.dropout >= 0.f && c.dropout < 1.f)) { err = "dropout must be in [0, 1)"; return 1; }
   int64_t off = 0;
   int cur = c.input_dim, stage = 0, act_cols = 0, dmax = 4, aux = 0;
   auto add = [&](int layer, const char* name, int nd, int s0, int s1, int s2) {
@@ -102,6 +103,7 @@ int build_model(const SgnnConfig& c, ModelDev& M, std::vector<SgnnParamInfo>& ta
       if (d.output_dim < 1 || d.output_dim > 128) { err = "output_dim must be in [1, 128]"; return 1; }
       LayerDev& L = M.L[M.n_node];
       L.kind = d.kind; L.din = d.input_dim; L.dout = d.output_dim; L.act = d.act; L.bias = d.bias;
+      L.drop = d.dropout && c.dropout > 0.f; L.ref = i;
       L.w_off = add(i, d.kind == SGNN_LAYER_GCN ? "weights_0" : "weights", 2, L.din, L.dout, 1);
       L.b_off = d.bias ? add(i, "bias", 1, L.dout, 1, 1) : 0;
       L.out_off = act_cols; act_cols += round_up(L.dout, 4);
@@ -128,6 +130,7 @@ int build_model(const SgnnConfig& c, ModelDev& M, std::vector<SgnnParamInfo>& ta
       if (d.kind == SGNN_LAYER_NTN) {
         if (d.input_dim != M.emb_dim) { err = "NTN: input_dim must equal the flattened representation width"; return 1; }
         M.K = d.aux; M.pair_act = d.act; M.pair_bias = d.bias;
+        M.pair_drop = d.dropout && c.dropout > 0.f; M.pair_ref = i;
         if (M.K < 1 || M.K > 64) { err = "NTN: feature_map_dim must be in [1, 64]"; return 1; }
         if ((int64_t)M.D * M.D * M.K > 32768) { err = "NTN: input_dim^2 * feature_map_dim must be <= 32768"; return 1; }
         M.w_off = add(i, "weights_W", 3, M.D, M.D, M.K);
@@ -144,6 +147,7 @@ int build_model(const SgnnConfig& c, ModelDev& M, std::vector<SgnnParamInfo>& ta
   if (stage != 2) { err = "the layer chain must end with NTN or Dot"; return 1; }
   if (M.emb_dim > 64) { err = "flattened representation wider than 64 is not supported"; return 1; }
   M.final_act = c.final_act; M.yeta = c.yeta; M.ntn_mode = c.ntn_mode; M.loss_mode = c.loss_mode;
+  M.keep = 1.0f - c.dropout; M.inv_keep = 1.0f / M.keep;
   M.n_params = (int)off; M.input_dim = c.input_dim;
   M.ld = round_up(dmax, 4) + 4;
   M.act_ld = act_cols + 4;
@@ -560,9 +564,18 @@ static int launch_pairs(SgnnHandle h, bool bwd, const SgnnGraphBatch* b, const i
   cudaStream_t st = (cudaStream_t)stream;
   const float invB = 1.0f / (float)global_batch;
   const float s1 = (float)target_sum, s2 = (float)target_sqsum;
+  // dropout is on for train, val and test alike (layers capture FLAGS.dropout as a constant)
+  const int dropping = h->cfg.dropout > 0.f;
+  uint32_t dbase = 0;
+  if (dropping) {
+    const uint32_t s32 = (uint32_t)(h->drop_seed ^ (h->drop_seed >> 32));
+    dbase = sgnn_fmix32(s32 ^ sgnn_fmix32((uint32_t)h->drop_counter + 0x9E3779B9u));
+    h->drop_counter += 1;
+  }
 #define SGNN_LAUNCH_PAIRS(NM, BW)                                                                        \
   train_pairs_kernel<NM, BW><<<blocks, wpb * 32, h->train_smem[v], st>>>(                                \
-      h->M, to_dev(b), h->d_params, g1, g2, target_sim, n_pairs, invB, s1, s2, h->d_grads, loss, raw, sim)
+      h->M, to_dev(b), h->d_params, g1, g2, target_sim, n_pairs, invB, s1, s2, h->d_grads, loss, raw, sim,      \
+      dropping, dbase)
   if (v == 0) { if (bwd) SGNN_LAUNCH_PAIRS(16, true); else SGNN_LAUNCH_PAIRS(16, false); }
   else { if (bwd) SGNN_LAUNCH_PAIRS(32, true); else SGNN_LAUNCH_PAIRS(32, false); }
 #undef SGNN_LAUNCH_PAIRS
@@ -600,6 +613,12 @@ int sgnn_apply_adam(SgnnHandle h, float grad_scale, float* loss_dev, void* strea
                                                        c.weight_decay, (float)lr_t, c.beta1, c.beta2, c.epsilon,
                                                        loss_dev);
   CUDA_OK(h, cudaGetLastError());
+  return 0;
+}
+
+int sgnn_set_dropout_stream(SgnnHandle h, uint64_t seed, uint64_t counter) {
+  if (!h) return 1;
+  h->drop_seed = seed; h->drop_counter = counter;
   return 0;
 }
 

@@ -11,6 +11,8 @@ struct LayerDev {
   float fparam;
   int out_off;   // column offset of this layer's output inside a saved-activation row (train)
   int wt_off;    // offset of the transposed copy inside the "aux weights" smem region
+  int drop;      // dropout on this layer's INPUT (spec dropout=True and FLAGS.dropout > 0)
+  int ref;       // index of the layer in the reference's layer list (dropout stream key)
 };
 
 // Flattened description of one model (SgnnConfig after validation).  Passed by value as a
@@ -29,6 +31,8 @@ struct ModelDev {
   int ld;                        // row stride (floats) of per-warp activation buffers
   int act_ld;                    // row stride of the saved-activation rows (train)
   int aux_floats;                // size of the transposed/permuted weight region (train)
+  int pair_drop, pair_ref;       // dropout on the pair layer's two inputs (layers.py:287-288)
+  float keep, inv_keep;          // keep_prob = 1 - FLAGS.dropout, and 1 / keep_prob
 };
 
 struct BatchDev {
@@ -59,6 +63,22 @@ __device__ __forceinline__ float sgnn_act_grad(float y, float x, int act, float 
     case SGNN_ACT_SIM_KERNEL: return -2.f * yeta * x * y;
     default: return 1.f;
   }
+}
+
+// ---- dropout stream (build-defined counter-based hash; oracle/siamese_oracle.py Dropout) ----
+// keep iff floor(keep_prob + u) == 1, kept values scaled by 1/keep_prob (layers.py:332-338, tf.nn.dropout)
+__host__ __device__ __forceinline__ uint32_t sgnn_fmix32(uint32_t x) {
+  x ^= x >> 16; x *= 0x85EBCA6Bu; x ^= x >> 13; x *= 0xC2B2AE35u; x ^= x >> 16;
+  return x;
+}
+__device__ __forceinline__ uint32_t drop_layer_key(uint32_t base, int slot, int layer) {
+  const uint32_t sk = sgnn_fmix32(base ^ ((uint32_t)slot * 0x9E3779B1u + 0x7F4A7C15u));
+  return sgnn_fmix32(sk ^ ((uint32_t)(layer + 1) * 0x85EBCA77u));
+}
+__device__ __forceinline__ float drop_mask(uint32_t layer_key, int row, int col, float keep, float inv_keep) {
+  const uint32_t h = sgnn_fmix32(layer_key + (uint32_t)(row * 131 + col) * 0x9E3779B9u);
+  const float u = (float)(h >> 8) * 5.9604644775390625e-8f;
+  return floorf(keep + u) >= 1.f ? inv_keep : 0.f;
 }
 
 __device__ __forceinline__ float warp_sum(float v) {

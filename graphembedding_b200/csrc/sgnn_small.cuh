@@ -113,21 +113,41 @@ __device__ __forceinline__ void warp_aggregate(const GraphS& G, const float* T, 
 }
 
 // One node-level layer (GCN or Dense).  Hin: [n][ldin]; T: scratch [n][ldt]; Hout: [n][ldo].
+// drop (training / single-pair evaluation with FLAGS.dropout > 0): dropout on the layer input.
+// Layer 0 masks whole one-hot rows (sparse_dropout: one draw per non-zero, layers.py:332-338) through
+// nmask[NMAX]; later layers mask Hin IN PLACE (so the saved activation is the masked one the weight
+// gradient needs).
 template <int NMAX>
 __device__ __forceinline__ void node_layer_fwd(const LayerDev& L, int l, const GraphS& G,
-                                               const float* W, const float* Hin, int ldin, float* T,
-                                               int ldt, float* Hout, int ldo, int lane) {
+                                               const float* W, float* Hin, int ldin, float* T,
+                                               int ldt, float* Hout, int ldo, int lane,
+                                               bool drop = false, uint32_t dkey = 0, float keep = 1.f,
+                                               float inv_keep = 1.f, float* nmask = nullptr) {
   const float* w = W + L.w_off;
   const float* b = L.bias ? W + L.b_off : nullptr;
+  if (drop && l > 0) {
+    for (int idx = lane; idx < G.n * L.din; idx += 32) {
+      const int i = idx / L.din, k = idx - i * L.din;
+      Hin[i * ldin + k] *= drop_mask(dkey, i, k, keep, inv_keep);
+    }
+    __syncwarp();
+  }
   if (L.kind == SGNN_LAYER_GCN) {
     if (l == 0) {
+      if (nmask) {
+        for (int i = lane; i < G.n; i += 32) nmask[i] = drop ? drop_mask(dkey, i, 0, keep, inv_keep) : 1.f;
+        __syncwarp();
+      }
       // sparse one-hot input (graphs.py:55-62): X.W is a row gather of W
       for (int j = lane; j < L.dout; j += 32) {
         const float bj = b ? b[j] : 0.f;
         for (int i = 0; i < G.n; ++i) {
           float s = 0.f;
-          for (int e = G.rp[i]; e < G.rp[i + 1]; ++e)
-            s = fmaf(G.val[e], w[G.lab[G.col[e]] * L.dout + j], s);
+          for (int e = G.rp[i]; e < G.rp[i + 1]; ++e) {
+            const int c = G.col[e];
+            const float v = nmask ? G.val[e] * nmask[c] : G.val[e];
+            s = fmaf(v, w[G.lab[c] * L.dout + j], s);
+          }
           Hout[i * ldo + j] = sgnn_act(s + bj, L.act, 0.f);
         }
       }
@@ -198,17 +218,19 @@ __device__ __forceinline__ void pool_fwd(const ModelDev& M, const GraphS& G, con
 template <int NMAX>
 __device__ __forceinline__ void graph_fwd(const ModelDev& M, const GraphS& G, const float* W,
                                           float* bufs, float* acts, float* emb, float* save,
-                                          int lane) {
+                                          int lane, uint32_t dbase = 0, int slot = 0, float* nmask = nullptr) {
   const int ld = M.ld;
   float* T = bufs + 2 * NMAX * ld;
-  const float* Hin = nullptr;
+  float* Hin = nullptr;
   int ldin = 0;
   for (int l = 0; l < M.n_node; ++l) {
     const LayerDev& L = M.L[l];
     float* Hout; int ldo;
     if (acts) { Hout = acts + L.out_off; ldo = M.act_ld; }
     else { Hout = bufs + (l & 1) * NMAX * ld; ldo = ld; }
-    node_layer_fwd<NMAX>(L, l, G, W, Hin, ldin, T, ld, Hout, ldo, lane);
+    const bool drop = nmask != nullptr && L.drop;   // nmask is only supplied by the dropout-enabled callers
+    const uint32_t dkey = drop ? drop_layer_key(dbase, slot, L.ref) : 0u;
+    node_layer_fwd<NMAX>(L, l, G, W, Hin, ldin, T, ld, Hout, ldo, lane, drop, dkey, M.keep, M.inv_keep, nmask);
     Hin = Hout; ldin = ldo;
   }
   pool_fwd(M, G, W, Hin, ldin, emb, save, lane);
@@ -338,7 +360,7 @@ pair_score_kernel(const __grid_constant__ ModelDev M, const float* __restrict__ 
 // parameter per CTA.
 // ---------------------------------------------------------------------------------------
 struct TrainLayout {
-  int acts, csr, save, emb, ubuf, vbuf, mbuf, tbuf, dmbuf, dx, gbuf, total;
+  int acts, csr, save, emb, ubuf, vbuf, mbuf, tbuf, dmbuf, dx, gbuf, nmask, total;
 };
 
 __host__ __device__ inline TrainLayout train_layout(const ModelDev& M, int nmax, int csr_words) {
@@ -357,6 +379,7 @@ __host__ __device__ inline TrainLayout train_layout(const ModelDev& M, int nmax,
   t.dmbuf = o; o += Kp;
   t.dx = o; o += 2 * ((M.emb_dim + r4) & ~r4) > 2 * Dp ? 2 * ((M.emb_dim + r4) & ~r4) : 2 * Dp;
   t.gbuf = o; o += 3 * nmax * M.ld;
+  t.nmask = o; o += 2 * nmax;   // layer-0 node masks of the two arms (dropout)
   t.total = o;
   return t;
 }
@@ -434,18 +457,26 @@ __device__ __forceinline__ void pool_bwd(const ModelDev& M, const GraphS& G, con
 template <int NMAX>
 __device__ __forceinline__ void graph_bwd(const ModelDev& M, const GraphS& G, const float* W,
                                           const float* s_aux, const float* acts, float* Gcur,
-                                          float* Gnxt, float* T, float* s_g, int lane) {
+                                          float* Gnxt, float* T, float* s_g, int lane,
+                                          bool dropping = false, uint32_t dbase = 0, int slot = 0,
+                                          const float* nmask = nullptr) {
   const int ld = M.ld, n = G.n;
   for (int l = M.n_node - 1; l >= 0; --l) {
     const LayerDev& L = M.L[l];
     const float* Hout = acts + L.out_off;
     const int dout = L.dout;
+    // If the NEXT node layer dropped its input, the saved Hout is y * mask (mask in {0, 1/keep}) and the
+    // incoming gradient is w.r.t. the masked value: dL/dy = g * mask, and y = saved * keep where kept.
+    const bool masked = dropping && l + 1 < M.n_node && M.L[l + 1].drop;
+    const uint32_t mkey = masked ? drop_layer_key(dbase, slot, M.L[l + 1].ref) : 0u;
     // dZ = dOut * act'(out); bias gradient
     for (int j = lane; j < dout; j += 32) {
       float sb = 0.f;
       for (int i = 0; i < n; ++i) {
-        const float y = Hout[i * M.act_ld + j];
-        const float g = Gcur[i * ld + j] * sgnn_act_grad(y, 0.f, L.act, 0.f);
+        float y = Hout[i * M.act_ld + j];
+        float g = Gcur[i * ld + j];
+        if (masked) { g *= drop_mask(mkey, i, j, M.keep, M.inv_keep); y *= M.keep; }
+        g *= sgnn_act_grad(y, 0.f, L.act, 0.f);
         Gcur[i * ld + j] = g;
         sb += g;
       }
@@ -459,9 +490,10 @@ __device__ __forceinline__ void graph_bwd(const ModelDev& M, const GraphS& G, co
       dXW = T;
     }
     if (l == 0) {
-      // one-hot input: dW[label_i][:] += dXW[i][:]
+      // one-hot input: dW[label_i][:] += mask_i * dXW[i][:]
       for (int j = lane; j < dout; j += 32)
-        for (int i = 0; i < n; ++i) atomicAdd(&s_g[L.w_off + G.lab[i] * dout + j], dXW[i * ld + j]);
+        for (int i = 0; i < n; ++i)
+          atomicAdd(&s_g[L.w_off + G.lab[i] * dout + j], nmask ? nmask[i] * dXW[i * ld + j] : dXW[i * ld + j]);
     } else {
       const float* Hin = acts + M.L[l - 1].out_off;
       const int din = L.din;
@@ -498,7 +530,7 @@ train_pairs_kernel(const __grid_constant__ ModelDev M, const BatchDev B,
                    const int32_t* __restrict__ g2, const float* __restrict__ target_sim, int n_pairs,
                    float inv_global_batch, float tsum, float tsqsum, float* __restrict__ grads,
                    float* __restrict__ loss, float* __restrict__ raw_out,
-                   float* __restrict__ sim_out) {
+                   float* __restrict__ sim_out, int dropping, uint32_t dbase) {
   extern __shared__ __align__(16) float smem[];
   using Geo = SmallGeom<NMAX>;
   const int wfl = (M.n_params + 3) / 4 * 4;
@@ -524,15 +556,21 @@ train_pairs_kernel(const __grid_constant__ ModelDev M, const BatchDev B,
 
   for (int p = blockIdx.x * wpb + warp; p < n_pairs; p += gridDim.x * wpb) {
     GraphS Gs[2];
-    float* acts[2]; float* embs[2]; float* saves[2];
+    float* acts[2]; float* embs[2]; float* saves[2]; float* nmask[2];
     const int gid[2] = {g1[p], g2[p]};
 #pragma unroll
     for (int s = 0; s < 2; ++s) {
       acts[s] = my + TL.acts + s * NMAX * M.act_ld;
       embs[s] = my + TL.emb + s * embp;
       saves[s] = my + TL.save + s * savep;
+      nmask[s] = dropping ? my + TL.nmask + s * NMAX : nullptr;
       Gs[s] = load_graph<NMAX>(B, gid[s], my + TL.csr + s * Geo::CSR_WORDS, lane);
-      graph_fwd<NMAX>(M, Gs[s], s_w, my + TL.gbuf, acts[s], embs[s], saves[s], lane);
+      graph_fwd<NMAX>(M, Gs[s], s_w, my + TL.gbuf, acts[s], embs[s], saves[s], lane, dbase, 2 * p + s, nmask[s]);
+      if (dropping && M.pair_drop) {   // dropout on the pair layer's inputs (layers.py:287-288)
+        const uint32_t key = drop_layer_key(dbase, 2 * p + s, M.pair_ref);
+        for (int a = lane; a < M.emb_dim; a += 32) embs[s][a] *= drop_mask(key, 0, a, M.keep, M.inv_keep);
+        __syncwarp();
+      }
     }
     float st = 0.f, su = 0.f;
     float* ub = my + TL.ubuf; float* vb = my + TL.vbuf; float* mb = my + TL.mbuf;
@@ -599,6 +637,15 @@ train_pairs_kernel(const __grid_constant__ ModelDev M, const BatchDev B,
       }
     }
     __syncwarp();
+    if (dropping && M.pair_drop) {   // gradient w.r.t. the un-dropped representations
+#pragma unroll
+      for (int s = 0; s < 2; ++s) {
+        const uint32_t key = drop_layer_key(dbase, 2 * p + s, M.pair_ref);
+        float* dx = s == 0 ? dx1 : dx2;
+        for (int a = lane; a < M.emb_dim; a += 32) dx[a] *= drop_mask(key, 0, a, M.keep, M.inv_keep);
+      }
+      __syncwarp();
+    }
 
     // ---- pooling + node layers backward for both arms ----
 #pragma unroll
@@ -607,7 +654,8 @@ train_pairs_kernel(const __grid_constant__ ModelDev M, const BatchDev B,
       const float* Hlast = acts[s] + M.L[M.n_node - 1].out_off;
       pool_bwd<NMAX>(M, Gs[s], s_w, s_aux + M.pool_wt_off, Hlast, M.act_ld, s == 0 ? dx1 : dx2,
                      saves[s], Gcur, M.ld, T, s_g, lane);
-      graph_bwd<NMAX>(M, Gs[s], s_w, s_aux, acts[s], Gcur, Gnxt, T, s_g, lane);
+      graph_bwd<NMAX>(M, Gs[s], s_w, s_aux, acts[s], Gcur, Gnxt, T, s_g, lane, dropping != 0, dbase, 2 * p + s,
+                      nmask[s]);
     }
     __syncwarp();
   }

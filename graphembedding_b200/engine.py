@@ -214,6 +214,10 @@ class SgnnEngine(object):
         check(self.h, lib().sgnn_apply_adam(self.h, float(grad_scale), _ptr(loss), _stream_ptr(stream)))
         self.launches += 1
 
+    def set_dropout_stream(self, seed, counter=0):
+        """Seed / position of the dropout mask stream (one counter value per train/eval call)."""
+        check(self.h, lib().sgnn_set_dropout_stream(self.h, int(seed), int(counter)))
+
     def zero_grads(self, stream=None):
         check(self.h, lib().sgnn_zero_grads(self.h, _stream_ptr(stream)))
 

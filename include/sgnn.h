@@ -73,7 +73,9 @@ typedef struct {
   float weight_decay;    /* config.py:104-105 */
   float learning_rate;   /* config.py:107 */
   float beta1, beta2, epsilon; /* tf.train.AdamOptimizer defaults, models.py:28-29 */
-  float dropout;         /* config.py:103 (0 for parity runs) */
+  float dropout;         /* config.py:103.  Honoured by sgnn_train_step / sgnn_eval_pairs (the reference
+                          * keeps dropout on for train, val and test alike); the batched
+                          * embedding / all-pairs entry points are deterministic (no dropout). */
   int32_t precision;     /* SGNN_PREC_* for the all-pairs scorer */
   int32_t device;        /* CUDA ordinal */
 } SgnnConfig;
@@ -182,6 +184,12 @@ int sgnn_eval_pairs(SgnnHandle h, const SgnnGraphBatch* batch_dev, const int32_t
  * loss_dev[1] = weight-decay loss term if loss_dev != NULL. */
 int sgnn_apply_adam(SgnnHandle h, float grad_scale, float* loss_dev, void* stream);
 int sgnn_zero_grads(SgnnHandle h, void* stream);
+/* Dropout masks (layers.py:45-49, 98-100, 196, 287-288, 332-338) come from a counter-based hash of
+ * (seed, counter, pair slot, layer, element): each sgnn_train_step / sgnn_eval_pairs call consumes one
+ * counter value.  TensorFlow's own random stream cannot be reproduced; the mask SEMANTICS (keep iff
+ * floor(keep_prob + u) == 1, scale 1/keep_prob, one draw per node for the sparse first layer) are the
+ * reference's. */
+int sgnn_set_dropout_stream(SgnnHandle h, uint64_t seed, uint64_t counter);
 
 /* ranking metrics on device (src/metrics.py:14-82, results.py:51-109; Kendall tau-b is
  * build-defined, pinned to scipy.stats.kendalltau).  true_sim/pred_sim are m x n. */

@@ -237,6 +237,53 @@ def _act(name, yeta=None):
     raise RuntimeError('Unknown activation function {}'.format(name))
 
 
+# ---------------------------------------------------------------------------
+# dropout  (layers.py:45-49, 98-100, 196, 287-288, 332-338)
+# ---------------------------------------------------------------------------
+# The reference draws its masks from TensorFlow's RNG, which cannot be reproduced without TF.  The
+# SEMANTICS are restated here (keep iff floor(keep_prob + u) == 1, kept values scaled by 1/keep_prob;
+# the sparse variant on layer 0 masks whole one-hot rows, i.e. one draw per node); the uniform stream
+# u is BUILD-DEFINED -- a counter-based hash shared by this oracle and the CUDA kernels, so that masks
+# are identical on both sides.  "parity unpinned by reference" for the stream itself.
+def _fmix32(x):
+    x = np.asarray(x, np.uint64) & np.uint64(0xFFFFFFFF)
+    x ^= x >> np.uint64(16)
+    x = (x * np.uint64(0x85EBCA6B)) & np.uint64(0xFFFFFFFF)
+    x ^= x >> np.uint64(13)
+    x = (x * np.uint64(0xC2B2AE35)) & np.uint64(0xFFFFFFFF)
+    x ^= x >> np.uint64(16)
+    return x
+
+
+class Dropout(object):
+    """Mask generator: ``mask(slot, layer, rows, cols)`` -> float64 array [rows, cols] of
+    {0, 1/keep_prob}.  slot = 2 * (pair index) + arm; layer = index in the layer list."""
+
+    def __init__(self, rate, seed=0, counter=0):
+        self.rate = float(rate)
+        self.keep = np.float32(1.0) - np.float32(rate)
+        seed = int(seed)
+        s32 = (seed ^ (seed >> 32)) & 0xFFFFFFFF
+        self.base = _fmix32(np.uint64(s32) ^ _fmix32((int(counter) + 0x9E3779B9) & 0xFFFFFFFF))
+
+    def uniform(self, slot, layer, rows, cols):
+        M = np.uint64(0xFFFFFFFF)
+        sk = _fmix32(self.base ^ np.uint64((int(slot) * 0x9E3779B1 + 0x7F4A7C15) & 0xFFFFFFFF))
+        lk = _fmix32(sk ^ np.uint64(((int(layer) + 1) * 0x85EBCA77) & 0xFFFFFFFF))
+        r = np.arange(rows, dtype=np.uint64)[:, None]
+        c = np.arange(cols, dtype=np.uint64)[None, :]
+        e = ((r * np.uint64(131) + c) * np.uint64(0x9E3779B9)) & M
+        h = _fmix32((lk + e) & M)
+        return (h >> np.uint64(8)).astype(np.float32) * np.float32(2.0 ** -24)
+
+    def mask(self, slot, layer, rows, cols):
+        if self.rate == 0.0:
+            return np.ones((rows, cols))
+        u = self.uniform(slot, layer, rows, cols)
+        keep = np.floor(self.keep + u) >= 1                                   # layers.py:334-336
+        return keep.astype(np.float64) * float(np.float32(1.0) / self.keep)   # :338, tf.nn.dropout
+
+
 class Graph(object):
     """One pre-processed graph: integer labels (one-hot column per node) and
     the normalised adjacency as COO, as ``ModelGraph`` holds them
@@ -263,22 +310,32 @@ class Graph(object):
         return a
 
 
-def graph_forward(layers, P, g, input_dim, dtype=torch.float64):
+def graph_forward(layers, P, g, input_dim, dtype=torch.float64, drop=None, slot=0):
     """Node-level layers + pooling for one graph; returns the flattened
     representation the pair layer consumes (layers.py:91-118, 136-140,
-    154-160, 192-205, 223-227)."""
+    154-160, 192-205, 223-227).  ``drop``: a Dropout (masks keyed by ``slot``)."""
+    def dmask(li, L, x, sparse=False):
+        if drop is None or not L.get('dropout', False) or drop.rate == 0.0:
+            return x
+        if sparse:      # sparse_dropout: one draw per non-zero = per node of the one-hot X
+            mk = drop.mask(slot, li, x.shape[0], 1)
+        else:
+            mk = drop.mask(slot, li, x.shape[0], x.shape[1])
+        return x * torch.as_tensor(mk, dtype=dtype)
     a = g.a_hat(dtype)
     x = torch.zeros((g.n, input_dim), dtype=dtype)       # one-hot, row-normalised (graphs.py:55-62)
     x[torch.arange(g.n), torch.as_tensor(g.labels)] = 1.0
     for li, L in enumerate(layers):
         k = L['kind']
-        if k == 'GraphConvolution':                       # layers.py:96-118 (dropout=0)
+        if k == 'GraphConvolution':                       # layers.py:96-118
+            x = dmask(li, L, x, sparse=bool(L.get('sparse_inputs', False)))
             pre = x @ P[(li, 'weights_0')]
             out = a @ pre
             if L['bias']:
                 out = out + P[(li, 'bias')]
             x = _act(L['act'])(out)
         elif k == 'Dense':                                # :192-205
+            x = dmask(li, L, x)
             out = x @ P[(li, 'weights')]
             if L['bias']:
                 out = out + P[(li, 'bias')]
@@ -303,7 +360,7 @@ def graph_forward(layers, P, g, input_dim, dtype=torch.float64):
     return x.reshape(-1)
 
 
-def pair_forward(layers, P, x1, x2, ntn_mode='reference'):
+def pair_forward(layers, P, x1, x2, ntn_mode='reference', drop=None, pair=0):
     """NTN / Dot on one pair of flattened representations (layers.py:249-252,
     282-310).  ``ntn_mode='reference'`` reproduces the (K,1)*(K,1,1)
     broadcast of layers.py:305-308 (F5): score = (sum U)(sum act(m)); 'paper'
@@ -312,6 +369,9 @@ def pair_forward(layers, P, x1, x2, ntn_mode='reference'):
     if L['kind'] == 'Dot':
         return (x1 * x2).sum()
     W, V, U = P[(li, 'weights_W')], P[(li, 'weights_V')], P[(li, 'weights_U')]
+    if drop is not None and L.get('dropout', False) and drop.rate != 0.0:    # layers.py:287-288
+        x1 = x1 * torch.as_tensor(drop.mask(2 * pair, li, 1, x1.numel()).reshape(-1), dtype=x1.dtype)
+        x2 = x2 * torch.as_tensor(drop.mask(2 * pair + 1, li, 1, x2.numel()).reshape(-1), dtype=x2.dtype)
     x1r, x2r = x1.reshape(1, -1), x2.reshape(1, -1)
     fm = []
     for k in range(L['feature_map_dim']):                 # layers.py:295-303
@@ -327,14 +387,14 @@ def pair_forward(layers, P, x1, x2, ntn_mode='reference'):
     return (U.reshape(-1) * tbp.reshape(-1)).sum()
 
 
-def forward_pairs(layers, P, g1s, g2s, input_dim, dtype=torch.float64, ntn_mode='reference'):
+def forward_pairs(layers, P, g1s, g2s, input_dim, dtype=torch.float64, ntn_mode='reference', drop=None):
     """Raw (pre final_act) scores for B pairs; arm i is paired with arm i+B
     (model_mse.py:117-126)."""
     outs = []
-    for g1, g2 in zip(g1s, g2s):
-        x1 = graph_forward(layers, P, g1, input_dim, dtype)
-        x2 = graph_forward(layers, P, g2, input_dim, dtype)
-        outs.append(pair_forward(layers, P, x1, x2, ntn_mode))
+    for p, (g1, g2) in enumerate(zip(g1s, g2s)):
+        x1 = graph_forward(layers, P, g1, input_dim, dtype, drop, 2 * p)
+        x2 = graph_forward(layers, P, g2, input_dim, dtype, drop, 2 * p + 1)
+        outs.append(pair_forward(layers, P, x1, x2, ntn_mode, drop, p))
     return torch.stack(outs)
 
 
@@ -377,10 +437,10 @@ class TFAdam(object):
 
 def loss_and_grads(layers, flat_params, g1s, g2s, targets_sim, input_dim, dtype=torch.float64,
                    final_act='sim_kernel', yeta=0.6, weight_decay=5e-4,
-                   loss_mode='reference', ntn_mode='reference'):
+                   loss_mode='reference', ntn_mode='reference', drop=None):
     """-> (loss, mse_part, predictions, flat gradient of the TOTAL loss)."""
     P = unflatten(layers, flat_params, dtype, requires_grad=True)
-    raw = forward_pairs(layers, P, g1s, g2s, input_dim, dtype, ntn_mode)
+    raw = forward_pairs(layers, P, g1s, g2s, input_dim, dtype, ntn_mode, drop)
     loss, mse, pred = total_loss(layers, P, raw, targets_sim, final_act, yeta, weight_decay, loss_mode)
     keys = [(li, name) for li, name, _ in param_table(layers)]
     grads = torch.autograd.grad(loss, [P[k] for k in keys], allow_unused=True)

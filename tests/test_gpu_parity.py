@@ -274,3 +274,45 @@ def test_metrics_module_routes_through_device_kernels():
             metrics.use_engine(None)
         assert np.allclose(dev_p, host_p, rtol=0, atol=1e-12)
         assert np.allclose(dev_t[1], host_t[1], rtol=0, atol=1e-12, equal_nan=True)
+
+
+@pytest.mark.parametrize('cfg', ['default', 'avg_ntn', 'att3', 'dense_dot'])
+def test_dropout_forward_and_gradients_match_oracle_with_same_masks(cfg):
+    """FLAGS.dropout > 0 (the reference default is 0.1 and it stays on at train/val/test).
+    Mask semantics are the reference's (layers.py:332-338); the uniform stream is a build-defined
+    counter hash shared with the oracle ("parity unpinned by reference" for the stream), so predictions,
+    loss and gradients must agree to the fp32 gate with identical masks on both sides."""
+    rate = 0.3
+    eng, layers, flat, gs, enc, batch = _setup(cfg, 40, loss_mode='paired', ntn_mode='reference', dropout=rate)
+    B = 20
+    rng = np.random.default_rng(12)
+    tgt = rng.uniform(0.05, 1.0, size=B).astype(np.float32)
+    dev = batch.to(eng.device)
+    g1 = torch.arange(0, B, dtype=torch.int32, device=eng.device)
+    g2 = torch.arange(B, 2 * B, dtype=torch.int32, device=eng.device)
+    og = oracle_graphs(gs, enc)
+    olayers = O.parse_layer_specs(CONFIGS[cfg], enc.input_dim())
+    for counter in (0, 7):
+        eng.set_dropout_stream(1234567, counter)
+        eng.zero_grads()
+        loss = eng.train_step(dev, g1, g2, torch.as_tensor(tgt, device=eng.device))
+        grads = eng.device_buffers()[1].cpu().numpy().astype(np.float64)
+        drop = O.Dropout(rate, seed=1234567, counter=counter)
+        l, mse, pred, ref_g, raw = O.loss_and_grads(olayers, flat, og[:B], og[B:2 * B], tgt, enc.input_dim(),
+                                                    weight_decay=0.0, loss_mode='paired', ntn_mode='reference',
+                                                    drop=drop)
+        assert abs(float(loss[0]) - mse) <= RTOL * max(abs(mse), 1e-3), (cfg, counter)
+        gscale = np.max(np.abs(ref_g))
+        assert np.max(np.abs(grads - ref_g)) <= 2e-4 * gscale, (cfg, counter)
+        # forward-only entry point ('val' / 'test' of run_tf) consumes the next counter value
+        _, raw_d, sim_d = eng.eval_pairs(dev, g1, g2)
+        drop2 = O.Dropout(rate, seed=1234567, counter=counter + 1)
+        P = O.unflatten(olayers, flat, torch.float64)
+        ref_raw = O.forward_pairs(olayers, P, og[:B], og[B:2 * B], enc.input_dim(), drop=drop2).numpy()
+        assert rel_err(raw_d.cpu().numpy(), ref_raw, floor=1e-2) <= 5 * RTOL, (cfg, counter)
+    # masks really drop something and differ between calls
+    no_drop = O.forward_pairs(olayers, P, og[:B], og[B:2 * B], enc.input_dim()).numpy()
+    if any(L.get('dropout') for L in olayers):      # dense_dot has dropout=False everywhere: masks are no-ops
+        assert np.max(np.abs(no_drop - ref_raw)) > 1e-3
+    else:
+        assert np.max(np.abs(no_drop - ref_raw)) == 0

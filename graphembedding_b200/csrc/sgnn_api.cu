@@ -38,6 +38,8 @@ struct SgnnHandle_t {
   float *d_params = nullptr, *d_grads = nullptr, *d_m = nullptr, *d_v = nullptr, *d_loss = nullptr;
   int64_t adam_t = 0;
   uint64_t drop_seed = 0, drop_counter = 0;   // dropout stream: one counter value per train/eval call
+  float *d_rowsA = nullptr, *d_rowsB = nullptr;   // large-graph path: node-row activations (global workspace)
+  int64_t cap_rows = 0;                           // in node rows
   float *d_P = nullptr, *d_C = nullptr;  // all-pairs query tables
   int64_t cap_P = 0;
   __nv_bfloat16 *d_Atc = nullptr, *d_Btc = nullptr;  // tensor-core operands in UMMA tile order
@@ -319,6 +321,7 @@ int sgnn_destroy(SgnnHandle h) {
   cudaSetDevice(h->device);
   cudaFree(h->d_params); cudaFree(h->d_grads); cudaFree(h->d_m); cudaFree(h->d_v); cudaFree(h->d_loss);
   cudaFree(h->d_P); cudaFree(h->d_C); cudaFree(h->d_Atc); cudaFree(h->d_Btc);
+  cudaFree(h->d_rowsA); cudaFree(h->d_rowsB);
   HostWs& w = h->ws;
   for (int s = 0; s < 2; ++s) {
     cudaFree(w.node_off[s]); cudaFree(w.labels[s]); cudaFree(w.rowptr[s]); cudaFree(w.col[s]); cudaFree(w.val[s]);
@@ -407,6 +410,11 @@ int sgnn_reserve(SgnnHandle h, int64_t max_graphs, int64_t max_nodes, int64_t ma
         dev_alloc(h, &w.emb_db, w.cap_graphs * E))
       return 1;
   }
+  if (max_nodes > h->cap_rows) {   // node-row workspace of the large-graph (N > 32) embedding kernel
+    const int64_t fl = max_nodes * (int64_t)sgnn_large_row_stride(h->M);
+    if (dev_alloc(h, &h->d_rowsA, fl) || dev_alloc(h, &h->d_rowsB, fl)) return 1;
+    h->cap_rows = max_nodes;
+  }
   if (max_pairs > w.cap_pairs) {
     w.cap_pairs = max_pairs;
     if (dev_alloc(h, &w.g1, max_pairs) || dev_alloc(h, &w.g2, max_pairs) || dev_alloc(h, &w.target, max_pairs) ||
@@ -449,9 +457,15 @@ int sgnn_reserve(SgnnHandle h, int64_t max_graphs, int64_t max_nodes, int64_t ma
 int sgnn_embed_graphs(SgnnHandle h, const SgnnGraphBatch* b, float* emb_dev, void* stream) {
   if (!h || !b || !emb_dev) return fail(h, "sgnn_embed_graphs: null argument");
   if (b->n_graphs == 0) return 0;
-  if (b->max_nodes > 32)
-    return fail(h, "graphs with more than 32 nodes need the large-graph path (not built yet)");
   cudaStream_t st = (cudaStream_t)stream;
+  if (b->max_nodes > 32) {   // Web-shaped / large graphs: CTA per graph, rows in the global workspace
+    if (b->total_nodes > h->cap_rows)
+      return fail(h, "node-row workspace too small for graphs with more than 32 nodes: call sgnn_reserve(max_nodes >= total_nodes) first");
+    const cudaError_t e = sgnn_launch_embed_large(h->M, to_dev(b), h->d_params, h->d_rowsA, h->d_rowsB, emb_dev,
+                                                  h->sm_count, h->smem_optin, st);
+    if (e != cudaSuccess) return fail(h, std::string("sgnn_embed_graphs (large-graph path): ") + cudaGetErrorString(e));
+    return 0;
+  }
   {
     const cudaError_t e = sgnn_launch_embed_tile(h->M, to_dev(b), b->max_nodes, h->d_params, emb_dev, h->sm_count,
                                                  h->smem_optin, st);

@@ -19,3 +19,8 @@ cudaError_t sgnn_launch_kendall(const float* true_sim, const float* pred_sim, in
 // does not fit this kernel's shared memory (the caller then uses the warp-per-graph kernel)
 cudaError_t sgnn_launch_embed_tile(const ModelDev& M, const BatchDev& B, int max_nodes, const float* params,
                                    float* emb, int sm_count, int smem_optin, cudaStream_t st);
+
+// CTA-per-graph embedding for graphs of any size; bufA / bufB: total_nodes x sgnn_large_row_stride floats each
+int sgnn_large_row_stride(const ModelDev& M);
+cudaError_t sgnn_launch_embed_large(const ModelDev& M, const BatchDev& B, const float* params, float* bufA,
+                                    float* bufB, float* emb, int sm_count, int smem_optin, cudaStream_t st);

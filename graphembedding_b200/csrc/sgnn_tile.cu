@@ -1,6 +1,8 @@
 // Translation unit of the node-per-thread small-graph kernels (sgnn_tile.cuh).
+#include "sgnn_large.cuh"
 #include "sgnn_tile.cuh"
 #include "sgnn_internal.h"
+#include <algorithm>
 
 cudaError_t sgnn_launch_embed_tile(const ModelDev& M, const BatchDev& B, int max_nodes, const float* params,
                                    float* emb, int sm_count, int smem_optin, cudaStream_t st) {
@@ -16,5 +18,20 @@ cudaError_t sgnn_launch_embed_tile(const ModelDev& M, const BatchDev& B, int max
   cudaError_t e = cudaFuncSetAttribute(embed_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   embed_tile_kernel<<<blocks, TILE_WARPS * 32, smem, st>>>(M, P, B, params, emb);
+  return cudaGetLastError();
+}
+
+int sgnn_large_row_stride(const ModelDev& M) { return make_emb_plan(M, 32).ldh; }
+
+cudaError_t sgnn_launch_embed_large(const ModelDev& M, const BatchDev& B, const float* params, float* bufA,
+                                    float* bufB, float* emb, int sm_count, int smem_optin, cudaStream_t st) {
+  const EmbPlan P = make_emb_plan(M, 32);
+  const int scratch = std::max(M.n_params, (2 + LARGE_THREADS / 32) * M.node_dim);
+  const size_t smem = ((size_t)P.w_floats + (size_t)round_up(scratch, 4)) * sizeof(float);
+  if (smem > (size_t)smem_optin) return cudaErrorInvalidValue;
+  cudaError_t e = cudaFuncSetAttribute(embed_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  const int blocks = std::min(B.n_graphs, sm_count * 8);
+  embed_large_kernel<<<blocks, LARGE_THREADS, smem, st>>>(M, P, B, nullptr, B.n_graphs, params, bufA, bufB, emb);
   return cudaGetLastError();
 }

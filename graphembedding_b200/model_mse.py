@@ -59,6 +59,7 @@ class SiameseGCNTNMSE(object):
             learning_rate=get('learning_rate'), dropout=get('dropout'), precision=get('precision'),
             device=get('device'))
         self.engine.init_params(get('seed'))                                # glorot / zeros, inits.py
+        self.engine.set_dropout_stream(get('seed'))                         # mask stream of FLAGS.dropout
         self.loss = Token('loss')
         self.opt_op = Token('opt_op')
         self.test_output = Token('test_output')

@@ -316,3 +316,36 @@ def test_dropout_forward_and_gradients_match_oracle_with_same_masks(cfg):
         assert np.max(np.abs(no_drop - ref_raw)) > 1e-3
     else:
         assert np.max(np.abs(no_drop - ref_raw)) == 0
+
+
+@pytest.mark.parametrize('cfg', ['avg_ntn', 'att3', 'dense_dot'])
+def test_web_shaped_large_graphs_match_oracle(cfg):
+    """BASELINE configs[4]: Web-shaped graphs (100..500 nodes, E ~ 2N) go through the CTA-per-graph
+    large-graph embedding kernel (CSR neighbour gather over global node rows) + the pair layer."""
+    from graphembedding_b200.graphs import pack_nx_graphs
+    from graphembedding_b200.engine import SgnnEngine
+    from graphembedding_b200.layers_factory import parse_layers
+    gs = corpus(16, 100, 500, seed=21)
+    gs += corpus(6, 2, 40, seed=22)            # mixed sizes in one batch (small graphs take the same kernel)
+    enc = encoder_for(gs)
+    layers = parse_layers(CONFIGS[cfg], enc.input_dim())
+    eng = SgnnEngine(layers, enc.input_dim())
+    flat = O.init_params(O.parse_layer_specs(CONFIGS[cfg], enc.input_dim()), seed=3)
+    flat = flat + (np.random.default_rng(1).standard_normal(flat.shape) * 0.01).astype(np.float32)
+    eng.set_params(flat)
+    batch = pack_nx_graphs(gs, enc)
+    assert batch.max_nodes > 100
+    with pytest.raises(RuntimeError, match='sgnn_reserve'):
+        eng.embed(batch.to(eng.device))          # the node-row workspace must be reserved first
+    eng.reserve(max_nodes=batch.total_nodes)
+    emb = eng.embed(batch.to(eng.device)).cpu().numpy()
+    P = O.unflatten(layers, flat, torch.float64)
+    og = oracle_graphs(gs, enc)
+    ref = np.stack([O.graph_forward(layers, P, g, enc.input_dim(), torch.float64).numpy() for g in og])
+    assert np.max(np.abs(emb - ref)) <= RTOL * max(1.0, np.max(np.abs(ref))), cfg
+    B = len(gs) // 2
+    g1 = torch.arange(0, B, dtype=torch.int32, device=eng.device)
+    g2 = torch.arange(B, 2 * B, dtype=torch.int32, device=eng.device)
+    raw, _ = eng.forward_pairs(batch.to(eng.device), g1, g2)
+    ref_raw = O.forward_pairs(layers, P, og[:B], og[B:2 * B], enc.input_dim(), torch.float64).numpy()
+    assert np.max(np.abs(raw.cpu().numpy() - ref_raw)) <= RTOL * max(1.0, np.max(np.abs(ref_raw))), cfg

@@ -32,16 +32,33 @@ __device__ __forceinline__ void split_bf16(float x, __nv_bfloat16& hi, __nv_bflo
 // Operand preparation, ONE launch: blocks [0, q_blocks) build the B tiles (queries), the rest the A
 // tiles (database graphs).
 //
-// B: thread = (query, kk); it walks the K feature maps of its column kk of P' / C.  With
-// KC == K + 1 (relu inner activation) row K of the query holds sum_k w_k * row_k (w = 1 in reference
-// mode, U in paper mode): the tensor core then also delivers sum_k w_k m_k, and
+// B is a small GEMM: out[q][c] = const[c] + sum_a x_q[a] * Wm[a][c] over the columns c = (kk, k) of
+// P' / C (kk < D: P'[q][k][kk] = V[k][D+kk] + sum_a x[a] W[a][kk][k];  kk == D: C[q][k] = b[k] +
+// V[k][0:D] . x;  above: 0).  A block stages the coefficient columns of PREP_COLS columns once and
+// applies them to PREP_Q queries held in shared memory (x broadcast as float4).  With KC == K + 1
+// (relu inner activation) column (kk, K) holds sum_k w_k * column (kk, k) (w = 1 in reference mode,
+// U in paper mode): the tensor core then also delivers sum_k w_k m_k, and
 //   sum_k w_k relu(m_k) = (sum_k w_k m_k + sum_k w_k |m_k|) / 2
 // costs ONE add-with-|x|-modifier per accumulator element in the epilogue instead of max + add.
 // A: one thread per (database graph, K chunk).
-__global__ void __launch_bounds__(128)
-tc_prep_kernel(const __grid_constant__ ModelDev M, const TcGeom G, int q_blocks, const float* __restrict__ params,
-               const float* __restrict__ emb_q, const float* __restrict__ emb_db, __nv_bfloat16* __restrict__ A,
-               __nv_bfloat16* __restrict__ B) {
+constexpr int PREP_COLS = 256;   // = block size
+constexpr int PREP_Q = 8;
+
+__device__ __forceinline__ float tc_prep_coef(const ModelDev& M, const float* __restrict__ params, int D, int K, int a,
+                                              int kk, int k) {   // a == D: the constant term
+  if (M.pair_kind == SGNN_LAYER_DOT) return (a < D && a == kk) ? 1.f : 0.f;
+  const float* W = params + M.w_off;
+  const float* V = params + M.v_off;
+  if (kk < D) return a < D ? W[a * D * K + kk * K + k] : V[k * 2 * D + D + kk];
+  if (kk == D) return a < D ? V[k * 2 * D + a] : (M.pair_bias ? params[M.b_off + k] : 0.f);
+  return 0.f;
+}
+
+__global__ void __launch_bounds__(PREP_COLS)
+tc_prep_kernel(const __grid_constant__ ModelDev M, const TcGeom G, int q_blocks, int col_blocks,
+               const float* __restrict__ params, const float* __restrict__ emb_q,
+               const float* __restrict__ emb_db, __nv_bfloat16* __restrict__ A, __nv_bfloat16* __restrict__ B) {
+  extern __shared__ __align__(16) float prep_smem[];
   if ((int)blockIdx.x >= q_blocks) {
     const int idx = (blockIdx.x - q_blocks) * blockDim.x + threadIdx.x;
     const int total = G.n_gtiles * 128 * G.KCH;
@@ -62,42 +79,63 @@ tc_prep_kernel(const __grid_constant__ ModelDev M, const TcGeom G, int q_blocks,
       *reinterpret_cast<uint4*>(A + base + (size_t)G.KCH * 1024) = *reinterpret_cast<const uint4*>(lo);
     return;
   }
-  const int D = G.D, K = G.K, DK16 = G.KCH * 8, DK = D * K;
-  const int qpb = blockDim.x / DK16;
-  const int ql = threadIdx.x / DK16, kk = threadIdx.x - ql * DK16;
-  const int q = blockIdx.x * qpb + ql;
-  if (ql >= qpb || q >= G.m) return;
-  const int qb = q / G.QH, qq = q - qb * G.QH;
-  const int row0 = qq * G.KC;
-  const float* x = emb_q + (size_t)q * D;
-  const bool dot = M.pair_kind == SGNN_LAYER_DOT;
-  const bool ref = M.ntn_mode == SGNN_NTN_REFERENCE;
-  const float* W = params + M.w_off;
-  const float* V = params + M.v_off;
-  __nv_bfloat16* Bq = B + ((size_t)(qb * G.parts) * G.KCH + (kk >> 3)) * (TC_NPAD * 8) + (kk & 7);
-  const size_t lo_off = (size_t)G.KCH * TC_NPAD * 8;
-  auto put = [&](int row, float v) {
-    __nv_bfloat16 hi, lo;
-    split_bf16(v, hi, lo);
-    Bq[(size_t)row * 8] = hi;
-    if (G.parts == 2) Bq[(size_t)row * 8 + lo_off] = lo;
-  };
-  float sum = 0.f;
-  for (int k = 0; k < K; ++k) {
-    float v = 0.f;
-    if (dot) {
-      v = kk < D ? x[kk] : 0.f;
-    } else if (kk < D) {          // P'[q][k][kk] = V[k][D + kk] + sum_a x[a] W[a][kk][k]
-      v = V[k * 2 * D + D + kk];
-      for (int a = 0; a < D; ++a) v = fmaf(x[a], W[a * DK + kk * K + k], v);
-    } else if (kk == D) {         // C[q][k] = b[k] + V[k][0:D] . x
-      v = M.pair_bias ? params[M.b_off + k] : 0.f;
-      for (int a = 0; a < D; ++a) v = fmaf(V[k * 2 * D + a], x[a], v);
-    }
-    put(row0 + k, v);
-    sum = fmaf(dot || ref ? 1.f : params[M.u_off + k], v, sum);
+  const int D = G.D, K = G.K, KC = G.KC, DK16 = G.KCH * 8;
+  const int C = DK16 * KC;
+  const int cpb = (PREP_COLS / KC) * KC;          // columns per block: whole (kk, 0..KC) groups
+  const int cb = blockIdx.x % col_blocks, qblk = blockIdx.x / col_blocks;
+  const int c = cb * cpb + threadIdx.x;
+  const int q0 = qblk * PREP_Q;
+  float* Wm = prep_smem;                          // [D + 1][PREP_COLS]
+  float* xs = prep_smem + (D + 1) * PREP_COLS;    // [D][PREP_Q] (transposed: queries contiguous)
+  const bool on = (int)threadIdx.x < cpb && c < C;
+  const int kk = on ? c / KC : 0, k = on ? c - kk * KC : 0;
+  const bool ref = M.pair_kind == SGNN_LAYER_DOT || M.ntn_mode == SGNN_NTN_REFERENCE;
+  if (on && k < K)
+    for (int a = 0; a <= D; ++a) Wm[a * PREP_COLS + threadIdx.x] = tc_prep_coef(M, params, D, K, a, kk, k);
+  for (int i = threadIdx.x; i < D * PREP_Q; i += blockDim.x) {
+    const int a = i / PREP_Q, qq = i - a * PREP_Q;
+    xs[i] = q0 + qq < G.m ? emb_q[(size_t)(q0 + qq) * D + a] : 0.f;
   }
-  if (G.KC > K) put(row0 + K, sum);
+  __syncthreads();
+  if (on && k == K) {   // the sum column: its K source columns sit just left of it in shared memory
+    for (int a = 0; a <= D; ++a) {
+      float v = 0.f;
+      for (int kq = 0; kq < K; ++kq)
+        v = fmaf(ref ? 1.f : params[M.u_off + kq], Wm[a * PREP_COLS + threadIdx.x - K + kq], v);
+      Wm[a * PREP_COLS + threadIdx.x] = v;
+    }
+  }
+  __syncthreads();
+  if (!on) return;
+  float acc[PREP_Q];
+  const float cst = Wm[D * PREP_COLS + threadIdx.x];
+#pragma unroll
+  for (int qq = 0; qq < PREP_Q; ++qq) acc[qq] = cst;
+  for (int a = 0; a < D; ++a) {
+    const float w = Wm[a * PREP_COLS + threadIdx.x];
+    const float4* x4 = reinterpret_cast<const float4*>(xs + a * PREP_Q);
+#pragma unroll
+    for (int v4 = 0; v4 < PREP_Q / 4; ++v4) {
+      const float4 x = x4[v4];
+      acc[4 * v4 + 0] = fmaf(x.x, w, acc[4 * v4 + 0]);
+      acc[4 * v4 + 1] = fmaf(x.y, w, acc[4 * v4 + 1]);
+      acc[4 * v4 + 2] = fmaf(x.z, w, acc[4 * v4 + 2]);
+      acc[4 * v4 + 3] = fmaf(x.w, w, acc[4 * v4 + 3]);
+    }
+  }
+  const size_t lo_off = (size_t)G.KCH * TC_NPAD * 8;
+#pragma unroll
+  for (int qq = 0; qq < PREP_Q; ++qq) {
+    const int q = q0 + qq;
+    if (q < G.m) {
+      const int qb = q / G.QH, row = (q - qb * G.QH) * KC + k;
+      __nv_bfloat16* dst = B + ((size_t)(qb * G.parts) * G.KCH + (kk >> 3)) * (TC_NPAD * 8) + (size_t)row * 8 + (kk & 7);
+      __nv_bfloat16 hi, lo;
+      split_bf16(acc[qq], hi, lo);
+      *dst = hi;
+      if (G.parts == 2) dst[lo_off] = lo;
+    }
+  }
 }
 
 struct TcEpi {

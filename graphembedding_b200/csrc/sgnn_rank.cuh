@@ -72,71 +72,115 @@ __device__ __forceinline__ float rank_key_score(unsigned long long key) {
   return __uint_as_float(u);
 }
 
-// Top-k for k <= 256, two streaming passes over the row instead of k.  Pass 1: every thread
-// keeps the largest key of its strided slice; the k-th largest of those 256 slice maxima is a
-// lower bound of the k-th largest key of the row (k distinct elements are >= it).  Pass 2 gathers
-// the (few) keys >= that bound into shared memory, where each candidate finds its rank by
-// counting.  Falls back to the k-round selection when more than TOPK_CAND keys survive.
+// Top-k for k <= 256, two streaming passes over the row instead of k.  Pass 1: every thread keeps
+// the largest (score, index) key of its slice.  Each warp sorts its 32 slice maxima (register bitonic
+// sort over shuffles) and publishes its j-th largest, j = ceil(k / 8); the minimum L of the eight
+// published keys has at least 8 j >= k elements >= it, so L is a lower bound of the row's k-th
+// largest key.  Pass 2 gathers the (few) keys >= L into shared memory, where each candidate finds its
+// exact rank by counting.  Keys carry the index, so ties cost nothing extra.  Rows with more than
+// TOPK_CAND survivors fall back to k selection rounds.  Rows are read as float4 when aligned.
 constexpr int TOPK_CAND = 1024;
+
+__device__ __forceinline__ unsigned int orderable_u32(float f) {
+  f += 0.f;   // -0.0 -> +0.0 (numpy compares them equal)
+  const unsigned int u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
 
 __global__ void __launch_bounds__(256)
 topk_select_kernel(const float* __restrict__ sim, const int32_t* __restrict__ col_ids, int n, int64_t ld,
                    int k, int32_t* __restrict__ ids, float* __restrict__ vals) {
-  __shared__ unsigned long long s_max[256];
   __shared__ unsigned long long s_cand[TOPK_CAND];
   __shared__ unsigned long long s_red[32];
-  __shared__ unsigned long long s_thr;
+  __shared__ unsigned long long s_warp[8];
   __shared__ int s_cnt;
   const float* r = sim + (size_t)blockIdx.x * ld;
   const int32_t* cid = col_ids ? col_ids + (size_t)blockIdx.x * ld : nullptr;
-  const int tid = threadIdx.x;
-  unsigned long long best = 0ull;
-#pragma unroll 8
-  for (int i = tid; i < n; i += 256) {
-    const unsigned long long key = rank_key(r[i], cid ? cid[i] : i);
-    best = key > best ? key : best;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const bool vec = (ld & 3) == 0 && (reinterpret_cast<uintptr_t>(sim) & 15) == 0;
+  const int n4 = vec ? n >> 2 : 0;
+  const float4* r4 = reinterpret_cast<const float4*>(r);
+  // slice maximum: element positions grow inside a thread, so ">=" keeps the higher position on ties
+  unsigned int bu = 0u;
+  int bi = -1;
+  auto see = [&](float f, int i) {
+    const unsigned int u = orderable_u32(f);
+    if (u >= bu) { bu = u; bi = i; }
+  };
+#pragma unroll 4
+  for (int i = tid; i < n4; i += 256) {
+    const float4 v = r4[i];
+    see(v.x, 4 * i); see(v.y, 4 * i + 1); see(v.z, 4 * i + 2); see(v.w, 4 * i + 3);
   }
-  s_max[tid] = best;
-  if (tid == 0) s_cnt = 0;
-  __syncthreads();
-  if (best != 0ull) {
-    int above = 0;
-#pragma unroll 8
-    for (int j = 0; j < 256; ++j) above += s_max[j] > best ? 1 : 0;
-    if (above == k - 1) s_thr = best;   // keys are unique: exactly one thread
-  }
-  __syncthreads();
-  const unsigned long long thr = s_thr;
-#pragma unroll 8
-  for (int i = tid; i < n; i += 256) {
-    const unsigned long long key = rank_key(r[i], cid ? cid[i] : i);
-    if (key >= thr) {
-      const int pos = atomicAdd(&s_cnt, 1);
-      if (pos < TOPK_CAND) s_cand[pos] = key;
+  for (int i = 4 * n4 + tid; i < n; i += 256) see(r[i], i);
+  unsigned long long key = 0ull;
+  if (bi >= 0) {
+    key = ((unsigned long long)bu << 32) | (unsigned int)(cid ? cid[bi] : bi);
+    if (cid) {   // merge mode: ties break on the carried (global) id, not on the position
+      // the slice maximum by (score, id) may be another position with the same score: rescan the ties
+      for (int i = tid; i < n; i += 256)
+        if (orderable_u32(r[i]) == bu) {
+          const unsigned long long kk = ((unsigned long long)bu << 32) | (unsigned int)cid[i];
+          key = kk > key ? kk : key;
+        }
     }
   }
+  if (tid == 0) s_cnt = 0;
+  // descending bitonic sort of the warp's 32 keys
+#pragma unroll
+  for (int k2 = 2; k2 <= 32; k2 <<= 1) {
+#pragma unroll
+    for (int j2 = k2 >> 1; j2 > 0; j2 >>= 1) {
+      const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, j2);
+      const bool take_max = ((lane & j2) == 0) == ((lane & k2) == 0);
+      key = take_max ? (key > other ? key : other) : (key < other ? key : other);
+    }
+  }
+  const int j = (k + 7) >> 3;   // 1..32
+  const unsigned long long tw = __shfl_sync(0xffffffffu, key, j - 1);
+  if (lane == 0) s_warp[warp] = tw;
+  __syncthreads();
+  unsigned long long thr = s_warp[0];
+#pragma unroll
+  for (int w = 1; w < 8; ++w) thr = s_warp[w] < thr ? s_warp[w] : thr;
+  auto push = [&](float f, int i) {
+    const unsigned int u = orderable_u32(f);
+    if (u >= (unsigned int)(thr >> 32)) {   // cheap 32-bit pre-filter, then the exact 64-bit test
+      const unsigned long long kk = ((unsigned long long)u << 32) | (unsigned int)(cid ? cid[i] : i);
+      if (kk >= thr) {
+        const int pos = atomicAdd(&s_cnt, 1);
+        if (pos < TOPK_CAND) s_cand[pos] = kk;
+      }
+    }
+  };
+#pragma unroll 4
+  for (int i = tid; i < n4; i += 256) {
+    const float4 v = r4[i];
+    push(v.x, 4 * i); push(v.y, 4 * i + 1); push(v.z, 4 * i + 2); push(v.w, 4 * i + 3);
+  }
+  for (int i = 4 * n4 + tid; i < n; i += 256) push(r[i], i);
   __syncthreads();
   const int c = s_cnt;
   int32_t* out_i = ids + (size_t)blockIdx.x * k;
   float* out_v = vals ? vals + (size_t)blockIdx.x * k : nullptr;
   if (c <= TOPK_CAND) {
-    for (int j = tid; j < c; j += 256) {
-      const unsigned long long key = s_cand[j];
+    for (int q = tid; q < c; q += 256) {
+      const unsigned long long kq = s_cand[q];
       int rank = 0;
-      for (int t = 0; t < c; ++t) rank += s_cand[t] > key ? 1 : 0;
+      for (int t = 0; t < c; ++t) rank += s_cand[t] > kq ? 1 : 0;
       if (rank < k) {
-        out_i[rank] = (int)(key & 0xffffffffull);
-        if (out_v) out_v[rank] = rank_key_score(key);
+        out_i[rank] = (int)(kq & 0xffffffffull);
+        if (out_v) out_v[rank] = rank_key_score(kq);
       }
     }
     return;
   }
-  unsigned long long prev = ~0ull;   // pathological rows: k selection rounds over keys >= thr
+  unsigned long long prev = ~0ull;   // pathological rows: k selection rounds
   for (int round = 0; round < k; ++round) {
     unsigned long long bk = 0ull;
     for (int i = tid; i < n; i += 256) {
-      const unsigned long long key = rank_key(r[i], cid ? cid[i] : i);
-      if (key < prev && key > bk) bk = key;
+      const unsigned long long kk = rank_key(r[i], cid ? cid[i] : i);
+      if (kk < prev && kk > bk) bk = kk;
     }
     bk = block_max_u64(bk, s_red);
     if (tid == 0) {
@@ -174,12 +218,6 @@ sort_rows_kernel(const float* __restrict__ sim, int n, int n_pad, int64_t ld,
 // ---------------------------------------------------------------------------------------
 // Ranking metrics, one CTA (1024 threads) per query row, everything in shared memory.
 // ---------------------------------------------------------------------------------------
-__device__ __forceinline__ unsigned int orderable_u32(float f) {
-  f += 0.f;
-  const unsigned int u = __float_as_uint(f);
-  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
-}
-
 // in-place bitonic sort of n_pad (power of two) 64-bit keys; DESC selects the direction
 template <bool DESC>
 __device__ __forceinline__ void block_bitonic_u64(unsigned long long* s_keys, int n_pad) {

@@ -32,13 +32,16 @@ cudaError_t sgnn_tc_launch(const ModelDev& M, const TcGeom& G, bool relu, bool r
                            float* sim, int64_t ld, cudaStream_t st) {
   __nv_bfloat16* A = static_cast<__nv_bfloat16*>(A_ws);
   __nv_bfloat16* B = static_cast<__nv_bfloat16*>(B_ws);
-  const int dk16 = G.KCH * 8;
-  if (dk16 > 128) return cudaErrorInvalidValue;
-  const int qpb = 128 / dk16;
-  const int q_blocks = (G.m + qpb - 1) / qpb;
-  const int db_blocks = (G.n_gtiles * 128 * G.KCH + 127) / 128;
-  tc_prep_kernel<<<q_blocks + db_blocks, 128, 0, st>>>(M, G, q_blocks, params, emb_q, emb_db, A, B);
-  cudaError_t e = cudaGetLastError();
+  const int C = G.KCH * 8 * G.KC;
+  const int col_blocks = (C + (PREP_COLS / G.KC) * G.KC - 1) / ((PREP_COLS / G.KC) * G.KC);
+  const int q_blocks = col_blocks * ((G.m + PREP_Q - 1) / PREP_Q);
+  const int db_blocks = (G.n_gtiles * 128 * G.KCH + PREP_COLS - 1) / PREP_COLS;
+  const size_t prep_smem = ((size_t)(G.D + 1) * PREP_COLS + (size_t)G.D * PREP_Q) * sizeof(float);
+  cudaError_t e = cudaFuncSetAttribute(tc_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)prep_smem);
+  if (e != cudaSuccess) return e;
+  tc_prep_kernel<<<q_blocks + db_blocks, PREP_COLS, prep_smem, st>>>(M, G, q_blocks, col_blocks, params, emb_q, emb_db,
+                                                                      A, B);
+  e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   if (G.K == 10) return dispatch<10>(relu, ref, simk, M, G, grid, smem, params, A, B, sim, ld, st);
   if (G.K == 16) return dispatch<16>(relu, ref, simk, M, G, grid, smem, params, A, B, sim, ld, st);

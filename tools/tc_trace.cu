@@ -32,8 +32,14 @@ int main(int argc, char** argv) {
   cudaMalloc(&A, na * 2); cudaMalloc(&B, nb * 2); cudaMemset(A, 0, na * 2); cudaMemset(B, 0, nb * 2);
   const int ntr = 64 * 8;
   cudaMalloc(&trace, ntr * 8); cudaMemset(trace, 0, ntr * 8);
-  const int qpb = 128 / (G.KCH * 8), q_blocks = (m + qpb - 1) / qpb, db_blocks = (G.n_gtiles * 128 * G.KCH + 127) / 128;
-  tc_prep_kernel<<<q_blocks + db_blocks, 128>>>(M, G, q_blocks, params, eq, ed, A, B);
+  {
+    const int C = G.KCH * 8 * G.KC, col_blocks = (C + (PREP_COLS / G.KC) * G.KC - 1) / ((PREP_COLS / G.KC) * G.KC);
+    const int q_blocks = col_blocks * ((m + PREP_Q - 1) / PREP_Q);
+    const int db_blocks = (G.n_gtiles * 128 * G.KCH + PREP_COLS - 1) / PREP_COLS;
+    const size_t ps = ((size_t)(G.D + 1) * PREP_COLS + (size_t)G.D * PREP_Q) * sizeof(float);
+    cudaFuncSetAttribute(tc_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ps);
+    tc_prep_kernel<<<q_blocks + db_blocks, PREP_COLS, ps>>>(M, G, q_blocks, col_blocks, params, eq, ed, A, B);
+  }
   G.stages = std::min(G.qb_per_group, TC_MAX_STAGES);
   size_t smem = (size_t)TC_GA_MAX * tc_a_bytes(G) + (size_t)G.stages * tc_b_bytes(G) + TC_TAIL_BYTES + 1024;
   smem = std::max<size_t>(smem, 120 * 1024);

@@ -20,6 +20,8 @@ struct HostWs {  // device staging for the *_host entry points (sized by sgnn_re
   int32_t *node_off[2] = {nullptr, nullptr}, *labels[2] = {nullptr, nullptr};
   int32_t *rowptr[2] = {nullptr, nullptr}, *col[2] = {nullptr, nullptr};
   float* val[2] = {nullptr, nullptr};
+  uint8_t* arena[2] = {nullptr, nullptr};   // one-copy upload target for batches whose host arrays are contiguous
+  int64_t arena_cap = 0;
   int32_t *g1 = nullptr, *g2 = nullptr;
   float *target = nullptr, *raw = nullptr, *sim_pairs = nullptr, *emb = nullptr;
   float *emb_q = nullptr, *emb_db = nullptr, *sim = nullptr, *topk_vals = nullptr;
@@ -46,6 +48,8 @@ struct SgnnHandle_t {
   int64_t cap_Atc = 0, cap_Btc = 0;                   // in elements
   int dep = 16;                           // padded embedding width of the all-pairs scorer
   cudaStream_t stream = nullptr;          // used by *_host entry points
+  cudaStream_t copy_stream = nullptr;     // host -> device uploads that overlap compute (sgnn_rank_host)
+  cudaEvent_t chunk_ev[8] = {};
   HostWs ws;
   // launch geometry decided at create
   int embed_wpb[2] = {8, 8}, train_wpb[2] = {4, 4};
@@ -308,8 +312,11 @@ int sgnn_create(const SgnnConfig* cfg, SgnnHandle* out) {
   cudaMemset(h->d_m, 0, np * sizeof(float));
   cudaMemset(h->d_v, 0, np * sizeof(float));
   cudaMemset(h->d_loss, 0, 4 * sizeof(float));
-  if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess)
+  if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking) != cudaSuccess)
     return bail("cudaStreamCreate");
+  for (auto& ev : h->chunk_ev)
+    if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) return bail("cudaEventCreate");
   h->dep = h->M.emb_dim <= 16 ? 16 : (h->M.emb_dim <= 32 ? 32 : 64);
   if (plan_launches(h)) return bail("planning launches");
   *out = h;
@@ -325,10 +332,13 @@ int sgnn_destroy(SgnnHandle h) {
   HostWs& w = h->ws;
   for (int s = 0; s < 2; ++s) {
     cudaFree(w.node_off[s]); cudaFree(w.labels[s]); cudaFree(w.rowptr[s]); cudaFree(w.col[s]); cudaFree(w.val[s]);
+    cudaFree(w.arena[s]);
   }
   cudaFree(w.g1); cudaFree(w.g2); cudaFree(w.target); cudaFree(w.raw); cudaFree(w.sim_pairs); cudaFree(w.emb);
   cudaFree(w.emb_q); cudaFree(w.emb_db); cudaFree(w.sim); cudaFree(w.topk_vals); cudaFree(w.topk_ids);
   if (h->stream) cudaStreamDestroy(h->stream);
+  if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+  for (auto& ev : h->chunk_ev) if (ev) cudaEventDestroy(ev);
   delete h;
   return 0;
 }
@@ -400,10 +410,11 @@ int sgnn_reserve(SgnnHandle h, int64_t max_graphs, int64_t max_nodes, int64_t ma
     w.cap_graphs = std::max(w.cap_graphs, max_graphs);
     w.cap_nodes = std::max(w.cap_nodes, max_nodes);
     w.cap_nnz = std::max(w.cap_nnz, max_nnz);
+    w.arena_cap = 4 * (w.cap_graphs + 1 + w.cap_nodes + w.cap_nodes + 1 + 2 * w.cap_nnz) + 5 * 256;
     for (int s = 0; s < 2; ++s) {
       if (dev_alloc(h, &w.node_off[s], w.cap_graphs + 1) || dev_alloc(h, &w.labels[s], w.cap_nodes) ||
           dev_alloc(h, &w.rowptr[s], w.cap_nodes + 1) || dev_alloc(h, &w.col[s], w.cap_nnz) ||
-          dev_alloc(h, &w.val[s], w.cap_nnz))
+          dev_alloc(h, &w.val[s], w.cap_nnz) || dev_alloc(h, &w.arena[s], w.arena_cap))
         return 1;
     }
     if (dev_alloc(h, &w.emb, w.cap_graphs * E) || dev_alloc(h, &w.emb_q, w.cap_graphs * E) ||
@@ -662,20 +673,49 @@ int sgnn_kendall_tau(SgnnHandle h, const float* true_sim_dev, const float* pred_
 }
 
 // ---- host-buffer entry points ---------------------------------------------------------
-static int upload_batch(SgnnHandle h, const SgnnGraphBatch* b, int slot, SgnnGraphBatch* dev) {
+// Host batch -> device.  Every cudaMemcpyAsync costs the calling thread several microseconds, which at
+// this problem size is comparable to the kernels, so when the caller's five arrays lie back to back in
+// ONE host allocation (PackedBatch.pin() lays them out that way, 16-byte aligned) the whole span goes
+// up as a single copy into an arena with the same relative layout; otherwise five copies.
+static int upload_batch_on(SgnnHandle h, const SgnnGraphBatch* b, int slot, SgnnGraphBatch* dev, cudaStream_t st) {
   HostWs& w = h->ws;
   if (b->n_graphs > w.cap_graphs || b->total_nodes > w.cap_nodes || b->nnz > w.cap_nnz)
     return fail(h, "host workspace too small: call sgnn_reserve first");
-  cudaStream_t st = h->stream;
-  CUDA_OK(h, cudaMemcpyAsync(w.node_off[slot], b->node_off, (size_t)(b->n_graphs + 1) * 4, cudaMemcpyHostToDevice, st));
-  CUDA_OK(h, cudaMemcpyAsync(w.labels[slot], b->labels, (size_t)b->total_nodes * 4, cudaMemcpyHostToDevice, st));
-  CUDA_OK(h, cudaMemcpyAsync(w.rowptr[slot], b->rowptr, (size_t)(b->total_nodes + 1) * 4, cudaMemcpyHostToDevice, st));
-  CUDA_OK(h, cudaMemcpyAsync(w.col[slot], b->col, (size_t)b->nnz * 4, cudaMemcpyHostToDevice, st));
-  CUDA_OK(h, cudaMemcpyAsync(w.val[slot], b->val, (size_t)b->nnz * 4, cudaMemcpyHostToDevice, st));
   *dev = *b;
+  const uint8_t* p[5] = {(const uint8_t*)b->node_off, (const uint8_t*)b->labels, (const uint8_t*)b->rowptr,
+                         (const uint8_t*)b->col, (const uint8_t*)b->val};
+  const size_t sz[5] = {(size_t)(b->n_graphs + 1) * 4, (size_t)b->total_nodes * 4, (size_t)(b->total_nodes + 1) * 4,
+                        (size_t)b->nnz * 4, (size_t)b->nnz * 4};
+  const uint8_t* lo = p[0];
+  const uint8_t* hi = p[0] + sz[0];
+  size_t total = 0;
+  for (int i = 0; i < 5; ++i) {
+    lo = p[i] < lo ? p[i] : lo;
+    hi = p[i] + sz[i] > hi ? p[i] + sz[i] : hi;
+    total += sz[i];
+  }
+  const size_t span = (size_t)(hi - lo);
+  if (span <= total + 5 * 64 && (int64_t)span <= w.arena_cap && ((uintptr_t)lo & 15) == 0) {
+    CUDA_OK(h, cudaMemcpyAsync(w.arena[slot], lo, span, cudaMemcpyHostToDevice, st));
+    dev->node_off = (const int32_t*)(w.arena[slot] + (p[0] - lo));
+    dev->labels = (const int32_t*)(w.arena[slot] + (p[1] - lo));
+    dev->rowptr = (const int32_t*)(w.arena[slot] + (p[2] - lo));
+    dev->col = (const int32_t*)(w.arena[slot] + (p[3] - lo));
+    dev->val = (const float*)(w.arena[slot] + (p[4] - lo));
+    return 0;
+  }
+  CUDA_OK(h, cudaMemcpyAsync(w.node_off[slot], b->node_off, sz[0], cudaMemcpyHostToDevice, st));
+  CUDA_OK(h, cudaMemcpyAsync(w.labels[slot], b->labels, sz[1], cudaMemcpyHostToDevice, st));
+  CUDA_OK(h, cudaMemcpyAsync(w.rowptr[slot], b->rowptr, sz[2], cudaMemcpyHostToDevice, st));
+  CUDA_OK(h, cudaMemcpyAsync(w.col[slot], b->col, sz[3], cudaMemcpyHostToDevice, st));
+  CUDA_OK(h, cudaMemcpyAsync(w.val[slot], b->val, sz[4], cudaMemcpyHostToDevice, st));
   dev->node_off = w.node_off[slot]; dev->labels = w.labels[slot]; dev->rowptr = w.rowptr[slot];
   dev->col = w.col[slot]; dev->val = w.val[slot];
   return 0;
+}
+
+static int upload_batch(SgnnHandle h, const SgnnGraphBatch* b, int slot, SgnnGraphBatch* dev) {
+  return upload_batch_on(h, b, slot, dev, h->stream);
 }
 
 int sgnn_forward_pairs_host(SgnnHandle h, const SgnnGraphBatch* b, const int32_t* g1, const int32_t* g2,
@@ -704,10 +744,16 @@ int sgnn_rank_host(SgnnHandle h, const SgnnGraphBatch* q, const SgnnGraphBatch* 
   const int64_t m = q->n_graphs, n = db->n_graphs;
   if (m * n > w.cap_q * w.cap_db || m > w.cap_q || (int64_t)m * k > w.cap_topk)
     return fail(h, "host workspace too small: call sgnn_reserve first");
+  cudaStream_t st = h->stream, cs = h->copy_stream;
+  // the database upload (8 bytes per non-zero over PCIe) runs on the copy stream while the compute
+  // stream uploads and embeds the queries
   SgnnGraphBatch dq, ddb;
-  if (upload_batch(h, q, 0, &dq) || upload_batch(h, db, 1, &ddb)) return 1;
-  cudaStream_t st = h->stream;
-  if (sgnn_embed_graphs(h, &dq, w.emb_q, st) || sgnn_embed_graphs(h, &ddb, w.emb_db, st)) return 1;
+  if (upload_batch_on(h, db, 1, &ddb, cs)) return 1;
+  CUDA_OK(h, cudaEventRecord(h->chunk_ev[0], cs));
+  if (upload_batch_on(h, q, 0, &dq, st)) return 1;
+  if (sgnn_embed_graphs(h, &dq, w.emb_q, st)) return 1;
+  CUDA_OK(h, cudaStreamWaitEvent(st, h->chunk_ev[0], 0));
+  if (sgnn_embed_graphs(h, &ddb, w.emb_db, st)) return 1;
   if (sgnn_score_all_pairs(h, w.emb_q, (int)m, w.emb_db, (int)n, w.sim, n, st)) return 1;
   if (k > 0 && topk_ids_host) {
     if (sgnn_topk(h, w.sim, (int)m, (int)n, n, k, w.topk_ids, w.topk_vals, st)) return 1;

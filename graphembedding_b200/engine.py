@@ -239,7 +239,7 @@ class SgnnEngine(object):
         sq, sd = queries.struct(), db.struct()
         check(self.h, lib().sgnn_rank_host(self.h, C.byref(sq), C.byref(sd), k, _ptr(ids), _ptr(vals),
                                            _ptr(sim)))
-        self.launches += 5
+        self.launches += 5   # embed(queries) + embed(database) + operand prep + scorer + top-k
         return ids, vals
 
     def train_step_host(self, batch, g1, g2, target_sim, loss=None):

@@ -166,9 +166,23 @@ class PackedBatch(object):
                            max_nodes=self.max_nodes)
 
     def pin(self):
+        """Pinned host copy whose five arrays lie back to back (16-byte aligned) in ONE allocation, so
+        the *_host entry points can upload the batch with a single copy."""
         import torch
-        return PackedBatch(*[torch.as_tensor(getattr(self, f)).pin_memory() for f in self.FIELDS],
-                           max_nodes=self.max_nodes)
+        arrs = [np.ascontiguousarray(np.asarray(getattr(self, f))) for f in self.FIELDS]
+        offs, total = [], 0
+        for a in arrs:
+            offs.append(total)
+            total += (a.nbytes + 15) // 16 * 16
+        arena = torch.empty(max(total, 16), dtype=torch.uint8).pin_memory()
+        out = []
+        for a, o in zip(arrs, offs):
+            t = arena[o:o + a.nbytes].view(torch.float32 if a.dtype == np.float32 else torch.int32)
+            t.copy_(torch.as_tensor(a))
+            out.append(t)
+        pb = PackedBatch(*out, max_nodes=self.max_nodes)
+        pb._arena = arena
+        return pb
 
     def nbytes(self):
         return 4 * (self.n_graphs + 1 + self.total_nodes + self.total_nodes + 1 + 2 * self.nnz)

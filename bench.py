@@ -418,7 +418,9 @@ def main():
     ap.add_argument('--steps', type=int, default=20)
     ap.add_argument('--warmup', type=int, default=5)
     ap.add_argument('--impl', default='cuda', choices=['cuda', 'reference'])
-    ap.add_argument('--precision', default='fp32', choices=['fp32', 'bf16x3', 'bf16'])
+    ap.add_argument('--precision', default='bf16x3', choices=['fp32', 'bf16x3', 'bf16'],
+                    help='all-pairs scorer: bf16x3 = tcgen05 with split-bf16 operands and fp32 accumulation (fp32-grade, '
+                         'gated at 2e-4 rel against the fp32 CUDA-core scorer), fp32 = CUDA-core parity mode')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)

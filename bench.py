@@ -359,6 +359,9 @@ def run_cuda(args):
 
     train = run_train(torch, dist, dev, rank, world, local, args, barrier, max_over_ranks)
 
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
     if rank != 0:
         return
     line = {'metric': 'graph-pairs/sec (all-pairs ranking inference)', 'value': value, 'unit': 'pairs/s',

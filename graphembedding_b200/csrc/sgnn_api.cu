@@ -473,7 +473,7 @@ int sgnn_embed_graphs(SgnnHandle h, const SgnnGraphBatch* b, float* emb_dev, voi
     if (b->total_nodes > h->cap_rows)
       return fail(h, "node-row workspace too small for graphs with more than 32 nodes: call sgnn_reserve(max_nodes >= total_nodes) first");
     const cudaError_t e = sgnn_launch_embed_large(h->M, to_dev(b), h->d_params, h->d_rowsA, h->d_rowsB, emb_dev,
-                                                  h->sm_count, h->smem_optin, st);
+                                                  nullptr, h->sm_count, h->smem_optin, st);
     if (e != cudaSuccess) return fail(h, std::string("sgnn_embed_graphs (large-graph path): ") + cudaGetErrorString(e));
     return 0;
   }
@@ -492,6 +492,31 @@ int sgnn_embed_graphs(SgnnHandle h, const SgnnGraphBatch* b, float* emb_dev, voi
   else
     embed_kernel<32><<<blocks, wpb * 32, h->embed_smem[1], st>>>(h->M, to_dev(b), h->d_params, emb_dev);
   CUDA_OK(h, cudaGetLastError());
+  return 0;
+}
+
+int sgnn_node_dim(SgnnHandle h) { return h ? h->M.node_dim : -1; }
+
+int sgnn_node_embeddings(SgnnHandle h, const SgnnGraphBatch* b, float* node_out_dev, void* stream) {
+  if (!h || !b || !node_out_dev) return fail(h, "sgnn_node_embeddings: null argument");
+  if (b->n_graphs == 0) return 0;
+  if (b->total_nodes > h->cap_rows)
+    return fail(h, "node-row workspace too small: call sgnn_reserve(max_nodes >= total_nodes) first");
+  const cudaError_t e = sgnn_launch_embed_large(h->M, to_dev(b), h->d_params, h->d_rowsA, h->d_rowsB, nullptr,
+                                                node_out_dev, h->sm_count, h->smem_optin, (cudaStream_t)stream);
+  if (e != cudaSuccess) return fail(h, std::string("sgnn_node_embeddings: ") + cudaGetErrorString(e));
+  return 0;
+}
+
+int sgnn_pair_histogram(SgnnHandle h, const float* node_emb_dev, const int32_t* node_off_dev, const int32_t* g1_dev,
+                        const int32_t* g2_dev, int32_t n_pairs, int32_t bins, float* hist_dev, int32_t* counts_dev,
+                        void* stream) {
+  if (!h || !node_emb_dev || !node_off_dev || !g1_dev || !g2_dev) return fail(h, "sgnn_pair_histogram: null argument");
+  if (bins < 1 || bins > 32) return fail(h, "sgnn_pair_histogram: bins must be in [1, 32]");
+  if (n_pairs == 0) return 0;
+  const cudaError_t e = sgnn_launch_pair_histogram(node_emb_dev, h->M.node_dim, node_off_dev, g1_dev, g2_dev, n_pairs,
+                                                   bins, hist_dev, counts_dev, h->sm_count, (cudaStream_t)stream);
+  if (e != cudaSuccess) return fail(h, std::string("sgnn_pair_histogram: ") + cudaGetErrorString(e));
   return 0;
 }
 

@@ -22,5 +22,10 @@ cudaError_t sgnn_launch_embed_tile(const ModelDev& M, const BatchDev& B, int max
 
 // CTA-per-graph embedding for graphs of any size; bufA / bufB: total_nodes x sgnn_large_row_stride floats each
 int sgnn_large_row_stride(const ModelDev& M);
+// emb may be NULL (node rows only); node_out may be NULL
 cudaError_t sgnn_launch_embed_large(const ModelDev& M, const BatchDev& B, const float* params, float* bufA,
-                                    float* bufB, float* emb, int sm_count, int smem_optin, cudaStream_t st);
+                                    float* bufB, float* emb, float* node_out, int sm_count, int smem_optin,
+                                    cudaStream_t st);
+cudaError_t sgnn_launch_pair_histogram(const float* node_emb, int d, const int32_t* node_off, const int32_t* g1,
+                                       const int32_t* g2, int n_pairs, int bins, float* hist, int32_t* counts,
+                                       int sm_count, cudaStream_t st);

@@ -53,7 +53,8 @@ __device__ __noinline__ void large_layer_phase(const LayerDev& L, int phase, con
 __global__ void __launch_bounds__(LARGE_THREADS)
 embed_large_kernel(const __grid_constant__ ModelDev M, const __grid_constant__ EmbPlan P, const BatchDev B,
                    const int32_t* __restrict__ which, int n_which, const float* __restrict__ params,
-                   float* __restrict__ bufA, float* __restrict__ bufB, float* __restrict__ emb) {
+                   float* __restrict__ bufA, float* __restrict__ bufB, float* __restrict__ emb,
+                   float* __restrict__ node_out) {
   extern __shared__ __align__(16) float smem[];
   float* s_w = smem;
   float* s_red = smem + P.w_floats;          // [2 * d + 8 warps * d] pooling scratch, also raw staging
@@ -81,6 +82,13 @@ embed_large_kernel(const __grid_constant__ ModelDev M, const __grid_constant__ E
       }
     }
     const float* H = cur;
+    if (node_out) {   // node-level output of the last node layer, [total_nodes][node_dim] (histogram feature)
+      for (int idx = threadIdx.x; idx < n * d; idx += blockDim.x) {
+        const int i = idx / d, c = idx - i * d;
+        node_out[(size_t)(base + i) * d + c] = H[(size_t)i * ldh + c];
+      }
+    }
+    if (!emb) { __syncthreads(); continue; }
     float* out = emb + (size_t)g * E;
     if (M.pool_kind == SGNN_LAYER_PADDING) {
       for (int idx = threadIdx.x; idx < E; idx += blockDim.x) {
@@ -124,6 +132,51 @@ embed_large_kernel(const __grid_constant__ ModelDev M, const __grid_constant__ E
           __syncthreads();
         }
       }
+    }
+    __syncthreads();
+  }
+}
+
+// Pairwise node-node similarity histogram (SimGNN's histogram feature; ABSENT from the reference snapshot,
+// SURVEY F1 -- build-defined): for a pair (G1, G2) with node embeddings H1 [N1 x d], H2 [N2 x d],
+//   s_ij = sigmoid(H1_i . H2_j),  bin_ij = min(bins - 1, floor(s_ij * bins))   (fixed width over [0, 1],
+//   tf.histogram_fixed_width semantics),  hist[b] = #{bin_ij == b} / (N1 N2).
+// One CTA per pair; a warp scores 32 (i, j) cells at a time and counts them per bin with ballot + popc
+// (lane b accumulates bin b), so there are no shared-memory atomics.  bins <= 32.
+__global__ void __launch_bounds__(128)
+pair_histogram_kernel(const float* __restrict__ node_emb, int d, const int32_t* __restrict__ node_off,
+                      const int32_t* __restrict__ g1, const int32_t* __restrict__ g2, int n_pairs, int bins,
+                      float* __restrict__ hist, int32_t* __restrict__ counts) {
+  __shared__ int s_cnt[4][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int p = blockIdx.x; p < n_pairs; p += gridDim.x) {
+    const int a0 = node_off[g1[p]], n1 = node_off[g1[p] + 1] - a0;
+    const int b0 = node_off[g2[p]], n2 = node_off[g2[p] + 1] - b0;
+    const int cells = n1 * n2;
+    int mine = 0;   // lane b: cells of this warp that fell into bin b
+    for (int c0 = warp * 32; c0 < cells; c0 += 128) {
+      const int c = c0 + lane;
+      int bin = -1;
+      if (c < cells) {
+        const int i = c / n2, j = c - i * n2;
+        const float* x = node_emb + (size_t)(a0 + i) * d;
+        const float* y = node_emb + (size_t)(b0 + j) * d;
+        float s = 0.f;
+        for (int k = 0; k < d; ++k) s = fmaf(x[k], y[k], s);
+        s = 1.f / (1.f + expf(-s));
+        bin = min(bins - 1, (int)floorf(s * (float)bins));
+      }
+      for (int b = 0; b < bins; ++b) {
+        const unsigned m = __ballot_sync(0xffffffffu, bin == b);
+        if (lane == b) mine += __popc(m);
+      }
+    }
+    s_cnt[warp][lane] = mine;
+    __syncthreads();
+    if (threadIdx.x < bins) {
+      const int tot = s_cnt[0][lane] + s_cnt[1][lane] + s_cnt[2][lane] + s_cnt[3][lane];
+      if (counts) counts[(size_t)p * bins + lane] = tot;
+      if (hist) hist[(size_t)p * bins + lane] = cells > 0 ? (float)tot / (float)cells : 0.f;
     }
     __syncthreads();
   }

@@ -53,12 +53,13 @@ def gather_topk_candidates(local_vals, local_ids, id_offset, dist=None, group=No
     if world == 1:
         return local_vals, ids
     m, k = local_vals.shape
-    gv = torch.empty((world * m, k), dtype=local_vals.dtype, device=local_vals.device)   # rank-major concat
-    gi = torch.empty((world * m, k), dtype=ids.dtype, device=ids.device)
-    dist.all_gather_into_tensor(gv, local_vals.contiguous(), group=group)
-    dist.all_gather_into_tensor(gi, ids.contiguous(), group=group)
-    cv = gv.view(world, m, k).permute(1, 0, 2).reshape(m, world * k).contiguous()
-    ci = gi.view(world, m, k).permute(1, 0, 2).reshape(m, world * k).contiguous()
+    # ONE collective: scores (bit pattern) and ids travel together as int32 [2, m, k]
+    packed = torch.stack([local_vals.contiguous().view(torch.int32), ids.to(torch.int32)], dim=0)
+    got = torch.empty((world * 2 * m, k), dtype=torch.int32, device=packed.device)   # rank-major concat
+    dist.all_gather_into_tensor(got, packed.view(2 * m, k), group=group)
+    got = got.view(world, 2, m, k)
+    cv = got[:, 0].permute(1, 0, 2).reshape(m, world * k).contiguous().view(local_vals.dtype)
+    ci = got[:, 1].permute(1, 0, 2).reshape(m, world * k).contiguous()
     return cv, ci
 
 

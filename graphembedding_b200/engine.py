@@ -93,6 +93,27 @@ class SgnnEngine(object):
         self.launches += 1
         return out
 
+    def node_embeddings(self, batch, stream=None):
+        """Last node-layer output of every node, [total_nodes, node_dim] (needs reserve(max_nodes))."""
+        import torch
+        d = int(lib().sgnn_node_dim(self.h))
+        out = torch.empty((batch.total_nodes, d), dtype=torch.float32, device=self.device)
+        s = batch.struct()
+        check(self.h, lib().sgnn_node_embeddings(self.h, C.byref(s), _ptr(out), _stream_ptr(stream)))
+        self.launches += 1
+        return out
+
+    def pair_histogram(self, node_emb, node_off, g1, g2, bins=16, stream=None):
+        """SimGNN node-node similarity histogram per pair -> (hist [P, bins] float32, counts int32)."""
+        import torch
+        n = int(g1.numel())
+        hist = torch.empty((n, bins), dtype=torch.float32, device=self.device)
+        counts = torch.empty((n, bins), dtype=torch.int32, device=self.device)
+        check(self.h, lib().sgnn_pair_histogram(self.h, _ptr(node_emb), _ptr(node_off), _ptr(g1), _ptr(g2), n,
+                                                int(bins), _ptr(hist), _ptr(counts), _stream_ptr(stream)))
+        self.launches += 1
+        return hist, counts
+
     def score_pairs(self, emb, g1, g2, stream=None):
         import torch
         n = int(g1.numel())

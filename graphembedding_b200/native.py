@@ -66,6 +66,9 @@ SIGNATURES = {
     'sgnn_device_buffers': (C.c_int, [_P, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P), C.POINTER(_P)]),
     'sgnn_reserve': (C.c_int, [_P, _I64, _I64, _I64, _I64, _I64, _I64]),
     'sgnn_embed_graphs': (C.c_int, [_P, _BP, _P, _P]),
+    'sgnn_node_dim': (C.c_int, [_P]),
+    'sgnn_node_embeddings': (C.c_int, [_P, _BP, _P, _P]),
+    'sgnn_pair_histogram': (C.c_int, [_P, _P, _P, _P, _P, _I32, _I32, _P, _P, _P]),
     'sgnn_score_pairs': (C.c_int, [_P, _P, _P, _P, _I32, _P, _P, _P]),
     'sgnn_forward_pairs': (C.c_int, [_P, _BP, _P, _P, _I32, _P, _P, _P, _P]),
     'sgnn_score_all_pairs': (C.c_int, [_P, _P, _I32, _P, _I32, _P, _I64, _P]),

@@ -140,6 +140,18 @@ int sgnn_reserve(SgnnHandle h, int64_t max_graphs, int64_t max_nodes, int64_t ma
 /* GCN/Dense/pooling stack of every graph in the batch -> emb[n_graphs][embed_dim]
  * (layers.py:91-118, 136-140, 154-160, 192-205, 223-227). */
 int sgnn_embed_graphs(SgnnHandle h, const SgnnGraphBatch* batch_dev, float* emb_dev, void* stream);
+/* Node-level output of the last GraphConvolution/Dense layer of every graph,
+ * node_out[total_nodes][sgnn_node_dim] (the input of the pooling layer, layers.py:136-160).  Needs the
+ * node-row workspace: sgnn_reserve(max_nodes >= total_nodes). */
+int sgnn_node_dim(SgnnHandle h);
+int sgnn_node_embeddings(SgnnHandle h, const SgnnGraphBatch* batch_dev, float* node_out_dev, void* stream);
+/* Pairwise node-node similarity histogram of SimGNN.  NOT in the reference snapshot (only TensorBoard
+ * summaries are called "histogram" there, models.py:116 / layers.py:43) -- build-defined:
+ *   s_ij = sigmoid(H1_i . H2_j); bin = min(bins-1, floor(s_ij * bins)); hist[b] = count_b / (N1 N2).
+ * hist_dev [n_pairs][bins] and counts_dev [n_pairs][bins] (either may be NULL); bins <= 32. */
+int sgnn_pair_histogram(SgnnHandle h, const float* node_emb_dev, const int32_t* node_off_dev, const int32_t* g1_dev,
+                        const int32_t* g2_dev, int32_t n_pairs, int32_t bins, float* hist_dev, int32_t* counts_dev,
+                        void* stream);
 /* NTN/Dot + final_act on listed pairs (layers.py:249-252, 282-310; model_mse.py:39-45).
  * raw_dev / sim_dev may be NULL. */
 int sgnn_score_pairs(SgnnHandle h, const float* emb_dev, const int32_t* g1_dev, const int32_t* g2_dev,

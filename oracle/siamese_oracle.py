@@ -310,6 +310,27 @@ class Graph(object):
         return a
 
 
+def node_forward(layers, P, g, input_dim, dtype=torch.float64):
+    """Output of the last GraphConvolution / Dense layer, [n, node_dim] (the pooling layer's input)."""
+    node_layers = []
+    for L in layers:
+        if L['kind'] not in ('GraphConvolution', 'Dense'):
+            break
+        node_layers.append(L)
+    return graph_forward(node_layers, P, g, input_dim, dtype).reshape(g.n, -1)
+
+
+def pair_histogram(h1, h2, bins):
+    """SimGNN's node-node similarity histogram.  NOT in the reference snapshot (only
+    TensorBoard summaries are called histogram there) -- build-defined, shared with the CUDA op:
+    s_ij = sigmoid(h1_i . h2_j), fixed-width bins over [0, 1] (tf.histogram_fixed_width clamps the
+    top edge into the last bin), normalised by N1 N2.  Returns (hist, counts, scores)."""
+    s = torch.sigmoid(h1 @ h2.T).reshape(-1).numpy().astype(np.float64)
+    idx = np.minimum(bins - 1, np.floor(s * bins).astype(np.int64))
+    counts = np.bincount(idx, minlength=bins).astype(np.int64)
+    return counts / float(max(1, s.size)), counts, s
+
+
 def graph_forward(layers, P, g, input_dim, dtype=torch.float64, drop=None, slot=0):
     """Node-level layers + pooling for one graph; returns the flattened
     representation the pair layer consumes (layers.py:91-118, 136-140,

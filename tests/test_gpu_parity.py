@@ -349,3 +349,44 @@ def test_web_shaped_large_graphs_match_oracle(cfg):
     raw, _ = eng.forward_pairs(batch.to(eng.device), g1, g2)
     ref_raw = O.forward_pairs(layers, P, og[:B], og[B:2 * B], enc.input_dim(), torch.float64).numpy()
     assert np.max(np.abs(raw.cpu().numpy() - ref_raw)) <= RTOL * max(1.0, np.max(np.abs(ref_raw))), cfg
+
+
+@pytest.mark.parametrize('n_lo,n_hi,bins', [(2, 10, 16), (20, 120, 8), (3, 30, 32)])
+def test_node_embeddings_and_pair_histogram_match_oracle(n_lo, n_hi, bins):
+    """SURVEY a24 (build-defined, absent from the reference snapshot): node-level outputs and the
+    SimGNN node-node similarity histogram.  Counts are integers: they must equal the fp64 oracle's
+    except for cells whose score lies within 1e-5 of a bin edge (fp32 vs fp64 rounding), which may
+    move to the neighbouring bin."""
+    from graphembedding_b200.graphs import pack_nx_graphs
+    from graphembedding_b200.engine import SgnnEngine
+    from graphembedding_b200.layers_factory import parse_layers
+    gs = corpus(24, n_lo, n_hi, seed=31)
+    enc = encoder_for(gs)
+    layers = parse_layers(CONFIGS['avg_ntn'], enc.input_dim())
+    eng = SgnnEngine(layers, enc.input_dim())
+    flat = O.init_params(O.parse_layer_specs(CONFIGS['avg_ntn'], enc.input_dim()), seed=5)
+    eng.set_params(flat)
+    batch = pack_nx_graphs(gs, enc)
+    eng.reserve(max_nodes=batch.total_nodes)
+    bd = batch.to(eng.device)
+    rows = eng.node_embeddings(bd)
+    P = O.unflatten(layers, flat, torch.float64)
+    og = oracle_graphs(gs, enc)
+    ref_rows = [O.node_forward(layers, P, g, enc.input_dim(), torch.float64) for g in og]
+    ref_cat = torch.cat(ref_rows, 0).numpy()
+    assert rows.shape == ref_cat.shape
+    assert np.max(np.abs(rows.cpu().numpy() - ref_cat)) <= RTOL * max(1.0, np.max(np.abs(ref_cat)))
+    B = len(gs) // 2
+    g1 = torch.arange(0, B, dtype=torch.int32, device=eng.device)
+    g2 = torch.arange(B, 2 * B, dtype=torch.int32, device=eng.device)
+    hist, counts = eng.pair_histogram(rows, bd.node_off, g1, g2, bins=bins)
+    hist, counts = hist.cpu().numpy(), counts.cpu().numpy()
+    for p in range(B):
+        rh, rc, s = O.pair_histogram(ref_rows[p], ref_rows[B + p], bins)
+        assert counts[p].sum() == s.size
+        edge = np.abs(s * bins - np.round(s * bins)) < 1e-5 * bins
+        if not edge.any():
+            assert np.array_equal(counts[p], rc), (p, counts[p], rc)
+        else:
+            assert np.abs(counts[p] - rc).sum() <= 2 * int(edge.sum())
+        assert np.max(np.abs(hist[p] - counts[p] / float(s.size))) < 1e-6

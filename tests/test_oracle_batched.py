@@ -48,3 +48,18 @@ def test_batched_train_step_equals_oracle():
     new, loss = OB.train_step(layers, flat, a1, lab, A, mask, n, g1, g2, tgt, dtype=torch.float64)
     l, _, _, g, _ = O.loss_and_grads(layers, flat, og[:10], og[10:], tgt, enc.input_dim())
     assert abs(l - loss) < 1e-12 and np.allclose(new, a2.step(flat, g), rtol=0, atol=1e-12)
+
+
+def test_pair_histogram_known_answers():
+    """Build-defined SimGNN histogram (a24): zero embeddings -> every score is sigmoid(0) = 0.5, large
+    positive dot products land in the LAST bin (top edge clamped), counts sum to N1 N2."""
+    import torch
+    from util import O
+    h1, h2 = torch.zeros((3, 4), dtype=torch.float64), torch.zeros((5, 4), dtype=torch.float64)
+    hist, counts, s = O.pair_histogram(h1, h2, 16)
+    assert counts[8] == 15 and counts.sum() == 15 and abs(hist.sum() - 1.0) < 1e-12
+    h1 = torch.full((2, 4), 10.0, dtype=torch.float64)
+    hist, counts, s = O.pair_histogram(h1, h1, 8)
+    assert counts[7] == 4 and (s <= 1.0).all()
+    hist, counts, s = O.pair_histogram(h1, -h1, 8)
+    assert counts[0] == 4

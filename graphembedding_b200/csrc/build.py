@@ -7,11 +7,13 @@ import sys
 from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB = os.path.join(HERE, 'libsgnn.so')
-OBJ = os.path.join(HERE, 'build')
+# SGNN_DEFINES="-DSGNN_TILE_TRACE" SGNN_LIB_SUFFIX=_trace builds an instrumented copy next to the product library
+SUFFIX = os.environ.get('SGNN_LIB_SUFFIX', '')
+LIB = os.path.join(HERE, 'libsgnn%s.so' % SUFFIX)
+OBJ = os.path.join(HERE, 'build' + SUFFIX)
 DEP_SUFFIX = ('.cuh', '.cu', '.cpp', '.h')
 FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
-         '--expt-relaxed-constexpr', '--extended-lambda', '-Xcompiler', '-fPIC']
+         '--expt-relaxed-constexpr', '--extended-lambda', '-Xcompiler', '-fPIC'] + os.environ.get('SGNN_DEFINES', '').split()
 
 
 def _deps():

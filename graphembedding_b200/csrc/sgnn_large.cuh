@@ -58,7 +58,9 @@ embed_large_kernel(const __grid_constant__ ModelDev M, const __grid_constant__ E
   extern __shared__ __align__(16) float smem[];
   float* s_w = smem;
   float* s_red = smem + P.w_floats;          // [2 * d + 8 warps * d] pooling scratch, also raw staging
-  tile_stage_weights(M, P, params, s_w, s_red);
+  tile_stage_weights_async(M, P, params, s_w);
+  tile_cp_async_wait_all();
+  __syncthreads();
   const int ldh = P.ldh, d = M.node_dim, E = M.emb_dim;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
   for (int gi = blockIdx.x; gi < n_which; gi += gridDim.x) {

@@ -8,16 +8,27 @@ cudaError_t sgnn_launch_embed_tile(const ModelDev& M, const BatchDev& B, int max
                                    float* emb, int sm_count, int smem_optin, cudaStream_t st) {
   if (max_nodes > 32) return cudaErrorInvalidValue;
   const EmbPlan P = make_emb_plan(M, max_nodes);
-  const size_t smem = ((size_t)P.w_floats + (size_t)TILE_WARPS * P.warp_floats) * sizeof(float);
-  if (smem > (size_t)smem_optin) return cudaErrorInvalidValue;
   const int n_tiles = (B.n_graphs + P.gpw - 1) / P.gpw;
-  const int per_sm = smem * 2 <= (size_t)smem_optin ? 2 : 1;
-  int blocks = (n_tiles + TILE_WARPS - 1) / TILE_WARPS;
+  // Warps (= tiles in flight) per CTA: as many as let two CTAs share an SM (1 KB per CTA is reserved),
+  // so that a batch of <= 2 x warps x SMs tiles finishes in one round with every tile resident at once.
+  const size_t sm_bytes = (size_t)smem_optin + 1024;
+  auto bytes_for = [&](int w) { return ((size_t)P.w_floats + (size_t)w * P.warp_floats) * sizeof(float); };
+  int warps = TILE_MAX_WARPS;
+  while (warps > 4 && 2 * (bytes_for(warps) + 1024) > sm_bytes) --warps;
+  if (bytes_for(warps) > (size_t)smem_optin) warps = 1;
+  const size_t smem = bytes_for(warps);
+  if (smem > (size_t)smem_optin) return cudaErrorInvalidValue;
+  const int per_sm = 2 * (smem + 1024) <= sm_bytes ? 2 : 1;
+  int blocks = (n_tiles + warps - 1) / warps;
   if (blocks > sm_count * per_sm) blocks = sm_count * per_sm;
-  if ((size_t)M.n_params > (size_t)TILE_WARPS * P.warp_floats) return cudaErrorInvalidValue;
-  cudaError_t e = cudaFuncSetAttribute(embed_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  else if (blocks < sm_count) {   // few tiles: spread them over all SMs with narrower CTAs
+    warps = (n_tiles + sm_count - 1) / sm_count;
+    blocks = (n_tiles + warps - 1) / warps;
+  }
+  cudaError_t e = cudaFuncSetAttribute(embed_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)bytes_for(warps));
   if (e != cudaSuccess) return e;
-  embed_tile_kernel<<<blocks, TILE_WARPS * 32, smem, st>>>(M, P, B, params, emb);
+  embed_tile_kernel<<<blocks, warps * 32, bytes_for(warps), st>>>(M, P, B, params, emb);
   return cudaGetLastError();
 }
 
@@ -35,7 +46,7 @@ cudaError_t sgnn_launch_embed_large(const ModelDev& M, const BatchDev& B, const 
                                     float* bufB, float* emb, float* node_out, int sm_count, int smem_optin,
                                     cudaStream_t st) {
   const EmbPlan P = make_emb_plan(M, 32);
-  const int scratch = std::max(M.n_params, (2 + LARGE_THREADS / 32) * M.node_dim);
+  const int scratch = (2 + LARGE_THREADS / 32) * M.node_dim;
   const size_t smem = ((size_t)P.w_floats + (size_t)round_up(scratch, 4)) * sizeof(float);
   if (smem > (size_t)smem_optin) return cudaErrorInvalidValue;
   cudaError_t e = cudaFuncSetAttribute(embed_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -45,3 +56,10 @@ cudaError_t sgnn_launch_embed_large(const ModelDev& M, const BatchDev& B, const 
                                                           node_out);
   return cudaGetLastError();
 }
+
+#ifdef SGNN_TILE_TRACE
+extern "C" int sgnn_debug_tile_trace(unsigned long long* out, int n) {
+  cudaDeviceSynchronize();
+  return (int)cudaMemcpyFromSymbol(out, g_tile_trace, sizeof(unsigned long long) * (size_t)n);
+}
+#endif

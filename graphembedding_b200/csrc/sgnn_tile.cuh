@@ -15,8 +15,24 @@
 #pragma once
 #include "sgnn_common.cuh"
 
-constexpr int TILE_CSR_CAP = 320;   // staged nnz per tile (falls back to global reads beyond)
-constexpr int TILE_WARPS = 8;
+// Build with -DSGNN_TILE_TRACE to stamp the phases of warp 0's first tile of every CTA (tools/tile_probe.py)
+#ifdef SGNN_TILE_TRACE
+__device__ unsigned long long g_tile_trace[1024 * 8];
+#define TILE_STAMP(i)                                                                   \
+  do {                                                                                  \
+    if (threadIdx.x == 0 && blockIdx.x < 1024) {                                        \
+      unsigned long long t_;                                                            \
+      if ((i) == 0 || (i) == 7) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));  \
+      else t_ = clock64();                                                              \
+      g_tile_trace[blockIdx.x * 8 + (i)] = t_;                                          \
+    }                                                                                   \
+  } while (0)
+#else
+#define TILE_STAMP(i)
+#endif
+
+constexpr int TILE_CSR_CAP = 160;   // staged nnz per tile (falls back to global reads beyond)
+constexpr int TILE_MAX_WARPS = 12;  // warps (= tiles in flight) per CTA; the launcher picks <= this
 
 struct EmbPlan {
   int w_s[SGNN_MAX_LAYERS];    // offset (floats) of layer l's padded weight matrix in shared memory
@@ -24,14 +40,15 @@ struct EmbPlan {
   int ldw[SGNN_MAX_LAYERS];    // padded row stride of the weight matrix
   int att_s;                   // attention weights [d][d] (row stride d), -1 if unused
   int w_floats;                // total staged floats (multiple of 4)
-  int ldh;                     // row stride of the per-warp activation buffers (ldh % 8 == 4)
+  int ldh;                     // row stride of activation buffer A (holds every layer's output; ldh % 8 == 4)
+  int ldb;                     // row stride of buffer B (outputs of layers l >= 1 only; ldb % 8 == 4)
   int gpw;                     // graphs per warp tile
   int warp_floats;             // per-warp shared memory (floats)
 };
 
 inline EmbPlan make_emb_plan(const ModelDev& M, int max_nodes) {
   EmbPlan P;
-  int o = 0, dmax = 4;
+  int o = 0, dmax = 4, dmax1 = 4;
   for (int l = 0; l < M.n_node; ++l) {
     const LayerDev& L = M.L[l];
     int ldw = round_up(L.dout, 4);
@@ -40,37 +57,53 @@ inline EmbPlan make_emb_plan(const ModelDev& M, int max_nodes) {
     P.ldw[l] = ldw; P.w_s[l] = o; o += rows * ldw;
     P.b_s[l] = o; o += round_up(L.dout, 4);
     dmax = dmax > L.dout ? dmax : L.dout;
+    if (l > 0) dmax1 = dmax1 > L.dout ? dmax1 : L.dout;
   }
   P.att_s = -1;
-  if (M.pool_kind == SGNN_LAYER_ATTENTION) { P.att_s = o; o += round_up(M.node_dim * M.node_dim, 4); }
+  if (M.pool_kind == SGNN_LAYER_ATTENTION) {
+    P.att_s = o; o += round_up(M.node_dim * M.node_dim, 4);
+    dmax1 = dmax1 > M.node_dim ? dmax1 : M.node_dim;   // pooling scratch lives in the idle buffer
+  }
   P.w_floats = round_up(o, 4);
   P.ldh = round_up(dmax, 4);
   if (P.ldh % 8 == 0) P.ldh += 4;
+  P.ldb = round_up(dmax1, 4);
+  if (P.ldb % 8 == 0) P.ldb += 4;
   int gpw = max_nodes > 0 ? 32 / max_nodes : 1;
   P.gpw = gpw < 1 ? 1 : (gpw > 16 ? 16 : gpw);
-  P.warp_floats = 2 * 32 * P.ldh + 2 * TILE_CSR_CAP + 32 + 32;
+  P.warp_floats = 32 * P.ldh + 32 * P.ldb + 2 * TILE_CSR_CAP + 32 + 32;
   return P;
 }
 
-// raw: a scratch area of >= n_params floats (the per-warp buffers, unused before the tile loop)
-__device__ __forceinline__ void tile_stage_weights(const ModelDev& M, const EmbPlan& P, const float* __restrict__ params,
-                                                   float* s_w, float* raw) {
-  for (int i = threadIdx.x; i < P.w_floats; i += blockDim.x) s_w[i] = 0.f;
-#pragma unroll 4
-  for (int i = threadIdx.x; i < M.n_params; i += blockDim.x) raw[i] = params[i];   // coalesced, loads in flight together
-  __syncthreads();
+__device__ __forceinline__ void tile_cp_async4(float* dst_smem, const float* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src)
+               : "memory");
+}
+__device__ __forceinline__ void tile_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void tile_cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// Weights of the node layers (+ attention) into the padded shared layout, asynchronously: the
+// caller overlaps the first tile's CSR loads with the copy and waits (cp.async wait + CTA barrier)
+// before the first layer.  Warp-per-row, lane-per-column: no index arithmetic beyond adds.
+__device__ __forceinline__ void tile_stage_weights_async(const ModelDev& M, const EmbPlan& P,
+                                                         const float* __restrict__ params, float* s_w) {
+  float4* z = reinterpret_cast<float4*>(s_w);
+  for (int i = threadIdx.x; i < P.w_floats / 4; i += blockDim.x) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  __syncthreads();   // the zero fill is ordered before the asynchronous element copies
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
   for (int l = 0; l < M.n_node; ++l) {
     const LayerDev& L = M.L[l];
-    for (int i = threadIdx.x; i < L.din * L.dout; i += blockDim.x) {
-      const int k = i / L.dout, j = i - k * L.dout;
-      s_w[P.w_s[l] + k * P.ldw[l] + j] = raw[L.w_off + i];
-    }
-    if (L.bias)
-      for (int j = threadIdx.x; j < L.dout; j += blockDim.x) s_w[P.b_s[l] + j] = raw[L.b_off + j];
+    const float* src = params + L.w_off;
+    float* dst = s_w + P.w_s[l];
+    for (int k = warp; k < L.din; k += nw)
+      for (int j = lane; j < L.dout; j += 32) tile_cp_async4(dst + k * P.ldw[l] + j, src + k * L.dout + j);
+    if (L.bias && warp == (l % nw))
+      for (int j = lane; j < L.dout; j += 32) tile_cp_async4(s_w + P.b_s[l] + j, params + L.b_off + j);
   }
   if (P.att_s >= 0)
-    for (int i = threadIdx.x; i < M.node_dim * M.node_dim; i += blockDim.x) s_w[P.att_s + i] = raw[M.pool_w_off + i];
-  __syncthreads();
+    for (int i = threadIdx.x; i < M.node_dim * M.node_dim; i += blockDim.x)
+      tile_cp_async4(s_w + P.att_s + i, params + M.pool_w_off + i);
+  tile_cp_async_commit();
 }
 
 struct TileCtx {
@@ -167,8 +200,8 @@ __device__ __forceinline__ void tile_row_gemm(const float* hrow, int din, const 
 // One node layer of one tile with JT accumulators per pass.  first: gather of W rows by label into
 // cur.  GCN: cur -> (gemm) oth -> (aggregate) cur.  Dense: cur -> oth (caller swaps).
 template <int JT>
-__device__ __noinline__ void tile_layer(const LayerDev& L, bool first, const TileCtx& T, const float* W, int ldw,
-                                        const float* b, float* cur, float* oth, int ldh, int lane) {
+__device__ __forceinline__ void tile_layer(const LayerDev& L, bool first, const TileCtx& T, const float* W, int ldw,
+                                        const float* b, float* cur, int ldc, float* oth, int ldo, int lane) {
   const bool gcn = L.kind == SGNN_LAYER_GCN;
   if (first) {
     if (T.on)
@@ -177,7 +210,7 @@ __device__ __noinline__ void tile_layer(const LayerDev& L, bool first, const Til
 #pragma unroll
         for (int jj = 0; jj < JT; ++jj) acc[jj] = 0.f;
         tile_gather<JT, true>(T, W, ldw, j0, L.dout, acc);
-        tile_store_row<JT>(cur + lane * ldh, acc, b, j0, L.dout, L.act);
+        tile_store_row<JT>(cur + lane * ldc, acc, b, j0, L.dout, L.act);
       }
     __syncwarp();
     return;
@@ -187,8 +220,8 @@ __device__ __noinline__ void tile_layer(const LayerDev& L, bool first, const Til
       float acc[JT];
 #pragma unroll
       for (int jj = 0; jj < JT; ++jj) acc[jj] = 0.f;
-      tile_row_gemm<JT>(cur + lane * ldh, round_up4(L.din), W, ldw, j0, L.dout, acc);
-      tile_store_row<JT>(oth + lane * ldh, acc, gcn ? nullptr : b, j0, L.dout, gcn ? (int)SGNN_ACT_IDENTITY : L.act);
+      tile_row_gemm<JT>(cur + lane * ldc, round_up4(L.din), W, ldw, j0, L.dout, acc);
+      tile_store_row<JT>(oth + lane * ldo, acc, gcn ? nullptr : b, j0, L.dout, gcn ? (int)SGNN_ACT_IDENTITY : L.act);
     }
   __syncwarp();
   if (!gcn) return;
@@ -197,77 +230,99 @@ __device__ __noinline__ void tile_layer(const LayerDev& L, bool first, const Til
       float acc[JT];
 #pragma unroll
       for (int jj = 0; jj < JT; ++jj) acc[jj] = 0.f;
-      tile_gather<JT, false>(T, oth, ldh, j0, L.dout, acc);
-      tile_store_row<JT>(cur + lane * ldh, acc, b, j0, L.dout, L.act);
+      tile_gather<JT, false>(T, oth, ldo, j0, L.dout, acc);
+      tile_store_row<JT>(cur + lane * ldc, acc, b, j0, L.dout, L.act);
     }
   __syncwarp();
 }
 
-// all node layers of one tile; returns the buffer holding the last layer's output rows
+// all node layers of one tile; returns the buffer holding the last layer's output rows (stride *ld_out).
+// Buffer A (stride ldh) can hold any layer's output; buffer B (stride ldb) only those of layers >= 1.
 __device__ __forceinline__ float* tile_node_layers(const ModelDev& M, const EmbPlan& P, const TileCtx& T,
-                                                   const float* s_w, float* bufA, float* bufB, int lane) {
+                                                   const float* s_w, float* bufA, float* bufB, int lane,
+                                                   int* ld_out) {
   float* cur = bufA;
   float* oth = bufB;
+  int ldc = P.ldh, ldo = P.ldb;
   for (int l = 0; l < M.n_node; ++l) {
     const LayerDev& L = M.L[l];
     const float* W = s_w + P.w_s[l];
     const float* b = L.bias ? s_w + P.b_s[l] : nullptr;
-    if (L.dout > 16) tile_layer<32>(L, l == 0, T, W, P.ldw[l], b, cur, oth, P.ldh, lane);
-    else if (L.dout > 4) tile_layer<16>(L, l == 0, T, W, P.ldw[l], b, cur, oth, P.ldh, lane);
-    else tile_layer<4>(L, l == 0, T, W, P.ldw[l], b, cur, oth, P.ldh, lane);
-    if (l > 0 && L.kind != SGNN_LAYER_GCN) { float* sw = cur; cur = oth; oth = sw; }
+    if (L.dout > 4) tile_layer<16>(L, l == 0, T, W, P.ldw[l], b, cur, ldc, oth, ldo, lane);
+    else tile_layer<4>(L, l == 0, T, W, P.ldw[l], b, cur, ldc, oth, ldo, lane);
+    if (l > 0 && L.kind != SGNN_LAYER_GCN) {
+      float* sw = cur; cur = oth; oth = sw;
+      const int t = ldc; ldc = ldo; ldo = t;
+    }
   }
+  *ld_out = ldc;
   return cur;
 }
 
-__global__ void __launch_bounds__(TILE_WARPS * 32)
+__global__ void __launch_bounds__(TILE_MAX_WARPS * 32, 2)
 embed_tile_kernel(const __grid_constant__ ModelDev M, const __grid_constant__ EmbPlan P, const BatchDev B,
                   const float* __restrict__ params, float* __restrict__ emb) {
   extern __shared__ __align__(16) float smem[];
   float* s_w = smem;
-  tile_stage_weights(M, P, params, s_w, smem + P.w_floats);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  TILE_STAMP(0);
+  TILE_STAMP(1);
+  tile_stage_weights_async(M, P, params, s_w);
+  TILE_STAMP(2);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
   float* my = smem + P.w_floats + warp * P.warp_floats;
   float* bufA = my;
   float* bufB = bufA + 32 * P.ldh;
-  int* s_col = reinterpret_cast<int*>(bufB + 32 * P.ldh);
+  int* s_col = reinterpret_cast<int*>(bufB + 32 * P.ldb);
   float* s_val = reinterpret_cast<float*>(s_col + TILE_CSR_CAP);
   int* s_lab = reinterpret_cast<int*>(s_val + TILE_CSR_CAP);
   float* s_att = reinterpret_cast<float*>(s_lab + 32);
   const int gpw = P.gpw;
   const int n_tiles = (B.n_graphs + gpw - 1) / gpw;
   const int E = M.emb_dim, d = M.node_dim;
-  for (int t = blockIdx.x * TILE_WARPS + warp; t < n_tiles; t += gridDim.x * TILE_WARPS) {
-    const int g0 = t * gpw, g1 = min(B.n_graphs, g0 + gpw);
-    // lanes 0..gpw hold the node offsets of the tile's graphs
-    const int my_no = B.node_off[min(g0 + lane, g1)];
-    const int base = __shfl_sync(0xffffffffu, my_no, 0);
-    const int n_rows = __shfl_sync(0xffffffffu, my_no, g1 - g0) - base;
+  bool w_ready = false;
+  for (int t = blockIdx.x * nw + warp; ; t += gridDim.x * nw) {
+    const bool live = t < n_tiles;     // warps without a tile still take part in the one CTA barrier below
     TileCtx T;
-    T.n_rows = n_rows; T.on = lane < n_rows;
-    int gi = 0;   // my graph inside the tile
-    T.g_off = 0;
-    for (int k = 1; k <= g1 - g0; ++k) {
-      const int off = __shfl_sync(0xffffffffu, my_no, k) - base;
-      if (k < g1 - g0 && lane >= off) { gi = k; T.g_off = off; }
+    int my_no = 0, base = 0, g0 = 0, g1 = 0, gi = 0;
+    if (live) {
+      g0 = t * gpw; g1 = min(B.n_graphs, g0 + gpw);
+      // lanes 0..gpw hold the node offsets of the tile's graphs
+      my_no = B.node_off[min(g0 + lane, g1)];
+      base = __shfl_sync(0xffffffffu, my_no, 0);
+      const int n_rows = __shfl_sync(0xffffffffu, my_no, g1 - g0) - base;
+      T.n_rows = n_rows; T.on = lane < n_rows;
+      T.g_off = 0;
+      for (int k = 1; k < g1 - g0; ++k) {
+        const int off = __shfl_sync(0xffffffffu, my_no, k) - base;
+        if (lane >= off) { gi = k; T.g_off = off; }
+      }
+      const int rp_lo = B.rowptr[base + min(lane, n_rows)];
+      const int rp_hi = B.rowptr[base + min(lane + 1, n_rows)];
+      const int lab = T.on ? B.labels[base + lane] : 0;
+      const int tile_e0 = __shfl_sync(0xffffffffu, rp_lo, 0);
+      const int tile_nnz = __shfl_sync(0xffffffffu, rp_hi, 31) - tile_e0;   // lane 31 read rowptr[base + n_rows]
+      T.e0 = rp_lo - tile_e0; T.e1 = T.on ? rp_hi - tile_e0 : T.e0;
+      s_lab[lane] = lab;
+      if (tile_nnz <= TILE_CSR_CAP) {
+        for (int e = lane; e < tile_nnz; e += 32) { s_col[e] = B.col[tile_e0 + e]; s_val[e] = B.val[tile_e0 + e]; }
+        T.col = s_col; T.val = s_val;
+      } else {
+        T.col = B.col + tile_e0; T.val = B.val + tile_e0;
+      }
+      T.lab = s_lab;
+      __syncwarp();
     }
-    const int rp_lo = B.rowptr[base + min(lane, n_rows)];
-    const int rp_hi = B.rowptr[base + min(lane + 1, n_rows)];
-    const int tile_e0 = __shfl_sync(0xffffffffu, rp_lo, 0);
-    const int tile_nnz = B.rowptr[base + n_rows] - tile_e0;
-    T.e0 = rp_lo - tile_e0; T.e1 = T.on ? rp_hi - tile_e0 : T.e0;
-    s_lab[lane] = T.on ? B.labels[base + lane] : 0;
-    if (tile_nnz <= TILE_CSR_CAP) {
-      for (int e = lane; e < tile_nnz; e += 32) { s_col[e] = B.col[tile_e0 + e]; s_val[e] = B.val[tile_e0 + e]; }
-      T.col = s_col; T.val = s_val;
-    } else {
-      T.col = B.col + tile_e0; T.val = B.val + tile_e0;
+    if (!w_ready) {   // the first tile's CSR loads overlapped the weight copy
+      tile_cp_async_wait_all();
+      __syncthreads();
+      w_ready = true;
     }
-    T.lab = s_lab;
-    __syncwarp();
-    float* H = tile_node_layers(M, P, T, s_w, bufA, bufB, lane);
+    if (!live) break;
+    if (t == blockIdx.x * nw) TILE_STAMP(3);
+    int ldh;
+    float* H = tile_node_layers(M, P, T, s_w, bufA, bufB, lane, &ldh);
+    if (t == blockIdx.x * nw) TILE_STAMP(4);
     float* scratch = H == bufA ? bufB : bufA;
-    const int ldh = P.ldh;
     // ---- pooling, per graph of the tile ----
     if (M.pool_kind == SGNN_LAYER_PADDING) {
       for (int k = 0; k < g1 - g0; ++k) {
@@ -279,47 +334,58 @@ embed_tile_kernel(const __grid_constant__ ModelDev M, const __grid_constant__ Em
           out[idx] = p < n ? H[(off + p) * ldh + c] : M.pool_fparam;
         }
       }
-    } else if (M.pool_kind == SGNN_LAYER_AVERAGE) {
-      for (int idx = lane; idx < (g1 - g0) * d; idx += 32) {
-        const int k = idx / d, j = idx - k * d;
-        const int off = B.node_off[g0 + k] - base, n = B.node_off[g0 + k + 1] - base - off;
-        float s = 0.f;
-        for (int i = 0; i < n; ++i) s += H[(off + i) * ldh + j];
-        emb[(size_t)(g0 + k) * E + j] = s / (float)n;
+    } else {
+      // Average / Attention: lane idx owns output (graph k, column j); graph extents come by shuffle
+      const int cnt = (g1 - g0) * d;
+      float* s_mean = scratch;                 // [gpw][d]   (Attention only)
+      float* s_c = scratch + cnt;              // [gpw][d]
+      const bool att = M.pool_kind == SGNN_LAYER_ATTENTION;
+      for (int i0 = 0; i0 < cnt; i0 += 32) {
+        const int idx = i0 + lane;
+        const bool ok = idx < cnt;
+        const int k = ok ? idx / d : 0, j = idx - k * d;
+        const int off = __shfl_sync(0xffffffffu, my_no, k) - base;
+        const int n = __shfl_sync(0xffffffffu, my_no, k + 1) - base - off;
+        if (ok) {
+          float s = 0.f;
+          for (int i = 0; i < n; ++i) s += H[(off + i) * ldh + j];
+          s /= (float)n;
+          if (att) s_mean[idx] = s; else emb[(size_t)(g0 + k) * E + j] = s;
+        }
       }
-    } else {   // Attention (layers.py:154-160)
-      float* s_mean = scratch;                 // [gpw][d]
-      float* s_c = scratch + (g1 - g0) * d;    // [gpw][d]
-      const float* Wa = s_w + P.att_s;
-      for (int idx = lane; idx < (g1 - g0) * d; idx += 32) {
-        const int k = idx / d, j = idx - k * d;
-        const int off = B.node_off[g0 + k] - base, n = B.node_off[g0 + k + 1] - base - off;
-        float s = 0.f;
-        for (int i = 0; i < n; ++i) s += H[(off + i) * ldh + j];
-        s_mean[idx] = s / (float)n;
-      }
-      __syncwarp();
-      for (int idx = lane; idx < (g1 - g0) * d; idx += 32) {
-        const int k = idx / d, j = idx - k * d;
-        float s = 0.f;
-        for (int kk = 0; kk < d; ++kk) s = fmaf(s_mean[k * d + kk], Wa[kk * d + j], s);
-        s_c[idx] = tanhf(s);
-      }
-      __syncwarp();
-      if (T.on) {
-        float s = 0.f;
-        for (int kk = 0; kk < d; ++kk) s = fmaf(H[lane * ldh + kk], s_c[gi * d + kk], s);
-        s_att[lane] = 1.f / (1.f + expf(-s));
-      }
-      __syncwarp();
-      for (int idx = lane; idx < (g1 - g0) * d; idx += 32) {
-        const int k = idx / d, j = idx - k * d;
-        const int off = B.node_off[g0 + k] - base, n = B.node_off[g0 + k + 1] - base - off;
-        float s = 0.f;
-        for (int i = 0; i < n; ++i) s = fmaf(s_att[off + i], H[(off + i) * ldh + j], s);
-        emb[(size_t)(g0 + k) * E + j] = s;
+      if (att) {   // layers.py:154-160
+        const float* Wa = s_w + P.att_s;
+        __syncwarp();
+        for (int idx = lane; idx < cnt; idx += 32) {
+          const int k = idx / d, j = idx - k * d;
+          float s = 0.f;
+          for (int kk = 0; kk < d; ++kk) s = fmaf(s_mean[k * d + kk], Wa[kk * d + j], s);
+          s_c[idx] = tanhf(s);
+        }
+        __syncwarp();
+        if (T.on) {
+          float s = 0.f;
+          for (int kk = 0; kk < d; ++kk) s = fmaf(H[lane * ldh + kk], s_c[gi * d + kk], s);
+          s_att[lane] = 1.f / (1.f + expf(-s));
+        }
+        __syncwarp();
+        for (int i0 = 0; i0 < cnt; i0 += 32) {
+          const int idx = i0 + lane;
+          const bool ok = idx < cnt;
+          const int k = ok ? idx / d : 0, j = idx - k * d;
+          const int off = __shfl_sync(0xffffffffu, my_no, k) - base;
+          const int n = __shfl_sync(0xffffffffu, my_no, k + 1) - base - off;
+          if (ok) {
+            float s = 0.f;
+            for (int i = 0; i < n; ++i) s = fmaf(s_att[off + i], H[(off + i) * ldh + j], s);
+            emb[(size_t)(g0 + k) * E + j] = s;
+          }
+        }
       }
     }
     __syncwarp();
+    if (t == blockIdx.x * nw) TILE_STAMP(5);
   }
+  TILE_STAMP(6);
+  TILE_STAMP(7);
 }

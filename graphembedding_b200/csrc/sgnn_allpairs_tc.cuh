@@ -146,6 +146,9 @@ struct TcEpi {
   float* sim;
   int64_t ld;
   int m, n;
+  unsigned long long* smax;   // optional [m][n_slices]: largest rank key (orderable score << 32 | graph id,
+                              // sgnn_rank.cuh) of every 32-graph slice -- hints for topk_hint_kernel
+  int n_slices;
 #ifdef SGNN_TC_TRACE
   long long* trace; int tile;
 #endif
@@ -155,6 +158,20 @@ struct TcEpi {
 #else
 #define TC_ESTAMP(slot) do { } while (0)
 #endif
+
+__device__ __forceinline__ float tc_warp_max(float x) {   // CREDUX.MAX.F32: one instruction, uniform result
+  float y;
+  asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// same key as rank_key() in sgnn_rank.cuh: descending key order = descending score, ties -> higher id first
+__device__ __forceinline__ unsigned long long tc_rank_key(float f, int idx) {
+  f += 0.f;
+  unsigned int u = __float_as_uint(f);
+  u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+  return ((unsigned long long)u << 32) | (unsigned int)idx;
+}
 
 __device__ __forceinline__ float tc_ex2(float x) {
   float y;
@@ -180,7 +197,7 @@ __device__ __forceinline__ float tc_finish(const TcEpi& E, float st) {
 // rest).  KT > 0: K known at compile time; the part is pulled into registers with one wait, the
 // warp signals the buffer's MMA issuer at once (8 warps share a buffer), and the arithmetic + stores
 // run from registers while the other warps of the scheduler cover the TMEM load latency.
-template <int KT, bool RELU, bool REF, bool SIMK, int PART>
+template <int KT, bool RELU, bool REF, bool SIMK, int PART, bool HINT>
 __device__ __forceinline__ void tc_epilogue_part(const TcEpi& E, uint32_t taddr, int K, int KCr, int QH, int qrow0,
                                                  int g, uint64_t* t_empty, int lane) {
   const int64_t ld = E.ld;
@@ -203,6 +220,11 @@ __device__ __forceinline__ void tc_epilogue_part(const TcEpi& E, uint32_t taddr,
 #pragma unroll
       for (int k = 0; k < KT; ++k) u[k] = E.sU[k];
     }
+    static_assert(NQ <= 32, "one lane per query keeps the slice maximum");
+    constexpr bool hint = HINT;
+    const float off_row = g < E.n ? 0.f : -INFINITY;   // rows past the database never win a slice
+    float keep = 0.f;
+    unsigned keep_mask = 1u;
 #pragma unroll
     for (int q = 0; q < NQ; ++q) {
       float st;
@@ -221,7 +243,16 @@ __device__ __forceinline__ void tc_epilogue_part(const TcEpi& E, uint32_t taddr,
       const float sv = tc_finish<RELU, REF, SIMK>(E, st);
       if (q < qmax) *p = sv;
       p += ld;
+      if (hint) {   // slice maximum and which lanes hold it (ties -> highest graph id, the reference's order)
+        const float mine = sv + off_row;
+        const float w = tc_warp_max(mine);
+        const unsigned who = __ballot_sync(0xffffffffu, mine == w);
+        if (lane == q) { keep = w; keep_mask = who; }
+      }
     }
+    if (hint && lane < min(NQ, E.m - (qrow0 + Q0)))
+      E.smax[(size_t)(qrow0 + Q0 + lane) * E.n_slices + (g >> 5)] =
+          tc_rank_key(keep, (g & ~31) + 31 - __clz(keep_mask | 1u));
   } else {
     const int QA = (QH + 1) / 2;
     const int q0 = PART ? QA : 0, nq = PART ? QH - QA : QA;
@@ -231,6 +262,10 @@ __device__ __forceinline__ void tc_epilogue_part(const TcEpi& E, uint32_t taddr,
     const uint32_t t0 = taddr + q0 * KCr;
     float st = 0.f;
     int kk = 0, qq = 0;
+    constexpr bool hint = HINT;
+    const int qrows = min(nq, E.m - (qrow0 + q0));
+    float keep = 0.f;
+    int keep_lane = 0;
     for (int c0 = 0; c0 < cols; c0 += 8) {
       float v[8];
       tc::tmem_ld8(t0 + c0, v);   // may read past this part's columns, never past the 128-column tile + 7
@@ -248,6 +283,17 @@ __device__ __forceinline__ void tc_epilogue_part(const TcEpi& E, uint32_t taddr,
           if (++kk == KCr) {
             const float sv = tc_finish<RELU, REF, SIMK>(E, st);
             if (qq < qmax) p[(size_t)qq * ld] = sv;
+            if (hint) {   // lane (qq mod 32) keeps query qq's slice maximum; flushed every 32 queries
+              const float mine = g < E.n ? sv : -INFINITY;
+              const float w = tc_warp_max(mine);
+              const int top = 31 - __clz(__ballot_sync(0xffffffffu, mine == w));
+              if (lane == (qq & 31)) { keep = w; keep_lane = top; }
+              if ((qq & 31) == 31 || qq == nq - 1) {
+                const int qrow = (qq & ~31) + lane;
+                if (qrow <= qq && qrow < qrows)
+                  E.smax[(size_t)(qrow0 + q0 + qrow) * E.n_slices + (g >> 5)] = tc_rank_key(keep, (g & ~31) + keep_lane);
+              }
+            }
             st = 0.f; kk = 0; ++qq;
           }
         }
@@ -263,7 +309,7 @@ template <int KT, bool RELU, bool REF, bool SIMK>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 allpairs_tc_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const float* __restrict__ params,
                    const __nv_bfloat16* __restrict__ Ag, const __nv_bfloat16* __restrict__ Bg,
-                   float* __restrict__ sim, int64_t ld
+                   float* __restrict__ sim, int64_t ld, unsigned long long* __restrict__ smax
 #ifdef SGNN_TC_TRACE
                    , long long* __restrict__ trace   // [tile][8] clock64 stamps of CTA 0 (tools/tc_trace.cu)
 #endif
@@ -393,6 +439,7 @@ allpairs_tc_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const flo
     TcEpi E;
     E.sU = sU; E.yeta = M.yeta; E.final_act = M.final_act; E.pair_act = dot ? SGNN_ACT_IDENTITY : M.pair_act;
     E.sim = sim; E.ld = ld; E.m = G.m; E.n = G.n;
+    E.smax = smax; E.n_slices = G.n_gtiles * 4;
     float su = 0.f;
     for (int k = 0; k < G.K; ++k) su += sU[k];
     E.su = su;
@@ -418,10 +465,17 @@ allpairs_tc_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const flo
 #ifdef SGNN_TC_TRACE
       E.trace = trace; E.tile = it;
 #endif
-      if (part == 0)
-        tc_epilogue_part<KT, RELU, REF, SIMK, 0>(E, taddr, G.K, G.KC, G.QH, (qb0 + i) * G.QH, g, t_empty + buf, lane);
-      else
-        tc_epilogue_part<KT, RELU, REF, SIMK, 1>(E, taddr, G.K, G.KC, G.QH, (qb0 + i) * G.QH, g, t_empty + buf, lane);
+      if (smax == nullptr) {
+        if (part == 0)
+          tc_epilogue_part<KT, RELU, REF, SIMK, 0, false>(E, taddr, G.K, G.KC, G.QH, (qb0 + i) * G.QH, g, t_empty + buf, lane);
+        else
+          tc_epilogue_part<KT, RELU, REF, SIMK, 1, false>(E, taddr, G.K, G.KC, G.QH, (qb0 + i) * G.QH, g, t_empty + buf, lane);
+      } else {
+        if (part == 0)
+          tc_epilogue_part<KT, RELU, REF, SIMK, 0, true>(E, taddr, G.K, G.KC, G.QH, (qb0 + i) * G.QH, g, t_empty + buf, lane);
+        else
+          tc_epilogue_part<KT, RELU, REF, SIMK, 1, true>(E, taddr, G.K, G.KC, G.QH, (qb0 + i) * G.QH, g, t_empty + buf, lane);
+      }
       if (lg == 0 && lane == 0) TC_STAMP(it, 6);
       ga += TC_EPI_GROUPS;
       while (ga >= ga_count) { ga -= ga_count; ++i; }

@@ -46,6 +46,8 @@ struct SgnnHandle_t {
   int64_t cap_P = 0;
   __nv_bfloat16 *d_Atc = nullptr, *d_Btc = nullptr;  // tensor-core operands in UMMA tile order
   int64_t cap_Atc = 0, cap_Btc = 0;                   // in elements
+  unsigned long long* d_smax = nullptr;                          // [queries][32-graph slices] slice maxima (top-k hints)
+  int64_t cap_smax = 0;
   int dep = 16;                           // padded embedding width of the all-pairs scorer
   cudaStream_t stream = nullptr;          // used by *_host entry points
   cudaStream_t copy_stream = nullptr;     // host -> device uploads that overlap compute (sgnn_rank_host)
@@ -231,9 +233,14 @@ int ensure_query_tables(SgnnHandle h, int64_t m) {
 }
 
 
+// Stages of sgnn_score_all_pairs: the query-side tables, the database-side operand, the scorer.
+// sgnn_rank_device / sgnn_rank_host issue them separately so that the query side overlaps the
+// database upload / embedding.
+enum { SCORE_PREP_Q = 1, SCORE_PREP_DB = 2, SCORE_MAIN = 4, SCORE_ALL = 7 };
+
 // tcgen05 path of sgnn_score_all_pairs (SGNN_PREC_BF16X3 / SGNN_PREC_BF16)
 int score_all_pairs_tc(SgnnHandle h, const float* emb_q, int m, const float* emb_db, int n, float* sim,
-                       int64_t ld, cudaStream_t st) {
+                       int64_t ld, cudaStream_t st, int stages, unsigned long long* smax) {
   const ModelDev& M = h->M;
   const bool ntn = M.pair_kind == SGNN_LAYER_NTN;
   TcGeom G;
@@ -266,12 +273,72 @@ int score_all_pairs_tc(SgnnHandle h, const float* emb_q, int m, const float* emb
   size_t smem = fixed + (size_t)G.stages * tc_b_bytes(G);
   smem = std::max<size_t>(smem, 120 * 1024);  // one CTA per SM: each CTA owns all 512 TMEM columns
   const int grid = g_groups * q_groups;
-  const cudaError_t e = sgnn_tc_launch(M, G, relu, ref, simk, grid, smem, h->d_params, emb_q, emb_db, h->d_Atc,
-                                       h->d_Btc, sim, ld, st);
+  cudaError_t e = cudaSuccess;
+  if (stages & SCORE_PREP_Q) e = sgnn_tc_prep_q(M, G, h->d_params, emb_q, h->d_Btc, st);
+  if (e == cudaSuccess && (stages & SCORE_PREP_DB)) e = sgnn_tc_prep_db(M, G, emb_db, h->d_Atc, st);
+  if (e == cudaSuccess && (stages & SCORE_MAIN))
+    e = sgnn_tc_score(M, G, relu, ref, simk, grid, smem, h->d_params, h->d_Atc, h->d_Btc, sim, ld, smax, st);
   if (e != cudaSuccess) return fail(h, std::string("tensor-core all-pairs launch: ") + cudaGetErrorString(e));
   return 0;
 }
 
+int score_all_pairs_stages(SgnnHandle h, const float* emb_q, int32_t m, const float* emb_db, int32_t n,
+                           float* sim_dev, int64_t ld, cudaStream_t st, int stages,
+                           unsigned long long* smax = nullptr);
+// scorer + top-k of the fused ranking entry points: with the tensor-core scorer and a long enough
+// row, the scorer emits slice maxima and the top-k kernel reads those instead of the rows
+int score_and_topk(SgnnHandle h, const float* emb_q, int m, const float* emb_db, int n, float* sim, int64_t ld,
+                   int stages, int k, int32_t* ids, float* vals, cudaStream_t st);
+
+}  // namespace
+
+namespace {
+int score_and_topk(SgnnHandle h, const float* emb_q, int m, const float* emb_db, int n, float* sim, int64_t ld,
+                   int stages, int k, int32_t* ids, float* vals, cudaStream_t st) {
+  const int n_slices = tc_n_slices(n);
+  const bool want_topk = k > 0 && ids;
+  // hinted kernels: warp per row for k <= 32 and 1024..32768 columns, CTA per row for k <= 256 and >= 8192
+  const bool hint = want_topk && h->cfg.precision != SGNN_PREC_FP32 && (int64_t)m * n_slices <= h->cap_smax &&
+                    ((k <= 32 && n_slices >= 32 && n_slices <= 1024) || (k <= 256 && n_slices >= 256));
+  if (score_all_pairs_stages(h, emb_q, m, emb_db, n, sim, ld, st, stages, hint ? h->d_smax : nullptr)) return 1;
+  if (!want_topk) return 0;
+  if (!hint) return sgnn_topk(h, sim, m, n, ld, k, ids, vals, st);
+  const cudaError_t e = sgnn_launch_topk_hint(sim, h->d_smax, n_slices, m, n, ld, k, ids, vals, st);
+  if (e != cudaSuccess) return fail(h, std::string("top-k (hinted): ") + cudaGetErrorString(e));
+  return 0;
+}
+
+int score_all_pairs_stages(SgnnHandle h, const float* emb_q, int32_t m, const float* emb_db, int32_t n,
+                           float* sim_dev, int64_t ld, cudaStream_t st, int stages, unsigned long long* smax) {
+  if (m == 0 || n == 0) return 0;
+  if (ld < n) return fail(h, "sgnn_score_all_pairs: ld < n");
+  if (ensure_query_tables(h, m)) return 1;
+  const ModelDev& M = h->M;
+  const int K = M.pair_kind == SGNN_LAYER_NTN ? M.K : 1;
+  if (h->cfg.precision != SGNN_PREC_FP32) return score_all_pairs_tc(h, emb_q, m, emb_db, n, sim_dev, ld, st, stages, smax);
+  const int DEP = h->dep;
+  if (stages & SCORE_PREP_Q) {
+    allpairs_prep_kernel<<<(m + 3) / 4, 128, 0, st>>>(M, h->d_params, emb_q, m, DEP, h->d_P, h->d_C);
+    CUDA_OK(h, cudaGetLastError());
+  }
+  if (!(stages & SCORE_MAIN)) return 0;
+  constexpr int QC = 8;
+  const int gx = (n + 127) / 128;
+  // enough query blocks to fill the machine a few times over
+  int gy = std::max(1, std::min((m + QC - 1) / QC, (h->sm_count * 8 + gx - 1) / gx));
+  const int qpb = ((m + gy - 1) / gy + QC - 1) / QC * QC;
+  gy = (m + qpb - 1) / qpb;
+  const size_t smem = ((size_t)QC * K * DEP + QC * K + K) * sizeof(float);
+  dim3 grid(gx, gy);
+  if (DEP == 16)
+    allpairs_fp32_kernel<16, QC><<<grid, 128, smem, st>>>(M, h->d_params, h->d_P, h->d_C, emb_db, m, n, qpb, sim_dev, ld);
+  else if (DEP == 32)
+    allpairs_fp32_kernel<32, QC><<<grid, 128, smem, st>>>(M, h->d_params, h->d_P, h->d_C, emb_db, m, n, qpb, sim_dev, ld);
+  else
+    allpairs_fp32_kernel<64, QC><<<grid, 128, smem, st>>>(M, h->d_params, h->d_P, h->d_C, emb_db, m, n, qpb, sim_dev, ld);
+  CUDA_OK(h, cudaGetLastError());
+  return 0;
+}
 }  // namespace
 
 extern "C" {
@@ -327,7 +394,7 @@ int sgnn_destroy(SgnnHandle h) {
   if (!h) return 0;
   cudaSetDevice(h->device);
   cudaFree(h->d_params); cudaFree(h->d_grads); cudaFree(h->d_m); cudaFree(h->d_v); cudaFree(h->d_loss);
-  cudaFree(h->d_P); cudaFree(h->d_C); cudaFree(h->d_Atc); cudaFree(h->d_Btc);
+  cudaFree(h->d_P); cudaFree(h->d_C); cudaFree(h->d_Atc); cudaFree(h->d_Btc); cudaFree(h->d_smax);
   cudaFree(h->d_rowsA); cudaFree(h->d_rowsB);
   HostWs& w = h->ws;
   for (int s = 0; s < 2; ++s) {
@@ -454,6 +521,11 @@ int sgnn_reserve(SgnnHandle h, int64_t max_graphs, int64_t max_nodes, int64_t ma
       CUDA_OK(h, cudaMemset(h->d_Btc, 0, need_b * sizeof(__nv_bfloat16)));
       h->cap_Btc = need_b;
     }
+    const int64_t need_s = max_queries * (int64_t)tc_n_slices((int)max_db);
+    if (need_s > h->cap_smax) {
+      if (dev_alloc(h, &h->d_smax, need_s)) return 1;
+      h->cap_smax = need_s;
+    }
   }
   if (max_queries * max_db > w.cap_q * w.cap_db || max_queries > w.cap_q) {
     w.cap_q = std::max(w.cap_q, max_queries);
@@ -540,32 +612,7 @@ int sgnn_forward_pairs(SgnnHandle h, const SgnnGraphBatch* b, const int32_t* g1,
 int sgnn_score_all_pairs(SgnnHandle h, const float* emb_q, int32_t m, const float* emb_db, int32_t n,
                          float* sim_dev, int64_t ld, void* stream) {
   if (!h || !emb_q || !emb_db || !sim_dev) return fail(h, "sgnn_score_all_pairs: null argument");
-  if (m == 0 || n == 0) return 0;
-  if (ld < n) return fail(h, "sgnn_score_all_pairs: ld < n");
-  if (ensure_query_tables(h, m)) return 1;
-  cudaStream_t st = (cudaStream_t)stream;
-  const ModelDev& M = h->M;
-  const int K = M.pair_kind == SGNN_LAYER_NTN ? M.K : 1;
-  if (h->cfg.precision != SGNN_PREC_FP32) return score_all_pairs_tc(h, emb_q, m, emb_db, n, sim_dev, ld, st);
-  const int DEP = h->dep;
-  allpairs_prep_kernel<<<(m + 3) / 4, 128, 0, st>>>(M, h->d_params, emb_q, m, DEP, h->d_P, h->d_C);
-  CUDA_OK(h, cudaGetLastError());
-  constexpr int QC = 8;
-  const int gx = (n + 127) / 128;
-  // enough query blocks to fill the machine a few times over
-  int gy = std::max(1, std::min((m + QC - 1) / QC, (h->sm_count * 8 + gx - 1) / gx));
-  const int qpb = ((m + gy - 1) / gy + QC - 1) / QC * QC;
-  gy = (m + qpb - 1) / qpb;
-  const size_t smem = ((size_t)QC * K * DEP + QC * K + K) * sizeof(float);
-  dim3 grid(gx, gy);
-  if (DEP == 16)
-    allpairs_fp32_kernel<16, QC><<<grid, 128, smem, st>>>(M, h->d_params, h->d_P, h->d_C, emb_db, m, n, qpb, sim_dev, ld);
-  else if (DEP == 32)
-    allpairs_fp32_kernel<32, QC><<<grid, 128, smem, st>>>(M, h->d_params, h->d_P, h->d_C, emb_db, m, n, qpb, sim_dev, ld);
-  else
-    allpairs_fp32_kernel<64, QC><<<grid, 128, smem, st>>>(M, h->d_params, h->d_P, h->d_C, emb_db, m, n, qpb, sim_dev, ld);
-  CUDA_OK(h, cudaGetLastError());
-  return 0;
+  return score_all_pairs_stages(h, emb_q, m, emb_db, n, sim_dev, ld, (cudaStream_t)stream, SCORE_ALL);
 }
 
 #define LAUNCH_OK(h, what, expr)                                                              \
@@ -761,6 +808,33 @@ int sgnn_forward_pairs_host(SgnnHandle h, const SgnnGraphBatch* b, const int32_t
   return 0;
 }
 
+int sgnn_rank_device(SgnnHandle h, const SgnnGraphBatch* q_dev, const SgnnGraphBatch* db_dev, int32_t k,
+                     float* emb_q_dev, float* emb_db_dev, float* sim_dev, int64_t ld, int32_t* topk_ids_dev,
+                     float* topk_vals_dev, void* stream) {
+  if (!h || !q_dev || !db_dev || !emb_q_dev || !emb_db_dev || !sim_dev)
+    return fail(h, "sgnn_rank_device: null argument");
+  const int m = q_dev->n_graphs, n = db_dev->n_graphs;
+  if (m == 0 || n == 0) return 0;
+  cudaStream_t st = (cudaStream_t)stream, side = h->copy_stream;
+  // fork: the query branch (embed + query-side scorer tables) runs beside the database branch
+  CUDA_OK(h, cudaEventRecord(h->chunk_ev[1], st));
+  CUDA_OK(h, cudaStreamWaitEvent(side, h->chunk_ev[1], 0));
+  if (sgnn_embed_graphs(h, q_dev, emb_q_dev, side)) return 1;
+  if (score_all_pairs_stages(h, emb_q_dev, m, emb_db_dev, n, sim_dev, ld, side, SCORE_PREP_Q)) return 1;
+  CUDA_OK(h, cudaEventRecord(h->chunk_ev[2], side));
+  if (sgnn_embed_graphs(h, db_dev, emb_db_dev, st)) return 1;
+  if (score_all_pairs_stages(h, emb_q_dev, m, emb_db_dev, n, sim_dev, ld, st, SCORE_PREP_DB)) return 1;
+  CUDA_OK(h, cudaStreamWaitEvent(st, h->chunk_ev[2], 0));   // join
+  return score_and_topk(h, emb_q_dev, m, emb_db_dev, n, sim_dev, ld, SCORE_MAIN, k, topk_ids_dev, topk_vals_dev, st);
+}
+
+int sgnn_debug_slice_hints(SgnnHandle h, unsigned long long** hints_dev, int64_t* capacity) {
+  if (!h || !hints_dev) return fail(h, "sgnn_debug_slice_hints: null argument");
+  *hints_dev = h->d_smax;
+  if (capacity) *capacity = h->cap_smax;
+  return 0;
+}
+
 int sgnn_rank_host(SgnnHandle h, const SgnnGraphBatch* q, const SgnnGraphBatch* db, int32_t k,
                    int32_t* topk_ids_host, float* topk_vals_host, float* sim_host) {
   if (!h || !q || !db) return fail(h, "sgnn_rank_host: null argument");
@@ -777,11 +851,15 @@ int sgnn_rank_host(SgnnHandle h, const SgnnGraphBatch* q, const SgnnGraphBatch* 
   CUDA_OK(h, cudaEventRecord(h->chunk_ev[0], cs));
   if (upload_batch_on(h, q, 0, &dq, st)) return 1;
   if (sgnn_embed_graphs(h, &dq, w.emb_q, st)) return 1;
+  // query-side tables of the scorer are ready before the database lands
+  if (score_all_pairs_stages(h, w.emb_q, (int)m, w.emb_db, (int)n, w.sim, n, st, SCORE_PREP_Q)) return 1;
   CUDA_OK(h, cudaStreamWaitEvent(st, h->chunk_ev[0], 0));
   if (sgnn_embed_graphs(h, &ddb, w.emb_db, st)) return 1;
-  if (sgnn_score_all_pairs(h, w.emb_q, (int)m, w.emb_db, (int)n, w.sim, n, st)) return 1;
-  if (k > 0 && topk_ids_host) {
-    if (sgnn_topk(h, w.sim, (int)m, (int)n, n, k, w.topk_ids, w.topk_vals, st)) return 1;
+  const bool want_topk = k > 0 && topk_ids_host;
+  if (score_and_topk(h, w.emb_q, (int)m, w.emb_db, (int)n, w.sim, n, SCORE_PREP_DB | SCORE_MAIN, want_topk ? k : 0,
+                     w.topk_ids, w.topk_vals, st))
+    return 1;
+  if (want_topk) {
     CUDA_OK(h, cudaMemcpyAsync(topk_ids_host, w.topk_ids, (size_t)m * k * 4, cudaMemcpyDeviceToHost, st));
     if (topk_vals_host)
       CUDA_OK(h, cudaMemcpyAsync(topk_vals_host, w.topk_vals, (size_t)m * k * 4, cudaMemcpyDeviceToHost, st));

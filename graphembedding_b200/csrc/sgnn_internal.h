@@ -8,6 +8,9 @@
 cudaError_t sgnn_launch_topk(const float* sim, const int32_t* col_ids, int m, int n, int64_t ld, int k,
                              int32_t* ids, float* vals, cudaStream_t st);
 // returns cudaErrorInvalidValue if a row does not fit the shared-memory sorter
+// top-k from slice-maximum hints (smax [m][n_slices], 32 columns per slice) written by the tensor-core scorer
+cudaError_t sgnn_launch_topk_hint(const float* sim, const unsigned long long* smax, int n_slices, int m, int n, int64_t ld, int k,
+                                  int32_t* ids, float* vals, cudaStream_t st);
 cudaError_t sgnn_launch_sort_rows(const float* sim, int m, int n, int64_t ld, int32_t* ids, int smem_optin,
                                   cudaStream_t st);
 cudaError_t sgnn_launch_prec_at_k(const float* true_sim, const float* pred_sim, int m, int n, const int32_t* ks,

@@ -20,6 +20,20 @@ cudaError_t sgnn_launch_topk(const float* sim, const int32_t* col_ids, int m, in
   return cudaGetLastError();
 }
 
+cudaError_t sgnn_launch_topk_hint(const float* sim, const unsigned long long* smax, int n_slices, int m, int n, int64_t ld, int k,
+                                  int32_t* ids, float* vals, cudaStream_t st) {
+  const int blocks = (m + 7) / 8;
+  if (k <= 32 && n_slices >= 32 && n_slices <= 32 * 10)
+    topk_hint_warp_kernel<10><<<blocks, 256, 0, st>>>(sim, smax, n_slices, m, n, ld, k, ids, vals);
+  else if (k <= 32 && n_slices >= 32 && n_slices <= 32 * 32)
+    topk_hint_warp_kernel<32><<<blocks, 256, 0, st>>>(sim, smax, n_slices, m, n, ld, k, ids, vals);
+  else if (n_slices >= 256)
+    topk_hint_kernel<<<m, 256, 0, st>>>(sim, smax, n_slices, n, ld, k, ids, vals);
+  else
+    return cudaErrorInvalidValue;
+  return cudaGetLastError();
+}
+
 cudaError_t sgnn_launch_sort_rows(const float* sim, int m, int n, int64_t ld, int32_t* ids, int smem_optin,
                                   cudaStream_t st) {
   const int n_pad = pad_pow2(n);
@@ -56,3 +70,10 @@ cudaError_t sgnn_launch_kendall(const float* true_sim, const float* pred_sim, in
   kendall_tau_kernel<<<m, 1024, bytes, st>>>(true_sim, pred_sim, n, n_pad, counts, tau);
   return cudaGetLastError();
 }
+
+#ifdef SGNN_TILE_TRACE
+extern "C" int sgnn_debug_topk_trace(int* out, int n) {
+  cudaDeviceSynchronize();
+  return (int)cudaMemcpyFromSymbol(out, g_topk_dbg, sizeof(int) * (size_t)n);
+}
+#endif

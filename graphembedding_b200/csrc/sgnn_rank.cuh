@@ -191,6 +191,251 @@ topk_select_kernel(const float* __restrict__ sim, const int32_t* __restrict__ co
   }
 }
 
+// Top-k with slice-maximum hints.  The tensor-core scorer also emits, for every query row, the
+// largest rank key (score, then graph id) of every 32-column slice (smax [m][n_slices]).  The k-th
+// largest slice key is a lower bound of the row's k-th largest key (k different slices each hold
+// an element >= it), and a slice whose largest key is below the bound holds no top-k element: the
+// kernel reads n / 32 hints plus a handful of slices instead of the row (twice).  Because the
+// keys carry the graph id, rows full of equal scores cost nothing extra.  Bound, candidate ranking
+// and tie order are those of topk_select_kernel.
+#ifdef SGNN_TILE_TRACE
+__device__ int g_topk_dbg[4096 * 4];   // per row: candidates, hot slices, clock cycles, fell back
+#endif
+__global__ void __launch_bounds__(256)
+topk_hint_kernel(const float* __restrict__ sim, const unsigned long long* __restrict__ smax, int n_slices, int n,
+                 int64_t ld, int k, int32_t* __restrict__ ids, float* __restrict__ vals) {
+  __shared__ unsigned long long s_cand[TOPK_CAND];
+  __shared__ unsigned long long s_red[32];
+  __shared__ unsigned long long s_top[8][32];
+  __shared__ unsigned long long s_thr;
+  __shared__ int s_cnt;
+#ifdef SGNN_TILE_TRACE
+  const long long dbg_t0 = clock64();
+  int dbg_hot = 0;
+#endif
+  const float* r = sim + (size_t)blockIdx.x * ld;
+  const unsigned long long* h = smax + (size_t)blockIdx.x * n_slices;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  // thread maximum over its hints (threads own disjoint slices); the EXACT k-th largest of the 256
+  // thread maxima is the bound: each warp sorts its 32 keys, and a key of global rank < k only has
+  // keys of local rank < k above it, so counting over every warp's first min(k, 32) keys is exact
+  unsigned long long key = 0ull;
+  for (int i = tid; i < n_slices; i += 256) {
+    const unsigned long long u = h[i];
+    key = u > key ? u : key;
+  }
+  if (tid == 0) { s_cnt = 0; s_thr = 0ull; }
+#pragma unroll
+  for (int k2 = 2; k2 <= 32; k2 <<= 1) {
+#pragma unroll
+    for (int j2 = k2 >> 1; j2 > 0; j2 >>= 1) {
+      const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, j2);
+      const bool take_max = ((lane & j2) == 0) == ((lane & k2) == 0);
+      key = take_max ? (key > other ? key : other) : (key < other ? key : other);
+    }
+  }
+  const int kk32 = k < 32 ? k : 32;
+  if (lane < kk32) s_top[warp][lane] = key;
+  __syncthreads();
+  if (lane < kk32 && key != 0ull) {
+    int above = 0;
+    for (int w = 0; w < 8; ++w)
+      for (int l = 0; l < kk32; ++l) above += s_top[w][l] > key ? 1 : 0;
+    if (above == k - 1) s_thr = key;   // keys are unique: one writer
+  }
+  __syncthreads();
+  const unsigned long long thr = s_thr;
+  const unsigned int thr_u = (unsigned int)(thr >> 32);
+  // slices that can hold a top-k element; a warp reads up to four of them per step, lane = element
+  for (int s0 = warp * 32; s0 < n_slices; s0 += 256) {
+    const int sl = s0 + lane;
+    const bool hot = sl < n_slices && thr != 0ull && h[sl] >= thr;
+    unsigned int todo = __ballot_sync(0xffffffffu, hot);
+#ifdef SGNN_TILE_TRACE
+    dbg_hot += __popc(todo);
+#endif
+    while (todo) {
+      int idx[4];
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        idx[u] = -1;
+        if (todo) {
+          idx[u] = (s0 + __ffs(todo) - 1) * 32 + lane;
+          todo &= todo - 1;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = idx[u] >= 0 && idx[u] < n ? r[idx[u]] : 0.f;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (idx[u] >= 0 && idx[u] < n) {
+          const unsigned int ou = orderable_u32(v[u]);
+          if (ou >= thr_u) {
+            const unsigned long long kk = ((unsigned long long)ou << 32) | (unsigned int)idx[u];
+            if (kk >= thr) {
+              const int pos = atomicAdd(&s_cnt, 1);
+              if (pos < TOPK_CAND) s_cand[pos] = kk;
+            }
+          }
+        }
+      }
+    }
+  }
+  __syncthreads();
+  const int c = s_cnt;
+#ifdef SGNN_TILE_TRACE
+  if (blockIdx.x < 4096 && lane == 0) {
+    if (tid == 0) { g_topk_dbg[blockIdx.x * 4] = c; g_topk_dbg[blockIdx.x * 4 + 2] = (int)(clock64() - dbg_t0);
+                    g_topk_dbg[blockIdx.x * 4 + 3] = !(c >= k && c <= TOPK_CAND); g_topk_dbg[blockIdx.x * 4 + 1] = 0; }
+    __threadfence_block();
+  }
+  __syncthreads();
+  if (blockIdx.x < 4096 && lane == 0) atomicAdd(&g_topk_dbg[blockIdx.x * 4 + 1], dbg_hot);
+#endif
+  int32_t* out_i = ids + (size_t)blockIdx.x * k;
+  float* out_v = vals ? vals + (size_t)blockIdx.x * k : nullptr;
+  if (c >= k && c <= TOPK_CAND) {
+    for (int q = tid; q < c; q += 256) {
+      const unsigned long long kq = s_cand[q];
+      int rank = 0;
+      for (int t = 0; t < c; ++t) rank += s_cand[t] > kq ? 1 : 0;
+      if (rank < k) {
+        out_i[rank] = (int)(kq & 0xffffffffull);
+        if (out_v) out_v[rank] = rank_key_score(kq);
+      }
+    }
+    return;
+  }
+  unsigned long long prev = ~0ull;   // no usable bound: k selection rounds over the row
+  for (int round = 0; round < k; ++round) {
+    unsigned long long bk = 0ull;
+    for (int i = tid; i < n; i += 256) {
+      const unsigned long long kk = rank_key(r[i], i);
+      if (kk < prev && kk > bk) bk = kk;
+    }
+    bk = block_max_u64(bk, s_red);
+    if (tid == 0) {
+      out_i[round] = (int)(bk & 0xffffffffull);
+      if (out_v) out_v[round] = rank_key_score(bk);
+    }
+    prev = bk;
+  }
+}
+
+// Warp-per-row version of the hinted top-k for k <= 32 and rows of <= 1024 * HMAX columns: the
+// hints of a row sit in registers (HMAX per lane), the bound is the k-th largest LANE maximum
+// (lanes own disjoint slices), the hot slices are read four at a time, and the handful of
+// candidates is ranked by counting -- no CTA barrier anywhere, so a row costs about one chain of
+// three dependent memory accesses.  Rows whose candidates overflow fall back to k selection rounds
+// by the same warp.
+constexpr int TOPK_WARP_CAND = 128;
+constexpr int TOPK_WARP_HOT = 96;
+
+template <int HMAX>
+__global__ void __launch_bounds__(256)
+topk_hint_warp_kernel(const float* __restrict__ sim, const unsigned long long* __restrict__ smax, int n_slices, int m,
+                      int n, int64_t ld, int k, int32_t* __restrict__ ids, float* __restrict__ vals) {
+  __shared__ unsigned long long s_cand[8][TOPK_WARP_CAND];
+  __shared__ int s_hot[8][TOPK_WARP_HOT];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int row = blockIdx.x * 8 + warp;
+  if (row >= m) return;
+  const float* r = sim + (size_t)row * ld;
+  const unsigned long long* h = smax + (size_t)row * n_slices;
+  unsigned long long hk[HMAX];
+#pragma unroll
+  for (int j = 0; j < HMAX; ++j) hk[j] = j * 32 + lane < n_slices ? h[j * 32 + lane] : 0ull;
+  unsigned long long key = hk[0];
+#pragma unroll
+  for (int j = 1; j < HMAX; ++j) key = hk[j] > key ? hk[j] : key;
+#pragma unroll
+  for (int k2 = 2; k2 <= 32; k2 <<= 1) {
+#pragma unroll
+    for (int j2 = k2 >> 1; j2 > 0; j2 >>= 1) {
+      const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, j2);
+      const bool take_max = ((lane & j2) == 0) == ((lane & k2) == 0);
+      key = take_max ? (key > other ? key : other) : (key < other ? key : other);
+    }
+  }
+  const unsigned long long thr = __shfl_sync(0xffffffffu, key, k - 1);
+  const unsigned int thr_u = (unsigned int)(thr >> 32);
+  const unsigned int lt = (1u << lane) - 1u;
+  int n_hot = 0;
+  if (thr != 0ull) {
+#pragma unroll
+    for (int j = 0; j < HMAX; ++j) {
+      const bool hot = hk[j] >= thr;
+      const unsigned int mk = __ballot_sync(0xffffffffu, hot);
+      const int pos = n_hot + __popc(mk & lt);
+      if (hot && pos < TOPK_WARP_HOT) s_hot[warp][pos] = j * 32 + lane;
+      n_hot += __popc(mk);
+    }
+  }
+  __syncwarp();
+  int c = 0;
+  bool ok = thr != 0ull && n_hot <= TOPK_WARP_HOT;
+  if (ok) {
+    for (int t0 = 0; t0 < n_hot; t0 += 4) {
+      int idx[4];
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        idx[u] = t0 + u < n_hot ? s_hot[warp][t0 + u] * 32 + lane : n;
+        v[u] = idx[u] < n ? r[idx[u]] : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        bool take = false;
+        unsigned long long kk = 0ull;
+        if (idx[u] < n) {
+          const unsigned int ou = orderable_u32(v[u]);
+          kk = ((unsigned long long)ou << 32) | (unsigned int)idx[u];
+          take = ou >= thr_u && kk >= thr;
+        }
+        const unsigned int mk = __ballot_sync(0xffffffffu, take);
+        const int pos = c + __popc(mk & lt);
+        if (take && pos < TOPK_WARP_CAND) s_cand[warp][pos] = kk;
+        c += __popc(mk);
+      }
+    }
+    ok = c >= k && c <= TOPK_WARP_CAND;
+  }
+  __syncwarp();
+  int32_t* out_i = ids + (size_t)row * k;
+  float* out_v = vals ? vals + (size_t)row * k : nullptr;
+  if (ok) {
+    for (int q = lane; q < c; q += 32) {
+      const unsigned long long kq = s_cand[warp][q];
+      int rank = 0;
+      for (int t = 0; t < c; ++t) rank += s_cand[warp][t] > kq ? 1 : 0;
+      if (rank < k) {
+        out_i[rank] = (int)(kq & 0xffffffffull);
+        if (out_v) out_v[rank] = rank_key_score(kq);
+      }
+    }
+    return;
+  }
+  unsigned long long prev = ~0ull;   // k selection rounds by this warp
+  for (int round = 0; round < k; ++round) {
+    unsigned long long bk = 0ull;
+    for (int i = lane; i < n; i += 32) {
+      const unsigned long long kk = rank_key(r[i], i);
+      if (kk < prev && kk > bk) bk = kk;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const unsigned long long t = __shfl_xor_sync(0xffffffffu, bk, o);
+      bk = t > bk ? t : bk;
+    }
+    if (lane == 0) {
+      out_i[round] = (int)(bk & 0xffffffffull);
+      if (out_v) out_v[round] = rank_key_score(bk);
+    }
+    prev = bk;
+  }
+}
+
 // Full descending ranking of one row per CTA: bitonic sort of 64-bit keys in shared memory.
 __global__ void __launch_bounds__(1024)
 sort_rows_kernel(const float* __restrict__ sim, int n, int n_pad, int64_t ld,

@@ -5,21 +5,22 @@ namespace {
 
 template <int KT, bool RELU, bool REF, bool SIMK>
 cudaError_t launch(const ModelDev& M, const TcGeom& G, int grid, size_t smem, const float* params,
-                   const __nv_bfloat16* A, const __nv_bfloat16* B, float* sim, int64_t ld, cudaStream_t st) {
+                   const __nv_bfloat16* A, const __nv_bfloat16* B, float* sim, int64_t ld, unsigned long long* smax,
+                   cudaStream_t st) {
   auto kern = allpairs_tc_kernel<KT, RELU, REF, SIMK>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  kern<<<grid, TC_THREADS, smem, st>>>(M, G, params, A, B, sim, ld);
+  kern<<<grid, TC_THREADS, smem, st>>>(M, G, params, A, B, sim, ld, smax);
   return cudaGetLastError();
 }
 
 template <int KT>
 cudaError_t dispatch(bool relu, bool ref, bool simk, const ModelDev& M, const TcGeom& G, int grid, size_t smem,
                      const float* params, const __nv_bfloat16* A, const __nv_bfloat16* B, float* sim, int64_t ld,
-                     cudaStream_t st) {
+                     unsigned long long* smax, cudaStream_t st) {
 #define SGNN_TC3(R, F)                                                              \
-  (simk ? launch<KT, R, F, true>(M, G, grid, smem, params, A, B, sim, ld, st)       \
-        : launch<KT, R, F, false>(M, G, grid, smem, params, A, B, sim, ld, st))
+  (simk ? launch<KT, R, F, true>(M, G, grid, smem, params, A, B, sim, ld, smax, st)       \
+        : launch<KT, R, F, false>(M, G, grid, smem, params, A, B, sim, ld, smax, st))
   return relu ? (ref ? SGNN_TC3(true, true) : SGNN_TC3(true, false))
               : (ref ? SGNN_TC3(false, true) : SGNN_TC3(false, false));
 #undef SGNN_TC3
@@ -27,23 +28,38 @@ cudaError_t dispatch(bool relu, bool ref, bool simk, const ModelDev& M, const Tc
 
 }  // namespace
 
-cudaError_t sgnn_tc_launch(const ModelDev& M, const TcGeom& G, bool relu, bool ref, bool simk, int grid, size_t smem,
-                           const float* params, const float* emb_q, const float* emb_db, void* A_ws, void* B_ws,
-                           float* sim, int64_t ld, cudaStream_t st) {
-  __nv_bfloat16* A = static_cast<__nv_bfloat16*>(A_ws);
-  __nv_bfloat16* B = static_cast<__nv_bfloat16*>(B_ws);
+namespace {
+cudaError_t prep_launch(const ModelDev& M, const TcGeom& G, bool q_part, const float* params, const float* emb_q,
+                        const float* emb_db, __nv_bfloat16* A, __nv_bfloat16* B, cudaStream_t st) {
   const int C = G.KCH * 8 * G.KC;
-  const int col_blocks = (C + (PREP_COLS / G.KC) * G.KC - 1) / ((PREP_COLS / G.KC) * G.KC);
-  const int q_blocks = col_blocks * ((G.m + PREP_Q - 1) / PREP_Q);
-  const int db_blocks = (G.n_gtiles * 128 * G.KCH + PREP_COLS - 1) / PREP_COLS;
+  const int cpb = (PREP_COLS / G.KC) * G.KC;
+  const int col_blocks = (C + cpb - 1) / cpb;
+  const int q_blocks = q_part ? col_blocks * ((G.m + PREP_Q - 1) / PREP_Q) : 0;
+  const int db_blocks = q_part ? 0 : (G.n_gtiles * 128 * G.KCH + PREP_COLS - 1) / PREP_COLS;
   const size_t prep_smem = ((size_t)(G.D + 1) * PREP_COLS + (size_t)G.D * PREP_Q) * sizeof(float);
   cudaError_t e = cudaFuncSetAttribute(tc_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)prep_smem);
   if (e != cudaSuccess) return e;
-  tc_prep_kernel<<<q_blocks + db_blocks, PREP_COLS, prep_smem, st>>>(M, G, q_blocks, col_blocks, params, emb_q, emb_db,
-                                                                      A, B);
-  e = cudaGetLastError();
-  if (e != cudaSuccess) return e;
-  if (G.K == 10) return dispatch<10>(relu, ref, simk, M, G, grid, smem, params, A, B, sim, ld, st);
-  if (G.K == 16) return dispatch<16>(relu, ref, simk, M, G, grid, smem, params, A, B, sim, ld, st);
-  return dispatch<0>(relu, ref, simk, M, G, grid, smem, params, A, B, sim, ld, st);
+  tc_prep_kernel<<<q_blocks + db_blocks, PREP_COLS, q_part ? prep_smem : 0, st>>>(M, G, q_blocks, col_blocks, params,
+                                                                                  emb_q, emb_db, A, B);
+  return cudaGetLastError();
+}
+}  // namespace
+
+cudaError_t sgnn_tc_prep_q(const ModelDev& M, const TcGeom& G, const float* params, const float* emb_q, void* B_ws,
+                           cudaStream_t st) {
+  return prep_launch(M, G, true, params, emb_q, nullptr, nullptr, static_cast<__nv_bfloat16*>(B_ws), st);
+}
+
+cudaError_t sgnn_tc_prep_db(const ModelDev& M, const TcGeom& G, const float* emb_db, void* A_ws, cudaStream_t st) {
+  return prep_launch(M, G, false, nullptr, nullptr, emb_db, static_cast<__nv_bfloat16*>(A_ws), nullptr, st);
+}
+
+cudaError_t sgnn_tc_score(const ModelDev& M, const TcGeom& G, bool relu, bool ref, bool simk, int grid, size_t smem,
+                          const float* params, const void* A_ws, const void* B_ws, float* sim, int64_t ld,
+                          unsigned long long* smax, cudaStream_t st) {
+  const __nv_bfloat16* A = static_cast<const __nv_bfloat16*>(A_ws);
+  const __nv_bfloat16* B = static_cast<const __nv_bfloat16*>(B_ws);
+  if (G.K == 10) return dispatch<10>(relu, ref, simk, M, G, grid, smem, params, A, B, sim, ld, smax, st);
+  if (G.K == 16) return dispatch<16>(relu, ref, simk, M, G, grid, smem, params, A, B, sim, ld, smax, st);
+  return dispatch<0>(relu, ref, simk, M, G, grid, smem, params, A, B, sim, ld, smax, st);
 }

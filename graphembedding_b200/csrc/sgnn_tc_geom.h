@@ -33,7 +33,15 @@ __host__ __device__ inline int tc_a_bytes(const TcGeom& G) { return G.parts * G.
 __host__ __device__ inline int tc_b_bytes(const TcGeom& G) { return G.parts * G.KCH * TC_NPAD * 16; }
 constexpr int TC_TAIL_BYTES = (1 + 2 * TC_MAX_STAGES + 2 * TC_BUFS) * 8 + 16 + 4 * 64;   // barriers, TMEM slot, U
 
-// prep kernels + allpairs_tc_kernel on `st` (defined in sgnn_tc.cu)
-cudaError_t sgnn_tc_launch(const ModelDev& M, const TcGeom& G, bool relu, bool ref, bool simk, int grid, size_t smem,
-                           const float* params, const float* emb_q, const float* emb_db, void* A_ws, void* B_ws,
-                           float* sim, int64_t ld, cudaStream_t st);
+// The three stages of the tensor-core scorer (defined in sgnn_tc.cu).  The query-side operand
+// (B_ws: the per-query NTN tables, bf16 hi/lo) depends only on the query embeddings and the
+// database-side operand (A_ws) only on the database embeddings, so a caller may prepare them on
+// different streams; sgnn_tc_score needs both.
+cudaError_t sgnn_tc_prep_q(const ModelDev& M, const TcGeom& G, const float* params, const float* emb_q, void* B_ws,
+                           cudaStream_t st);
+cudaError_t sgnn_tc_prep_db(const ModelDev& M, const TcGeom& G, const float* emb_db, void* A_ws, cudaStream_t st);
+cudaError_t sgnn_tc_score(const ModelDev& M, const TcGeom& G, bool relu, bool ref, bool simk, int grid, size_t smem,
+                          const float* params, const void* A_ws, const void* B_ws, float* sim, int64_t ld,
+                          unsigned long long* smax, cudaStream_t st);
+// smax (optional): [m][4 * n_gtiles] largest rank key of every 32-graph slice of every sim row (sgnn_launch_topk_hint)
+inline int tc_n_slices(int n) { return ((n + 127) / 128) * 4; }

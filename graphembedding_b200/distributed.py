@@ -77,10 +77,7 @@ def sharded_rank(engine, queries_dev, db_shard_dev, id_offset, k, dist=None, gro
                  emb_db=None, sim=None):
     """One database-sharded ranking step on this rank: embed, score the local tile, local top-k,
     all-gather, merge.  Returns (ids, vals) of the global top-k (identical on every rank)."""
-    emb_q = engine.embed(queries_dev, out=emb_q)
-    emb_db = engine.embed(db_shard_dev, out=emb_db)
-    sim = engine.score_all_pairs(emb_q, emb_db, out=sim)
-    ids, vals = engine.topk(sim, k)
+    ids, vals, sim = engine.rank_device(queries_dev, db_shard_dev, k, emb_q=emb_q, emb_db=emb_db, sim=sim)
     world = dist.get_world_size(group) if dist is not None and dist.is_initialized() else 1
     if world == 1 and id_offset == 0:
         return ids, vals

@@ -28,6 +28,7 @@ class SgnnEngine(object):
         if rc != 0:
             raise native.SgnnError(lib().sgnn_last_error(None).decode())
         self.h = h
+        self.precision = 'fp32' if self.cfg.precision == 0 else 'tc'   # SGNN_PREC_FP32 / tensor-core scorer
         self.n_params = int(lib().sgnn_param_count(h))
         self.emb_dim = int(lib().sgnn_embed_dim(h))
         self.launches = 0  # kernels launched through this object (bench.py's gpu_launches)
@@ -135,7 +136,7 @@ class SgnnEngine(object):
             out = torch.empty((m, n), dtype=torch.float32, device=self.device)
         check(self.h, lib().sgnn_score_all_pairs(self.h, _ptr(emb_q), m, _ptr(emb_db), n, _ptr(out),
                                                  out.stride(0), _stream_ptr(stream)))
-        self.launches += 2
+        self.launches += 2 if self.precision == 'fp32' else 3   # operand prep (query / database side) + scorer
         return out
 
     def topk(self, sim, k, stream=None):
@@ -253,6 +254,24 @@ class SgnnEngine(object):
         self.launches += 2
         return raw, sim
 
+    def rank_device(self, queries, db, k, emb_q=None, emb_db=None, sim=None, ids=None, vals=None, stream=None):
+        """The whole ranking step on device-resident batches (sgnn_rank_device): the query branch
+        overlaps the database branch.  Returns (ids, vals, sim)."""
+        import torch
+        m, n, E = queries.n_graphs, db.n_graphs, self.emb_dim
+        dev = self.device
+        emb_q = torch.empty((m, E), dtype=torch.float32, device=dev) if emb_q is None else emb_q
+        emb_db = torch.empty((n, E), dtype=torch.float32, device=dev) if emb_db is None else emb_db
+        sim = torch.empty((m, n), dtype=torch.float32, device=dev) if sim is None else sim
+        if k > 0:
+            ids = torch.empty((m, k), dtype=torch.int32, device=dev) if ids is None else ids
+            vals = torch.empty((m, k), dtype=torch.float32, device=dev) if vals is None else vals
+        sq, sd = queries.struct(), db.struct()
+        check(self.h, lib().sgnn_rank_device(self.h, C.byref(sq), C.byref(sd), int(k), _ptr(emb_q), _ptr(emb_db),
+                                             _ptr(sim), sim.stride(0), _ptr(ids), _ptr(vals), _stream_ptr(stream)))
+        self.launches += 6 if k > 0 else 5   # 2 embeds, 2 operand preps, scorer, top-k
+        return ids, vals, sim
+
     def rank_host(self, queries, db, k, ids=None, vals=None, sim=None):
         m = queries.n_graphs
         ids = np.empty((m, k), np.int32) if ids is None else ids
@@ -260,7 +279,7 @@ class SgnnEngine(object):
         sq, sd = queries.struct(), db.struct()
         check(self.h, lib().sgnn_rank_host(self.h, C.byref(sq), C.byref(sd), k, _ptr(ids), _ptr(vals),
                                            _ptr(sim)))
-        self.launches += 5   # embed(queries) + embed(database) + operand prep + scorer + top-k
+        self.launches += 6   # embed(queries) + embed(database) + 2 operand preps + scorer + top-k
         return ids, vals
 
     def train_step_host(self, batch, g1, g2, target_sim, loss=None):

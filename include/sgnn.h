@@ -214,6 +214,19 @@ int sgnn_kendall_tau(SgnnHandle h, const float* true_sim_dev, const float* pred_
  * inside).  These are the `e2e` path of bench.py. ---------------------------------------- */
 int sgnn_forward_pairs_host(SgnnHandle h, const SgnnGraphBatch* batch_host, const int32_t* g1,
                             const int32_t* g2, int32_t n_pairs, float* raw_host, float* sim_host);
+/* The whole ranking step on DEVICE-resident batches (what test() + Result do per model,
+ * train.py:99-127): embeds queries and database, scores all pairs into sim_dev [m][ld], and (k > 0,
+ * topk_ids_dev != NULL) selects the top-k.  Same result as sgnn_embed_graphs x2 + sgnn_score_all_pairs +
+ * sgnn_topk on one stream; the query branch (embedding + query-side scorer tables) runs on an internal
+ * stream beside the database branch and joins before the scorer.  Every output is complete in
+ * `stream` order. */
+int sgnn_rank_device(SgnnHandle h, const SgnnGraphBatch* q_dev, const SgnnGraphBatch* db_dev, int32_t k,
+                     float* emb_q_dev, float* emb_db_dev, float* sim_dev, int64_t ld, int32_t* topk_ids_dev,
+                     float* topk_vals_dev, void* stream);
+/* Test hook: the slice-maximum hints the tensor-core scorer left for the top-k kernel during the last
+ * sgnn_rank_device / sgnn_rank_host call ([m][4 * ceil(n / 128)] 64-bit rank keys: orderable score << 32 |
+ * database id of the largest element of every 32-column slice of sim). */
+int sgnn_debug_slice_hints(SgnnHandle h, unsigned long long** hints_dev, int64_t* capacity);
 /* embeds queries + database, scores all pairs, returns top-k ids/values per query; the
  * full m x n matrix is copied back only if sim_host != NULL. */
 int sgnn_rank_host(SgnnHandle h, const SgnnGraphBatch* queries_host, const SgnnGraphBatch* db_host,

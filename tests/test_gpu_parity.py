@@ -390,3 +390,60 @@ def test_node_embeddings_and_pair_histogram_match_oracle(n_lo, n_hi, bins):
         else:
             assert np.abs(counts[p] - rc).sum() <= 2 * int(edge.sum())
         assert np.max(np.abs(hist[p] - counts[p] / float(s.size))) < 1e-6
+
+
+@pytest.mark.parametrize('precision', ['fp32', 'bf16x3'])
+def test_rank_device_equals_the_separate_calls(precision):
+    """sgnn_rank_device forks the query branch onto an internal stream; outputs must be bit-identical
+    to embed + embed + score_all_pairs + topk issued on one stream."""
+    from graphembedding_b200.graphs import pack_nx_graphs
+    from graphembedding_b200.engine import SgnnEngine
+    from graphembedding_b200.layers_factory import parse_layers
+    gs = corpus(700, 2, 10, seed=41)
+    enc = encoder_for(gs)
+    layers = parse_layers(CONFIGS['default'], enc.input_dim())
+    eng = SgnnEngine(layers, enc.input_dim(), precision=precision)
+    eng.init_params(7)
+    q, db = pack_nx_graphs(gs[:150], enc), pack_nx_graphs(gs[150:], enc)
+    eng.reserve(max_graphs=len(gs), max_nodes=db.total_nodes, max_nnz=db.nnz, max_queries=150, max_db=550)
+    qd, dbd = q.to(eng.device), db.to(eng.device)
+    sim_ref = eng.score_all_pairs(eng.embed(qd), eng.embed(dbd))
+    ids_ref, vals_ref = eng.topk(sim_ref, 10)
+    for _ in range(3):      # repeated: the fork/join events are reused
+        ids, vals, sim = eng.rank_device(qd, dbd, 10)
+        assert torch.equal(sim, sim_ref) and torch.equal(ids, ids_ref) and torch.equal(vals, vals_ref)
+    _, _, sim0 = eng.rank_device(qd, dbd, 0)
+    assert torch.equal(sim0, sim_ref)
+
+
+@pytest.mark.parametrize('kind', ['random', 'duplicates', 'all_equal'])
+def test_hinted_topk_in_rank_device_matches_plain_topk(kind):
+    """Rows of >= 8192 scores: the tensor-core scorer emits 32-column slice maxima and the top-k
+    kernel reads those hints.  Ids/values must equal sgnn_topk on the same sim matrix (reference
+    tie order, results.py:221-224), including databases full of exact ties (fallback path)."""
+    from graphembedding_b200.graphs import pack_nx_graphs
+    from graphembedding_b200.engine import SgnnEngine
+    from graphembedding_b200.layers_factory import parse_layers
+    n_db = 8300
+    base = corpus(400, 2, 10, seed=51)
+    enc = encoder_for(base)
+    if kind == 'random':
+        dbg = corpus(n_db, 2, 10, seed=52)
+        enc = encoder_for(base + dbg)
+    elif kind == 'duplicates':
+        dbg = [base[i % 300] for i in range(n_db)]
+    else:
+        dbg = [base[0]] * n_db
+    layers = parse_layers(CONFIGS['default'], enc.input_dim())
+    eng = SgnnEngine(layers, enc.input_dim(), precision='bf16x3')
+    eng.init_params(11)
+    q, db = pack_nx_graphs(base[300:345], enc), pack_nx_graphs(dbg, enc)
+    eng.reserve(max_graphs=n_db, max_nodes=db.total_nodes, max_nnz=db.nnz, max_queries=45, max_db=n_db)
+    qd, dbd = q.to(eng.device), db.to(eng.device)
+    for k in (1, 10, 100):
+        ids, vals, sim = eng.rank_device(qd, dbd, k)
+        ids_ref, vals_ref = eng.topk(sim, k)
+        assert torch.equal(ids, ids_ref) and torch.equal(vals, vals_ref), (kind, k)
+    # and the host entry point
+    ids_h, vals_h = eng.rank_host(q, db, 10)
+    assert np.array_equal(ids_h, eng.topk(sim, 10)[0].cpu().numpy())

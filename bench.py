@@ -266,6 +266,9 @@ def run_cuda(args):
         raise SystemExit('bench.py: no CUDA device (the product path has no CPU fallback)')
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
+    # a real (non-legacy) stream: sgnn_rank_device replays its step as a CUDA graph, and stream
+    # capture is not allowed on the legacy default stream
+    torch.cuda.set_stream(torch.cuda.Stream())
     if world > 1:
         if os.environ.get('NCCL_DEBUG', 'VERSION').upper() == 'VERSION':
             os.environ['NCCL_DEBUG'] = 'WARN'    # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
@@ -296,9 +299,24 @@ def run_cuda(args):
 
     from graphembedding_b200 import distributed as DS
 
-    def step():   # database sharded over ranks: local top-k, all-gather of the candidates, merge (global ids)
+    # database sharded over ranks: local top-k, candidate exchange over NVLink peer memory (fallback: NCCL
+    # all-gather + merge kernel), global ids
+    peer, exchange = None, 'none (1 GPU)'
+    if world > 1:
+        try:
+            peer, exchange = DS.PeerTopk(eng, M_QUERIES, TOPK, dist), 'p2p push + merge kernels (CUDA IPC peer memory)'
+        except Exception as e:   # no peer access between the GPUs: library collective
+            sys.stderr.write('bench.py: peer exchange unavailable (%s); using NCCL all-gather\n' % e)
+            exchange = 'nccl all-gather + merge kernel'
+        flag = torch.tensor([1 if peer is not None else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 0 and peer is not None:
+            peer.close()
+            peer, exchange = None, 'nccl all-gather + merge kernel'
+
+    def step():
         out['ids'], out['vals'] = DS.sharded_rank(eng, qd, dbd, rank * N_DB, TOPK, dist if world > 1 else None,
-                                                  emb_q=emb_q, emb_db=emb_db, sim=sim)
+                                                  emb_q=emb_q, emb_db=emb_db, sim=sim, peer=peer)
 
     clocks = ClockSampler(local)
     clocks.start()
@@ -358,10 +376,14 @@ def run_cuda(args):
         assert torch.equal(ids_h.to(dev), out['ids']), 'host entry point and device path disagree'
     e2e = {'value': M_QUERIES * N_DB * world / (e2e_ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': e2e_ms,
            'h2d_bytes_per_step': q.nbytes() + db.nbytes(), 'd2h_bytes_per_step': 2 * 4 * M_QUERIES * TOPK}
+    if world > 1:
+        e2e['note'] = 'per-rank sgnn_rank_host on its own shard (host in, local top-k out); the cross-rank merge is in value'
 
     train = run_train(torch, dist, dev, rank, world, local, args, barrier, max_over_ranks)
 
     if world > 1:
+        if peer is not None:
+            peer.close()
         dist.barrier()
         dist.destroy_process_group()
     if rank != 0:
@@ -370,8 +392,8 @@ def run_cuda(args):
             'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms_per_step,
             'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
             'dtype': 'f32' if args.precision == 'fp32' else args.precision, 'data': 'synthetic',
-            'config': workload_config(), 'clocks': clk, 'e2e': e2e, 'gpu_launches': launches,
-            'roofline': roofline, 'train': train}
+            'config': dict(workload_config(), exchange=exchange), 'clocks': clk, 'e2e': e2e,
+            'gpu_launches': launches, 'roofline': roofline, 'train': train}
     if world == 1 and not args.no_cpu_baseline:
         v, cores, sample = cpu_rank_baseline(DEFAULT_LAYERS, q, db)
         line['cpu_baseline'] = {'value': v, 'unit': 'pairs/s', 'cores': cores, 'kind': 'port', 'sample': sample,

@@ -97,12 +97,15 @@ tc_prep_kernel(const __grid_constant__ ModelDev M, const TcGeom G, int q_blocks,
     xs[i] = q0 + qq < G.m ? emb_q[(size_t)(q0 + qq) * D + a] : 0.f;
   }
   __syncthreads();
-  if (on && k == K) {   // the sum column: its K source columns sit just left of it in shared memory
-    for (int a = 0; a <= D; ++a) {
-      float v = 0.f;
-      for (int kq = 0; kq < K; ++kq)
-        v = fmaf(ref ? 1.f : params[M.u_off + kq], Wm[a * PREP_COLS + threadIdx.x - K + kq], v);
-      Wm[a * PREP_COLS + threadIdx.x] = v;
+  if (KC > K) {   // the sum columns: one (coefficient row a, column group) per thread, K-term sums in parallel
+    const int groups = cpb / KC;
+    for (int t = threadIdx.x; t < (D + 1) * groups; t += blockDim.x) {
+      const int a = t / groups, col = (t - a * groups) * KC;
+      if (cb * cpb + col + K < C) {
+        float v = 0.f;
+        for (int kq = 0; kq < K; ++kq) v = fmaf(ref ? 1.f : params[M.u_off + kq], Wm[a * PREP_COLS + col + kq], v);
+        Wm[a * PREP_COLS + col + K] = v;
+      }
     }
   }
   __syncthreads();

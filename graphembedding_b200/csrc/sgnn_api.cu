@@ -31,8 +31,30 @@ struct HostWs {  // device staging for the *_host entry points (sized by sgnn_re
 
 }  // namespace
 
+// A ranking step is six dependent-ish kernel launches of 3..30 us each plus two copies: replayed
+// as one CUDA graph, the launch gaps and the per-call driver work disappear.  A slot remembers the
+// arguments of the last call; the second call with the same arguments captures the stream work,
+// later ones replay it.  Any sgnn_reserve (workspaces may move) drops the graphs.
+struct GraphSlot {
+  uint64_t key = 0;
+  bool seen = false;
+  cudaGraphExec_t exec = nullptr;
+  void drop() {
+    if (exec) cudaGraphExecDestroy(exec);
+    exec = nullptr; seen = false; key = 0;
+  }
+};
+
 struct SgnnHandle_t {
   SgnnConfig cfg;
+  // peer-memory top-k exchange (sgnn_peer.cuh): own buffer + the peers' buffers opened through CUDA IPC
+  int peer_world = 0, peer_rank = 0;
+  int64_t peer_slot_elems = 0;
+  unsigned long long peer_epoch = 0;
+  void* peer_bufs[16] = {};
+  unsigned int* peer_done = nullptr;
+  bool use_graphs = true;               // SGNN_NO_GRAPHS=1 or a failed capture turns replay off
+  GraphSlot g_rank_device, g_rank_host;
   ModelDev M;
   int device = 0, sm_count = 148, smem_optin = 0;
   std::string err;
@@ -341,6 +363,62 @@ int score_all_pairs_stages(SgnnHandle h, const float* emb_q, int32_t m, const fl
 }
 }  // namespace
 
+namespace {
+uint64_t fnv1a(const void* data, size_t bytes) {
+  const uint8_t* p = static_cast<const uint8_t*>(data);
+  uint64_t x = 1469598103934665603ull;
+  for (size_t i = 0; i < bytes; ++i) x = (x ^ p[i]) * 1099511628211ull;
+  return x ? x : 1;
+}
+
+void key_batch(uint64_t* k, const SgnnGraphBatch* b) {
+  k[0] = (uint64_t)(uintptr_t)b->node_off; k[1] = (uint64_t)(uintptr_t)b->labels;
+  k[2] = (uint64_t)(uintptr_t)b->rowptr;   k[3] = (uint64_t)(uintptr_t)b->col;
+  k[4] = (uint64_t)(uintptr_t)b->val;
+  k[5] = ((uint64_t)(uint32_t)b->n_graphs << 32) | (uint32_t)b->max_nodes;
+  k[6] = ((uint64_t)(uint32_t)b->total_nodes << 32) | (uint32_t)b->nnz;
+}
+
+// run `body` (stream work only, starting and ending on `st`) eagerly, or capture / replay it
+template <typename F>
+int run_cached(SgnnHandle h, GraphSlot& slot, uint64_t key, cudaStream_t st, F body) {
+  if (!h->use_graphs || st == nullptr || st == cudaStreamLegacy) return body();
+  if (slot.exec && slot.key == key) {
+    CUDA_OK(h, cudaGraphLaunch(slot.exec, st));
+    return 0;
+  }
+  if (!(slot.seen && slot.key == key)) {   // first sighting of these arguments: run eagerly
+    slot.drop();
+    slot.key = key; slot.seen = true;
+    return body();
+  }
+  if (cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+    cudaGetLastError();
+    h->use_graphs = false;
+    return body();
+  }
+  const int rc = body();
+  cudaGraph_t g = nullptr;
+  const cudaError_t e = cudaStreamEndCapture(st, &g);
+  if (rc != 0 || e != cudaSuccess || g == nullptr) {
+    if (g) cudaGraphDestroy(g);
+    cudaGetLastError();
+    h->use_graphs = false;
+    return rc != 0 ? rc : body();
+  }
+  const cudaError_t e2 = cudaGraphInstantiate(&slot.exec, g, 0);
+  cudaGraphDestroy(g);
+  if (e2 != cudaSuccess) {
+    cudaGetLastError();
+    slot.exec = nullptr;
+    h->use_graphs = false;
+    return body();
+  }
+  CUDA_OK(h, cudaGraphLaunch(slot.exec, st));
+  return 0;
+}
+}  // namespace
+
 extern "C" {
 
 int sgnn_abi_version(void) { return SGNN_ABI_VERSION; }
@@ -362,6 +440,7 @@ int sgnn_create(const SgnnConfig* cfg, SgnnHandle* out) {
                              cudaGetErrorString(e) + ")");
   }
   h->device = cfg->device;
+  if (const char* ng = getenv("SGNN_NO_GRAPHS")) h->use_graphs = !(ng[0] && ng[0] != '0');
   if (cudaSetDevice(h->device) != cudaSuccess) { delete h; return fail(nullptr, "cudaSetDevice failed"); }
   cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, h->device);
   cudaDeviceGetAttribute(&h->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device);
@@ -404,6 +483,9 @@ int sgnn_destroy(SgnnHandle h) {
   cudaFree(w.g1); cudaFree(w.g2); cudaFree(w.target); cudaFree(w.raw); cudaFree(w.sim_pairs); cudaFree(w.emb);
   cudaFree(w.emb_q); cudaFree(w.emb_db); cudaFree(w.sim); cudaFree(w.topk_vals); cudaFree(w.topk_ids);
   if (h->stream) cudaStreamDestroy(h->stream);
+  h->g_rank_device.drop();
+  h->g_rank_host.drop();
+  sgnn_peer_destroy(h);
   if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
   for (auto& ev : h->chunk_ev) if (ev) cudaEventDestroy(ev);
   delete h;
@@ -471,6 +553,8 @@ int sgnn_reserve(SgnnHandle h, int64_t max_graphs, int64_t max_nodes, int64_t ma
   if (!h) return 1;
   CUDA_OK(h, cudaSetDevice(h->device));
   CUDA_OK(h, cudaDeviceSynchronize());
+  h->g_rank_device.drop();
+  h->g_rank_host.drop();
   HostWs& w = h->ws;
   const int E = h->M.emb_dim;
   if (max_graphs > w.cap_graphs || max_nodes > w.cap_nodes || max_nnz > w.cap_nnz) {
@@ -816,16 +900,90 @@ int sgnn_rank_device(SgnnHandle h, const SgnnGraphBatch* q_dev, const SgnnGraphB
   const int m = q_dev->n_graphs, n = db_dev->n_graphs;
   if (m == 0 || n == 0) return 0;
   cudaStream_t st = (cudaStream_t)stream, side = h->copy_stream;
-  // fork: the query branch (embed + query-side scorer tables) runs beside the database branch
-  CUDA_OK(h, cudaEventRecord(h->chunk_ev[1], st));
-  CUDA_OK(h, cudaStreamWaitEvent(side, h->chunk_ev[1], 0));
-  if (sgnn_embed_graphs(h, q_dev, emb_q_dev, side)) return 1;
-  if (score_all_pairs_stages(h, emb_q_dev, m, emb_db_dev, n, sim_dev, ld, side, SCORE_PREP_Q)) return 1;
-  CUDA_OK(h, cudaEventRecord(h->chunk_ev[2], side));
-  if (sgnn_embed_graphs(h, db_dev, emb_db_dev, st)) return 1;
-  if (score_all_pairs_stages(h, emb_q_dev, m, emb_db_dev, n, sim_dev, ld, st, SCORE_PREP_DB)) return 1;
-  CUDA_OK(h, cudaStreamWaitEvent(st, h->chunk_ev[2], 0));   // join
-  return score_and_topk(h, emb_q_dev, m, emb_db_dev, n, sim_dev, ld, SCORE_MAIN, k, topk_ids_dev, topk_vals_dev, st);
+  auto body = [&]() -> int {
+    // fork: the query branch (embed + query-side scorer tables) runs beside the database branch
+    CUDA_OK(h, cudaEventRecord(h->chunk_ev[1], st));
+    if (sgnn_embed_graphs(h, db_dev, emb_db_dev, st)) return 1;
+    if (score_all_pairs_stages(h, emb_q_dev, m, emb_db_dev, n, sim_dev, ld, st, SCORE_PREP_DB)) return 1;
+    CUDA_OK(h, cudaStreamWaitEvent(side, h->chunk_ev[1], 0));
+    if (sgnn_embed_graphs(h, q_dev, emb_q_dev, side)) return 1;
+    if (score_all_pairs_stages(h, emb_q_dev, m, emb_db_dev, n, sim_dev, ld, side, SCORE_PREP_Q)) return 1;
+    CUDA_OK(h, cudaEventRecord(h->chunk_ev[2], side));
+    CUDA_OK(h, cudaStreamWaitEvent(st, h->chunk_ev[2], 0));   // join
+    return score_and_topk(h, emb_q_dev, m, emb_db_dev, n, sim_dev, ld, SCORE_MAIN, k, topk_ids_dev, topk_vals_dev,
+                          st);
+  };
+  uint64_t kb[22] = {};
+  key_batch(kb, q_dev);
+  key_batch(kb + 7, db_dev);
+  kb[14] = (uint64_t)k; kb[15] = (uint64_t)(uintptr_t)emb_q_dev; kb[16] = (uint64_t)(uintptr_t)emb_db_dev;
+  kb[17] = (uint64_t)(uintptr_t)sim_dev; kb[18] = (uint64_t)ld; kb[19] = (uint64_t)(uintptr_t)topk_ids_dev;
+  kb[20] = (uint64_t)(uintptr_t)topk_vals_dev; kb[21] = (uint64_t)(uintptr_t)st;
+  return run_cached(h, h->g_rank_device, fnv1a(kb, sizeof(kb)), st, body);
+}
+
+int sgnn_peer_destroy(SgnnHandle h) {
+  if (!h) return 1;
+  cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
+  for (int r = 0; r < h->peer_world; ++r) {
+    if (!h->peer_bufs[r]) continue;
+    if (r == h->peer_rank) cudaFree(h->peer_bufs[r]);
+    else cudaIpcCloseMemHandle(h->peer_bufs[r]);
+    h->peer_bufs[r] = nullptr;
+  }
+  if (h->peer_done) cudaFree(h->peer_done);
+  h->peer_done = nullptr;
+  h->peer_world = 0;
+  return 0;
+}
+
+int sgnn_peer_create(SgnnHandle h, int32_t world, int32_t rank, int32_t m_cap, int32_t k_cap, uint8_t* ipc_handle_out) {
+  if (!h || !ipc_handle_out) return fail(h, "sgnn_peer_create: null argument");
+  if (world < 1 || world > 16 || rank < 0 || rank >= world) return fail(h, "sgnn_peer_create: bad world / rank");
+  static_assert(sizeof(cudaIpcMemHandle_t) == SGNN_IPC_HANDLE_BYTES, "IPC handle size");
+  CUDA_OK(h, cudaSetDevice(h->device));
+  sgnn_peer_destroy(h);
+  h->peer_world = world; h->peer_rank = rank; h->peer_epoch = 0;
+  h->peer_slot_elems = (int64_t)m_cap * k_cap;
+  const int64_t bytes = sgnn_peer_buffer_bytes(world, h->peer_slot_elems);
+  CUDA_OK(h, cudaMalloc(&h->peer_bufs[rank], (size_t)bytes));
+  CUDA_OK(h, cudaMemset(h->peer_bufs[rank], 0, (size_t)bytes));
+  CUDA_OK(h, cudaMalloc(reinterpret_cast<void**>(&h->peer_done), sizeof(unsigned int)));
+  CUDA_OK(h, cudaMemset(h->peer_done, 0, sizeof(unsigned int)));
+  CUDA_OK(h, cudaDeviceSynchronize());
+  cudaIpcMemHandle_t hd;
+  CUDA_OK(h, cudaIpcGetMemHandle(&hd, h->peer_bufs[rank]));
+  memcpy(ipc_handle_out, &hd, sizeof(hd));
+  return 0;
+}
+
+int sgnn_peer_connect(SgnnHandle h, const uint8_t* all_handles) {
+  if (!h || !all_handles) return fail(h, "sgnn_peer_connect: null argument");
+  if (h->peer_world == 0) return fail(h, "sgnn_peer_connect: call sgnn_peer_create first");
+  CUDA_OK(h, cudaSetDevice(h->device));
+  for (int r = 0; r < h->peer_world; ++r) {
+    if (r == h->peer_rank) continue;
+    cudaIpcMemHandle_t hd;
+    memcpy(&hd, all_handles + (size_t)r * SGNN_IPC_HANDLE_BYTES, sizeof(hd));
+    CUDA_OK(h, cudaIpcOpenMemHandle(&h->peer_bufs[r], hd, cudaIpcMemLazyEnablePeerAccess));
+  }
+  return 0;
+}
+
+int sgnn_topk_exchange(SgnnHandle h, const float* vals_dev, const int32_t* ids_dev, int32_t m, int32_t k,
+                       int32_t id_offset, int32_t* out_ids_dev, float* out_vals_dev, void* stream) {
+  if (!h || !vals_dev || !ids_dev || !out_ids_dev) return fail(h, "sgnn_topk_exchange: null argument");
+  if (h->peer_world == 0) return fail(h, "sgnn_topk_exchange: no peer exchange set up (sgnn_peer_create/connect)");
+  for (int r = 0; r < h->peer_world; ++r)
+    if (!h->peer_bufs[r]) return fail(h, "sgnn_topk_exchange: peers not connected");
+  if ((int64_t)m * k > h->peer_slot_elems) return fail(h, "sgnn_topk_exchange: m * k exceeds the exchange slot");
+  h->peer_epoch += 1;
+  const cudaError_t e = sgnn_launch_peer_exchange(vals_dev, ids_dev, m, k, id_offset, h->peer_rank, h->peer_world,
+                                                  h->peer_slot_elems, h->peer_bufs, h->peer_epoch, h->peer_done,
+                                                  out_ids_dev, out_vals_dev, (cudaStream_t)stream);
+  if (e != cudaSuccess) return fail(h, std::string("sgnn_topk_exchange: ") + cudaGetErrorString(e));
+  return 0;
 }
 
 int sgnn_debug_slice_hints(SgnnHandle h, unsigned long long** hints_dev, int64_t* capacity) {
@@ -844,27 +1002,38 @@ int sgnn_rank_host(SgnnHandle h, const SgnnGraphBatch* q, const SgnnGraphBatch* 
   if (m * n > w.cap_q * w.cap_db || m > w.cap_q || (int64_t)m * k > w.cap_topk)
     return fail(h, "host workspace too small: call sgnn_reserve first");
   cudaStream_t st = h->stream, cs = h->copy_stream;
-  // the database upload (8 bytes per non-zero over PCIe) runs on the copy stream while the compute
-  // stream uploads and embeds the queries
-  SgnnGraphBatch dq, ddb;
-  if (upload_batch_on(h, db, 1, &ddb, cs)) return 1;
-  CUDA_OK(h, cudaEventRecord(h->chunk_ev[0], cs));
-  if (upload_batch_on(h, q, 0, &dq, st)) return 1;
-  if (sgnn_embed_graphs(h, &dq, w.emb_q, st)) return 1;
-  // query-side tables of the scorer are ready before the database lands
-  if (score_all_pairs_stages(h, w.emb_q, (int)m, w.emb_db, (int)n, w.sim, n, st, SCORE_PREP_Q)) return 1;
-  CUDA_OK(h, cudaStreamWaitEvent(st, h->chunk_ev[0], 0));
-  if (sgnn_embed_graphs(h, &ddb, w.emb_db, st)) return 1;
   const bool want_topk = k > 0 && topk_ids_host;
-  if (score_and_topk(h, w.emb_q, (int)m, w.emb_db, (int)n, w.sim, n, SCORE_PREP_DB | SCORE_MAIN, want_topk ? k : 0,
-                     w.topk_ids, w.topk_vals, st))
-    return 1;
-  if (want_topk) {
-    CUDA_OK(h, cudaMemcpyAsync(topk_ids_host, w.topk_ids, (size_t)m * k * 4, cudaMemcpyDeviceToHost, st));
-    if (topk_vals_host)
-      CUDA_OK(h, cudaMemcpyAsync(topk_vals_host, w.topk_vals, (size_t)m * k * 4, cudaMemcpyDeviceToHost, st));
-  }
-  if (sim_host) CUDA_OK(h, cudaMemcpyAsync(sim_host, w.sim, (size_t)m * n * 4, cudaMemcpyDeviceToHost, st));
+  auto body = [&]() -> int {
+    // the database upload (8 bytes per non-zero over PCIe) runs on the copy stream while the compute
+    // stream uploads and embeds the queries
+    SgnnGraphBatch dq, ddb;
+    CUDA_OK(h, cudaEventRecord(h->chunk_ev[3], st));
+    CUDA_OK(h, cudaStreamWaitEvent(cs, h->chunk_ev[3], 0));
+    if (upload_batch_on(h, db, 1, &ddb, cs)) return 1;
+    CUDA_OK(h, cudaEventRecord(h->chunk_ev[0], cs));
+    if (upload_batch_on(h, q, 0, &dq, st)) return 1;
+    if (sgnn_embed_graphs(h, &dq, w.emb_q, st)) return 1;
+    // query-side tables of the scorer are ready before the database lands
+    if (score_all_pairs_stages(h, w.emb_q, (int)m, w.emb_db, (int)n, w.sim, n, st, SCORE_PREP_Q)) return 1;
+    CUDA_OK(h, cudaStreamWaitEvent(st, h->chunk_ev[0], 0));
+    if (sgnn_embed_graphs(h, &ddb, w.emb_db, st)) return 1;
+    if (score_and_topk(h, w.emb_q, (int)m, w.emb_db, (int)n, w.sim, n, SCORE_PREP_DB | SCORE_MAIN,
+                       want_topk ? k : 0, w.topk_ids, w.topk_vals, st))
+      return 1;
+    if (want_topk) {
+      CUDA_OK(h, cudaMemcpyAsync(topk_ids_host, w.topk_ids, (size_t)m * k * 4, cudaMemcpyDeviceToHost, st));
+      if (topk_vals_host)
+        CUDA_OK(h, cudaMemcpyAsync(topk_vals_host, w.topk_vals, (size_t)m * k * 4, cudaMemcpyDeviceToHost, st));
+    }
+    if (sim_host) CUDA_OK(h, cudaMemcpyAsync(sim_host, w.sim, (size_t)m * n * 4, cudaMemcpyDeviceToHost, st));
+    return 0;
+  };
+  uint64_t kb[18] = {};
+  key_batch(kb, q);
+  key_batch(kb + 7, db);
+  kb[14] = (uint64_t)k; kb[15] = (uint64_t)(uintptr_t)topk_ids_host; kb[16] = (uint64_t)(uintptr_t)topk_vals_host;
+  kb[17] = (uint64_t)(uintptr_t)sim_host;
+  if (run_cached(h, h->g_rank_host, fnv1a(kb, sizeof(kb)), st, body)) return 1;
   CUDA_OK(h, cudaStreamSynchronize(st));
   return 0;
 }

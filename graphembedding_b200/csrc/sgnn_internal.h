@@ -11,6 +11,12 @@ cudaError_t sgnn_launch_topk(const float* sim, const int32_t* col_ids, int m, in
 // top-k from slice-maximum hints (smax [m][n_slices], 32 columns per slice) written by the tensor-core scorer
 cudaError_t sgnn_launch_topk_hint(const float* sim, const unsigned long long* smax, int n_slices, int m, int n, int64_t ld, int k,
                                   int32_t* ids, float* vals, cudaStream_t st);
+// push the local top-k into every peer's exchange buffer, then merge the world * k candidates (sgnn_peer.cuh)
+cudaError_t sgnn_launch_peer_exchange(const float* vals, const int32_t* ids, int m, int k, int id_offset, int rank,
+                                      int world, int64_t slot_elems, void* const* peer_bufs,
+                                      unsigned long long epoch, unsigned int* done_counter, int32_t* out_ids,
+                                      float* out_vals, cudaStream_t st);
+int64_t sgnn_peer_buffer_bytes(int world, int64_t slot_elems);
 cudaError_t sgnn_launch_sort_rows(const float* sim, int m, int n, int64_t ld, int32_t* ids, int smem_optin,
                                   cudaStream_t st);
 cudaError_t sgnn_launch_prec_at_k(const float* true_sim, const float* pred_sim, int m, int n, const int32_t* ks,

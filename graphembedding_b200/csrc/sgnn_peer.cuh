@@ -1,0 +1,93 @@
+// Top-k candidate exchange between the GPUs of one node over NVLink / NVSwitch peer memory.
+//
+// All-pairs ranking shards the DATABASE over ranks; every rank ends a step with a local
+// top-k [m][k] per query and needs the k best of the world * k candidates.  The exchange is a
+// candidate all-gather of m * k * 8 bytes per rank -- 80 KB: pure latency.  Instead of a library
+// all-gather plus glue kernels, every rank PUSHES its candidates straight into a slot of every
+// peer's exchange buffer (remote stores over NVLink into memory opened through CUDA IPC), publishes
+// a per-sender epoch flag with release semantics at system scope, and the merge kernel of every
+// rank acquires the world flags and ranks the candidates by counting.  Two kernels, no host
+// round trip, no staging copies.
+//
+// Exchange buffer of one rank (device memory of that rank, opened by every peer):
+//   u64 flags[2][PEER_MAX_WORLD]            epoch of the newest complete push of sender r, per parity
+//   u64 cand[2][world][m_cap * k_cap]       (orderable score << 32 | global id) keys, per parity
+// Parity = epoch & 1 double-buffers the slots: a sender can only be one epoch ahead of a receiver
+// (it needs the receiver's flag of epoch e before it finishes epoch e), so the slot it overwrites at
+// epoch e + 2 has been merged by then.
+#pragma once
+#include "sgnn_rank.cuh"
+
+constexpr int PEER_MAX_WORLD = 16;
+constexpr size_t PEER_HEADER_BYTES = 2 * PEER_MAX_WORLD * sizeof(unsigned long long);
+
+struct PeerPtrs {
+  unsigned long long* base[PEER_MAX_WORLD];   // exchange buffer of every rank (own included)
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Every rank: local candidates -> slot `rank` of every peer, then the epoch flag.  done_counter is a
+// local device word (zero before and after each launch).
+__global__ void __launch_bounds__(256)
+peer_push_kernel(const float* __restrict__ vals, const int32_t* __restrict__ ids, int count, int id_offset,
+                 int rank, int world, int64_t slot_elems, PeerPtrs P, unsigned long long epoch,
+                 unsigned int* __restrict__ done_counter) {
+  const int parity = (int)(epoch & 1ull);
+  const size_t slot = PEER_HEADER_BYTES / 8 + ((size_t)parity * world + rank) * slot_elems;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+    const unsigned long long key = rank_key(vals[i], ids[i] + id_offset);
+    for (int r = 0; r < world; ++r) P.base[r][slot + i] = key;
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int prev = atomicAdd(done_counter, 1u);
+    if (prev == gridDim.x - 1) {   // last CTA: every candidate of this rank is visible system-wide
+      *done_counter = 0u;
+      __threadfence_system();
+      for (int r = 0; r < world; ++r) st_release_sys(P.base[r] + parity * PEER_MAX_WORLD + rank, epoch);
+    }
+  }
+}
+
+// Every rank: wait for the world flags of this epoch, then top-k of the world * k candidates of
+// each row (keys are unique: the global id is part of the key).  One warp per row.
+__global__ void __launch_bounds__(256)
+peer_merge_kernel(const unsigned long long* __restrict__ mine, int m, int k, int world, int64_t slot_elems,
+                  unsigned long long epoch, int32_t* __restrict__ ids, float* __restrict__ vals) {
+  extern __shared__ unsigned long long s_keys[];   // [8 warps][world * k]
+  const int parity = (int)(epoch & 1ull);
+  if (threadIdx.x < world) {
+    const unsigned long long* f = mine + parity * PEER_MAX_WORLD + threadIdx.x;
+    while (ld_acquire_sys(f) < epoch) __nanosleep(64);
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int row = blockIdx.x * 8 + warp;
+  if (row >= m) return;
+  const int c = world * k;
+  unsigned long long* sk = s_keys + (size_t)warp * c;
+  const unsigned long long* cand = mine + PEER_HEADER_BYTES / 8 + (size_t)parity * world * slot_elems;
+  for (int t = lane; t < c; t += 32) {
+    const int r = t / k, j = t - r * k;
+    sk[t] = __ldcg(cand + (size_t)r * slot_elems + (size_t)row * k + j);   // written by peers: bypass L1
+  }
+  __syncwarp();
+  for (int t = lane; t < c; t += 32) {
+    const unsigned long long kq = sk[t];
+    int rk = 0;
+    for (int u = 0; u < c; ++u) rk += sk[u] > kq ? 1 : 0;
+    if (rk < k) {
+      ids[(size_t)row * k + rk] = (int)(kq & 0xffffffffull);
+      if (vals) vals[(size_t)row * k + rk] = rank_key_score(kq);
+    }
+  }
+}

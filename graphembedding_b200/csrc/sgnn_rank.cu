@@ -1,6 +1,7 @@
 // Translation unit of the ranking / metric kernels (sgnn_rank.cuh).
 #include "sgnn_rank.cuh"
 #include "sgnn_internal.h"
+#include <algorithm>
 
 static int pad_pow2(int n) {
   int p = 2;
@@ -77,3 +78,30 @@ extern "C" int sgnn_debug_topk_trace(int* out, int n) {
   return (int)cudaMemcpyFromSymbol(out, g_topk_dbg, sizeof(int) * (size_t)n);
 }
 #endif
+
+// ---- peer-memory candidate exchange (sgnn_peer.cuh) ----
+#include "sgnn_peer.cuh"
+
+cudaError_t sgnn_launch_peer_exchange(const float* vals, const int32_t* ids, int m, int k, int id_offset, int rank,
+                                      int world, int64_t slot_elems, void* const* peer_bufs,
+                                      unsigned long long epoch, unsigned int* done_counter, int32_t* out_ids,
+                                      float* out_vals, cudaStream_t st) {
+  if (world < 1 || world > PEER_MAX_WORLD || (int64_t)m * k > slot_elems) return cudaErrorInvalidValue;
+  PeerPtrs P;
+  for (int r = 0; r < PEER_MAX_WORLD; ++r)
+    P.base[r] = r < world ? static_cast<unsigned long long*>(peer_bufs[r]) : nullptr;
+  const int count = m * k;
+  const int blocks = std::max(1, std::min(64, (count + 255) / 256));
+  peer_push_kernel<<<blocks, 256, 0, st>>>(vals, ids, count, id_offset, rank, world, slot_elems, P, epoch,
+                                           done_counter);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  const size_t smem = (size_t)8 * world * k * sizeof(unsigned long long);
+  if (smem > 48 * 1024) return cudaErrorInvalidValue;
+  peer_merge_kernel<<<(m + 7) / 8, 256, smem, st>>>(P.base[rank], m, k, world, slot_elems, epoch, out_ids, out_vals);
+  return cudaGetLastError();
+}
+
+int64_t sgnn_peer_buffer_bytes(int world, int64_t slot_elems) {
+  return (int64_t)PEER_HEADER_BYTES + 2 * (int64_t)world * slot_elems * (int64_t)sizeof(unsigned long long);
+}

@@ -8,9 +8,11 @@
   F6) needs the target sum / square sum of the GLOBAL batch: targets are host data, so they are
   computed on the host from the global batch -- no extra collective.
 * All-pairs ranking shards the DATABASE contiguously; queries are replicated.  Each rank scores its
-  m x n_r tile and keeps a local top-k with GLOBAL ids; the (score, id) candidates are all-gathered
-  (m x k x 8 bytes per rank) and merged with the reference's tie order (results.py:221-224: equal
-  scores -> higher index first), which ``sgnn_topk_merge`` reproduces on device.
+  m x n_r tile and keeps a local top-k; the (score, GLOBAL id) candidates of all ranks are merged
+  with the reference's tie order (results.py:221-224: equal scores -> higher index first).  On the
+  GPUs of one node the exchange is ``PeerTopk``: every rank pushes its candidates into every peer's
+  buffer over NVLink peer memory and merges on arrival (two kernels, sgnn_peer.cuh).  The
+  all-gather + ``sgnn_topk_merge`` path is the fallback (no peer access) and what the gloo tests run.
 
 Nothing here touches the reference's semantics; the functions are written against plain tensors so
 that the world_size-2 gloo tests (tests/test_dist_gloo.py) exercise exactly the code the GPU path
@@ -63,6 +65,32 @@ def gather_topk_candidates(local_vals, local_ids, id_offset, dist=None, group=No
     return cv, ci
 
 
+class PeerTopk(object):
+    """Peer-memory candidate exchange of one process group (one process per GPU, one node).
+
+    Setup is a host-side all-gather of 64-byte CUDA IPC handles; each step is
+    ``engine.topk_exchange`` (a push kernel + a merge kernel, no library collective).  Every rank
+    must call ``exchange`` the same number of times."""
+
+    def __init__(self, engine, m_cap, k_cap, dist, group=None):
+        self.engine, self.dist, self.group = engine, dist, group
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        mine = engine.peer_create(world, rank, m_cap, k_cap)
+        handles = [None] * world
+        dist.all_gather_object(handles, mine, group=group)
+        engine.peer_connect(handles)
+        dist.barrier(group=group)
+
+    def exchange(self, local_vals, local_ids, id_offset, out_ids=None, out_vals=None):
+        return self.engine.topk_exchange(local_vals, local_ids, id_offset, out_ids=out_ids, out_vals=out_vals)
+
+    def close(self):
+        import torch
+        torch.cuda.synchronize()
+        self.dist.barrier(group=self.group)   # no peer is still writing into / reading from a buffer
+        self.engine.peer_destroy()
+
+
 def merge_topk_host(cand_vals, cand_ids, k):
     """Host statement of the merge ``sgnn_topk_merge`` performs on device: descending score, ties
     -> higher GLOBAL id first (a stable ascending mergesort on (score, id) reversed,
@@ -74,13 +102,17 @@ def merge_topk_host(cand_vals, cand_ids, k):
 
 
 def sharded_rank(engine, queries_dev, db_shard_dev, id_offset, k, dist=None, group=None, emb_q=None,
-                 emb_db=None, sim=None):
+                 emb_db=None, sim=None, peer=None, ids=None, vals=None):
     """One database-sharded ranking step on this rank: embed, score the local tile, local top-k,
-    all-gather, merge.  Returns (ids, vals) of the global top-k (identical on every rank)."""
-    ids, vals, sim = engine.rank_device(queries_dev, db_shard_dev, k, emb_q=emb_q, emb_db=emb_db, sim=sim)
+    candidate exchange + merge (``peer``: a PeerTopk; else all-gather + merge kernel).  Returns
+    (ids, vals) of the global top-k (identical on every rank)."""
+    ids, vals, sim = engine.rank_device(queries_dev, db_shard_dev, k, emb_q=emb_q, emb_db=emb_db, sim=sim,
+                                        ids=ids, vals=vals)
     world = dist.get_world_size(group) if dist is not None and dist.is_initialized() else 1
     if world == 1 and id_offset == 0:
         return ids, vals
+    if peer is not None:
+        return peer.exchange(vals, ids, id_offset)
     cv, ci = gather_topk_candidates(vals, ids, id_offset, dist, group)
     return engine.topk_merge(cv, ci, k)
 

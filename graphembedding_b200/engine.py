@@ -159,6 +159,34 @@ class SgnnEngine(object):
         self.launches += 1
         return ids, vals
 
+    # ---- multi-GPU candidate exchange over peer memory (sgnn_peer_*) -------------------
+    def peer_create(self, world, rank, m_cap, k_cap):
+        """Allocate this rank's exchange buffer; returns its 64-byte CUDA IPC handle."""
+        buf = (C.c_uint8 * 64)()
+        check(self.h, lib().sgnn_peer_create(self.h, int(world), int(rank), int(m_cap), int(k_cap), buf))
+        return bytes(buf)
+
+    def peer_connect(self, handles):
+        """handles: the world IPC handles in rank order (own included)."""
+        blob = b''.join(handles)
+        arr = (C.c_uint8 * len(blob)).from_buffer_copy(blob)
+        check(self.h, lib().sgnn_peer_connect(self.h, arr))
+
+    def peer_destroy(self):
+        if getattr(self, 'h', None):
+            lib().sgnn_peer_destroy(self.h)
+
+    def topk_exchange(self, vals, ids, id_offset, out_ids=None, out_vals=None, stream=None):
+        """Push the local top-k (LOCAL ids + id_offset) to every peer and merge: global (ids, vals)."""
+        import torch
+        m, k = vals.shape
+        out_ids = torch.empty((m, k), dtype=torch.int32, device=self.device) if out_ids is None else out_ids
+        out_vals = torch.empty((m, k), dtype=torch.float32, device=self.device) if out_vals is None else out_vals
+        check(self.h, lib().sgnn_topk_exchange(self.h, _ptr(vals), _ptr(ids), m, k, int(id_offset), _ptr(out_ids),
+                                               _ptr(out_vals), _stream_ptr(stream)))
+        self.launches += 2
+        return out_ids, out_vals
+
     def sort_rows(self, sim, stream=None):
         import torch
         m, n = sim.shape

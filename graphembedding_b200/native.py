@@ -84,6 +84,10 @@ SIGNATURES = {
     'sgnn_kendall_tau': (C.c_int, [_P, _P, _P, _I32, _I32, _P, _P, _P]),
     'sgnn_forward_pairs_host': (C.c_int, [_P, _BP, _P, _P, _I32, _P, _P]),
     'sgnn_rank_device': (C.c_int, [_P, _BP, _BP, _I32, _P, _P, _P, _I64, _P, _P, _P]),
+    'sgnn_peer_create': (C.c_int, [_P, _I32, _I32, _I32, _I32, _P]),
+    'sgnn_peer_connect': (C.c_int, [_P, _P]),
+    'sgnn_topk_exchange': (C.c_int, [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P]),
+    'sgnn_peer_destroy': (C.c_int, [_P]),
     'sgnn_debug_slice_hints': (C.c_int, [_P, _P, _P]),
     'sgnn_rank_host': (C.c_int, [_P, _BP, _BP, _I32, _P, _P, _P]),
     'sgnn_train_step_host': (C.c_int, [_P, _BP, _P, _P, _P, _I32, _P]),

@@ -223,6 +223,25 @@ int sgnn_forward_pairs_host(SgnnHandle h, const SgnnGraphBatch* batch_host, cons
 int sgnn_rank_device(SgnnHandle h, const SgnnGraphBatch* q_dev, const SgnnGraphBatch* db_dev, int32_t k,
                      float* emb_q_dev, float* emb_db_dev, float* sim_dev, int64_t ld, int32_t* topk_ids_dev,
                      float* topk_vals_dev, void* stream);
+/* ---- multi-GPU ranking: top-k candidate exchange over NVLink peer memory ------------------------
+ * The database is sharded over the GPUs of one node (one process per GPU); every rank holds a
+ * local top-k [m][k] (LOCAL ids + its shard's id_offset) and needs the global one.  Instead of a
+ * library all-gather + merge, every rank pushes its candidates into a slot of every peer's exchange
+ * buffer (remote stores over NVLink into CUDA-IPC-opened memory), raises an epoch flag, and merges
+ * the world * k candidates of each query when all flags of the epoch have arrived.  Tie order as
+ * sgnn_topk (results.py:221-224) on GLOBAL ids.
+ *   1. every rank: sgnn_peer_create(...)  -> 64-byte IPC handle
+ *   2. all-gather the handles on the host (torch.distributed / MPI / files)
+ *   3. every rank: sgnn_peer_connect(all_handles [world][64])
+ *   4. per step, on EVERY rank, the same number of times: sgnn_topk_exchange(...)
+ *   5. host barrier, then sgnn_peer_destroy (also done by sgnn_destroy). */
+#define SGNN_IPC_HANDLE_BYTES 64
+int sgnn_peer_create(SgnnHandle h, int32_t world, int32_t rank, int32_t m_cap, int32_t k_cap,
+                     uint8_t* ipc_handle_out);
+int sgnn_peer_connect(SgnnHandle h, const uint8_t* all_handles);
+int sgnn_topk_exchange(SgnnHandle h, const float* vals_dev, const int32_t* ids_dev, int32_t m, int32_t k,
+                       int32_t id_offset, int32_t* out_ids_dev, float* out_vals_dev, void* stream);
+int sgnn_peer_destroy(SgnnHandle h);
 /* Test hook: the slice-maximum hints the tensor-core scorer left for the top-k kernel during the last
  * sgnn_rank_device / sgnn_rank_host call ([m][4 * ceil(n / 128)] 64-bit rank keys: orderable score << 32 |
  * database id of the largest element of every 32-column slice of sim). */

@@ -409,9 +409,32 @@ def test_rank_device_equals_the_separate_calls(precision):
     qd, dbd = q.to(eng.device), db.to(eng.device)
     sim_ref = eng.score_all_pairs(eng.embed(qd), eng.embed(dbd))
     ids_ref, vals_ref = eng.topk(sim_ref, 10)
-    for _ in range(3):      # repeated: the fork/join events are reused
+    for _ in range(3):      # repeated: the fork/join events are reused (legacy stream: always eager)
         ids, vals, sim = eng.rank_device(qd, dbd, 10)
         assert torch.equal(sim, sim_ref) and torch.equal(ids, ids_ref) and torch.equal(vals, vals_ref)
+    # on a real stream the second call with the same buffers is captured and later ones replay a CUDA graph
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    E = eng.emb_dim
+    bufs = dict(emb_q=torch.empty((150, E), device=eng.device), emb_db=torch.empty((550, E), device=eng.device),
+                sim=torch.empty((150, 550), device=eng.device),
+                ids=torch.empty((150, 10), dtype=torch.int32, device=eng.device),
+                vals=torch.empty((150, 10), device=eng.device))
+    with torch.cuda.stream(s):
+        for it in range(5):
+            for b in bufs.values():
+                b.zero_()
+            ids, vals, sim = eng.rank_device(qd, dbd, 10, **bufs)
+            s.synchronize()
+            assert torch.equal(sim, sim_ref) and torch.equal(ids, ids_ref) and torch.equal(vals, vals_ref), it
+        if precision == 'fp32':   # new parameters are picked up by the replayed graph (read at run time)
+            eng.init_params(8)
+            ids2, vals2, sim2 = eng.rank_device(qd, dbd, 10, **bufs)
+            s.synchronize()
+            ref2 = eng.score_all_pairs(eng.embed(qd), eng.embed(dbd))
+            s.synchronize()
+            assert torch.equal(sim2, ref2) and not torch.equal(ref2, sim_ref)
+            eng.init_params(7)
     _, _, sim0 = eng.rank_device(qd, dbd, 0)
     assert torch.equal(sim0, sim_ref)
 

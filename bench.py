@@ -294,6 +294,8 @@ def run_cuda(args):
     emb_q = torch.empty((M_QUERIES, eng.emb_dim), dtype=torch.float32, device=dev)
     emb_db = torch.empty((N_DB, eng.emb_dim), dtype=torch.float32, device=dev)
     sim = torch.empty((M_QUERIES, N_DB), dtype=torch.float32, device=dev)
+    ids_d = torch.empty((M_QUERIES, TOPK), dtype=torch.int32, device=dev)
+    vals_d = torch.empty((M_QUERIES, TOPK), dtype=torch.float32, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     out = {}
 
@@ -316,7 +318,7 @@ def run_cuda(args):
 
     def step():
         out['ids'], out['vals'] = DS.sharded_rank(eng, qd, dbd, rank * N_DB, TOPK, dist if world > 1 else None,
-                                                  emb_q=emb_q, emb_db=emb_db, sim=sim, peer=peer)
+                                                  emb_q=emb_q, emb_db=emb_db, sim=sim, peer=peer, ids=ids_d, vals=vals_d)
 
     clocks = ClockSampler(local)
     clocks.start()

@@ -38,10 +38,28 @@ struct HostWs {  // device staging for the *_host entry points (sized by sgnn_re
 struct GraphSlot {
   uint64_t key = 0;
   bool seen = false;
+  uint64_t used = 0;                    // LRU stamp
   cudaGraphExec_t exec = nullptr;
   void drop() {
     if (exec) cudaGraphExecDestroy(exec);
-    exec = nullptr; seen = false; key = 0;
+    exec = nullptr; seen = false; key = 0; used = 0;
+  }
+};
+
+// a few argument sets per entry point (callers often ping-pong between two output buffers)
+struct GraphCache {
+  GraphSlot slot[4];
+  uint64_t clock = 0;
+  void drop() { for (auto& s : slot) s.drop(); }
+  GraphSlot& find(uint64_t key) {   // the slot holding `key`, else the least recently used one (reset)
+    GraphSlot* lru = &slot[0];
+    for (auto& s : slot) {
+      if (s.seen && s.key == key) { s.used = ++clock; return s; }
+      if (s.used < lru->used) lru = &s;
+    }
+    lru->drop();
+    lru->used = ++clock;
+    return *lru;
   }
 };
 
@@ -54,7 +72,7 @@ struct SgnnHandle_t {
   void* peer_bufs[16] = {};
   unsigned int* peer_done = nullptr;
   bool use_graphs = true;               // SGNN_NO_GRAPHS=1 or a failed capture turns replay off
-  GraphSlot g_rank_device, g_rank_host;
+  GraphCache g_rank_device, g_rank_host;
   ModelDev M;
   int device = 0, sm_count = 148, smem_optin = 0;
   std::string err;
@@ -381,14 +399,14 @@ void key_batch(uint64_t* k, const SgnnGraphBatch* b) {
 
 // run `body` (stream work only, starting and ending on `st`) eagerly, or capture / replay it
 template <typename F>
-int run_cached(SgnnHandle h, GraphSlot& slot, uint64_t key, cudaStream_t st, F body) {
+int run_cached(SgnnHandle h, GraphCache& cache, uint64_t key, cudaStream_t st, F body) {
   if (!h->use_graphs || st == nullptr || st == cudaStreamLegacy) return body();
+  GraphSlot& slot = cache.find(key);
   if (slot.exec && slot.key == key) {
     CUDA_OK(h, cudaGraphLaunch(slot.exec, st));
     return 0;
   }
   if (!(slot.seen && slot.key == key)) {   // first sighting of these arguments: run eagerly
-    slot.drop();
     slot.key = key; slot.seen = true;
     return body();
   }

@@ -48,13 +48,13 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "{\n\t"
       ".reg .pred p;\n\t"
       "WAIT_LOOP:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
       "@p bra DONE;\n\t"
       "bra WAIT_LOOP;\n\t"
       "DONE:\n\t"
       "}" ::"r"(smem_u32(bar)),
-      "r"(parity)
-      : "memory");
+      "r"(parity), "r"(0x989680u)   // suspend-time hint: the warp sleeps in hardware until the phase flips instead of
+      : "memory");                  // re-issuing the poll (a polling issuer warp costs the epilogue warps issue slots)
 }
 #endif
 

@@ -10,6 +10,7 @@
 #include "sgnn_common.cuh"
 #include "sgnn_internal.h"
 #include "sgnn_small.cuh"
+#include "sgnn_train_team.cuh"
 
 namespace {
 
@@ -95,7 +96,8 @@ struct SgnnHandle_t {
   HostWs ws;
   // launch geometry decided at create
   int embed_wpb[2] = {8, 8}, train_wpb[2] = {4, 4};
-  size_t embed_smem[2] = {0, 0}, train_smem[2] = {0, 0}, pair_smem = 0;
+  size_t embed_smem[2] = {0, 0}, train_smem[2] = {0, 0}, pair_smem = 0, team_smem32 = 0;
+  bool use_team = false;
 };
 
 namespace {
@@ -249,6 +251,15 @@ int plan_launches(SgnnHandle h) {
   if (set_smem(h, train_pairs_kernel<16, false>, h->train_smem[0])) return 1;
   if (set_smem(h, train_pairs_kernel<32, false>, h->train_smem[1])) return 1;
   if (set_smem(h, pair_score_kernel, h->pair_smem)) return 1;
+  // CTA-per-pair team kernel (sgnn_train_team.cuh): used whenever it fits; SGNN_TRAIN_KERNEL=warp forces the
+  // warp-per-pair kernel (cross-checks)
+  h->team_smem32 = team_smem_floats(M, 32) * sizeof(float);
+  h->use_team = h->team_smem32 <= budget;
+  if (const char* tk = getenv("SGNN_TRAIN_KERNEL")) h->use_team = h->use_team && strcmp(tk, "warp") != 0;
+  if (h->use_team) {
+    if (set_smem(h, train_team_kernel<true>, h->team_smem32)) return 1;
+    if (set_smem(h, train_team_kernel<false>, h->team_smem32)) return 1;
+  }
   return 0;
 }
 
@@ -770,6 +781,22 @@ static int launch_pairs(SgnnHandle h, bool bwd, const SgnnGraphBatch* b, const i
     const uint32_t s32 = (uint32_t)(h->drop_seed ^ (h->drop_seed >> 32));
     dbase = sgnn_fmix32(s32 ^ sgnn_fmix32((uint32_t)h->drop_counter + 0x9E3779B9u));
     h->drop_counter += 1;
+  }
+  if (h->use_team) {
+    const int nmax = std::max(4, (int)b->max_nodes);
+    const size_t smem = team_smem_floats(h->M, nmax) * sizeof(float);
+    const int per_sm = std::max<size_t>(1, std::min<size_t>(2, (size_t)h->smem_optin / (smem + 1024)));
+    const int tblocks = std::min(n_pairs, h->sm_count * per_sm);
+    if (bwd)
+      train_team_kernel<true><<<tblocks, TEAM_CTA, smem, st>>>(h->M, to_dev(b), nmax, h->d_params, g1, g2, target_sim,
+                                                               n_pairs, invB, s1, s2, h->d_grads, loss, raw, sim,
+                                                               dropping, dbase);
+    else
+      train_team_kernel<false><<<tblocks, TEAM_CTA, smem, st>>>(h->M, to_dev(b), nmax, h->d_params, g1, g2, target_sim,
+                                                                n_pairs, invB, s1, s2, h->d_grads, loss, raw, sim,
+                                                                dropping, dbase);
+    CUDA_OK(h, cudaGetLastError());
+    return 0;
   }
 #define SGNN_LAUNCH_PAIRS(NM, BW)                                                                        \
   train_pairs_kernel<NM, BW><<<blocks, wpb * 32, h->train_smem[v], st>>>(                                \

@@ -417,11 +417,24 @@ def run_train(torch, dist, dev, rank, world, local, args, barrier, max_over_rank
     loss = torch.zeros(4, dtype=torch.float32, device=dev)
     grads = eng.device_buffers()[1]
     gb = TRAIN_BATCH * world
+    peer, allreduce = None, 'none (1 GPU)'
+    if world > 1:   # gradient push over peer memory fused into Adam; fallback: NCCL all-reduce + Adam
+        try:
+            peer, allreduce = DS.PeerTopk(eng, 0, 0, dist), 'p2p push fused into Adam (CUDA IPC peer memory)'
+        except Exception as e:
+            sys.stderr.write('bench.py: peer exchange unavailable (%s); using NCCL all-reduce\n' % e)
+        flag = torch.tensor([1 if peer is not None else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 0:
+            if peer is not None:
+                peer.close()
+            peer, allreduce = None, 'nccl all-reduce'
 
     def step(i):
         g1, g2, t, s1, s2 = feeds[i % len(feeds)]
         loss.zero_()
-        DS.data_parallel_step(eng, bd, g1, g2, t, gb, s1, s2, loss, dist if world > 1 else None, grads=grads)
+        DS.data_parallel_step(eng, bd, g1, g2, t, gb, s1, s2, loss, dist if world > 1 else None, grads=grads,
+                              peer=peer)
 
     n = max(args.steps * 10, 100)
     for i in range(10):
@@ -435,7 +448,9 @@ def run_train(torch, dist, dev, rank, world, local, args, barrier, max_over_rank
     b.record()
     barrier()
     ms = max_over_ranks(a.elapsed_time(b)) / n
-    return {'workload': 'BASELINE configs[2]: DP training, {} pairs/GPU/step, {} AIDS10knef-shaped graphs (2..30 nodes), '
+    if peer is not None:
+        peer.close()
+    return {'allreduce': allreduce, 'workload': 'BASELINE configs[2]: DP training, {} pairs/GPU/step, {} AIDS10knef-shaped graphs (2..30 nodes), '
                         'GCN32-GCN16-Average-NTN(16,10), fwd+bwd+allreduce+Adam, fp32'.format(TRAIN_BATCH, TRAIN_GRAPHS),
             'value': TRAIN_BATCH * world / (ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': ms, 'steps': n,
             'gpu_launches': eng.launches - l0, 'final_loss': float(loss[0] + loss[1])}

@@ -69,7 +69,7 @@ struct SgnnHandle_t {
   // peer-memory top-k exchange (sgnn_peer.cuh): own buffer + the peers' buffers opened through CUDA IPC
   int peer_world = 0, peer_rank = 0;
   int64_t peer_slot_elems = 0;
-  unsigned long long peer_epoch = 0;
+  unsigned long long peer_epoch = 0, peer_gepoch = 0;
   void* peer_bufs[16] = {};
   unsigned int* peer_done = nullptr;
   bool use_graphs = true;               // SGNN_NO_GRAPHS=1 or a failed capture turns replay off
@@ -842,6 +842,25 @@ int sgnn_apply_adam(SgnnHandle h, float grad_scale, float* loss_dev, void* strea
   return 0;
 }
 
+int sgnn_apply_adam_allreduce(SgnnHandle h, float grad_scale, float* loss_dev, void* stream) {
+  if (!h) return 1;
+  if (h->peer_world == 0) return fail(h, "sgnn_apply_adam_allreduce: no peer exchange set up (sgnn_peer_create/connect)");
+  for (int r = 0; r < h->peer_world; ++r)
+    if (!h->peer_bufs[r]) return fail(h, "sgnn_apply_adam_allreduce: peers not connected");
+  h->adam_t += 1;
+  h->peer_gepoch += 1;
+  const SgnnConfig& c = h->cfg;
+  const double t = (double)h->adam_t;
+  const double lr_t = (double)c.learning_rate * std::sqrt(1.0 - std::pow((double)c.beta2, t)) /
+                      (1.0 - std::pow((double)c.beta1, t));
+  const cudaError_t e = sgnn_launch_peer_adam(h->M.n_params, h->peer_rank, h->peer_world, h->peer_slot_elems,
+                                              h->peer_bufs, h->peer_gepoch, h->peer_done, h->d_params, h->d_grads,
+                                              h->d_m, h->d_v, grad_scale, c.weight_decay, (float)lr_t, c.beta1,
+                                              c.beta2, c.epsilon, loss_dev, h->sm_count, (cudaStream_t)stream);
+  if (e != cudaSuccess) return fail(h, std::string("sgnn_apply_adam_allreduce: ") + cudaGetErrorString(e));
+  return 0;
+}
+
 int sgnn_set_dropout_stream(SgnnHandle h, uint64_t seed, uint64_t counter) {
   if (!h) return 1;
   h->drop_seed = seed; h->drop_counter = counter;
@@ -989,9 +1008,9 @@ int sgnn_peer_create(SgnnHandle h, int32_t world, int32_t rank, int32_t m_cap, i
   static_assert(sizeof(cudaIpcMemHandle_t) == SGNN_IPC_HANDLE_BYTES, "IPC handle size");
   CUDA_OK(h, cudaSetDevice(h->device));
   sgnn_peer_destroy(h);
-  h->peer_world = world; h->peer_rank = rank; h->peer_epoch = 0;
+  h->peer_world = world; h->peer_rank = rank; h->peer_epoch = 0; h->peer_gepoch = 0;
   h->peer_slot_elems = (int64_t)m_cap * k_cap;
-  const int64_t bytes = sgnn_peer_buffer_bytes(world, h->peer_slot_elems);
+  const int64_t bytes = sgnn_peer_buffer_bytes(world, h->peer_slot_elems, h->M.n_params);
   CUDA_OK(h, cudaMalloc(&h->peer_bufs[rank], (size_t)bytes));
   CUDA_OK(h, cudaMemset(h->peer_bufs[rank], 0, (size_t)bytes));
   CUDA_OK(h, cudaMalloc(reinterpret_cast<void**>(&h->peer_done), sizeof(unsigned int)));

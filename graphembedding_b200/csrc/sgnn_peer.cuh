@@ -91,3 +91,64 @@ peer_merge_kernel(const unsigned long long* __restrict__ mine, int m, int k, int
     }
   }
 }
+
+// ---- data-parallel training: gradient all-reduce fused into the optimiser ----------------------
+// The flat gradient blob is 11-40 KB: again pure latency.  Every rank pushes its blob into slot
+// `rank` of every peer's gradient region (second region of the same exchange buffer), and the Adam
+// kernel of every rank sums the world slots IN RANK ORDER (so all ranks apply bit-identical updates)
+// as it reads them -- there is no separate reduced-gradient pass and no library collective.
+// Region (after the candidate region, `goff` u64 words from the base):
+//   u64 gflags[2][PEER_MAX_WORLD]; float grad[2][world][n_pad]
+__global__ void __launch_bounds__(256)
+peer_grad_push_kernel(const float* __restrict__ grads, int n, int n_pad, int rank, int world, size_t goff,
+                      PeerPtrs P, unsigned long long epoch, unsigned int* __restrict__ done_counter) {
+  const int parity = (int)(epoch & 1ull);
+  const size_t slot = (size_t)(parity * world + rank) * n_pad;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float g = grads[i];
+    for (int r = 0; r < world; ++r)
+      reinterpret_cast<float*>(P.base[r] + goff + 2 * PEER_MAX_WORLD)[slot + i] = g;
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int prev = atomicAdd(done_counter, 1u);
+    if (prev == gridDim.x - 1) {
+      *done_counter = 0u;
+      __threadfence_system();
+      for (int r = 0; r < world; ++r) st_release_sys(P.base[r] + goff + parity * PEER_MAX_WORLD + rank, epoch);
+    }
+  }
+}
+
+// weight decay gradient + TF-1 Adam (as adam_kernel) on the sum of the world gradient slots
+__global__ void __launch_bounds__(256)
+adam_peer_kernel(int n, int n_pad, int world, const unsigned long long* __restrict__ mine, size_t goff,
+                 unsigned long long epoch, float* __restrict__ params, float* __restrict__ grads,
+                 float* __restrict__ m, float* __restrict__ v, float grad_scale, float wd, float lr_t, float b1,
+                 float b2, float eps, float* __restrict__ loss) {
+  const int parity = (int)(epoch & 1ull);
+  if (threadIdx.x < world) {
+    const unsigned long long* f = mine + goff + parity * PEER_MAX_WORLD + threadIdx.x;
+    while (ld_acquire_sys(f) < epoch) __nanosleep(64);
+  }
+  __syncthreads();
+  const float* slots = reinterpret_cast<const float*>(mine + goff + 2 * PEER_MAX_WORLD) + (size_t)parity * world * n_pad;
+  float wdl = 0.f;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    float gs = 0.f;
+    for (int r = 0; r < world; ++r) gs += __ldcg(slots + (size_t)r * n_pad + i);   // rank order: same sum everywhere
+    const float p = params[i];
+    const float g = gs * grad_scale + wd * p;
+    wdl = fmaf(p, p, wdl);
+    const float mi = b1 * m[i] + (1.f - b1) * g;
+    const float vi = b2 * v[i] + (1.f - b2) * g * g;
+    m[i] = mi; v[i] = vi;
+    params[i] = p - lr_t * mi / (sqrtf(vi) + eps);
+    grads[i] = 0.f;
+  }
+  if (loss) {
+    wdl = warp_sum(wdl);
+    if ((threadIdx.x & 31) == 0 && wdl != 0.f) atomicAdd(loss + 1, 0.5f * wd * wdl);
+  }
+}

@@ -102,6 +102,31 @@ cudaError_t sgnn_launch_peer_exchange(const float* vals, const int32_t* ids, int
   return cudaGetLastError();
 }
 
-int64_t sgnn_peer_buffer_bytes(int world, int64_t slot_elems) {
-  return (int64_t)PEER_HEADER_BYTES + 2 * (int64_t)world * slot_elems * (int64_t)sizeof(unsigned long long);
+// u64 words of the candidate region = offset of the gradient region
+int64_t sgnn_peer_grad_offset(int world, int64_t slot_elems) {
+  return (int64_t)(PEER_HEADER_BYTES / 8) + 2 * (int64_t)world * slot_elems;
+}
+
+int64_t sgnn_peer_buffer_bytes(int world, int64_t slot_elems, int n_params) {
+  const int64_t n_pad = (n_params + 3) / 4 * 4;
+  return sgnn_peer_grad_offset(world, slot_elems) * 8 + (int64_t)PEER_HEADER_BYTES + 2 * (int64_t)world * n_pad * 4;
+}
+
+cudaError_t sgnn_launch_peer_adam(int n, int rank, int world, int64_t slot_elems, void* const* peer_bufs,
+                                  unsigned long long epoch, unsigned int* done_counter, float* params, float* grads,
+                                  float* m, float* v, float grad_scale, float wd, float lr_t, float b1, float b2,
+                                  float eps, float* loss, int sm_count, cudaStream_t st) {
+  if (world < 1 || world > PEER_MAX_WORLD) return cudaErrorInvalidValue;
+  PeerPtrs P;
+  for (int r = 0; r < PEER_MAX_WORLD; ++r)
+    P.base[r] = r < world ? static_cast<unsigned long long*>(peer_bufs[r]) : nullptr;
+  const int n_pad = (n + 3) / 4 * 4;
+  const size_t goff = (size_t)sgnn_peer_grad_offset(world, slot_elems);
+  const int blocks = std::max(1, std::min((n + 255) / 256, sm_count));
+  peer_grad_push_kernel<<<blocks, 256, 0, st>>>(grads, n, n_pad, rank, world, goff, P, epoch, done_counter);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  adam_peer_kernel<<<blocks, 256, 0, st>>>(n, n_pad, world, P.base[rank], goff, epoch, params, grads, m, v, grad_scale,
+                                           wd, lr_t, b1, b2, eps, loss);
+  return cudaGetLastError();
 }

@@ -84,6 +84,10 @@ class PeerTopk(object):
     def exchange(self, local_vals, local_ids, id_offset, out_ids=None, out_vals=None):
         return self.engine.topk_exchange(local_vals, local_ids, id_offset, out_ids=out_ids, out_vals=out_vals)
 
+    def adam_allreduce(self, grad_scale=1.0, loss=None):
+        """DP optimiser step: gradient push + Adam on the rank-ordered sum of the world blobs."""
+        self.engine.apply_adam_allreduce(grad_scale, loss)
+
     def close(self):
         import torch
         torch.cuda.synchronize()
@@ -118,9 +122,13 @@ def sharded_rank(engine, queries_dev, db_shard_dev, id_offset, k, dist=None, gro
 
 
 def data_parallel_step(engine, batch_dev, g1, g2, target_sim, global_batch, target_sum, target_sqsum, loss,
-                       dist=None, group=None, grads=None):
-    """One DP optimiser step: local fwd+bwd, gradient all-reduce, identical Adam on every rank."""
+                       dist=None, group=None, grads=None, peer=None):
+    """One DP optimiser step: local fwd+bwd, gradient all-reduce, identical Adam on every rank.
+    ``peer`` (a PeerTopk of this engine): the all-reduce is the peer-memory push fused into Adam."""
     engine.train_step(batch_dev, g1, g2, target_sim, global_batch, target_sum, target_sqsum, loss=loss)
+    if peer is not None:
+        peer.adam_allreduce(1.0, loss)
+        return loss
     if grads is None:
         grads = engine.device_buffers()[1]
     allreduce_gradients(grads, dist, group)

@@ -264,6 +264,11 @@ class SgnnEngine(object):
         check(self.h, lib().sgnn_apply_adam(self.h, float(grad_scale), _ptr(loss), _stream_ptr(stream)))
         self.launches += 1
 
+    def apply_adam_allreduce(self, grad_scale=1.0, loss=None, stream=None):
+        """Collective: push the gradient blob to every peer, Adam on the rank-ordered sum (peer_create first)."""
+        check(self.h, lib().sgnn_apply_adam_allreduce(self.h, float(grad_scale), _ptr(loss), _stream_ptr(stream)))
+        self.launches += 2
+
     def set_dropout_stream(self, seed, counter=0):
         """Seed / position of the dropout mask stream (one counter value per train/eval call)."""
         check(self.h, lib().sgnn_set_dropout_stream(self.h, int(seed), int(counter)))

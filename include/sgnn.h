@@ -242,6 +242,11 @@ int sgnn_peer_connect(SgnnHandle h, const uint8_t* all_handles);
 int sgnn_topk_exchange(SgnnHandle h, const float* vals_dev, const int32_t* ids_dev, int32_t m, int32_t k,
                        int32_t id_offset, int32_t* out_ids_dev, float* out_vals_dev, void* stream);
 int sgnn_peer_destroy(SgnnHandle h);
+/* Data-parallel optimiser step over the same peer buffers: every rank pushes its flat gradient blob
+ * (sgnn_train_step output) into every peer's buffer and applies sgnn_apply_adam to the RANK-ORDERED SUM
+ * of the world blobs, read in place by the Adam kernel (all ranks apply bit-identical updates; no
+ * separate all-reduce).  Collective: every rank calls it once per step. */
+int sgnn_apply_adam_allreduce(SgnnHandle h, float grad_scale, float* loss_dev, void* stream);
 /* Test hook: the slice-maximum hints the tensor-core scorer left for the top-k kernel during the last
  * sgnn_rank_device / sgnn_rank_host call ([m][4 * ceil(n / 128)] 64-bit rank keys: orderable score << 32 |
  * database id of the largest element of every 32-column slice of sim). */

@@ -236,15 +236,19 @@ def workload_config():
     return {'workload': 'all-pairs ranking, BASELINE configs[3]: {} queries x {} database graphs per GPU, '
                         'AIDS-shaped (2..10 nodes, 29 labels), reference default flags model '
                         '(GCN32-GCN16-Dense1-Pad10-NTN(10,10)), top-{}'.format(M_QUERIES, N_DB, TOPK),
-            'queries': M_QUERIES, 'db_per_gpu': N_DB, 'topk': TOPK, 'l2': 'flushed between timed steps (256 MiB write)',
+            'queries': M_QUERIES, 'db_per_gpu': N_DB, 'topk': TOPK, 'l2': 'flushed between timed steps (256 MiB write; N > 1: followed by a device-side barrier, both untimed)',
             'ntn_mode': 'reference', 'dropout': 0.0}
 
 
-def timed_steps(torch, fn, steps, flush):
-    """K device-timed calls of fn with an L2 flush before each; returns total ms."""
+def timed_steps(torch, fn, steps, flush, align=None):
+    """K device-timed calls of fn with an L2 flush before each; returns total ms.  align (N > 1): a
+    device-side barrier between the flush and the start event, so that every rank's timed step starts
+    together and the timed region holds the step, not the other ranks' flushes."""
     evs = []
     for _ in range(steps):
         flush.zero_()
+        if align is not None:
+            align()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         fn()
@@ -269,9 +273,12 @@ def run_cuda(args):
     # a real (non-legacy) stream: sgnn_rank_device replays its step as a CUDA graph, and stream
     # capture is not allowed on the legacy default stream
     torch.cuda.set_stream(torch.cuda.Stream())
+    # rank 0 prints ONE JSON line on stdout: libraries that write to file descriptor 1 (NCCL's version banner)
+    # are sent to stderr for the duration of the run, the JSON line goes to the saved descriptor
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
-        if os.environ.get('NCCL_DEBUG', 'VERSION').upper() == 'VERSION':
-            os.environ['NCCL_DEBUG'] = 'WARN'    # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
         dist.init_process_group('nccl', device_id=dev)
 
     def barrier():
@@ -296,6 +303,7 @@ def run_cuda(args):
     sim = torch.empty((M_QUERIES, N_DB), dtype=torch.float32, device=dev)
     ids_d = torch.empty((M_QUERIES, TOPK), dtype=torch.int32, device=dev)
     vals_d = torch.empty((M_QUERIES, TOPK), dtype=torch.float32, device=dev)
+    gids_d, gvals_d = torch.empty_like(ids_d), torch.empty_like(vals_d)   # global top-k after the exchange (N > 1)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     out = {}
 
@@ -318,7 +326,8 @@ def run_cuda(args):
 
     def step():
         out['ids'], out['vals'] = DS.sharded_rank(eng, qd, dbd, rank * N_DB, TOPK, dist if world > 1 else None,
-                                                  emb_q=emb_q, emb_db=emb_db, sim=sim, peer=peer, ids=ids_d, vals=vals_d)
+                                                  emb_q=emb_q, emb_db=emb_db, sim=sim, peer=peer, ids=ids_d, vals=vals_d,
+                                                  out_ids=gids_d, out_vals=gvals_d)
 
     clocks = ClockSampler(local)
     clocks.start()
@@ -334,7 +343,7 @@ def run_cuda(args):
     launches0 = eng.launches
     barrier()
     clocks.mark('timed_begin')
-    total_ms = timed_steps(torch, step, args.steps, flush)
+    total_ms = timed_steps(torch, step, args.steps, flush, align=peer.barrier if peer is not None else None)
     barrier()
     clocks.mark('timed_end')
     launches = eng.launches - launches0
@@ -400,7 +409,8 @@ def run_cuda(args):
         v, cores, sample = cpu_rank_baseline(DEFAULT_LAYERS, q, db)
         line['cpu_baseline'] = {'value': v, 'unit': 'pairs/s', 'cores': cores, 'kind': 'port', 'sample': sample,
                                 'per_pair_reference_structure_pairs_per_s': cpu_per_pair_rate(DEFAULT_LAYERS, q, db)}
-    print(json.dumps(line))
+    sys.stdout.flush()
+    os.write(json_fd, (json.dumps(line) + '\n').encode())
 
 
 def run_train(torch, dist, dev, rank, world, local, args, barrier, max_over_ranks):

@@ -69,11 +69,11 @@ struct SgnnHandle_t {
   // peer-memory top-k exchange (sgnn_peer.cuh): own buffer + the peers' buffers opened through CUDA IPC
   int peer_world = 0, peer_rank = 0;
   int64_t peer_slot_elems = 0;
-  unsigned long long peer_epoch = 0, peer_gepoch = 0;
+  unsigned long long* d_peer_epoch = nullptr;   // device words: candidate / gradient / barrier epochs
   void* peer_bufs[16] = {};
   unsigned int* peer_done = nullptr;
   bool use_graphs = true;               // SGNN_NO_GRAPHS=1 or a failed capture turns replay off
-  GraphCache g_rank_device, g_rank_host;
+  GraphCache g_rank_device, g_rank_host, g_rank_sharded;
   ModelDev M;
   int device = 0, sm_count = 148, smem_optin = 0;
   std::string err;
@@ -514,6 +514,7 @@ int sgnn_destroy(SgnnHandle h) {
   if (h->stream) cudaStreamDestroy(h->stream);
   h->g_rank_device.drop();
   h->g_rank_host.drop();
+  h->g_rank_sharded.drop();
   sgnn_peer_destroy(h);
   if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
   for (auto& ev : h->chunk_ev) if (ev) cudaEventDestroy(ev);
@@ -584,6 +585,7 @@ int sgnn_reserve(SgnnHandle h, int64_t max_graphs, int64_t max_nodes, int64_t ma
   CUDA_OK(h, cudaDeviceSynchronize());
   h->g_rank_device.drop();
   h->g_rank_host.drop();
+  h->g_rank_sharded.drop();
   HostWs& w = h->ws;
   const int E = h->M.emb_dim;
   if (max_graphs > w.cap_graphs || max_nodes > w.cap_nodes || max_nnz > w.cap_nnz) {
@@ -842,19 +844,29 @@ int sgnn_apply_adam(SgnnHandle h, float grad_scale, float* loss_dev, void* strea
   return 0;
 }
 
+int sgnn_peer_barrier(SgnnHandle h, void* stream) {
+  if (!h) return 1;
+  if (h->peer_world == 0) return fail(h, "sgnn_peer_barrier: no peer exchange set up (sgnn_peer_create/connect)");
+  for (int r = 0; r < h->peer_world; ++r)
+    if (!h->peer_bufs[r]) return fail(h, "sgnn_peer_barrier: peers not connected");
+  const cudaError_t e = sgnn_launch_peer_barrier(h->peer_rank, h->peer_world, h->peer_bufs, h->d_peer_epoch,
+                                                 (cudaStream_t)stream);
+  if (e != cudaSuccess) return fail(h, std::string("sgnn_peer_barrier: ") + cudaGetErrorString(e));
+  return 0;
+}
+
 int sgnn_apply_adam_allreduce(SgnnHandle h, float grad_scale, float* loss_dev, void* stream) {
   if (!h) return 1;
   if (h->peer_world == 0) return fail(h, "sgnn_apply_adam_allreduce: no peer exchange set up (sgnn_peer_create/connect)");
   for (int r = 0; r < h->peer_world; ++r)
     if (!h->peer_bufs[r]) return fail(h, "sgnn_apply_adam_allreduce: peers not connected");
   h->adam_t += 1;
-  h->peer_gepoch += 1;
   const SgnnConfig& c = h->cfg;
   const double t = (double)h->adam_t;
   const double lr_t = (double)c.learning_rate * std::sqrt(1.0 - std::pow((double)c.beta2, t)) /
                       (1.0 - std::pow((double)c.beta1, t));
   const cudaError_t e = sgnn_launch_peer_adam(h->M.n_params, h->peer_rank, h->peer_world, h->peer_slot_elems,
-                                              h->peer_bufs, h->peer_gepoch, h->peer_done, h->d_params, h->d_grads,
+                                              h->peer_bufs, h->d_peer_epoch, h->peer_done, h->d_params, h->d_grads,
                                               h->d_m, h->d_v, grad_scale, c.weight_decay, (float)lr_t, c.beta1,
                                               c.beta2, c.epsilon, loss_dev, h->sm_count, (cudaStream_t)stream);
   if (e != cudaSuccess) return fail(h, std::string("sgnn_apply_adam_allreduce: ") + cudaGetErrorString(e));
@@ -997,7 +1009,9 @@ int sgnn_peer_destroy(SgnnHandle h) {
     h->peer_bufs[r] = nullptr;
   }
   if (h->peer_done) cudaFree(h->peer_done);
-  h->peer_done = nullptr;
+  if (h->d_peer_epoch) cudaFree(h->d_peer_epoch);
+  h->peer_done = nullptr; h->d_peer_epoch = nullptr;
+  h->g_rank_sharded.drop();
   h->peer_world = 0;
   return 0;
 }
@@ -1008,13 +1022,15 @@ int sgnn_peer_create(SgnnHandle h, int32_t world, int32_t rank, int32_t m_cap, i
   static_assert(sizeof(cudaIpcMemHandle_t) == SGNN_IPC_HANDLE_BYTES, "IPC handle size");
   CUDA_OK(h, cudaSetDevice(h->device));
   sgnn_peer_destroy(h);
-  h->peer_world = world; h->peer_rank = rank; h->peer_epoch = 0; h->peer_gepoch = 0;
+  h->peer_world = world; h->peer_rank = rank;
   h->peer_slot_elems = (int64_t)m_cap * k_cap;
   const int64_t bytes = sgnn_peer_buffer_bytes(world, h->peer_slot_elems, h->M.n_params);
   CUDA_OK(h, cudaMalloc(&h->peer_bufs[rank], (size_t)bytes));
   CUDA_OK(h, cudaMemset(h->peer_bufs[rank], 0, (size_t)bytes));
   CUDA_OK(h, cudaMalloc(reinterpret_cast<void**>(&h->peer_done), sizeof(unsigned int)));
   CUDA_OK(h, cudaMemset(h->peer_done, 0, sizeof(unsigned int)));
+  CUDA_OK(h, cudaMalloc(reinterpret_cast<void**>(&h->d_peer_epoch), 4 * sizeof(unsigned long long)));
+  CUDA_OK(h, cudaMemset(h->d_peer_epoch, 0, 4 * sizeof(unsigned long long)));
   CUDA_OK(h, cudaDeviceSynchronize());
   cudaIpcMemHandle_t hd;
   CUDA_OK(h, cudaIpcGetMemHandle(&hd, h->peer_bufs[rank]));
@@ -1042,12 +1058,42 @@ int sgnn_topk_exchange(SgnnHandle h, const float* vals_dev, const int32_t* ids_d
   for (int r = 0; r < h->peer_world; ++r)
     if (!h->peer_bufs[r]) return fail(h, "sgnn_topk_exchange: peers not connected");
   if ((int64_t)m * k > h->peer_slot_elems) return fail(h, "sgnn_topk_exchange: m * k exceeds the exchange slot");
-  h->peer_epoch += 1;
   const cudaError_t e = sgnn_launch_peer_exchange(vals_dev, ids_dev, m, k, id_offset, h->peer_rank, h->peer_world,
-                                                  h->peer_slot_elems, h->peer_bufs, h->peer_epoch, h->peer_done,
+                                                  h->peer_slot_elems, h->peer_bufs, h->d_peer_epoch, h->peer_done,
                                                   out_ids_dev, out_vals_dev, (cudaStream_t)stream);
   if (e != cudaSuccess) return fail(h, std::string("sgnn_topk_exchange: ") + cudaGetErrorString(e));
   return 0;
+}
+
+int sgnn_rank_sharded(SgnnHandle h, const SgnnGraphBatch* q_dev, const SgnnGraphBatch* db_dev, int32_t k,
+                      int32_t id_offset, float* emb_q_dev, float* emb_db_dev, float* sim_dev, int64_t ld,
+                      int32_t* local_ids_dev, float* local_vals_dev, int32_t* out_ids_dev, float* out_vals_dev,
+                      void* stream) {
+  if (!h || !q_dev || !db_dev || !emb_q_dev || !emb_db_dev || !sim_dev || !local_ids_dev || !local_vals_dev ||
+      !out_ids_dev)
+    return fail(h, "sgnn_rank_sharded: null argument");
+  if (k <= 0) return fail(h, "sgnn_rank_sharded: k must be positive");
+  if (h->peer_world == 0) return fail(h, "sgnn_rank_sharded: no peer exchange set up (sgnn_peer_create/connect)");
+  const int m = q_dev->n_graphs;
+  cudaStream_t st = (cudaStream_t)stream;
+  auto body = [&]() -> int {
+    const bool saved = h->use_graphs;
+    h->use_graphs = false;   // the inner entry points run inline: this call is the unit that is captured
+    int rc = sgnn_rank_device(h, q_dev, db_dev, k, emb_q_dev, emb_db_dev, sim_dev, ld, local_ids_dev, local_vals_dev,
+                              stream);
+    if (!rc) rc = sgnn_topk_exchange(h, local_vals_dev, local_ids_dev, m, k, id_offset, out_ids_dev, out_vals_dev, stream);
+    h->use_graphs = saved;
+    return rc;
+  };
+  uint64_t kb[26] = {};
+  key_batch(kb, q_dev);
+  key_batch(kb + 7, db_dev);
+  kb[14] = (uint64_t)k; kb[15] = (uint64_t)(uintptr_t)emb_q_dev; kb[16] = (uint64_t)(uintptr_t)emb_db_dev;
+  kb[17] = (uint64_t)(uintptr_t)sim_dev; kb[18] = (uint64_t)ld; kb[19] = (uint64_t)(uintptr_t)local_ids_dev;
+  kb[20] = (uint64_t)(uintptr_t)local_vals_dev; kb[21] = (uint64_t)(uintptr_t)st;
+  kb[22] = (uint64_t)(uint32_t)id_offset; kb[23] = (uint64_t)(uintptr_t)out_ids_dev;
+  kb[24] = (uint64_t)(uintptr_t)out_vals_dev; kb[25] = (uint64_t)(uintptr_t)h->peer_bufs[h->peer_rank];
+  return run_cached(h, h->g_rank_sharded, fnv1a(kb, sizeof(kb)), st, body);
 }
 
 int sgnn_debug_slice_hints(SgnnHandle h, unsigned long long** hints_dev, int64_t* capacity) {

@@ -14,12 +14,14 @@ cudaError_t sgnn_launch_topk_hint(const float* sim, const unsigned long long* sm
 // push the local top-k into every peer's exchange buffer, then merge the world * k candidates (sgnn_peer.cuh)
 cudaError_t sgnn_launch_peer_exchange(const float* vals, const int32_t* ids, int m, int k, int id_offset, int rank,
                                       int world, int64_t slot_elems, void* const* peer_bufs,
-                                      unsigned long long epoch, unsigned int* done_counter, int32_t* out_ids,
+                                      unsigned long long* epoch_ctr, unsigned int* done_counter, int32_t* out_ids,
                                       float* out_vals, cudaStream_t st);
+cudaError_t sgnn_launch_peer_barrier(int rank, int world, void* const* peer_bufs, unsigned long long* epoch_ctr,
+                                     cudaStream_t st);
 int64_t sgnn_peer_buffer_bytes(int world, int64_t slot_elems, int n_params);
 // push the local gradient blob to every peer, then Adam on the rank-ordered sum of the world slots (sgnn_peer.cuh)
 cudaError_t sgnn_launch_peer_adam(int n, int rank, int world, int64_t slot_elems, void* const* peer_bufs,
-                                  unsigned long long epoch, unsigned int* done_counter, float* params, float* grads,
+                                  unsigned long long* epoch_ctr, unsigned int* done_counter, float* params, float* grads,
                                   float* m, float* v, float grad_scale, float wd, float lr_t, float b1, float b2,
                                   float eps, float* loss, int sm_count, cudaStream_t st);
 cudaError_t sgnn_launch_sort_rows(const float* sim, int m, int n, int64_t ld, int32_t* ids, int smem_optin,

@@ -11,6 +11,7 @@
 //
 // Exchange buffer of one rank (device memory of that rank, opened by every peer):
 //   u64 flags[2][PEER_MAX_WORLD]            epoch of the newest complete push of sender r, per parity
+//   u64 bflags[PEER_MAX_WORLD]              device-side barrier (sgnn_peer_barrier): arrival epoch of rank r
 //   u64 cand[2][world][m_cap * k_cap]       (orderable score << 32 | global id) keys, per parity
 // Parity = epoch & 1 double-buffers the slots: a sender can only be one epoch ahead of a receiver
 // (it needs the receiver's flag of epoch e before it finishes epoch e), so the slot it overwrites at
@@ -19,7 +20,7 @@
 #include "sgnn_rank.cuh"
 
 constexpr int PEER_MAX_WORLD = 16;
-constexpr size_t PEER_HEADER_BYTES = 2 * PEER_MAX_WORLD * sizeof(unsigned long long);
+constexpr size_t PEER_HEADER_BYTES = 3 * PEER_MAX_WORLD * sizeof(unsigned long long);
 
 struct PeerPtrs {
   unsigned long long* base[PEER_MAX_WORLD];   // exchange buffer of every rank (own included)
@@ -34,12 +35,28 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
   return v;
 }
 
+// Stream-ordered barrier between the ranks, no host involvement: arrive at every peer, wait for every peer.
+// Epochs live in DEVICE memory (epoch_ctr[0] candidates, [1] gradients, [2] barrier) and are advanced by the
+// kernels themselves, so the launches carry no per-step host argument and can sit inside a CUDA graph.
+__global__ void peer_barrier_kernel(int rank, int world, PeerPtrs P, unsigned long long* epoch_ctr) {
+  const unsigned long long epoch = *epoch_ctr + 1;
+  __syncwarp();
+  if (threadIdx.x == 0) *epoch_ctr = epoch;
+  if ((int)threadIdx.x < world) {
+    __threadfence_system();
+    st_release_sys(P.base[threadIdx.x] + 2 * PEER_MAX_WORLD + rank, epoch);
+    const unsigned long long* f = P.base[rank] + 2 * PEER_MAX_WORLD + threadIdx.x;
+    while (ld_acquire_sys(f) < epoch) __nanosleep(32);
+  }
+}
+
 // Every rank: local candidates -> slot `rank` of every peer, then the epoch flag.  done_counter is a
 // local device word (zero before and after each launch).
 __global__ void __launch_bounds__(256)
 peer_push_kernel(const float* __restrict__ vals, const int32_t* __restrict__ ids, int count, int id_offset,
-                 int rank, int world, int64_t slot_elems, PeerPtrs P, unsigned long long epoch,
+                 int rank, int world, int64_t slot_elems, PeerPtrs P, unsigned long long* epoch_ctr,
                  unsigned int* __restrict__ done_counter) {
+  const unsigned long long epoch = *epoch_ctr + 1;   // advanced by the last CTA, after every CTA has read it
   const int parity = (int)(epoch & 1ull);
   const size_t slot = PEER_HEADER_BYTES / 8 + ((size_t)parity * world + rank) * slot_elems;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
@@ -54,6 +71,7 @@ peer_push_kernel(const float* __restrict__ vals, const int32_t* __restrict__ ids
       *done_counter = 0u;
       __threadfence_system();
       for (int r = 0; r < world; ++r) st_release_sys(P.base[r] + parity * PEER_MAX_WORLD + rank, epoch);
+      *epoch_ctr = epoch;
     }
   }
 }
@@ -62,8 +80,10 @@ peer_push_kernel(const float* __restrict__ vals, const int32_t* __restrict__ ids
 // each row (keys are unique: the global id is part of the key).  One warp per row.
 __global__ void __launch_bounds__(256)
 peer_merge_kernel(const unsigned long long* __restrict__ mine, int m, int k, int world, int64_t slot_elems,
-                  unsigned long long epoch, int32_t* __restrict__ ids, float* __restrict__ vals) {
+                  const unsigned long long* __restrict__ epoch_ctr, int32_t* __restrict__ ids,
+                  float* __restrict__ vals) {
   extern __shared__ unsigned long long s_keys[];   // [8 warps][world * k]
+  const unsigned long long epoch = *epoch_ctr;     // the push kernel ahead of us in the stream advanced it
   const int parity = (int)(epoch & 1ull);
   if (threadIdx.x < world) {
     const unsigned long long* f = mine + parity * PEER_MAX_WORLD + threadIdx.x;
@@ -101,7 +121,8 @@ peer_merge_kernel(const unsigned long long* __restrict__ mine, int m, int k, int
 //   u64 gflags[2][PEER_MAX_WORLD]; float grad[2][world][n_pad]
 __global__ void __launch_bounds__(256)
 peer_grad_push_kernel(const float* __restrict__ grads, int n, int n_pad, int rank, int world, size_t goff,
-                      PeerPtrs P, unsigned long long epoch, unsigned int* __restrict__ done_counter) {
+                      PeerPtrs P, unsigned long long* epoch_ctr, unsigned int* __restrict__ done_counter) {
+  const unsigned long long epoch = *epoch_ctr + 1;
   const int parity = (int)(epoch & 1ull);
   const size_t slot = (size_t)(parity * world + rank) * n_pad;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -117,6 +138,7 @@ peer_grad_push_kernel(const float* __restrict__ grads, int n, int n_pad, int ran
       *done_counter = 0u;
       __threadfence_system();
       for (int r = 0; r < world; ++r) st_release_sys(P.base[r] + goff + parity * PEER_MAX_WORLD + rank, epoch);
+      *epoch_ctr = epoch;
     }
   }
 }
@@ -124,9 +146,11 @@ peer_grad_push_kernel(const float* __restrict__ grads, int n, int n_pad, int ran
 // weight decay gradient + TF-1 Adam (as adam_kernel) on the sum of the world gradient slots
 __global__ void __launch_bounds__(256)
 adam_peer_kernel(int n, int n_pad, int world, const unsigned long long* __restrict__ mine, size_t goff,
-                 unsigned long long epoch, float* __restrict__ params, float* __restrict__ grads,
+                 const unsigned long long* __restrict__ epoch_ctr, float* __restrict__ params,
+                 float* __restrict__ grads,
                  float* __restrict__ m, float* __restrict__ v, float grad_scale, float wd, float lr_t, float b1,
                  float b2, float eps, float* __restrict__ loss) {
+  const unsigned long long epoch = *epoch_ctr;
   const int parity = (int)(epoch & 1ull);
   if (threadIdx.x < world) {
     const unsigned long long* f = mine + goff + parity * PEER_MAX_WORLD + threadIdx.x;

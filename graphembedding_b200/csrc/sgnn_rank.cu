@@ -84,7 +84,7 @@ extern "C" int sgnn_debug_topk_trace(int* out, int n) {
 
 cudaError_t sgnn_launch_peer_exchange(const float* vals, const int32_t* ids, int m, int k, int id_offset, int rank,
                                       int world, int64_t slot_elems, void* const* peer_bufs,
-                                      unsigned long long epoch, unsigned int* done_counter, int32_t* out_ids,
+                                      unsigned long long* epoch_ctr, unsigned int* done_counter, int32_t* out_ids,
                                       float* out_vals, cudaStream_t st) {
   if (world < 1 || world > PEER_MAX_WORLD || (int64_t)m * k > slot_elems) return cudaErrorInvalidValue;
   PeerPtrs P;
@@ -92,13 +92,23 @@ cudaError_t sgnn_launch_peer_exchange(const float* vals, const int32_t* ids, int
     P.base[r] = r < world ? static_cast<unsigned long long*>(peer_bufs[r]) : nullptr;
   const int count = m * k;
   const int blocks = std::max(1, std::min(64, (count + 255) / 256));
-  peer_push_kernel<<<blocks, 256, 0, st>>>(vals, ids, count, id_offset, rank, world, slot_elems, P, epoch,
+  peer_push_kernel<<<blocks, 256, 0, st>>>(vals, ids, count, id_offset, rank, world, slot_elems, P, epoch_ctr,
                                            done_counter);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   const size_t smem = (size_t)8 * world * k * sizeof(unsigned long long);
   if (smem > 48 * 1024) return cudaErrorInvalidValue;
-  peer_merge_kernel<<<(m + 7) / 8, 256, smem, st>>>(P.base[rank], m, k, world, slot_elems, epoch, out_ids, out_vals);
+  peer_merge_kernel<<<(m + 7) / 8, 256, smem, st>>>(P.base[rank], m, k, world, slot_elems, epoch_ctr, out_ids, out_vals);
+  return cudaGetLastError();
+}
+
+cudaError_t sgnn_launch_peer_barrier(int rank, int world, void* const* peer_bufs, unsigned long long* epoch_ctr,
+                                     cudaStream_t st) {
+  if (world < 1 || world > PEER_MAX_WORLD) return cudaErrorInvalidValue;
+  PeerPtrs P;
+  for (int r = 0; r < PEER_MAX_WORLD; ++r)
+    P.base[r] = r < world ? static_cast<unsigned long long*>(peer_bufs[r]) : nullptr;
+  peer_barrier_kernel<<<1, 32, 0, st>>>(rank, world, P, epoch_ctr + 2);
   return cudaGetLastError();
 }
 
@@ -113,7 +123,7 @@ int64_t sgnn_peer_buffer_bytes(int world, int64_t slot_elems, int n_params) {
 }
 
 cudaError_t sgnn_launch_peer_adam(int n, int rank, int world, int64_t slot_elems, void* const* peer_bufs,
-                                  unsigned long long epoch, unsigned int* done_counter, float* params, float* grads,
+                                  unsigned long long* epoch_ctr, unsigned int* done_counter, float* params, float* grads,
                                   float* m, float* v, float grad_scale, float wd, float lr_t, float b1, float b2,
                                   float eps, float* loss, int sm_count, cudaStream_t st) {
   if (world < 1 || world > PEER_MAX_WORLD) return cudaErrorInvalidValue;
@@ -123,10 +133,10 @@ cudaError_t sgnn_launch_peer_adam(int n, int rank, int world, int64_t slot_elems
   const int n_pad = (n + 3) / 4 * 4;
   const size_t goff = (size_t)sgnn_peer_grad_offset(world, slot_elems);
   const int blocks = std::max(1, std::min((n + 255) / 256, sm_count));
-  peer_grad_push_kernel<<<blocks, 256, 0, st>>>(grads, n, n_pad, rank, world, goff, P, epoch, done_counter);
+  peer_grad_push_kernel<<<blocks, 256, 0, st>>>(grads, n, n_pad, rank, world, goff, P, epoch_ctr + 1, done_counter);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
-  adam_peer_kernel<<<blocks, 256, 0, st>>>(n, n_pad, world, P.base[rank], goff, epoch, params, grads, m, v, grad_scale,
+  adam_peer_kernel<<<blocks, 256, 0, st>>>(n, n_pad, world, P.base[rank], goff, epoch_ctr + 1, params, grads, m, v, grad_scale,
                                            wd, lr_t, b1, b2, eps, loss);
   return cudaGetLastError();
 }

@@ -84,6 +84,10 @@ class PeerTopk(object):
     def exchange(self, local_vals, local_ids, id_offset, out_ids=None, out_vals=None):
         return self.engine.topk_exchange(local_vals, local_ids, id_offset, out_ids=out_ids, out_vals=out_vals)
 
+    def barrier(self):
+        """Device-side, stream-ordered barrier between the ranks (no host synchronisation)."""
+        self.engine.peer_barrier()
+
     def adam_allreduce(self, grad_scale=1.0, loss=None):
         """DP optimiser step: gradient push + Adam on the rank-ordered sum of the world blobs."""
         self.engine.apply_adam_allreduce(grad_scale, loss)
@@ -106,10 +110,13 @@ def merge_topk_host(cand_vals, cand_ids, k):
 
 
 def sharded_rank(engine, queries_dev, db_shard_dev, id_offset, k, dist=None, group=None, emb_q=None,
-                 emb_db=None, sim=None, peer=None, ids=None, vals=None):
+                 emb_db=None, sim=None, peer=None, ids=None, vals=None, out_ids=None, out_vals=None):
     """One database-sharded ranking step on this rank: embed, score the local tile, local top-k,
     candidate exchange + merge (``peer``: a PeerTopk; else all-gather + merge kernel).  Returns
     (ids, vals) of the global top-k (identical on every rank)."""
+    if peer is not None:   # one replayable unit: local ranking + push + merge
+        return engine.rank_sharded(queries_dev, db_shard_dev, k, id_offset, emb_q=emb_q, emb_db=emb_db, sim=sim,
+                                   ids=ids, vals=vals, out_ids=out_ids, out_vals=out_vals)
     ids, vals, sim = engine.rank_device(queries_dev, db_shard_dev, k, emb_q=emb_q, emb_db=emb_db, sim=sim,
                                         ids=ids, vals=vals)
     world = dist.get_world_size(group) if dist is not None and dist.is_initialized() else 1

@@ -176,6 +176,9 @@ class SgnnEngine(object):
         if getattr(self, 'h', None):
             lib().sgnn_peer_destroy(self.h)
 
+    def peer_barrier(self, stream=None):
+        check(self.h, lib().sgnn_peer_barrier(self.h, _stream_ptr(stream)))
+
     def topk_exchange(self, vals, ids, id_offset, out_ids=None, out_vals=None, stream=None):
         """Push the local top-k (LOCAL ids + id_offset) to every peer and merge: global (ids, vals)."""
         import torch
@@ -304,6 +307,28 @@ class SgnnEngine(object):
                                              _ptr(sim), sim.stride(0), _ptr(ids), _ptr(vals), _stream_ptr(stream)))
         self.launches += 6 if k > 0 else 5   # 2 embeds, 2 operand preps, scorer, top-k
         return ids, vals, sim
+
+    def rank_sharded(self, queries, db_shard, k, id_offset, emb_q=None, emb_db=None, sim=None, ids=None, vals=None,
+                     out_ids=None, out_vals=None, stream=None):
+        """Collective (peer_create/connect first): rank this rank's database shard, exchange the candidates over
+        peer memory, merge.  One CUDA-graph launch per call once the buffers repeat.  Returns global (ids, vals)."""
+        import torch
+        m, n, E = queries.n_graphs, db_shard.n_graphs, self.emb_dim
+        dev = self.device
+        f32, i32 = torch.float32, torch.int32
+        emb_q = torch.empty((m, E), dtype=f32, device=dev) if emb_q is None else emb_q
+        emb_db = torch.empty((n, E), dtype=f32, device=dev) if emb_db is None else emb_db
+        sim = torch.empty((m, n), dtype=f32, device=dev) if sim is None else sim
+        ids = torch.empty((m, k), dtype=i32, device=dev) if ids is None else ids
+        vals = torch.empty((m, k), dtype=f32, device=dev) if vals is None else vals
+        out_ids = torch.empty((m, k), dtype=i32, device=dev) if out_ids is None else out_ids
+        out_vals = torch.empty((m, k), dtype=f32, device=dev) if out_vals is None else out_vals
+        sq, sd = queries.struct(), db_shard.struct()
+        check(self.h, lib().sgnn_rank_sharded(self.h, C.byref(sq), C.byref(sd), int(k), int(id_offset), _ptr(emb_q),
+                                              _ptr(emb_db), _ptr(sim), sim.stride(0), _ptr(ids), _ptr(vals),
+                                              _ptr(out_ids), _ptr(out_vals), _stream_ptr(stream)))
+        self.launches += 8   # 2 embeds, 2 operand preps, scorer, top-k, push, merge
+        return out_ids, out_vals
 
     def rank_host(self, queries, db, k, ids=None, vals=None, sim=None):
         m = queries.n_graphs

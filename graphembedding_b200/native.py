@@ -88,6 +88,8 @@ SIGNATURES = {
     'sgnn_peer_connect': (C.c_int, [_P, _P]),
     'sgnn_topk_exchange': (C.c_int, [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P]),
     'sgnn_peer_destroy': (C.c_int, [_P]),
+    'sgnn_rank_sharded': (C.c_int, [_P, _BP, _BP, _I32, _I32, _P, _P, _P, _I64, _P, _P, _P, _P, _P]),
+    'sgnn_peer_barrier': (C.c_int, [_P, _P]),
     'sgnn_apply_adam_allreduce': (C.c_int, [_P, _F, _P, _P]),
     'sgnn_debug_slice_hints': (C.c_int, [_P, _P, _P]),
     'sgnn_rank_host': (C.c_int, [_P, _BP, _BP, _I32, _P, _P, _P]),

@@ -242,6 +242,15 @@ int sgnn_peer_connect(SgnnHandle h, const uint8_t* all_handles);
 int sgnn_topk_exchange(SgnnHandle h, const float* vals_dev, const int32_t* ids_dev, int32_t m, int32_t k,
                        int32_t id_offset, int32_t* out_ids_dev, float* out_vals_dev, void* stream);
 int sgnn_peer_destroy(SgnnHandle h);
+/* sgnn_rank_device on this rank's database shard + sgnn_topk_exchange, as ONE replayable unit (the exchange
+ * epochs live in device memory, so the whole sharded step is a single CUDA graph launch per rank). */
+int sgnn_rank_sharded(SgnnHandle h, const SgnnGraphBatch* q_dev, const SgnnGraphBatch* db_shard_dev, int32_t k,
+                      int32_t id_offset, float* emb_q_dev, float* emb_db_dev, float* sim_dev, int64_t ld,
+                      int32_t* local_ids_dev, float* local_vals_dev, int32_t* out_ids_dev, float* out_vals_dev,
+                      void* stream);
+/* Stream-ordered barrier between the ranks (one tiny kernel: arrive at every peer, wait for every peer);
+ * collective.  Work enqueued after it starts on all GPUs within a few microseconds of each other. */
+int sgnn_peer_barrier(SgnnHandle h, void* stream);
 /* Data-parallel optimiser step over the same peer buffers: every rank pushes its flat gradient blob
  * (sgnn_train_step output) into every peer's buffer and applies sgnn_apply_adam to the RANK-ORDERED SUM
  * of the world blobs, read in place by the Adam kernel (all ranks apply bit-identical updates; no

@@ -83,6 +83,10 @@ struct SgnnHandle_t {
   uint64_t drop_seed = 0, drop_counter = 0;   // dropout stream: one counter value per train/eval call
   float *d_rowsA = nullptr, *d_rowsB = nullptr;   // large-graph path: node-row activations (global workspace)
   int64_t cap_rows = 0;                           // in node rows
+  // histogram head: last node-level rows of the query / database side of the ranking entry points
+  float* d_hnodes[2] = {nullptr, nullptr};
+  int64_t cap_hnodes = 0;                         // in node rows, each side
+  struct NodeSide { const float* rows; const int32_t* node_off; int max_nodes; } hside[2] = {};
   float *d_P = nullptr, *d_C = nullptr;  // all-pairs query tables
   int64_t cap_P = 0;
   __nv_bfloat16 *d_Atc = nullptr, *d_Btc = nullptr;  // tensor-core operands in UMMA tile order
@@ -122,8 +126,8 @@ BatchDev to_dev(const SgnnGraphBatch* b) {
 }
 
 const char* kind_name(int k) {
-  static const char* names[] = {"GraphConvolution", "Dense", "Padding", "Average", "Attention", "NTN", "Dot"};
-  return (k >= 0 && k <= 6) ? names[k] : "?";
+  static const char* names[] = {"GraphConvolution", "Dense", "Padding", "Average", "Attention", "NTN", "Dot", "Histogram"};
+  return (k >= 0 && k <= 7) ? names[k] : "?";
 }
 
 // Validate the layer chain and lay the flat parameter blob out in the reference's variable
@@ -135,7 +139,7 @@ int build_model(const SgnnConfig& c, ModelDev& M, std::vector<SgnnParamInfo>& ta
   if (c.input_dim < 1) { err = "input_dim must be >= 1"; return 1; }
   if (!(c.dropout >= 0.f && c.dropout < 1.f)) { err = "dropout must be in [0, 1)"; return 1; }
   int64_t off = 0;
-  int cur = c.input_dim, stage = 0, act_cols = 0, dmax = 4, aux = 0;
+  int cur = c.input_dim, stage = 0, act_cols = 0, dmax = 4, aux = 0, head_cols = 0;
   auto add = [&](int layer, const char* name, int nd, int s0, int s1, int s2) {
     SgnnParamInfo p; memset(&p, 0, sizeof(p));
     p.layer = layer; strncpy(p.name, name, sizeof(p.name) - 1); p.ndim = nd;
@@ -146,7 +150,25 @@ int build_model(const SgnnConfig& c, ModelDev& M, std::vector<SgnnParamInfo>& ta
   M.pool_kind = -1; M.pair_kind = -1;
   for (int i = 0; i < c.num_layers; ++i) {
     const SgnnLayerDesc& d = c.layers[i];
-    if (d.kind == SGNN_LAYER_GCN || d.kind == SGNN_LAYER_DENSE) {
+    if (d.kind == SGNN_LAYER_DENSE && stage == 2) {   // SimGNN-style head: Dense on the pair row (sgnn.h)
+      if (M.pair_kind != SGNN_LAYER_NTN) { err = "a Dense head needs an NTN pair layer"; return 1; }
+      if (M.n_head == SGNN_MAX_HEAD) { err = "at most 6 Dense layers after the NTN"; return 1; }
+      if (d.input_dim != cur) { err = "layer " + std::to_string(i) + ": input_dim does not match the previous width"; return 1; }
+      if (d.output_dim < 1 || d.output_dim > 128) { err = "output_dim must be in [1, 128]"; return 1; }
+      LayerDev& L = M.Hd[M.n_head];
+      L.kind = d.kind; L.din = d.input_dim; L.dout = d.output_dim; L.act = d.act; L.bias = d.bias;
+      L.drop = d.dropout && c.dropout > 0.f; L.ref = i;
+      L.w_off = add(i, "weights", 2, L.din, L.dout, 1);
+      L.b_off = d.bias ? add(i, "bias", 1, L.dout, 1, 1) : 0;
+      L.out_off = head_cols; head_cols += round_up(L.dout, 4);
+      cur = L.dout; ++M.n_head;
+    } else if (d.kind == SGNN_LAYER_HISTOGRAM) {
+      if (stage != 2 || M.pair_kind != SGNN_LAYER_NTN || M.n_head != 0 || M.hist_bins != 0) {
+        err = "Histogram must directly follow the NTN layer"; return 1;
+      }
+      if (d.aux < 1 || d.aux > 32) { err = "Histogram: bins must be in [1, 32]"; return 1; }
+      M.hist_bins = d.aux; cur = M.K + d.aux; head_cols = round_up(cur, 4);
+    } else if (d.kind == SGNN_LAYER_GCN || d.kind == SGNN_LAYER_DENSE) {
       if (stage != 0) { err = std::string(kind_name(d.kind)) + " after the pooling layer is not supported"; return 1; }
       if (i == 0 && d.kind != SGNN_LAYER_GCN) { err = "layer_0 must be GraphConvolution (model_mse.py:97)"; return 1; }
       if (d.input_dim != cur) { err = "layer " + std::to_string(i) + ": input_dim does not match the previous width"; return 1; }
@@ -175,7 +197,8 @@ int build_model(const SgnnConfig& c, ModelDev& M, std::vector<SgnnParamInfo>& ta
         }
       }
     } else if (d.kind == SGNN_LAYER_NTN || d.kind == SGNN_LAYER_DOT) {
-      if (stage != 1 || i != c.num_layers - 1) { err = "the pair layer (NTN/Dot) must be last and follow a pooling layer"; return 1; }
+      if (stage != 1) { err = "the pair layer (NTN/Dot) must follow a pooling layer"; return 1; }
+      if (d.kind == SGNN_LAYER_DOT && i != c.num_layers - 1) { err = "Dot must be the last layer"; return 1; }
       M.pair_kind = d.kind; M.D = M.emb_dim; stage = 2;
       if (d.kind == SGNN_LAYER_NTN) {
         if (d.input_dim != M.emb_dim) { err = "NTN: input_dim must equal the flattened representation width"; return 1; }
@@ -187,6 +210,7 @@ int build_model(const SgnnConfig& c, ModelDev& M, std::vector<SgnnParamInfo>& ta
         M.v_off = add(i, "weights_V", 2, M.K, 2 * M.D, 1);
         M.u_off = add(i, "weights_U", 2, M.K, 1, 1);
         M.b_off = d.bias ? add(i, "bias", 1, M.K, 1, 1) : 0;
+        cur = M.K; head_cols = round_up(M.K, 4);
       } else {
         M.K = 1; M.pair_act = SGNN_ACT_IDENTITY;
       }
@@ -194,7 +218,11 @@ int build_model(const SgnnConfig& c, ModelDev& M, std::vector<SgnnParamInfo>& ta
       err = "Unknown layer kind " + std::to_string(d.kind); return 1;
     }
   }
-  if (stage != 2) { err = "the layer chain must end with NTN or Dot"; return 1; }
+  if (stage != 2) { err = "the layer chain must end with NTN or Dot (or an NTN followed by a Histogram / Dense head)"; return 1; }
+  if (M.hist_bins > 0 && M.n_head == 0) { err = "Histogram must be followed by a Dense head"; return 1; }
+  if (M.n_head > 0 && M.Hd[M.n_head - 1].dout != 1) { err = "the Dense head must end with output_dim=1"; return 1; }
+  M.head_in = M.n_head > 0 ? M.K + M.hist_bins : 0;
+  M.head_floats = M.n_head > 0 ? head_cols : 0;
   if (M.emb_dim > 64) { err = "flattened representation wider than 64 is not supported"; return 1; }
   M.final_act = c.final_act; M.yeta = c.yeta; M.ntn_mode = c.ntn_mode; M.loss_mode = c.loss_mode;
   M.keep = 1.0f - c.dropout; M.inv_keep = 1.0f / M.keep;
@@ -256,6 +284,8 @@ int plan_launches(SgnnHandle h) {
   h->team_smem32 = team_smem_floats(M, 32) * sizeof(float);
   h->use_team = h->team_smem32 <= budget;
   if (const char* tk = getenv("SGNN_TRAIN_KERNEL")) h->use_team = h->use_team && strcmp(tk, "warp") != 0;
+  if (M.n_head > 0 && !h->use_team)
+    return fail(h, "a model with a Dense / Histogram head needs the CTA-per-pair training kernel, which does not fit shared memory");
   if (h->use_team) {
     if (set_smem(h, train_team_kernel<true>, h->team_smem32)) return 1;
     if (set_smem(h, train_team_kernel<false>, h->team_smem32)) return 1;
@@ -349,7 +379,7 @@ int score_and_topk(SgnnHandle h, const float* emb_q, int m, const float* emb_db,
   const int n_slices = tc_n_slices(n);
   const bool want_topk = k > 0 && ids;
   // hinted kernels: warp per row for k <= 32 and 1024..32768 columns, CTA per row for k <= 256 and >= 8192
-  const bool hint = want_topk && h->cfg.precision != SGNN_PREC_FP32 && (int64_t)m * n_slices <= h->cap_smax &&
+  const bool hint = want_topk && h->cfg.precision != SGNN_PREC_FP32 && h->M.n_head == 0 && (int64_t)m * n_slices <= h->cap_smax &&
                     ((k <= 32 && n_slices >= 32 && n_slices <= 1024) || (k <= 256 && n_slices >= 256));
   if (score_all_pairs_stages(h, emb_q, m, emb_db, n, sim, ld, st, stages, hint ? h->d_smax : nullptr)) return 1;
   if (!want_topk) return 0;
@@ -366,6 +396,25 @@ int score_all_pairs_stages(SgnnHandle h, const float* emb_q, int32_t m, const fl
   if (ensure_query_tables(h, m)) return 1;
   const ModelDev& M = h->M;
   const int K = M.pair_kind == SGNN_LAYER_NTN ? M.K : 1;
+  if (M.n_head > 0) {   // SimGNN-style head: CUDA-core kernel (sgnn_head.cu), fp32 whatever cfg.precision says
+    if (stages & SCORE_PREP_Q) {
+      allpairs_prep_kernel<<<(m + 3) / 4, 128, 0, st>>>(M, h->d_params, emb_q, m, h->dep, h->d_P, h->d_C);
+      CUDA_OK(h, cudaGetLastError());
+    }
+    if (!(stages & SCORE_MAIN)) return 0;
+    if (M.hist_bins > 0 && (!h->hside[0].rows || !h->hside[1].rows))
+      return fail(h, "the model has a Histogram layer: all-pairs scoring needs the node rows of both sides "
+                     "(sgnn_score_all_pairs_nodes, or the sgnn_rank_* entry points)");
+    const cudaError_t e = sgnn_launch_allpairs_head(M, h->dep, h->d_params, h->d_P, h->d_C, emb_db, h->hside[0].rows,
+                                                    h->hside[0].node_off, h->hside[0].max_nodes, h->hside[1].rows,
+                                                    h->hside[1].node_off, h->hside[1].max_nodes, m, n, sim_dev, ld,
+                                                    h->sm_count, h->smem_optin, st);
+    if (e == cudaErrorInvalidValue)
+      return fail(h, "all-pairs head kernel: unsupported shape (head widths and node_dim must be <= 32, embedding <= 32, "
+                     "and one graph's node rows must fit shared memory)");
+    if (e != cudaSuccess) return fail(h, std::string("all-pairs head kernel: ") + cudaGetErrorString(e));
+    return 0;
+  }
   if (h->cfg.precision != SGNN_PREC_FP32) return score_all_pairs_tc(h, emb_q, m, emb_db, n, sim_dev, ld, st, stages, smax);
   const int DEP = h->dep;
   if (stages & SCORE_PREP_Q) {
@@ -448,6 +497,39 @@ int run_cached(SgnnHandle h, GraphCache& cache, uint64_t key, cudaStream_t st, F
 }
 }  // namespace
 
+namespace {
+// pooled embeddings AND last node-level rows of a batch in one pass (node_out may be NULL)
+int embed_nodes(SgnnHandle h, const SgnnGraphBatch* b, float* emb_dev, float* node_out, cudaStream_t st) {
+  if (b->n_graphs == 0) return 0;
+  if (b->max_nodes <= 32) {
+    const cudaError_t e = sgnn_launch_embed_tile(h->M, to_dev(b), b->max_nodes, h->d_params, emb_dev, node_out,
+                                                 h->sm_count, h->smem_optin, st);
+    if (e == cudaSuccess) return 0;
+    if (e != cudaErrorInvalidValue) return fail(h, std::string("embedding (tile kernel): ") + cudaGetErrorString(e));
+    cudaGetLastError();
+  }
+  if (b->total_nodes > h->cap_rows)
+    return fail(h, "node-row workspace too small: call sgnn_reserve(max_nodes >= total_nodes) first");
+  const cudaError_t e = sgnn_launch_embed_large(h->M, to_dev(b), h->d_params, h->d_rowsA, h->d_rowsB, emb_dev, node_out,
+                                                h->sm_count, h->smem_optin, st);
+  if (e != cudaSuccess) return fail(h, std::string("embedding (large-graph path): ") + cudaGetErrorString(e));
+  return 0;
+}
+
+// embedding of one side (0 = queries, 1 = database) of a ranking entry point; with a Histogram head the
+// side's node rows are kept for the all-pairs head kernel
+int embed_side(SgnnHandle h, const SgnnGraphBatch* b, float* emb_dev, int side, cudaStream_t st) {
+  if (h->M.hist_bins == 0) return sgnn_embed_graphs(h, b, emb_dev, st);
+  if (b->total_nodes > h->cap_hnodes)
+    return fail(h, "node-row workspace of the histogram head too small: call sgnn_reserve(max_nodes >= total_nodes) first");
+  if (embed_nodes(h, b, emb_dev, h->d_hnodes[side], st)) return 1;
+  h->hside[side].rows = h->d_hnodes[side];
+  h->hside[side].node_off = b->node_off;
+  h->hside[side].max_nodes = b->max_nodes;
+  return 0;
+}
+}  // namespace
+
 extern "C" {
 
 int sgnn_abi_version(void) { return SGNN_ABI_VERSION; }
@@ -503,7 +585,7 @@ int sgnn_destroy(SgnnHandle h) {
   cudaSetDevice(h->device);
   cudaFree(h->d_params); cudaFree(h->d_grads); cudaFree(h->d_m); cudaFree(h->d_v); cudaFree(h->d_loss);
   cudaFree(h->d_P); cudaFree(h->d_C); cudaFree(h->d_Atc); cudaFree(h->d_Btc); cudaFree(h->d_smax);
-  cudaFree(h->d_rowsA); cudaFree(h->d_rowsB);
+  cudaFree(h->d_rowsA); cudaFree(h->d_rowsB); cudaFree(h->d_hnodes[0]); cudaFree(h->d_hnodes[1]);
   HostWs& w = h->ws;
   for (int s = 0; s < 2; ++s) {
     cudaFree(w.node_off[s]); cudaFree(w.labels[s]); cudaFree(w.rowptr[s]); cudaFree(w.col[s]); cudaFree(w.val[s]);
@@ -608,6 +690,11 @@ int sgnn_reserve(SgnnHandle h, int64_t max_graphs, int64_t max_nodes, int64_t ma
     if (dev_alloc(h, &h->d_rowsA, fl) || dev_alloc(h, &h->d_rowsB, fl)) return 1;
     h->cap_rows = max_nodes;
   }
+  if (h->M.hist_bins > 0 && max_nodes > h->cap_hnodes) {
+    const int64_t fl = max_nodes * (int64_t)h->M.node_dim;
+    if (dev_alloc(h, &h->d_hnodes[0], fl) || dev_alloc(h, &h->d_hnodes[1], fl)) return 1;
+    h->cap_hnodes = max_nodes;
+  }
   if (max_pairs > w.cap_pairs) {
     w.cap_pairs = max_pairs;
     if (dev_alloc(h, &w.g1, max_pairs) || dev_alloc(h, &w.g2, max_pairs) || dev_alloc(h, &w.target, max_pairs) ||
@@ -665,7 +752,7 @@ int sgnn_embed_graphs(SgnnHandle h, const SgnnGraphBatch* b, float* emb_dev, voi
     return 0;
   }
   {
-    const cudaError_t e = sgnn_launch_embed_tile(h->M, to_dev(b), b->max_nodes, h->d_params, emb_dev, h->sm_count,
+    const cudaError_t e = sgnn_launch_embed_tile(h->M, to_dev(b), b->max_nodes, h->d_params, emb_dev, nullptr, h->sm_count,
                                                  h->smem_optin, st);
     if (e == cudaSuccess) return 0;
     if (e != cudaErrorInvalidValue) return fail(h, std::string("sgnn_embed_graphs: ") + cudaGetErrorString(e));
@@ -695,6 +782,11 @@ int sgnn_node_embeddings(SgnnHandle h, const SgnnGraphBatch* b, float* node_out_
   return 0;
 }
 
+int sgnn_embed_graphs_nodes(SgnnHandle h, const SgnnGraphBatch* b, float* emb_dev, float* node_out_dev, void* stream) {
+  if (!h || !b || !emb_dev || !node_out_dev) return fail(h, "sgnn_embed_graphs_nodes: null argument");
+  return embed_nodes(h, b, emb_dev, node_out_dev, (cudaStream_t)stream);
+}
+
 int sgnn_pair_histogram(SgnnHandle h, const float* node_emb_dev, const int32_t* node_off_dev, const int32_t* g1_dev,
                         const int32_t* g2_dev, int32_t n_pairs, int32_t bins, float* hist_dev, int32_t* counts_dev,
                         void* stream) {
@@ -710,6 +802,8 @@ int sgnn_pair_histogram(SgnnHandle h, const float* node_emb_dev, const int32_t* 
 int sgnn_score_pairs(SgnnHandle h, const float* emb_dev, const int32_t* g1, const int32_t* g2, int32_t n_pairs,
                      float* raw_dev, float* sim_dev, void* stream) {
   if (!h || !emb_dev || !g1 || !g2) return fail(h, "sgnn_score_pairs: null argument");
+  if (h->M.n_head > 0)
+    return fail(h, "sgnn_score_pairs: the model has a Dense / Histogram head after the NTN; use sgnn_forward_pairs or sgnn_eval_pairs");
   if (n_pairs == 0) return 0;
   const int blocks = std::min((n_pairs + 7) / 8, h->sm_count * 4);
   pair_score_kernel<<<blocks, 256, h->pair_smem, (cudaStream_t)stream>>>(h->M, h->d_params, emb_dev, g1, g2,
@@ -718,8 +812,16 @@ int sgnn_score_pairs(SgnnHandle h, const float* emb_dev, const int32_t* g1, cons
   return 0;
 }
 
+static int launch_pairs(SgnnHandle h, bool bwd, const SgnnGraphBatch* b, const int32_t* g1, const int32_t* g2,
+                        const float* target_sim, int32_t n_pairs, int32_t global_batch, double target_sum,
+                        double target_sqsum, float* loss, float* raw, float* sim, void* stream, bool no_dropout = false);
+
 int sgnn_forward_pairs(SgnnHandle h, const SgnnGraphBatch* b, const int32_t* g1, const int32_t* g2,
                        int32_t n_pairs, float* emb_ws_dev, float* raw_dev, float* sim_dev, void* stream) {
+  if (h && h->M.n_head > 0) {   // head models: the per-pair kernel holds the node rows the histogram needs
+    if (!b || !g1 || !g2) return fail(h, "sgnn_forward_pairs: null argument");
+    return launch_pairs(h, false, b, g1, g2, nullptr, n_pairs, n_pairs, 0.0, 0.0, nullptr, raw_dev, sim_dev, stream, true);
+  }
   if (sgnn_embed_graphs(h, b, emb_ws_dev, stream)) return 1;
   return sgnn_score_pairs(h, emb_ws_dev, g1, g2, n_pairs, raw_dev, sim_dev, stream);
 }
@@ -727,6 +829,18 @@ int sgnn_forward_pairs(SgnnHandle h, const SgnnGraphBatch* b, const int32_t* g1,
 int sgnn_score_all_pairs(SgnnHandle h, const float* emb_q, int32_t m, const float* emb_db, int32_t n,
                          float* sim_dev, int64_t ld, void* stream) {
   if (!h || !emb_q || !emb_db || !sim_dev) return fail(h, "sgnn_score_all_pairs: null argument");
+  h->hside[0].rows = h->hside[1].rows = nullptr;
+  return score_all_pairs_stages(h, emb_q, m, emb_db, n, sim_dev, ld, (cudaStream_t)stream, SCORE_ALL);
+}
+
+int sgnn_score_all_pairs_nodes(SgnnHandle h, const float* emb_q, const float* nodes_q, const int32_t* node_off_q,
+                               int32_t max_nodes_q, int32_t m, const float* emb_db, const float* nodes_db,
+                               const int32_t* node_off_db, int32_t max_nodes_db, int32_t n, float* sim_dev, int64_t ld,
+                               void* stream) {
+  if (!h || !emb_q || !emb_db || !sim_dev || !nodes_q || !node_off_q || !nodes_db || !node_off_db)
+    return fail(h, "sgnn_score_all_pairs_nodes: null argument");
+  h->hside[0].rows = nodes_q; h->hside[0].node_off = node_off_q; h->hside[0].max_nodes = max_nodes_q;
+  h->hside[1].rows = nodes_db; h->hside[1].node_off = node_off_db; h->hside[1].max_nodes = max_nodes_db;
   return score_all_pairs_stages(h, emb_q, m, emb_db, n, sim_dev, ld, (cudaStream_t)stream, SCORE_ALL);
 }
 
@@ -766,7 +880,7 @@ int sgnn_sort_rows(SgnnHandle h, const float* sim_dev, int32_t m, int32_t n, int
 
 static int launch_pairs(SgnnHandle h, bool bwd, const SgnnGraphBatch* b, const int32_t* g1, const int32_t* g2,
                         const float* target_sim, int32_t n_pairs, int32_t global_batch, double target_sum,
-                        double target_sqsum, float* loss, float* raw, float* sim, void* stream) {
+                        double target_sqsum, float* loss, float* raw, float* sim, void* stream, bool no_dropout) {
   if (n_pairs == 0) return 0;
   if (global_batch < n_pairs) return fail(h, "global_batch < n_pairs");
   if (b->max_nodes > 32) return fail(h, "graphs with more than 32 nodes need the large-graph path (not built yet)");
@@ -777,7 +891,7 @@ static int launch_pairs(SgnnHandle h, bool bwd, const SgnnGraphBatch* b, const i
   const float invB = 1.0f / (float)global_batch;
   const float s1 = (float)target_sum, s2 = (float)target_sqsum;
   // dropout is on for train, val and test alike (layers capture FLAGS.dropout as a constant)
-  const int dropping = h->cfg.dropout > 0.f;
+  const int dropping = h->cfg.dropout > 0.f && !no_dropout;
   uint32_t dbase = 0;
   if (dropping) {
     const uint32_t s32 = (uint32_t)(h->drop_seed ^ (h->drop_seed >> 32));
@@ -979,10 +1093,10 @@ int sgnn_rank_device(SgnnHandle h, const SgnnGraphBatch* q_dev, const SgnnGraphB
   auto body = [&]() -> int {
     // fork: the query branch (embed + query-side scorer tables) runs beside the database branch
     CUDA_OK(h, cudaEventRecord(h->chunk_ev[1], st));
-    if (sgnn_embed_graphs(h, db_dev, emb_db_dev, st)) return 1;
+    if (embed_side(h, db_dev, emb_db_dev, 1, st)) return 1;
     if (score_all_pairs_stages(h, emb_q_dev, m, emb_db_dev, n, sim_dev, ld, st, SCORE_PREP_DB)) return 1;
     CUDA_OK(h, cudaStreamWaitEvent(side, h->chunk_ev[1], 0));
-    if (sgnn_embed_graphs(h, q_dev, emb_q_dev, side)) return 1;
+    if (embed_side(h, q_dev, emb_q_dev, 0, side)) return 1;
     if (score_all_pairs_stages(h, emb_q_dev, m, emb_db_dev, n, sim_dev, ld, side, SCORE_PREP_Q)) return 1;
     CUDA_OK(h, cudaEventRecord(h->chunk_ev[2], side));
     CUDA_OK(h, cudaStreamWaitEvent(st, h->chunk_ev[2], 0));   // join
@@ -1122,11 +1236,11 @@ int sgnn_rank_host(SgnnHandle h, const SgnnGraphBatch* q, const SgnnGraphBatch* 
     if (upload_batch_on(h, db, 1, &ddb, cs)) return 1;
     CUDA_OK(h, cudaEventRecord(h->chunk_ev[0], cs));
     if (upload_batch_on(h, q, 0, &dq, st)) return 1;
-    if (sgnn_embed_graphs(h, &dq, w.emb_q, st)) return 1;
+    if (embed_side(h, &dq, w.emb_q, 0, st)) return 1;
     // query-side tables of the scorer are ready before the database lands
     if (score_all_pairs_stages(h, w.emb_q, (int)m, w.emb_db, (int)n, w.sim, n, st, SCORE_PREP_Q)) return 1;
     CUDA_OK(h, cudaStreamWaitEvent(st, h->chunk_ev[0], 0));
-    if (sgnn_embed_graphs(h, &ddb, w.emb_db, st)) return 1;
+    if (embed_side(h, &ddb, w.emb_db, 1, st)) return 1;
     if (score_and_topk(h, w.emb_q, (int)m, w.emb_db, (int)n, w.sim, n, SCORE_PREP_DB | SCORE_MAIN,
                        want_topk ? k : 0, w.topk_ids, w.topk_vals, st))
       return 1;

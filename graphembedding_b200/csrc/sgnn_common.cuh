@@ -33,6 +33,12 @@ struct ModelDev {
   int aux_floats;                // size of the transposed/permuted weight region (train)
   int pair_drop, pair_ref;       // dropout on the pair layer's two inputs (layers.py:287-288)
   float keep, inv_keep;          // keep_prob = 1 - FLAGS.dropout, and 1 / keep_prob
+  // SimGNN-style head (sgnn.h): pair-level layers after the NTN
+  int n_head;                    // Dense layers after the NTN (0 = the NTN's scalar is the raw score)
+  int hist_bins;                 // Histogram layer right after the NTN (0 = none)
+  int head_in;                   // K + hist_bins
+  int head_floats;               // head_in + sum of the head layers' widths, each rounded up to 4
+  LayerDev Hd[SGNN_MAX_HEAD];    // out_off = offset of the layer's output inside the head activation row
 };
 
 struct BatchDev {

@@ -1,0 +1,298 @@
+// All-pairs scoring for models with a SimGNN-style head (include/sgnn.h: NTN K-vector | node-node
+// similarity histogram -> Dense layers).  The head and the histogram are BUILD-DEFINED (absent from the
+// reference snapshot); the NTN slab is layers.py:282-310, the Dense rows
+// layers.py:192-205, the m x n loop train.py:57-61.
+//
+// CUDA-core kernel: thread = one database graph.  The graph's pooled embedding lives in registers, its
+// last node-level rows in a private shared-memory stripe (stride = 4 * odd words, so 16-byte reads by the
+// 32 lanes of a warp hit 32 different bank groups).  The CTA walks a block of queries; per query the
+// factorised NTN tables P'/C (sgnn_allpairs.cuh), the query's node rows and the head weights are read as
+// warp-uniform broadcasts.  Per pair:
+//   f_k   = U_k * inneract(C[q][k] + P'[q][k][:] . x_g)                       (2 D K flops)
+//   s_ij  = sigmoid(Hq_i . Hg_j), bin = min(bins - 1, floor(s_ij * bins))     (2 N_q N_g d flops)
+//   head  = Dense stack on [f | counts / (N_q N_g)]
+// The histogram arithmetic (sequential fmaf dot, 1 / (1 + expf(-s)), floorf) is the same as in
+// pair_histogram_kernel and the training kernel, so all three agree on every bin index; zero padding only
+// ever adds fmaf(x, 0, s) = s terms.  Per-thread bin counters are a private shared-memory column.
+#include <algorithm>
+#include "sgnn_common.cuh"
+#include "sgnn_internal.h"
+
+struct HeadPlan {
+  int threads;       // database graphs per CTA
+  int S;             // words per database-graph stripe (node rows, stride ND each)
+  int nmax_q;        // node rows reserved per staged query
+  int hw_floats;     // head weight region
+  int q_floats;      // one staged query: P' [K][DEP] | C [K] | rows [nmax_q][ND] | n (1, padded to 4)
+  int w0, b0;        // offsets inside the head weight region: layer 0 weights [head_in][H0], bias [H0]
+  int wl, bl;        // later layers: [n_head-1][H0][H0], [n_head-1][H0]
+};
+
+constexpr int HEAD_QC = 4;   // queries staged per round
+
+template <int H0>
+__host__ __device__ inline void head_plan_weights(const ModelDev& M, HeadPlan& P) {
+  int o = round_up4(M.K);          // U
+  P.w0 = o; o += M.head_in * H0;
+  P.b0 = o; o += H0;
+  P.wl = o; o += (M.n_head - 1) * H0 * H0;
+  P.bl = o; o += (M.n_head - 1) * H0;
+  P.hw_floats = o;
+}
+
+template <int DEP, int H0, int ND>
+__global__ void __launch_bounds__(128)
+allpairs_head_kernel(const __grid_constant__ ModelDev M, const __grid_constant__ HeadPlan HP,
+                     const float* __restrict__ params, const float* __restrict__ Pq, const float* __restrict__ Cq,
+                     const float* __restrict__ emb_db, const float* __restrict__ nodes_q,
+                     const int32_t* __restrict__ node_off_q, const float* __restrict__ nodes_db,
+                     const int32_t* __restrict__ node_off_db, int m, int n, int q_per_block,
+                     float* __restrict__ sim, int64_t ld) {
+  extern __shared__ __align__(16) float smem[];
+  const int T = blockDim.x, tid = threadIdx.x;
+  const int K = M.K, D = M.emb_dim, d = M.node_dim, bins = M.hist_bins;
+  float* s_hw = smem;
+  float* s_q = s_hw + HP.hw_floats;                       // [HEAD_QC][q_floats]
+  float* s_rows = s_q + HEAD_QC * HP.q_floats;            // [T][S]
+  int* s_cnt = reinterpret_cast<int*>(s_rows + (size_t)T * HP.S);   // [bins][T]
+
+  // ---- head weights, zero-padded to H0 columns (and H0 rows for the later layers) ----
+  for (int i = tid; i < HP.hw_floats; i += T) s_hw[i] = 0.f;
+  __syncthreads();
+  for (int k = tid; k < K; k += T) s_hw[k] = params[M.u_off + k];
+  {
+    const LayerDev& L = M.Hd[0];
+    for (int i = tid; i < L.din * L.dout; i += T) {
+      const int k = i / L.dout, j = i - k * L.dout;
+      s_hw[HP.w0 + k * H0 + j] = params[L.w_off + i];
+    }
+    if (L.bias) for (int j = tid; j < L.dout; j += T) s_hw[HP.b0 + j] = params[L.b_off + j];
+  }
+  for (int l = 1; l < M.n_head; ++l) {
+    const LayerDev& L = M.Hd[l];
+    for (int i = tid; i < L.din * L.dout; i += T) {
+      const int k = i / L.dout, j = i - k * L.dout;
+      s_hw[HP.wl + ((l - 1) * H0 + k) * H0 + j] = params[L.w_off + i];
+    }
+    if (L.bias) for (int j = tid; j < L.dout; j += T) s_hw[HP.bl + (l - 1) * H0 + j] = params[L.b_off + j];
+  }
+
+  // ---- this CTA's database graphs: embedding -> registers, node rows -> private stripes ----
+  const int g0 = blockIdx.x * T;
+  const int g = g0 + tid;
+  float x[DEP];
+#pragma unroll
+  for (int b = 0; b < DEP; ++b) x[b] = (g < n && b < D) ? emb_db[(size_t)g * D + b] : 0.f;
+  const int n_g = (g < n && bins > 0) ? node_off_db[g + 1] - node_off_db[g] : 0;
+  if (bins > 0) {
+    const int lane = tid & 31, warp = tid >> 5, nw = T >> 5;
+    for (int gi = warp; gi < T && g0 + gi < n; gi += nw) {
+      const int base = node_off_db[g0 + gi];
+      const int cnt = node_off_db[g0 + gi + 1] - base;
+      float* dst = s_rows + (size_t)gi * HP.S;
+      for (int idx = lane; idx < cnt * ND; idx += 32) {
+        const int r = idx / ND, c = idx - r * ND;
+        dst[idx] = c < d ? nodes_db[(size_t)(base + r) * d + c] : 0.f;
+      }
+    }
+  }
+  const float* my_rows = s_rows + (size_t)tid * HP.S;
+  int* my_cnt = s_cnt + tid;
+  const int act = M.pair_act;
+  const int q_begin = blockIdx.y * q_per_block;
+  const int q_end = min(m, q_begin + q_per_block);
+
+  for (int q0 = q_begin; q0 < q_end; q0 += HEAD_QC) {
+    const int nq = min(HEAD_QC, q_end - q0);
+    __syncthreads();
+    for (int qi = 0; qi < nq; ++qi) {
+      float* sq = s_q + qi * HP.q_floats;
+      const float4* src = reinterpret_cast<const float4*>(Pq + (size_t)(q0 + qi) * K * DEP);
+      float4* dst = reinterpret_cast<float4*>(sq);
+      for (int i = tid; i < K * DEP / 4; i += T) dst[i] = src[i];
+      float* sc = sq + K * DEP;
+      for (int k = tid; k < K; k += T) sc[k] = Cq[(size_t)(q0 + qi) * K + k];
+      float* sr = sc + round_up4(K);
+      if (bins > 0) {
+        const int base = node_off_q[q0 + qi];
+        const int cnt = node_off_q[q0 + qi + 1] - base;
+        for (int idx = tid; idx < cnt * ND; idx += T) {
+          const int r = idx / ND, c = idx - r * ND;
+          sr[idx] = c < d ? nodes_q[(size_t)(base + r) * d + c] : 0.f;
+        }
+        if (tid == 0) reinterpret_cast<int*>(sr + HP.nmax_q * ND)[0] = cnt;
+      }
+    }
+    __syncthreads();
+    if (g >= n) continue;
+    for (int qi = 0; qi < nq; ++qi) {
+      const float* sq = s_q + qi * HP.q_floats;
+      const float* sc = sq + K * DEP;
+      const float* sr = sc + round_up4(K);
+      const int n_q = bins > 0 ? reinterpret_cast<const int*>(sr + HP.nmax_q * ND)[0] : 0;
+      float acc[H0];
+#pragma unroll
+      for (int j = 0; j < H0; ++j) acc[j] = 0.f;
+      // ---- NTN K-vector, folded straight into head layer 0 (row k of W0) ----
+      for (int k = 0; k < K; ++k) {
+        const float4* p4 = reinterpret_cast<const float4*>(sq + k * DEP);
+        float mk = sc[k];
+#pragma unroll
+        for (int b = 0; b < DEP / 4; ++b) {
+          const float4 p = p4[b];
+          mk = fmaf(p.x, x[4 * b + 0], mk);
+          mk = fmaf(p.y, x[4 * b + 1], mk);
+          mk = fmaf(p.z, x[4 * b + 2], mk);
+          mk = fmaf(p.w, x[4 * b + 3], mk);
+        }
+        const float f = s_hw[k] * sgnn_act(mk, act, M.yeta);
+        const float4* w4 = reinterpret_cast<const float4*>(s_hw + HP.w0 + k * H0);
+#pragma unroll
+        for (int j = 0; j < H0 / 4; ++j) {
+          const float4 w = w4[j];
+          acc[4 * j + 0] = fmaf(f, w.x, acc[4 * j + 0]);
+          acc[4 * j + 1] = fmaf(f, w.y, acc[4 * j + 1]);
+          acc[4 * j + 2] = fmaf(f, w.z, acc[4 * j + 2]);
+          acc[4 * j + 3] = fmaf(f, w.w, acc[4 * j + 3]);
+        }
+      }
+      // ---- node-node similarity histogram ----
+      if (bins > 0) {
+        for (int b = 0; b < bins; ++b) my_cnt[b * T] = 0;
+        const float fb = (float)bins;
+        for (int j = 0; j < n_g; ++j) {
+          float hj[ND];
+          const float4* r4 = reinterpret_cast<const float4*>(my_rows + j * ND);
+#pragma unroll
+          for (int c = 0; c < ND / 4; ++c) {
+            const float4 v = r4[c];
+            hj[4 * c] = v.x; hj[4 * c + 1] = v.y; hj[4 * c + 2] = v.z; hj[4 * c + 3] = v.w;
+          }
+          for (int i = 0; i < n_q; ++i) {
+            const float4* q4 = reinterpret_cast<const float4*>(sr + i * ND);
+            float s = 0.f;
+#pragma unroll
+            for (int c = 0; c < ND / 4; ++c) {
+              const float4 v = q4[c];
+              s = fmaf(v.x, hj[4 * c + 0], s);
+              s = fmaf(v.y, hj[4 * c + 1], s);
+              s = fmaf(v.z, hj[4 * c + 2], s);
+              s = fmaf(v.w, hj[4 * c + 3], s);
+            }
+            s = 1.f / (1.f + expf(-s));
+            const int bin = min(bins - 1, (int)floorf(s * fb));
+            my_cnt[bin * T] += 1;
+          }
+        }
+        const int cells = n_q * n_g;
+        for (int b = 0; b < bins; ++b) {
+          const float hb = cells > 0 ? (float)my_cnt[b * T] / (float)cells : 0.f;
+          const float4* w4 = reinterpret_cast<const float4*>(s_hw + HP.w0 + (K + b) * H0);
+#pragma unroll
+          for (int j = 0; j < H0 / 4; ++j) {
+            const float4 w = w4[j];
+            acc[4 * j + 0] = fmaf(hb, w.x, acc[4 * j + 0]);
+            acc[4 * j + 1] = fmaf(hb, w.y, acc[4 * j + 1]);
+            acc[4 * j + 2] = fmaf(hb, w.z, acc[4 * j + 2]);
+            acc[4 * j + 3] = fmaf(hb, w.w, acc[4 * j + 3]);
+          }
+        }
+      }
+      // ---- rest of the head ----
+      {
+        const int a0 = M.Hd[0].act;
+#pragma unroll
+        for (int j = 0; j < H0; ++j) acc[j] = sgnn_act(acc[j] + s_hw[HP.b0 + j], a0, M.yeta);
+      }
+      for (int l = 1; l < M.n_head; ++l) {
+        const float* w = s_hw + HP.wl + (l - 1) * H0 * H0;
+        const float* bl = s_hw + HP.bl + (l - 1) * H0;
+        const int din = M.Hd[l].din, al = M.Hd[l].act;
+        float nxt[H0];
+#pragma unroll
+        for (int j = 0; j < H0; ++j) nxt[j] = 0.f;
+#pragma unroll
+        for (int k = 0; k < H0; ++k) {
+          if (k < din) {
+            const float4* w4 = reinterpret_cast<const float4*>(w + k * H0);
+#pragma unroll
+            for (int j = 0; j < H0 / 4; ++j) {
+              const float4 v = w4[j];
+              nxt[4 * j + 0] = fmaf(acc[k], v.x, nxt[4 * j + 0]);
+              nxt[4 * j + 1] = fmaf(acc[k], v.y, nxt[4 * j + 1]);
+              nxt[4 * j + 2] = fmaf(acc[k], v.z, nxt[4 * j + 2]);
+              nxt[4 * j + 3] = fmaf(acc[k], v.w, nxt[4 * j + 3]);
+            }
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < H0; ++j) acc[j] = sgnn_act(nxt[j] + bl[j], al, M.yeta);
+      }
+      sim[(size_t)(q0 + qi) * ld + g] = sgnn_act(acc[0], M.final_act, M.yeta);
+    }
+  }
+}
+
+template <int DEP, int H0, int ND>
+static cudaError_t launch_head(const ModelDev& M, const float* params, const float* Pq, const float* Cq,
+                               const float* emb_db, const float* nodes_q, const int32_t* node_off_q, int max_nodes_q,
+                               const float* nodes_db, const int32_t* node_off_db, int max_nodes_db, int m, int n,
+                               float* sim, int64_t ld, int sm_count, int smem_optin, cudaStream_t st) {
+  HeadPlan P;
+  head_plan_weights<H0>(M, P);
+  P.nmax_q = M.hist_bins > 0 ? std::max(1, max_nodes_q) : 0;
+  P.q_floats = M.K * DEP + round_up4(M.K) + P.nmax_q * ND + 4;
+  const int rows = M.hist_bins > 0 ? std::max(1, max_nodes_db) * ND : 0;
+  P.S = (rows + 7) / 8 * 8 + 4;   // 4 * odd words: conflict-free 16-byte reads across a warp
+  auto bytes_for = [&](int t) {
+    return ((size_t)P.hw_floats + (size_t)HEAD_QC * P.q_floats + (size_t)t * P.S + (size_t)M.hist_bins * t) * sizeof(float);
+  };
+  int threads = 0;
+  for (int t = 128; t >= 32 && !threads; t >>= 1)
+    if (2 * (bytes_for(t) + 1024) <= (size_t)smem_optin + 1024) threads = t;
+  for (int t = 128; t >= 32 && !threads; t >>= 1)
+    if (bytes_for(t) <= (size_t)smem_optin) threads = t;
+  if (!threads) return cudaErrorInvalidValue;
+  P.threads = threads;
+  const size_t smem = bytes_for(threads);
+  auto kern = allpairs_head_kernel<DEP, H0, ND>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  const int gx = (n + threads - 1) / threads;
+  // about four CTAs per SM in flight over the whole grid; a CTA keeps its database stripe for all its queries
+  int gy = std::max(1, std::min((m + HEAD_QC - 1) / HEAD_QC, (sm_count * 4 + gx - 1) / gx));
+  const int qpb = ((m + gy - 1) / gy + HEAD_QC - 1) / HEAD_QC * HEAD_QC;
+  gy = (m + qpb - 1) / qpb;
+  kern<<<dim3(gx, gy), threads, smem, st>>>(M, P, params, Pq, Cq, emb_db, nodes_q, node_off_q, nodes_db, node_off_db,
+                                            m, n, qpb, sim, ld);
+  return cudaGetLastError();
+}
+
+cudaError_t sgnn_launch_allpairs_head(const ModelDev& M, int DEP, const float* params, const float* Pq, const float* Cq,
+                                      const float* emb_db, const float* nodes_q, const int32_t* node_off_q,
+                                      int max_nodes_q, const float* nodes_db, const int32_t* node_off_db,
+                                      int max_nodes_db, int m, int n, float* sim, int64_t ld, int sm_count,
+                                      int smem_optin, cudaStream_t st) {
+  if (M.n_head < 1) return cudaErrorInvalidValue;
+  int hmax = 0;
+  for (int l = 0; l < M.n_head; ++l) {
+    hmax = std::max(hmax, M.Hd[l].dout);
+    if (l > 0) hmax = std::max(hmax, M.Hd[l].din);
+  }
+  const int nd = M.node_dim;
+  if (hmax > 32 || nd > 32 || (DEP != 16 && DEP != 32)) return cudaErrorInvalidValue;
+#define SGNN_HEAD_ARGS M, params, Pq, Cq, emb_db, nodes_q, node_off_q, max_nodes_q, nodes_db, node_off_db, \
+                       max_nodes_db, m, n, sim, ld, sm_count, smem_optin, st
+  const int key = (DEP == 32 ? 4 : 0) | (hmax > 16 ? 2 : 0) | (nd > 16 ? 1 : 0);
+  switch (key) {
+    case 0: return launch_head<16, 16, 16>(SGNN_HEAD_ARGS);
+    case 1: return launch_head<16, 16, 32>(SGNN_HEAD_ARGS);
+    case 2: return launch_head<16, 32, 16>(SGNN_HEAD_ARGS);
+    case 3: return launch_head<16, 32, 32>(SGNN_HEAD_ARGS);
+    case 4: return launch_head<32, 16, 16>(SGNN_HEAD_ARGS);
+    case 5: return launch_head<32, 16, 32>(SGNN_HEAD_ARGS);
+    case 6: return launch_head<32, 32, 16>(SGNN_HEAD_ARGS);
+    default: return launch_head<32, 32, 32>(SGNN_HEAD_ARGS);
+  }
+#undef SGNN_HEAD_ARGS
+}

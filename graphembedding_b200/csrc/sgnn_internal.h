@@ -34,7 +34,7 @@ cudaError_t sgnn_launch_kendall(const float* true_sim, const float* pred_sim, in
 // node-per-thread embedding of small graphs (max_nodes <= 32); cudaErrorInvalidValue if the model
 // does not fit this kernel's shared memory (the caller then uses the warp-per-graph kernel)
 cudaError_t sgnn_launch_embed_tile(const ModelDev& M, const BatchDev& B, int max_nodes, const float* params,
-                                   float* emb, int sm_count, int smem_optin, cudaStream_t st);
+                                   float* emb, float* node_out, int sm_count, int smem_optin, cudaStream_t st);
 
 // CTA-per-graph embedding for graphs of any size; bufA / bufB: total_nodes x sgnn_large_row_stride floats each
 int sgnn_large_row_stride(const ModelDev& M);
@@ -45,3 +45,11 @@ cudaError_t sgnn_launch_embed_large(const ModelDev& M, const BatchDev& B, const 
 cudaError_t sgnn_launch_pair_histogram(const float* node_emb, int d, const int32_t* node_off, const int32_t* g1,
                                        const int32_t* g2, int n_pairs, int bins, float* hist, int32_t* counts,
                                        int sm_count, cudaStream_t st);
+
+// all-pairs scorer for models with a SimGNN-style head (sgnn_head.cu); P / C: per-query NTN tables of
+// allpairs_prep_kernel with row stride DEP.  cudaErrorInvalidValue: shape not supported by the kernel.
+cudaError_t sgnn_launch_allpairs_head(const ModelDev& M, int DEP, const float* params, const float* Pq, const float* Cq,
+                                      const float* emb_db, const float* nodes_q, const int32_t* node_off_q,
+                                      int max_nodes_q, const float* nodes_db, const int32_t* node_off_db,
+                                      int max_nodes_db, int m, int n, float* sim, int64_t ld, int sm_count,
+                                      int smem_optin, cudaStream_t st);

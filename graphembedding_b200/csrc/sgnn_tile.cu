@@ -5,7 +5,7 @@
 #include <algorithm>
 
 cudaError_t sgnn_launch_embed_tile(const ModelDev& M, const BatchDev& B, int max_nodes, const float* params,
-                                   float* emb, int sm_count, int smem_optin, cudaStream_t st) {
+                                   float* emb, float* node_out, int sm_count, int smem_optin, cudaStream_t st) {
   if (max_nodes > 32) return cudaErrorInvalidValue;
   const EmbPlan P = make_emb_plan(M, max_nodes);
   const int n_tiles = (B.n_graphs + P.gpw - 1) / P.gpw;
@@ -28,7 +28,7 @@ cudaError_t sgnn_launch_embed_tile(const ModelDev& M, const BatchDev& B, int max
   cudaError_t e = cudaFuncSetAttribute(embed_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)bytes_for(warps));
   if (e != cudaSuccess) return e;
-  embed_tile_kernel<<<blocks, warps * 32, bytes_for(warps), st>>>(M, P, B, params, emb);
+  embed_tile_kernel<<<blocks, warps * 32, bytes_for(warps), st>>>(M, P, B, params, emb, node_out);
   return cudaGetLastError();
 }
 

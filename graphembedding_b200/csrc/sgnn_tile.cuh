@@ -261,7 +261,7 @@ __device__ __forceinline__ float* tile_node_layers(const ModelDev& M, const EmbP
 
 __global__ void __launch_bounds__(TILE_MAX_WARPS * 32, 2)
 embed_tile_kernel(const __grid_constant__ ModelDev M, const __grid_constant__ EmbPlan P, const BatchDev B,
-                  const float* __restrict__ params, float* __restrict__ emb) {
+                  const float* __restrict__ params, float* __restrict__ emb, float* __restrict__ node_out) {
   extern __shared__ __align__(16) float smem[];
   float* s_w = smem;
   TILE_STAMP(0);
@@ -323,6 +323,13 @@ embed_tile_kernel(const __grid_constant__ ModelDev M, const __grid_constant__ Em
     float* H = tile_node_layers(M, P, T, s_w, bufA, bufB, lane, &ldh);
     if (t == blockIdx.x * nw) TILE_STAMP(4);
     float* scratch = H == bufA ? bufB : bufA;
+    if (node_out) {   // last node-level rows of the tile (the histogram layer's input), [total_nodes][node_dim]
+      __syncwarp();
+      for (int idx = lane; idx < T.n_rows * d; idx += 32) {
+        const int r = idx / d, c = idx - r * d;
+        node_out[(size_t)(base + r) * d + c] = H[r * ldh + c];
+      }
+    }
     // ---- pooling, per graph of the tile ----
     if (M.pool_kind == SGNN_LAYER_PADDING) {
       for (int k = 0; k < g1 - g0; ++k) {

@@ -30,7 +30,7 @@ __device__ __forceinline__ void team_sync(const Team& t) {   // immediate barrie
 struct TeamLayout {
   int nmax, emax;
   int csr, acts, T, G0, G1, emb, save, nmask, dx, arm_total;
-  int ub, vb, mb, tb, dmb, scal, pair_total;
+  int ub, vb, mb, tb, dmb, scal, hf, hg, hcnt, pair_total;
 };
 
 __host__ __device__ inline TeamLayout team_layout(const ModelDev& M, int nmax) {
@@ -55,6 +55,10 @@ __host__ __device__ inline TeamLayout team_layout(const ModelDev& M, int nmax) {
   t.tb = o; o += Kp;
   t.dmb = o; o += Kp;
   t.scal = o; o += 8;
+  // SimGNN-style head: activation row (features | layer outputs), pre-activation / gradient row, histogram counters
+  t.hf = o; o += round_up4(M.head_floats);
+  t.hg = o; o += round_up4(M.head_floats);
+  t.hcnt = o; o += M.hist_bins > 0 ? 32 : 0;
   t.pair_total = o;
   return t;
 }
@@ -324,6 +328,101 @@ __device__ __forceinline__ void team_graph_bwd(const ModelDev& M, const GraphS& 
   }
 }
 
+// ---- SimGNN-style head (sgnn.h; build-defined): histogram features + Dense layers on the pair row ----
+// All TEAM_CTA threads.  On entry hf[0..K) = U_k * inneract(m_k), hcnt zeroed.  Leaves the raw score in scal[0],
+// the layer outputs in hf and the pre-activations in hg (read by the backward pass).
+__device__ __forceinline__ void team_head_fwd(const ModelDev& M, const float* W, const float* arms, const TeamLayout& TL,
+                                              int n_mine, float* hf, float* hg, int* hcnt, float* scal, bool dropping,
+                                              uint32_t dbase, int p) {
+  const int tid = threadIdx.x;
+  const int K = M.K, bins = M.hist_bins;
+  if (bins > 0) {
+    // node counts of the two arms (each team knows its own)
+    if (tid == 0) scal[3] = __int_as_float(n_mine);
+    if (tid == TEAM_THREADS) scal[4] = __int_as_float(n_mine);
+    __syncthreads();
+    const int n1 = __float_as_int(scal[3]), n2 = __float_as_int(scal[4]);
+    const int d = M.node_dim, ald = M.act_ld;
+    const float* H1 = arms + TL.acts + M.L[M.n_node - 1].out_off;
+    const float* H2 = arms + TL.arm_total + TL.acts + M.L[M.n_node - 1].out_off;
+    const int cells = n1 * n2;
+    // same arithmetic as pair_histogram_kernel (sgnn_large.cuh): sequential fmaf dot, sigmoid, floor(s * bins)
+    for (int c = tid; c < cells; c += TEAM_CTA) {
+      const int i = c / n2, j = c - i * n2;
+      const float* x = H1 + i * ald;
+      const float* y = H2 + j * ald;
+      float s = 0.f;
+      for (int k = 0; k < d; ++k) s = fmaf(x[k], y[k], s);
+      s = 1.f / (1.f + expf(-s));
+      atomicAdd(&hcnt[min(bins - 1, (int)floorf(s * (float)bins))], 1);
+    }
+    __syncthreads();
+    if (tid < bins) hf[K + tid] = cells > 0 ? (float)hcnt[tid] / (float)cells : 0.f;
+    __syncthreads();
+  }
+  int in_off = 0;
+  for (int l = 0; l < M.n_head; ++l) {
+    const LayerDev& L = M.Hd[l];
+    float* in = hf + in_off;
+    if (dropping && L.drop) {   // Dense dropout on its input (layers.py:196); the saved input is the masked one
+      const uint32_t key = drop_layer_key(dbase, 2 * p, L.ref);
+      for (int k = tid; k < L.din; k += TEAM_CTA) in[k] *= drop_mask(key, 0, k, M.keep, M.inv_keep);
+      __syncthreads();
+    }
+    const float* w = W + L.w_off;
+    for (int j = tid; j < L.dout; j += TEAM_CTA) {
+      float s = 0.f;
+      for (int k = 0; k < L.din; ++k) s = fmaf(in[k], w[k * L.dout + j], s);
+      s += L.bias ? W[L.b_off + j] : 0.f;
+      hg[L.out_off + j] = s;
+      hf[L.out_off + j] = sgnn_act(s, L.act, M.yeta);
+    }
+    __syncthreads();
+    in_off = L.out_off;
+  }
+  if (tid == 0) scal[0] = hf[in_off];
+}
+
+// graw = dL/d(raw).  Accumulates the head's parameter gradients into s_g and leaves dL/d(f_k) in hg[0..K).
+__device__ __forceinline__ void team_head_bwd(const ModelDev& M, const float* W, float* s_g, const float* hf, float* hg,
+                                              float graw, bool dropping, uint32_t dbase, int p) {
+  const int tid = threadIdx.x;
+  {
+    const LayerDev& L = M.Hd[M.n_head - 1];
+    if (tid == 0) hg[L.out_off] = graw * sgnn_act_grad(hf[L.out_off], hg[L.out_off], L.act, M.yeta);
+    __syncthreads();
+  }
+  for (int l = M.n_head - 1; l >= 0; --l) {
+    const LayerDev& L = M.Hd[l];
+    const int in_off = l > 0 ? M.Hd[l - 1].out_off : 0;
+    const float* in = hf + in_off;
+    const float* dz = hg + L.out_off;
+    const float* w = W + L.w_off;
+    if (L.bias)
+      for (int j = tid; j < L.dout; j += TEAM_CTA) atomicAdd(&s_g[L.b_off + j], dz[j]);
+    for (int idx = tid; idx < L.din * L.dout; idx += TEAM_CTA) {
+      const int k = idx / L.dout, j = idx - k * L.dout;
+      atomicAdd(&s_g[L.w_off + idx], in[k] * dz[j]);
+    }
+    const bool masked = dropping && L.drop;
+    const uint32_t key = masked ? drop_layer_key(dbase, 2 * p, L.ref) : 0u;
+    for (int k = tid; k < L.din; k += TEAM_CTA) {
+      float s = 0.f;
+      for (int j = 0; j < L.dout; ++j) s = fmaf(w[k * L.dout + j], dz[j], s);
+      if (masked) s *= drop_mask(key, 0, k, M.keep, M.inv_keep);
+      if (l > 0) {
+        const LayerDev& Lp = M.Hd[l - 1];
+        // the saved output of layer l-1 is masked in place if layer l dropped its input: y = saved * keep where kept
+        float y = hf[in_off + k];
+        if (masked) y *= M.keep;
+        s *= sgnn_act_grad(y, hg[in_off + k], Lp.act, M.yeta);
+      }
+      hg[in_off + k] = s;
+    }
+    __syncthreads();
+  }
+}
+
 template <bool BWD>
 __global__ void __launch_bounds__(TEAM_CTA, 2)
 train_team_kernel(const __grid_constant__ ModelDev M, const BatchDev B, int nmax, const float* __restrict__ params,
@@ -356,6 +455,7 @@ train_team_kernel(const __grid_constant__ ModelDev M, const BatchDev B, int nmax
   float* arm = arms + arm_id * TL.arm_total;
   float* ub = pairb + TL.ub; float* vb = pairb + TL.vb; float* mb = pairb + TL.mb;
   float* tb = pairb + TL.tb; float* dmb = pairb + TL.dmb; float* scal = pairb + TL.scal;
+  float* hf = pairb + TL.hf; float* hg = pairb + TL.hg; int* hcnt = reinterpret_cast<int*>(pairb + TL.hcnt);
   const float* x1 = arms + TL.emb;
   const float* x2 = arms + TL.arm_total + TL.emb;
   float* dx1 = arms + TL.dx;
@@ -398,12 +498,19 @@ train_team_kernel(const __grid_constant__ ModelDev M, const BatchDev B, int nmax
           const float t = sgnn_act(s, M.pair_act, M.yeta);
           mb[k] = s; tb[k] = t;
           st += t; su += U[k]; sut = fmaf(U[k], t, sut);
+          if (M.n_head > 0) hf[k] = U[k] * t;   // head: the NTN emits its K-vector (sgnn.h)
         }
         st = warp_sum(st); su = warp_sum(su); sut = warp_sum(sut);
         if (tid == 0) {
           scal[0] = M.ntn_mode == SGNN_NTN_REFERENCE ? su * st : sut;   // F5: layers.py:305-308
           scal[1] = st; scal[2] = su;
         }
+      } else if (M.hist_bins > 0 && tid >= 32 && tid < 64) {
+        hcnt[tid - 32] = 0;
+      }
+      if (M.n_head > 0) {
+        __syncthreads();
+        team_head_fwd(M, s_w, arms, TL, G.n, hf, hg, hcnt, scal, dropping != 0, dbase, p);
       }
     }
     __syncthreads();
@@ -431,9 +538,14 @@ train_team_kernel(const __grid_constant__ ModelDev M, const BatchDev B, int nmax
     if (M.pair_kind == SGNN_LAYER_DOT) {
       for (int a = tid; a < D; a += TEAM_CTA) { dx1[a] = graw * x2[a]; dx2[a] = graw * x1[a]; }
     } else {
+      if (M.n_head > 0) {   // head backward: leaves dL/d(f_k) in hg[0..K)
+        team_head_bwd(M, s_w, s_g, hf, hg, graw, dropping != 0, dbase, p);
+        __syncthreads();
+      }
       for (int k = tid; k < K; k += TEAM_CTA) {
         float dt;
-        if (M.ntn_mode == SGNN_NTN_REFERENCE) { dt = graw * su; atomicAdd(&s_g[M.u_off + k], graw * st); }
+        if (M.n_head > 0) { dt = hg[k] * U[k]; atomicAdd(&s_g[M.u_off + k], hg[k] * tb[k]); }
+        else if (M.ntn_mode == SGNN_NTN_REFERENCE) { dt = graw * su; atomicAdd(&s_g[M.u_off + k], graw * st); }
         else { dt = graw * U[k]; atomicAdd(&s_g[M.u_off + k], graw * tb[k]); }
         const float dm = dt * sgnn_act_grad(tb[k], mb[k], M.pair_act, M.yeta);
         dmb[k] = dm;

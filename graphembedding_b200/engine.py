@@ -21,6 +21,8 @@ class SgnnEngine(object):
         if not torch.cuda.is_available():
             raise native.SgnnError('no CUDA device: the sm_100a path has no CPU fallback')
         self.layers = layers
+        pair_at = [i for i, L in enumerate(layers) if L['kind'] in ('NTN', 'Dot')]
+        self.has_head = bool(pair_at) and pair_at[0] < len(layers) - 1   # Histogram / Dense after the NTN
         self.cfg = native.make_config(layers, input_dim, **kw)
         self.device = torch.device('cuda', self.cfg.device)
         h = C.c_void_p()
@@ -126,8 +128,42 @@ class SgnnEngine(object):
         return raw, sim
 
     def forward_pairs(self, batch, g1, g2, stream=None):
+        if self.has_head:   # one per-pair kernel (the histogram needs the node rows): sgnn_forward_pairs
+            import torch
+            n = int(g1.numel())
+            raw = torch.empty(n, dtype=torch.float32, device=self.device)
+            sim = torch.empty(n, dtype=torch.float32, device=self.device)
+            s = batch.struct()
+            check(self.h, lib().sgnn_forward_pairs(self.h, C.byref(s), _ptr(g1), _ptr(g2), n, None, _ptr(raw),
+                                                   _ptr(sim), _stream_ptr(stream)))
+            self.launches += 1
+            return raw, sim
         emb = self.embed(batch, stream=stream)
         return self.score_pairs(emb, g1, g2, stream=stream)
+
+    def embed_nodes(self, batch, stream=None):
+        """(pooled embeddings [G, emb_dim], last node-level rows [total_nodes, node_dim]) in one pass."""
+        import torch
+        d = int(lib().sgnn_node_dim(self.h))
+        emb = torch.empty((batch.n_graphs, self.emb_dim), dtype=torch.float32, device=self.device)
+        rows = torch.empty((batch.total_nodes, d), dtype=torch.float32, device=self.device)
+        s = batch.struct()
+        check(self.h, lib().sgnn_embed_graphs_nodes(self.h, C.byref(s), _ptr(emb), _ptr(rows), _stream_ptr(stream)))
+        self.launches += 1
+        return emb, rows
+
+    def score_all_pairs_nodes(self, emb_q, rows_q, batch_q, emb_db, rows_db, batch_db, out=None, stream=None):
+        """All-pairs scores of a model with a Histogram head (needs both sides' node rows)."""
+        import torch
+        m, n = emb_q.shape[0], emb_db.shape[0]
+        if out is None:
+            out = torch.empty((m, n), dtype=torch.float32, device=self.device)
+        check(self.h, lib().sgnn_score_all_pairs_nodes(
+            self.h, _ptr(emb_q), _ptr(rows_q), _ptr(batch_q.node_off), batch_q.max_nodes, m, _ptr(emb_db),
+            _ptr(rows_db), _ptr(batch_db.node_off), batch_db.max_nodes, n, _ptr(out), out.stride(0),
+            _stream_ptr(stream)))
+        self.launches += 2
+        return out
 
     def score_all_pairs(self, emb_q, emb_db, out=None, stream=None):
         import torch

@@ -2,18 +2,21 @@
 ``'Name:key=val,key=val'`` strings -> plain dict descriptions that ``native.make_config``
 turns into the POD ``SgnnLayerDesc[]`` handed to ``sgnn_create``.  Same layer names, same
 arity checks and error behaviour (RuntimeError); ``Attention`` (layers.py:143-160, defined
-but never wired into the reference's factory) is accepted as an addition."""
+but never wired into the reference's factory) is accepted as an addition, and so is the
+SimGNN-style head (build-defined): ``Histogram:bins=B`` right after the NTN and ``Dense``
+layers after that, the last with ``output_dim=1`` (include/sgnn.h, SGNN_LAYER_HISTOGRAM)."""
 import numpy as np
 
 _ARITY = {'GraphConvolution': (5, 6), 'Average': (0, 0), 'NTN': (5, 5), 'Dot': (0, 0),
-          'Dense': (5, 5), 'Padding': (2, 2), 'Attention': (1, 1)}
+          'Dense': (5, 5), 'Padding': (2, 2), 'Attention': (1, 1), 'Histogram': (1, 1)}
 _ARITY_MSG = {'GraphConvolution': 'GraphConvolution layer must have 3-4 specs',
               'Average': 'Average layer must have 0 specs',
               'NTN': 'Average layer must have 0 specs',   # sic: reference message, :67
               'Dot': 'Dot layer must have 0 specs',
               'Dense': 'Dot layer must have 5 specs',     # sic: reference message, :84
               'Padding': 'Padding layer must have 2 specs',
-              'Attention': 'Attention layer must have 1 spec'}
+              'Attention': 'Attention layer must have 1 spec',
+              'Histogram': 'Histogram layer must have 1 spec'}
 ACTIVATIONS = ('relu', 'identity', 'sigmoid', 'tanh', 'sim_kernel')
 
 
@@ -67,6 +70,8 @@ def parse_layer(spec, layer_id, model_input_dim):
         out.update(max_in_dims=int(kv['max_in_dims']), padding_value=int(kv['padding_value']))
     elif head == 'Attention':
         out.update(input_dim=int(kv['input_dim']))
+    elif head == 'Histogram':
+        out.update(bins=int(kv['bins']))
     return out
 
 

@@ -12,7 +12,7 @@ SGNN_MAX_LAYERS = 12
 ABI_VERSION = 1
 
 LAYER_KINDS = {'GraphConvolution': 0, 'Dense': 1, 'Padding': 2, 'Average': 3, 'Attention': 4,
-               'NTN': 5, 'Dot': 6}
+               'NTN': 5, 'Dot': 6, 'Histogram': 7}
 ACTS = {'relu': 0, 'identity': 1, 'sigmoid': 2, 'tanh': 3, 'sim_kernel': 4}
 NTN_MODES = {'reference': 0, 'paper': 1}
 LOSS_MODES = {'reference': 0, 'paired': 1}
@@ -68,6 +68,8 @@ SIGNATURES = {
     'sgnn_embed_graphs': (C.c_int, [_P, _BP, _P, _P]),
     'sgnn_node_dim': (C.c_int, [_P]),
     'sgnn_node_embeddings': (C.c_int, [_P, _BP, _P, _P]),
+    'sgnn_embed_graphs_nodes': (C.c_int, [_P, _BP, _P, _P, _P]),
+    'sgnn_score_all_pairs_nodes': (C.c_int, [_P, _P, _P, _P, _I32, _I32, _P, _P, _P, _I32, _I32, _P, _I64, _P]),
     'sgnn_pair_histogram': (C.c_int, [_P, _P, _P, _P, _P, _I32, _I32, _P, _P, _P]),
     'sgnn_score_pairs': (C.c_int, [_P, _P, _P, _P, _I32, _P, _P, _P]),
     'sgnn_forward_pairs': (C.c_int, [_P, _BP, _P, _P, _I32, _P, _P, _P, _P]),
@@ -268,7 +270,7 @@ def make_config(layers, input_dim, final_act='sim_kernel', yeta=0.6, ntn_mode='r
         d.bias = int(bool(L.get('bias', False)))
         d.dropout = int(bool(L.get('dropout', False)))
         d.sparse_inputs = int(bool(L.get('sparse_inputs', False)))
-        d.aux = int(L.get('max_in_dims', L.get('feature_map_dim', 0)) or 0)
+        d.aux = int(L.get('max_in_dims', L.get('feature_map_dim', L.get('bins', 0))) or 0)
         d.fparam = float(L.get('padding_value', 0.0))
     cfg.input_dim = int(input_dim)
     cfg.final_act = ACTS[final_act]

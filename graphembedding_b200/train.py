@@ -103,12 +103,21 @@ def all_pairs_similarity(data, model, k=10):
     q_ids = np.array([model._gid(offsets, data.test_data.get_graph(i)) for i in range(m)], np.int64)
     d_ids = np.array([model._gid(offsets, data.get_orig_train_graph(j)) for j in range(n)], np.int64)
     eng.reserve(max_queries=m, max_db=n)
-    torch.cuda.synchronize()
-    t = time()
-    emb = eng.embed(dev)
-    emb_q = emb[torch.as_tensor(q_ids, device=eng.device)].contiguous()
-    emb_d = emb[torch.as_tensor(d_ids, device=eng.device)].contiguous()
-    sim = eng.score_all_pairs(emb_q, emb_d)
+    if eng.has_head:   # SimGNN-style head: the histogram needs each side's node rows next to the embeddings
+        host = model._ensure_resident(data)[3]
+        qb, db = host.select(q_ids).to(eng.device), host.select(d_ids).to(eng.device)
+        torch.cuda.synchronize()
+        t = time()
+        emb_q, rows_q = eng.embed_nodes(qb)
+        emb_d, rows_d = eng.embed_nodes(db)
+        sim = eng.score_all_pairs_nodes(emb_q, rows_q, qb, emb_d, rows_d, db)
+    else:
+        torch.cuda.synchronize()
+        t = time()
+        emb = eng.embed(dev)
+        emb_q = emb[torch.as_tensor(q_ids, device=eng.device)].contiguous()
+        emb_d = emb[torch.as_tensor(d_ids, device=eng.device)].contiguous()
+        sim = eng.score_all_pairs(emb_q, emb_d)
     ids, _ = eng.topk(sim, min(k, n - 1)) if n > 1 else (None, None)
     torch.cuda.synchronize()
     secs = time() - t

@@ -37,8 +37,16 @@ enum {
   SGNN_LAYER_AVERAGE = 3,   /* layers.py:121-140 */
   SGNN_LAYER_ATTENTION = 4, /* layers.py:143-160 */
   SGNN_LAYER_NTN = 5,       /* layers.py:255-310 */
-  SGNN_LAYER_DOT = 6        /* layers.py:230-252 */
+  SGNN_LAYER_DOT = 6,       /* layers.py:230-252 */
+  SGNN_LAYER_HISTOGRAM = 7  /* SimGNN pairwise node-node histogram; build-defined (absent from the reference
+                             * snapshot): aux = bins.  Must directly follow the NTN. */
 };
+/* SimGNN-style head (build-defined): layers AFTER the NTN.  With a head the NTN emits its
+ * K-vector f_k = U_k * inneract(m_k) (no sum); an optional Histogram appends `bins` features (node-node
+ * similarity histogram of the last node-level outputs, constant for the gradient); Dense layers
+ * (layers.py:192-205 on the 1 x (K + bins) pair row) reduce it to the raw score (last output_dim = 1),
+ * to which final_act is applied.  At most SGNN_MAX_HEAD Dense layers. */
+#define SGNN_MAX_HEAD 6
 
 /* activations: layers_factory.py:101-114 */
 enum { SGNN_ACT_RELU = 0, SGNN_ACT_IDENTITY = 1, SGNN_ACT_SIGMOID = 2, SGNN_ACT_TANH = 3,
@@ -56,7 +64,7 @@ typedef struct {
   int32_t bias;          /* 0/1 */
   int32_t dropout;       /* 0/1: layer spec `dropout=True` (layers.py:45-49) */
   int32_t sparse_inputs; /* GCN */
-  int32_t aux;           /* Padding: max_in_dims; NTN: feature_map_dim */
+  int32_t aux;           /* Padding: max_in_dims; NTN: feature_map_dim; Histogram: bins */
   float fparam;          /* Padding: padding_value */
 } SgnnLayerDesc;
 
@@ -145,6 +153,10 @@ int sgnn_embed_graphs(SgnnHandle h, const SgnnGraphBatch* batch_dev, float* emb_
  * node-row workspace: sgnn_reserve(max_nodes >= total_nodes). */
 int sgnn_node_dim(SgnnHandle h);
 int sgnn_node_embeddings(SgnnHandle h, const SgnnGraphBatch* batch_dev, float* node_out_dev, void* stream);
+/* sgnn_embed_graphs and sgnn_node_embeddings in ONE pass: emb_dev [n_graphs][embed_dim] and
+ * node_out_dev [total_nodes][sgnn_node_dim].  Graphs of <= 32 nodes need no workspace. */
+int sgnn_embed_graphs_nodes(SgnnHandle h, const SgnnGraphBatch* batch_dev, float* emb_dev, float* node_out_dev,
+                            void* stream);
 /* Pairwise node-node similarity histogram of SimGNN.  NOT in the reference snapshot (only TensorBoard
  * summaries are called "histogram" there, models.py:116 / layers.py:43) -- build-defined:
  *   s_ij = sigmoid(H1_i . H2_j); bin = min(bins-1, floor(s_ij * bins)); hist[b] = count_b / (N1 N2).
@@ -164,6 +176,13 @@ int sgnn_forward_pairs(SgnnHandle h, const SgnnGraphBatch* batch_dev, const int3
  * (query i, database j). */
 int sgnn_score_all_pairs(SgnnHandle h, const float* emb_q_dev, int32_t m, const float* emb_db_dev,
                          int32_t n, float* sim_dev, int64_t ld, void* stream);
+/* sgnn_score_all_pairs for models with a Histogram head (SGNN_LAYER_HISTOGRAM): the histogram needs the last
+ * node-level rows of both sides (sgnn_embed_graphs_nodes / sgnn_node_embeddings) next to the pooled embeddings.
+ * node_off_* [graphs + 1] index rows of nodes_* [total_nodes][sgnn_node_dim]; max_nodes_* = largest graph. */
+int sgnn_score_all_pairs_nodes(SgnnHandle h, const float* emb_q_dev, const float* nodes_q_dev,
+                               const int32_t* node_off_q_dev, int32_t max_nodes_q, int32_t m, const float* emb_db_dev,
+                               const float* nodes_db_dev, const int32_t* node_off_db_dev, int32_t max_nodes_db,
+                               int32_t n, float* sim_dev, int64_t ld, void* stream);
 /* descending top-k per row with the reference's tie order (results.py:221-224: stable
  * ascending mergesort reversed => equal scores come out higher index first). */
 int sgnn_topk(SgnnHandle h, const float* sim_dev, int32_t m, int32_t n, int64_t ld, int32_t k,

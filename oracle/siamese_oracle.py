@@ -85,6 +85,10 @@ def parse_layer_specs(spec_strings, input_dim):
             layers.append(dict(kind=name, input_dim=int(info['input_dim']),
                                output_dim=int(info['output_dim']), dropout=_bool(info['dropout']),
                                act=info['act'], bias=_bool(info['bias'])))
+        elif name == 'Histogram':  # build extension (SimGNN's pairwise node-node histogram)
+            if len(info) != 1:
+                raise RuntimeError('Histogram layer must have 1 spec')
+            layers.append(dict(kind=name, bins=int(info['bins'])))
         elif name == 'Padding':  # :94-98
             if len(info) != 2:
                 raise RuntimeError('Padding layer must have 2 specs')
@@ -94,6 +98,19 @@ def parse_layer_specs(spec_strings, input_dim):
             raise RuntimeError('Unknown layer {}'.format(name))
     return layers
 
+
+SIMGNN_LAYERS = [  # BASELINE.json configs[0]: SimGNN-style chain (build-chosen widths, SURVEY section 8 notation)
+    'GraphConvolution:output_dim=64,act=relu,dropout=True,bias=True,sparse_inputs=True',
+    'GraphConvolution:input_dim=64,output_dim=32,act=relu,dropout=True,bias=True,sparse_inputs=False',
+    'GraphConvolution:input_dim=32,output_dim=16,act=identity,dropout=True,bias=True,sparse_inputs=False',
+    'Attention:input_dim=16',
+    'NTN:input_dim=16,feature_map_dim=16,inneract=relu,dropout=True,bias=True',
+    'Histogram:bins=16',
+    'Dense:input_dim=32,output_dim=16,dropout=False,act=relu,bias=True',
+    'Dense:input_dim=16,output_dim=8,dropout=False,act=relu,bias=True',
+    'Dense:input_dim=8,output_dim=4,dropout=False,act=relu,bias=True',
+    'Dense:input_dim=4,output_dim=1,dropout=False,act=identity,bias=True',
+]
 
 DEFAULT_LAYERS = [  # model/Siamese/config.py:44-66
     'GraphConvolution:output_dim=32,act=relu,dropout=True,bias=True,sparse_inputs=True',
@@ -314,7 +331,7 @@ def node_forward(layers, P, g, input_dim, dtype=torch.float64):
     """Output of the last GraphConvolution / Dense layer, [n, node_dim] (the pooling layer's input)."""
     node_layers = []
     for L in layers:
-        if L['kind'] not in ('GraphConvolution', 'Dense'):
+        if L['kind'] not in NODE_LAYERS:
             break
         node_layers.append(L)
     return graph_forward(node_layers, P, g, input_dim, dtype).reshape(g.n, -1)
@@ -331,10 +348,12 @@ def pair_histogram(h1, h2, bins):
     return counts / float(max(1, s.size)), counts, s
 
 
-def graph_forward(layers, P, g, input_dim, dtype=torch.float64, drop=None, slot=0):
+def graph_forward(layers, P, g, input_dim, dtype=torch.float64, drop=None, slot=0, with_nodes=False):
     """Node-level layers + pooling for one graph; returns the flattened
     representation the pair layer consumes (layers.py:91-118, 136-140,
-    154-160, 192-205, 223-227).  ``drop``: a Dropout (masks keyed by ``slot``)."""
+    154-160, 192-205, 223-227).  ``drop``: a Dropout (masks keyed by ``slot``).
+    ``with_nodes``: also return the last node-level output [n, node_dim] (the histogram's input)."""
+    nodes = None
     def dmask(li, L, x, sparse=False):
         if drop is None or not L.get('dropout', False) or drop.rate == 0.0:
             return x
@@ -362,14 +381,17 @@ def graph_forward(layers, P, g, input_dim, dtype=torch.float64, drop=None, slot=
                 out = out + P[(li, 'bias')]
             x = _act(L['act'])(out)
         elif k == 'Padding':                              # :223-227
+            nodes = x
             if x.shape[0] > L['max_in_dims']:
                 raise ValueError('Paddings must be non-negative')
             pad = torch.full((L['max_in_dims'] - x.shape[0], x.shape[1]),
                              float(L['padding_value']), dtype=dtype)
             x = torch.cat([x, pad], 0)
         elif k == 'Average':                              # :136-140
+            nodes = x
             x = x.mean(0)
         elif k == 'Attention':                            # :154-160
+            nodes = x
             temp = x.mean(0).reshape(1, -1)
             h_avg = torch.tanh((temp @ P[(li, 'weights')]).reshape(-1, 1))
             att = torch.sigmoid(x @ h_avg)
@@ -378,15 +400,28 @@ def graph_forward(layers, P, g, input_dim, dtype=torch.float64, drop=None, slot=
             break
         else:
             raise RuntimeError(k)
+    if with_nodes:
+        return x.reshape(-1), (x if nodes is None else nodes)
     return x.reshape(-1)
 
 
-def pair_forward(layers, P, x1, x2, ntn_mode='reference', drop=None, pair=0):
+def head_layers(layers):
+    """(index of the pair layer, [(index, layer)] of the pair-level layers after it).  A non-empty tail is the
+    SimGNN-style head -- BUILD-DEFINED, absent from the reference snapshot: the NTN emits
+    its K-vector f_k = U_k * inneract(m_k) (no sum), an optional ``Histogram:bins=B`` appends the pairwise
+    node-node histogram of the last node-level outputs (a constant for the gradient, as in SimGNN), and
+    ``Dense`` layers (layers.py:192-205 applied to the 1 x (K+B) row) reduce it to the raw score."""
+    pi = [i for i, l in enumerate(layers) if l['kind'] in PAIR_LAYERS][0]
+    return pi, [(i, l) for i, l in enumerate(layers) if i > pi]
+
+
+def pair_forward(layers, P, x1, x2, ntn_mode='reference', drop=None, pair=0, h1=None, h2=None):
     """NTN / Dot on one pair of flattened representations (layers.py:249-252,
     282-310).  ``ntn_mode='reference'`` reproduces the (K,1)*(K,1,1)
     broadcast of layers.py:305-308 (F5): score = (sum U)(sum act(m)); 'paper'
-    gives sum_k U_k act(m_k)."""
+    gives sum_k U_k act(m_k).  With a head (see head_layers) h1 / h2 are the node-level outputs."""
     li, L = [(i, l) for i, l in enumerate(layers) if l['kind'] in PAIR_LAYERS][0]
+    _, tail = head_layers(layers)
     if L['kind'] == 'Dot':
         return (x1 * x2).sum()
     W, V, U = P[(li, 'weights_W')], P[(li, 'weights_V')], P[(li, 'weights_U')]
@@ -403,6 +438,21 @@ def pair_forward(layers, P, x1, x2, ntn_mode='reference', drop=None, pair=0):
             mid = mid + P[(li, 'bias')][k]
         fm.append(mid)
     tbp = _act(L['inneract'])(torch.stack(fm))            # (K,1,1)   :305-306
+    if tail:
+        f = (U.reshape(-1) * tbp.reshape(-1)).reshape(1, -1)
+        for hi, HL in tail:
+            if HL['kind'] == 'Histogram':
+                hist, _, _ = pair_histogram(h1.detach(), h2.detach(), HL['bins'])
+                f = torch.cat([f, torch.as_tensor(hist, dtype=f.dtype).reshape(1, -1)], 1)
+            else:                                         # Dense on the pair row (layers.py:192-205)
+                if drop is not None and HL.get('dropout', False) and drop.rate != 0.0:
+                    f = f * torch.as_tensor(drop.mask(2 * pair, hi, 1, f.shape[1]), dtype=f.dtype)
+                f = f @ P[(hi, 'weights')]
+                if HL['bias']:
+                    f = f + P[(hi, 'bias')]
+                f = _act(HL['act'])(f)
+        assert f.numel() == 1, 'the head must end with Dense:output_dim=1'
+        return f.reshape(())
     if ntn_mode == 'reference':
         return (U * tbp).sum()                            # (K,1)*(K,1,1) -> (K,K,1)   :308
     return (U.reshape(-1) * tbp.reshape(-1)).sum()
@@ -413,10 +463,27 @@ def forward_pairs(layers, P, g1s, g2s, input_dim, dtype=torch.float64, ntn_mode=
     (model_mse.py:117-126)."""
     outs = []
     for p, (g1, g2) in enumerate(zip(g1s, g2s)):
-        x1 = graph_forward(layers, P, g1, input_dim, dtype, drop, 2 * p)
-        x2 = graph_forward(layers, P, g2, input_dim, dtype, drop, 2 * p + 1)
-        outs.append(pair_forward(layers, P, x1, x2, ntn_mode, drop, p))
+        x1, h1 = graph_forward(layers, P, g1, input_dim, dtype, drop, 2 * p, with_nodes=True)
+        x2, h2 = graph_forward(layers, P, g2, input_dim, dtype, drop, 2 * p + 1, with_nodes=True)
+        outs.append(pair_forward(layers, P, x1, x2, ntn_mode, drop, p, h1, h2))
     return torch.stack(outs)
+
+
+def pair_bin_margins(layers, P, g1s, g2s, input_dim, drop=None):
+    """Per pair: distance (in score units) of the closest node-node score to a histogram bin edge, or
+    inf without a Histogram layer.  A pair whose margin is below fp32 resolution may land in the
+    neighbouring bin on the device; tests use this to tell rounding from errors."""
+    _, tail = head_layers(layers)
+    bins = [L['bins'] for _, L in tail if L['kind'] == 'Histogram']
+    out = np.full(len(g1s), np.inf)
+    if not bins:
+        return out
+    for p, (g1, g2) in enumerate(zip(g1s, g2s)):
+        _, h1 = graph_forward(layers, P, g1, input_dim, torch.float64, drop, 2 * p, with_nodes=True)
+        _, h2 = graph_forward(layers, P, g2, input_dim, torch.float64, drop, 2 * p + 1, with_nodes=True)
+        _, _, sc = pair_histogram(h1.detach(), h2.detach(), bins[0])
+        out[p] = np.min(np.abs(sc * bins[0] - np.round(sc * bins[0]))) / bins[0]
+    return out
 
 
 def total_loss(layers, P, raw, targets_sim, final_act='sim_kernel', yeta=0.6,

@@ -33,7 +33,22 @@ DENSE_DOT = [
     'Average',
     'Dot',
 ]
-CONFIGS = {'default': DEFAULT, 'avg_ntn': AVG_NTN, 'att3': ATT3, 'dense_dot': DENSE_DOT}
+SIMGNN = list(O.SIMGNN_LAYERS)   # BASELINE configs[0]: 3 GCN + Attention + NTN(16,16) + Histogram(16) + FC 32-16-8-4-1
+HEAD_NOHIST = AVG_NTN + [        # Dense head straight on the NTN's K-vector
+    'Dense:input_dim=10,output_dim=4,dropout=False,act=tanh,bias=True',
+    'Dense:input_dim=4,output_dim=1,dropout=False,act=identity,bias=False',
+]
+HEAD_DROP = [                    # head with dropout on its Dense inputs, odd widths, 7 bins
+    'GraphConvolution:output_dim=20,act=relu,dropout=True,bias=True,sparse_inputs=True',
+    'GraphConvolution:input_dim=20,output_dim=12,act=tanh,dropout=True,bias=True,sparse_inputs=False',
+    'Average',
+    'NTN:input_dim=12,feature_map_dim=6,inneract=sigmoid,dropout=True,bias=True',
+    'Histogram:bins=7',
+    'Dense:input_dim=13,output_dim=9,dropout=True,act=sigmoid,bias=True',
+    'Dense:input_dim=9,output_dim=5,dropout=True,act=relu,bias=True',
+    'Dense:input_dim=5,output_dim=1,dropout=False,act=identity,bias=True',
+]
+CONFIGS = {'simgnn': SIMGNN, 'head_nohist': HEAD_NOHIST, 'head_drop': HEAD_DROP, 'default': DEFAULT, 'avg_ntn': AVG_NTN, 'att3': ATT3, 'dense_dot': DENSE_DOT}
 
 
 def corpus(num, n_lo=2, n_hi=10, seed=7):

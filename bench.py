@@ -37,6 +37,18 @@ DEFAULT_LAYERS = [
 ]
 TRAIN_LAYERS = DEFAULT_LAYERS[:2] + [  # tuning.py:74-93 (Average pooling: AIDS10k graphs exceed Padding's 10)
     'Average', 'NTN:input_dim=16,feature_map_dim=10,inneract=relu,dropout=True,bias=True']
+SIMGNN_LAYERS = [  # BASELINE configs[0]/[1]: SimGNN-style chain (3 GCN + Attention + NTN(16,16) + Histogram(16) + FC head)
+    'GraphConvolution:output_dim=64,act=relu,dropout=True,bias=True,sparse_inputs=True',
+    'GraphConvolution:input_dim=64,output_dim=32,act=relu,dropout=True,bias=True,sparse_inputs=False',
+    'GraphConvolution:input_dim=32,output_dim=16,act=identity,dropout=True,bias=True,sparse_inputs=False',
+    'Attention:input_dim=16',
+    'NTN:input_dim=16,feature_map_dim=16,inneract=relu,dropout=True,bias=True',
+    'Histogram:bins=16',
+    'Dense:input_dim=32,output_dim=16,dropout=False,act=relu,bias=True',
+    'Dense:input_dim=16,output_dim=8,dropout=False,act=relu,bias=True',
+    'Dense:input_dim=8,output_dim=4,dropout=False,act=relu,bias=True',
+    'Dense:input_dim=4,output_dim=1,dropout=False,act=identity,bias=True',
+]
 M_QUERIES, N_DB, TOPK = 1000, 10000, 10
 TRAIN_BATCH, TRAIN_GRAPHS = 128, 4096
 
@@ -391,6 +403,7 @@ def run_cuda(args):
         e2e['note'] = 'per-rank sgnn_rank_host on its own shard (host in, local top-k out); the cross-rank merge is in value'
 
     train = run_train(torch, dist, dev, rank, world, local, args, barrier, max_over_ranks)
+    simgnn = run_simgnn(torch, dist, dev, rank, world, local, args, barrier, max_over_ranks, qd, dbd, flush)
 
     if world > 1:
         if peer is not None:
@@ -404,13 +417,90 @@ def run_cuda(args):
             'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
             'dtype': 'f32' if args.precision == 'fp32' else args.precision, 'data': 'synthetic',
             'config': dict(workload_config(), exchange=exchange), 'clocks': clk, 'e2e': e2e,
-            'gpu_launches': launches, 'roofline': roofline, 'train': train}
+            'gpu_launches': launches, 'roofline': roofline, 'train': train, 'simgnn': simgnn}
     if world == 1 and not args.no_cpu_baseline:
         v, cores, sample = cpu_rank_baseline(DEFAULT_LAYERS, q, db)
         line['cpu_baseline'] = {'value': v, 'unit': 'pairs/s', 'cores': cores, 'kind': 'port', 'sample': sample,
                                 'per_pair_reference_structure_pairs_per_s': cpu_per_pair_rate(DEFAULT_LAYERS, q, db)}
     sys.stdout.flush()
     os.write(json_fd, (json.dumps(line) + '\n').encode())
+
+
+def run_simgnn(torch, dist, dev, rank, world, local, args, barrier, max_over_ranks, qd, dbd, flush):
+    """The same ranking step and the same training step on the SimGNN-style chain (BASELINE configs[0]/[1]:
+    3 GCN + Attention + NTN(16,16) + 16-bin node-node histogram + FC 32-16-8-4-1): per-rank shards, no
+    cross-rank exchange in the timed region (the candidate exchange is the headline's)."""
+    from graphembedding_b200 import distributed as DS
+    from graphembedding_b200.engine import SgnnEngine
+    from graphembedding_b200.layers_factory import parse_layers
+    layers = parse_layers(SIMGNN_LAYERS, 29)
+    eng = SgnnEngine(layers, 29, device=local, final_act='sigmoid', loss_mode='paired')
+    eng.init_params(123)
+    eng.reserve(max_graphs=N_DB, max_nodes=max(qd.total_nodes, dbd.total_nodes), max_nnz=dbd.nnz,
+                max_queries=M_QUERIES, max_db=N_DB)
+    E = eng.emb_dim
+    bufs = dict(emb_q=torch.empty((M_QUERIES, E), device=dev), emb_db=torch.empty((N_DB, E), device=dev),
+                sim=torch.empty((M_QUERIES, N_DB), device=dev),
+                ids=torch.empty((M_QUERIES, TOPK), dtype=torch.int32, device=dev),
+                vals=torch.empty((M_QUERIES, TOPK), device=dev))
+    for _ in range(max(3, args.warmup)):
+        eng.rank_device(qd, dbd, TOPK, **bufs)
+    torch.cuda.synchronize()
+    l0 = eng.launches
+    barrier()
+    ms = timed_steps(torch, lambda: eng.rank_device(qd, dbd, TOPK, **bufs), args.steps, flush)
+    barrier()
+    ms = max_over_ranks(ms) / args.steps
+    launches = eng.launches - l0
+    eq, rq = eng.embed_nodes(qd)
+    ed, rd = eng.embed_nodes(dbd)
+    k_ms = timed_steps(torch, lambda: eng.score_all_pairs_nodes(eq, rq, qd, ed, rd, dbd, out=bufs['sim']),
+                       args.steps, flush) / args.steps
+    e_ms = timed_steps(torch, lambda: (eng.embed_nodes(qd), eng.embed_nodes(dbd)), args.steps, flush) / args.steps
+    # algorithmic flops of the pair stage (SURVEY 8d): NTN 2DK (factorised per query) + histogram 2 N1 N2 d + head
+    no_q, no_d = qd.node_off.cpu().numpy(), dbd.node_off.cpu().numpy()
+    nq, nd = np.diff(no_q).astype(np.float64), np.diff(no_d).astype(np.float64)
+    cells = nq.sum() * nd.sum()
+    pi = [i for i, L in enumerate(layers) if L['kind'] == 'NTN'][0]
+    head_macs = sum(L['input_dim'] * L['output_dim'] for L in layers[pi + 1:] if L['kind'] == 'Dense')
+    flops = 2.0 * (16 * 16 + head_macs) * M_QUERIES * N_DB + 2.0 * 16 * cells
+    # ---- training on the same chain: BASELINE configs[2] shape (128 pairs / GPU / step, graphs <= 30 nodes) ----
+    enc, batch, batches = make_train_data(rank, world)
+    bd = batch.to(dev)
+    feeds = [(torch.as_tensor(a, device=dev), torch.as_tensor(b, device=dev), torch.as_tensor(t, device=dev), s1, s2)
+             for a, b, t, s1, s2 in batches]
+    loss = torch.zeros(4, dtype=torch.float32, device=dev)
+    grads = eng.device_buffers()[1]
+    gb = TRAIN_BATCH * world
+
+    def tstep(i):
+        g1, g2, t, s1, s2 = feeds[i % len(feeds)]
+        loss.zero_()
+        DS.data_parallel_step(eng, bd, g1, g2, t, gb, s1, s2, loss, dist if world > 1 else None, grads=grads)
+
+    n = max(args.steps * 10, 100)
+    for i in range(10):
+        tstep(i)
+    barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for i in range(n):
+        tstep(i)
+    b.record()
+    barrier()
+    t_ms = max_over_ranks(a.elapsed_time(b)) / n
+    return {'workload': 'BASELINE configs[0]/[1] chain on the headline data: {} queries x {} database graphs per GPU, '
+                        'GCN64-GCN32-GCN16-Attention-NTN(16,16)-Histogram(16)-FC(32-16-8-4-1), sigmoid, top-{}; '
+                        'fp32 CUDA-core all-pairs head kernel'.format(M_QUERIES, N_DB, TOPK),
+            'value': M_QUERIES * N_DB * world / (ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': ms,
+            'gpu_launches': launches,
+            'stage_ms': {'embed_q_plus_db_with_node_rows': e_ms, 'prep_plus_allpairs_head': k_ms},
+            'pair_stage': {'algorithmic_gflop': flops / 1e9, 'achieved_tflops_fp32': flops / (k_ms * 1e-3) / 1e12,
+                           'node_node_cells': cells},
+            'train': {'value': TRAIN_BATCH * world / (t_ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': t_ms, 'steps': n,
+                      'allreduce': 'none (1 GPU)' if world == 1 else 'nccl all-reduce',
+                      'workload': '{} pairs/GPU/step, AIDS10knef-shaped graphs (2..30 nodes), fwd+bwd+Adam, fp32'.format(TRAIN_BATCH),
+                      'final_loss': float(loss[0] + loss[1])}}
 
 
 def run_train(torch, dist, dev, rank, world, local, args, barrier, max_over_ranks):

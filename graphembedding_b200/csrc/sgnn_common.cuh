@@ -87,6 +87,11 @@ __device__ __forceinline__ float drop_mask(uint32_t layer_key, int row, int col,
   return floorf(keep + u) >= 1.f ? inv_keep : 0.f;
 }
 
+// sigmoid of a node-node score in the histogram layer: ONE definition for the three kernels that bin scores
+// (pair_histogram_kernel, the training kernel, the all-pairs head kernel), so they agree on every bin index.
+// ex2.approx + rcp.approx: |error| < 3e-7, far inside the 1e-5 bin-edge band the parity tests exclude.
+__device__ __forceinline__ float sgnn_hist_sigmoid(float s) { return __fdividef(1.f, 1.f + __expf(-s)); }
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -19,16 +19,16 @@
 #include "sgnn_internal.h"
 
 struct HeadPlan {
-  int threads;       // database graphs per CTA
+  int T;             // database graphs per CTA (the CTA has 2 T threads: two query lanes per graph)
   int S;             // words per database-graph stripe (node rows, stride ND each)
   int nmax_q;        // node rows reserved per staged query
   int hw_floats;     // head weight region
-  int q_floats;      // one staged query: P' [K][DEP] | C [K] | rows [nmax_q][ND] | n (1, padded to 4)
+  int q_floats;      // one staged query: P' [K][DEP] | C [K] | rows [nmax_q + 1][ND] | n (1, padded to 4)
   int w0, b0;        // offsets inside the head weight region: layer 0 weights [head_in][H0], bias [H0]
   int wl, bl;        // later layers: [n_head-1][H0][H0], [n_head-1][H0]
 };
 
-constexpr int HEAD_QC = 4;   // queries staged per round
+constexpr int HEAD_QC = 4;   // queries staged per round (two per query lane)
 
 template <int H0>
 __host__ __device__ inline void head_plan_weights(const ModelDev& M, HeadPlan& P) {
@@ -40,8 +40,64 @@ __host__ __device__ inline void head_plan_weights(const ModelDev& M, HeadPlan& P
   P.hw_floats = o;
 }
 
-template <int DEP, int H0, int ND>
-__global__ void __launch_bounds__(128)
+// Bin counters of one pair, in registers.  A cell adds 1 to a 4-bit field of `nib` (16 bins per 64-bit word);
+// every 12 cells the nibbles are folded into 8-bit fields (even / odd bins), and those spill into the thread's
+// shared-memory column only when a pair has more than ~240 cells (graphs beyond AIDS size).
+template <int NB>
+struct BinCounters {
+  static constexpr int W = NB / 16;
+  unsigned long long nib[W], ev[W], od[W];
+  int since_nib, since_byte;
+  bool spilled;
+  __device__ __forceinline__ void reset() {
+#pragma unroll
+    for (int w = 0; w < W; ++w) nib[w] = ev[w] = od[w] = 0ull;
+    since_nib = since_byte = 0; spilled = false;
+  }
+  __device__ __forceinline__ void add(int bin, bool valid) {
+    if (W == 1) {
+      nib[0] += (unsigned long long)valid << (bin * 4);
+    } else {
+#pragma unroll
+      for (int w = 0; w < W; ++w) nib[w] += (unsigned long long)(valid && (bin >> 4) == w) << ((bin & 15) * 4);
+    }
+  }
+  __device__ __forceinline__ void fold() {
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+      ev[w] += nib[w] & 0x0F0F0F0F0F0F0F0Full;
+      od[w] += (nib[w] >> 4) & 0x0F0F0F0F0F0F0F0Full;
+      nib[w] = 0ull;
+    }
+    since_byte += since_nib; since_nib = 0;
+  }
+  __device__ __forceinline__ int byte_of(int b) const {   // b: compile-time after unrolling
+    const unsigned long long v = (b & 1) ? od[b >> 4] : ev[b >> 4];
+    return (int)((v >> (((b & 15) >> 1) * 8)) & 0xFFull);
+  }
+  __device__ __forceinline__ void spill(int* col, int T, int bins) {
+    for (int b = 0; b < bins; ++b) {
+      int v = 0;
+#pragma unroll
+      for (int c = 0; c < NB; ++c) if (c == b) v = byte_of(c);
+      col[b * T] = (spilled ? col[b * T] : 0) + v;
+    }
+#pragma unroll
+    for (int w = 0; w < W; ++w) ev[w] = od[w] = 0ull;
+    since_byte = 0; spilled = true;
+  }
+  // after every group of up to 4 cells
+  __device__ __forceinline__ void tick(int* col, int T, int bins) {
+    since_nib += 4;
+    if (since_nib > 11) {
+      fold();
+      if (since_byte > 240) spill(col, T, bins);
+    }
+  }
+};
+
+template <int DEP, int H0, int ND, int NB>
+__global__ void __launch_bounds__(256)
 allpairs_head_kernel(const __grid_constant__ ModelDev M, const __grid_constant__ HeadPlan HP,
                      const float* __restrict__ params, const float* __restrict__ Pq, const float* __restrict__ Cq,
                      const float* __restrict__ emb_db, const float* __restrict__ nodes_q,
@@ -49,54 +105,55 @@ allpairs_head_kernel(const __grid_constant__ ModelDev M, const __grid_constant__
                      const int32_t* __restrict__ node_off_db, int m, int n, int q_per_block,
                      float* __restrict__ sim, int64_t ld) {
   extern __shared__ __align__(16) float smem[];
-  const int T = blockDim.x, tid = threadIdx.x;
+  const int NT = blockDim.x, tid = threadIdx.x, T = HP.T;
+  const int gl = tid % T, ql = tid / T;   // graph lane, query lane (uniform per warp: T is a multiple of 32)
   const int K = M.K, D = M.emb_dim, d = M.node_dim, bins = M.hist_bins;
   float* s_hw = smem;
   float* s_q = s_hw + HP.hw_floats;                       // [HEAD_QC][q_floats]
   float* s_rows = s_q + HEAD_QC * HP.q_floats;            // [T][S]
-  int* s_cnt = reinterpret_cast<int*>(s_rows + (size_t)T * HP.S);   // [bins][T]
+  int* s_cnt = reinterpret_cast<int*>(s_rows + (size_t)T * HP.S);   // [bins][2 T]: spill columns (large pairs only)
 
   // ---- head weights, zero-padded to H0 columns (and H0 rows for the later layers) ----
-  for (int i = tid; i < HP.hw_floats; i += T) s_hw[i] = 0.f;
+  for (int i = tid; i < HP.hw_floats; i += NT) s_hw[i] = 0.f;
   __syncthreads();
-  for (int k = tid; k < K; k += T) s_hw[k] = params[M.u_off + k];
+  for (int k = tid; k < K; k += NT) s_hw[k] = params[M.u_off + k];
   {
     const LayerDev& L = M.Hd[0];
-    for (int i = tid; i < L.din * L.dout; i += T) {
+    for (int i = tid; i < L.din * L.dout; i += NT) {
       const int k = i / L.dout, j = i - k * L.dout;
       s_hw[HP.w0 + k * H0 + j] = params[L.w_off + i];
     }
-    if (L.bias) for (int j = tid; j < L.dout; j += T) s_hw[HP.b0 + j] = params[L.b_off + j];
+    if (L.bias) for (int j = tid; j < L.dout; j += NT) s_hw[HP.b0 + j] = params[L.b_off + j];
   }
   for (int l = 1; l < M.n_head; ++l) {
     const LayerDev& L = M.Hd[l];
-    for (int i = tid; i < L.din * L.dout; i += T) {
+    for (int i = tid; i < L.din * L.dout; i += NT) {
       const int k = i / L.dout, j = i - k * L.dout;
       s_hw[HP.wl + ((l - 1) * H0 + k) * H0 + j] = params[L.w_off + i];
     }
-    if (L.bias) for (int j = tid; j < L.dout; j += T) s_hw[HP.bl + (l - 1) * H0 + j] = params[L.b_off + j];
+    if (L.bias) for (int j = tid; j < L.dout; j += NT) s_hw[HP.bl + (l - 1) * H0 + j] = params[L.b_off + j];
   }
 
   // ---- this CTA's database graphs: embedding -> registers, node rows -> private stripes ----
   const int g0 = blockIdx.x * T;
-  const int g = g0 + tid;
+  const int g = g0 + gl;
   float x[DEP];
 #pragma unroll
   for (int b = 0; b < DEP; ++b) x[b] = (g < n && b < D) ? emb_db[(size_t)g * D + b] : 0.f;
   const int n_g = (g < n && bins > 0) ? node_off_db[g + 1] - node_off_db[g] : 0;
   if (bins > 0) {
-    const int lane = tid & 31, warp = tid >> 5, nw = T >> 5;
+    const int lane = tid & 31, warp = tid >> 5, nw = NT >> 5;
     for (int gi = warp; gi < T && g0 + gi < n; gi += nw) {
       const int base = node_off_db[g0 + gi];
       const int cnt = node_off_db[g0 + gi + 1] - base;
       float* dst = s_rows + (size_t)gi * HP.S;
-      for (int idx = lane; idx < cnt * ND; idx += 32) {
-        const int r = idx / ND, c = idx - r * ND;
-        dst[idx] = c < d ? nodes_db[(size_t)(base + r) * d + c] : 0.f;
+      for (int idx = lane; idx < (cnt + 1) * ND; idx += 32) {   // one zero row behind the last: the 2 x 2 cell blocks
+        const int r = idx / ND, c = idx - r * ND;               // read it for odd node counts
+        dst[idx] = (r < cnt && c < d) ? nodes_db[(size_t)(base + r) * d + c] : 0.f;
       }
     }
   }
-  const float* my_rows = s_rows + (size_t)tid * HP.S;
+  const float* my_rows = s_rows + (size_t)gl * HP.S;
   int* my_cnt = s_cnt + tid;
   const int act = M.pair_act;
   const int q_begin = blockIdx.y * q_per_block;
@@ -109,31 +166,32 @@ allpairs_head_kernel(const __grid_constant__ ModelDev M, const __grid_constant__
       float* sq = s_q + qi * HP.q_floats;
       const float4* src = reinterpret_cast<const float4*>(Pq + (size_t)(q0 + qi) * K * DEP);
       float4* dst = reinterpret_cast<float4*>(sq);
-      for (int i = tid; i < K * DEP / 4; i += T) dst[i] = src[i];
+      for (int i = tid; i < K * DEP / 4; i += NT) dst[i] = src[i];
       float* sc = sq + K * DEP;
-      for (int k = tid; k < K; k += T) sc[k] = Cq[(size_t)(q0 + qi) * K + k];
+      for (int k = tid; k < K; k += NT) sc[k] = Cq[(size_t)(q0 + qi) * K + k];
       float* sr = sc + round_up4(K);
       if (bins > 0) {
         const int base = node_off_q[q0 + qi];
         const int cnt = node_off_q[q0 + qi + 1] - base;
-        for (int idx = tid; idx < cnt * ND; idx += T) {
+        for (int idx = tid; idx < (cnt + 1) * ND; idx += NT) {
           const int r = idx / ND, c = idx - r * ND;
-          sr[idx] = c < d ? nodes_q[(size_t)(base + r) * d + c] : 0.f;
+          sr[idx] = (r < cnt && c < d) ? nodes_q[(size_t)(base + r) * d + c] : 0.f;
         }
-        if (tid == 0) reinterpret_cast<int*>(sr + HP.nmax_q * ND)[0] = cnt;
+        if (tid == 0) reinterpret_cast<int*>(sr + (HP.nmax_q + 1) * ND)[0] = cnt;
       }
     }
     __syncthreads();
     if (g >= n) continue;
-    for (int qi = 0; qi < nq; ++qi) {
+    for (int qi = ql; qi < nq; qi += 2) {
       const float* sq = s_q + qi * HP.q_floats;
       const float* sc = sq + K * DEP;
       const float* sr = sc + round_up4(K);
-      const int n_q = bins > 0 ? reinterpret_cast<const int*>(sr + HP.nmax_q * ND)[0] : 0;
+      const int n_q = bins > 0 ? reinterpret_cast<const int*>(sr + (HP.nmax_q + 1) * ND)[0] : 0;
       float acc[H0];
 #pragma unroll
       for (int j = 0; j < H0; ++j) acc[j] = 0.f;
       // ---- NTN K-vector, folded straight into head layer 0 (row k of W0) ----
+#pragma unroll 2
       for (int k = 0; k < K; ++k) {
         const float4* p4 = reinterpret_cast<const float4*>(sq + k * DEP);
         float mk = sc[k];
@@ -156,45 +214,64 @@ allpairs_head_kernel(const __grid_constant__ ModelDev M, const __grid_constant__
           acc[4 * j + 3] = fmaf(f, w.w, acc[4 * j + 3]);
         }
       }
-      // ---- node-node similarity histogram ----
+      // ---- node-node similarity histogram: 2 x 2 blocks of cells = four independent chains ----
       if (bins > 0) {
-        for (int b = 0; b < bins; ++b) my_cnt[b * T] = 0;
+        BinCounters<NB> bc;
+        bc.reset();
         const float fb = (float)bins;
-        for (int j = 0; j < n_g; ++j) {
-          float hj[ND];
-          const float4* r4 = reinterpret_cast<const float4*>(my_rows + j * ND);
+        const int bmax = bins - 1;
+        for (int j = 0; j < n_g; j += 2) {
+          float ha[ND], hb[ND];
+          const float4* ra = reinterpret_cast<const float4*>(my_rows + j * ND);
+          const float4* rb = reinterpret_cast<const float4*>(my_rows + (j + 1) * ND);
 #pragma unroll
           for (int c = 0; c < ND / 4; ++c) {
-            const float4 v = r4[c];
-            hj[4 * c] = v.x; hj[4 * c + 1] = v.y; hj[4 * c + 2] = v.z; hj[4 * c + 3] = v.w;
+            const float4 u = ra[c], v = rb[c];
+            ha[4 * c] = u.x; ha[4 * c + 1] = u.y; ha[4 * c + 2] = u.z; ha[4 * c + 3] = u.w;
+            hb[4 * c] = v.x; hb[4 * c + 1] = v.y; hb[4 * c + 2] = v.z; hb[4 * c + 3] = v.w;
           }
-          for (int i = 0; i < n_q; ++i) {
-            const float4* q4 = reinterpret_cast<const float4*>(sr + i * ND);
-            float s = 0.f;
+          const bool vj = j + 1 < n_g;
+          for (int i = 0; i < n_q; i += 2) {
+            const float4* qa = reinterpret_cast<const float4*>(sr + i * ND);
+            const float4* qb = reinterpret_cast<const float4*>(sr + (i + 1) * ND);
+            float s00 = 0.f, s01 = 0.f, s10 = 0.f, s11 = 0.f;
 #pragma unroll
             for (int c = 0; c < ND / 4; ++c) {
-              const float4 v = q4[c];
-              s = fmaf(v.x, hj[4 * c + 0], s);
-              s = fmaf(v.y, hj[4 * c + 1], s);
-              s = fmaf(v.z, hj[4 * c + 2], s);
-              s = fmaf(v.w, hj[4 * c + 3], s);
+              const float4 u = qa[c], v = qb[c];
+              s00 = fmaf(u.x, ha[4 * c], s00); s01 = fmaf(u.x, hb[4 * c], s01);
+              s10 = fmaf(v.x, ha[4 * c], s10); s11 = fmaf(v.x, hb[4 * c], s11);
+              s00 = fmaf(u.y, ha[4 * c + 1], s00); s01 = fmaf(u.y, hb[4 * c + 1], s01);
+              s10 = fmaf(v.y, ha[4 * c + 1], s10); s11 = fmaf(v.y, hb[4 * c + 1], s11);
+              s00 = fmaf(u.z, ha[4 * c + 2], s00); s01 = fmaf(u.z, hb[4 * c + 2], s01);
+              s10 = fmaf(v.z, ha[4 * c + 2], s10); s11 = fmaf(v.z, hb[4 * c + 2], s11);
+              s00 = fmaf(u.w, ha[4 * c + 3], s00); s01 = fmaf(u.w, hb[4 * c + 3], s01);
+              s10 = fmaf(v.w, ha[4 * c + 3], s10); s11 = fmaf(v.w, hb[4 * c + 3], s11);
             }
-            s = 1.f / (1.f + expf(-s));
-            const int bin = min(bins - 1, (int)floorf(s * fb));
-            my_cnt[bin * T] += 1;
+            const bool vi = i + 1 < n_q;
+            bc.add(min(bmax, (int)floorf(sgnn_hist_sigmoid(s00) * fb)), true);
+            bc.add(min(bmax, (int)floorf(sgnn_hist_sigmoid(s01) * fb)), vj);
+            bc.add(min(bmax, (int)floorf(sgnn_hist_sigmoid(s10) * fb)), vi);
+            bc.add(min(bmax, (int)floorf(sgnn_hist_sigmoid(s11) * fb)), vi && vj);
+            bc.tick(my_cnt, NT, bins);
           }
         }
+        bc.fold();
         const int cells = n_q * n_g;
-        for (int b = 0; b < bins; ++b) {
-          const float hb = cells > 0 ? (float)my_cnt[b * T] / (float)cells : 0.f;
-          const float4* w4 = reinterpret_cast<const float4*>(s_hw + HP.w0 + (K + b) * H0);
+        const float inv_cells = cells > 0 ? 1.f / (float)cells : 0.f;
 #pragma unroll
-          for (int j = 0; j < H0 / 4; ++j) {
-            const float4 w = w4[j];
-            acc[4 * j + 0] = fmaf(hb, w.x, acc[4 * j + 0]);
-            acc[4 * j + 1] = fmaf(hb, w.y, acc[4 * j + 1]);
-            acc[4 * j + 2] = fmaf(hb, w.z, acc[4 * j + 2]);
-            acc[4 * j + 3] = fmaf(hb, w.w, acc[4 * j + 3]);
+        for (int b = 0; b < NB; ++b) {
+          if (b < bins) {
+            const int cnt = bc.byte_of(b) + (bc.spilled ? my_cnt[b * NT] : 0);
+            const float hb = (float)cnt * inv_cells;
+            const float4* w4 = reinterpret_cast<const float4*>(s_hw + HP.w0 + (K + b) * H0);
+#pragma unroll
+            for (int j = 0; j < H0 / 4; ++j) {
+              const float4 w = w4[j];
+              acc[4 * j + 0] = fmaf(hb, w.x, acc[4 * j + 0]);
+              acc[4 * j + 1] = fmaf(hb, w.y, acc[4 * j + 1]);
+              acc[4 * j + 2] = fmaf(hb, w.z, acc[4 * j + 2]);
+              acc[4 * j + 3] = fmaf(hb, w.w, acc[4 * j + 3]);
+            }
           }
         }
       }
@@ -207,7 +284,7 @@ allpairs_head_kernel(const __grid_constant__ ModelDev M, const __grid_constant__
       for (int l = 1; l < M.n_head; ++l) {
         const float* w = s_hw + HP.wl + (l - 1) * H0 * H0;
         const float* bl = s_hw + HP.bl + (l - 1) * H0;
-        const int din = M.Hd[l].din, al = M.Hd[l].act;
+        const int din = M.Hd[l].din, dout = M.Hd[l].dout, al = M.Hd[l].act;
         float nxt[H0];
 #pragma unroll
         for (int j = 0; j < H0; ++j) nxt[j] = 0.f;
@@ -217,11 +294,13 @@ allpairs_head_kernel(const __grid_constant__ ModelDev M, const __grid_constant__
             const float4* w4 = reinterpret_cast<const float4*>(w + k * H0);
 #pragma unroll
             for (int j = 0; j < H0 / 4; ++j) {
-              const float4 v = w4[j];
-              nxt[4 * j + 0] = fmaf(acc[k], v.x, nxt[4 * j + 0]);
-              nxt[4 * j + 1] = fmaf(acc[k], v.y, nxt[4 * j + 1]);
-              nxt[4 * j + 2] = fmaf(acc[k], v.z, nxt[4 * j + 2]);
-              nxt[4 * j + 3] = fmaf(acc[k], v.w, nxt[4 * j + 3]);
+              if (4 * j < dout) {
+                const float4 v = w4[j];
+                nxt[4 * j + 0] = fmaf(acc[k], v.x, nxt[4 * j + 0]);
+                nxt[4 * j + 1] = fmaf(acc[k], v.y, nxt[4 * j + 1]);
+                nxt[4 * j + 2] = fmaf(acc[k], v.z, nxt[4 * j + 2]);
+                nxt[4 * j + 3] = fmaf(acc[k], v.w, nxt[4 * j + 3]);
+              }
             }
           }
         }
@@ -233,38 +312,39 @@ allpairs_head_kernel(const __grid_constant__ ModelDev M, const __grid_constant__
   }
 }
 
-template <int DEP, int H0, int ND>
+template <int DEP, int H0, int ND, int NB>
 static cudaError_t launch_head(const ModelDev& M, const float* params, const float* Pq, const float* Cq,
                                const float* emb_db, const float* nodes_q, const int32_t* node_off_q, int max_nodes_q,
                                const float* nodes_db, const int32_t* node_off_db, int max_nodes_db, int m, int n,
                                float* sim, int64_t ld, int sm_count, int smem_optin, cudaStream_t st) {
   HeadPlan P;
   head_plan_weights<H0>(M, P);
-  P.nmax_q = M.hist_bins > 0 ? std::max(1, max_nodes_q) : 0;
-  P.q_floats = M.K * DEP + round_up4(M.K) + P.nmax_q * ND + 4;
-  const int rows = M.hist_bins > 0 ? std::max(1, max_nodes_db) * ND : 0;
-  P.S = (rows + 7) / 8 * 8 + 4;   // 4 * odd words: conflict-free 16-byte reads across a warp
+  const bool hist = M.hist_bins > 0;
+  P.nmax_q = hist ? std::max(1, max_nodes_q) : 0;
+  P.q_floats = M.K * DEP + round_up4(M.K) + (hist ? (P.nmax_q + 1) * ND + 4 : 0);
+  const int rows = hist ? (std::max(1, max_nodes_db) + 1) * ND : 0;
+  P.S = hist ? (rows + 7) / 8 * 8 + 4 : 0;   // 4 * odd words: conflict-free 16-byte reads across a warp
   auto bytes_for = [&](int t) {
-    return ((size_t)P.hw_floats + (size_t)HEAD_QC * P.q_floats + (size_t)t * P.S + (size_t)M.hist_bins * t) * sizeof(float);
+    return ((size_t)P.hw_floats + (size_t)HEAD_QC * P.q_floats + (size_t)t * P.S + (size_t)M.hist_bins * 2 * t) * sizeof(float);
   };
-  int threads = 0;
-  for (int t = 128; t >= 32 && !threads; t >>= 1)
-    if (2 * (bytes_for(t) + 1024) <= (size_t)smem_optin + 1024) threads = t;
-  for (int t = 128; t >= 32 && !threads; t >>= 1)
-    if (bytes_for(t) <= (size_t)smem_optin) threads = t;
-  if (!threads) return cudaErrorInvalidValue;
-  P.threads = threads;
-  const size_t smem = bytes_for(threads);
-  auto kern = allpairs_head_kernel<DEP, H0, ND>;
+  int T = 0;
+  for (int t = 128; t >= 32 && !T; t >>= 1)
+    if (2 * (bytes_for(t) + 1024) <= (size_t)smem_optin + 1024) T = t;
+  for (int t = 128; t >= 32 && !T; t >>= 1)
+    if (bytes_for(t) <= (size_t)smem_optin) T = t;
+  if (!T) return cudaErrorInvalidValue;
+  P.T = T;
+  const size_t smem = bytes_for(T);
+  auto kern = allpairs_head_kernel<DEP, H0, ND, NB>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  const int gx = (n + threads - 1) / threads;
-  // about four CTAs per SM in flight over the whole grid; a CTA keeps its database stripe for all its queries
+  const int gx = (n + T - 1) / T;
+  // about four CTAs per SM over the whole grid; a CTA keeps its database stripes for all its queries
   int gy = std::max(1, std::min((m + HEAD_QC - 1) / HEAD_QC, (sm_count * 4 + gx - 1) / gx));
   const int qpb = ((m + gy - 1) / gy + HEAD_QC - 1) / HEAD_QC * HEAD_QC;
   gy = (m + qpb - 1) / qpb;
-  kern<<<dim3(gx, gy), threads, smem, st>>>(M, P, params, Pq, Cq, emb_db, nodes_q, node_off_q, nodes_db, node_off_db,
-                                            m, n, qpb, sim, ld);
+  kern<<<dim3(gx, gy), 2 * T, smem, st>>>(M, P, params, Pq, Cq, emb_db, nodes_q, node_off_q, nodes_db, node_off_db,
+                                          m, n, qpb, sim, ld);
   return cudaGetLastError();
 }
 
@@ -284,15 +364,27 @@ cudaError_t sgnn_launch_allpairs_head(const ModelDev& M, int DEP, const float* p
 #define SGNN_HEAD_ARGS M, params, Pq, Cq, emb_db, nodes_q, node_off_q, max_nodes_q, nodes_db, node_off_db, \
                        max_nodes_db, m, n, sim, ld, sm_count, smem_optin, st
   const int key = (DEP == 32 ? 4 : 0) | (hmax > 16 ? 2 : 0) | (nd > 16 ? 1 : 0);
+  if (M.hist_bins <= 16) {
+    switch (key) {
+      case 0: return launch_head<16, 16, 16, 16>(SGNN_HEAD_ARGS);
+      case 1: return launch_head<16, 16, 32, 16>(SGNN_HEAD_ARGS);
+      case 2: return launch_head<16, 32, 16, 16>(SGNN_HEAD_ARGS);
+      case 3: return launch_head<16, 32, 32, 16>(SGNN_HEAD_ARGS);
+      case 4: return launch_head<32, 16, 16, 16>(SGNN_HEAD_ARGS);
+      case 5: return launch_head<32, 16, 32, 16>(SGNN_HEAD_ARGS);
+      case 6: return launch_head<32, 32, 16, 16>(SGNN_HEAD_ARGS);
+      default: return launch_head<32, 32, 32, 16>(SGNN_HEAD_ARGS);
+    }
+  }
   switch (key) {
-    case 0: return launch_head<16, 16, 16>(SGNN_HEAD_ARGS);
-    case 1: return launch_head<16, 16, 32>(SGNN_HEAD_ARGS);
-    case 2: return launch_head<16, 32, 16>(SGNN_HEAD_ARGS);
-    case 3: return launch_head<16, 32, 32>(SGNN_HEAD_ARGS);
-    case 4: return launch_head<32, 16, 16>(SGNN_HEAD_ARGS);
-    case 5: return launch_head<32, 16, 32>(SGNN_HEAD_ARGS);
-    case 6: return launch_head<32, 32, 16>(SGNN_HEAD_ARGS);
-    default: return launch_head<32, 32, 32>(SGNN_HEAD_ARGS);
+    case 0: return launch_head<16, 16, 16, 32>(SGNN_HEAD_ARGS);
+    case 1: return launch_head<16, 16, 32, 32>(SGNN_HEAD_ARGS);
+    case 2: return launch_head<16, 32, 16, 32>(SGNN_HEAD_ARGS);
+    case 3: return launch_head<16, 32, 32, 32>(SGNN_HEAD_ARGS);
+    case 4: return launch_head<32, 16, 16, 32>(SGNN_HEAD_ARGS);
+    case 5: return launch_head<32, 16, 32, 32>(SGNN_HEAD_ARGS);
+    case 6: return launch_head<32, 32, 16, 32>(SGNN_HEAD_ARGS);
+    default: return launch_head<32, 32, 32, 32>(SGNN_HEAD_ARGS);
   }
 #undef SGNN_HEAD_ARGS
 }

@@ -165,8 +165,7 @@ pair_histogram_kernel(const float* __restrict__ node_emb, int d, const int32_t* 
         const float* y = node_emb + (size_t)(b0 + j) * d;
         float s = 0.f;
         for (int k = 0; k < d; ++k) s = fmaf(x[k], y[k], s);
-        s = 1.f / (1.f + expf(-s));
-        bin = min(bins - 1, (int)floorf(s * (float)bins));
+        bin = min(bins - 1, (int)floorf(sgnn_hist_sigmoid(s) * (float)bins));
       }
       for (int b = 0; b < bins; ++b) {
         const unsigned m = __ballot_sync(0xffffffffu, bin == b);
@@ -178,7 +177,7 @@ pair_histogram_kernel(const float* __restrict__ node_emb, int d, const int32_t* 
     if (threadIdx.x < bins) {
       const int tot = s_cnt[0][lane] + s_cnt[1][lane] + s_cnt[2][lane] + s_cnt[3][lane];
       if (counts) counts[(size_t)p * bins + lane] = tot;
-      if (hist) hist[(size_t)p * bins + lane] = cells > 0 ? (float)tot / (float)cells : 0.f;
+      if (hist) hist[(size_t)p * bins + lane] = cells > 0 ? (float)tot * (1.f / (float)cells) : 0.f;
     }
     __syncthreads();
   }

@@ -353,11 +353,10 @@ __device__ __forceinline__ void team_head_fwd(const ModelDev& M, const float* W,
       const float* y = H2 + j * ald;
       float s = 0.f;
       for (int k = 0; k < d; ++k) s = fmaf(x[k], y[k], s);
-      s = 1.f / (1.f + expf(-s));
-      atomicAdd(&hcnt[min(bins - 1, (int)floorf(s * (float)bins))], 1);
+      atomicAdd(&hcnt[min(bins - 1, (int)floorf(sgnn_hist_sigmoid(s) * (float)bins))], 1);
     }
     __syncthreads();
-    if (tid < bins) hf[K + tid] = cells > 0 ? (float)hcnt[tid] / (float)cells : 0.f;
+    if (tid < bins) hf[K + tid] = cells > 0 ? (float)hcnt[tid] * (1.f / (float)cells) : 0.f;
     __syncthreads();
   }
   int in_off = 0;

@@ -111,7 +111,8 @@ allpairs_head_kernel(const __grid_constant__ ModelDev M, const __grid_constant__
   float* s_hw = smem;
   float* s_q = s_hw + HP.hw_floats;                       // [HEAD_QC][q_floats]
   float* s_rows = s_q + HEAD_QC * HP.q_floats;            // [T][S]
-  int* s_cnt = reinterpret_cast<int*>(s_rows + (size_t)T * HP.S);   // [bins][2 T]: spill columns (large pairs only)
+  // behind the stripes: ND words of padding, then [bins][2 T] spill columns (only when a pair can exceed 240 cells)
+  int* s_cnt = reinterpret_cast<int*>(s_rows + (size_t)T * HP.S + ND);
 
   // ---- head weights, zero-padded to H0 columns (and H0 rows for the later layers) ----
   for (int i = tid; i < HP.hw_floats; i += NT) s_hw[i] = 0.f;
@@ -147,9 +148,11 @@ allpairs_head_kernel(const __grid_constant__ ModelDev M, const __grid_constant__
       const int base = node_off_db[g0 + gi];
       const int cnt = node_off_db[g0 + gi + 1] - base;
       float* dst = s_rows + (size_t)gi * HP.S;
-      for (int idx = lane; idx < (cnt + 1) * ND; idx += 32) {   // one zero row behind the last: the 2 x 2 cell blocks
-        const int r = idx / ND, c = idx - r * ND;               // read it for odd node counts
-        dst[idx] = (r < cnt && c < d) ? nodes_db[(size_t)(base + r) * d + c] : 0.f;
+      // (for an odd node count the 2 x 2 cell blocks read one row past the last: whatever lies there -- the
+      // next stripe or the tail padding -- is computed on and discarded by the validity flags)
+      for (int idx = lane; idx < cnt * ND; idx += 32) {
+        const int r = idx / ND, c = idx - r * ND;
+        dst[idx] = c < d ? nodes_db[(size_t)(base + r) * d + c] : 0.f;
       }
     }
   }
@@ -322,16 +325,22 @@ static cudaError_t launch_head(const ModelDev& M, const float* params, const flo
   const bool hist = M.hist_bins > 0;
   P.nmax_q = hist ? std::max(1, max_nodes_q) : 0;
   P.q_floats = M.K * DEP + round_up4(M.K) + (hist ? (P.nmax_q + 1) * ND + 4 : 0);
-  const int rows = hist ? (std::max(1, max_nodes_db) + 1) * ND : 0;
+  const int rows = hist ? std::max(1, max_nodes_db) * ND : 0;
   P.S = hist ? (rows + 7) / 8 * 8 + 4 : 0;   // 4 * odd words: conflict-free 16-byte reads across a warp
+  const bool can_spill = hist && (int64_t)max_nodes_q * max_nodes_db > 240;   // BinCounters byte fields hold 255
   auto bytes_for = [&](int t) {
-    return ((size_t)P.hw_floats + (size_t)HEAD_QC * P.q_floats + (size_t)t * P.S + (size_t)M.hist_bins * 2 * t) * sizeof(float);
+    return ((size_t)P.hw_floats + (size_t)HEAD_QC * P.q_floats + (size_t)t * P.S + ND +
+            (can_spill ? (size_t)M.hist_bins * 2 * t : 0)) * sizeof(float);
   };
-  int T = 0;
-  for (int t = 128; t >= 32 && !T; t >>= 1)
-    if (2 * (bytes_for(t) + 1024) <= (size_t)smem_optin + 1024) T = t;
-  for (int t = 128; t >= 32 && !T; t >>= 1)
-    if (bytes_for(t) <= (size_t)smem_optin) T = t;
+  // stripes per CTA: the choice that keeps the most warps resident (shared memory: 1 KB reserved per CTA;
+  // registers: 4 CTAs of 128 threads or 2 of 256)
+  int T = 0, best = 0;
+  for (int t = 128; t >= 32; t >>= 1) {
+    if (bytes_for(t) > (size_t)smem_optin) continue;
+    const int by_smem = (int)(((size_t)smem_optin + 1024) / (bytes_for(t) + 1024));
+    const int warps = std::min(by_smem, 512 / (2 * t)) * (2 * t / 32);
+    if (warps > best) { best = warps; T = t; }
+  }
   if (!T) return cudaErrorInvalidValue;
   P.T = T;
   const size_t smem = bytes_for(T);
@@ -339,8 +348,9 @@ static cudaError_t launch_head(const ModelDev& M, const float* params, const flo
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   const int gx = (n + T - 1) / T;
-  // about four CTAs per SM over the whole grid; a CTA keeps its database stripes for all its queries
-  int gy = std::max(1, std::min((m + HEAD_QC - 1) / HEAD_QC, (sm_count * 4 + gx - 1) / gx));
+  // ~24 CTAs per SM over the whole grid (6+ waves of the resident set, so the last wave costs a few per cent);
+  // a CTA keeps its database stripes for all its queries -- re-staging them per CTA is ~20 bytes per pair from L2
+  int gy = std::max(1, std::min((m + HEAD_QC - 1) / HEAD_QC, (sm_count * 24 + gx - 1) / gx));
   const int qpb = ((m + gy - 1) / gy + HEAD_QC - 1) / HEAD_QC * HEAD_QC;
   gy = (m + qpb - 1) / qpb;
   kern<<<dim3(gx, gy), 2 * T, smem, st>>>(M, P, params, Pq, Cq, emb_db, nodes_q, node_off_q, nodes_db, node_off_db,

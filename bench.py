@@ -397,8 +397,32 @@ def run_cuda(args):
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / args.steps
     if world == 1:
         assert torch.equal(ids_h.to(dev), out['ids']), 'host entry point and device path disagree'
-    e2e = {'value': M_QUERIES * N_DB * world / (e2e_ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': e2e_ms,
-           'h2d_bytes_per_step': q.nbytes() + db.nbytes(), 'd2h_bytes_per_step': 2 * 4 * M_QUERIES * TOPK}
+    csr = {'value': M_QUERIES * N_DB * world / (e2e_ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': e2e_ms,
+           'h2d_bytes_per_step': q.nbytes() + db.nbytes(), 'd2h_bytes_per_step': 2 * 4 * M_QUERIES * TOPK,
+           'entry_point': 'sgnn_rank_host (int32 / float CSR arrays from pinned host memory)'}
+    # the same step with the batches in the compact wire format (sgnn_compact_batch: byte-wide fields + value
+    # dictionary, built once per dataset on the host like the CSR itself; expanded on the device every step)
+    qc, dbc = q.compact(), db.compact()
+    e2e = csr
+    if qc is not None and dbc is not None:
+        ids_c = torch.empty((M_QUERIES, TOPK), dtype=torch.int32).pin_memory()
+        vals_c = torch.empty((M_QUERIES, TOPK), dtype=torch.float32).pin_memory()
+        t_w = time.perf_counter()
+        n_w = 0
+        while n_w < args.warmup or time.perf_counter() - t_w < 0.1:
+            eng.rank_host_compact(qc, dbc, TOPK, ids=ids_c, vals=vals_c)
+            n_w += 1
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            eng.rank_host_compact(qc, dbc, TOPK, ids=ids_c, vals=vals_c)
+        barrier()
+        c_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / args.steps
+        assert torch.equal(ids_c, ids_h), 'compact and plain host entry points disagree'
+        e2e = {'value': M_QUERIES * N_DB * world / (c_ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': c_ms,
+               'h2d_bytes_per_step': int(qc.numel() + dbc.numel()), 'd2h_bytes_per_step': 2 * 4 * M_QUERIES * TOPK,
+               'entry_point': 'sgnn_rank_host_compact (compact wire blobs from pinned host memory, expanded on the device)',
+               'plain_csr': csr}
     if world > 1:
         e2e['note'] = 'per-rank sgnn_rank_host on its own shard (host in, local top-k out); the cross-rank merge is in value'
 

@@ -11,6 +11,7 @@
 #include "sgnn_internal.h"
 #include "sgnn_small.cuh"
 #include "sgnn_train_team.cuh"
+#include "sgnn_compact.h"
 
 namespace {
 
@@ -1060,6 +1061,62 @@ static int upload_batch_on(SgnnHandle h, const SgnnGraphBatch* b, int slot, Sgnn
   return 0;
 }
 
+// Expansion of a compact blob (sgnn_compact.h) into the int32 / float CSR arrays the kernels read: one warp
+// per graph; row offsets by a warp prefix sum over the row lengths (32 nodes at a time with a carry), then the
+// graph's entries are written by all lanes (coalesced), values from the dictionary.
+__global__ void __launch_bounds__(256)
+expand_compact_kernel(const uint8_t* __restrict__ blob, int32_t* __restrict__ node_off, int32_t* __restrict__ labels,
+                      int32_t* __restrict__ rowptr, int32_t* __restrict__ col, float* __restrict__ val) {
+  const SgnnCompactHeader* hd = reinterpret_cast<const SgnnCompactHeader*>(blob);
+  const int G = hd->n_graphs, N = hd->total_nodes;
+  const SgnnCompactLayout L = sgnn_compact_layout(G, N, hd->nnz, hd->n_codes);
+  const int32_t* no = reinterpret_cast<const int32_t*>(blob + L.node_off);
+  const int32_t* eo = reinterpret_cast<const int32_t*>(blob + L.e_off);
+  const float* dict = reinterpret_cast<const float*>(blob + L.dict);
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+  for (int g = warp; g < G; g += nwarps) {
+    const int n0 = no[g], n1 = no[g + 1], e0 = eo[g], e1 = eo[g + 1];
+    if (lane == 0) {
+      node_off[g] = n0;
+      if (g == G - 1) { node_off[G] = n1; rowptr[N] = e1; }
+    }
+    int carry = e0;
+    for (int i0 = n0; i0 < n1; i0 += 32) {
+      const int i = i0 + lane;
+      const int len = i < n1 ? blob[L.row_nnz + i] : 0;
+      int incl = len;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+      }
+      if (i < n1) { rowptr[i] = carry + incl - len; labels[i] = blob[L.labels + i]; }
+      carry += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    for (int e = e0 + lane; e < e1; e += 32) { col[e] = blob[L.col + e]; val[e] = dict[blob[L.vcode + e]]; }
+  }
+}
+
+// compact host blob -> arena (one copy) -> expanded arrays of `slot`
+static int upload_compact_on(SgnnHandle h, const uint8_t* blob, int slot, SgnnGraphBatch* dev, cudaStream_t st) {
+  HostWs& w = h->ws;
+  SgnnCompactHeader hd;
+  memcpy(&hd, blob, sizeof(hd));
+  if (hd.magic != SGNN_COMPACT_MAGIC) return fail(h, "not a compact batch (sgnn_compact_batch)");
+  if (hd.n_graphs > w.cap_graphs || hd.total_nodes > w.cap_nodes || hd.nnz > w.cap_nnz || hd.total_bytes > w.arena_cap)
+    return fail(h, "host workspace too small: call sgnn_reserve first");
+  CUDA_OK(h, cudaMemcpyAsync(w.arena[slot], blob, (size_t)hd.total_bytes, cudaMemcpyHostToDevice, st));
+  const int blocks = std::max(1, std::min((hd.n_graphs + 7) / 8, h->sm_count * 8));
+  expand_compact_kernel<<<blocks, 256, 0, st>>>(w.arena[slot], w.node_off[slot], w.labels[slot], w.rowptr[slot],
+                                                w.col[slot], w.val[slot]);
+  CUDA_OK(h, cudaGetLastError());
+  dev->n_graphs = hd.n_graphs; dev->total_nodes = hd.total_nodes; dev->nnz = hd.nnz; dev->max_nodes = hd.max_nodes;
+  dev->node_off = w.node_off[slot]; dev->labels = w.labels[slot]; dev->rowptr = w.rowptr[slot];
+  dev->col = w.col[slot]; dev->val = w.val[slot];
+  return 0;
+}
+
 static int upload_batch(SgnnHandle h, const SgnnGraphBatch* b, int slot, SgnnGraphBatch* dev) {
   return upload_batch_on(h, b, slot, dev, h->stream);
 }
@@ -1217,25 +1274,25 @@ int sgnn_debug_slice_hints(SgnnHandle h, unsigned long long** hints_dev, int64_t
   return 0;
 }
 
-int sgnn_rank_host(SgnnHandle h, const SgnnGraphBatch* q, const SgnnGraphBatch* db, int32_t k,
-                   int32_t* topk_ids_host, float* topk_vals_host, float* sim_host) {
-  if (!h || !q || !db) return fail(h, "sgnn_rank_host: null argument");
-  CUDA_OK(h, cudaSetDevice(h->device));
+}  // extern "C"
+
+// shared body of sgnn_rank_host / sgnn_rank_host_compact: `up(slot, dev, stream)` uploads one side
+template <typename UpQ, typename UpDb>
+static int rank_host_impl(SgnnHandle h, int64_t m, int64_t n, const uint64_t* key_words, int n_key, UpQ up_q, UpDb up_db,
+                          int32_t k, int32_t* topk_ids_host, float* topk_vals_host, float* sim_host) {
   HostWs& w = h->ws;
-  const int64_t m = q->n_graphs, n = db->n_graphs;
   if (m * n > w.cap_q * w.cap_db || m > w.cap_q || (int64_t)m * k > w.cap_topk)
     return fail(h, "host workspace too small: call sgnn_reserve first");
   cudaStream_t st = h->stream, cs = h->copy_stream;
   const bool want_topk = k > 0 && topk_ids_host;
   auto body = [&]() -> int {
-    // the database upload (8 bytes per non-zero over PCIe) runs on the copy stream while the compute
-    // stream uploads and embeds the queries
+    // the database upload (PCIe) runs on the copy stream while the compute stream uploads and embeds the queries
     SgnnGraphBatch dq, ddb;
     CUDA_OK(h, cudaEventRecord(h->chunk_ev[3], st));
     CUDA_OK(h, cudaStreamWaitEvent(cs, h->chunk_ev[3], 0));
-    if (upload_batch_on(h, db, 1, &ddb, cs)) return 1;
+    if (up_db(1, &ddb, cs)) return 1;
     CUDA_OK(h, cudaEventRecord(h->chunk_ev[0], cs));
-    if (upload_batch_on(h, q, 0, &dq, st)) return 1;
+    if (up_q(0, &dq, st)) return 1;
     if (embed_side(h, &dq, w.emb_q, 0, st)) return 1;
     // query-side tables of the scorer are ready before the database lands
     if (score_all_pairs_stages(h, w.emb_q, (int)m, w.emb_db, (int)n, w.sim, n, st, SCORE_PREP_Q)) return 1;
@@ -1252,14 +1309,50 @@ int sgnn_rank_host(SgnnHandle h, const SgnnGraphBatch* q, const SgnnGraphBatch* 
     if (sim_host) CUDA_OK(h, cudaMemcpyAsync(sim_host, w.sim, (size_t)m * n * 4, cudaMemcpyDeviceToHost, st));
     return 0;
   };
+  if (run_cached(h, h->g_rank_host, fnv1a(key_words, sizeof(uint64_t) * (size_t)n_key), st, body)) return 1;
+  CUDA_OK(h, cudaStreamSynchronize(st));
+  return 0;
+}
+
+extern "C" {
+
+int sgnn_rank_host(SgnnHandle h, const SgnnGraphBatch* q, const SgnnGraphBatch* db, int32_t k,
+                   int32_t* topk_ids_host, float* topk_vals_host, float* sim_host) {
+  if (!h || !q || !db) return fail(h, "sgnn_rank_host: null argument");
+  CUDA_OK(h, cudaSetDevice(h->device));
   uint64_t kb[18] = {};
   key_batch(kb, q);
   key_batch(kb + 7, db);
   kb[14] = (uint64_t)k; kb[15] = (uint64_t)(uintptr_t)topk_ids_host; kb[16] = (uint64_t)(uintptr_t)topk_vals_host;
   kb[17] = (uint64_t)(uintptr_t)sim_host;
-  if (run_cached(h, h->g_rank_host, fnv1a(kb, sizeof(kb)), st, body)) return 1;
-  CUDA_OK(h, cudaStreamSynchronize(st));
-  return 0;
+  return rank_host_impl(
+      h, q->n_graphs, db->n_graphs, kb, 18,
+      [&](int slot, SgnnGraphBatch* d, cudaStream_t s) { return upload_batch_on(h, q, slot, d, s); },
+      [&](int slot, SgnnGraphBatch* d, cudaStream_t s) { return upload_batch_on(h, db, slot, d, s); }, k, topk_ids_host,
+      topk_vals_host, sim_host);
+}
+
+int sgnn_rank_host_compact(SgnnHandle h, const uint8_t* q_blob, const uint8_t* db_blob, int32_t k,
+                           int32_t* topk_ids_host, float* topk_vals_host, float* sim_host) {
+  if (!h || !q_blob || !db_blob) return fail(h, "sgnn_rank_host_compact: null argument");
+  CUDA_OK(h, cudaSetDevice(h->device));
+  SgnnCompactHeader hq, hdb;
+  memcpy(&hq, q_blob, sizeof(hq));
+  memcpy(&hdb, db_blob, sizeof(hdb));
+  if (hq.magic != SGNN_COMPACT_MAGIC || hdb.magic != SGNN_COMPACT_MAGIC)
+    return fail(h, "sgnn_rank_host_compact: not a compact batch (sgnn_compact_batch)");
+  uint64_t kb[12] = {};
+  kb[0] = (uint64_t)(uintptr_t)q_blob; kb[1] = (uint64_t)(uintptr_t)db_blob;
+  kb[2] = ((uint64_t)(uint32_t)hq.n_graphs << 32) | (uint32_t)hq.max_nodes; kb[3] = (uint64_t)hq.total_bytes;
+  kb[4] = ((uint64_t)(uint32_t)hdb.n_graphs << 32) | (uint32_t)hdb.max_nodes; kb[5] = (uint64_t)hdb.total_bytes;
+  kb[6] = (uint64_t)k; kb[7] = (uint64_t)(uintptr_t)topk_ids_host; kb[8] = (uint64_t)(uintptr_t)topk_vals_host;
+  kb[9] = (uint64_t)(uintptr_t)sim_host; kb[10] = ((uint64_t)(uint32_t)hq.total_nodes << 32) | (uint32_t)hdb.total_nodes;
+  kb[11] = 0x636f6d70616374ull;   // distinct from the plain entry point's keys
+  return rank_host_impl(
+      h, hq.n_graphs, hdb.n_graphs, kb, 12,
+      [&](int slot, SgnnGraphBatch* d, cudaStream_t s) { return upload_compact_on(h, q_blob, slot, d, s); },
+      [&](int slot, SgnnGraphBatch* d, cudaStream_t s) { return upload_compact_on(h, db_blob, slot, d, s); }, k,
+      topk_ids_host, topk_vals_host, sim_host);
 }
 
 int sgnn_train_step_host(SgnnHandle h, const SgnnGraphBatch* b, const int32_t* g1, const int32_t* g2,

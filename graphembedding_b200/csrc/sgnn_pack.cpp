@@ -62,3 +62,99 @@ extern "C" int sgnn_pack_graphs(int32_t n_graphs, const int32_t* node_counts, co
   if (max_nodes_out) *max_nodes_out = max_n;
   return 0;
 }
+
+// ---- compact wire format of a packed batch (for the host-buffer entry points) -----------------------
+// A ranking step over PCIe is bound by the upload of the batch (287 B per AIDS-sized graph as int32/float
+// CSR).  The CSR of small labelled graphs is highly redundant: labels, row lengths and local column indices
+// fit a byte, and A_hat takes a handful of distinct values (products of deg^-1/2).  The compact blob carries
+//   header | node_off int32[G+1] | e_off int32[G+1] | labels u8[N] | row_nnz u8[N] | col u8[nnz] |
+//   vcode u8[nnz] | dict float[n_codes]
+// (~80 B per graph) and a device kernel expands it back into EXACTLY the arrays it was built from (values
+// come out of the dictionary, so they are bit-identical by construction).  Batches that do not fit the
+// byte fields (labels or row lengths > 255, graphs > 256 nodes, > 256 distinct values) return 4 and the
+// caller stays on the plain format.
+#include <cstring>
+#include <map>
+#include "sgnn_compact.h"
+
+extern "C" int64_t sgnn_compact_bound(const SgnnGraphBatch* b) {
+  if (!b) return -1;
+  return sgnn_compact_layout(b->n_graphs, b->total_nodes, b->nnz, 256).total;
+}
+
+extern "C" int sgnn_compact_batch(const SgnnGraphBatch* b, uint8_t* out, int64_t cap, int64_t* bytes_out) {
+  if (!b || !out) return 1;
+  const int32_t G = b->n_graphs, N = b->total_nodes;
+  const int64_t nnz = b->nnz;
+  if (b->max_nodes > 256) return 4;
+  std::map<uint32_t, int> codes;   // by bit pattern: -0.0f / NaN payloads stay distinct
+  std::vector<uint8_t> vcode((size_t)nnz);
+  for (int64_t e = 0; e < nnz; ++e) {
+    uint32_t bits;
+    std::memcpy(&bits, &b->val[e], 4);
+    auto it = codes.find(bits);
+    if (it == codes.end()) {
+      if (codes.size() == 256) return 4;
+      it = codes.emplace(bits, (int)codes.size()).first;
+    }
+    vcode[(size_t)e] = (uint8_t)it->second;
+  }
+  const SgnnCompactLayout L = sgnn_compact_layout(G, N, nnz, (int)codes.size());
+  if (L.total > cap) return 5;
+  std::memset(out, 0, (size_t)L.total);
+  SgnnCompactHeader hd;
+  std::memset(&hd, 0, sizeof(hd));
+  hd.magic = SGNN_COMPACT_MAGIC; hd.n_graphs = G; hd.total_nodes = N; hd.nnz = nnz; hd.max_nodes = b->max_nodes;
+  hd.n_codes = (int32_t)codes.size(); hd.total_bytes = L.total;
+  std::memcpy(out, &hd, sizeof(hd));
+  int32_t* node_off = reinterpret_cast<int32_t*>(out + L.node_off);
+  int32_t* e_off = reinterpret_cast<int32_t*>(out + L.e_off);
+  for (int32_t g = 0; g <= G; ++g) {
+    node_off[g] = b->node_off[g];
+    e_off[g] = b->rowptr[b->node_off[g]];
+  }
+  for (int32_t i = 0; i < N; ++i) {
+    const int32_t len = b->rowptr[i + 1] - b->rowptr[i];
+    if (b->labels[i] < 0 || b->labels[i] > 255 || len < 0 || len > 255) return 4;
+    out[L.labels + i] = (uint8_t)b->labels[i];
+    out[L.row_nnz + i] = (uint8_t)len;
+  }
+  for (int64_t e = 0; e < nnz; ++e) {
+    if (b->col[e] < 0 || b->col[e] > 255) return 4;
+    out[L.col + e] = (uint8_t)b->col[e];
+    out[L.vcode + e] = vcode[(size_t)e];
+  }
+  float* dict = reinterpret_cast<float*>(out + L.dict);
+  for (const auto& kv : codes) std::memcpy(&dict[kv.second], &kv.first, 4);
+  if (bytes_out) *bytes_out = L.total;
+  return 0;
+}
+
+// Host restatement of the device expansion (tests: blob -> arrays must reproduce the batch bit for bit).
+extern "C" int sgnn_expand_compact_host(const uint8_t* blob, int32_t* node_off, int32_t* labels, int32_t* rowptr,
+                                        int32_t* col, float* val) {
+  if (!blob) return 1;
+  SgnnCompactHeader hd;
+  std::memcpy(&hd, blob, sizeof(hd));
+  if (hd.magic != SGNN_COMPACT_MAGIC) return 2;
+  const SgnnCompactLayout L = sgnn_compact_layout(hd.n_graphs, hd.total_nodes, hd.nnz, hd.n_codes);
+  const int32_t* no = reinterpret_cast<const int32_t*>(blob + L.node_off);
+  const int32_t* eo = reinterpret_cast<const int32_t*>(blob + L.e_off);
+  const float* dict = reinterpret_cast<const float*>(blob + L.dict);
+  for (int32_t g = 0; g < hd.n_graphs; ++g) {
+    node_off[g] = no[g];
+    int32_t e = eo[g];
+    for (int32_t i = no[g]; i < no[g + 1]; ++i) {
+      rowptr[i] = e;
+      labels[i] = blob[L.labels + i];
+      e += blob[L.row_nnz + i];
+    }
+  }
+  node_off[hd.n_graphs] = no[hd.n_graphs];
+  rowptr[hd.total_nodes] = (int32_t)hd.nnz;
+  for (int64_t e = 0; e < hd.nnz; ++e) {
+    col[e] = blob[L.col + e];
+    val[e] = dict[blob[L.vcode + e]];
+  }
+  return 0;
+}

@@ -376,6 +376,16 @@ class SgnnEngine(object):
         self.launches += 6   # embed(queries) + embed(database) + 2 operand preps + scorer + top-k
         return ids, vals
 
+    def rank_host_compact(self, q_blob, db_blob, k, ids=None, vals=None, sim=None):
+        """sgnn_rank_host on compact blobs (PackedBatch.compact())."""
+        m = int(np.frombuffer(bytes(np.asarray(q_blob[4:8])), np.int32)[0])
+        ids = np.empty((m, k), np.int32) if ids is None else ids
+        vals = np.empty((m, k), np.float32) if vals is None else vals
+        check(self.h, lib().sgnn_rank_host_compact(self.h, _ptr(q_blob), _ptr(db_blob), k, _ptr(ids), _ptr(vals),
+                                                   _ptr(sim)))
+        self.launches += 8   # 2 expansions + embed(queries) + embed(database) + 2 operand preps + scorer + top-k
+        return ids, vals
+
     def train_step_host(self, batch, g1, g2, target_sim, loss=None):
         loss = np.zeros(2, np.float32) if loss is None else loss
         s = batch.struct()

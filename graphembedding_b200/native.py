@@ -95,6 +95,10 @@ SIGNATURES = {
     'sgnn_apply_adam_allreduce': (C.c_int, [_P, _F, _P, _P]),
     'sgnn_debug_slice_hints': (C.c_int, [_P, _P, _P]),
     'sgnn_rank_host': (C.c_int, [_P, _BP, _BP, _I32, _P, _P, _P]),
+    'sgnn_compact_bound': (_I64, [_BP]),
+    'sgnn_compact_batch': (C.c_int, [_BP, _P, _I64, _P]),
+    'sgnn_expand_compact_host': (C.c_int, [_P, _P, _P, _P, _P, _P]),
+    'sgnn_rank_host_compact': (C.c_int, [_P, _P, _P, _I32, _P, _P, _P]),
     'sgnn_train_step_host': (C.c_int, [_P, _BP, _P, _P, _P, _I32, _P]),
 }
 
@@ -197,6 +201,39 @@ class PackedBatch(object):
         pb = PackedBatch(*out, max_nodes=self.max_nodes)
         pb._arena = arena
         return pb
+
+    def compact(self, pinned=True):
+        """Compact wire blob (sgnn_compact_batch) as a uint8 torch tensor, pinned by default; None if the batch
+        does not fit the byte-wide fields."""
+        import torch
+        host = PackedBatch(*[np.ascontiguousarray(np.asarray(getattr(self, f))) for f in self.FIELDS],
+                           max_nodes=self.max_nodes)
+        st = host.struct()
+        cap = int(lib().sgnn_compact_bound(C.byref(st)))
+        blob = torch.empty(cap, dtype=torch.uint8)
+        if pinned and torch.cuda.is_available():
+            blob = blob.pin_memory()
+        n = C.c_int64(0)
+        rc = lib().sgnn_compact_batch(C.byref(st), blob.data_ptr(), cap, C.addressof(n))
+        if rc == 4:
+            return None
+        if rc != 0:
+            raise SgnnError('sgnn_compact_batch failed with code {}'.format(rc))
+        return blob[:n.value]
+
+    @staticmethod
+    def from_compact(blob):
+        """Host expansion of a compact blob (sgnn_expand_compact_host) -> PackedBatch (numpy)."""
+        hdr = np.frombuffer(bytes(np.asarray(blob[:64])), np.int32)
+        G, N, mx = int(hdr[1]), int(hdr[2]), int(hdr[3])
+        nnz = int(np.frombuffer(bytes(np.asarray(blob[16:24])), np.int64)[0])
+        arr = np.ascontiguousarray(np.asarray(blob))
+        node_off, labels = np.empty(G + 1, np.int32), np.empty(N, np.int32)
+        rowptr, col, val = np.empty(N + 1, np.int32), np.empty(max(nnz, 1), np.int32), np.empty(max(nnz, 1), np.float32)
+        rc = lib().sgnn_expand_compact_host(_ptr(arr), _ptr(node_off), _ptr(labels), _ptr(rowptr), _ptr(col), _ptr(val))
+        if rc != 0:
+            raise SgnnError('sgnn_expand_compact_host failed with code {}'.format(rc))
+        return PackedBatch(node_off, labels, rowptr, col[:nnz], val[:nnz], mx)
 
     def nbytes(self):
         return 4 * (self.n_graphs + 1 + self.total_nodes + self.total_nodes + 1 + 2 * self.nnz)

@@ -283,6 +283,21 @@ int sgnn_debug_slice_hints(SgnnHandle h, unsigned long long** hints_dev, int64_t
  * full m x n matrix is copied back only if sim_host != NULL. */
 int sgnn_rank_host(SgnnHandle h, const SgnnGraphBatch* queries_host, const SgnnGraphBatch* db_host,
                    int32_t k, int32_t* topk_ids_host, float* topk_vals_host, float* sim_host);
+/* ---- compact wire format for the host-buffer entry points ---------------------------------------------
+ * Over PCIe a ranking step is bound by the upload of the batch.  sgnn_compact_batch (host, no GPU) re-encodes a
+ * packed batch as byte-wide labels / row lengths / column indices plus a dictionary of the distinct A_hat
+ * values (~80 B per AIDS-sized graph instead of 287 B); the device expands it back into exactly the arrays it was
+ * built from (bit-identical: values come out of the dictionary).  Returns 4 if the batch does not fit the byte
+ * fields (labels or row lengths > 255, graphs > 256 nodes, > 256 distinct values) -- stay on sgnn_rank_host then --
+ * and 5 if `capacity` < sgnn_compact_bound(batch).  The blob is self-describing and relocatable. */
+int64_t sgnn_compact_bound(const SgnnGraphBatch* batch_host);
+int sgnn_compact_batch(const SgnnGraphBatch* batch_host, uint8_t* blob_out, int64_t capacity, int64_t* bytes_out);
+/* host restatement of the device expansion (tests / tools): blob -> the five arrays of the batch */
+int sgnn_expand_compact_host(const uint8_t* blob, int32_t* node_off, int32_t* labels, int32_t* rowptr, int32_t* col,
+                             float* val);
+/* sgnn_rank_host on two compact blobs (pinned host memory for full PCIe rate) */
+int sgnn_rank_host_compact(SgnnHandle h, const uint8_t* queries_blob, const uint8_t* db_blob, int32_t k,
+                           int32_t* topk_ids_host, float* topk_vals_host, float* sim_host);
 /* one optimizer step: forward + backward + Adam; returns [mse_part, wd_part] */
 int sgnn_train_step_host(SgnnHandle h, const SgnnGraphBatch* batch_host, const int32_t* g1,
                          const int32_t* g2, const float* target_sim, int32_t n_pairs, float* loss_host);

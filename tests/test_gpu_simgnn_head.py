@@ -213,3 +213,23 @@ def test_head_chain_validation_errors():
             SgnnEngine(parse_layers(spec, 29), 29)
     with pytest.raises(RuntimeError):
         parse_layers(base + ['Histogram'], 29)          # arity, like layers_factory.py:38-39
+
+
+@pytest.mark.parametrize('cfg,kw', [('default', dict(precision='bf16x3')), ('default', dict(precision='fp32')),
+                                    ('simgnn', dict(final_act='sigmoid'))])
+def test_rank_host_compact_equals_rank_host(cfg, kw):
+    """The compact wire format (sgnn_compact_batch, expanded on the device) must give the same bits as the
+    plain host entry point: the expansion reproduces the CSR arrays exactly."""
+    eng, layers, flat, gs, enc, batch = _setup(cfg, 700, **kw)
+    from graphembedding_b200.graphs import pack_nx_graphs
+    m, n, k = 150, 550, 10
+    q, db = pack_nx_graphs(gs[:m], enc), pack_nx_graphs(gs[m:], enc)
+    eng.reserve(max_graphs=len(gs), max_nodes=batch.total_nodes, max_nnz=batch.nnz, max_queries=m, max_db=n)
+    sim_a, sim_b = np.empty((m, n), np.float32), np.empty((m, n), np.float32)
+    ids_a, vals_a = eng.rank_host(q.pin(), db.pin(), k, sim=sim_a)
+    qc, dbc = q.compact(), db.compact()
+    assert qc is not None and dbc is not None and qc.is_pinned()
+    for _ in range(4):      # eager, capture, replay, replay
+        sim_b[:] = 0
+        ids_b, vals_b = eng.rank_host_compact(qc, dbc, k, sim=sim_b)
+        assert np.array_equal(ids_a, ids_b) and np.array_equal(vals_a, vals_b) and np.array_equal(sim_a, sim_b)

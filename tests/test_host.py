@@ -244,3 +244,42 @@ def test_feed_construction_draws_like_the_reference(name):
             assert [order[i] for i in feed.g2] == [c[2] for c in calls[:B]]
             assert feed.dists.ravel().tolist() == dd
             assert feed.norm_dists.ravel().tolist() == nd
+
+
+@pytest.mark.parametrize('n_hi,num', [(10, 300), (30, 64), (200, 6)])
+def test_compact_wire_format_round_trip_is_bit_exact(n_hi, num):
+    """sgnn_compact_batch -> sgnn_expand_compact_host (the host restatement of the device expansion kernel)
+    must reproduce the five arrays of the batch bit for bit; the blob is ~3.5x smaller for AIDS-sized graphs."""
+    from graphembedding_b200.native import PackedBatch
+    from util import corpus, encoder_for
+    from graphembedding_b200.graphs import pack_nx_graphs
+    gs = corpus(num, 2, n_hi, seed=17)
+    b = pack_nx_graphs(gs, encoder_for(gs))
+    blob = b.compact(pinned=False)
+    assert blob is not None and blob.numel() % 16 == 0
+    back = PackedBatch.from_compact(blob)
+    for f in PackedBatch.FIELDS:
+        x, y = np.asarray(getattr(b, f)), np.asarray(getattr(back, f))
+        assert x.dtype == y.dtype and x.shape == y.shape, f
+        assert x.tobytes() == y.tobytes(), f
+    assert (back.n_graphs, back.total_nodes, back.nnz, back.max_nodes) == (b.n_graphs, b.total_nodes, b.nnz, b.max_nodes)
+    if n_hi == 10:
+        assert blob.numel() < b.nbytes() / 3
+
+
+def test_compact_wire_format_rejects_what_does_not_fit_a_byte():
+    from graphembedding_b200.native import PackedBatch
+    # a 300-node path graph: node indices exceed the byte-wide column field
+    n = 300
+    b = PackedBatch.from_lists([np.zeros(n, np.int32)], [np.array([[i, i + 1] for i in range(n - 1)], np.int32)])
+    assert b.compact(pinned=False) is None
+    # label 256 does not fit either
+    b = PackedBatch.from_lists([np.array([0, 256], np.int32)], [np.array([[0, 1]], np.int32)])
+    assert b.compact(pinned=False) is None
+    # empty batch and single isolated node are fine
+    e = PackedBatch.from_lists([], [])
+    blob = e.compact(pinned=False)
+    assert blob is not None and PackedBatch.from_compact(blob).n_graphs == 0
+    one = PackedBatch.from_lists([np.array([3], np.int32)], [np.zeros((0, 2), np.int32)])
+    back = PackedBatch.from_compact(one.compact(pinned=False))
+    assert back.val.tolist() == [1.0] and back.labels.tolist() == [3] and back.rowptr.tolist() == [0, 1]

@@ -428,6 +428,7 @@ def run_cuda(args):
 
     train = run_train(torch, dist, dev, rank, world, local, args, barrier, max_over_ranks)
     simgnn = run_simgnn(torch, dist, dev, rank, world, local, args, barrier, max_over_ranks, qd, dbd, flush)
+    web = run_web(torch, dev, rank, world, local, args, barrier, max_over_ranks, flush)
 
     if world > 1:
         if peer is not None:
@@ -441,13 +442,67 @@ def run_cuda(args):
             'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
             'dtype': 'f32' if args.precision == 'fp32' else args.precision, 'data': 'synthetic',
             'config': dict(workload_config(), exchange=exchange), 'clocks': clk, 'e2e': e2e,
-            'gpu_launches': launches, 'roofline': roofline, 'train': train, 'simgnn': simgnn}
+            'gpu_launches': launches, 'roofline': roofline, 'train': train, 'simgnn': simgnn, 'web': web}
     if world == 1 and not args.no_cpu_baseline:
         v, cores, sample = cpu_rank_baseline(DEFAULT_LAYERS, q, db)
         line['cpu_baseline'] = {'value': v, 'unit': 'pairs/s', 'cores': cores, 'kind': 'port', 'sample': sample,
                                 'per_pair_reference_structure_pairs_per_s': cpu_per_pair_rate(DEFAULT_LAYERS, q, db)}
     sys.stdout.flush()
     os.write(json_fd, (json.dumps(line) + '\n').encode())
+
+
+def run_web(torch, dev, rank, world, local, args, barrier, max_over_ranks, flush):
+    """BASELINE configs[4]: Web-shaped larger graphs (N ~ U[100, 500], E ~ 2N, 32 labels) stressing the CSR
+    gather (large-graph embedding kernel, node rows in a global workspace) and the node-node similarity
+    histogram.  One step = embed WEB_GRAPHS graphs (pooled embeddings + node rows), NTN-score WEB_PAIRS listed
+    pairs and build their 16-bin histograms."""
+    from graphembedding_b200 import data as D
+    from graphembedding_b200.engine import SgnnEngine
+    from graphembedding_b200.graphs import NodeFeatureOneHotEncoder, pack_nx_graphs
+    from graphembedding_b200.layers_factory import parse_layers
+    WEB_GRAPHS, WEB_PAIRS = 256, 4096
+    W = type('WebBench', (D.WebData,), {'num_train': WEB_GRAPHS})
+    gs = W(True).graphs
+    enc = NodeFeatureOneHotEncoder(gs, 'type', feat_idx_dic={l: i for i, l in enumerate(D.WebData.labels)})
+    batch = pack_nx_graphs(gs, enc)
+    eng = SgnnEngine(parse_layers(TRAIN_LAYERS, 32), 32, device=local)
+    eng.init_params(123)
+    eng.reserve(max_graphs=WEB_GRAPHS, max_nodes=batch.total_nodes, max_nnz=batch.nnz, max_pairs=WEB_PAIRS)
+    bd = batch.to(dev)
+    rng = np.random.default_rng(7 + rank)
+    g1 = torch.as_tensor(rng.integers(0, WEB_GRAPHS, WEB_PAIRS).astype(np.int32), device=dev)
+    g2 = torch.as_tensor(rng.integers(0, WEB_GRAPHS, WEB_PAIRS).astype(np.int32), device=dev)
+    out = {}
+
+    def step():
+        emb, rows = eng.embed_nodes(bd)
+        out['raw'], out['sim'] = eng.score_pairs(emb, g1, g2)
+        out['hist'], _ = eng.pair_histogram(rows, bd.node_off, g1, g2, bins=16)
+
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    barrier()
+    ms = max_over_ranks(timed_steps(torch, step, args.steps, flush)) / args.steps
+    e_ms = timed_steps(torch, lambda: eng.embed_nodes(bd), args.steps, flush) / args.steps
+    emb, rows = eng.embed_nodes(bd)
+    h_ms = timed_steps(torch, lambda: eng.pair_histogram(rows, bd.node_off, g1, g2, bins=16), args.steps, flush) / args.steps
+    no = batch.node_off
+    n1 = np.diff(no)[g1.cpu().numpy()].astype(np.float64)
+    n2 = np.diff(no)[g2.cpu().numpy()].astype(np.float64)
+    cells = float((n1 * n2).sum())
+    peak, _ = peaks()
+    gather_bytes = float(batch.algorithmic_bytes() + 4 * batch.total_nodes * 16 + 4 * WEB_GRAPHS * 16)
+    return {'workload': 'BASELINE configs[4]: {} Web-shaped graphs (N~U[100,500], mean {:.0f} nodes, {} non-zeros), '
+                        'GCN32-GCN16-Average-NTN(16,10) + 16-bin node-node histogram on {} listed pairs per GPU'
+                        .format(WEB_GRAPHS, batch.total_nodes / WEB_GRAPHS, batch.nnz, WEB_PAIRS),
+            'value': WEB_PAIRS * world / (ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': ms,
+            'graphs_per_s': WEB_GRAPHS * world / (ms * 1e-3),
+            'stage_ms': {'embed_large_with_node_rows': e_ms, 'pair_histogram': h_ms},
+            'embed_gather': {'algorithmic_bytes': gather_bytes, 'achieved_GBps': gather_bytes / (e_ms * 1e-3) / 1e9,
+                             'hbm_peak_GBps': peak},
+            'histogram': {'node_node_cells': cells, 'cells_per_s': cells / (h_ms * 1e-3),
+                          'gflops_fp32': 2.0 * 16 * cells / (h_ms * 1e-3) / 1e9}}
 
 
 def run_simgnn(torch, dist, dev, rank, world, local, args, barrier, max_over_ranks, qd, dbd, flush):

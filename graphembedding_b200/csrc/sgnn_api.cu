@@ -794,8 +794,13 @@ int sgnn_pair_histogram(SgnnHandle h, const float* node_emb_dev, const int32_t* 
   if (!h || !node_emb_dev || !node_off_dev || !g1_dev || !g2_dev) return fail(h, "sgnn_pair_histogram: null argument");
   if (bins < 1 || bins > 32) return fail(h, "sgnn_pair_histogram: bins must be in [1, 32]");
   if (n_pairs == 0) return 0;
-  const cudaError_t e = sgnn_launch_pair_histogram(node_emb_dev, h->M.node_dim, node_off_dev, g1_dev, g2_dev, n_pairs,
+  cudaError_t e = sgnn_launch_pair_histogram_tiled(node_emb_dev, h->M.node_dim, node_off_dev, g1_dev, g2_dev, n_pairs,
                                                    bins, hist_dev, counts_dev, h->sm_count, (cudaStream_t)stream);
+  if (e == cudaErrorInvalidValue) {   // node_dim > 32: generic cell-per-lane kernel
+    cudaGetLastError();
+    e = sgnn_launch_pair_histogram(node_emb_dev, h->M.node_dim, node_off_dev, g1_dev, g2_dev, n_pairs, bins, hist_dev,
+                                   counts_dev, h->sm_count, (cudaStream_t)stream);
+  }
   if (e != cudaSuccess) return fail(h, std::string("sgnn_pair_histogram: ") + cudaGetErrorString(e));
   return 0;
 }

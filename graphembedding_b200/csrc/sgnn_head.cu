@@ -75,16 +75,23 @@ struct BinCounters {
     const unsigned long long v = (b & 1) ? od[b >> 4] : ev[b >> 4];
     return (int)((v >> (((b & 15) >> 1) * 8)) & 0xFFull);
   }
-  __device__ __forceinline__ void spill(int* col, int T, int bins) {
+  // f(b, count) for every bin b < bins, then the byte fields are cleared
+  template <typename F>
+  __device__ __forceinline__ void drain(int bins, F f) {
     for (int b = 0; b < bins; ++b) {
       int v = 0;
 #pragma unroll
       for (int c = 0; c < NB; ++c) if (c == b) v = byte_of(c);
-      col[b * T] = (spilled ? col[b * T] : 0) + v;
+      f(b, v);
     }
 #pragma unroll
     for (int w = 0; w < W; ++w) ev[w] = od[w] = 0ull;
-    since_byte = 0; spilled = true;
+    since_byte = 0;
+  }
+  __device__ __forceinline__ void spill(int* col, int T, int bins) {
+    const bool first = !spilled;
+    drain(bins, [&](int b, int v) { col[b * T] = (first ? 0 : col[b * T]) + v; });
+    spilled = true;
   }
   // after every group of up to 4 cells
   __device__ __forceinline__ void tick(int* col, int T, int bins) {
@@ -92,6 +99,15 @@ struct BinCounters {
     if (since_nib > 11) {
       fold();
       if (since_byte > 240) spill(col, T, bins);
+    }
+  }
+  // same, draining into f when the byte fields fill up
+  template <typename F>
+  __device__ __forceinline__ void tick_drain(int bins, F f) {
+    since_nib += 4;
+    if (since_nib > 11) {
+      fold();
+      if (since_byte > 240) drain(bins, f);
     }
   }
 };
@@ -313,6 +329,109 @@ allpairs_head_kernel(const __grid_constant__ ModelDev M, const __grid_constant__
       sim[(size_t)(q0 + qi) * ld + g] = sgnn_act(acc[0], M.final_act, M.yeta);
     }
   }
+}
+
+// Pairwise node-node similarity histogram of LISTED pairs for graphs of any size (Web-shaped: 100..500 nodes,
+// ~10^5 cells per pair).  CTA per pair; the second graph's node rows are staged in shared memory in tiles of up to
+// 512 (d <= 16) or 256 rows; a work unit = two rows of the first graph (registers) x a chunk of 32 staged rows, processed as
+// 2 x 2 blocks of cells (four independent chains); consecutive lanes take consecutive row pairs of the SAME chunk,
+// so the staged rows are warp-uniform broadcasts.  Bins are counted in registers (BinCounters) and drained into
+// CTA-wide shared counters.  Same cell arithmetic as the other two binning kernels.
+constexpr int HIST_TILE_FLOATS = 8192;   // staged rows: 512 at ND = 16, 256 at ND = 32 (32 KB static)
+constexpr int HIST_THREADS = 256;
+
+template <int ND, int NB>
+__global__ void __launch_bounds__(HIST_THREADS)
+pair_histogram_tiled_kernel(const float* __restrict__ node_emb, int d, const int32_t* __restrict__ node_off,
+                            const int32_t* __restrict__ g1, const int32_t* __restrict__ g2, int n_pairs, int bins,
+                            float* __restrict__ hist, int32_t* __restrict__ counts) {
+  constexpr int HIST_TJ = HIST_TILE_FLOATS / ND;
+  __shared__ __align__(16) float s_h2[(HIST_TJ + 1) * ND];
+  __shared__ int s_cnt[32];
+  const int tid = threadIdx.x;
+  const float fb = (float)bins;
+  const int bmax = bins - 1;
+  for (int p = blockIdx.x; p < n_pairs; p += gridDim.x) {
+    const int a0 = node_off[g1[p]], n1 = node_off[g1[p] + 1] - a0;
+    const int b0 = node_off[g2[p]], n2 = node_off[g2[p] + 1] - b0;
+    if (tid < 32) s_cnt[tid] = 0;
+    BinCounters<NB> bc;
+    bc.reset();
+    auto to_cta = [&](int b, int v) { if (v) atomicAdd(&s_cnt[b], v); };
+    const int nip = (n1 + 1) >> 1;
+    for (int j0 = 0; j0 < n2; j0 += HIST_TJ) {
+      const int tj = min(HIST_TJ, n2 - j0);
+      __syncthreads();
+      for (int idx = tid; idx < (tj + 1) * ND; idx += HIST_THREADS) {   // one zero row behind the tile (odd counts)
+        const int r = idx / ND, c = idx - r * ND;
+        s_h2[idx] = (r < tj && c < d) ? node_emb[(size_t)(b0 + j0 + r) * d + c] : 0.f;
+      }
+      __syncthreads();
+      const int nchunks = (tj + 31) >> 5;
+      for (int u = tid; u < nip * nchunks; u += HIST_THREADS) {
+        const int jc = u / nip, ip = u - jc * nip;
+        const int i = 2 * ip;
+        const bool vi = i + 1 < n1;
+        float ha[ND], hb[ND];
+#pragma unroll
+        for (int c = 0; c < ND; ++c) {
+          ha[c] = c < d ? node_emb[(size_t)(a0 + i) * d + c] : 0.f;
+          hb[c] = (vi && c < d) ? node_emb[(size_t)(a0 + i + 1) * d + c] : 0.f;
+        }
+        const int jend = min(tj, (jc + 1) << 5);
+        for (int j = jc << 5; j < jend; j += 2) {
+          const float4* qa = reinterpret_cast<const float4*>(s_h2 + j * ND);
+          const float4* qb = reinterpret_cast<const float4*>(s_h2 + (j + 1) * ND);
+          float s00 = 0.f, s01 = 0.f, s10 = 0.f, s11 = 0.f;   // s[i-row][j-row]
+#pragma unroll
+          for (int c = 0; c < ND / 4; ++c) {
+            const float4 x = qa[c], y = qb[c];
+            s00 = fmaf(ha[4 * c], x.x, s00); s01 = fmaf(ha[4 * c], y.x, s01);
+            s10 = fmaf(hb[4 * c], x.x, s10); s11 = fmaf(hb[4 * c], y.x, s11);
+            s00 = fmaf(ha[4 * c + 1], x.y, s00); s01 = fmaf(ha[4 * c + 1], y.y, s01);
+            s10 = fmaf(hb[4 * c + 1], x.y, s10); s11 = fmaf(hb[4 * c + 1], y.y, s11);
+            s00 = fmaf(ha[4 * c + 2], x.z, s00); s01 = fmaf(ha[4 * c + 2], y.z, s01);
+            s10 = fmaf(hb[4 * c + 2], x.z, s10); s11 = fmaf(hb[4 * c + 2], y.z, s11);
+            s00 = fmaf(ha[4 * c + 3], x.w, s00); s01 = fmaf(ha[4 * c + 3], y.w, s01);
+            s10 = fmaf(hb[4 * c + 3], x.w, s10); s11 = fmaf(hb[4 * c + 3], y.w, s11);
+          }
+          const bool vj = j + 1 < jend;
+          bc.add(min(bmax, (int)floorf(sgnn_hist_sigmoid(s00) * fb)), true);
+          bc.add(min(bmax, (int)floorf(sgnn_hist_sigmoid(s01) * fb)), vj);
+          bc.add(min(bmax, (int)floorf(sgnn_hist_sigmoid(s10) * fb)), vi);
+          bc.add(min(bmax, (int)floorf(sgnn_hist_sigmoid(s11) * fb)), vi && vj);
+          bc.tick_drain(bins, to_cta);
+        }
+      }
+    }
+    bc.fold();
+    bc.drain(bins, to_cta);
+    __syncthreads();
+    if (tid < bins) {
+      const int cells = n1 * n2;
+      const int tot = s_cnt[tid];
+      if (counts) counts[(size_t)p * bins + tid] = tot;
+      if (hist) hist[(size_t)p * bins + tid] = cells > 0 ? (float)tot * (1.f / (float)cells) : 0.f;
+    }
+    __syncthreads();
+  }
+}
+
+// returns cudaErrorInvalidValue when d > 32 (the caller keeps the generic kernel)
+cudaError_t sgnn_launch_pair_histogram_tiled(const float* node_emb, int d, const int32_t* node_off, const int32_t* g1,
+                                             const int32_t* g2, int n_pairs, int bins, float* hist, int32_t* counts,
+                                             int sm_count, cudaStream_t st) {
+  if (d > 32 || bins > 32) return cudaErrorInvalidValue;
+  const int blocks = std::min(n_pairs, sm_count * 8);
+  if (d <= 16 && bins <= 16)
+    pair_histogram_tiled_kernel<16, 16><<<blocks, HIST_THREADS, 0, st>>>(node_emb, d, node_off, g1, g2, n_pairs, bins, hist, counts);
+  else if (d <= 16)
+    pair_histogram_tiled_kernel<16, 32><<<blocks, HIST_THREADS, 0, st>>>(node_emb, d, node_off, g1, g2, n_pairs, bins, hist, counts);
+  else if (bins <= 16)
+    pair_histogram_tiled_kernel<32, 16><<<blocks, HIST_THREADS, 0, st>>>(node_emb, d, node_off, g1, g2, n_pairs, bins, hist, counts);
+  else
+    pair_histogram_tiled_kernel<32, 32><<<blocks, HIST_THREADS, 0, st>>>(node_emb, d, node_off, g1, g2, n_pairs, bins, hist, counts);
+  return cudaGetLastError();
 }
 
 template <int DEP, int H0, int ND, int NB>

@@ -53,3 +53,7 @@ cudaError_t sgnn_launch_allpairs_head(const ModelDev& M, int DEP, const float* p
                                       int max_nodes_q, const float* nodes_db, const int32_t* node_off_db,
                                       int max_nodes_db, int m, int n, float* sim, int64_t ld, int sm_count,
                                       int smem_optin, cudaStream_t st);
+// register-blocked histogram of listed pairs (sgnn_head.cu); cudaErrorInvalidValue when node_dim > 32
+cudaError_t sgnn_launch_pair_histogram_tiled(const float* node_emb, int d, const int32_t* node_off, const int32_t* g1,
+                                             const int32_t* g2, int n_pairs, int bins, float* hist, int32_t* counts,
+                                             int sm_count, cudaStream_t st);

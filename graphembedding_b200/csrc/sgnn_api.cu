@@ -907,7 +907,7 @@ static int launch_pairs(SgnnHandle h, bool bwd, const SgnnGraphBatch* b, const i
   if (h->use_team) {
     const int nmax = std::max(4, (int)b->max_nodes);
     const size_t smem = team_smem_floats(h->M, nmax) * sizeof(float);
-    const int per_sm = std::max<size_t>(1, std::min<size_t>(2, (size_t)h->smem_optin / (smem + 1024)));
+    const int per_sm = std::max<size_t>(1, std::min<size_t>(TEAM_CTA <= 256 ? 2 : 1, (size_t)h->smem_optin / (smem + 1024)));
     const int tblocks = std::min(n_pairs, h->sm_count * per_sm);
     if (bwd)
       train_team_kernel<true><<<tblocks, TEAM_CTA, smem, st>>>(h->M, to_dev(b), nmax, h->d_params, g1, g2, target_sim,

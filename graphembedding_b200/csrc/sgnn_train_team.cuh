@@ -2,11 +2,12 @@
 //
 // A mini-batch is 128 pairs per GPU (BASELINE configs[2]): with one warp per pair (sgnn_small.cuh,
 // the first version) the whole GPU runs 128 warps, each a 42 k-instruction dependent chain -- 166 us
-// per step at < 1 warp per SM.  Here a CTA of 256 threads owns one pair: the two arms (graphs) of the
-// pair run on two 128-thread TEAMS synchronised by named barriers (bar.sync 1 / 2), every loop of the
+// per step at < 1 warp per SM.  Here a CTA of 2 x TEAM_THREADS threads owns one pair: the two arms (graphs) of the
+// pair run on two TEAMS (256 threads each: 128 -> 256 took the 128-pair step from 44 to 36 us, the SimGNN chain from
+// 100 to 74 us -- the kernel is latency-bound, not issue-bound) synchronised by named barriers (bar.sync 1 / 2), every loop of the
 // forward and backward pass is flattened over its independent outputs (node row x feature column,
 // weight row x column, ...) and strided over the team, and the pair layer (NTN / Dot) forward and
-// backward use all 256 threads.  Same math, same order of floating-point reductions inside one output
+// backward use all threads of the CTA.  Same math, same order of floating-point reductions inside one output
 // as the warp kernel; parameter gradients accumulate in a per-CTA shared buffer (shared-memory atomics:
 // the two teams update the same weights) and are flushed with one global atomic per parameter.
 // Reference math: model/Siamese/layers.py:91-118 (GCN), :136-140 (Average), :154-160 (Attention),
@@ -14,7 +15,10 @@
 #pragma once
 #include "sgnn_small.cuh"
 
-constexpr int TEAM_THREADS = 128;
+#ifndef SGNN_TEAM_THREADS
+#define SGNN_TEAM_THREADS 256
+#endif
+constexpr int TEAM_THREADS = SGNN_TEAM_THREADS;
 constexpr int TEAM_CTA = 2 * TEAM_THREADS;
 
 struct Team {
@@ -105,16 +109,27 @@ __device__ __forceinline__ void team_aggregate(const GraphS& G, const float* T, 
   }
 }
 
-// Out[i][j] = sum_k H[i][k] * W[k*dout + j] through epi(i, j, v), flattened over (i, j)
+// Out[i][j] = sum_k H[i][k] * W[k*dout + j] through epi(i, j, v), flattened over (i, j).  A thread carries TWO
+// outputs per pass (idx and idx + TEAM_THREADS): the k-chains are serial by definition (fixed summation order),
+// so the second chain is what fills the FMA latency.
 template <typename Epi>
 __device__ __forceinline__ void team_gemm(const float* H, int ldh, int n, int din, const float* W, int dout,
                                           const Team& tm, Epi epi) {
-  for (int idx = tm.tid; idx < n * dout; idx += TEAM_THREADS) {
+  const int total = n * dout;
+  for (int idx = tm.tid; idx < total; idx += 2 * TEAM_THREADS) {
+    const int idx2 = idx + TEAM_THREADS;
+    const bool two = idx2 < total;
     const int i = idx / dout, j = idx - i * dout;
+    const int i2 = two ? idx2 / dout : i, j2 = two ? idx2 - i2 * dout : j;
     const float* h = H + i * ldh;
-    float s = 0.f;
-    for (int k = 0; k < din; ++k) s = fmaf(h[k], W[k * dout + j], s);
+    const float* h2 = H + i2 * ldh;
+    float s = 0.f, s2 = 0.f;
+    for (int k = 0; k < din; ++k) {
+      s = fmaf(h[k], W[k * dout + j], s);
+      s2 = fmaf(h2[k], W[k * dout + j2], s2);
+    }
     epi(i, j, s);
+    if (two) epi(i2, j2, s2);
   }
 }
 
@@ -309,18 +324,33 @@ __device__ __forceinline__ void team_graph_bwd(const ModelDev& M, const GraphS& 
     } else {
       const float* Hin = acts + M.L[l - 1].out_off;
       const int din = L.din;
-      for (int idx = tm.tid; idx < din * dout; idx += TEAM_THREADS) {   // dW[k][j] = sum_i Hin[i][k] dXW[i][j]
+      // two outputs per thread and pass (see team_gemm): independent chains hide the FMA latency
+      for (int idx = tm.tid; idx < din * dout; idx += 2 * TEAM_THREADS) {   // dW[k][j] = sum_i Hin[i][k] dXW[i][j]
+        const int idx2 = idx + TEAM_THREADS;
+        const bool two = idx2 < din * dout;
         const int k = idx / dout, j = idx - k * dout;
-        float s = 0.f;
-        for (int i = 0; i < n; ++i) s = fmaf(Hin[i * ald + k], dXW[i * ld + j], s);
+        const int k2 = two ? idx2 / dout : k, j2 = two ? idx2 - k2 * dout : j;
+        float s = 0.f, s2 = 0.f;
+        for (int i = 0; i < n; ++i) {
+          s = fmaf(Hin[i * ald + k], dXW[i * ld + j], s);
+          s2 = fmaf(Hin[i * ald + k2], dXW[i * ld + j2], s2);
+        }
         atomicAdd(&s_g[L.w_off + idx], s);
+        if (two) atomicAdd(&s_g[L.w_off + idx2], s2);
       }
       const float* Wt = s_aux + L.wt_off;   // [dout][din]
-      for (int idx = tm.tid; idx < n * din; idx += TEAM_THREADS) {      // dHin[i][k] = sum_j dXW[i][j] W[k][j]
+      for (int idx = tm.tid; idx < n * din; idx += 2 * TEAM_THREADS) {      // dHin[i][k] = sum_j dXW[i][j] W[k][j]
+        const int idx2 = idx + TEAM_THREADS;
+        const bool two = idx2 < n * din;
         const int i = idx / din, k = idx - i * din;
-        float s = 0.f;
-        for (int j = 0; j < dout; ++j) s = fmaf(dXW[i * ld + j], Wt[j * din + k], s);
+        const int i2 = two ? idx2 / din : i, k2 = two ? idx2 - i2 * din : k;
+        float s = 0.f, s2 = 0.f;
+        for (int j = 0; j < dout; ++j) {
+          s = fmaf(dXW[i * ld + j], Wt[j * din + k], s);
+          s2 = fmaf(dXW[i2 * ld + j], Wt[j * din + k2], s2);
+        }
         Gnxt[i * ld + k] = s;
+        if (two) Gnxt[i2 * ld + k2] = s2;
       }
       float* sw = Gcur; Gcur = Gnxt; Gnxt = sw;
     }
@@ -423,7 +453,7 @@ __device__ __forceinline__ void team_head_bwd(const ModelDev& M, const float* W,
 }
 
 template <bool BWD>
-__global__ void __launch_bounds__(TEAM_CTA, 2)
+__global__ void __launch_bounds__(TEAM_CTA, TEAM_CTA <= 256 ? 2 : 1)
 train_team_kernel(const __grid_constant__ ModelDev M, const BatchDev B, int nmax, const float* __restrict__ params,
                   const int32_t* __restrict__ g1, const int32_t* __restrict__ g2,
                   const float* __restrict__ target_sim, int n_pairs, float inv_global_batch, float tsum, float tsqsum,
@@ -470,7 +500,7 @@ train_team_kernel(const __grid_constant__ ModelDev M, const BatchDev B, int nmax
     const GraphS G = team_load_graph(B, gid, arm + TL.csr, TL, tm);
     team_graph_fwd(M, G, s_w, arm, TL, tm, dropping != 0, dbase, slot);
     __syncthreads();
-    // ---- pair layer forward (layers.py:249-252, 282-310), all 256 threads ----
+    // ---- pair layer forward (layers.py:249-252, 282-310), all threads of the CTA ----
     if (M.pair_kind == SGNN_LAYER_DOT) {
       if (tid < 32) {
         float s = 0.f;

@@ -7,7 +7,9 @@ from graphembedding_b200 import distributed as DS
 from graphembedding_b200.engine import SgnnEngine
 from graphembedding_b200.layers_factory import parse_layers
 enc, batch, batches = bench.make_train_data(0, 1)
-eng = SgnnEngine(parse_layers(bench.TRAIN_LAYERS, 29), 29, loss_mode='paired', ntn_mode='reference')
+simgnn = os.environ.get('PROBE_LAYERS') == 'simgnn'
+eng = SgnnEngine(parse_layers(bench.SIMGNN_LAYERS if simgnn else bench.TRAIN_LAYERS, 29), 29, loss_mode='paired',
+                 ntn_mode='reference', final_act='sigmoid' if simgnn else 'sim_kernel')
 eng.init_params(123)
 dev = eng.device
 bd = batch.to(dev)

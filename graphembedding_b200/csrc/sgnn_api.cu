@@ -839,6 +839,15 @@ int sgnn_score_all_pairs(SgnnHandle h, const float* emb_q, int32_t m, const floa
   return score_all_pairs_stages(h, emb_q, m, emb_db, n, sim_dev, ld, (cudaStream_t)stream, SCORE_ALL);
 }
 
+int sgnn_score_all_pairs_stages(SgnnHandle h, const float* emb_q, int32_t m, const float* emb_db, int32_t n,
+                                float* sim_dev, int64_t ld, int32_t stages, void* stream) {
+  if (!h || !emb_q || !emb_db || !sim_dev) return fail(h, "sgnn_score_all_pairs_stages: null argument");
+  if (stages < 1 || stages > SGNN_STAGE_ALL) return fail(h, "sgnn_score_all_pairs_stages: bad stage mask");
+  static_assert(SGNN_STAGE_PREP_QUERIES == SCORE_PREP_Q && SGNN_STAGE_PREP_DATABASE == SCORE_PREP_DB &&
+                SGNN_STAGE_SCORE == SCORE_MAIN, "stage flags");
+  return score_all_pairs_stages(h, emb_q, m, emb_db, n, sim_dev, ld, (cudaStream_t)stream, stages);
+}
+
 int sgnn_score_all_pairs_nodes(SgnnHandle h, const float* emb_q, const float* nodes_q, const int32_t* node_off_q,
                                int32_t max_nodes_q, int32_t m, const float* emb_db, const float* nodes_db,
                                const int32_t* node_off_db, int32_t max_nodes_db, int32_t n, float* sim_dev, int64_t ld,

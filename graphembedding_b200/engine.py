@@ -175,6 +175,16 @@ class SgnnEngine(object):
         self.launches += 2 if self.precision == 'fp32' else 3   # operand prep (query / database side) + scorer
         return out
 
+    STAGE_PREP_QUERIES, STAGE_PREP_DATABASE, STAGE_SCORE = 1, 2, 4
+
+    def score_all_pairs_stages(self, emb_q, emb_db, out, stages, stream=None):
+        """Selected stages of score_all_pairs (sgnn_score_all_pairs_stages)."""
+        m, n = emb_q.shape[0], emb_db.shape[0]
+        check(self.h, lib().sgnn_score_all_pairs_stages(self.h, _ptr(emb_q), m, _ptr(emb_db), n, _ptr(out),
+                                                        out.stride(0), int(stages), _stream_ptr(stream)))
+        self.launches += bin(int(stages)).count('1') if self.precision != 'fp32' else bin(int(stages) & 5).count('1')
+        return out
+
     def topk(self, sim, k, stream=None):
         import torch
         m, n = sim.shape

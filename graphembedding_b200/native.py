@@ -74,6 +74,7 @@ SIGNATURES = {
     'sgnn_score_pairs': (C.c_int, [_P, _P, _P, _P, _I32, _P, _P, _P]),
     'sgnn_forward_pairs': (C.c_int, [_P, _BP, _P, _P, _I32, _P, _P, _P, _P]),
     'sgnn_score_all_pairs': (C.c_int, [_P, _P, _I32, _P, _I32, _P, _I64, _P]),
+    'sgnn_score_all_pairs_stages': (C.c_int, [_P, _P, _I32, _P, _I32, _P, _I64, _I32, _P]),
     'sgnn_topk': (C.c_int, [_P, _P, _I32, _I32, _I64, _I32, _P, _P, _P]),
     'sgnn_topk_merge': (C.c_int, [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P]),
     'sgnn_sort_rows': (C.c_int, [_P, _P, _I32, _I32, _I64, _P, _P]),

@@ -176,6 +176,13 @@ int sgnn_forward_pairs(SgnnHandle h, const SgnnGraphBatch* batch_dev, const int3
  * (query i, database j). */
 int sgnn_score_all_pairs(SgnnHandle h, const float* emb_q_dev, int32_t m, const float* emb_db_dev,
                          int32_t n, float* sim_dev, int64_t ld, void* stream);
+/* sgnn_score_all_pairs in separately callable stages (bit flags, any combination, in this order): the query-side
+ * operand / tables, the database-side operand, the scorer proper.  Lets a caller prepare the query side while the
+ * database is still being uploaded or embedded (what sgnn_rank_host / sgnn_rank_device do internally), and lets
+ * bench.py time the scorer kernel alone.  SGNN_STAGE_ALL == sgnn_score_all_pairs. */
+enum { SGNN_STAGE_PREP_QUERIES = 1, SGNN_STAGE_PREP_DATABASE = 2, SGNN_STAGE_SCORE = 4, SGNN_STAGE_ALL = 7 };
+int sgnn_score_all_pairs_stages(SgnnHandle h, const float* emb_q_dev, int32_t m, const float* emb_db_dev, int32_t n,
+                                float* sim_dev, int64_t ld, int32_t stages, void* stream);
 /* sgnn_score_all_pairs for models with a Histogram head (SGNN_LAYER_HISTOGRAM): the histogram needs the last
  * node-level rows of both sides (sgnn_embed_graphs_nodes / sgnn_node_embeddings) next to the pooled embeddings.
  * node_off_* [graphs + 1] index rows of nodes_* [total_nodes][sgnn_node_dim]; max_nodes_* = largest graph. */

@@ -470,3 +470,25 @@ def test_hinted_topk_in_rank_device_matches_plain_topk(kind):
     # and the host entry point
     ids_h, vals_h = eng.rank_host(q, db, 10)
     assert np.array_equal(ids_h, eng.topk(sim, 10)[0].cpu().numpy())
+
+
+@pytest.mark.parametrize('precision', ['fp32', 'bf16x3'])
+def test_score_all_pairs_stages_compose_to_the_single_call(precision):
+    """sgnn_score_all_pairs_stages: query-side prep, database-side prep and the scorer issued separately (in
+    any grouping) must give the bits of sgnn_score_all_pairs."""
+    eng, layers, flat, gs, enc, batch = _setup('default', 300, precision=precision)
+    emb = eng.embed(batch.to(eng.device))
+    eq, ed = emb[:40].contiguous(), emb[40:].contiguous()
+    eng.reserve(max_queries=40, max_db=260)
+    ref = eng.score_all_pairs(eq, ed)
+    out = torch.zeros_like(ref)
+    eng.score_all_pairs_stages(eq, ed, out, eng.STAGE_PREP_QUERIES)
+    eng.score_all_pairs_stages(eq, ed, out, eng.STAGE_PREP_DATABASE)
+    eng.score_all_pairs_stages(eq, ed, out, eng.STAGE_SCORE)
+    assert torch.equal(out, ref)
+    out.zero_()
+    eng.score_all_pairs_stages(eq, ed, out, eng.STAGE_PREP_QUERIES | eng.STAGE_PREP_DATABASE)
+    eng.score_all_pairs_stages(eq, ed, out, eng.STAGE_SCORE)
+    assert torch.equal(out, ref)
+    with pytest.raises(RuntimeError):
+        eng.score_all_pairs_stages(eq, ed, out, 8)

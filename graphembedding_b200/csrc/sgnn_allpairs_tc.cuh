@@ -24,11 +24,6 @@
 #include "sgnn_tc.cuh"
 #include "sgnn_tc_geom.h"
 
-__device__ __forceinline__ void split_bf16(float x, __nv_bfloat16& hi, __nv_bfloat16& lo) {
-  hi = __float2bfloat16_rn(x);
-  lo = __float2bfloat16_rn(x - __bfloat162float(hi));
-}
-
 // Operand preparation, ONE launch: blocks [0, q_blocks) build the B tiles (queries), the rest the A
 // tiles (database graphs).
 //
@@ -43,16 +38,6 @@ __device__ __forceinline__ void split_bf16(float x, __nv_bfloat16& hi, __nv_bflo
 // A: one thread per (database graph, K chunk).
 constexpr int PREP_COLS = 256;   // = block size
 constexpr int PREP_Q = 8;
-
-__device__ __forceinline__ float tc_prep_coef(const ModelDev& M, const float* __restrict__ params, int D, int K, int a,
-                                              int kk, int k) {   // a == D: the constant term
-  if (M.pair_kind == SGNN_LAYER_DOT) return (a < D && a == kk) ? 1.f : 0.f;
-  const float* W = params + M.w_off;
-  const float* V = params + M.v_off;
-  if (kk < D) return a < D ? W[a * D * K + kk * K + k] : V[k * 2 * D + D + kk];
-  if (kk == D) return a < D ? V[k * 2 * D + a] : (M.pair_bias ? params[M.b_off + k] : 0.f);
-  return 0.f;
-}
 
 __global__ void __launch_bounds__(PREP_COLS)
 tc_prep_kernel(const __grid_constant__ ModelDev M, const TcGeom G, int q_blocks, int col_blocks,
@@ -131,6 +116,79 @@ tc_prep_kernel(const __grid_constant__ ModelDev M, const TcGeom G, int q_blocks,
   for (int qq = 0; qq < PREP_Q; ++qq) {
     const int q = q0 + qq;
     if (q < G.m) {
+      const int qb = q / G.QH, row = (q - qb * G.QH) * KC + k;
+      __nv_bfloat16* dst = B + ((size_t)(qb * G.parts) * G.KCH + (kk >> 3)) * (TC_NPAD * 8) + (size_t)row * 8 + (kk & 7);
+      __nv_bfloat16 hi, lo;
+      split_bf16(acc[qq], hi, lo);
+      *dst = hi;
+      if (G.parts == 2) dst[lo_off] = lo;
+    }
+  }
+}
+
+// Query-side operand in two small kernels without shared memory, sized to run BESIDE the database embedding
+// (whose two resident CTAs leave 4 K registers and ~3 KB of shared memory per SM): on the high-priority side
+// stream of the ranking step they start at once instead of waiting for that kernel to drain.  (The staged
+// tc_prep_kernel above needs 8 K registers + 11.6 KB per CTA and was serialised behind it: 10 us on the critical
+// path of a 70 us step.)
+//   tc_coef_kernel:   Wm[a][c], the (D + 1) x C coefficient matrix of the columns c = (kk, k) of P' / C --
+//                     depends on the parameters only, so it does not wait for the query embeddings;
+//   tc_prep_q_kernel: out[q][c] = Wm[D][c] + sum_a x_q[a] Wm[a][c], thread = one column for PREPQ_Q queries,
+//                     coalesced coefficient loads, warp-uniform embedding loads.
+// Same arithmetic and summation order as tc_prep_kernel's query branch => identical operand bits.
+constexpr int PREPQ_THREADS = 64;
+constexpr int PREPQ_Q = 8;
+
+__global__ void __launch_bounds__(PREPQ_THREADS)
+tc_coef_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const float* __restrict__ params,
+               float* __restrict__ Wm) {
+  const int D = G.D, K = G.K, KC = G.KC;
+  const int C = G.KCH * 8 * KC;
+  const int idx = blockIdx.x * PREPQ_THREADS + threadIdx.x;
+  if (idx >= (D + 1) * C) return;
+  const int a = idx / C, c = idx - a * C;
+  const int kk = c / KC, k = c - kk * KC;
+  float v;
+  if (k < K) {
+    v = tc_prep_coef(M, params, D, K, a, kk, k);
+  } else {   // KC == K + 1: the column sum_k w_k (.) of the |x| form of relu
+    const bool ref = M.pair_kind == SGNN_LAYER_DOT || M.ntn_mode == SGNN_NTN_REFERENCE;
+    v = 0.f;
+#pragma unroll 4
+    for (int kq = 0; kq < K; ++kq)
+      v = fmaf(ref ? 1.f : params[M.u_off + kq], tc_prep_coef(M, params, D, K, a, kk, kq), v);
+  }
+  Wm[idx] = v;
+}
+
+__global__ void __launch_bounds__(PREPQ_THREADS, 16)
+tc_prep_q_kernel(const TcGeom G, const float* __restrict__ Wm, const float* __restrict__ emb_q,
+                 __nv_bfloat16* __restrict__ B) {
+  const int D = G.D, KC = G.KC;
+  const int C = G.KCH * 8 * KC;
+  const int c = blockIdx.x * PREPQ_THREADS + threadIdx.x;
+  if (c >= C) return;
+  const int kk = c / KC, k = c - kk * KC;
+  const int q0 = blockIdx.y * PREPQ_Q;
+  float acc[PREPQ_Q];
+  const float cst = Wm[(size_t)D * C + c];
+#pragma unroll
+  for (int qq = 0; qq < PREPQ_Q; ++qq) acc[qq] = cst;
+  const int nq = min(PREPQ_Q, G.m - q0);
+#pragma unroll 4
+  for (int a = 0; a < D; ++a) {
+    const float w = Wm[(size_t)a * C + c];
+#pragma unroll
+    for (int qq = 0; qq < PREPQ_Q; ++qq) {
+      const float x = qq < nq ? __ldg(emb_q + (size_t)(q0 + qq) * D + a) : 0.f;
+      acc[qq] = fmaf(x, w, acc[qq]);
+    }
+  }
+  const size_t lo_off = (size_t)G.KCH * TC_NPAD * 8;
+#pragma unroll
+  for (int qq = 0; qq < PREPQ_Q; ++qq) {
+    const int q = q0 + qq;
+    if (qq < nq) {
       const int qb = q / G.QH, row = (q - qb * G.QH) * KC + k;
       __nv_bfloat16* dst = B + ((size_t)(qb * G.parts) * G.KCH + (kk >> 3)) * (TC_NPAD * 8) + (size_t)row * 8 + (kk & 7);
       __nv_bfloat16 hi, lo;

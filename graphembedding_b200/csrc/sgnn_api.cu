@@ -88,6 +88,7 @@ struct SgnnHandle_t {
   float* d_hnodes[2] = {nullptr, nullptr};
   int64_t cap_hnodes = 0;                         // in node rows, each side
   struct NodeSide { const float* rows; const int32_t* node_off; int max_nodes; } hside[2] = {};
+  float* d_coef = nullptr;               // tensor-core scorer: query-side coefficient matrix (tc_coef_kernel)
   float *d_P = nullptr, *d_C = nullptr;  // all-pairs query tables
   int64_t cap_P = 0;
   __nv_bfloat16 *d_Atc = nullptr, *d_Btc = nullptr;  // tensor-core operands in UMMA tile order
@@ -318,7 +319,10 @@ int ensure_query_tables(SgnnHandle h, int64_t m) {
 // Stages of sgnn_score_all_pairs: the query-side tables, the database-side operand, the scorer.
 // sgnn_rank_device / sgnn_rank_host issue them separately so that the query side overlaps the
 // database upload / embedding.
-enum { SCORE_PREP_Q = 1, SCORE_PREP_DB = 2, SCORE_MAIN = 4, SCORE_ALL = 7 };
+enum { SCORE_PREP_Q = 1, SCORE_PREP_DB = 2, SCORE_MAIN = 4, SCORE_ALL = 7,
+       // internal refinements of SCORE_PREP_Q for the tensor-core scorer: the coefficient matrix depends on the
+       // parameters only, so the ranking entry points compute it before / beside the query embedding
+       SCORE_COEF_ONLY = 8, SCORE_COEF_READY = 16 };
 
 // tcgen05 path of sgnn_score_all_pairs (SGNN_PREC_BF16X3 / SGNN_PREC_BF16)
 int score_all_pairs_tc(SgnnHandle h, const float* emb_q, int m, const float* emb_db, int n, float* sim,
@@ -356,7 +360,9 @@ int score_all_pairs_tc(SgnnHandle h, const float* emb_q, int m, const float* emb
   smem = std::max<size_t>(smem, 120 * 1024);  // one CTA per SM: each CTA owns all 512 TMEM columns
   const int grid = g_groups * q_groups;
   cudaError_t e = cudaSuccess;
-  if (stages & SCORE_PREP_Q) e = sgnn_tc_prep_q(M, G, h->d_params, emb_q, h->d_Btc, st);
+  if (stages & SCORE_COEF_ONLY) e = sgnn_tc_prep_q(M, G, h->d_params, emb_q, h->d_Btc, h->d_coef, 1, st);
+  if (e == cudaSuccess && (stages & SCORE_PREP_Q))
+    e = sgnn_tc_prep_q(M, G, h->d_params, emb_q, h->d_Btc, h->d_coef, (stages & SCORE_COEF_READY) ? 2 : 0, st);
   if (e == cudaSuccess && (stages & SCORE_PREP_DB)) e = sgnn_tc_prep_db(M, G, emb_db, h->d_Atc, st);
   if (e == cudaSuccess && (stages & SCORE_MAIN))
     e = sgnn_tc_score(M, G, relu, ref, simk, grid, smem, h->d_params, h->d_Atc, h->d_Btc, sim, ld, smax, st);
@@ -503,8 +509,8 @@ namespace {
 int embed_nodes(SgnnHandle h, const SgnnGraphBatch* b, float* emb_dev, float* node_out, cudaStream_t st) {
   if (b->n_graphs == 0) return 0;
   if (b->max_nodes <= 32) {
-    const cudaError_t e = sgnn_launch_embed_tile(h->M, to_dev(b), b->max_nodes, h->d_params, emb_dev, node_out,
-                                                 h->sm_count, h->smem_optin, st);
+    const cudaError_t e = sgnn_launch_embed_tile(h->M, to_dev(b), b->max_nodes, h->d_params, emb_dev, node_out, nullptr,
+                                                 0, 0, nullptr, 0, 0, 0, 0, h->sm_count, h->smem_optin, st);
     if (e == cudaSuccess) return 0;
     if (e != cudaErrorInvalidValue) return fail(h, std::string("embedding (tile kernel): ") + cudaGetErrorString(e));
     cudaGetLastError();
@@ -519,7 +525,35 @@ int embed_nodes(SgnnHandle h, const SgnnGraphBatch* b, float* emb_dev, float* no
 
 // embedding of one side (0 = queries, 1 = database) of a ranking entry point; with a Histogram head the
 // side's node rows are kept for the all-pairs head kernel
-int embed_side(SgnnHandle h, const SgnnGraphBatch* b, float* emb_dev, int side, cudaStream_t st) {
+// *fused (optional): the tile kernel also wrote the side's operand of the tensor-core scorer (database: A tiles,
+// queries: B tiles), so the caller skips SCORE_PREP_DB / SCORE_PREP_Q
+int embed_side(SgnnHandle h, const SgnnGraphBatch* b, float* emb_dev, int side, cudaStream_t st, bool* fused = nullptr,
+               const SgnnGraphBatch* beside = nullptr) {
+  if (fused) *fused = false;
+  // Database side: on by default (one kernel less on the critical chain).  Query side: measured neutral (the
+  // query embedding gets heavier by what the two small operand kernels cost, 70.9 vs 70.2 us per step), so it stays
+  // an opt-in (SGNN_FUSED_QUERY_PREP=1) and the default query branch is embed -> tc_coef -> tc_prep_q.
+  static const bool no_fuse = getenv("SGNN_NO_FUSED_PREP") != nullptr;
+  static const bool fuse_q = getenv("SGNN_FUSED_QUERY_PREP") != nullptr;
+  if (fused && !no_fuse && (side == 1 || fuse_q) && h->M.n_head == 0 && h->cfg.precision != SGNN_PREC_FP32 &&
+      b->n_graphs > 0 && b->max_nodes <= 32) {
+    const ModelDev& M = h->M;
+    const bool ntn = M.pair_kind == SGNN_LAYER_NTN;
+    const int K = ntn ? M.K : 1;
+    const int kc = tc_cols_per_query(K, ntn && M.pair_act == SGNN_ACT_RELU), qh = 128 / kc;
+    const int kch = round_up(M.emb_dim + 1, 16) / 8, parts = h->cfg.precision == SGNN_PREC_BF16 ? 1 : 2;
+    const int64_t need = side == 1 ? (int64_t)((b->n_graphs + 127) / 128) * parts * kch * 1024
+                                   : (int64_t)((b->n_graphs + qh - 1) / qh) * parts * kch * (TC_NPAD * 8);
+    if (need <= (side == 1 ? h->cap_Atc : h->cap_Btc)) {
+      const cudaError_t e = sgnn_launch_embed_tile(M, to_dev(b), b->max_nodes, h->d_params, emb_dev, nullptr,
+                                                   side == 1 ? h->d_Atc : nullptr, kch, parts,
+                                                   side == 0 ? h->d_Btc : nullptr, K, kc, beside ? beside->n_graphs : 0,
+                                                   beside ? beside->max_nodes : 0, h->sm_count, h->smem_optin, st);
+      if (e == cudaSuccess) { *fused = true; return 0; }
+      if (e != cudaErrorInvalidValue) return fail(h, std::string("embedding (tile kernel): ") + cudaGetErrorString(e));
+      cudaGetLastError();
+    }
+  }
   if (h->M.hist_bins == 0) return sgnn_embed_graphs(h, b, emb_dev, st);
   if (b->total_nodes > h->cap_hnodes)
     return fail(h, "node-row workspace of the histogram head too small: call sgnn_reserve(max_nodes >= total_nodes) first");
@@ -570,12 +604,24 @@ int sgnn_create(const SgnnConfig* cfg, SgnnHandle* out) {
   cudaMemset(h->d_m, 0, np * sizeof(float));
   cudaMemset(h->d_v, 0, np * sizeof(float));
   cudaMemset(h->d_loss, 0, 4 * sizeof(float));
+  // the side stream carries the (small) query branch of the ranking step next to the (large) database branch: at
+  // the highest priority its CTAs are placed first instead of queueing behind the database embedding's
+  int prio_lo = 0, prio_hi = 0;
+  cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
   if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
-      cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking) != cudaSuccess)
+      cudaStreamCreateWithPriority(&h->copy_stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess)
     return bail("cudaStreamCreate");
   for (auto& ev : h->chunk_ev)
     if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) return bail("cudaEventCreate");
   h->dep = h->M.emb_dim <= 16 ? 16 : (h->M.emb_dim <= 32 ? 32 : 64);
+  {
+    const ModelDev& M = h->M;
+    const bool ntn = M.pair_kind == SGNN_LAYER_NTN;
+    const int kc = tc_cols_per_query(ntn ? M.K : 1, ntn && M.pair_act == SGNN_ACT_RELU);
+    const int64_t cols = (int64_t)(round_up(M.emb_dim + 1, 16) / 8) * 8 * kc;
+    if (cudaMalloc(reinterpret_cast<void**>(&h->d_coef), (size_t)((M.emb_dim + 1) * cols) * sizeof(float)) != cudaSuccess)
+      h->d_coef = nullptr;   // the staged single-kernel query prep is used instead
+  }
   if (plan_launches(h)) return bail("planning launches");
   *out = h;
   return 0;
@@ -585,7 +631,7 @@ int sgnn_destroy(SgnnHandle h) {
   if (!h) return 0;
   cudaSetDevice(h->device);
   cudaFree(h->d_params); cudaFree(h->d_grads); cudaFree(h->d_m); cudaFree(h->d_v); cudaFree(h->d_loss);
-  cudaFree(h->d_P); cudaFree(h->d_C); cudaFree(h->d_Atc); cudaFree(h->d_Btc); cudaFree(h->d_smax);
+  cudaFree(h->d_coef); cudaFree(h->d_P); cudaFree(h->d_C); cudaFree(h->d_Atc); cudaFree(h->d_Btc); cudaFree(h->d_smax);
   cudaFree(h->d_rowsA); cudaFree(h->d_rowsB); cudaFree(h->d_hnodes[0]); cudaFree(h->d_hnodes[1]);
   HostWs& w = h->ws;
   for (int s = 0; s < 2; ++s) {
@@ -753,7 +799,7 @@ int sgnn_embed_graphs(SgnnHandle h, const SgnnGraphBatch* b, float* emb_dev, voi
     return 0;
   }
   {
-    const cudaError_t e = sgnn_launch_embed_tile(h->M, to_dev(b), b->max_nodes, h->d_params, emb_dev, nullptr, h->sm_count,
+    const cudaError_t e = sgnn_launch_embed_tile(h->M, to_dev(b), b->max_nodes, h->d_params, emb_dev, nullptr, nullptr, 0, 0, nullptr, 0, 0, 0, 0, h->sm_count,
                                                  h->smem_optin, st);
     if (e == cudaSuccess) return 0;
     if (e != cudaErrorInvalidValue) return fail(h, std::string("sgnn_embed_graphs: ") + cudaGetErrorString(e));
@@ -1162,14 +1208,20 @@ int sgnn_rank_device(SgnnHandle h, const SgnnGraphBatch* q_dev, const SgnnGraphB
   if (m == 0 || n == 0) return 0;
   cudaStream_t st = (cudaStream_t)stream, side = h->copy_stream;
   auto body = [&]() -> int {
-    // fork: the query branch (embed + query-side scorer tables) runs beside the database branch
+    // fork: the query branch (embed + query-side scorer tables) runs beside the database branch.  It is enqueued
+    // FIRST and on a high-priority stream: the database embedding alone fills every SM, and queued behind it the
+    // query branch (22 us of small kernels) would extend the critical path instead of hiding under it.
     CUDA_OK(h, cudaEventRecord(h->chunk_ev[1], st));
-    if (embed_side(h, db_dev, emb_db_dev, 1, st)) return 1;
-    if (score_all_pairs_stages(h, emb_q_dev, m, emb_db_dev, n, sim_dev, ld, st, SCORE_PREP_DB)) return 1;
     CUDA_OK(h, cudaStreamWaitEvent(side, h->chunk_ev[1], 0));
-    if (embed_side(h, q_dev, emb_q_dev, 0, side)) return 1;
-    if (score_all_pairs_stages(h, emb_q_dev, m, emb_db_dev, n, sim_dev, ld, side, SCORE_PREP_Q)) return 1;
+    // (the query embedding must be the FIRST kernel of the step: its CTAs do not fit beside the database embedding's,
+    // the two small operand kernels after it do)
+    bool fused_b = false;
+    if (embed_side(h, q_dev, emb_q_dev, 0, side, &fused_b, db_dev)) return 1;
+    if (!fused_b && score_all_pairs_stages(h, emb_q_dev, m, emb_db_dev, n, sim_dev, ld, side, SCORE_PREP_Q)) return 1;
     CUDA_OK(h, cudaEventRecord(h->chunk_ev[2], side));
+    bool fused_a = false;
+    if (embed_side(h, db_dev, emb_db_dev, 1, st, &fused_a)) return 1;
+    if (!fused_a && score_all_pairs_stages(h, emb_q_dev, m, emb_db_dev, n, sim_dev, ld, st, SCORE_PREP_DB)) return 1;
     CUDA_OK(h, cudaStreamWaitEvent(st, h->chunk_ev[2], 0));   // join
     return score_and_topk(h, emb_q_dev, m, emb_db_dev, n, sim_dev, ld, SCORE_MAIN, k, topk_ids_dev, topk_vals_dev,
                           st);
@@ -1307,12 +1359,14 @@ static int rank_host_impl(SgnnHandle h, int64_t m, int64_t n, const uint64_t* ke
     if (up_db(1, &ddb, cs)) return 1;
     CUDA_OK(h, cudaEventRecord(h->chunk_ev[0], cs));
     if (up_q(0, &dq, st)) return 1;
-    if (embed_side(h, &dq, w.emb_q, 0, st)) return 1;
+    bool fused_b = false;
+    if (embed_side(h, &dq, w.emb_q, 0, st, &fused_b)) return 1;
     // query-side tables of the scorer are ready before the database lands
-    if (score_all_pairs_stages(h, w.emb_q, (int)m, w.emb_db, (int)n, w.sim, n, st, SCORE_PREP_Q)) return 1;
+    if (!fused_b && score_all_pairs_stages(h, w.emb_q, (int)m, w.emb_db, (int)n, w.sim, n, st, SCORE_PREP_Q)) return 1;
     CUDA_OK(h, cudaStreamWaitEvent(st, h->chunk_ev[0], 0));
-    if (embed_side(h, &ddb, w.emb_db, 1, st)) return 1;
-    if (score_and_topk(h, w.emb_q, (int)m, w.emb_db, (int)n, w.sim, n, SCORE_PREP_DB | SCORE_MAIN,
+    bool fused_a = false;
+    if (embed_side(h, &ddb, w.emb_db, 1, st, &fused_a)) return 1;
+    if (score_and_topk(h, w.emb_q, (int)m, w.emb_db, (int)n, w.sim, n, (fused_a ? 0 : SCORE_PREP_DB) | SCORE_MAIN,
                        want_topk ? k : 0, w.topk_ids, w.topk_vals, st))
       return 1;
     if (want_topk) {

@@ -34,7 +34,13 @@ cudaError_t sgnn_launch_kendall(const float* true_sim, const float* pred_sim, in
 // node-per-thread embedding of small graphs (max_nodes <= 32); cudaErrorInvalidValue if the model
 // does not fit this kernel's shared memory (the caller then uses the warp-per-graph kernel)
 cudaError_t sgnn_launch_embed_tile(const ModelDev& M, const BatchDev& B, int max_nodes, const float* params,
-                                   float* emb, float* node_out, int sm_count, int smem_optin, cudaStream_t st);
+                                   float* emb, float* node_out, void* tc_operand_a, int kch, int parts,
+                                   void* tc_operand_b, int ntn_k, int kc, int beside_graphs, int beside_max_nodes,
+                                   int sm_count, int smem_optin, cudaStream_t st);
+// beside_graphs / beside_max_nodes (optional, 0 = none): a larger batch that is embedded concurrently -- a small
+// batch is then packed into the CTA slots that one leaves free
+// tc_operand_a / tc_operand_b (optional): also write the database-side / query-side operand of the tensor-core
+// scorer for the embedded graphs (TileOperandOut, sgnn_tile.cuh)
 
 // CTA-per-graph embedding for graphs of any size; bufA / bufB: total_nodes x sgnn_large_row_stride floats each
 int sgnn_large_row_stride(const ModelDev& M);

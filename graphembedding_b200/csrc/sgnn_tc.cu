@@ -1,4 +1,5 @@
 // Translation unit of the tcgen05 all-pairs scorer (kernels in sgnn_allpairs_tc.cuh).
+#include <cstdlib>
 #include "sgnn_allpairs_tc.cuh"
 
 namespace {
@@ -46,8 +47,19 @@ cudaError_t prep_launch(const ModelDev& M, const TcGeom& G, bool q_part, const f
 }  // namespace
 
 cudaError_t sgnn_tc_prep_q(const ModelDev& M, const TcGeom& G, const float* params, const float* emb_q, void* B_ws,
-                           cudaStream_t st) {
-  return prep_launch(M, G, true, params, emb_q, nullptr, nullptr, static_cast<__nv_bfloat16*>(B_ws), st);
+                           float* coef_ws, int mode, cudaStream_t st) {
+  static const bool staged = getenv("SGNN_PREP_Q_STAGED") != nullptr;   // the shared-memory version (cross-checks)
+  if (staged || !coef_ws) {
+    if (mode == 1) return cudaSuccess;
+    return prep_launch(M, G, true, params, emb_q, nullptr, nullptr, static_cast<__nv_bfloat16*>(B_ws), st);
+  }
+  const int C = G.KCH * 8 * G.KC;
+  if (mode != 2)
+    tc_coef_kernel<<<((G.D + 1) * C + PREPQ_THREADS - 1) / PREPQ_THREADS, PREPQ_THREADS, 0, st>>>(M, G, params, coef_ws);
+  if (mode == 1) return cudaGetLastError();
+  const dim3 grid((C + PREPQ_THREADS - 1) / PREPQ_THREADS, (G.m + PREPQ_Q - 1) / PREPQ_Q);
+  tc_prep_q_kernel<<<grid, PREPQ_THREADS, 0, st>>>(G, coef_ws, emb_q, static_cast<__nv_bfloat16*>(B_ws));
+  return cudaGetLastError();
 }
 
 cudaError_t sgnn_tc_prep_db(const ModelDev& M, const TcGeom& G, const float* emb_db, void* A_ws, cudaStream_t st) {

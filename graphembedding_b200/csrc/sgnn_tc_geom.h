@@ -33,12 +33,33 @@ __host__ __device__ inline int tc_a_bytes(const TcGeom& G) { return G.parts * G.
 __host__ __device__ inline int tc_b_bytes(const TcGeom& G) { return G.parts * G.KCH * TC_NPAD * 16; }
 constexpr int TC_TAIL_BYTES = (1 + 2 * TC_MAX_STAGES + 2 * TC_BUFS) * 8 + 16 + 4 * 64;   // barriers, TMEM slot, U
 
+#if defined(__CUDACC__)
+__device__ __forceinline__ void split_bf16(float x, __nv_bfloat16& hi, __nv_bfloat16& lo) {
+  hi = __float2bfloat16_rn(x);
+  lo = __float2bfloat16_rn(x - __bfloat162float(hi));
+}
+
+// coefficient of x_q[a] (a == D: the constant term) in column (kk, k) of the query-side operand P' / C
+__device__ __forceinline__ float tc_prep_coef(const ModelDev& M, const float* __restrict__ params, int D, int K, int a,
+                                              int kk, int k) {   // a == D: the constant term
+  if (M.pair_kind == SGNN_LAYER_DOT) return (a < D && a == kk) ? 1.f : 0.f;
+  const float* W = params + M.w_off;
+  const float* V = params + M.v_off;
+  if (kk < D) return a < D ? W[a * D * K + kk * K + k] : V[k * 2 * D + D + kk];
+  if (kk == D) return a < D ? V[k * 2 * D + a] : (M.pair_bias ? params[M.b_off + k] : 0.f);
+  return 0.f;
+}
+
+#endif
+
 // The three stages of the tensor-core scorer (defined in sgnn_tc.cu).  The query-side operand
 // (B_ws: the per-query NTN tables, bf16 hi/lo) depends only on the query embeddings and the
 // database-side operand (A_ws) only on the database embeddings, so a caller may prepare them on
 // different streams; sgnn_tc_score needs both.
+// coef_ws: (D + 1) x (KCH * 8 * KC) floats for the query-side coefficient matrix (NULL: staged single-kernel version)
 cudaError_t sgnn_tc_prep_q(const ModelDev& M, const TcGeom& G, const float* params, const float* emb_q, void* B_ws,
-                           cudaStream_t st);
+                           float* coef_ws, int mode, cudaStream_t st);
+// mode 0: coefficient matrix + operand; 1: coefficient matrix only (needs no embeddings); 2: operand only
 cudaError_t sgnn_tc_prep_db(const ModelDev& M, const TcGeom& G, const float* emb_db, void* A_ws, cudaStream_t st);
 cudaError_t sgnn_tc_score(const ModelDev& M, const TcGeom& G, bool relu, bool ref, bool simk, int grid, size_t smem,
                           const float* params, const void* A_ws, const void* B_ws, float* sim, int64_t ld,

@@ -13,7 +13,9 @@
 // read as broadcast float4.  Pooling (Padding / Average / Attention, layers.py:136-160, 223-227)
 // is done per graph by the same warp.
 #pragma once
+#include <cuda_bf16.h>
 #include "sgnn_common.cuh"
+#include "sgnn_tc_geom.h"
 
 // Build with -DSGNN_TILE_TRACE to stamp the phases of warp 0's first tile of every CTA (tools/tile_probe.py)
 #ifdef SGNN_TILE_TRACE
@@ -259,15 +261,42 @@ __device__ __forceinline__ float* tile_node_layers(const ModelDev& M, const EmbP
   return cur;
 }
 
+// Optional fused output: the database-side operand of the tensor-core all-pairs scorer (what tc_prep_kernel's
+// database branch builds from emb: bf16 hi / lo split of [x_g, 1, 0...] in the UMMA K-major core-matrix order,
+// sgnn_allpairs_tc.cuh) written by the warp that just pooled the graphs -- one kernel and one launch gap less on
+// the critical path of the ranking step.
+struct TileOperandOut {
+  __nv_bfloat16* A;   // NULL = off
+  int KCH, parts;     // 16-byte K chunks per part; 1 = bf16, 2 = bf16x3 (hi + lo)
+  // QUERY side (what tc_prep_kernel's query branch / tc_coef_kernel + tc_prep_q_kernel build): every CTA computes
+  // the (D + 1) x C coefficient matrix of the operand's columns into shared memory while its weights are in flight,
+  // and the warp that pooled a tile's graphs writes their operand rows -- the whole query branch of the ranking
+  // step is then ONE kernel (each extra graph node on that branch costs ~3 us of launch latency).
+  __nv_bfloat16* B;   // NULL = off
+  int K, KC, QH;      // NTN feature maps, accumulator columns per query, queries per 128-row B tile
+  int wm_off;         // float offset of the coefficient matrix inside dynamic shared memory
+};
+
 __global__ void __launch_bounds__(TILE_MAX_WARPS * 32, 2)
 embed_tile_kernel(const __grid_constant__ ModelDev M, const __grid_constant__ EmbPlan P, const BatchDev B,
-                  const float* __restrict__ params, float* __restrict__ emb, float* __restrict__ node_out) {
+                  const float* __restrict__ params, float* __restrict__ emb, float* __restrict__ node_out,
+                  const TileOperandOut ao) {
   extern __shared__ __align__(16) float smem[];
   float* s_w = smem;
   TILE_STAMP(0);
   TILE_STAMP(1);
   tile_stage_weights_async(M, P, params, s_w);
   TILE_STAMP(2);
+  if (ao.B) {   // coefficient matrix of the query-side operand, pass 1: the plain columns (one parameter each);
+    const int D1 = M.emb_dim + 1, C = ao.KCH * 8 * ao.KC;   // the relu sum columns follow the first CTA barrier
+    float* Wm = smem + ao.wm_off;
+#pragma unroll 4
+    for (int idx = threadIdx.x; idx < D1 * C; idx += blockDim.x) {
+      const int a = idx / C, c = idx - a * C;
+      const int kk = c / ao.KC, k = c - kk * ao.KC;
+      Wm[idx] = k < ao.K ? tc_prep_coef(M, params, M.emb_dim, ao.K, a, kk, k) : 0.f;
+    }
+  }
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
   float* my = smem + P.w_floats + warp * P.warp_floats;
   float* bufA = my;
@@ -316,6 +345,18 @@ embed_tile_kernel(const __grid_constant__ ModelDev M, const __grid_constant__ Em
       tile_cp_async_wait_all();
       __syncthreads();
       w_ready = true;
+      if (ao.B && ao.KC > ao.K) {   // pass 2: sum columns sum_k w_k Wm[a][(kk, k)], same order as tc_prep_kernel
+        const int D1 = M.emb_dim + 1, C = ao.KCH * 8 * ao.KC, groups = ao.KCH * 8;
+        float* Wm = smem + ao.wm_off;
+        const bool ref = M.pair_kind == SGNN_LAYER_DOT || M.ntn_mode == SGNN_NTN_REFERENCE;
+        for (int it = threadIdx.x; it < D1 * groups; it += blockDim.x) {
+          const int a = it / groups, col = (it - a * groups) * ao.KC;
+          float v = 0.f;
+          for (int kq = 0; kq < ao.K; ++kq) v = fmaf(ref ? 1.f : params[M.u_off + kq], Wm[a * C + col + kq], v);
+          Wm[a * C + col + ao.K] = v;
+        }
+        __syncthreads();
+      }
     }
     if (!live) break;
     if (t == blockIdx.x * nw) TILE_STAMP(3);
@@ -391,6 +432,56 @@ embed_tile_kernel(const __grid_constant__ ModelDev M, const __grid_constant__ Em
       }
     }
     __syncwarp();
+    if (ao.A) {   // the rows this warp just wrote (ordered by the __syncwarp above), re-read through L2
+      for (int item = lane; item < (g1 - g0) * ao.KCH; item += 32) {
+        const int gi = item / ao.KCH, kc = item - gi * ao.KCH;
+        const int g = g0 + gi;
+        __align__(16) __nv_bfloat16 hi[8], lo[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int b = kc * 8 + j;
+          const float v = b < E ? __ldcg(emb + (size_t)g * E + b) : (b == E ? 1.f : 0.f);
+          hi[j] = __float2bfloat16_rn(v);
+          lo[j] = __float2bfloat16_rn(v - __bfloat162float(hi[j]));
+        }
+        const size_t base = ((size_t)((g >> 7) * ao.parts) * ao.KCH + kc) * 1024 + (size_t)(g & 127) * 8;
+        *reinterpret_cast<uint4*>(ao.A + base) = *reinterpret_cast<const uint4*>(hi);
+        if (ao.parts == 2)
+          *reinterpret_cast<uint4*>(ao.A + base + (size_t)ao.KCH * 1024) = *reinterpret_cast<const uint4*>(lo);
+      }
+    }
+    if (ao.B) {   // operand rows of the tile's queries: lane = column, same summation order as tc_prep_q_kernel
+      const int C = ao.KCH * 8 * ao.KC, ng = g1 - g0;
+      const float* Wm = smem + ao.wm_off;
+      float* xs = scratch;   // [ng][E]: the rows this warp just wrote, one L2 round trip
+      for (int i = lane; i < ng * E; i += 32) xs[i] = __ldcg(emb + (size_t)g0 * E + i);
+      __syncwarp();
+      const size_t lo_off = (size_t)ao.KCH * TC_NPAD * 8;
+      for (int c = lane; c < C; c += 32) {
+        const int kk = c / ao.KC, k = c - kk * ao.KC;
+        const float cst = Wm[E * C + c];
+        for (int q0 = 0; q0 < ng; q0 += 4) {
+          float acc[4] = {cst, cst, cst, cst};
+          for (int a = 0; a < E; ++a) {
+            const float w = Wm[a * C + c];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[j] = fmaf(q0 + j < ng ? xs[(q0 + j) * E + a] : 0.f, w, acc[j]);
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (q0 + j < ng) {
+              const int q = g0 + q0 + j;
+              const int qb = q / ao.QH, row = (q - qb * ao.QH) * ao.KC + k;
+              __nv_bfloat16* dst = ao.B + ((size_t)(qb * ao.parts) * ao.KCH + (kk >> 3)) * (TC_NPAD * 8) + (size_t)row * 8 + (kk & 7);
+              const __nv_bfloat16 hi = __float2bfloat16_rn(acc[j]);
+              *dst = hi;
+              if (ao.parts == 2) dst[lo_off] = __float2bfloat16_rn(acc[j] - __bfloat162float(hi));
+            }
+          }
+        }
+      }
+      __syncwarp();
+    }
     if (t == blockIdx.x * nw) TILE_STAMP(5);
   }
   TILE_STAMP(6);

@@ -172,7 +172,7 @@ class SgnnEngine(object):
             out = torch.empty((m, n), dtype=torch.float32, device=self.device)
         check(self.h, lib().sgnn_score_all_pairs(self.h, _ptr(emb_q), m, _ptr(emb_db), n, _ptr(out),
                                                  out.stride(0), _stream_ptr(stream)))
-        self.launches += 2 if self.precision == 'fp32' else 3   # operand prep (query / database side) + scorer
+        self.launches += 2 if (self.precision == 'fp32' or self.has_head) else 4   # coefficient matrix, operand prep (query / database side), scorer
         return out
 
     STAGE_PREP_QUERIES, STAGE_PREP_DATABASE, STAGE_SCORE = 1, 2, 4
@@ -182,7 +182,10 @@ class SgnnEngine(object):
         m, n = emb_q.shape[0], emb_db.shape[0]
         check(self.h, lib().sgnn_score_all_pairs_stages(self.h, _ptr(emb_q), m, _ptr(emb_db), n, _ptr(out),
                                                         out.stride(0), int(stages), _stream_ptr(stream)))
-        self.launches += bin(int(stages)).count('1') if self.precision != 'fp32' else bin(int(stages) & 5).count('1')
+        if self.precision == 'fp32' or self.has_head:
+            self.launches += bin(int(stages) & 5).count('1')
+        else:
+            self.launches += bin(int(stages)).count('1') + (int(stages) & 1)   # query prep = coefficient matrix + operand
         return out
 
     def topk(self, sim, k, stream=None):
@@ -336,6 +339,19 @@ class SgnnEngine(object):
         self.launches += 2
         return raw, sim
 
+    def _rank_launches(self, db, k):
+        """Kernels of one ranking step: 2 embeddings, scorer, (top-k), plus the operand preparation of the scorer
+        unless the tile embedding kernels wrote the tensor-core operands themselves (graphs of <= 32 nodes, no head)."""
+        n = 3 + (1 if k > 0 else 0)
+        small = db is None or db.max_nodes <= 32
+        if self.precision == 'fp32' or self.has_head:
+            n += 1                      # query-side tables
+        else:
+            n += 2                      # query side: coefficient matrix + operand
+            if not small:
+                n += 1                  # database-side operand (otherwise written by the embedding kernel)
+        return n
+
     def rank_device(self, queries, db, k, emb_q=None, emb_db=None, sim=None, ids=None, vals=None, stream=None):
         """The whole ranking step on device-resident batches (sgnn_rank_device): the query branch
         overlaps the database branch.  Returns (ids, vals, sim)."""
@@ -351,7 +367,7 @@ class SgnnEngine(object):
         sq, sd = queries.struct(), db.struct()
         check(self.h, lib().sgnn_rank_device(self.h, C.byref(sq), C.byref(sd), int(k), _ptr(emb_q), _ptr(emb_db),
                                              _ptr(sim), sim.stride(0), _ptr(ids), _ptr(vals), _stream_ptr(stream)))
-        self.launches += 6 if k > 0 else 5   # 2 embeds, 2 operand preps, scorer, top-k
+        self.launches += self._rank_launches(db, k)
         return ids, vals, sim
 
     def rank_sharded(self, queries, db_shard, k, id_offset, emb_q=None, emb_db=None, sim=None, ids=None, vals=None,
@@ -373,7 +389,7 @@ class SgnnEngine(object):
         check(self.h, lib().sgnn_rank_sharded(self.h, C.byref(sq), C.byref(sd), int(k), int(id_offset), _ptr(emb_q),
                                               _ptr(emb_db), _ptr(sim), sim.stride(0), _ptr(ids), _ptr(vals),
                                               _ptr(out_ids), _ptr(out_vals), _stream_ptr(stream)))
-        self.launches += 8   # 2 embeds, 2 operand preps, scorer, top-k, push, merge
+        self.launches += 2 + self._rank_launches(db_shard, k)   # + push, merge
         return out_ids, out_vals
 
     def rank_host(self, queries, db, k, ids=None, vals=None, sim=None):
@@ -383,7 +399,7 @@ class SgnnEngine(object):
         sq, sd = queries.struct(), db.struct()
         check(self.h, lib().sgnn_rank_host(self.h, C.byref(sq), C.byref(sd), k, _ptr(ids), _ptr(vals),
                                            _ptr(sim)))
-        self.launches += 6   # embed(queries) + embed(database) + 2 operand preps + scorer + top-k
+        self.launches += self._rank_launches(db, k)
         return ids, vals
 
     def rank_host_compact(self, q_blob, db_blob, k, ids=None, vals=None, sim=None):
@@ -393,7 +409,7 @@ class SgnnEngine(object):
         vals = np.empty((m, k), np.float32) if vals is None else vals
         check(self.h, lib().sgnn_rank_host_compact(self.h, _ptr(q_blob), _ptr(db_blob), k, _ptr(ids), _ptr(vals),
                                                    _ptr(sim)))
-        self.launches += 8   # 2 expansions + embed(queries) + embed(database) + 2 operand preps + scorer + top-k
+        self.launches += 2 + self._rank_launches(None, k)   # + 2 expansions (compact blobs: graphs of <= 256 nodes)
         return ids, vals
 
     def train_step_host(self, batch, g1, g2, target_sim, loss=None):

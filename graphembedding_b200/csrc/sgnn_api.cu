@@ -289,8 +289,10 @@ int plan_launches(SgnnHandle h) {
   if (M.n_head > 0 && !h->use_team)
     return fail(h, "a model with a Dense / Histogram head needs the CTA-per-pair training kernel, which does not fit shared memory");
   if (h->use_team) {
-    if (set_smem(h, train_team_kernel<true>, h->team_smem32)) return 1;
-    if (set_smem(h, train_team_kernel<false>, h->team_smem32)) return 1;
+    // opt in to all of the SM's shared memory: the per-arm buffers grow with the batch's largest graph, and
+    // graphs well beyond 32 nodes still fit for the usual layer widths (launch_pairs checks per call)
+    if (set_smem(h, train_team_kernel<true>, (size_t)h->smem_optin)) return 1;
+    if (set_smem(h, train_team_kernel<false>, (size_t)h->smem_optin)) return 1;
   }
   return 0;
 }
@@ -944,7 +946,13 @@ static int launch_pairs(SgnnHandle h, bool bwd, const SgnnGraphBatch* b, const i
                         double target_sqsum, float* loss, float* raw, float* sim, void* stream, bool no_dropout) {
   if (n_pairs == 0) return 0;
   if (global_batch < n_pairs) return fail(h, "global_batch < n_pairs");
-  if (b->max_nodes > 32) return fail(h, "graphs with more than 32 nodes need the large-graph path (not built yet)");
+  if (b->max_nodes > 32) {   // beyond the warp-per-pair kernel; the CTA-per-pair kernel takes what fits shared memory
+    const size_t need = h->use_team ? team_smem_floats(h->M, (int)b->max_nodes) * sizeof(float) : 0;
+    if (!h->use_team || need > (size_t)h->smem_optin)
+      return fail(h, "graphs of up to " + std::to_string(b->max_nodes) + " nodes do not fit the per-pair kernel's shared memory (" +
+                         std::to_string(need / 1024) + " KB needed): listed-pair training / evaluation of graphs this large "
+                         "is not built yet (embedding, all-pairs scoring and the histogram op handle them)");
+  }
   const int v = b->max_nodes <= 16 ? 0 : 1;
   const int wpb = h->train_wpb[v];
   const int blocks = std::min((n_pairs + wpb - 1) / wpb, h->sm_count * 2);

@@ -492,3 +492,40 @@ def test_score_all_pairs_stages_compose_to_the_single_call(precision):
     assert torch.equal(out, ref)
     with pytest.raises(RuntimeError):
         eng.score_all_pairs_stages(eq, ed, out, 8)
+
+
+@pytest.mark.parametrize('cfg,n_hi', [('avg_ntn', 100), ('att3', 40), ('dense_dot', 64)])
+def test_listed_pair_training_beyond_32_nodes(cfg, n_hi):
+    """The CTA-per-pair kernel keeps a pair's activations in shared memory and takes any graph size that fits
+    (far beyond the 32-node tile kernels): loss, predictions and gradients against the fp64 oracle on graphs of
+    up to 100 nodes; an over-sized batch fails loudly instead of falling back."""
+    layers_spec = list(CONFIGS[cfg])
+    from graphembedding_b200.engine import SgnnEngine
+    from graphembedding_b200.graphs import pack_nx_graphs
+    from graphembedding_b200.layers_factory import parse_layers
+    gs = corpus(24, max(2, n_hi // 2), n_hi, seed=19)
+    enc = encoder_for(gs)
+    layers = parse_layers(layers_spec, enc.input_dim())
+    eng = SgnnEngine(layers, enc.input_dim(), loss_mode='paired')
+    flat = O.init_params(O.parse_layer_specs(layers_spec, enc.input_dim()), seed=11)
+    eng.set_params(flat)
+    batch = pack_nx_graphs(gs, enc)
+    assert batch.max_nodes > 32
+    B = 12
+    tgt = np.random.default_rng(2).uniform(0.05, 1.0, size=B).astype(np.float32)
+    g1 = torch.arange(0, B, dtype=torch.int32, device=eng.device)
+    g2 = torch.arange(B, 2 * B, dtype=torch.int32, device=eng.device)
+    dev = batch.to(eng.device)
+    loss = eng.train_step(dev, g1, g2, torch.as_tensor(tgt, device=eng.device))
+    grads = eng.device_buffers()[1].cpu().numpy().astype(np.float64)
+    og = oracle_graphs(gs, enc)
+    l, mse, pred, ref_g, raw = O.loss_and_grads(layers, flat, og[:B], og[B:2 * B], tgt, enc.input_dim(),
+                                                weight_decay=0.0, loss_mode='paired')
+    assert abs(float(loss[0]) - mse) <= RTOL * max(abs(mse), 1e-3)
+    assert np.max(np.abs(grads - ref_g)) <= 2e-4 * np.max(np.abs(ref_g))
+    _, raw_d, sim_d = eng.eval_pairs(dev, g1, g2)
+    assert np.max(np.abs(raw_d.cpu().numpy() - raw)) <= RTOL * max(1.0, np.max(np.abs(raw)))
+    if cfg == 'avg_ntn':   # a 500-node batch does not fit: loud error, no fallback
+        big = pack_nx_graphs(corpus(4, 400, 500, seed=3), enc).to(eng.device)
+        with pytest.raises(RuntimeError, match='do not fit'):
+            eng.train_step(big, g1[:2], g2[:2] - B + 2, torch.as_tensor(tgt[:2], device=eng.device))

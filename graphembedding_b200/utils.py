@@ -18,3 +18,9 @@ def check_flags():
 
 def print_msec(sec):
     return '{:.2f}msec'.format(sec * 1000)
+
+
+def get_ts():
+    """src/utils.py:142-147: timestamp used in log / result file names."""
+    import datetime
+    return datetime.datetime.now().strftime('%Y-%m-%dT%H:%M:%S')

@@ -80,3 +80,20 @@ def test_unknown_tvt_raises_like_reference():
     d, fl, data, dc, model, sess, saver = _setup('default')
     with pytest.raises((RuntimeError, AssertionError)):
         run_tf(data, dc, model, saver, sess, 'bogus')
+
+
+def test_tuning_sweep_runs_end_to_end(tmp_path):
+    """two points of the sweep through the real train.main() (train + validate + all-pairs test +
+    metrics on the device), CSV in the reference's layout."""
+    from graphembedding_b200 import tuning
+    grid = [(True, 0.6, 'sim_kernel', 0.01, 20, 0.25, 0.0), (False, 0.01, 'sigmoid', 0.01, 20, 0.25, 0.1)]
+    path = str(tmp_path / 'sweep.csv')
+    best_train, best_val = tuning.tune(file_name=path, grid=grid)
+    lines = open(path).read().strip().split('\n')
+    assert lines[0].split(',') == tuning.header and len(lines) == 1 + 2 + 5
+    for ln in lines[1:3]:
+        cells = ln.split(',')
+        assert len(cells) == len(tuning.header)
+        vals = [float(c) for c in cells[6:]]
+        assert all(np.isfinite(vals)) and all(0.0 <= v <= 1.0 for v in vals[4:24])
+    assert len(best_train) == len(best_val) == len(tuning.header) - 2

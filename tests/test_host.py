@@ -283,3 +283,43 @@ def test_compact_wire_format_rejects_what_does_not_fit_a_byte():
     one = PackedBatch.from_lists([np.array([3], np.int32)], [np.zeros((0, 2), np.int32)])
     back = PackedBatch.from_compact(one.compact(pinned=False))
     assert back.val.tolist() == [1.0] and back.labels.tolist() == [3] and back.rowptr.tolist() == [0, 1]
+
+
+def test_tuning_tables_and_csv_layout_match_the_reference():
+    """the sweep driver's tables are the reference's (tests/golden/tuning.json, extracted from
+    model/Siamese/tuning.py with tests/golden/make_tuning_golden.py) and one sweep point writes the reference's
+    CSV layout (tuning.py:113-158)."""
+    from graphembedding_b200 import tuning
+    g = _load('tuning.json')
+    for name in ('dataset', 'header', 'model', 'dist_norm_range', 'yeta_range_norm', 'yeta_range_nonorm',
+                 'final_act_range', 'lr_range', 'iter_range', 'val_ratio_range', 'dropout_range', 'layers'):
+        assert getattr(tuning, name) == g[name], name
+    pts = list(tuning.grid_points())
+    assert len(pts) == (6 + 4) * 5 * 6 * 4 * 2 * 2 and pts[0] == (True, 0.1, 'identity', 0.06, 500, 0.25, 0.1)
+    assert pts[-1] == (False, 0.0005, 'sim_kernel', 0.001, 2000, 0.4, 0.5)
+    aps = np.linspace(0.1, 1.0, 12)
+    res = {k: {tuning.model: v} for k, v in (('mrr_norm', 0.5), ('mrr_nonorm', 0.4), ('mse_norm', 0.01),
+                                              ('mse_nonorm', 0.02))}
+    res['apk_norm'] = {tuning.model: {'aps': aps}}
+    res['apk_nonorm'] = {tuning.model: {'aps': aps[::-1]}}
+    row = tuning.parse_results(res)
+    assert len(row) == 24 and row[:10] == list(aps[:10]) and row[-4:] == [0.5, 0.4, 0.01, 0.02]
+    import tempfile
+    calls = []
+
+    def fake_main():
+        from graphembedding_b200.config import FLAGS
+        calls.append((FLAGS.dist_norm, FLAGS.yeta, FLAGS.final_act, FLAGS.learning_rate, FLAGS.iters,
+                      FLAGS.valid_percentage, FLAGS.dropout, FLAGS.num_layers, FLAGS.layer_2))
+        return [0.3, 0.1 + 0.01 * len(calls), 0.2], [0.0] * 3, [0.5, 0.4 - 0.01 * len(calls)], [0.0] * 2, res
+
+    with tempfile.TemporaryDirectory() as d:
+        path = os.path.join(d, 'sweep.csv')
+        best_train, best_val = tuning.tune(file_name=path, limit=3, run=fake_main)
+        lines = open(path).read().strip().split('\n')
+    assert calls[0] == (True, 0.1, 'identity', 0.06, 500, 0.25, 0.1, 4, 'Average') and len(calls) == 3
+    assert lines[0].split(',') == tuning.header
+    assert len(lines) == 1 + 3 + 5 and lines[4] == 'Final results:'
+    assert len(lines[1].split(',')) == len(tuning.header)
+    assert best_train[6] == pytest.approx(0.11) and best_val[6] == pytest.approx(0.37)
+    assert len(lines[5].split(',')) == len(lines[6].split(',')) == len(tuning.header) - 2

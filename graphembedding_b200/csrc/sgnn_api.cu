@@ -783,7 +783,9 @@ int sgnn_reserve(SgnnHandle h, int64_t max_graphs, int64_t max_nodes, int64_t ma
     w.cap_db = std::max(w.cap_db, max_db);
     if (dev_alloc(h, &w.sim, w.cap_q * w.cap_db)) return 1;
     w.cap_topk = w.cap_q * 64;
-    if (dev_alloc(h, &w.topk_ids, w.cap_topk) || dev_alloc(h, &w.topk_vals, w.cap_topk)) return 1;
+    // ids and values of one call lie back to back in the ids allocation (one device -> host copy when the
+    // caller's two host arrays are contiguous too)
+    if (dev_alloc(h, &w.topk_ids, 2 * w.cap_topk) || dev_alloc(h, &w.topk_vals, w.cap_topk)) return 1;
   }
   return 0;
 }
@@ -1375,12 +1377,17 @@ static int rank_host_impl(SgnnHandle h, int64_t m, int64_t n, const uint64_t* ke
     bool fused_a = false;
     if (embed_side(h, &ddb, w.emb_db, 1, st, &fused_a)) return 1;
     if (score_and_topk(h, w.emb_q, (int)m, w.emb_db, (int)n, w.sim, n, (fused_a ? 0 : SCORE_PREP_DB) | SCORE_MAIN,
-                       want_topk ? k : 0, w.topk_ids, w.topk_vals, st))
+                       want_topk ? k : 0, w.topk_ids, reinterpret_cast<float*>(w.topk_ids + m * k), st))
       return 1;
     if (want_topk) {
-      CUDA_OK(h, cudaMemcpyAsync(topk_ids_host, w.topk_ids, (size_t)m * k * 4, cudaMemcpyDeviceToHost, st));
-      if (topk_vals_host)
-        CUDA_OK(h, cudaMemcpyAsync(topk_vals_host, w.topk_vals, (size_t)m * k * 4, cudaMemcpyDeviceToHost, st));
+      const size_t bytes = (size_t)m * k * 4;
+      if (topk_vals_host == reinterpret_cast<float*>(topk_ids_host + m * k)) {   // contiguous on both sides: one copy
+        CUDA_OK(h, cudaMemcpyAsync(topk_ids_host, w.topk_ids, 2 * bytes, cudaMemcpyDeviceToHost, st));
+      } else {
+        CUDA_OK(h, cudaMemcpyAsync(topk_ids_host, w.topk_ids, bytes, cudaMemcpyDeviceToHost, st));
+        if (topk_vals_host)
+          CUDA_OK(h, cudaMemcpyAsync(topk_vals_host, w.topk_ids + m * k, bytes, cudaMemcpyDeviceToHost, st));
+      }
     }
     if (sim_host) CUDA_OK(h, cudaMemcpyAsync(sim_host, w.sim, (size_t)m * n * 4, cudaMemcpyDeviceToHost, st));
     return 0;

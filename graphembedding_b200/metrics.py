@@ -165,7 +165,9 @@ def kendall_tau(true_r, pred_r, norm):
     dev = _on_device(true_r, pred_r, norm)
     if dev is not None:
         taus = _ENGINE.kendall_tau(dev[0], dev[1])[0].cpu().numpy()
-        return float(np.nanmean(taus)), taus
+        # tau-b is undefined (NaN) for a row that is constant on either side; a sweep point whose model collapsed
+        # to a constant has only such rows
+        return (float(np.nanmean(taus)) if np.any(~np.isnan(taus)) else float('nan')), taus
     t = true_r.dist_sim_mat(norm)
     if hasattr(true_r, 'dist_mat'):
         t = -t

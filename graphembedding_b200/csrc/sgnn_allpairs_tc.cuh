@@ -164,38 +164,41 @@ tc_coef_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const float* 
 __global__ void __launch_bounds__(PREPQ_THREADS, 16)
 tc_prep_q_kernel(const TcGeom G, const float* __restrict__ Wm, const float* __restrict__ emb_q,
                  __nv_bfloat16* __restrict__ B) {
+  __shared__ float xs[PREPQ_Q * 64];   // the block's query embeddings (D <= 64): 2 KB, fits the leftover too
   const int D = G.D, KC = G.KC;
   const int C = G.KCH * 8 * KC;
   const int c = blockIdx.x * PREPQ_THREADS + threadIdx.x;
+  const int q0 = blockIdx.y * PREPQ_Q;
+  const int nq = min(PREPQ_Q, G.m - q0);
+  for (int i = threadIdx.x; i < PREPQ_Q * D; i += PREPQ_THREADS)   // PREPQ_Q consecutive rows = one contiguous span
+    xs[i] = i < nq * D ? emb_q[(size_t)q0 * D + i] : 0.f;
+  __syncthreads();
   if (c >= C) return;
   const int kk = c / KC, k = c - kk * KC;
-  const int q0 = blockIdx.y * PREPQ_Q;
   float acc[PREPQ_Q];
   const float cst = Wm[(size_t)D * C + c];
 #pragma unroll
   for (int qq = 0; qq < PREPQ_Q; ++qq) acc[qq] = cst;
-  const int nq = min(PREPQ_Q, G.m - q0);
-#pragma unroll 4
+#pragma unroll 5
   for (int a = 0; a < D; ++a) {
     const float w = Wm[(size_t)a * C + c];
 #pragma unroll
-    for (int qq = 0; qq < PREPQ_Q; ++qq) {
-      const float x = qq < nq ? __ldg(emb_q + (size_t)(q0 + qq) * D + a) : 0.f;
-      acc[qq] = fmaf(x, w, acc[qq]);
-    }
+    for (int qq = 0; qq < PREPQ_Q; ++qq) acc[qq] = fmaf(xs[qq * D + a], w, acc[qq]);
   }
   const size_t lo_off = (size_t)G.KCH * TC_NPAD * 8;
+  int qb = q0 / G.QH, r = q0 - qb * G.QH;   // query q = q-block qb, slot r; advanced without further divisions
+  __nv_bfloat16* col = B + (size_t)(kk >> 3) * (TC_NPAD * 8) + (kk & 7);
+  const size_t qb_stride = (size_t)G.parts * G.KCH * (TC_NPAD * 8);
 #pragma unroll
   for (int qq = 0; qq < PREPQ_Q; ++qq) {
-    const int q = q0 + qq;
     if (qq < nq) {
-      const int qb = q / G.QH, row = (q - qb * G.QH) * KC + k;
-      __nv_bfloat16* dst = B + ((size_t)(qb * G.parts) * G.KCH + (kk >> 3)) * (TC_NPAD * 8) + (size_t)row * 8 + (kk & 7);
+      __nv_bfloat16* dst = col + (size_t)qb * qb_stride + (size_t)(r * KC + k) * 8;
       __nv_bfloat16 hi, lo;
       split_bf16(acc[qq], hi, lo);
       *dst = hi;
       if (G.parts == 2) dst[lo_off] = lo;
     }
+    if (++r == G.QH) { r = 0; ++qb; }
   }
 }
 

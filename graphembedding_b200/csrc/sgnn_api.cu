@@ -98,6 +98,7 @@ struct SgnnHandle_t {
   int dep = 16;                           // padded embedding width of the all-pairs scorer
   cudaStream_t stream = nullptr;          // used by *_host entry points
   cudaStream_t copy_stream = nullptr;     // host -> device uploads that overlap compute (sgnn_rank_host)
+  cudaStream_t aux_stream = nullptr;      // parameter-only work of the ranking step (tc_coef_kernel), beside both branches
   cudaEvent_t chunk_ev[8] = {};
   HostWs ws;
   // launch geometry decided at create
@@ -611,7 +612,8 @@ int sgnn_create(const SgnnConfig* cfg, SgnnHandle* out) {
   int prio_lo = 0, prio_hi = 0;
   cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
   if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
-      cudaStreamCreateWithPriority(&h->copy_stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess)
+      cudaStreamCreateWithPriority(&h->copy_stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess ||
+      cudaStreamCreateWithPriority(&h->aux_stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess)
     return bail("cudaStreamCreate");
   for (auto& ev : h->chunk_ev)
     if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) return bail("cudaEventCreate");
@@ -648,6 +650,7 @@ int sgnn_destroy(SgnnHandle h) {
   h->g_rank_sharded.drop();
   sgnn_peer_destroy(h);
   if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+  if (h->aux_stream) cudaStreamDestroy(h->aux_stream);
   for (auto& ev : h->chunk_ev) if (ev) cudaEventDestroy(ev);
   delete h;
   return 0;
@@ -1227,7 +1230,15 @@ int sgnn_rank_device(SgnnHandle h, const SgnnGraphBatch* q_dev, const SgnnGraphB
     // the two small operand kernels after it do)
     bool fused_b = false;
     if (embed_side(h, q_dev, emb_q_dev, 0, side, &fused_b, db_dev)) return 1;
-    if (!fused_b && score_all_pairs_stages(h, emb_q_dev, m, emb_db_dev, n, sim_dev, ld, side, SCORE_PREP_Q)) return 1;
+    if (!fused_b) {
+      // the coefficient matrix needs the parameters only: a third stream takes it off the query chain
+      cudaStream_t aux = h->aux_stream;
+      CUDA_OK(h, cudaStreamWaitEvent(aux, h->chunk_ev[1], 0));
+      if (score_all_pairs_stages(h, emb_q_dev, m, emb_db_dev, n, sim_dev, ld, aux, SCORE_COEF_ONLY)) return 1;
+      CUDA_OK(h, cudaEventRecord(h->chunk_ev[5], aux));
+      CUDA_OK(h, cudaStreamWaitEvent(side, h->chunk_ev[5], 0));
+      if (score_all_pairs_stages(h, emb_q_dev, m, emb_db_dev, n, sim_dev, ld, side, SCORE_PREP_Q | SCORE_COEF_READY)) return 1;
+    }
     CUDA_OK(h, cudaEventRecord(h->chunk_ev[2], side));
     bool fused_a = false;
     if (embed_side(h, db_dev, emb_db_dev, 1, st, &fused_a)) return 1;

@@ -404,9 +404,10 @@ class SgnnEngine(object):
 
     def rank_host_compact(self, q_blob, db_blob, k, ids=None, vals=None, sim=None):
         """sgnn_rank_host on compact blobs (PackedBatch.compact())."""
-        m = int(np.frombuffer(bytes(np.asarray(q_blob[4:8])), np.int32)[0])
-        ids = np.empty((m, k), np.int32) if ids is None else ids
-        vals = np.empty((m, k), np.float32) if vals is None else vals
+        if ids is None or vals is None:   # the header is only read when the outputs have to be sized here
+            m = int(np.frombuffer(bytes(np.asarray(q_blob[4:8])), np.int32)[0])
+            ids = np.empty((m, k), np.int32) if ids is None else ids
+            vals = np.empty((m, k), np.float32) if vals is None else vals
         check(self.h, lib().sgnn_rank_host_compact(self.h, _ptr(q_blob), _ptr(db_blob), k, _ptr(ids), _ptr(vals),
                                                    _ptr(sim)))
         self.launches += 2 + self._rank_launches(None, k)   # + 2 expansions (compact blobs: graphs of <= 256 nodes)

@@ -175,9 +175,13 @@ class PackedBatch(object):
         self.nnz = int(len(col))
 
     def struct(self):
-        return GraphBatch(self.n_graphs, self.total_nodes, self.nnz, self.max_nodes,
-                          _ptr(self.node_off), _ptr(self.labels), _ptr(self.rowptr), _ptr(self.col),
-                          _ptr(self.val))
+        """The SgnnGraphBatch view of this batch (built once: the arrays of a PackedBatch are never rebound)."""
+        st = getattr(self, '_struct', None)
+        if st is None:
+            st = self._struct = GraphBatch(self.n_graphs, self.total_nodes, self.nnz, self.max_nodes,
+                                           _ptr(self.node_off), _ptr(self.labels), _ptr(self.rowptr), _ptr(self.col),
+                                           _ptr(self.val))
+        return st
 
     def to(self, device):
         import torch

@@ -379,7 +379,7 @@ def run_cuda(args):
     alg_bytes = 4.0 * M_QUERIES * N_DB + 4.0 * (M_QUERIES + N_DB) * eng.emb_dim
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
     roofline = {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
-                'traffic': 2.2e6 if args.precision != 'fp32' else None,   # ncu --set full, profiles/r1o: 1.4 MB read + 0.8 MB written (sim stays in L2)
+                'traffic': 1.67e6 if args.precision != 'fp32' else None,   # ncu --set full, profiles/r1v_step_ncu_raw.csv: 1.43 MB read + 0.24 MB written per launch (sim stays in L2)
                 'kernel': 'allpairs_tc_kernel (tcgen05 scorer, SGNN_STAGE_SCORE)' if args.precision != 'fp32'
                 else 'allpairs_fp32_kernel',
                 'kernel_ms': k_ms, 'peak_source': peak_src,

@@ -373,10 +373,22 @@ pair_histogram_tiled_kernel(const float* __restrict__ node_emb, int d, const int
         const int i = 2 * ip;
         const bool vi = i + 1 < n1;
         float ha[ND], hb[ND];
+        if ((d & 3) == 0) {   // rows are 16-byte aligned: vector loads (row i + 1 of the last odd row is zeroed below)
+          const float4* ra = reinterpret_cast<const float4*>(node_emb + (size_t)(a0 + i) * d);
+          const float4* rb = reinterpret_cast<const float4*>(node_emb + (size_t)(a0 + (vi ? i + 1 : i)) * d);
 #pragma unroll
-        for (int c = 0; c < ND; ++c) {
-          ha[c] = c < d ? node_emb[(size_t)(a0 + i) * d + c] : 0.f;
-          hb[c] = (vi && c < d) ? node_emb[(size_t)(a0 + i + 1) * d + c] : 0.f;
+          for (int c = 0; c < ND / 4; ++c) {
+            const float4 u = 4 * c < d ? __ldg(ra + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+            const float4 v = (vi && 4 * c < d) ? __ldg(rb + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+            ha[4 * c] = u.x; ha[4 * c + 1] = u.y; ha[4 * c + 2] = u.z; ha[4 * c + 3] = u.w;
+            hb[4 * c] = v.x; hb[4 * c + 1] = v.y; hb[4 * c + 2] = v.z; hb[4 * c + 3] = v.w;
+          }
+        } else {
+#pragma unroll
+          for (int c = 0; c < ND; ++c) {
+            ha[c] = c < d ? node_emb[(size_t)(a0 + i) * d + c] : 0.f;
+            hb[c] = (vi && c < d) ? node_emb[(size_t)(a0 + i + 1) * d + c] : 0.f;
+          }
         }
         const int jend = min(tj, (jc + 1) << 5);
         for (int j = jc << 5; j < jend; j += 2) {

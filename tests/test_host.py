@@ -323,3 +323,25 @@ def test_tuning_tables_and_csv_layout_match_the_reference():
     assert len(lines[1].split(',')) == len(tuning.header)
     assert best_train[6] == pytest.approx(0.11) and best_val[6] == pytest.approx(0.37)
     assert len(lines[5].split(',')) == len(lines[6].split(',')) == len(tuning.header) - 2
+
+
+def test_header_constants_match_the_python_binding():
+    """Enumerations of include/sgnn.h that the Python side mirrors by value."""
+    from graphembedding_b200 import native
+    from graphembedding_b200.engine import SgnnEngine
+    hdr = open(os.path.join(ROOT, 'include', 'sgnn.h')).read()
+
+    def const(name):
+        m = re.search(r'\b' + name + r'\s*=\s*(\d+)', hdr) or re.search(r'#define\s+' + name + r'\s+(\d+)', hdr)
+        assert m, name
+        return int(m.group(1))
+    for kind, v in native.LAYER_KINDS.items():
+        cname = {'GraphConvolution': 'SGNN_LAYER_GCN'}.get(kind, 'SGNN_LAYER_' + kind.upper())
+        assert const(cname) == v, kind
+    for act, v in native.ACTS.items():
+        assert const('SGNN_ACT_' + act.upper()) == v, act
+    assert const('SGNN_PREC_FP32') == native.PRECISIONS['fp32'] and const('SGNN_PREC_BF16X3') == native.PRECISIONS['bf16x3']
+    assert const('SGNN_STAGE_PREP_QUERIES') == SgnnEngine.STAGE_PREP_QUERIES
+    assert const('SGNN_STAGE_PREP_DATABASE') == SgnnEngine.STAGE_PREP_DATABASE
+    assert const('SGNN_STAGE_SCORE') == SgnnEngine.STAGE_SCORE
+    assert const('SGNN_MAX_LAYERS') == native.SGNN_MAX_LAYERS and const('SGNN_ABI_VERSION') == native.ABI_VERSION

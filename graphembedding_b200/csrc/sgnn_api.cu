@@ -7,6 +7,7 @@
 
 #include "sgnn_allpairs.cuh"
 #include "sgnn_tc_geom.h"
+#include "sgnn_hist_tc_geom.h"
 #include "sgnn_common.cuh"
 #include "sgnn_internal.h"
 #include "sgnn_small.cuh"
@@ -95,6 +96,7 @@ struct SgnnHandle_t {
   int64_t cap_Atc = 0, cap_Btc = 0;                   // in elements
   unsigned long long* d_smax = nullptr;                          // [queries][32-graph slices] slice maxima (top-k hints)
   int64_t cap_smax = 0;
+  HistTcWs ht;                            // tensor-core node-node histogram: operand tiles, tile tables, count matrix
   int dep = 16;                           // padded embedding width of the all-pairs scorer
   cudaStream_t stream = nullptr;          // used by *_host entry points
   cudaStream_t copy_stream = nullptr;     // host -> device uploads that overlap compute (sgnn_rank_host)
@@ -313,6 +315,14 @@ int dev_alloc(SgnnHandle h, T** p, int64_t count) {
   return 0;
 }
 
+// the histogram layer of a head model runs on the tensor cores unless the engine was created with the fp32
+// (CUDA-core) precision or SGNN_HIST_TC=0
+bool hist_tc_enabled(SgnnHandle h) {
+  static const bool off = [] { const char* e = getenv("SGNN_HIST_TC"); return e && e[0] == '0'; }();
+  return !off && h->M.n_head > 0 && h->M.hist_bins >= 1 && h->M.hist_bins <= HT_MAX_BINS && h->M.node_dim <= 32 &&
+         h->cfg.precision != SGNN_PREC_FP32;
+}
+
 int ensure_query_tables(SgnnHandle h, int64_t m) {
   if (m <= h->cap_P) return 0;
   return fail(h, "query table workspace too small: call sgnn_reserve(max_queries >= m) first");
@@ -406,19 +416,43 @@ int score_all_pairs_stages(SgnnHandle h, const float* emb_q, int32_t m, const fl
   if (ensure_query_tables(h, m)) return 1;
   const ModelDev& M = h->M;
   const int K = M.pair_kind == SGNN_LAYER_NTN ? M.K : 1;
-  if (M.n_head > 0) {   // SimGNN-style head: CUDA-core kernel (sgnn_head.cu), fp32 whatever cfg.precision says
-    if (stages & SCORE_PREP_Q) {
-      allpairs_prep_kernel<<<(m + 3) / 4, 128, 0, st>>>(M, h->d_params, emb_q, m, h->dep, h->d_P, h->d_C);
-      CUDA_OK(h, cudaGetLastError());
-    }
-    if (!(stages & SCORE_MAIN)) return 0;
+  if (M.n_head > 0) {   // SimGNN-style head
     if (M.hist_bins > 0 && (!h->hside[0].rows || !h->hside[1].rows))
       return fail(h, "the model has a Histogram layer: all-pairs scoring needs the node rows of both sides "
                      "(sgnn_score_all_pairs_nodes, or the sgnn_rank_* entry points)");
-    const cudaError_t e = sgnn_launch_allpairs_head(M, h->dep, h->d_params, h->d_P, h->d_C, emb_db, h->hside[0].rows,
-                                                    h->hside[0].node_off, h->hside[0].max_nodes, h->hside[1].rows,
-                                                    h->hside[1].node_off, h->hside[1].max_nodes, m, n, sim_dev, ld,
-                                                    h->sm_count, h->smem_optin, st);
+    // histogram on the tensor cores (sgnn_hist_tc.cuh) whenever the shapes fit; else the CUDA-core kernel counts
+    const bool tc_hist = hist_tc_enabled(h) &&
+                         sgnn_hist_tc_supported(M.node_dim, M.hist_bins, h->hside[0].max_nodes, h->hside[1].max_nodes);
+    HistTcGeom HG;
+    if (tc_hist) {
+      const HistTcWs& t = h->ht;
+      HG.m = m; HG.n = n; HG.d = M.node_dim; HG.ksteps = t.ksteps; HG.parts = t.parts; HG.bins = M.hist_bins;
+      HG.S = 129 - h->hside[1].max_nodes;
+      HG.max_btiles = (int)std::min<int64_t>(t.cap_b_tiles, ht_max_btiles(m));
+      HG.max_atiles = (int)std::min<int64_t>(t.cap_a_tiles, (int64_t)n * h->hside[1].max_nodes / HG.S + 1);
+      if (m > t.cap_q || ht_max_btiles(m) > t.cap_b_tiles || (int64_t)m * n * HT_CNT_BYTES > t.cap_cnt || t.cap_a_tiles == 0)
+        return fail(h, "histogram workspace too small: call sgnn_reserve(max_nodes >= total_nodes, max_queries, max_db) first");
+    }
+    if (stages & SCORE_PREP_Q) {
+      allpairs_prep_kernel<<<(m + 3) / 4, 128, 0, st>>>(M, h->d_params, emb_q, m, h->dep, h->d_P, h->d_C);
+      CUDA_OK(h, cudaGetLastError());
+      if (tc_hist) CUDA_OK(h, sgnn_hist_tc_prep_q(HG, h->hside[0].rows, h->hside[0].node_off, h->ht, st));
+    }
+    if ((stages & SCORE_PREP_DB) && tc_hist)
+      CUDA_OK(h, sgnn_hist_tc_prep_db(HG, h->hside[1].rows, h->hside[1].node_off, h->ht, st));
+    if (!(stages & SCORE_MAIN)) return 0;
+    cudaError_t e;
+    if (tc_hist) {
+      CUDA_OK(h, sgnn_hist_tc_run(HG, h->ht, h->hside[1].node_off, h->sm_count, st));
+      e = sgnn_launch_allpairs_head_counts(M, h->dep, h->d_params, h->d_P, h->d_C, emb_db, h->hside[0].node_off,
+                                           h->hside[1].node_off, h->ht.cnt, m, n, sim_dev, ld, h->sm_count,
+                                           h->smem_optin, st);
+    } else {
+      e = sgnn_launch_allpairs_head(M, h->dep, h->d_params, h->d_P, h->d_C, emb_db, h->hside[0].rows,
+                                    h->hside[0].node_off, h->hside[0].max_nodes, h->hside[1].rows,
+                                    h->hside[1].node_off, h->hside[1].max_nodes, m, n, sim_dev, ld,
+                                    h->sm_count, h->smem_optin, st);
+    }
     if (e == cudaErrorInvalidValue)
       return fail(h, "all-pairs head kernel: unsupported shape (head widths and node_dim must be <= 32, embedding <= 32, "
                      "and one graph's node rows must fit shared memory)");
@@ -637,6 +671,8 @@ int sgnn_destroy(SgnnHandle h) {
   cudaFree(h->d_params); cudaFree(h->d_grads); cudaFree(h->d_m); cudaFree(h->d_v); cudaFree(h->d_loss);
   cudaFree(h->d_coef); cudaFree(h->d_P); cudaFree(h->d_C); cudaFree(h->d_Atc); cudaFree(h->d_Btc); cudaFree(h->d_smax);
   cudaFree(h->d_rowsA); cudaFree(h->d_rowsB); cudaFree(h->d_hnodes[0]); cudaFree(h->d_hnodes[1]);
+  cudaFree(h->ht.At); cudaFree(h->ht.Bt); cudaFree(h->ht.qmeta); cudaFree(h->ht.ameta); cudaFree(h->ht.status);
+  cudaFree(h->ht.cnt);
   HostWs& w = h->ws;
   for (int s = 0; s < 2; ++s) {
     cudaFree(w.node_off[s]); cudaFree(w.labels[s]); cudaFree(w.rowptr[s]); cudaFree(w.col[s]); cudaFree(w.val[s]);
@@ -746,6 +782,34 @@ int sgnn_reserve(SgnnHandle h, int64_t max_graphs, int64_t max_nodes, int64_t ma
     const int64_t fl = max_nodes * (int64_t)h->M.node_dim;
     if (dev_alloc(h, &h->d_hnodes[0], fl) || dev_alloc(h, &h->d_hnodes[1], fl)) return 1;
     h->cap_hnodes = max_nodes;
+  }
+  if (hist_tc_enabled(h)) {   // tensor-core histogram: operand tiles of both sides, tile tables, count matrix
+    HistTcWs& t = h->ht;
+    t.parts = h->cfg.precision == SGNN_PREC_BF16 ? 1 : 3;
+    t.ksteps = (h->M.node_dim + 15) / 16;
+    const int64_t tile = (int64_t)t.parts * t.ksteps * 4096;
+    const int64_t at = max_nodes > 0 ? ht_max_atiles(max_nodes) : 0, bt = max_queries > 0 ? ht_max_btiles(max_queries) : 0;
+    uint8_t* p8 = nullptr;
+    if (at > t.cap_a_tiles) {
+      p8 = static_cast<uint8_t*>(t.At); if (dev_alloc(h, &p8, at * tile)) return 1; t.At = p8;
+      if (dev_alloc(h, &t.ameta, at + 1)) return 1;
+      t.cap_a_tiles = at;
+    }
+    if (bt > t.cap_b_tiles || max_queries > t.cap_q) {
+      t.cap_b_tiles = std::max(t.cap_b_tiles, bt);
+      t.cap_q = std::max(t.cap_q, max_queries);
+      p8 = static_cast<uint8_t*>(t.Bt); if (dev_alloc(h, &p8, t.cap_b_tiles * tile)) return 1; t.Bt = p8;
+      if (dev_alloc(h, &t.qmeta, (int64_t)ht_qmeta_ints((int)t.cap_q, (int)t.cap_b_tiles))) return 1;
+    }
+    if (!t.status) {
+      if (dev_alloc(h, &t.status, 4)) return 1;
+      CUDA_OK(h, cudaMemset(t.status, 0, 16));
+    }
+    const int64_t need_cnt = max_queries * max_db * HT_CNT_BYTES;
+    if (need_cnt > t.cap_cnt) {
+      if (dev_alloc(h, &t.cnt, need_cnt)) return 1;
+      t.cap_cnt = need_cnt;
+    }
   }
   if (max_pairs > w.cap_pairs) {
     w.cap_pairs = max_pairs;
@@ -910,6 +974,36 @@ int sgnn_score_all_pairs_nodes(SgnnHandle h, const float* emb_q, const float* no
   h->hside[0].rows = nodes_q; h->hside[0].node_off = node_off_q; h->hside[0].max_nodes = max_nodes_q;
   h->hside[1].rows = nodes_db; h->hside[1].node_off = node_off_db; h->hside[1].max_nodes = max_nodes_db;
   return score_all_pairs_stages(h, emb_q, m, emb_db, n, sim_dev, ld, (cudaStream_t)stream, SCORE_ALL);
+}
+
+int sgnn_hist_all_pairs(SgnnHandle h, const float* nodes_q, const int32_t* node_off_q, int32_t max_nodes_q, int32_t m,
+                        const float* nodes_db, const int32_t* node_off_db, int32_t max_nodes_db, int32_t n,
+                        uint8_t* counts_dev, int32_t stages, void* stream) {
+  if (!h || !nodes_q || !node_off_q || !nodes_db || !node_off_db) return fail(h, "sgnn_hist_all_pairs: null argument");
+  if (stages < 1 || stages > SGNN_STAGE_ALL) return fail(h, "sgnn_hist_all_pairs: bad stage mask");
+  const ModelDev& M = h->M;
+  if (!hist_tc_enabled(h)) return fail(h, "sgnn_hist_all_pairs: needs a Histogram model (bins <= 16) and a tensor-core precision");
+  if (m == 0 || n == 0) return 0;
+  if (!sgnn_hist_tc_supported(M.node_dim, M.hist_bins, max_nodes_q, max_nodes_db)) {
+    fail(h, "sgnn_hist_all_pairs: graph sizes outside the tensor-core histogram (queries <= 15 nodes, database <= 64, product <= 255)");
+    return 4;
+  }
+  const HistTcWs& t = h->ht;
+  HistTcGeom HG;
+  HG.m = m; HG.n = n; HG.d = M.node_dim; HG.ksteps = t.ksteps; HG.parts = t.parts; HG.bins = M.hist_bins;
+  HG.S = 129 - max_nodes_db;
+  HG.max_btiles = (int)std::min<int64_t>(t.cap_b_tiles, ht_max_btiles(m));
+  HG.max_atiles = (int)std::min<int64_t>(t.cap_a_tiles, (int64_t)n * max_nodes_db / HG.S + 1);
+  if (m > t.cap_q || ht_max_btiles(m) > t.cap_b_tiles || t.cap_a_tiles == 0 ||
+      (!counts_dev && (int64_t)m * n * HT_CNT_BYTES > t.cap_cnt))
+    return fail(h, "histogram workspace too small: call sgnn_reserve(max_nodes >= total_nodes, max_queries, max_db) first");
+  cudaStream_t st = (cudaStream_t)stream;
+  HistTcWs w = t;
+  if (counts_dev) w.cnt = counts_dev;
+  if (stages & SGNN_STAGE_PREP_QUERIES) CUDA_OK(h, sgnn_hist_tc_prep_q(HG, nodes_q, node_off_q, w, st));
+  if (stages & SGNN_STAGE_PREP_DATABASE) CUDA_OK(h, sgnn_hist_tc_prep_db(HG, nodes_db, node_off_db, w, st));
+  if (stages & SGNN_STAGE_SCORE) CUDA_OK(h, sgnn_hist_tc_run(HG, w, node_off_db, h->sm_count, st));
+  return 0;
 }
 
 #define LAUNCH_OK(h, what, expr)                                                              \

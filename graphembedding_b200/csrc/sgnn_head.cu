@@ -112,14 +112,16 @@ struct BinCounters {
   }
 };
 
-template <int DEP, int H0, int ND, int NB>
+// PRE: the bin counts of every pair were computed beforehand (tensor-core histogram, sgnn_hist_tc.cuh) and are read
+// from cnt_in [m][n][16 bytes]; the node rows are then not staged and the cell loop is skipped.
+template <int DEP, int H0, int ND, int NB, bool PRE>
 __global__ void __launch_bounds__(256)
 allpairs_head_kernel(const __grid_constant__ ModelDev M, const __grid_constant__ HeadPlan HP,
                      const float* __restrict__ params, const float* __restrict__ Pq, const float* __restrict__ Cq,
                      const float* __restrict__ emb_db, const float* __restrict__ nodes_q,
                      const int32_t* __restrict__ node_off_q, const float* __restrict__ nodes_db,
                      const int32_t* __restrict__ node_off_db, int m, int n, int q_per_block,
-                     float* __restrict__ sim, int64_t ld) {
+                     float* __restrict__ sim, int64_t ld, const uint8_t* __restrict__ cnt_in) {
   extern __shared__ __align__(16) float smem[];
   const int NT = blockDim.x, tid = threadIdx.x, T = HP.T;
   const int gl = tid % T, ql = tid / T;   // graph lane, query lane (uniform per warp: T is a multiple of 32)
@@ -158,7 +160,7 @@ allpairs_head_kernel(const __grid_constant__ ModelDev M, const __grid_constant__
 #pragma unroll
   for (int b = 0; b < DEP; ++b) x[b] = (g < n && b < D) ? emb_db[(size_t)g * D + b] : 0.f;
   const int n_g = (g < n && bins > 0) ? node_off_db[g + 1] - node_off_db[g] : 0;
-  if (bins > 0) {
+  if (bins > 0 && !PRE) {
     const int lane = tid & 31, warp = tid >> 5, nw = NT >> 5;
     for (int gi = warp; gi < T && g0 + gi < n; gi += nw) {
       const int base = node_off_db[g0 + gi];
@@ -192,10 +194,11 @@ allpairs_head_kernel(const __grid_constant__ ModelDev M, const __grid_constant__
       if (bins > 0) {
         const int base = node_off_q[q0 + qi];
         const int cnt = node_off_q[q0 + qi + 1] - base;
-        for (int idx = tid; idx < (cnt + 1) * ND; idx += NT) {
-          const int r = idx / ND, c = idx - r * ND;
-          sr[idx] = (r < cnt && c < d) ? nodes_q[(size_t)(base + r) * d + c] : 0.f;
-        }
+        if (!PRE)
+          for (int idx = tid; idx < (cnt + 1) * ND; idx += NT) {
+            const int r = idx / ND, c = idx - r * ND;
+            sr[idx] = (r < cnt && c < d) ? nodes_q[(size_t)(base + r) * d + c] : 0.f;
+          }
         if (tid == 0) reinterpret_cast<int*>(sr + (HP.nmax_q + 1) * ND)[0] = cnt;
       }
     }
@@ -233,8 +236,30 @@ allpairs_head_kernel(const __grid_constant__ ModelDev M, const __grid_constant__
           acc[4 * j + 3] = fmaf(f, w.w, acc[4 * j + 3]);
         }
       }
-      // ---- node-node similarity histogram: 2 x 2 blocks of cells = four independent chains ----
-      if (bins > 0) {
+      // ---- node-node similarity histogram ----
+      if (PRE && bins > 0) {
+        const uint4 cw = *reinterpret_cast<const uint4*>(cnt_in + ((size_t)(q0 + qi) * n + g) * 16);
+        const int cells = n_q * n_g;
+        const float inv_cells = cells > 0 ? 1.f / (float)cells : 0.f;
+#pragma unroll
+        for (int b = 0; b < 16; ++b) {
+          if (b < bins) {
+            const unsigned wv = (b >> 2) == 0 ? cw.x : ((b >> 2) == 1 ? cw.y : ((b >> 2) == 2 ? cw.z : cw.w));
+            const float hb = (float)((wv >> ((b & 3) * 8)) & 0xFFu) * inv_cells;
+            const float4* w4 = reinterpret_cast<const float4*>(s_hw + HP.w0 + (K + b) * H0);
+#pragma unroll
+            for (int j = 0; j < H0 / 4; ++j) {
+              const float4 w = w4[j];
+              acc[4 * j + 0] = fmaf(hb, w.x, acc[4 * j + 0]);
+              acc[4 * j + 1] = fmaf(hb, w.y, acc[4 * j + 1]);
+              acc[4 * j + 2] = fmaf(hb, w.z, acc[4 * j + 2]);
+              acc[4 * j + 3] = fmaf(hb, w.w, acc[4 * j + 3]);
+            }
+          }
+        }
+      }
+      // 2 x 2 blocks of cells = four independent chains
+      if (!PRE && bins > 0) {
         BinCounters<NB> bc;
         bc.reset();
         const float fb = (float)bins;
@@ -293,6 +318,7 @@ allpairs_head_kernel(const __grid_constant__ ModelDev M, const __grid_constant__
             }
           }
         }
+      
       }
       // ---- rest of the head ----
       {
@@ -446,19 +472,21 @@ cudaError_t sgnn_launch_pair_histogram_tiled(const float* node_emb, int d, const
   return cudaGetLastError();
 }
 
-template <int DEP, int H0, int ND, int NB>
+template <int DEP, int H0, int ND, int NB, bool PRE = false>
 static cudaError_t launch_head(const ModelDev& M, const float* params, const float* Pq, const float* Cq,
                                const float* emb_db, const float* nodes_q, const int32_t* node_off_q, int max_nodes_q,
                                const float* nodes_db, const int32_t* node_off_db, int max_nodes_db, int m, int n,
-                               float* sim, int64_t ld, int sm_count, int smem_optin, cudaStream_t st) {
+                               float* sim, int64_t ld, int sm_count, int smem_optin, cudaStream_t st,
+                               const uint8_t* cnt_in = nullptr) {
   HeadPlan P;
   head_plan_weights<H0>(M, P);
   const bool hist = M.hist_bins > 0;
   P.nmax_q = hist ? std::max(1, max_nodes_q) : 0;
+  if (PRE) P.nmax_q = 0;   // node rows are not staged: the record keeps only the node count behind one padding row
   P.q_floats = M.K * DEP + round_up4(M.K) + (hist ? (P.nmax_q + 1) * ND + 4 : 0);
-  const int rows = hist ? std::max(1, max_nodes_db) * ND : 0;
-  P.S = hist ? (rows + 7) / 8 * 8 + 4 : 0;   // 4 * odd words: conflict-free 16-byte reads across a warp
-  const bool can_spill = hist && (int64_t)max_nodes_q * max_nodes_db > 240;   // BinCounters byte fields hold 255
+  const int rows = (hist && !PRE) ? std::max(1, max_nodes_db) * ND : 0;
+  P.S = (hist && !PRE) ? (rows + 7) / 8 * 8 + 4 : 0;   // 4 * odd words: conflict-free 16-byte reads across a warp
+  const bool can_spill = hist && !PRE && (int64_t)max_nodes_q * max_nodes_db > 240;   // BinCounters byte fields hold 255
   auto bytes_for = [&](int t) {
     return ((size_t)P.hw_floats + (size_t)HEAD_QC * P.q_floats + (size_t)t * P.S + ND +
             (can_spill ? (size_t)M.hist_bins * 2 * t : 0)) * sizeof(float);
@@ -475,7 +503,7 @@ static cudaError_t launch_head(const ModelDev& M, const float* params, const flo
   if (!T) return cudaErrorInvalidValue;
   P.T = T;
   const size_t smem = bytes_for(T);
-  auto kern = allpairs_head_kernel<DEP, H0, ND, NB>;
+  auto kern = allpairs_head_kernel<DEP, H0, ND, NB, PRE>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   const int gx = (n + T - 1) / T;
@@ -485,8 +513,26 @@ static cudaError_t launch_head(const ModelDev& M, const float* params, const flo
   const int qpb = ((m + gy - 1) / gy + HEAD_QC - 1) / HEAD_QC * HEAD_QC;
   gy = (m + qpb - 1) / qpb;
   kern<<<dim3(gx, gy), 2 * T, smem, st>>>(M, P, params, Pq, Cq, emb_db, nodes_q, node_off_q, nodes_db, node_off_db,
-                                          m, n, qpb, sim, ld);
+                                          m, n, qpb, sim, ld, cnt_in);
   return cudaGetLastError();
+}
+
+cudaError_t sgnn_launch_allpairs_head_counts(const ModelDev& M, int DEP, const float* params, const float* Pq,
+                                             const float* Cq, const float* emb_db, const int32_t* node_off_q,
+                                             const int32_t* node_off_db, const uint8_t* cnt_in, int m, int n,
+                                             float* sim, int64_t ld, int sm_count, int smem_optin, cudaStream_t st) {
+  if (M.n_head < 1 || M.hist_bins < 1 || M.hist_bins > 16) return cudaErrorInvalidValue;
+  int hmax = 0;
+  for (int l = 0; l < M.n_head; ++l) {
+    hmax = std::max(hmax, M.Hd[l].dout);
+    if (l > 0) hmax = std::max(hmax, M.Hd[l].din);
+  }
+  if (hmax > 32 || (DEP != 16 && DEP != 32)) return cudaErrorInvalidValue;
+#define SGNN_HEADC_ARGS M, params, Pq, Cq, emb_db, nullptr, node_off_q, 0, nullptr, node_off_db, 0, m, n, sim, ld, \
+                        sm_count, smem_optin, st, cnt_in
+  if (DEP == 16) return hmax <= 16 ? launch_head<16, 16, 16, 16, true>(SGNN_HEADC_ARGS) : launch_head<16, 32, 16, 16, true>(SGNN_HEADC_ARGS);
+  return hmax <= 16 ? launch_head<32, 16, 16, 16, true>(SGNN_HEADC_ARGS) : launch_head<32, 32, 16, 16, true>(SGNN_HEADC_ARGS);
+#undef SGNN_HEADC_ARGS
 }
 
 cudaError_t sgnn_launch_allpairs_head(const ModelDev& M, int DEP, const float* params, const float* Pq, const float* Cq,

@@ -59,6 +59,11 @@ cudaError_t sgnn_launch_allpairs_head(const ModelDev& M, int DEP, const float* p
                                       int max_nodes_q, const float* nodes_db, const int32_t* node_off_db,
                                       int max_nodes_db, int m, int n, float* sim, int64_t ld, int sm_count,
                                       int smem_optin, cudaStream_t st);
+// same head, bin counts of every pair precomputed by the tensor-core histogram (sgnn_hist_tc_geom.h): cnt_in [m][n][16]
+cudaError_t sgnn_launch_allpairs_head_counts(const ModelDev& M, int DEP, const float* params, const float* Pq,
+                                             const float* Cq, const float* emb_db, const int32_t* node_off_q,
+                                             const int32_t* node_off_db, const uint8_t* cnt_in, int m, int n,
+                                             float* sim, int64_t ld, int sm_count, int smem_optin, cudaStream_t st);
 // register-blocked histogram of listed pairs (sgnn_head.cu); cudaErrorInvalidValue when node_dim > 32
 cudaError_t sgnn_launch_pair_histogram_tiled(const float* node_emb, int d, const int32_t* node_off, const int32_t* g1,
                                              const int32_t* g2, int n_pairs, int bins, float* hist, int32_t* counts,

@@ -33,6 +33,7 @@ class SgnnEngine(object):
         self.precision = 'fp32' if self.cfg.precision == 0 else 'tc'   # SGNN_PREC_FP32 / tensor-core scorer
         self.n_params = int(lib().sgnn_param_count(h))
         self.emb_dim = int(lib().sgnn_embed_dim(h))
+        self.node_dim = int(lib().sgnn_node_dim(h))
         self.launches = 0  # kernels launched through this object (bench.py's gpu_launches)
 
     def close(self):
@@ -163,6 +164,23 @@ class SgnnEngine(object):
             _ptr(rows_db), _ptr(batch_db.node_off), batch_db.max_nodes, n, _ptr(out), out.stride(0),
             _stream_ptr(stream)))
         self.launches += 2
+        return out
+
+    def hist_all_pairs(self, rows_q, batch_q, rows_db, batch_db, out=None, stages=7, stream=None):
+        """Bin counts [m, n, 16] (uint8) of the Histogram layer for every (query, database) pair: one tensor-core
+        GEMM with a binning epilogue (sgnn_hist_all_pairs).  Raises ValueError when the graph sizes are outside
+        that kernel (use pair_histogram)."""
+        import torch
+        m, n = batch_q.n_graphs, batch_db.n_graphs
+        if out is None:
+            out = torch.zeros((m, n, 16), dtype=torch.uint8, device=self.device)
+        rc = lib().sgnn_hist_all_pairs(self.h, _ptr(rows_q), _ptr(batch_q.node_off), batch_q.max_nodes, m,
+                                       _ptr(rows_db), _ptr(batch_db.node_off), batch_db.max_nodes, n, _ptr(out),
+                                       int(stages), _stream_ptr(stream))
+        if rc == 4:
+            raise ValueError(lib().sgnn_last_error(self.h).decode())
+        check(self.h, rc)
+        self.launches += {1: 2, 2: 1, 4: 1}.get(int(stages), 4)
         return out
 
     def score_all_pairs(self, emb_q, emb_db, out=None, stream=None):

@@ -70,6 +70,7 @@ SIGNATURES = {
     'sgnn_node_embeddings': (C.c_int, [_P, _BP, _P, _P]),
     'sgnn_embed_graphs_nodes': (C.c_int, [_P, _BP, _P, _P, _P]),
     'sgnn_score_all_pairs_nodes': (C.c_int, [_P, _P, _P, _P, _I32, _I32, _P, _P, _P, _I32, _I32, _P, _I64, _P]),
+    'sgnn_hist_all_pairs': (C.c_int, [_P, _P, _P, _I32, _I32, _P, _P, _I32, _I32, _P, _I32, _P]),
     'sgnn_pair_histogram': (C.c_int, [_P, _P, _P, _P, _P, _I32, _I32, _P, _P, _P]),
     'sgnn_score_pairs': (C.c_int, [_P, _P, _P, _P, _I32, _P, _P, _P]),
     'sgnn_forward_pairs': (C.c_int, [_P, _BP, _P, _P, _I32, _P, _P, _P, _P]),

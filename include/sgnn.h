@@ -190,6 +190,16 @@ int sgnn_score_all_pairs_nodes(SgnnHandle h, const float* emb_q_dev, const float
                                const int32_t* node_off_q_dev, int32_t max_nodes_q, int32_t m, const float* emb_db_dev,
                                const float* nodes_db_dev, const int32_t* node_off_db_dev, int32_t max_nodes_db,
                                int32_t n, float* sim_dev, int64_t ld, void* stream);
+/* The Histogram layer of every (query, database) pair as ONE tensor-core GEMM with a binning epilogue
+ * (csrc/sgnn_hist_tc.cuh; semantics of sgnn_pair_histogram, build-defined): counts_dev
+ * [m][n][16] bytes, byte b = number of node-node cells of pair (i, j) in bin b (bytes >= bins are 0).
+ * Needs bins <= 16, node width <= 32, max_nodes_q <= 15, max_nodes_db <= 64, max_nodes_q * max_nodes_db <= 255
+ * (return code 4 otherwise: use sgnn_pair_histogram) and an engine created with a tensor-core precision;
+ * workspace: sgnn_reserve(max_nodes >= database node rows, max_queries >= m, max_db >= n).  counts_dev may be
+ * NULL (the internal count matrix that sgnn_score_all_pairs_nodes reads is filled).  stages: SGNN_STAGE_* flags. */
+int sgnn_hist_all_pairs(SgnnHandle h, const float* nodes_q_dev, const int32_t* node_off_q_dev, int32_t max_nodes_q,
+                        int32_t m, const float* nodes_db_dev, const int32_t* node_off_db_dev, int32_t max_nodes_db,
+                        int32_t n, uint8_t* counts_dev, int32_t stages, void* stream);
 /* descending top-k per row with the reference's tie order (results.py:221-224: stable
  * ascending mergesort reversed => equal scores come out higher index first). */
 int sgnn_topk(SgnnHandle h, const float* sim_dev, int32_t m, int32_t n, int64_t ld, int32_t k,

@@ -88,7 +88,7 @@ struct SgnnHandle_t {
   // histogram head: last node-level rows of the query / database side of the ranking entry points
   float* d_hnodes[2] = {nullptr, nullptr};
   int64_t cap_hnodes = 0;                         // in node rows, each side
-  struct NodeSide { const float* rows; const int32_t* node_off; int max_nodes; } hside[2] = {};
+  struct NodeSide { const float* rows; const int32_t* node_off; int max_nodes; int64_t total_rows; } hside[2] = {};   // total_rows < 0: unknown
   float* d_coef = nullptr;               // tensor-core scorer: query-side coefficient matrix (tc_coef_kernel)
   float *d_P = nullptr, *d_C = nullptr;  // all-pairs query tables
   int64_t cap_P = 0;
@@ -417,28 +417,39 @@ int score_all_pairs_stages(SgnnHandle h, const float* emb_q, int32_t m, const fl
   const ModelDev& M = h->M;
   const int K = M.pair_kind == SGNN_LAYER_NTN ? M.K : 1;
   if (M.n_head > 0) {   // SimGNN-style head
-    if (M.hist_bins > 0 && (!h->hside[0].rows || !h->hside[1].rows))
+    // each stage needs the node rows of ITS side (the ranking entry points prepare the query side before the
+    // database has been embedded)
+    const bool need_q = M.hist_bins > 0 && (stages & (SCORE_PREP_Q | SCORE_MAIN));
+    const bool need_db = M.hist_bins > 0 && (stages & (SCORE_PREP_DB | SCORE_MAIN));
+    if ((need_q && !h->hside[0].rows) || (need_db && !h->hside[1].rows))
       return fail(h, "the model has a Histogram layer: all-pairs scoring needs the node rows of both sides "
                      "(sgnn_score_all_pairs_nodes, or the sgnn_rank_* entry points)");
-    // histogram on the tensor cores (sgnn_hist_tc.cuh) whenever the shapes fit; else the CUDA-core kernel counts
-    const bool tc_hist = hist_tc_enabled(h) &&
+    // histogram on the tensor cores (sgnn_hist_tc.cuh) whenever the shapes fit, else the CUDA-core kernel counts.
+    // A side's operand is prepared whenever THAT side fits (the other side may not be known yet); the scorer stage
+    // decides with both.
+    const bool tc_on = hist_tc_enabled(h);
+    const bool tc_q = tc_on && need_q && sgnn_hist_tc_supported(M.node_dim, M.hist_bins, h->hside[0].max_nodes, 1);
+    const bool tc_db = tc_on && need_db && sgnn_hist_tc_supported(M.node_dim, M.hist_bins, 1, h->hside[1].max_nodes);
+    const bool tc_hist = tc_q && tc_db &&
                          sgnn_hist_tc_supported(M.node_dim, M.hist_bins, h->hside[0].max_nodes, h->hside[1].max_nodes);
     HistTcGeom HG;
-    if (tc_hist) {
+    if (tc_q || tc_db) {
       const HistTcWs& t = h->ht;
+      const int mx_db = tc_db ? h->hside[1].max_nodes : 1;
       HG.m = m; HG.n = n; HG.d = M.node_dim; HG.ksteps = t.ksteps; HG.parts = t.parts; HG.bins = M.hist_bins;
-      HG.S = 129 - h->hside[1].max_nodes;
+      HG.S = 129 - mx_db;
       HG.max_btiles = (int)std::min<int64_t>(t.cap_b_tiles, ht_max_btiles(m));
-      HG.max_atiles = (int)std::min<int64_t>(t.cap_a_tiles, (int64_t)n * h->hside[1].max_nodes / HG.S + 1);
-      if (m > t.cap_q || ht_max_btiles(m) > t.cap_b_tiles || (int64_t)m * n * HT_CNT_BYTES > t.cap_cnt || t.cap_a_tiles == 0)
+      HG.max_atiles = (int)std::min<int64_t>(t.cap_a_tiles, (int64_t)n * mx_db / HG.S + 1);
+      if (m > t.cap_q || ht_max_btiles(m) > t.cap_b_tiles || (int64_t)m * n * HT_CNT_BYTES > t.cap_cnt || t.cap_a_tiles == 0 ||
+          (tc_db && (h->hside[1].total_rows >= 0 ? h->hside[1].total_rows : (int64_t)n * mx_db) / HG.S + 1 > t.cap_a_tiles))
         return fail(h, "histogram workspace too small: call sgnn_reserve(max_nodes >= total_nodes, max_queries, max_db) first");
     }
     if (stages & SCORE_PREP_Q) {
       allpairs_prep_kernel<<<(m + 3) / 4, 128, 0, st>>>(M, h->d_params, emb_q, m, h->dep, h->d_P, h->d_C);
       CUDA_OK(h, cudaGetLastError());
-      if (tc_hist) CUDA_OK(h, sgnn_hist_tc_prep_q(HG, h->hside[0].rows, h->hside[0].node_off, h->ht, st));
+      if (tc_q) CUDA_OK(h, sgnn_hist_tc_prep_q(HG, h->hside[0].rows, h->hside[0].node_off, h->ht, st));
     }
-    if ((stages & SCORE_PREP_DB) && tc_hist)
+    if ((stages & SCORE_PREP_DB) && tc_db)
       CUDA_OK(h, sgnn_hist_tc_prep_db(HG, h->hside[1].rows, h->hside[1].node_off, h->ht, st));
     if (!(stages & SCORE_MAIN)) return 0;
     cudaError_t e;
@@ -598,6 +609,7 @@ int embed_side(SgnnHandle h, const SgnnGraphBatch* b, float* emb_dev, int side, 
   h->hside[side].rows = h->d_hnodes[side];
   h->hside[side].node_off = b->node_off;
   h->hside[side].max_nodes = b->max_nodes;
+  h->hside[side].total_rows = b->total_nodes;
   return 0;
 }
 }  // namespace
@@ -973,6 +985,7 @@ int sgnn_score_all_pairs_nodes(SgnnHandle h, const float* emb_q, const float* no
     return fail(h, "sgnn_score_all_pairs_nodes: null argument");
   h->hside[0].rows = nodes_q; h->hside[0].node_off = node_off_q; h->hside[0].max_nodes = max_nodes_q;
   h->hside[1].rows = nodes_db; h->hside[1].node_off = node_off_db; h->hside[1].max_nodes = max_nodes_db;
+  h->hside[0].total_rows = h->hside[1].total_rows = -1;
   return score_all_pairs_stages(h, emb_q, m, emb_db, n, sim_dev, ld, (cudaStream_t)stream, SCORE_ALL);
 }
 
@@ -998,6 +1011,19 @@ int sgnn_hist_all_pairs(SgnnHandle h, const float* nodes_q, const int32_t* node_
       (!counts_dev && (int64_t)m * n * HT_CNT_BYTES > t.cap_cnt))
     return fail(h, "histogram workspace too small: call sgnn_reserve(max_nodes >= total_nodes, max_queries, max_db) first");
   cudaStream_t st = (cudaStream_t)stream;
+  if ((stages & SGNN_STAGE_PREP_DATABASE) && (int64_t)n * max_nodes_db / HG.S + 1 > t.cap_a_tiles) {
+    // the size-based bound does not fit the reserved tiles: look at the actual number of node rows (one 4-byte read;
+    // callers that cannot synchronise reserve max_nodes >= n * max_nodes_db)
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(st, &cs);
+    if (cs != cudaStreamCaptureStatusNone)
+      return fail(h, "histogram workspace too small for n * max_nodes_db node rows (checked conservatively under stream capture)");
+    int32_t total = 0;
+    CUDA_OK(h, cudaMemcpyAsync(&total, node_off_db + n, sizeof(total), cudaMemcpyDeviceToHost, st));
+    CUDA_OK(h, cudaStreamSynchronize(st));
+    if ((int64_t)total / HG.S + 1 > t.cap_a_tiles)
+      return fail(h, "histogram workspace too small: call sgnn_reserve(max_nodes >= database node rows) first");
+  }
   HistTcWs w = t;
   if (counts_dev) w.cnt = counts_dev;
   if (stages & SGNN_STAGE_PREP_QUERIES) CUDA_OK(h, sgnn_hist_tc_prep_q(HG, nodes_q, node_off_q, w, st));

@@ -486,7 +486,8 @@ static cudaError_t launch_head(const ModelDev& M, const float* params, const flo
   P.q_floats = M.K * DEP + round_up4(M.K) + (hist ? (P.nmax_q + 1) * ND + 4 : 0);
   const int rows = (hist && !PRE) ? std::max(1, max_nodes_db) * ND : 0;
   P.S = (hist && !PRE) ? (rows + 7) / 8 * 8 + 4 : 0;   // 4 * odd words: conflict-free 16-byte reads across a warp
-  const bool can_spill = hist && !PRE && (int64_t)max_nodes_q * max_nodes_db > 240;   // BinCounters byte fields hold 255
+  // (the 2 x 2 cell blocks tick the counters for the padded cells of odd node counts too: 15 x 15 graphs tick 256 times)
+  const bool can_spill = hist && !PRE && (int64_t)((max_nodes_q + 1) & ~1) * ((max_nodes_db + 1) & ~1) > 240;   // BinCounters byte fields hold 255
   auto bytes_for = [&](int t) {
     return ((size_t)P.hw_floats + (size_t)HEAD_QC * P.q_floats + (size_t)t * P.S + ND +
             (can_spill ? (size_t)M.hist_bins * 2 * t : 0)) * sizeof(float);

@@ -43,7 +43,8 @@ def _side(sizes, d, rng, scale, device):
 def _oracle_counts(rows_q, off_q, rows_db, off_db, bins):
     """(counts [m][n][bins], margin [m][n]) from the fp64 restatement of the layer (oracle pair_histogram)."""
     m, n = len(off_q) - 1, len(off_db) - 1
-    s = 1.0 / (1.0 + np.exp(-(rows_q.astype(np.float64) @ rows_db.astype(np.float64).T)))
+    with np.errstate(over='ignore'):          # exp overflows to inf for very negative scores: sigmoid = 0, as intended
+        s = 1.0 / (1.0 + np.exp(-(rows_q.astype(np.float64) @ rows_db.astype(np.float64).T)))
     idx = np.minimum(bins - 1, np.floor(s * bins).astype(np.int64))
     mar = np.abs(s * bins - np.clip(np.round(s * bins), 1, bins - 1)) / bins     # distance to the nearest INTERIOR edge
     counts = np.zeros((m, n, bins), np.int64)

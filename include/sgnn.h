@@ -200,6 +200,21 @@ int sgnn_score_all_pairs_nodes(SgnnHandle h, const float* emb_q_dev, const float
 int sgnn_hist_all_pairs(SgnnHandle h, const float* nodes_q_dev, const int32_t* node_off_q_dev, int32_t max_nodes_q,
                         int32_t m, const float* nodes_db_dev, const int32_t* node_off_db_dev, int32_t max_nodes_db,
                         int32_t n, uint8_t* counts_dev, int32_t stages, void* stream);
+/* sgnn_hist_all_pairs WITHOUT any allocation and without a handle.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight
+ * serving loops, harnesses that forbid it).  Same kernels and the same counts as sgnn_hist_all_pairs on a bf16x3
+ * engine; the scratch (operand tiles of both sides, tile tables) lives in a file-scope device array of
+ * SGNN_HIST_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit.  The call runs on the CURRENT
+ * device and calls no cudaMalloc / cudaFree.  Problems whose scratch exceeds the array are rejected with return code
+ * 5 (at node_dim <= 16 the array serves n * max_nodes_db up to about 23 000 next to 1 000 queries), shapes outside the kernel with 4 (as
+ * sgnn_hist_all_pairs); the message goes to err[err_cap] (may be NULL).  All calls on a device SHARE the array,
+ * which keeps the previous call's contents (every call rewrites or clears what it reads): calls that overlap on the
+ * GPU race -- issue them on one stream.  counts_dev [m][n][16] bytes; rows of queries without nodes are not written. */
+#define SGNN_HIST_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)
+int sgnn_hist_all_pairs_static(int32_t node_dim, int32_t bins, const float* nodes_q_dev, const int32_t* node_off_q_dev,
+                               int32_t max_nodes_q, int32_t m, const float* nodes_db_dev,
+                               const int32_t* node_off_db_dev, int32_t max_nodes_db, int32_t n, uint8_t* counts_dev,
+                               void* stream, char* err, int32_t err_cap);
 /* descending top-k per row with the reference's tie order (results.py:221-224: stable
  * ascending mergesort reversed => equal scores come out higher index first). */
 int sgnn_topk(SgnnHandle h, const float* sim_dev, int32_t m, int32_t n, int64_t ld, int32_t k,

@@ -139,9 +139,8 @@ def make_rank_data(rank):
     from graphembedding_b200 import data as D
     from graphembedding_b200.graphs import NodeFeatureOneHotEncoder, pack_nx_graphs
     enc = NodeFeatureOneHotEncoder([], 'type', feat_idx_dic={l: i for i, l in enumerate(D.AIDS_LABELS)})
-    q = pack_nx_graphs(D.synthetic_corpus(M_QUERIES, 2, 10, seed=124, gid_base=10 ** 6), enc)
-    db = pack_nx_graphs(D.synthetic_corpus(N_DB, 2, 10, seed=123 + 1000 * rank, gid_base=rank * N_DB), enc)
-    return enc, q, db
+    q_gs, db_gs = rank_corpora(rank)
+    return enc, pack_nx_graphs(q_gs, enc), pack_nx_graphs(db_gs, enc)
 
 
 def make_train_data(rank, world, n_batches=8):
@@ -166,73 +165,117 @@ def make_train_data(rank, world, n_batches=8):
     return enc, batch, out
 
 
-def cpu_rank_baseline(layers_spec, q, db, seconds_budget=15.0, threads=None):
-    """Oracle port on the host cores: batched torch-CPU all-pairs ranking step on a bounded
-    sample of queries against the full database (embedding of the sampled queries + all database
-    graphs + scoring + top-k).  Returns (pairs/s, cores, sample text)."""
+MODELS = {   # name -> (layer specs, engine keywords, short description)
+    'simgnn': (SIMGNN_LAYERS, dict(final_act='sigmoid'),
+               'SimGNN-style chain GCN64-GCN32-GCN16-Attention-NTN(16,16)-Histogram(16)-FC(32-16-8-4-1), sigmoid'),
+    'default': (DEFAULT_LAYERS, dict(),
+                'reference default flags model GCN32-GCN16-Dense1-Pad10-NTN(10,10), sim_kernel'),
+}
+HEADLINE = 'simgnn'
+
+
+def oracle_side(gs):
+    """networkx graphs -> padded oracle inputs (labels, A_hat, mask, n), with NOTHING of the product loaded: the
+    label index and the normalised adjacency come from the oracle's own restatement of graphs.py:55-117."""
+    from graphembedding_b200 import data as D          # synthetic generator only (pure Python)
+    from oracle import batched as OB
+    from oracle import siamese_oracle as O
+    idx = {l: i for i, l in enumerate(D.AIDS_LABELS)}
+    og = []
+    for g in gs:
+        pos = {v: i for i, v in enumerate(g.nodes())}
+        og.append(O.Graph.from_edges([idx[g.nodes[v]['type']] for v in g.nodes()],
+                                     [(pos[u], pos[v]) for u, v in g.edges()]))
+    return OB.pad_graphs(og, 29)
+
+
+def rank_corpora(rank):
+    from graphembedding_b200 import data as D
+    return (D.synthetic_corpus(M_QUERIES, 2, 10, seed=124, gid_base=10 ** 6),
+            D.synthetic_corpus(N_DB, 2, 10, seed=123 + 1000 * rank, gid_base=rank * N_DB))
+
+
+def cpu_rank_baseline(model, pq, pd, seconds_budget=15.0, threads=None, q_sample=None):
+    """Oracle port on the host cores: batched torch-CPU all-pairs ranking step (embedding of the sampled queries
+    and of ALL database graphs + scoring + top-k) on a bounded sample of the queries.  pq / pd: padded oracle
+    inputs (oracle_side / OB.pad_from_packed).  Returns (pairs/s, cores, sample text)."""
     import torch
     from oracle import batched as OB
     from oracle import siamese_oracle as O
     threads = threads or os.cpu_count()
     torch.set_num_threads(threads)
-    layers = O.parse_layer_specs(layers_spec, 29)
+    spec, kw, _ = MODELS[model]
+    layers = O.parse_layer_specs(spec, 29)
     P = O.unflatten(layers, O.init_params(layers, 123), torch.float32)
-    pq, pd = OB.pad_from_packed(q), OB.pad_from_packed(db)
+    head = any(L['kind'] == 'Histogram' for L in layers)
+    nq_all, nd_all = int(pq[0].shape[0]), int(pd[0].shape[0])
+    qs = nq_all if q_sample is None else min(q_sample, nq_all)
+    pq = tuple(t[:qs] for t in pq)
+    chunk = 8 if head else 100                     # the [Q, M, Nq, Nd] cell tensor of the histogram must stay small
     t0 = time.perf_counter()
     reps = 0
     while True:
-        xq = OB.embed(layers, P, *pq)
-        xd = OB.embed(layers, P, *pd)
-        for c in range(0, q.n_graphs, 100):           # chunked so that the [Q,K,M] tensor stays in cache
-            sim = OB.score_all_pairs(layers, P, xq[c:c + 100], xd)
+        if head:
+            xq, hq = OB.embed(layers, P, *pq, with_nodes=True)
+            xd, hd = OB.embed(layers, P, *pd, with_nodes=True)
+        else:
+            xq, xd = OB.embed(layers, P, *pq), OB.embed(layers, P, *pd)
+        for c in range(0, qs, chunk):
+            if head:
+                sim = OB.score_all_pairs_head(layers, P, xq[c:c + chunk], hq[c:c + chunk], pq[3][c:c + chunk], xd, hd,
+                                              pd[3], final_act=kw.get('final_act', 'sim_kernel'))
+            else:
+                sim = OB.score_all_pairs(layers, P, xq[c:c + chunk], xd)
             torch.topk(sim, TOPK, dim=1)
         reps += 1
         if time.perf_counter() - t0 > seconds_budget or reps >= 50:
             break
     dt = time.perf_counter() - t0
-    return q.n_graphs * db.n_graphs * reps / dt, threads, \
-        '{} full steps of {} queries x {} database graphs (embed + score + top-{}), batched torch-CPU fp32, ' \
-        'inputs pre-padded'.format(reps, q.n_graphs, db.n_graphs, TOPK)
+    return qs * nd_all * reps / dt, threads, \
+        '{} steps of {} of the {} queries x {} database graphs (embed + score + top-{}), batched torch-CPU fp32 ' \
+        'oracle port, inputs pre-padded'.format(reps, qs, nq_all, nd_all, TOPK)
 
 
-def cpu_per_pair_rate(layers_spec, q, db, n_pairs=200):
+def cpu_per_pair_rate(model, q_gs, db_gs, n_pairs=100):
     """The reference's own control flow: one un-batched forward per (query, database) pair
     (train.py:57-61), single thread."""
     import torch
+    from graphembedding_b200 import data as D
     from oracle import siamese_oracle as O
     torch.set_num_threads(1)
-    layers = O.parse_layer_specs(layers_spec, 29)
+    layers = O.parse_layer_specs(MODELS[model][0], 29)
     P = O.unflatten(layers, O.init_params(layers, 123), torch.float32)
+    idx = {l: i for i, l in enumerate(D.AIDS_LABELS)}
 
-    def graph(b, g):
-        lo, hi = b.node_off[g], b.node_off[g + 1]
-        rp = np.asarray(b.rowptr[lo:hi + 1])
-        rows = np.repeat(np.arange(hi - lo), np.diff(rp))
-        return O.Graph(b.labels[lo:hi], rows, b.col[rp[0]:rp[-1]], b.val[rp[0]:rp[-1]])
+    def graph(g):
+        pos = {v: i for i, v in enumerate(g.nodes())}
+        return O.Graph.from_edges([idx[g.nodes[v]['type']] for v in g.nodes()], [(pos[u], pos[v]) for u, v in g.edges()])
     t0 = time.perf_counter()
     for i in range(n_pairs):
-        g1, g2 = graph(q, i % q.n_graphs), graph(db, (7 * i) % db.n_graphs)
-        x1 = O.graph_forward(layers, P, g1, 29, torch.float32)
-        x2 = O.graph_forward(layers, P, g2, 29, torch.float32)
-        O.pair_forward(layers, P, x1, x2)
+        g1, g2 = graph(q_gs[i % len(q_gs)]), graph(db_gs[(7 * i) % len(db_gs)])
+        x1, h1 = O.graph_forward(layers, P, g1, 29, torch.float32, with_nodes=True)
+        x2, h2 = O.graph_forward(layers, P, g2, 29, torch.float32, with_nodes=True)
+        O.pair_forward(layers, P, x1, x2, h1=h1, h2=h2)
     torch.set_num_threads(os.cpu_count())
     return n_pairs / (time.perf_counter() - t0)
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU path restated (TensorFlow is not installed, so the
-    reference's own TF graph cannot run on this box; the oracle port stands in)."""
+    """--impl reference: the reference's CPU path restated (TensorFlow is not installed, so the reference's own
+    TF graph cannot run on this box; the oracle port stands in).  Loads nothing of the product: inputs are built
+    by the oracle's own preprocessing from the synthetic corpus."""
     rank = int(os.environ.get('RANK', 0))
     if rank != 0:
         return
-    enc, q, db = make_rank_data(0)
+    q_gs, db_gs = rank_corpora(0)
+    pq, pd = oracle_side(q_gs), oracle_side(db_gs)
     vals = []
     for s in range(args.warmup + args.steps):
-        v, cores, sample = cpu_rank_baseline(DEFAULT_LAYERS, q, db, seconds_budget=6.0)
+        v, cores, sample = cpu_rank_baseline(HEADLINE, pq, pd, seconds_budget=5.0, q_sample=64)
         if s >= args.warmup:
             vals.append(v)
     value = float(np.mean(vals))
-    pp = cpu_per_pair_rate(DEFAULT_LAYERS, q, db)
+    pp = cpu_per_pair_rate(HEADLINE, q_gs, db_gs)
     ms = 1000.0 * M_QUERIES * N_DB / value
     print(json.dumps({
         'impl': 'reference', 'metric': 'graph-pairs/sec (all-pairs ranking inference)', 'value': value,
@@ -244,11 +287,13 @@ def run_reference(args):
         'e2e': {'value': value, 'unit': 'pairs/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}))
 
 
-def workload_config():
-    return {'workload': 'all-pairs ranking, BASELINE configs[3]: {} queries x {} database graphs per GPU, '
-                        'AIDS-shaped (2..10 nodes, 29 labels), reference default flags model '
-                        '(GCN32-GCN16-Dense1-Pad10-NTN(10,10)), top-{}'.format(M_QUERIES, N_DB, TOPK),
-            'queries': M_QUERIES, 'db_per_gpu': N_DB, 'topk': TOPK, 'l2': 'flushed between timed steps (256 MiB write; N > 1: followed by a device-side barrier, both untimed)',
+def workload_config(model=None):
+    model = model or HEADLINE
+    return {'workload': 'all-pairs ranking, BASELINE configs[3] on the configs[0]/[1] model: {} queries x {} database '
+                        'graphs per GPU, AIDS-shaped (2..10 nodes, 29 labels), {}, top-{}'
+                        .format(M_QUERIES, N_DB, MODELS[model][2], TOPK),
+            'model': model, 'queries': M_QUERIES, 'db_per_gpu': N_DB, 'topk': TOPK,
+            'l2': 'flushed between timed steps (256 MiB write; N > 1: followed by a device-side barrier, both untimed)',
             'ntn_mode': 'reference', 'dropout': 0.0}
 
 
@@ -270,11 +315,261 @@ def timed_steps(torch, fn, steps, flush, align=None):
     return sum(a.elapsed_time(b) for a, b in evs)
 
 
+def peak_tflops():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return d.get('bf16_tflops_sustained', 1400.0), 'measured sustained bf16 (MEASURED_PEAKS.json)'
+    return 1400.0, 'fallback (B200_PROFILING.md, sustained)'
+
+
+def pair_stage_flops(layers, q, db):
+    """Algorithmic FLOPs of the pair stage, SURVEY 8(d): per pair NTN 2 D^2 K + 4 D K + 3 K, histogram
+    2 N1 N2 d + 2 N1 N2 (summed over the actual node counts), FC head 2 * sum(din * dout).  -> (ntn, hist, head)."""
+    pi = [i for i, L in enumerate(layers) if L['kind'] in ('NTN', 'Dot')][0]
+    L = layers[pi]
+    pairs = float(q.n_graphs) * float(db.n_graphs)
+    D, K = (L['input_dim'], L['feature_map_dim']) if L['kind'] == 'NTN' else (16, 1)
+    ntn = (2.0 * D * D * K + 4.0 * D * K + 3.0 * K) * pairs if L['kind'] == 'NTN' else 2.0 * D * pairs
+    hist = 0.0
+    if any(x['kind'] == 'Histogram' for x in layers):
+        d = [x for x in layers[:pi] if x['kind'] in ('GraphConvolution', 'Dense')][-1]['output_dim']
+        cells = float(np.diff(np.asarray(q.node_off)).sum()) * float(np.diff(np.asarray(db.node_off)).sum())
+        hist = (2.0 * d + 2.0) * cells
+    head = 2.0 * sum(x['input_dim'] * x['output_dim'] for x in layers[pi + 1:] if x['kind'] == 'Dense') * pairs
+    return ntn, hist, head
+
+
+def rank_bench(model, torch, dist, dev, rank, world, local, args, barrier, max_over_ranks, q, db, flush, clocks=None,
+               exchange_ok=True):
+    """The ranking step of one model: device-timed value, per-stage kernel times, roofline of the dominant kernel,
+    end-to-end through the host entry points, parity sample against the fp32 oracle port."""
+    from graphembedding_b200 import distributed as DS
+    from graphembedding_b200.engine import SgnnEngine
+    from graphembedding_b200.layers_factory import parse_layers
+    spec, kw, desc = MODELS[model]
+    layers = parse_layers(spec, 29)
+    eng = SgnnEngine(layers, 29, device=local, precision=args.precision, **kw)
+    eng.init_params(123)
+    eng.reserve(max_graphs=N_DB, max_nodes=max(q.total_nodes, db.total_nodes), max_nnz=db.nnz, max_queries=M_QUERIES,
+                max_db=N_DB)
+    qd, dbd = q.to(dev), db.to(dev)
+    E = eng.emb_dim
+    emb_q, emb_db = torch.empty((M_QUERIES, E), device=dev), torch.empty((N_DB, E), device=dev)
+    sim = torch.empty((M_QUERIES, N_DB), dtype=torch.float32, device=dev)
+    ids_d = torch.empty((M_QUERIES, TOPK), dtype=torch.int32, device=dev)
+    vals_d = torch.empty((M_QUERIES, TOPK), dtype=torch.float32, device=dev)
+    gids_d, gvals_d = torch.empty_like(ids_d), torch.empty_like(vals_d)   # global top-k after the exchange (N > 1)
+    out = {}
+    # database sharded over ranks: local top-k, candidate exchange over NVLink peer memory (fallback: NCCL
+    # all-gather + merge kernel), global ids
+    peer, exchange, verified = None, 'none (1 GPU)', None
+    if world > 1:
+        try:
+            peer, exchange = DS.PeerTopk(eng, M_QUERIES, TOPK, dist), 'p2p push + merge kernels (CUDA IPC peer memory)'
+        except Exception as e:   # no peer access between the GPUs: library collective
+            sys.stderr.write('bench.py: peer exchange unavailable (%s); using NCCL all-gather\n' % e)
+            exchange = 'nccl all-gather + merge kernel'
+        flag = torch.tensor([1 if peer is not None else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 0 and peer is not None:
+            peer.close()
+            peer, exchange = None, 'nccl all-gather + merge kernel'
+
+    def step():
+        out['ids'], out['vals'] = DS.sharded_rank(eng, qd, dbd, rank * N_DB, TOPK, dist if world > 1 else None,
+                                                  emb_q=emb_q, emb_db=emb_db, sim=sim, peer=peer, ids=ids_d, vals=vals_d,
+                                                  out_ids=gids_d, out_vals=gvals_d)
+
+    for _ in range(max(3, args.warmup)):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        # untimed verification: the peer-memory exchange must give what all-gather + merge kernel gives
+        step()
+        torch.cuda.synchronize()
+        got_i, got_v = out['ids'].clone(), out['vals'].clone()
+        li, lv, _ = eng.rank_device(qd, dbd, TOPK, emb_q=emb_q, emb_db=emb_db, sim=sim)
+        cv, ci = DS.gather_topk_candidates(lv, li, rank * N_DB, dist)
+        wi, wv = eng.topk_merge(cv, ci, TOPK)
+        torch.cuda.synchronize()
+        ok = torch.tensor([1 if (torch.equal(got_i, wi) and torch.equal(got_v, wv)) else 0], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        verified = bool(int(ok.item()))
+        assert verified, 'sharded ranking: exchange result differs from all-gather + merge'
+    if clocks is not None:
+        clocks.mark('load_begin')
+    t_pre = time.perf_counter()           # untimed pre-load: ~0.3 s of back-to-back steps so that the
+    while time.perf_counter() - t_pre < 0.3:   # clocks are in their loaded state and get sampled
+        for _ in range(20):
+            step()
+        torch.cuda.synchronize()
+    launches0 = eng.launches
+    barrier()
+    if clocks is not None:
+        clocks.mark('timed_begin')
+    total_ms = timed_steps(torch, step, args.steps, flush, align=peer.barrier if peer is not None else None)
+    barrier()
+    if clocks is not None:
+        clocks.mark('timed_end')
+    launches = eng.launches - launches0
+    ms_per_step = max_over_ranks(total_ms) / args.steps
+    res = {'model': model, 'value': M_QUERIES * N_DB * world / (ms_per_step * 1e-3), 'unit': 'pairs/s',
+           'ms_per_step': ms_per_step, 'gpu_launches': launches, 'exchange': exchange}
+    if verified is not None:
+        res['exchange_verified'] = verified
+    res.update(rank_stages(model, torch, eng, layers, q, db, qd, dbd, emb_q, emb_db, sim, args, flush))
+    if clocks is not None:
+        clocks.mark('load_end')
+    res['e2e'] = rank_e2e(torch, eng, q, db, dev, world, args, barrier, max_over_ranks, out.get('ids'))
+    if world == 1:
+        res['parity'] = rank_parity(model, torch, eng, layers, q, db, qd, dbd)
+    if peer is not None:
+        peer.close()
+    return res
+
+
+def committed_traffic(kernel):
+    """dram bytes per launch of `kernel` from the committed ncu capture of this round (profiles/traffic.json, written
+    from the --set full reports next to it), or None."""
+    p = os.path.join(ROOT, 'profiles', 'traffic.json')
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f).get(kernel)
+    return None
+
+
+def rank_stages(model, torch, eng, layers, q, db, qd, dbd, emb_q, emb_db, sim, args, flush):
+    """Per-stage kernel times of the ranking step (each timed alone on the launching stream, L2 flushed) and the
+    roofline of the dominant kernel."""
+    K = args.steps
+    ntn_f, hist_f, head_f = pair_stage_flops(layers, q, db)
+    t_ms = timed_steps(torch, lambda: eng.topk(sim, TOPK), K, flush) / K
+    if eng.has_head:
+        eq, rq = eng.embed_nodes(qd)
+        ed, rd = eng.embed_nodes(dbd)
+        e_ms = timed_steps(torch, lambda: (eng.embed_nodes(qd), eng.embed_nodes(dbd)), K, flush) / K
+        for _ in range(3):
+            eng.score_all_pairs_nodes(eq, rq, qd, ed, rd, dbd, out=sim)
+        s_ms = timed_steps(torch, lambda: eng.score_all_pairs_stages(eq, ed, sim, eng.STAGE_SCORE), K, flush) / K
+        p_ms = timed_steps(torch, lambda: eng.score_all_pairs_stages(eq, ed, sim, eng.STAGE_PREP_QUERIES |
+                                                                     eng.STAGE_PREP_DATABASE), K, flush) / K
+        stage = {'embed_q_plus_db_with_node_rows': e_ms, 'operand_prep_q_plus_db': p_ms,
+                 'scorer_stage_histogram_plus_head': s_ms, 'topk': t_ms}
+        peak, peak_src = peak_tflops()
+        tc_hist = args.precision != 'fp32'
+        if tc_hist:
+            cnt = torch.zeros((q.n_graphs, db.n_graphs, 16), dtype=torch.uint8, device=sim.device)
+            eng.hist_all_pairs(rq, qd, rd, dbd, out=cnt, stages=3)
+            k_ms = timed_steps(torch, lambda: eng.hist_all_pairs(rq, qd, rd, dbd, out=cnt, stages=4), K, flush) / K
+            stage['hist_tc_kernel'] = k_ms
+            stage['head_kernel_by_difference'] = s_ms - k_ms
+            kernel, k_flops = 'hist_tc_kernel (tcgen05 node-node GEMM + sigmoid/bin epilogue)', hist_f
+            del cnt
+        else:
+            k_ms, kernel, k_flops = s_ms, 'allpairs_head_kernel (fp32 CUDA cores)', ntn_f + hist_f + head_f
+        achieved = k_flops / (k_ms * 1e-3) / 1e12
+        # what actually bounds the binning epilogue: 1.5 MUFU (ex2 + half a shared rcp) per node-node cell on the
+        # XU pipe (16 lanes / clk / SM)
+        cells = hist_f / (2.0 * eng.node_dim + 2.0)
+        sm_hz = 148 * 1.9e9
+        roofline = {'bound': 'tensor', 'achieved': achieved, 'peak': peak, 'unit': 'TFLOP/s', 'frac': achieved / peak,
+                    'traffic': committed_traffic('hist_tc_kernel' if tc_hist else 'allpairs_head_kernel'),
+                    'kernel': kernel, 'kernel_ms': k_ms, 'peak_source': peak_src,
+                    'algorithmic_flops_per_launch': k_flops,
+                    'pair_stage': {'algorithmic_gflop': (ntn_f + hist_f + head_f) / 1e9, 'ms': s_ms,
+                                   'achieved_tflops': (ntn_f + hist_f + head_f) / (s_ms * 1e-3) / 1e12,
+                                   'frac': (ntn_f + hist_f + head_f) / (s_ms * 1e-3) / 1e12 / peak},
+                    'epilogue_floor': {'node_node_cells': cells, 'mufu_per_cell': 1.5,
+                                       'xu_floor_ms_at_1.9GHz': cells * 1.5 / 16.0 / sm_hz * 1e3,
+                                       'note': 'the kernel is bound by the sigmoid/bin epilogue (XU + issue), not by the MMA'},
+                    'stage_ms': stage}
+        return {'roofline': roofline}
+    for _ in range(3):
+        eng.score_all_pairs(emb_q, emb_db, out=sim)
+    # the scorer kernel proper (operands prepared above): the launch the roofline is quoted on
+    k_ms = timed_steps(torch, lambda: eng.score_all_pairs_stages(emb_q, emb_db, sim, eng.STAGE_SCORE), K, flush) / K
+    p_ms = timed_steps(torch, lambda: eng.score_all_pairs_stages(emb_q, emb_db, sim, eng.STAGE_PREP_QUERIES |
+                                                                 eng.STAGE_PREP_DATABASE), K, flush) / K
+    e_ms = timed_steps(torch, lambda: (eng.embed(qd, out=emb_q), eng.embed(dbd, out=emb_db)), K, flush) / K
+    peak, peak_src = peaks()
+    alg_bytes = 4.0 * M_QUERIES * N_DB + 4.0 * (M_QUERIES + N_DB) * eng.emb_dim
+    achieved = alg_bytes / (k_ms * 1e-3) / 1e9
+    tc = args.precision != 'fp32'
+    return {'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
+                         'traffic': committed_traffic('allpairs_tc_kernel' if tc else 'allpairs_fp32_kernel'),
+                         'kernel': 'allpairs_tc_kernel (tcgen05 scorer, SGNN_STAGE_SCORE)' if tc else 'allpairs_fp32_kernel',
+                         'kernel_ms': k_ms, 'peak_source': peak_src, 'algorithmic_bytes_per_launch': alg_bytes,
+                         'stage_ms': {'embed_q_plus_db': e_ms, 'operand_prep_q_plus_db': p_ms, 'scorer': k_ms, 'topk': t_ms}}}
+
+
+def rank_e2e(torch, eng, q, db, dev, world, args, barrier, max_over_ranks, dev_ids):
+    """The same step through the host C-ABI entry points: pinned HOST buffers in, top-k out, wall clock."""
+    def timed(fn):
+        t_w, n_w = time.perf_counter(), 0
+        while n_w < args.warmup or time.perf_counter() - t_w < 0.1:   # warm-up: >= W calls and >= 0.1 s (clocks settle)
+            fn()
+            n_w += 1
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            fn()
+        barrier()
+        return max_over_ranks((time.perf_counter() - t0) * 1e3) / args.steps
+    qp, dbp = q.pin(), db.pin()
+    ids_h = torch.empty((M_QUERIES, TOPK), dtype=torch.int32).pin_memory()
+    vals_h = torch.empty((M_QUERIES, TOPK), dtype=torch.float32).pin_memory()
+    e2e_ms = timed(lambda: eng.rank_host(qp, dbp, TOPK, ids=ids_h, vals=vals_h))
+    if world == 1 and dev_ids is not None:
+        assert torch.equal(ids_h.to(dev), dev_ids), 'host entry point and device path disagree'
+    d2h = 2 * 4 * M_QUERIES * TOPK
+    csr = {'value': M_QUERIES * N_DB * world / (e2e_ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': e2e_ms,
+           'h2d_bytes_per_step': q.nbytes() + db.nbytes(), 'd2h_bytes_per_step': d2h,
+           'entry_point': 'sgnn_rank_host (int32 / float CSR arrays from pinned host memory)'}
+    # the same step with the batches in the compact wire format (sgnn_compact_batch: byte-wide fields + value
+    # dictionary, built once per dataset on the host like the CSR itself; expanded on the device every step)
+    qc, dbc = q.compact(), db.compact()
+    e2e = csr
+    if qc is not None and dbc is not None:
+        both = torch.empty((2, M_QUERIES, TOPK), dtype=torch.int32).pin_memory()   # ids | values back to back: one D2H copy
+        ids_c, vals_c = both[0], both[1].view(torch.float32)
+        c_ms = timed(lambda: eng.rank_host_compact(qc, dbc, TOPK, ids=ids_c, vals=vals_c))
+        assert torch.equal(ids_c, ids_h), 'compact and plain host entry points disagree'
+        e2e = {'value': M_QUERIES * N_DB * world / (c_ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': c_ms,
+               'h2d_bytes_per_step': int(qc.numel() + dbc.numel()), 'd2h_bytes_per_step': d2h,
+               'entry_point': 'sgnn_rank_host_compact (compact wire blobs from pinned host memory, expanded on the device)',
+               'plain_csr': csr}
+    if world > 1:
+        e2e['note'] = 'per-rank host entry point on its own shard (host in, local top-k out); the cross-rank merge is in value'
+    return e2e
+
+
+def metrics_bench(torch, dev, args, flush):
+    """precision@10 and Kendall tau of the 1 k x 10 k similarity matrix on the device (sgnn_precision_at_k,
+    sgnn_kendall_tau; src/metrics.py:14-35, build-defined tau-b): both read two m x n fp32 matrices once."""
+    from graphembedding_b200.engine import SgnnEngine
+    from graphembedding_b200.layers_factory import parse_layers
+    eng = SgnnEngine(parse_layers(DEFAULT_LAYERS, 29), 29, device=dev.index)
+    g = torch.Generator(device=dev).manual_seed(1)
+    true_sim = torch.rand((M_QUERIES, N_DB), device=dev, generator=g)
+    pred_sim = (true_sim + 0.05 * torch.randn((M_QUERIES, N_DB), device=dev, generator=g)).clamp_(0, 1)
+    ks = np.array([TOPK], np.int32)
+    K = max(3, args.steps // 4)
+    for _ in range(2):
+        eng.precision_at_ks(true_sim, pred_sim, ks)
+        eng.kendall_tau(true_sim, pred_sim)
+    p_ms = timed_steps(torch, lambda: eng.precision_at_ks(true_sim, pred_sim, ks), K, flush) / K
+    k_ms = timed_steps(torch, lambda: eng.kendall_tau(true_sim, pred_sim), K, flush) / K
+    peak, _ = peaks()
+    by = 2.0 * 4.0 * M_QUERIES * N_DB
+    return {'precision_at_10_ms': p_ms, 'kendall_tau_ms': k_ms, 'algorithmic_bytes': by,
+            'precision_at_10_hbm_frac': by / (p_ms * 1e-3) / 1e9 / peak, 'kendall_tau_hbm_frac': by / (k_ms * 1e-3) / 1e9 / peak}
+
+
 def run_cuda(args):
     import torch
     import torch.distributed as dist
-    from graphembedding_b200.engine import SgnnEngine
-    from graphembedding_b200.layers_factory import parse_layers
     world = int(os.environ.get('WORLD_SIZE', 1))
     rank = int(os.environ.get('RANK', 0))
     local = int(os.environ.get('LOCAL_RANK', 0))
@@ -306,153 +601,45 @@ def run_cuda(args):
         return float(t.item())
 
     enc, q, db = make_rank_data(rank)
-    eng = SgnnEngine(parse_layers(DEFAULT_LAYERS, 29), 29, device=local, precision=args.precision)
-    eng.init_params(123)
-    eng.reserve(max_graphs=N_DB, max_nodes=db.total_nodes, max_nnz=db.nnz, max_queries=M_QUERIES, max_db=N_DB)
-    qd, dbd = q.to(dev), db.to(dev)
-    emb_q = torch.empty((M_QUERIES, eng.emb_dim), dtype=torch.float32, device=dev)
-    emb_db = torch.empty((N_DB, eng.emb_dim), dtype=torch.float32, device=dev)
-    sim = torch.empty((M_QUERIES, N_DB), dtype=torch.float32, device=dev)
-    ids_d = torch.empty((M_QUERIES, TOPK), dtype=torch.int32, device=dev)
-    vals_d = torch.empty((M_QUERIES, TOPK), dtype=torch.float32, device=dev)
-    gids_d, gvals_d = torch.empty_like(ids_d), torch.empty_like(vals_d)   # global top-k after the exchange (N > 1)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    out = {}
-
-    from graphembedding_b200 import distributed as DS
-
-    # database sharded over ranks: local top-k, candidate exchange over NVLink peer memory (fallback: NCCL
-    # all-gather + merge kernel), global ids
-    peer, exchange = None, 'none (1 GPU)'
-    if world > 1:
-        try:
-            peer, exchange = DS.PeerTopk(eng, M_QUERIES, TOPK, dist), 'p2p push + merge kernels (CUDA IPC peer memory)'
-        except Exception as e:   # no peer access between the GPUs: library collective
-            sys.stderr.write('bench.py: peer exchange unavailable (%s); using NCCL all-gather\n' % e)
-            exchange = 'nccl all-gather + merge kernel'
-        flag = torch.tensor([1 if peer is not None else 0], device=dev)
-        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-        if int(flag.item()) == 0 and peer is not None:
-            peer.close()
-            peer, exchange = None, 'nccl all-gather + merge kernel'
-
-    def step():
-        out['ids'], out['vals'] = DS.sharded_rank(eng, qd, dbd, rank * N_DB, TOPK, dist if world > 1 else None,
-                                                  emb_q=emb_q, emb_db=emb_db, sim=sim, peer=peer, ids=ids_d, vals=vals_d,
-                                                  out_ids=gids_d, out_vals=gvals_d)
-
     clocks = ClockSampler(local)
     clocks.start()
-    for _ in range(args.warmup):
-        step()
-    torch.cuda.synchronize()
-    clocks.mark('load_begin')
-    t_pre = time.perf_counter()           # untimed pre-load: ~0.3 s of back-to-back steps so that the
-    while time.perf_counter() - t_pre < 0.3:   # clocks are in their loaded state and get sampled
-        for _ in range(20):
-            step()
-        torch.cuda.synchronize()
-    launches0 = eng.launches
-    barrier()
-    clocks.mark('timed_begin')
-    total_ms = timed_steps(torch, step, args.steps, flush, align=peer.barrier if peer is not None else None)
-    barrier()
-    clocks.mark('timed_end')
-    launches = eng.launches - launches0
-    total_ms = max_over_ranks(total_ms)
-    ms_per_step = total_ms / args.steps
-    value = M_QUERIES * N_DB * world / (ms_per_step * 1e-3)
-
-    # ---- dominant kernel: the all-pairs scorer, timed alone on its launching stream ----
-    for _ in range(3):
-        eng.score_all_pairs(emb_q, emb_db, out=sim)
-    # the scorer kernel proper (operands prepared above): the launch the roofline is quoted on
-    k_ms = timed_steps(torch, lambda: eng.score_all_pairs_stages(emb_q, emb_db, sim, eng.STAGE_SCORE), args.steps,
-                       flush) / args.steps
-    p_ms = timed_steps(torch, lambda: eng.score_all_pairs_stages(emb_q, emb_db, sim, eng.STAGE_PREP_QUERIES |
-                                                                 eng.STAGE_PREP_DATABASE), args.steps, flush) / args.steps
-    e_ms = timed_steps(torch, lambda: (eng.embed(qd, out=emb_q), eng.embed(dbd, out=emb_db)), args.steps, flush) / args.steps
-    t_ms = timed_steps(torch, lambda: eng.topk(sim, TOPK), args.steps, flush) / args.steps
-    clocks.mark('load_end')
+    common = (torch, dist, dev, rank, world, local, args, barrier, max_over_ranks)
+    head = rank_bench(HEADLINE, *common, q, db, flush, clocks=clocks)
     clk = clocks.stop()
-    peak, peak_src = peaks()
-    alg_bytes = 4.0 * M_QUERIES * N_DB + 4.0 * (M_QUERIES + N_DB) * eng.emb_dim
-    achieved = alg_bytes / (k_ms * 1e-3) / 1e9
-    roofline = {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
-                'traffic': 1.67e6 if args.precision != 'fp32' else None,   # ncu --set full, profiles/r1v_step_ncu_raw.csv: 1.43 MB read + 0.24 MB written per launch (sim stays in L2)
-                'kernel': 'allpairs_tc_kernel (tcgen05 scorer, SGNN_STAGE_SCORE)' if args.precision != 'fp32'
-                else 'allpairs_fp32_kernel',
-                'kernel_ms': k_ms, 'peak_source': peak_src,
-                'algorithmic_bytes_per_launch': alg_bytes,
-                'stage_ms': {'embed_q_plus_db': e_ms, 'operand_prep_q_plus_db': p_ms, 'scorer': k_ms, 'topk': t_ms}}
-
-    # ---- e2e: host buffers in, top-k out, through the host C-ABI entry point ----
-    qp, dbp = q.pin(), db.pin()
-    ids_h = torch.empty((M_QUERIES, TOPK), dtype=torch.int32).pin_memory()
-    vals_h = torch.empty((M_QUERIES, TOPK), dtype=torch.float32).pin_memory()
-    t_w = time.perf_counter()
-    n_w = 0
-    while n_w < args.warmup or time.perf_counter() - t_w < 0.1:   # warm-up: >= W calls and >= 0.1 s (clocks settle)
-        eng.rank_host(qp, dbp, TOPK, ids=ids_h, vals=vals_h)
-        n_w += 1
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        eng.rank_host(qp, dbp, TOPK, ids=ids_h, vals=vals_h)
-    barrier()
-    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / args.steps
-    if world == 1:
-        assert torch.equal(ids_h.to(dev), out['ids']), 'host entry point and device path disagree'
-    csr = {'value': M_QUERIES * N_DB * world / (e2e_ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': e2e_ms,
-           'h2d_bytes_per_step': q.nbytes() + db.nbytes(), 'd2h_bytes_per_step': 2 * 4 * M_QUERIES * TOPK,
-           'entry_point': 'sgnn_rank_host (int32 / float CSR arrays from pinned host memory)'}
-    # the same step with the batches in the compact wire format (sgnn_compact_batch: byte-wide fields + value
-    # dictionary, built once per dataset on the host like the CSR itself; expanded on the device every step)
-    qc, dbc = q.compact(), db.compact()
-    e2e = csr
-    if qc is not None and dbc is not None:
-        both = torch.empty((2, M_QUERIES, TOPK), dtype=torch.int32).pin_memory()   # ids | values back to back: one D2H copy
-        ids_c, vals_c = both[0], both[1].view(torch.float32)
-        t_w = time.perf_counter()
-        n_w = 0
-        while n_w < args.warmup or time.perf_counter() - t_w < 0.1:
-            eng.rank_host_compact(qc, dbc, TOPK, ids=ids_c, vals=vals_c)
-            n_w += 1
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            eng.rank_host_compact(qc, dbc, TOPK, ids=ids_c, vals=vals_c)
-        barrier()
-        c_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / args.steps
-        assert torch.equal(ids_c, ids_h), 'compact and plain host entry points disagree'
-        e2e = {'value': M_QUERIES * N_DB * world / (c_ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': c_ms,
-               'h2d_bytes_per_step': int(qc.numel() + dbc.numel()), 'd2h_bytes_per_step': 2 * 4 * M_QUERIES * TOPK,
-               'entry_point': 'sgnn_rank_host_compact (compact wire blobs from pinned host memory, expanded on the device)',
-               'plain_csr': csr}
+    extra = {}
+    if not args.headline_only:
+        other = rank_bench('default', *common, q, db, flush)
+        extra['default_model'] = {k: other[k] for k in ('value', 'unit', 'ms_per_step', 'gpu_launches', 'roofline', 'e2e', 'parity')
+                                  if k in other}
+        extra['default_model']['workload'] = MODELS['default'][2]
+        extra['train'] = run_train('avg_ntn', *common)
+        extra['train_simgnn'] = run_train('simgnn', *common)
+        extra['web'] = run_web(torch, dev, rank, world, local, args, barrier, max_over_ranks, flush)
+        if world == 1:
+            extra['metrics'] = metrics_bench(torch, dev, args, flush)
     if world > 1:
-        e2e['note'] = 'per-rank sgnn_rank_host on its own shard (host in, local top-k out); the cross-rank merge is in value'
-
-    train = run_train(torch, dist, dev, rank, world, local, args, barrier, max_over_ranks)
-    simgnn = run_simgnn(torch, dist, dev, rank, world, local, args, barrier, max_over_ranks, qd, dbd, flush)
-    web = run_web(torch, dev, rank, world, local, args, barrier, max_over_ranks, flush)
-
-    if world > 1:
-        if peer is not None:
-            peer.close()
         dist.barrier()
         dist.destroy_process_group()
     if rank != 0:
         return
-    line = {'metric': 'graph-pairs/sec (all-pairs ranking inference)', 'value': value, 'unit': 'pairs/s',
-            'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms_per_step,
+    cfg = workload_config()
+    line = {'metric': 'graph-pairs/sec (all-pairs ranking inference)', 'value': head['value'], 'unit': 'pairs/s',
+            'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': head['ms_per_step'],
             'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
             'dtype': 'f32' if args.precision == 'fp32' else args.precision, 'data': 'synthetic',
-            'config': dict(workload_config(), exchange=exchange), 'clocks': clk, 'e2e': e2e,
-            'gpu_launches': launches, 'roofline': roofline, 'train': train, 'simgnn': simgnn, 'web': web}
+            'config': cfg, 'clocks': clk, 'e2e': head['e2e'], 'gpu_launches': head['gpu_launches'],
+            'roofline': head['roofline'], 'exchange': head['exchange']}
+    for k in ('exchange_verified', 'parity'):
+        if k in head:
+            line[k] = head[k]
     if world == 1 and not args.no_cpu_baseline:
-        v, cores, sample = cpu_rank_baseline(DEFAULT_LAYERS, q, db)
+        from oracle import batched as OB
+        v, cores, sample = cpu_rank_baseline(HEADLINE, OB.pad_from_packed(q), OB.pad_from_packed(db), q_sample=64)
+        q_gs, db_gs = rank_corpora(0)
         line['cpu_baseline'] = {'value': v, 'unit': 'pairs/s', 'cores': cores, 'kind': 'port', 'sample': sample,
-                                'per_pair_reference_structure_pairs_per_s': cpu_per_pair_rate(DEFAULT_LAYERS, q, db)}
+                                'per_pair_reference_structure_pairs_per_s': cpu_per_pair_rate(HEADLINE, q_gs, db_gs)}
+    line.update(extra)
     sys.stdout.flush()
     os.write(json_fd, (json.dumps(line) + '\n').encode())
 
@@ -511,90 +698,60 @@ def run_web(torch, dev, rank, world, local, args, barrier, max_over_ranks, flush
                           'gflops_fp32': 2.0 * 16 * cells / (h_ms * 1e-3) / 1e9}}
 
 
-def run_simgnn(torch, dist, dev, rank, world, local, args, barrier, max_over_ranks, qd, dbd, flush):
-    """The same ranking step and the same training step on the SimGNN-style chain (BASELINE configs[0]/[1]:
-    3 GCN + Attention + NTN(16,16) + 16-bin node-node histogram + FC 32-16-8-4-1): per-rank shards, no
-    cross-rank exchange in the timed region (the candidate exchange is the headline's)."""
+TRAIN_MODELS = {'avg_ntn': (TRAIN_LAYERS, 'GCN32-GCN16-Average-NTN(16,10)'),
+                'simgnn': (SIMGNN_LAYERS, 'GCN64-GCN32-GCN16-Attention-NTN(16,16)-Histogram(16)-FC(32-16-8-4-1)')}
+
+
+def train_cpu_baseline(name, batch, batches, seconds_budget=8.0):
+    """Oracle port of one optimiser step on the host cores: batched torch-CPU autograd + TF-1 Adam
+    (oracle/batched.py train_step) for chains without a head, the per-pair fp64 restatement for the SimGNN-style head."""
+    import torch
+    from oracle import batched as OB
+    from oracle import siamese_oracle as O
+    layers = O.parse_layer_specs(TRAIN_MODELS[name][0], 29)
+    flat = O.init_params(layers, 123)
+    g1, g2, t = batches[0][0], batches[0][1], batches[0][2]
+    if name == 'avg_ntn':
+        torch.set_num_threads(os.cpu_count())
+        lab, A, mask, n = OB.pad_from_packed(batch)
+        adam = O.TFAdam(len(flat))
+        t0, reps = time.perf_counter(), 0
+        while time.perf_counter() - t0 < seconds_budget and reps < 200:
+            flat, _ = OB.train_step(layers, flat, adam, lab, A, mask, n, torch.as_tensor(g1.astype(np.int64)),
+                                    torch.as_tensor(g2.astype(np.int64)), torch.as_tensor(t), loss_mode='paired')
+            reps += 1
+        dt = time.perf_counter() - t0
+        return {'value': reps * len(g1) / dt, 'unit': 'pairs/s', 'cores': os.cpu_count(), 'kind': 'port',
+                'sample': '{} optimiser steps of {} pairs, batched torch-CPU autograd + TF-1 Adam over all {} graphs'
+                          .format(reps, len(g1), batch.n_graphs)}
+    torch.set_num_threads(1)
+    no, rp = np.asarray(batch.node_off), np.asarray(batch.rowptr)
+
+    def graph(g):
+        lo, hi = no[g], no[g + 1]
+        r = rp[lo:hi + 1]
+        rows = np.repeat(np.arange(hi - lo), np.diff(r))
+        return O.Graph(np.asarray(batch.labels)[lo:hi], rows, np.asarray(batch.col)[r[0]:r[-1]], np.asarray(batch.val)[r[0]:r[-1]])
+    k = 16
+    a1, a2 = [graph(g) for g in g1[:k]], [graph(g) for g in g2[:k]]
+    t0 = time.perf_counter()
+    O.loss_and_grads(layers, flat, a1, a2, t[:k], 29, final_act='sigmoid', weight_decay=0.0, loss_mode='paired')
+    dt = time.perf_counter() - t0
+    torch.set_num_threads(os.cpu_count())
+    return {'value': k / dt, 'unit': 'pairs/s', 'cores': 1, 'kind': 'port',
+            'sample': 'forward + fp64 autograd backward of {} pairs, per-pair restatement (the reference control flow)'.format(k)}
+
+
+def run_train(name, torch, dist, dev, rank, world, local, args, barrier, max_over_ranks, cpu=True):
+    """BASELINE configs[2]: data-parallel training, TRAIN_BATCH pairs per GPU per step (fwd + bwd + gradient
+    exchange + Adam), plus a throughput point at BIG pairs per step that fills the GPU."""
     from graphembedding_b200 import distributed as DS
     from graphembedding_b200.engine import SgnnEngine
     from graphembedding_b200.layers_factory import parse_layers
-    layers = parse_layers(SIMGNN_LAYERS, 29)
-    eng = SgnnEngine(layers, 29, device=local, final_act='sigmoid', loss_mode='paired')
-    eng.init_params(123)
-    eng.reserve(max_graphs=N_DB, max_nodes=max(qd.total_nodes, dbd.total_nodes), max_nnz=dbd.nnz,
-                max_queries=M_QUERIES, max_db=N_DB)
-    E = eng.emb_dim
-    bufs = dict(emb_q=torch.empty((M_QUERIES, E), device=dev), emb_db=torch.empty((N_DB, E), device=dev),
-                sim=torch.empty((M_QUERIES, N_DB), device=dev),
-                ids=torch.empty((M_QUERIES, TOPK), dtype=torch.int32, device=dev),
-                vals=torch.empty((M_QUERIES, TOPK), device=dev))
-    for _ in range(max(3, args.warmup)):
-        eng.rank_device(qd, dbd, TOPK, **bufs)
-    torch.cuda.synchronize()
-    l0 = eng.launches
-    barrier()
-    ms = timed_steps(torch, lambda: eng.rank_device(qd, dbd, TOPK, **bufs), args.steps, flush)
-    barrier()
-    ms = max_over_ranks(ms) / args.steps
-    launches = eng.launches - l0
-    eq, rq = eng.embed_nodes(qd)
-    ed, rd = eng.embed_nodes(dbd)
-    k_ms = timed_steps(torch, lambda: eng.score_all_pairs_nodes(eq, rq, qd, ed, rd, dbd, out=bufs['sim']),
-                       args.steps, flush) / args.steps
-    e_ms = timed_steps(torch, lambda: (eng.embed_nodes(qd), eng.embed_nodes(dbd)), args.steps, flush) / args.steps
-    # algorithmic flops of the pair stage (SURVEY 8d): NTN 2DK (factorised per query) + histogram 2 N1 N2 d + head
-    no_q, no_d = qd.node_off.cpu().numpy(), dbd.node_off.cpu().numpy()
-    nq, nd = np.diff(no_q).astype(np.float64), np.diff(no_d).astype(np.float64)
-    cells = nq.sum() * nd.sum()
-    pi = [i for i, L in enumerate(layers) if L['kind'] == 'NTN'][0]
-    head_macs = sum(L['input_dim'] * L['output_dim'] for L in layers[pi + 1:] if L['kind'] == 'Dense')
-    flops = 2.0 * (16 * 16 + head_macs) * M_QUERIES * N_DB + 2.0 * 16 * cells
-    # ---- training on the same chain: BASELINE configs[2] shape (128 pairs / GPU / step, graphs <= 30 nodes) ----
+    spec, desc = TRAIN_MODELS[name]
     enc, batch, batches = make_train_data(rank, world)
-    bd = batch.to(dev)
-    feeds = [(torch.as_tensor(a, device=dev), torch.as_tensor(b, device=dev), torch.as_tensor(t, device=dev), s1, s2)
-             for a, b, t, s1, s2 in batches]
-    loss = torch.zeros(4, dtype=torch.float32, device=dev)
-    grads = eng.device_buffers()[1]
-    gb = TRAIN_BATCH * world
-
-    def tstep(i):
-        g1, g2, t, s1, s2 = feeds[i % len(feeds)]
-        loss.zero_()
-        DS.data_parallel_step(eng, bd, g1, g2, t, gb, s1, s2, loss, dist if world > 1 else None, grads=grads)
-
-    n = max(args.steps * 10, 100)
-    for i in range(10):
-        tstep(i)
-    barrier()
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record()
-    for i in range(n):
-        tstep(i)
-    b.record()
-    barrier()
-    t_ms = max_over_ranks(a.elapsed_time(b)) / n
-    return {'workload': 'BASELINE configs[0]/[1] chain on the headline data: {} queries x {} database graphs per GPU, '
-                        'GCN64-GCN32-GCN16-Attention-NTN(16,16)-Histogram(16)-FC(32-16-8-4-1), sigmoid, top-{}; '
-                        'fp32 CUDA-core all-pairs head kernel'.format(M_QUERIES, N_DB, TOPK),
-            'value': M_QUERIES * N_DB * world / (ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': ms,
-            'gpu_launches': launches,
-            'stage_ms': {'embed_q_plus_db_with_node_rows': e_ms, 'prep_plus_allpairs_head': k_ms},
-            'pair_stage': {'algorithmic_gflop': flops / 1e9, 'achieved_tflops_fp32': flops / (k_ms * 1e-3) / 1e12,
-                           'node_node_cells': cells},
-            'train': {'value': TRAIN_BATCH * world / (t_ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': t_ms, 'steps': n,
-                      'allreduce': 'none (1 GPU)' if world == 1 else 'nccl all-reduce',
-                      'workload': '{} pairs/GPU/step, AIDS10knef-shaped graphs (2..30 nodes), fwd+bwd+Adam, fp32'.format(TRAIN_BATCH),
-                      'final_loss': float(loss[0] + loss[1])}}
-
-
-def run_train(torch, dist, dev, rank, world, local, args, barrier, max_over_ranks):
-    """BASELINE configs[2]: data-parallel training, TRAIN_BATCH pairs per GPU per step."""
-    from graphembedding_b200 import distributed as DS
-    from graphembedding_b200.engine import SgnnEngine
-    from graphembedding_b200.layers_factory import parse_layers
-    enc, batch, batches = make_train_data(rank, world)
-    eng = SgnnEngine(parse_layers(TRAIN_LAYERS, 29), 29, device=local, loss_mode='paired', ntn_mode='reference')
+    kw = dict(final_act='sigmoid') if name == 'simgnn' else {}
+    eng = SgnnEngine(parse_layers(spec, 29), 29, device=local, loss_mode='paired', ntn_mode='reference', **kw)
     eng.init_params(123)
     bd = batch.to(dev)
     feeds = [(torch.as_tensor(a, device=dev), torch.as_tensor(b, device=dev), torch.as_tensor(t, device=dev), s1, s2)
@@ -621,24 +778,92 @@ def run_train(torch, dist, dev, rank, world, local, args, barrier, max_over_rank
         DS.data_parallel_step(eng, bd, g1, g2, t, gb, s1, s2, loss, dist if world > 1 else None, grads=grads,
                               peer=peer)
 
+    def timed(fn, n):
+        for i in range(10):
+            fn(i)
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for i in range(n):
+            fn(i)
+        b.record()
+        barrier()
+        return max_over_ranks(a.elapsed_time(b)) / n
+
     n = max(args.steps * 10, 100)
-    for i in range(10):
-        step(i)
     l0 = eng.launches
-    barrier()
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record()
-    for i in range(n):
-        step(i)
-    b.record()
-    barrier()
-    ms = max_over_ranks(a.elapsed_time(b)) / n
+    ms = timed(step, n)
+    launches = (eng.launches - l0) * n // (n + 10)
+    final_loss = float(loss[0] + loss[1])
+    # algorithmic bytes per pair: both graphs' CSR + 4 B target + 4 B output
+    no, rp = np.asarray(batch.node_off), np.asarray(batch.rowptr)
+    gbytes = 4.0 * np.diff(no) + 4.0 * (np.diff(no) + 1) + 8.0 * (rp[no[1:]] - rp[no[:-1]])
+
+    def roof(pairs_g1, pairs_g2, step_ms):
+        by = float(gbytes[pairs_g1].sum() + gbytes[pairs_g2].sum() + 8.0 * len(pairs_g1))
+        peak, src = peaks()
+        ach = by / (step_ms * 1e-3) / 1e9
+        return {'bound': 'hbm', 'achieved': ach, 'peak': peak, 'unit': 'GB/s', 'frac': ach / peak, 'traffic': None,
+                'kernel': 'train_team_kernel + adam_kernel (one optimiser step)', 'kernel_ms': step_ms,
+                'algorithmic_bytes_per_step': by, 'peak_source': src}
+    res = {'allreduce': allreduce, 'model': desc, 'value': TRAIN_BATCH * world / (ms * 1e-3), 'unit': 'pairs/s',
+           'ms_per_step': ms, 'steps': n, 'gpu_launches': launches, 'final_loss': final_loss, 'dtype': 'f32',
+           'roofline': roof(batches[0][0], batches[0][1], ms)}
+    # ---- throughput point: BIG pairs per step (random pairs of the same graphs, random targets), no exchange ----
+    BIG = 16384
+    rng = np.random.default_rng(5 + rank)
+    b1, b2 = rng.integers(0, TRAIN_GRAPHS, BIG).astype(np.int32), rng.integers(0, TRAIN_GRAPHS, BIG).astype(np.int32)
+    bt = rng.uniform(0.05, 1.0, BIG).astype(np.float32)
+    d1, d2, dt_ = torch.as_tensor(b1, device=dev), torch.as_tensor(b2, device=dev), torch.as_tensor(bt, device=dev)
+    ts, ts2 = float(bt.astype(np.float64).sum()), float((bt.astype(np.float64) ** 2).sum())
+
+    def big(i):
+        loss.zero_()
+        eng.train_step(bd, d1, d2, dt_, BIG, ts, ts2, loss=loss)
+        eng.apply_adam(1.0, loss)
+    bms = timed(big, max(args.steps, 20))
+    res['large_batch'] = {'pairs_per_step': BIG, 'value': BIG * world / (bms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': bms,
+                          'roofline': roof(b1, b2, bms), 'note': 'per-GPU replicas, no gradient exchange'}
+    if cpu and world == 1 and not args.no_cpu_baseline:
+        res['cpu_baseline'] = train_cpu_baseline(name, batch, batches)
     if peer is not None:
         peer.close()
-    return {'allreduce': allreduce, 'workload': 'BASELINE configs[2]: DP training, {} pairs/GPU/step, {} AIDS10knef-shaped graphs (2..30 nodes), '
-                        'GCN32-GCN16-Average-NTN(16,10), fwd+bwd+allreduce+Adam, fp32'.format(TRAIN_BATCH, TRAIN_GRAPHS),
-            'value': TRAIN_BATCH * world / (ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': ms, 'steps': n,
-            'gpu_launches': eng.launches - l0, 'final_loss': float(loss[0] + loss[1])}
+    return res
+
+
+def rank_parity(model, torch, eng, layers, q, db, qd, dbd, nq=64, nd=1000):
+    """Device scores of a sample (first nq queries x first nd database graphs) against the fp32 oracle port."""
+    from oracle import batched as OB
+    from oracle import siamese_oracle as O
+    from scipy.stats import kendalltau
+    spec, kw, _ = MODELS[model]
+    ol = O.parse_layer_specs(spec, 29)
+    P = O.unflatten(ol, O.init_params(ol, 123), torch.float32)
+    flat = O.init_params(ol, 123)
+    eng2_params = eng.get_params()
+    eng.set_params(flat)                       # identical weights on both sides
+    ids, vals, sim = eng.rank_device(qd, dbd, TOPK)
+    got = sim[:nq, :nd].cpu().numpy().astype(np.float64)
+    eng.set_params(eng2_params)
+    pq = tuple(t[:nq] for t in OB.pad_from_packed(q))
+    pd = tuple(t[:nd] for t in OB.pad_from_packed(db))
+    if eng.has_head:
+        xq, hq = OB.embed(ol, P, *pq, with_nodes=True)
+        xd, hd = OB.embed(ol, P, *pd, with_nodes=True)
+        ref = OB.score_all_pairs_head(ol, P, xq, hq, pq[3], xd, hd, pd[3], final_act=kw.get('final_act', 'sim_kernel'))
+    else:
+        ref = OB.score_all_pairs(ol, P, OB.embed(ol, P, *pq), OB.embed(ol, P, *pd))
+    ref = ref.numpy().astype(np.float64)
+    err = np.abs(got - ref)
+    top_g = np.argsort(-got, axis=1, kind='stable')[:, :TOPK]
+    top_r = np.argsort(-ref, axis=1, kind='stable')[:, :TOPK]
+    prec = float(np.mean([len(set(a) & set(b)) / float(TOPK) for a, b in zip(top_g, top_r)]))
+    tau = float(np.mean([kendalltau(a, b).statistic for a, b in zip(got, ref)]))
+    return {'sample': '{} queries x {} database graphs vs the fp32 torch-CPU oracle port'.format(nq, nd),
+            'max_abs_err': float(err.max()), 'max_rel_err': float((err / np.maximum(np.abs(ref), 1e-6)).max()),
+            'mse': float((err ** 2).mean()), 'frac_cells_err_gt_1e-4': float((err > 1e-4).mean()),
+            'prec_at_10_vs_oracle': prec, 'kendall_tau_vs_oracle': tau,
+            'note': 'cells above 1e-4 are pairs with a node-node score on a histogram bin edge (one count moves)'}
 
 
 def main():
@@ -647,6 +872,7 @@ def main():
     ap.add_argument('--steps', type=int, default=20)
     ap.add_argument('--warmup', type=int, default=5)
     ap.add_argument('--impl', default='cuda', choices=['cuda', 'reference'])
+    ap.add_argument('--headline-only', action='store_true', help='skip the sub-benchmarks (default model, train, web, metrics)')
     ap.add_argument('--precision', default='bf16x3', choices=['fp32', 'bf16x3', 'bf16'],
                     help='all-pairs scorer: bf16x3 = tcgen05 with split-bf16 operands and fp32 accumulation (fp32-grade, '
                          'gated at 2e-4 rel against the fp32 CUDA-core scorer), fp32 = CUDA-core parity mode')

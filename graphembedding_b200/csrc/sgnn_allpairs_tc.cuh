@@ -369,56 +369,31 @@ __device__ __forceinline__ void tc_epilogue_part(const TcEpi& E, uint32_t taddr,
   }
 }
 
-template <int KT, bool RELU, bool REF, bool SIMK>
-__global__ void __launch_bounds__(TC_THREADS, 1)
-allpairs_tc_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const float* __restrict__ params,
-                   const __nv_bfloat16* __restrict__ Ag, const __nv_bfloat16* __restrict__ Bg,
-                   float* __restrict__ sim, int64_t ld, unsigned long long* __restrict__ smax
-#ifdef SGNN_TC_TRACE
-                   , long long* __restrict__ trace   // [tile][8] clock64 stamps of CTA 0 (tools/tc_trace.cu)
-#endif
-                   ) {
+// Roles shared by the scorer kernels: the bulk-copy producer warp and the MMA issuer warps (everything but the epilogue).
+struct TcCtaWork { int gt0, ga_count, qb0, nq; };
+struct TcSmem {
+  uint8_t *sA, *sB;
+  uint64_t *a_full, *b_full, *b_empty, *t_full, *t_empty;
+  int a_bytes, b_bytes;
+};
 #ifdef SGNN_TC_TRACE
 #define TC_STAMP(tile, slot) do { if (blockIdx.x == 0) trace[(tile) * 8 + (slot)] = clock64(); } while (0)
 #else
 #define TC_STAMP(tile, slot) do { } while (0)
 #endif
-  extern __shared__ __align__(1024) uint8_t tc_smem[];
-  uint8_t* smem = tc_smem;
-  const int a_bytes = tc_a_bytes(G), b_bytes = tc_b_bytes(G);
-  uint8_t* sA = smem;
-  uint8_t* sB = sA + TC_GA_MAX * a_bytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + G.stages * b_bytes);
-  uint64_t* a_full = bars;                 // [1]
-  uint64_t* b_full = bars + 1;             // [G.stages]
-  uint64_t* b_empty = b_full + G.stages;  // [G.stages]
-  uint64_t* t_full = b_empty + G.stages;  // [TC_BUFS]
-  uint64_t* t_empty = t_full + TC_BUFS;    // [TC_BUFS]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + TC_BUFS);
-  float* sU = reinterpret_cast<float*>(tmem_slot + 4);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // this CTA's rectangle of work: GA database tiles x a range of query blocks
-  const int gg = blockIdx.x / G.q_groups, qg = blockIdx.x - gg * G.q_groups;
-  const int gt0 = gg * G.GA;
-  const int ga_count = min(G.GA, G.n_gtiles - gt0);
-  const int qb0 = qg * G.qb_per_group;
-  const int nq = max(0, min(G.qb_per_group, G.n_qblocks - qb0));
-
-  if (threadIdx.x == 0) {
-    tc::mbar_init(a_full, 1);
-    for (int s = 0; s < G.stages; ++s) { tc::mbar_init(b_full + s, 1); tc::mbar_init(b_empty + s, TC_BUFS); }
-    for (int b = 0; b < TC_BUFS; ++b) { tc::mbar_init(t_full + b, 1); tc::mbar_init(t_empty + b, 8); }
-    tc::fence_barrier_init();
-  }
-  const bool dot = M.pair_kind == SGNN_LAYER_DOT;
-  for (int k = threadIdx.x; k < G.K; k += blockDim.x) sU[k] = dot ? 1.f : params[M.u_off + k];
-  if (warp == TC_PROD_WARP) tc::tmem_alloc(tmem_slot, 512);
-  tc::tc_fence_before();
-  __syncthreads();
-  tc::tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
-
+__device__ __forceinline__ void tc_producer_mma_roles(const TcGeom& G, const TcCtaWork& Wk, const TcSmem& S,
+                                                      const __nv_bfloat16* __restrict__ Ag,
+                                                      const __nv_bfloat16* __restrict__ Bg, uint32_t tmem_base, int warp,
+                                                      int lane
+#ifdef SGNN_TC_TRACE
+                                                      , long long* __restrict__ trace
+#endif
+                                                      ) {
+  uint8_t* const sA = S.sA; uint8_t* const sB = S.sB;
+  uint64_t* const a_full = S.a_full; uint64_t* const b_full = S.b_full; uint64_t* const b_empty = S.b_empty;
+  uint64_t* const t_full = S.t_full; uint64_t* const t_empty = S.t_empty;
+  const int a_bytes = S.a_bytes, b_bytes = S.b_bytes;
+  const int gt0 = Wk.gt0, ga_count = Wk.ga_count, qb0 = Wk.qb0, nq = Wk.nq;
   if (warp == TC_PROD_WARP) {
     // ===== producer: A tiles once, then the stream of query-block B tiles =====
     if (lane == 0 && nq > 0) {
@@ -498,6 +473,62 @@ allpairs_tc_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const flo
         }
       }
     }
+  }
+}
+
+template <int KT, bool RELU, bool REF, bool SIMK>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+allpairs_tc_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const float* __restrict__ params,
+                   const __nv_bfloat16* __restrict__ Ag, const __nv_bfloat16* __restrict__ Bg,
+                   float* __restrict__ sim, int64_t ld, unsigned long long* __restrict__ smax
+#ifdef SGNN_TC_TRACE
+                   , long long* __restrict__ trace   // [tile][8] clock64 stamps of CTA 0 (tools/tc_trace.cu)
+#endif
+                   ) {
+  extern __shared__ __align__(1024) uint8_t tc_smem[];
+  uint8_t* smem = tc_smem;
+  const int a_bytes = tc_a_bytes(G), b_bytes = tc_b_bytes(G);
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + TC_GA_MAX * a_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + G.stages * b_bytes);
+  uint64_t* a_full = bars;                 // [1]
+  uint64_t* b_full = bars + 1;             // [G.stages]
+  uint64_t* b_empty = b_full + G.stages;  // [G.stages]
+  uint64_t* t_full = b_empty + G.stages;  // [TC_BUFS]
+  uint64_t* t_empty = t_full + TC_BUFS;    // [TC_BUFS]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + TC_BUFS);
+  float* sU = reinterpret_cast<float*>(tmem_slot + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // this CTA's rectangle of work: GA database tiles x a range of query blocks
+  const int gg = blockIdx.x / G.q_groups, qg = blockIdx.x - gg * G.q_groups;
+  const int gt0 = gg * G.GA;
+  const int ga_count = min(G.GA, G.n_gtiles - gt0);
+  const int qb0 = qg * G.qb_per_group;
+  const int nq = max(0, min(G.qb_per_group, G.n_qblocks - qb0));
+
+  if (threadIdx.x == 0) {
+    tc::mbar_init(a_full, 1);
+    for (int s = 0; s < G.stages; ++s) { tc::mbar_init(b_full + s, 1); tc::mbar_init(b_empty + s, TC_BUFS); }
+    for (int b = 0; b < TC_BUFS; ++b) { tc::mbar_init(t_full + b, 1); tc::mbar_init(t_empty + b, 8); }
+    tc::fence_barrier_init();
+  }
+  const bool dot = M.pair_kind == SGNN_LAYER_DOT;
+  for (int k = threadIdx.x; k < G.K; k += blockDim.x) sU[k] = dot ? 1.f : params[M.u_off + k];
+  if (warp == TC_PROD_WARP) tc::tmem_alloc(tmem_slot, 512);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp >= TC_PROD_WARP) {
+    TcCtaWork Wk{gt0, ga_count, qb0, nq};
+    TcSmem S{sA, sB, a_full, b_full, b_empty, t_full, t_empty, a_bytes, b_bytes};
+    tc_producer_mma_roles(G, Wk, S, Ag, Bg, tmem_base, warp, lane
+#ifdef SGNN_TC_TRACE
+                          , trace
+#endif
+                          );
   } else {
     // ===== epilogue warps =====
     TcEpi E;

@@ -1,0 +1,338 @@
+// All-pairs scorer for SimGNN-style chains on the tensor cores: the tcgen05 GEMM of sgnn_allpairs_tc.cuh delivers the
+// NTN pre-activations m_k(q, g) (layers.py:282-310, factorised per query) of 128 database graphs x 8 queries per
+// tile, and the epilogue -- thread = database graph, two queries at a time -- runs the rest of the chain out of TMEM:
+//   f_k = U_k * inneract(m_k);  hist_b = counts[q][g][b] / (N_q N_g)  (bin counts of the tensor-core histogram,
+//   sgnn_hist_tc.cuh);  Dense head 32 -> 16 -> 8 -> 4 -> 1 (layers.py:192-205 on the pair row);  final_act.
+// The head is BUILD-DEFINED (absent from the reference snapshot; pin = oracle head_layers /
+// pair_forward).  Head weights live in shared memory (U folded into the first 16 rows of layer 0) and are read as
+// warp-uniform 16-byte broadcasts; all multiply-adds are packed FFMA2 (fma.rn.f32x2), two outputs per instruction.
+// A count byte becomes a scaled float with one PRMT + one FMA:  fma(as_float(0x4B000000 | c), s, -2^23 s) = c s
+// exactly rounded.  Shapes served: K = 16 feature maps, head widths 16 / 8 / 4 / 1, 16 bins or no histogram;
+// everything else stays on the CUDA-core kernel (sgnn_head.cu).
+#pragma once
+#include "sgnn_allpairs_tc.cuh"
+
+constexpr int TCH_K = 16, TCH_H0 = 16, TCH_H1 = 8, TCH_H2 = 4;
+// shared-memory weight block (floats)
+constexpr int TCH_W0 = 0;                              // [32][16]  rows 0..15: U_k W0[k][:], rows 16..31: W0[16 + b][:]
+constexpr int TCH_B0 = TCH_W0 + 32 * TCH_H0;           // [16]
+constexpr int TCH_W1 = TCH_B0 + TCH_H0;                // [16][8]
+constexpr int TCH_B1 = TCH_W1 + TCH_H0 * TCH_H1;       // [8]
+constexpr int TCH_W2 = TCH_B1 + TCH_H1;                // [8][4]
+constexpr int TCH_B2 = TCH_W2 + TCH_H1 * TCH_H2;       // [4]
+constexpr int TCH_W3 = TCH_B2 + TCH_H2;                // [4]
+constexpr int TCH_B3 = TCH_W3 + TCH_H2;                // [1] (+3 pad)
+constexpr int TCH_FLOATS = TCH_B3 + 4;
+constexpr int TCH_SMEM_BYTES = TCH_FLOATS * 4 + 16;   // + alignment slack
+
+struct TcHeadEpi {
+  const float* sW;                 // shared-memory weight block
+  int act_ntn, act0, act1, act2, act3, final_act;
+  float yeta;
+  float* sim;
+  int64_t ld;
+  int m, n;
+  const uint8_t* cnt;              // [m][n][16] bin counts (HIST)
+  const int32_t* node_off_q;
+  const int32_t* node_off_db;
+};
+
+// activations other than relu / identity are out of line: the epilogue has to stay small (instruction fetch)
+__device__ __noinline__ float tch_slow_act(float x, int act, float yeta) { return sgnn_act(x, act, yeta); }
+template <int N>
+__device__ __forceinline__ void tch_act(float2* a, int act, float yeta) {
+  if (act == SGNN_ACT_RELU) {
+#pragma unroll
+    for (int i = 0; i < N; ++i) { a[i].x = fmaxf(a[i].x, 0.f); a[i].y = fmaxf(a[i].y, 0.f); }
+  } else if (act != SGNN_ACT_IDENTITY) {
+#pragma unroll
+    for (int i = 0; i < N; ++i) { a[i].x = tch_slow_act(a[i].x, act, yeta); a[i].y = tch_slow_act(a[i].y, act, yeta); }
+  }
+}
+__device__ __forceinline__ float tch_act1(float x, int act, float yeta) {
+  return act == SGNN_ACT_RELU ? fmaxf(x, 0.f) : (act == SGNN_ACT_IDENTITY ? x : tch_slow_act(x, act, yeta));
+}
+// acc[0 .. 2 NW) += f * w[0 .. 4 NW)   (NW float4 = 4 NW columns)
+template <int NW>
+__device__ __forceinline__ void tch_row(float2* acc, float f, const float4* __restrict__ w) {
+  const float2 ff = make_float2(f, f);
+#pragma unroll
+  for (int j = 0; j < NW; ++j) {
+    const float4 ww = w[j];
+    acc[2 * j] = __ffma2_rn(ff, make_float2(ww.x, ww.y), acc[2 * j]);
+    acc[2 * j + 1] = __ffma2_rn(ff, make_float2(ww.z, ww.w), acc[2 * j + 1]);
+  }
+}
+// the same weight row applied to two pairs (one shared-memory read)
+template <int NW>
+__device__ __forceinline__ void tch_row2(float2* accA, float2* accB, float fa, float fb, const float4* __restrict__ w) {
+  const float2 a2 = make_float2(fa, fa), b2 = make_float2(fb, fb);
+#pragma unroll
+  for (int j = 0; j < NW; ++j) {
+    const float4 ww = w[j];
+    const float2 lo = make_float2(ww.x, ww.y), hi = make_float2(ww.z, ww.w);
+    accA[2 * j] = __ffma2_rn(a2, lo, accA[2 * j]);
+    accA[2 * j + 1] = __ffma2_rn(a2, hi, accA[2 * j + 1]);
+    accB[2 * j] = __ffma2_rn(b2, lo, accB[2 * j]);
+    accB[2 * j + 1] = __ffma2_rn(b2, hi, accB[2 * j + 1]);
+  }
+}
+__device__ __forceinline__ float tch_count(unsigned word, int byte, float s, float ms) {   // count * s, exactly rounded
+  return fmaf(__uint_as_float(__byte_perm(word, 0x4B000000u, 0x7440u | (unsigned)byte)), s, ms);
+}
+
+// layers 1.. of the head on two pairs' layer-0 outputs (weight rows read once for both); final similarities in oa / ob
+__device__ __forceinline__ void tch_tail2(const TcHeadEpi& E, const float* sW, float2* a0, float2* b0, float& oa, float& ob) {
+  tch_act<TCH_H0 / 2>(a0, E.act0, E.yeta);
+  tch_act<TCH_H0 / 2>(b0, E.act0, E.yeta);
+  float2 a1[TCH_H1 / 2], b1[TCH_H1 / 2];
+  {
+    const float4* b = reinterpret_cast<const float4*>(sW + TCH_B1);
+#pragma unroll
+    for (int j = 0; j < TCH_H1 / 4; ++j) {
+      const float4 v = b[j];
+      a1[2 * j] = b1[2 * j] = make_float2(v.x, v.y);
+      a1[2 * j + 1] = b1[2 * j + 1] = make_float2(v.z, v.w);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < TCH_H0; ++k)
+    tch_row2<TCH_H1 / 4>(a1, b1, (k & 1) ? a0[k >> 1].y : a0[k >> 1].x, (k & 1) ? b0[k >> 1].y : b0[k >> 1].x,
+                         reinterpret_cast<const float4*>(sW + TCH_W1 + k * TCH_H1));
+  tch_act<TCH_H1 / 2>(a1, E.act1, E.yeta);
+  tch_act<TCH_H1 / 2>(b1, E.act1, E.yeta);
+  float2 a2[TCH_H2 / 2], b2[TCH_H2 / 2];
+  {
+    const float4 v = *reinterpret_cast<const float4*>(sW + TCH_B2);
+    a2[0] = b2[0] = make_float2(v.x, v.y); a2[1] = b2[1] = make_float2(v.z, v.w);
+  }
+#pragma unroll
+  for (int k = 0; k < TCH_H1; ++k)
+    tch_row2<TCH_H2 / 4>(a2, b2, (k & 1) ? a1[k >> 1].y : a1[k >> 1].x, (k & 1) ? b1[k >> 1].y : b1[k >> 1].x,
+                         reinterpret_cast<const float4*>(sW + TCH_W2 + k * TCH_H2));
+  tch_act<TCH_H2 / 2>(a2, E.act2, E.yeta);
+  tch_act<TCH_H2 / 2>(b2, E.act2, E.yeta);
+  const float4 w3 = *reinterpret_cast<const float4*>(sW + TCH_W3);
+  const float c3 = sW[TCH_B3];
+  oa = fmaf(a2[1].y, w3.w, fmaf(a2[1].x, w3.z, fmaf(a2[0].y, w3.y, fmaf(a2[0].x, w3.x, c3))));
+  ob = fmaf(b2[1].y, w3.w, fmaf(b2[1].x, w3.z, fmaf(b2[0].y, w3.y, fmaf(b2[0].x, w3.x, c3))));
+  oa = tch_slow_act(tch_act1(oa, E.act3, E.yeta), E.final_act, E.yeta);
+  ob = tch_slow_act(tch_act1(ob, E.act3, E.yeta), E.final_act, E.yeta);
+}
+
+// Epilogue of one tile part: this thread owns TMEM lane (database graph) g and the accumulator columns of queries
+// [qrow0 + 4 part, + 4) of the tile, processed as two passes of two queries.  The code is kept SMALL on purpose (part
+// is a run-time value, the k loops are rolled in chunks): 16 epilogue warps at different places of a fully unrolled
+// 50 KB epilogue starved on instruction fetch (ncu r2d: stall_no_instruction 5.7 per issue).
+template <bool HIST>
+__device__ __forceinline__ void tc_head_epilogue_part(const TcHeadEpi& E, uint32_t taddr, int qrow0, int part, int g,
+                                                      uint64_t* t_empty, int lane) {
+  const bool gv = g < E.n;
+  int n_g = 1;
+  if (HIST && gv) n_g = E.node_off_db[g + 1] - E.node_off_db[g];
+#pragma unroll 1
+  for (int qp = 0; qp < 2; ++qp) {
+    int opaque = 0;
+    asm volatile("" : "+r"(opaque));   // per pass: the weight reads must not be hoisted out of the loop (register pressure)
+    const float* sW = E.sW + opaque;   // (an offset, so that the pointer stays a shared-memory pointer: LDS, not LD)
+    const int qa = qrow0 + 4 * part + 2 * qp, qb = qa + 1;
+    const bool va = qa < E.m, vb = qb < E.m;
+    uint4 ca = make_uint4(0u, 0u, 0u, 0u), cb = ca;
+    int nqa = 0, nqb = 0;
+    if (HIST) {   // issued first: the loads are in flight while the NTN half runs
+      if (gv && va) ca = __ldg(reinterpret_cast<const uint4*>(E.cnt + ((size_t)qa * E.n + g) * 16));
+      if (gv && vb) cb = __ldg(reinterpret_cast<const uint4*>(E.cnt + ((size_t)qb * E.n + g) * 16));
+      if (va) nqa = E.node_off_q[qa + 1] - E.node_off_q[qa];
+      if (vb) nqb = E.node_off_q[qb + 1] - E.node_off_q[qb];
+    }
+    float2 A[TCH_H0 / 2], B[TCH_H0 / 2];
+    {
+      const float4* b = reinterpret_cast<const float4*>(sW + TCH_B0);
+#pragma unroll
+      for (int j = 0; j < TCH_H0 / 4; ++j) {
+        const float4 x = b[j];
+        A[2 * j] = B[2 * j] = make_float2(x.x, x.y);
+        A[2 * j + 1] = B[2 * j + 1] = make_float2(x.z, x.w);
+      }
+    }
+    // the two queries' m_k in chunks of 8 feature maps (16 live accumulator values instead of 32; the other epilogue
+    // warps of the scheduler cover the TMEM load latency)
+    const uint32_t t0 = taddr + (uint32_t)((4 * part + 2 * qp) * TCH_K);
+#pragma unroll 1
+    for (int kc = 0; kc < TCH_K; kc += 8) {
+      float va8[8], vb8[8];
+      tc::tmem_ld8(t0 + kc, va8);
+      tc::tmem_ld8(t0 + kc + TCH_K, vb8);
+      tc::tmem_ld_wait();
+      if (qp == 1 && kc == TCH_K - 8) {   // last TMEM read of this part: hand the buffer back to its MMA issuer
+        tc::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(t_empty);
+      }
+      const float4* w = reinterpret_cast<const float4*>(sW + TCH_W0 + kc * TCH_H0);
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        tch_row2<TCH_H0 / 4>(A, B, tch_act1(va8[k], E.act_ntn, E.yeta), tch_act1(vb8[k], E.act_ntn, E.yeta),
+                             w + k * (TCH_H0 / 4));
+    }
+    if (HIST) {
+      const float sa = nqa * n_g > 0 ? 1.f / (float)(nqa * n_g) : 0.f;
+      const float sb = nqb * n_g > 0 ? 1.f / (float)(nqb * n_g) : 0.f;
+      const float msa = -8388608.f * sa, msb = -8388608.f * sb;
+#pragma unroll 1
+      for (int wd = 0; wd < 4; ++wd) {   // four bins per count word; the words rotate through .x
+        const float4* w = reinterpret_cast<const float4*>(sW + TCH_W0 + (TCH_K + 4 * wd) * TCH_H0);
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+          tch_row2<TCH_H0 / 4>(A, B, tch_count(ca.x, b, sa, msa), tch_count(cb.x, b, sb, msb), w + b * (TCH_H0 / 4));
+        ca.x = ca.y; ca.y = ca.z; ca.z = ca.w;
+        cb.x = cb.y; cb.y = cb.z; cb.z = cb.w;
+      }
+    }
+    float oa, ob;
+    tch_tail2(E, sW, A, B, oa, ob);
+    if (gv && va) E.sim[(size_t)qa * E.ld + g] = oa;
+    if (gv && vb) E.sim[(size_t)qb * E.ld + g] = ob;
+  }
+}
+
+// Producer and MMA roles of the head kernel: ONE issuer warp for all four TMEM buffers (a tile's epilogue runs for
+// ~20 us, the issue rate does not matter), so the CTA has 18 warps and the epilogue gets 96 registers per thread
+// instead of the 80 that the 21-warp scorer leaves (register allocation is per 4 warps).
+constexpr int TCH_THREADS = 32 * (TC_EPI_WARPS + 2);
+constexpr int TCH_MMA_WARP = TC_EPI_WARPS + 1;
+__device__ __forceinline__ void tch_producer_mma_roles(const TcGeom& G, const TcCtaWork& Wk, const TcSmem& S,
+                                                       const __nv_bfloat16* __restrict__ Ag,
+                                                       const __nv_bfloat16* __restrict__ Bg, uint32_t tmem_base, int warp,
+                                                       int lane) {
+  const int ga_count = Wk.ga_count, nq = Wk.nq;
+  if (lane != 0 || nq <= 0) return;
+  if (warp == TC_PROD_WARP) {
+    tc::mbar_arrive_expect_tx(S.a_full, ga_count * S.a_bytes);
+    for (int ga = 0; ga < ga_count; ++ga)
+      tc::bulk_g2s(S.sA + ga * S.a_bytes, reinterpret_cast<const uint8_t*>(Ag) + (size_t)(Wk.gt0 + ga) * S.a_bytes,
+                   S.a_bytes, S.a_full);
+    for (int i = 0; i < nq; ++i) {
+      const int s = i % G.stages;
+      if (i >= G.stages) tc::mbar_wait(S.b_empty + s, ((i / G.stages) - 1) & 1);
+      tc::mbar_arrive_expect_tx(S.b_full + s, S.b_bytes);
+      tc::bulk_g2s(S.sB + s * S.b_bytes, reinterpret_cast<const uint8_t*>(Bg) + (size_t)(Wk.qb0 + i) * S.b_bytes,
+                   S.b_bytes, S.b_full + s);
+    }
+    return;
+  }
+  const uint32_t idesc = tc::umma_idesc_bf16(128, TC_NPAD);
+  const uint32_t a_part = (G.KCH * 128 * 16) >> 4, b_part = (G.KCH * TC_NPAD * 16) >> 4;   // in 16-byte units
+  const uint32_t a_ks = (2 * 128 * 16) >> 4, b_ks = (2 * TC_NPAD * 16) >> 4;
+  const uint64_t a_desc0 = tc::umma_desc(tc::smem_u32(S.sA), 128 * 16, 128);
+  const uint64_t b_desc0 = tc::umma_desc(tc::smem_u32(S.sB), TC_NPAD * 16, 128);
+  const uint32_t a_tile = (uint32_t)S.a_bytes >> 4, b_tile = (uint32_t)S.b_bytes >> 4;
+  const int combos = G.parts == 2 ? 3 : 1, ksteps = G.KCH / 2;
+  tc::mbar_wait(S.a_full, 0);
+  int it = 0;
+  for (int i = 0; i < nq; ++i) {   // tile order: query block i outer, database tile ga inner (as the epilogue walks it)
+    const int s = i % G.stages;
+    tc::mbar_wait(S.b_full + s, (i / G.stages) & 1);
+    const uint64_t bd0 = b_desc0 + (uint64_t)((uint32_t)s * b_tile);
+    for (int ga = 0; ga < ga_count; ++ga, ++it) {
+      const int buf = it & (TC_BUFS - 1);
+      if (it >= TC_BUFS) tc::mbar_wait(S.t_empty + buf, ((it / TC_BUFS) - 1) & 1);
+      tc::tc_fence_after();
+      const uint64_t ad0 = a_desc0 + (uint64_t)((uint32_t)ga * a_tile);
+      const uint32_t d_addr = tmem_base + (uint32_t)buf * TC_NPAD;
+      uint32_t acc = 0;
+      for (int c = 0; c < combos; ++c) {   // (hi,hi) (hi,lo) (lo,hi)
+        const uint32_t ao = c == 2 ? a_part : 0u, bo = c == 1 ? b_part : 0u;
+        for (int ks = 0; ks < ksteps; ++ks) {
+          tc::umma_bf16(d_addr, ad0 + ao + (uint64_t)(ks * a_ks), bd0 + bo + (uint64_t)(ks * b_ks), idesc, acc);
+          acc = 1;
+        }
+      }
+      tc::umma_commit(S.t_full + buf);
+    }
+    if (nq > G.stages) tc::umma_commit(S.b_empty + s);   // the stage is free once this block's MMAs have completed
+  }
+}
+
+template <bool HIST>
+__global__ void __launch_bounds__(TCH_THREADS, 1)
+allpairs_tc_head_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const float* __restrict__ params,
+                        const __nv_bfloat16* __restrict__ Ag, const __nv_bfloat16* __restrict__ Bg,
+                        float* __restrict__ sim, int64_t ld, const uint8_t* __restrict__ cnt,
+                        const int32_t* __restrict__ node_off_q, const int32_t* __restrict__ node_off_db) {
+  extern __shared__ __align__(1024) uint8_t tc_smem[];
+  uint8_t* smem = tc_smem;
+  const int a_bytes = tc_a_bytes(G), b_bytes = tc_b_bytes(G);
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + TC_GA_MAX * a_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + G.stages * b_bytes);
+  uint64_t* a_full = bars;
+  uint64_t* b_full = bars + 1;
+  uint64_t* b_empty = b_full + G.stages;
+  uint64_t* t_full = b_empty + G.stages;
+  uint64_t* t_empty = t_full + TC_BUFS;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + TC_BUFS);
+  // TCH_FLOATS, 16-byte aligned (pointer arithmetic, not an integer round trip: the pointer stays a shared-memory pointer)
+  float* sW = reinterpret_cast<float*>(tmem_slot + 4) + (((16u - (tc::smem_u32(tmem_slot + 4) & 15u)) & 15u) >> 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int gg = blockIdx.x / G.q_groups, qg = blockIdx.x - gg * G.q_groups;
+  const int gt0 = gg * G.GA;
+  const int ga_count = min(G.GA, G.n_gtiles - gt0);
+  const int qb0 = qg * G.qb_per_group;
+  const int nq = max(0, min(G.qb_per_group, G.n_qblocks - qb0));
+
+  if (threadIdx.x == 0) {
+    tc::mbar_init(a_full, 1);
+    for (int s = 0; s < G.stages; ++s) { tc::mbar_init(b_full + s, 1); tc::mbar_init(b_empty + s, 1); }
+    for (int b = 0; b < TC_BUFS; ++b) { tc::mbar_init(t_full + b, 1); tc::mbar_init(t_empty + b, 8); }
+    tc::fence_barrier_init();
+  }
+  // ---- head weights: U folded into the NTN rows of layer 0, missing biases = 0 ----
+  for (int i = threadIdx.x; i < TCH_FLOATS; i += blockDim.x) {
+    float w = 0.f;
+    if (i < TCH_B0) {
+      const int r = i / TCH_H0, j = i - r * TCH_H0;
+      if (r < M.Hd[0].din) w = params[M.Hd[0].w_off + r * TCH_H0 + j] * (r < TCH_K ? params[M.u_off + r] : 1.f);
+    } else if (i < TCH_W1) { if (M.Hd[0].bias) w = params[M.Hd[0].b_off + (i - TCH_B0)]; }
+    else if (i < TCH_B1) w = params[M.Hd[1].w_off + (i - TCH_W1)];
+    else if (i < TCH_W2) { if (M.Hd[1].bias) w = params[M.Hd[1].b_off + (i - TCH_B1)]; }
+    else if (i < TCH_B2) w = params[M.Hd[2].w_off + (i - TCH_W2)];
+    else if (i < TCH_W3) { if (M.Hd[2].bias) w = params[M.Hd[2].b_off + (i - TCH_B2)]; }
+    else if (i < TCH_B3) w = params[M.Hd[3].w_off + (i - TCH_W3)];
+    else if (i == TCH_B3) { if (M.Hd[3].bias) w = params[M.Hd[3].b_off]; }
+    sW[i] = w;
+  }
+  if (warp == TC_PROD_WARP) tc::tmem_alloc(tmem_slot, 512);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp >= TC_PROD_WARP) {
+    TcCtaWork Wk{gt0, ga_count, qb0, nq};
+    TcSmem S{sA, sB, a_full, b_full, b_empty, t_full, t_empty, a_bytes, b_bytes};
+    tch_producer_mma_roles(G, Wk, S, Ag, Bg, tmem_base, warp, lane);
+  } else {
+    TcHeadEpi E;
+    E.sW = sW; E.act_ntn = M.pair_act; E.act0 = M.Hd[0].act; E.act1 = M.Hd[1].act; E.act2 = M.Hd[2].act;
+    E.act3 = M.Hd[3].act; E.final_act = M.final_act; E.yeta = M.yeta;
+    E.sim = sim; E.ld = ld; E.m = G.m; E.n = G.n; E.cnt = cnt; E.node_off_q = node_off_q; E.node_off_db = node_off_db;
+    const int lg = warp & 3, part = (warp >> 2) & 1, grp = warp >> 3;
+    const int total = nq * ga_count;
+    int i = grp / ga_count, ga = grp - i * ga_count;
+    for (int it = grp; it < total; it += TC_EPI_GROUPS) {
+      const int buf = it & (TC_BUFS - 1);
+      tc::mbar_wait(t_full + buf, (it / TC_BUFS) & 1);
+      tc::tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + buf * TC_NPAD;
+      const int g = (gt0 + ga) * 128 + lg * 32 + lane;
+      tc_head_epilogue_part<HIST>(E, taddr, (qb0 + i) * G.QH, part, g, t_empty + buf, lane);
+      ga += TC_EPI_GROUPS;
+      while (ga >= ga_count) { ga -= ga_count; ++i; }
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == TC_PROD_WARP) tc::tmem_dealloc(tmem_base, 512);
+}

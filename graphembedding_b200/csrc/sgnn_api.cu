@@ -323,6 +323,13 @@ bool hist_tc_enabled(SgnnHandle h) {
          h->cfg.precision != SGNN_PREC_FP32;
 }
 
+// NTN + Dense head in the epilogue of the tcgen05 scorer (SGNN_HEAD_TC=0: keep the CUDA-core head kernel)
+bool head_tc_enabled(SgnnHandle h) {
+  static const bool off = [] { const char* e = getenv("SGNN_HEAD_TC"); return e && e[0] == '0'; }();
+  return !off && h->cfg.precision != SGNN_PREC_FP32 && sgnn_tc_head_supported(h->M) &&
+         (h->M.hist_bins == 0 || hist_tc_enabled(h));
+}
+
 int ensure_query_tables(SgnnHandle h, int64_t m) {
   if (m <= h->cap_P) return 0;
   return fail(h, "query table workspace too small: call sgnn_reserve(max_queries >= m) first");
@@ -338,12 +345,16 @@ enum { SCORE_PREP_Q = 1, SCORE_PREP_DB = 2, SCORE_MAIN = 4, SCORE_ALL = 7,
        SCORE_COEF_ONLY = 8, SCORE_COEF_READY = 16 };
 
 // tcgen05 path of sgnn_score_all_pairs (SGNN_PREC_BF16X3 / SGNN_PREC_BF16)
+// head: the SimGNN-style head runs in the scorer's epilogue (sgnn_allpairs_tc_head.cuh): K accumulator columns per
+// query (no |x| sum column), cnt = count matrix of the tensor-core histogram (NULL without a Histogram layer)
 int score_all_pairs_tc(SgnnHandle h, const float* emb_q, int m, const float* emb_db, int n, float* sim,
-                       int64_t ld, cudaStream_t st, int stages, unsigned long long* smax) {
+                       int64_t ld, cudaStream_t st, int stages, unsigned long long* smax, bool head = false,
+                       const uint8_t* cnt = nullptr, const int32_t* node_off_q = nullptr,
+                       const int32_t* node_off_db = nullptr) {
   const ModelDev& M = h->M;
   const bool ntn = M.pair_kind == SGNN_LAYER_NTN;
   TcGeom G;
-  const bool relu = ntn && M.pair_act == SGNN_ACT_RELU;
+  const bool relu = !head && ntn && M.pair_act == SGNN_ACT_RELU;
   const bool ref = ntn && M.ntn_mode == SGNN_NTN_REFERENCE;
   const bool simk = M.final_act == SGNN_ACT_SIM_KERNEL;
   G.m = m; G.n = n; G.D = M.emb_dim; G.K = ntn ? M.K : 1;
@@ -365,7 +376,7 @@ int score_all_pairs_tc(SgnnHandle h, const float* emb_q, int m, const float* emb
   const int64_t need_b = (int64_t)G.n_qblocks * G.parts * G.KCH * (TC_NPAD * 8);
   if (need_a > h->cap_Atc || need_b > h->cap_Btc)
     return fail(h, "tensor-core operand workspace too small: call sgnn_reserve(max_queries, max_db) first");
-  const size_t fixed = (size_t)TC_GA_MAX * tc_a_bytes(G) + TC_TAIL_BYTES + 1024;
+  const size_t fixed = (size_t)TC_GA_MAX * tc_a_bytes(G) + TC_TAIL_BYTES + 1024 + (head ? sgnn_tc_head_smem_bytes() : 0);
   if (fixed + 2 * (size_t)tc_b_bytes(G) > (size_t)h->smem_optin)
     return fail(h, "embedding too wide for the tensor-core all-pairs tiles");
   G.stages = (int)std::min<size_t>(std::min(G.qb_per_group, TC_MAX_STAGES), ((size_t)h->smem_optin - fixed) / tc_b_bytes(G));
@@ -378,7 +389,8 @@ int score_all_pairs_tc(SgnnHandle h, const float* emb_q, int m, const float* emb
     e = sgnn_tc_prep_q(M, G, h->d_params, emb_q, h->d_Btc, h->d_coef, (stages & SCORE_COEF_READY) ? 2 : 0, st);
   if (e == cudaSuccess && (stages & SCORE_PREP_DB)) e = sgnn_tc_prep_db(M, G, emb_db, h->d_Atc, st);
   if (e == cudaSuccess && (stages & SCORE_MAIN))
-    e = sgnn_tc_score(M, G, relu, ref, simk, grid, smem, h->d_params, h->d_Atc, h->d_Btc, sim, ld, smax, st);
+    e = head ? sgnn_tc_score_head(M, G, grid, smem, h->d_params, h->d_Atc, h->d_Btc, sim, ld, cnt, node_off_q, node_off_db, st)
+             : sgnn_tc_score(M, G, relu, ref, simk, grid, smem, h->d_params, h->d_Atc, h->d_Btc, sim, ld, smax, st);
   if (e != cudaSuccess) return fail(h, std::string("tensor-core all-pairs launch: ") + cudaGetErrorString(e));
   return 0;
 }
@@ -427,6 +439,13 @@ int score_all_pairs_stages(SgnnHandle h, const float* emb_q, int32_t m, const fl
     // histogram on the tensor cores (sgnn_hist_tc.cuh) whenever the shapes fit, else the CUDA-core kernel counts.
     // A side's operand is prepared whenever THAT side fits (the other side may not be known yet); the scorer stage
     // decides with both.
+    // the rest of the chain (NTN + Dense head) on the tensor-core scorer when the head has the shape that kernel
+    // serves; its operands are prepared beside the CUDA-core tables (which side decides is only known at the scorer)
+    const bool head_tc = head_tc_enabled(h);
+    if (head_tc) {
+      const int prep = stages & (SCORE_PREP_Q | SCORE_PREP_DB | SCORE_COEF_ONLY | SCORE_COEF_READY);
+      if (prep && score_all_pairs_tc(h, emb_q, m, emb_db, n, sim_dev, ld, st, prep, nullptr, true)) return 1;
+    }
     const bool tc_on = hist_tc_enabled(h);
     const bool tc_q = tc_on && need_q && sgnn_hist_tc_supported(M.node_dim, M.hist_bins, h->hside[0].max_nodes, 1);
     const bool tc_db = tc_on && need_db && sgnn_hist_tc_supported(M.node_dim, M.hist_bins, 1, h->hside[1].max_nodes);
@@ -453,6 +472,11 @@ int score_all_pairs_stages(SgnnHandle h, const float* emb_q, int32_t m, const fl
       CUDA_OK(h, sgnn_hist_tc_prep_db(HG, h->hside[1].rows, h->hside[1].node_off, h->ht, st));
     if (!(stages & SCORE_MAIN)) return 0;
     cudaError_t e;
+    if (head_tc && (M.hist_bins == 0 || tc_hist)) {
+      if (tc_hist) CUDA_OK(h, sgnn_hist_tc_run(HG, h->ht, h->hside[1].node_off, h->sm_count, st));
+      return score_all_pairs_tc(h, emb_q, m, emb_db, n, sim_dev, ld, st, SCORE_MAIN, nullptr, true,
+                                tc_hist ? h->ht.cnt : nullptr, h->hside[0].node_off, h->hside[1].node_off);
+    }
     if (tc_hist) {
       CUDA_OK(h, sgnn_hist_tc_run(HG, h->ht, h->hside[1].node_off, h->sm_count, st));
       e = sgnn_launch_allpairs_head_counts(M, h->dep, h->d_params, h->d_P, h->d_C, emb_db, h->hside[0].node_off,

@@ -1,6 +1,7 @@
 // Translation unit of the tcgen05 all-pairs scorer (kernels in sgnn_allpairs_tc.cuh).
 #include <cstdlib>
 #include "sgnn_allpairs_tc.cuh"
+#include "sgnn_allpairs_tc_head.cuh"
 
 namespace {
 
@@ -74,4 +75,30 @@ cudaError_t sgnn_tc_score(const ModelDev& M, const TcGeom& G, bool relu, bool re
   if (G.K == 10) return dispatch<10>(relu, ref, simk, M, G, grid, smem, params, A, B, sim, ld, smax, st);
   if (G.K == 16) return dispatch<16>(relu, ref, simk, M, G, grid, smem, params, A, B, sim, ld, smax, st);
   return dispatch<0>(relu, ref, simk, M, G, grid, smem, params, A, B, sim, ld, smax, st);
+}
+
+// ---- SimGNN-style head on the tensor-core scorer (sgnn_allpairs_tc_head.cuh) ----
+bool sgnn_tc_head_supported(const ModelDev& M) {
+  if (M.pair_kind != SGNN_LAYER_NTN || M.K != TCH_K || M.n_head != 4) return false;
+  if (M.hist_bins != 0 && M.hist_bins != 16) return false;
+  const int din0 = TCH_K + M.hist_bins;
+  return M.Hd[0].din == din0 && M.Hd[0].dout == TCH_H0 && M.Hd[1].din == TCH_H0 && M.Hd[1].dout == TCH_H1 &&
+         M.Hd[2].din == TCH_H1 && M.Hd[2].dout == TCH_H2 && M.Hd[3].din == TCH_H2 && M.Hd[3].dout == 1 &&
+         !M.Hd[0].drop && !M.Hd[1].drop && !M.Hd[2].drop && !M.Hd[3].drop;
+}
+int sgnn_tc_head_smem_bytes() { return TCH_SMEM_BYTES; }
+
+cudaError_t sgnn_tc_score_head(const ModelDev& M, const TcGeom& G, int grid, size_t smem, const float* params,
+                               const void* A_ws, const void* B_ws, float* sim, int64_t ld, const uint8_t* cnt,
+                               const int32_t* node_off_q, const int32_t* node_off_db, cudaStream_t st) {
+  if (!sgnn_tc_head_supported(M) || G.KC != TCH_K || G.QH != 8) return cudaErrorInvalidValue;
+  const __nv_bfloat16* A = static_cast<const __nv_bfloat16*>(A_ws);
+  const __nv_bfloat16* B = static_cast<const __nv_bfloat16*>(B_ws);
+  auto launch_it = [&](auto kern) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    kern<<<grid, TCH_THREADS, smem, st>>>(M, G, params, A, B, sim, ld, cnt, node_off_q, node_off_db);
+    return cudaGetLastError();
+  };
+  return M.hist_bins > 0 ? launch_it(allpairs_tc_head_kernel<true>) : launch_it(allpairs_tc_head_kernel<false>);
 }

@@ -65,4 +65,11 @@ cudaError_t sgnn_tc_score(const ModelDev& M, const TcGeom& G, bool relu, bool re
                           const float* params, const void* A_ws, const void* B_ws, float* sim, int64_t ld,
                           unsigned long long* smax, cudaStream_t st);
 // smax (optional): [m][4 * n_gtiles] largest rank key of every 32-graph slice of every sim row (sgnn_launch_topk_hint)
+// SimGNN-style head on the scorer's epilogue (sgnn_allpairs_tc_head.cuh): K = 16, head widths 16 / 8 / 4 / 1, no head
+// dropout, 16 bins (cnt = the tensor-core histogram's count matrix) or no histogram; G must be built with KC == K
+bool sgnn_tc_head_supported(const ModelDev& M);
+int sgnn_tc_head_smem_bytes();
+cudaError_t sgnn_tc_score_head(const ModelDev& M, const TcGeom& G, int grid, size_t smem, const float* params,
+                               const void* A_ws, const void* B_ws, float* sim, int64_t ld, const uint8_t* cnt,
+                               const int32_t* node_off_q, const int32_t* node_off_db, cudaStream_t st);
 inline int tc_n_slices(int n) { return ((n + 127) / 128) * 4; }

@@ -43,7 +43,8 @@ def pad_from_packed(batch, dtype=torch.float32):
     return lab_t, torch.as_tensor(A).to(dtype), lab_t >= 0, torch.as_tensor(counts.astype(np.int64))
 
 
-def embed(layers, P, lab, A, mask, n, dtype=torch.float32):
+def embed(layers, P, lab, A, mask, n, dtype=torch.float32, with_nodes=False):
+    """Pooled representations [G, emb]; with_nodes: also the last node-level rows [G, N, d] (zero beyond n)."""
     mf = mask.to(dtype).unsqueeze(-1)
     x = None
     for li, L in enumerate(layers):
@@ -72,12 +73,14 @@ def embed(layers, P, lab, A, mask, n, dtype=torch.float32):
             out[:, :keep] = torch.where(mask[:, :keep].unsqueeze(-1), x[:, :keep], out[:, :keep])
             return out.reshape(G, M * d)
         elif k == 'Average':
-            return x.sum(1) / n.to(dtype).unsqueeze(-1)
+            out = x.sum(1) / n.to(dtype).unsqueeze(-1)
+            return (out, x) if with_nodes else out
         elif k == 'Attention':
             mean = x.sum(1) / n.to(dtype).unsqueeze(-1)
             c = torch.tanh(mean @ P[(li, 'weights')])
             att = torch.sigmoid(torch.einsum('gnd,gd->gn', x, c)) * mask.to(dtype)
-            return torch.einsum('gn,gnd->gd', att, x)
+            out = torch.einsum('gn,gnd->gd', att, x)
+            return (out, x) if with_nodes else out
     raise RuntimeError('no pooling layer')
 
 
@@ -113,6 +116,41 @@ def score_all_pairs(layers, P, xq, xd, ntn_mode='reference', final_act='sim_kern
         t = O._act(L['inneract'])(m)
         raw = U.sum() * t.sum(1) if ntn_mode == 'reference' else torch.einsum('k,qkg->qg', U, t)
     return O._act(final_act, yeta)(raw)
+
+
+def score_all_pairs_head(layers, P, xq, hq, nq, xd, hd, nd, final_act='sigmoid', yeta=0.6):
+    """All-pairs scores of a SimGNN-style chain (oracle head_layers / pair_forward / pair_histogram, batched):
+    NTN K-vector f_k = U_k inneract(m_k), node-node histogram of sigmoid(Hq_i . Hd_j) over the real cells,
+    Dense head on [f | hist].  hq [Q,Nq,d], hd [M,Nd,d] zero-padded node rows, nq / nd node counts."""
+    li, L = _pair_layer(layers)
+    _, tail = O.head_layers(layers)
+    W, V, U = P[(li, 'weights_W')], P[(li, 'weights_V')], P[(li, 'weights_U')].reshape(-1)
+    D = xq.shape[1]
+    Pq = torch.einsum('qa,abk->qkb', xq, W) + V[:, D:].unsqueeze(0)
+    c = xq @ V[:, :D].t()
+    if L['bias']:
+        c = c + P[(li, 'bias')]
+    m = torch.einsum('qkb,gb->qgk', Pq, xd) + c.unsqueeze(1)
+    f = U * O._act(L['inneract'])(m)                                          # [Q,M,K]
+    for hi, HL in tail:
+        if HL['kind'] == 'Histogram':
+            B = HL['bins']
+            Q, M = xq.shape[0], xd.shape[0]
+            s = torch.sigmoid(torch.einsum('qid,gjd->qgij', hq, hd))
+            idx = torch.clamp((s * B).floor().long(), max=B - 1)
+            valid = (torch.arange(hq.shape[1]).unsqueeze(0) < nq.unsqueeze(1)).view(Q, 1, -1, 1) & \
+                    (torch.arange(hd.shape[1]).unsqueeze(0) < nd.unsqueeze(1)).view(1, M, 1, -1)
+            idx = torch.where(valid, idx, torch.full_like(idx, B))               # padding cells -> a discarded bin
+            counts = torch.zeros((Q, M, B + 1), dtype=f.dtype)
+            counts.scatter_add_(2, idx.reshape(Q, M, -1), torch.ones((Q, M, idx.shape[2] * idx.shape[3]), dtype=f.dtype))
+            cells = (nq.view(Q, 1) * nd.view(1, M)).clamp(min=1).to(f.dtype)
+            f = torch.cat([f, counts[:, :, :B] / cells.unsqueeze(-1)], -1)
+        else:
+            f = f @ P[(hi, 'weights')]
+            if HL['bias']:
+                f = f + P[(hi, 'bias')]
+            f = O._act(HL['act'])(f)
+    return O._act(final_act, yeta)(f.squeeze(-1))
 
 
 def train_step(layers, flat, adam, lab, A, mask, n, g1, g2, targets, final_act='sim_kernel', yeta=0.6,

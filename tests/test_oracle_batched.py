@@ -63,3 +63,23 @@ def test_pair_histogram_known_answers():
     assert counts[7] == 4 and (s <= 1.0).all()
     hist, counts, s = O.pair_histogram(h1, -h1, 8)
     assert counts[0] == 4
+
+
+@pytest.mark.parametrize('cfg', ['simgnn', 'head_drop', 'head_nohist'])
+def test_batched_head_scores_equal_per_pair_oracle(cfg):
+    """The batched SimGNN-style all-pairs port (bench.py's cpu_baseline for the headline model) against the
+    per-pair restatement (oracle pair_forward with head + pair_histogram), fp64, every cell."""
+    gs = corpus(26, 2, 10, seed=4)
+    enc = encoder_for(gs)
+    layers = O.parse_layer_specs(CONFIGS[cfg], enc.input_dim())
+    flat = O.init_params(layers, 5)
+    P = O.unflatten(layers, flat, torch.float64)
+    og = oracle_graphs(gs, enc)
+    lab, A, mask, n = OB.pad_graphs(og, enc.input_dim(), torch.float64)
+    emb, rows = OB.embed(layers, P, lab, A, mask, n, torch.float64, with_nodes=True)
+    m = 6
+    sim = OB.score_all_pairs_head(layers, P, emb[:m], rows[:m], n[:m], emb[m:], rows[m:], n[m:], final_act='sigmoid')
+    g1s = [og[i] for i in range(m) for _ in range(len(og) - m)]
+    g2s = [og[m + j] for _ in range(m) for j in range(len(og) - m)]
+    ref = torch.sigmoid(O.forward_pairs(layers, P, g1s, g2s, enc.input_dim(), torch.float64)).reshape(m, -1)
+    assert torch.allclose(sim, ref, rtol=1e-10, atol=1e-12)

@@ -37,85 +37,92 @@ struct TcHeadEpi {
   const int32_t* node_off_db;
 };
 
+// Packed pairs of floats live in 64-bit registers (fma.rn.f32x2 operands): with float2 the compiler keeps the halves
+// as separate scalars and shuffles them into aligned pairs around every FFMA2 (300 MOVs per pass).
+typedef unsigned long long tch_f2;
+__device__ __forceinline__ tch_f2 tch_pack(float lo, float hi) {
+  tch_f2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void tch_unpack(tch_f2 v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ void tch_fma2(tch_f2& d, tch_f2 a, tch_f2 b) {
+  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b));
+}
 // activations other than relu / identity are out of line: the epilogue has to stay small (instruction fetch)
 __device__ __noinline__ float tch_slow_act(float x, int act, float yeta) { return sgnn_act(x, act, yeta); }
-template <int N>
-__device__ __forceinline__ void tch_act(float2* a, int act, float yeta) {
-  if (act == SGNN_ACT_RELU) {
-#pragma unroll
-    for (int i = 0; i < N; ++i) { a[i].x = fmaxf(a[i].x, 0.f); a[i].y = fmaxf(a[i].y, 0.f); }
-  } else if (act != SGNN_ACT_IDENTITY) {
-#pragma unroll
-    for (int i = 0; i < N; ++i) { a[i].x = tch_slow_act(a[i].x, act, yeta); a[i].y = tch_slow_act(a[i].y, act, yeta); }
-  }
-}
 __device__ __forceinline__ float tch_act1(float x, int act, float yeta) {
   return act == SGNN_ACT_RELU ? fmaxf(x, 0.f) : (act == SGNN_ACT_IDENTITY ? x : tch_slow_act(x, act, yeta));
 }
-// acc[0 .. 2 NW) += f * w[0 .. 4 NW)   (NW float4 = 4 NW columns)
-template <int NW>
-__device__ __forceinline__ void tch_row(float2* acc, float f, const float4* __restrict__ w) {
-  const float2 ff = make_float2(f, f);
+template <int N>
+__device__ __forceinline__ void tch_act(tch_f2* a, int act, float yeta) {
+  if (act == SGNN_ACT_IDENTITY) return;
 #pragma unroll
-  for (int j = 0; j < NW; ++j) {
-    const float4 ww = w[j];
-    acc[2 * j] = __ffma2_rn(ff, make_float2(ww.x, ww.y), acc[2 * j]);
-    acc[2 * j + 1] = __ffma2_rn(ff, make_float2(ww.z, ww.w), acc[2 * j + 1]);
+  for (int i = 0; i < N; ++i) {
+    float lo, hi;
+    tch_unpack(a[i], lo, hi);
+    a[i] = tch_pack(tch_act1(lo, act, yeta), tch_act1(hi, act, yeta));
   }
 }
-// the same weight row applied to two pairs (one shared-memory read)
+// the same weight row (NW x 16 bytes = 4 NW columns) applied to two pairs: one shared-memory read per 16 bytes
 template <int NW>
-__device__ __forceinline__ void tch_row2(float2* accA, float2* accB, float fa, float fb, const float4* __restrict__ w) {
-  const float2 a2 = make_float2(fa, fa), b2 = make_float2(fb, fb);
+__device__ __forceinline__ void tch_row2(tch_f2* accA, tch_f2* accB, float fa, float fb, const float4* __restrict__ w) {
+  const tch_f2 a2 = tch_pack(fa, fa), b2 = tch_pack(fb, fb);
+  const ulonglong2* w2 = reinterpret_cast<const ulonglong2*>(w);
 #pragma unroll
   for (int j = 0; j < NW; ++j) {
-    const float4 ww = w[j];
-    const float2 lo = make_float2(ww.x, ww.y), hi = make_float2(ww.z, ww.w);
-    accA[2 * j] = __ffma2_rn(a2, lo, accA[2 * j]);
-    accA[2 * j + 1] = __ffma2_rn(a2, hi, accA[2 * j + 1]);
-    accB[2 * j] = __ffma2_rn(b2, lo, accB[2 * j]);
-    accB[2 * j + 1] = __ffma2_rn(b2, hi, accB[2 * j + 1]);
+    const ulonglong2 ww = w2[j];
+    tch_fma2(accA[2 * j], a2, ww.x);
+    tch_fma2(accA[2 * j + 1], a2, ww.y);
+    tch_fma2(accB[2 * j], b2, ww.x);
+    tch_fma2(accB[2 * j + 1], b2, ww.y);
   }
+}
+template <int NW>
+__device__ __forceinline__ void tch_bias2(tch_f2* a, tch_f2* b, const float* __restrict__ src) {
+  const ulonglong2* w2 = reinterpret_cast<const ulonglong2*>(src);
+#pragma unroll
+  for (int j = 0; j < NW; ++j) {
+    const ulonglong2 ww = w2[j];
+    a[2 * j] = b[2 * j] = ww.x;
+    a[2 * j + 1] = b[2 * j + 1] = ww.y;
+  }
+}
+__device__ __forceinline__ float tch_half(tch_f2 v, int hi) {
+  float a, b;
+  tch_unpack(v, a, b);
+  return hi ? b : a;
 }
 __device__ __forceinline__ float tch_count(unsigned word, int byte, float s, float ms) {   // count * s, exactly rounded
   return fmaf(__uint_as_float(__byte_perm(word, 0x4B000000u, 0x7440u | (unsigned)byte)), s, ms);
 }
 
 // layers 1.. of the head on two pairs' layer-0 outputs (weight rows read once for both); final similarities in oa / ob
-__device__ __forceinline__ void tch_tail2(const TcHeadEpi& E, const float* sW, float2* a0, float2* b0, float& oa, float& ob) {
+__device__ __forceinline__ void tch_tail2(const TcHeadEpi& E, const float* sW, tch_f2* a0, tch_f2* b0, float& oa, float& ob) {
   tch_act<TCH_H0 / 2>(a0, E.act0, E.yeta);
   tch_act<TCH_H0 / 2>(b0, E.act0, E.yeta);
-  float2 a1[TCH_H1 / 2], b1[TCH_H1 / 2];
-  {
-    const float4* b = reinterpret_cast<const float4*>(sW + TCH_B1);
-#pragma unroll
-    for (int j = 0; j < TCH_H1 / 4; ++j) {
-      const float4 v = b[j];
-      a1[2 * j] = b1[2 * j] = make_float2(v.x, v.y);
-      a1[2 * j + 1] = b1[2 * j + 1] = make_float2(v.z, v.w);
-    }
-  }
+  tch_f2 a1[TCH_H1 / 2], b1[TCH_H1 / 2];
+  tch_bias2<TCH_H1 / 4>(a1, b1, sW + TCH_B1);
 #pragma unroll
   for (int k = 0; k < TCH_H0; ++k)
-    tch_row2<TCH_H1 / 4>(a1, b1, (k & 1) ? a0[k >> 1].y : a0[k >> 1].x, (k & 1) ? b0[k >> 1].y : b0[k >> 1].x,
+    tch_row2<TCH_H1 / 4>(a1, b1, tch_half(a0[k >> 1], k & 1), tch_half(b0[k >> 1], k & 1),
                          reinterpret_cast<const float4*>(sW + TCH_W1 + k * TCH_H1));
   tch_act<TCH_H1 / 2>(a1, E.act1, E.yeta);
   tch_act<TCH_H1 / 2>(b1, E.act1, E.yeta);
-  float2 a2[TCH_H2 / 2], b2[TCH_H2 / 2];
-  {
-    const float4 v = *reinterpret_cast<const float4*>(sW + TCH_B2);
-    a2[0] = b2[0] = make_float2(v.x, v.y); a2[1] = b2[1] = make_float2(v.z, v.w);
-  }
+  tch_f2 a2[TCH_H2 / 2], b2[TCH_H2 / 2];
+  tch_bias2<TCH_H2 / 4>(a2, b2, sW + TCH_B2);
 #pragma unroll
   for (int k = 0; k < TCH_H1; ++k)
-    tch_row2<TCH_H2 / 4>(a2, b2, (k & 1) ? a1[k >> 1].y : a1[k >> 1].x, (k & 1) ? b1[k >> 1].y : b1[k >> 1].x,
+    tch_row2<TCH_H2 / 4>(a2, b2, tch_half(a1[k >> 1], k & 1), tch_half(b1[k >> 1], k & 1),
                          reinterpret_cast<const float4*>(sW + TCH_W2 + k * TCH_H2));
   tch_act<TCH_H2 / 2>(a2, E.act2, E.yeta);
   tch_act<TCH_H2 / 2>(b2, E.act2, E.yeta);
   const float4 w3 = *reinterpret_cast<const float4*>(sW + TCH_W3);
   const float c3 = sW[TCH_B3];
-  oa = fmaf(a2[1].y, w3.w, fmaf(a2[1].x, w3.z, fmaf(a2[0].y, w3.y, fmaf(a2[0].x, w3.x, c3))));
-  ob = fmaf(b2[1].y, w3.w, fmaf(b2[1].x, w3.z, fmaf(b2[0].y, w3.y, fmaf(b2[0].x, w3.x, c3))));
+  oa = fmaf(tch_half(a2[1], 1), w3.w, fmaf(tch_half(a2[1], 0), w3.z, fmaf(tch_half(a2[0], 1), w3.y, fmaf(tch_half(a2[0], 0), w3.x, c3))));
+  ob = fmaf(tch_half(b2[1], 1), w3.w, fmaf(tch_half(b2[1], 0), w3.z, fmaf(tch_half(b2[0], 1), w3.y, fmaf(tch_half(b2[0], 0), w3.x, c3))));
   oa = tch_slow_act(tch_act1(oa, E.act3, E.yeta), E.final_act, E.yeta);
   ob = tch_slow_act(tch_act1(ob, E.act3, E.yeta), E.final_act, E.yeta);
 }
@@ -145,16 +152,8 @@ __device__ __forceinline__ void tc_head_epilogue_part(const TcHeadEpi& E, uint32
       if (va) nqa = E.node_off_q[qa + 1] - E.node_off_q[qa];
       if (vb) nqb = E.node_off_q[qb + 1] - E.node_off_q[qb];
     }
-    float2 A[TCH_H0 / 2], B[TCH_H0 / 2];
-    {
-      const float4* b = reinterpret_cast<const float4*>(sW + TCH_B0);
-#pragma unroll
-      for (int j = 0; j < TCH_H0 / 4; ++j) {
-        const float4 x = b[j];
-        A[2 * j] = B[2 * j] = make_float2(x.x, x.y);
-        A[2 * j + 1] = B[2 * j + 1] = make_float2(x.z, x.w);
-      }
-    }
+    tch_f2 A[TCH_H0 / 2], B[TCH_H0 / 2];
+    tch_bias2<TCH_H0 / 4>(A, B, sW + TCH_B0);
     // the two queries' m_k in chunks of 8 feature maps (16 live accumulator values instead of 32; the other epilogue
     // warps of the scheduler cover the TMEM load latency)
     const uint32_t t0 = taddr + (uint32_t)((4 * part + 2 * qp) * TCH_K);

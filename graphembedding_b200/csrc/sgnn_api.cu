@@ -577,9 +577,19 @@ int run_cached(SgnnHandle h, GraphCache& cache, uint64_t key, cudaStream_t st, F
 }  // namespace
 
 namespace {
+// The Padding pool appends max_in_dims - N rows (layers.py:223-227): tf.pad raises for N > max_in_dims, and so do the
+// entry points that take a batch (the kernels would otherwise pool the first max_in_dims nodes only).
+int padding_guard(SgnnHandle h, const SgnnGraphBatch* b) {
+  if (h->M.pool_kind == SGNN_LAYER_PADDING && b->n_graphs > 0 && b->max_nodes > h->M.pool_aux)
+    return fail(h, "Padding: a graph of the batch has " + std::to_string(b->max_nodes) + " nodes, more than max_in_dims=" +
+                       std::to_string(h->M.pool_aux) + " (Paddings must be non-negative, layers.py:223-227)");
+  return 0;
+}
+
 // pooled embeddings AND last node-level rows of a batch in one pass (node_out may be NULL)
 int embed_nodes(SgnnHandle h, const SgnnGraphBatch* b, float* emb_dev, float* node_out, cudaStream_t st) {
   if (b->n_graphs == 0) return 0;
+  if (padding_guard(h, b)) return 1;
   if (b->max_nodes <= 32) {
     const cudaError_t e = sgnn_launch_embed_tile(h->M, to_dev(b), b->max_nodes, h->d_params, emb_dev, node_out, nullptr,
                                                  0, 0, nullptr, 0, 0, 0, 0, h->sm_count, h->smem_optin, st);
@@ -602,6 +612,7 @@ int embed_nodes(SgnnHandle h, const SgnnGraphBatch* b, float* emb_dev, float* no
 int embed_side(SgnnHandle h, const SgnnGraphBatch* b, float* emb_dev, int side, cudaStream_t st, bool* fused = nullptr,
                const SgnnGraphBatch* beside = nullptr) {
   if (fused) *fused = false;
+  if (padding_guard(h, b)) return 1;
   // Database side: on by default (one kernel less on the critical chain).  Query side: measured neutral (the
   // query embedding gets heavier by what the two small operand kernels cost, 70.9 vs 70.2 us per step), so it stays
   // an opt-in (SGNN_FUSED_QUERY_PREP=1) and the default query branch is embed -> tc_coef -> tc_prep_q.
@@ -896,6 +907,7 @@ int sgnn_reserve(SgnnHandle h, int64_t max_graphs, int64_t max_nodes, int64_t ma
 int sgnn_embed_graphs(SgnnHandle h, const SgnnGraphBatch* b, float* emb_dev, void* stream) {
   if (!h || !b || !emb_dev) return fail(h, "sgnn_embed_graphs: null argument");
   if (b->n_graphs == 0) return 0;
+  if (padding_guard(h, b)) return 1;
   cudaStream_t st = (cudaStream_t)stream;
   if (b->max_nodes > 32) {   // Web-shaped / large graphs: CTA per graph, rows in the global workspace
     if (b->total_nodes > h->cap_rows)
@@ -1095,6 +1107,7 @@ static int launch_pairs(SgnnHandle h, bool bwd, const SgnnGraphBatch* b, const i
                         double target_sqsum, float* loss, float* raw, float* sim, void* stream, bool no_dropout) {
   if (n_pairs == 0) return 0;
   if (global_batch < n_pairs) return fail(h, "global_batch < n_pairs");
+  if (padding_guard(h, b)) return 1;
   if (b->max_nodes > 32) {   // beyond the warp-per-pair kernel; the CTA-per-pair kernel takes what fits shared memory
     const size_t need = h->use_team ? team_smem_floats(h->M, (int)b->max_nodes) * sizeof(float) : 0;
     if (!h->use_team || need > (size_t)h->smem_optin)

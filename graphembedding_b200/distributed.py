@@ -120,10 +120,8 @@ def sharded_rank(engine, queries_dev, db_shard_dev, id_offset, k, dist=None, gro
     ids, vals, sim = engine.rank_device(queries_dev, db_shard_dev, k, emb_q=emb_q, emb_db=emb_db, sim=sim,
                                         ids=ids, vals=vals)
     world = dist.get_world_size(group) if dist is not None and dist.is_initialized() else 1
-    if world == 1 and id_offset == 0:
-        return ids, vals
-    if peer is not None:
-        return peer.exchange(vals, ids, id_offset)
+    if world == 1:
+        return (ids, vals) if id_offset == 0 else (ids + int(id_offset), vals)
     cv, ci = gather_topk_candidates(vals, ids, id_offset, dist, group)
     return engine.topk_merge(cv, ci, k)
 

@@ -267,12 +267,44 @@ def part_model(name):
     print('model golden', name, 'written: losses', [s['loss'] for s in steps])
 
 
+# ---------------------------------------------------------------------------------------
+def part_attention():
+    """The reference's Attention layer (layers.py:143-160) is unreachable through its factory, but the
+    class itself runs: layers.Attention(input_dim=d)._call_one_mat on the torch-backed TF-1 stand-in, fp64."""
+    os.environ.setdefault('TF1_SHIM_DTYPE', 'float64')
+    from oracle import tf1_shim
+    tf1_shim.install()
+    _ref_paths()
+    import config                                    # reference flags (layers.py reads FLAGS.dropout)
+    config.FLAGS(['make_golden', '--dropout=0', '--log=False'])
+    import layers as ref_layers                      # reference
+    import tensorflow as tf                          # the shim
+    rng = np.random.default_rng(77)
+    rec = []
+    for d, n in ((16, 7), (16, 1), (12, 10), (8, 30)):
+        layer = ref_layers.Attention(input_dim=d)
+        x_ph = tf.placeholder(tf.float32)
+        out_node = layer._call_one_mat(x_ph)         # the reference's graph for one N x D matrix
+        sess = tf1_shim.Session()
+        sess.run(tf1_shim.global_variables_initializer())
+        W = rng.uniform(-0.6, 0.6, size=(d, d)).astype(np.float32).astype(np.float64)
+        layer.vars['weights'].assign_value(W)
+        x = rng.standard_normal((n, d)).astype(np.float32).astype(np.float64)
+        out = np.asarray(sess.run(out_node, feed_dict={x_ph: x}), np.float64).reshape(-1)
+        rec.append(dict(d=d, n=n, weights=W.tolist(), x=x.tolist(), out=out.tolist()))
+    json.dump(rec, open(HERE + '/attention.json', 'w'))
+    print('attention golden written:', [len(r['out']) for r in rec])
+
+
 if __name__ == '__main__':
     if len(sys.argv) > 1 and sys.argv[1] == 'host':
         part_host()
     elif len(sys.argv) > 2 and sys.argv[1] == 'model':
         part_model(sys.argv[2])
+    elif len(sys.argv) > 1 and sys.argv[1] == 'attention':
+        part_attention()
     else:
         subprocess.check_call([sys.executable, __file__, 'host'])
         for nm in MODEL_CONFIGS:
             subprocess.check_call([sys.executable, __file__, 'model', nm])
+        subprocess.check_call([sys.executable, __file__, 'attention'])

@@ -9,7 +9,7 @@ import networkx as nx
 import numpy as np
 import pytest
 
-from util import ROOT
+from util import ROOT, close_fp32
 
 torch = pytest.importorskip('torch')
 pytestmark = pytest.mark.gpu
@@ -52,11 +52,11 @@ def test_all_pairs_test_matrix_matches_reference_run(name):
     ref = np.array(d['test_sim'])
     sim, ids, _ = all_pairs_similarity(data, model, k=3)
     assert sim.shape == ref.shape
-    assert np.max(np.abs(sim - ref) / np.maximum(np.abs(ref), 1e-3)) <= 5e-4
+    assert close_fp32(sim, ref)
     # single-pair run_tf('test', i, j) == the reference's per-pair loop (train.py:57-61)
     for i, j in ((0, 0), (1, 5), (4, 15)):
         s, secs = run_tf(data, dc, model, saver, sess, 'test', i, j)
-        assert abs(s - ref[i, j]) <= 5e-4 * max(abs(ref[i, j]), 1e-3) and secs > 0
+        assert close_fp32(s, ref[i, j]) and secs > 0
 
 
 @pytest.mark.parametrize('name', ['default', 'avg_ntn', 'dot'])

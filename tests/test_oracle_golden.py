@@ -154,3 +154,31 @@ def test_train_steps_match_reference_model_code(name):
         assert np.allclose(g, st['grads'], rtol=1e-9, atol=1e-13)
         p = adam.step(p, g)
         assert np.allclose(p, st['params_after'], rtol=0, atol=1e-11)
+
+
+def _attention_case(rec):
+    """A model whose node rows ARE the fixture's x: n isolated nodes with distinct labels (A_hat = I), one identity
+    GraphConvolution without bias whose weight matrix is x, then Attention(d)."""
+    d, n = rec['d'], rec['n']
+    specs = ['GraphConvolution:output_dim=%d,act=identity,dropout=False,bias=False,sparse_inputs=True' % d,
+             'Attention:input_dim=%d' % d, 'Dot']
+    layers = O.parse_layer_specs(specs, n)
+    g = O.Graph.from_edges(list(range(n)), [])
+    return specs, layers, g, np.array(rec['x']), np.array(rec['weights']), np.array(rec['out'])
+
+
+def test_attention_pooling_is_pinned_to_the_reference_class():
+    """layers.py:143-160 run by make_golden.py (reference class on the TF-1 stand-in): the oracle's Attention branch,
+    per graph and batched, must reproduce it (the factory cannot reach the class, SURVEY F2, but its math is the pin)."""
+    import torch
+    from oracle import batched as OB
+    recs = json.load(open(os.path.join(G, 'attention.json')))
+    assert len(recs) >= 4
+    for rec in recs:
+        specs, layers, g, x, W, out = _attention_case(rec)
+        P = {(0, 'weights_0'): torch.as_tensor(x), (1, 'weights'): torch.as_tensor(W)}
+        got = O.graph_forward(layers, P, g, rec['n'], torch.float64).numpy()
+        assert np.max(np.abs(got - out)) <= 1e-12
+        lab, A, mask, n = OB.pad_graphs([g], rec['n'], torch.float64)
+        got_b = OB.embed(layers, P, lab, A, mask, n, torch.float64).numpy()[0]
+        assert np.max(np.abs(got_b - out)) <= 1e-12

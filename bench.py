@@ -2,18 +2,21 @@
 """bench.py -- graph-pairs/s of the Siamese graph-pair similarity hot path on B200.
 
     python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
-    python bench.py --impl reference --steps K --warmup W    # CPU baseline arm (oracle port)
+    python bench.py --impl reference --steps K --warmup W    # CPU baseline arm (oracle port, nothing of the product loaded)
 
-Headline workload (config.workload): BASELINE.json configs[3] -- all-pairs similarity ranking,
-1 000 query x 10 000 database AIDS-shaped graphs (<= 10 nodes, 29 labels), the reference's default
-flag model (config.py:44-66), top-10 per query.  One "step" = embed every query and database
-graph, score every (query, database) pair, select the top-10 ids per query -- what the reference's
-test() does with m x n sess.run calls (train.py:57-61).  Nothing is cached across steps.
-With N GPUs every rank holds its own 10 000-graph database shard (weak scaling), queries are
-replicated, and the per-shard top-10 are all-gathered and merged.
+Headline workload (config.workload): BASELINE.json configs[3] on the configs[0]/[1] model -- all-pairs similarity
+ranking, 1 000 query x 10 000 database AIDS-shaped graphs (<= 10 nodes, 29 labels) per GPU, the SimGNN-style chain
+(3 GCN + Attention + NTN(16,16) + 16-bin node-node histogram + FC head), top-10 per query.  One "step" = embed every
+query and database graph, score every (query, database) pair, select the top-10 ids per query -- what the reference's
+test() does with m x n sess.run calls (train.py:57-61).  Nothing is cached across steps.  With N GPUs every rank
+holds its own 10 000-graph database shard (weak scaling), queries are replicated, and the per-shard top-10 are
+exchanged over peer memory and merged (verified once, untimed, against all-gather + merge: exchange_verified).
 
-Also measured and reported inside the same JSON line: "train" (configs[2]: data-parallel training,
-128 pairs/GPU/step on AIDS10knef-shaped graphs, fwd+bwd+allreduce+Adam).
+Also inside the same JSON line: `default_model` (the same step on the reference's default-flag model), `train` /
+`train_simgnn` (configs[2]: data-parallel training, 128 pairs/GPU/step on AIDS10knef-shaped graphs, fwd + bwd +
+gradient exchange + Adam, plus a 16 384-pair throughput point), `web` (configs[4]), `metrics` (precision@10 and
+Kendall tau kernels on the 1 k x 10 k matrix), `parity` (device scores vs the oracle port on a sample), and a
+compact `summary` at the end of the line.
 """
 import argparse
 import json
@@ -640,6 +643,16 @@ def run_cuda(args):
         line['cpu_baseline'] = {'value': v, 'unit': 'pairs/s', 'cores': cores, 'kind': 'port', 'sample': sample,
                                 'per_pair_reference_structure_pairs_per_s': cpu_per_pair_rate(HEADLINE, q_gs, db_gs)}
     line.update(extra)
+    # the driver keeps the last ~1 500 characters of the line: the numbers of every sub-benchmark once more, compactly
+    summ = {'headline_pairs_per_s': head['value'], 'headline_ms': head['ms_per_step'], 'e2e_pairs_per_s': head['e2e']['value'],
+            'roofline_frac': head['roofline']['frac'], 'exchange': head['exchange']}
+    if 'exchange_verified' in head:
+        summ['exchange_verified'] = head['exchange_verified']
+    for k in ('default_model', 'train', 'train_simgnn', 'web'):
+        if k in extra:
+            summ[k + '_pairs_per_s'] = extra[k]['value']
+            summ[k + '_ms'] = extra[k]['ms_per_step']
+    line['summary'] = summ
     sys.stdout.flush()
     os.write(json_fd, (json.dumps(line) + '\n').encode())
 

@@ -24,9 +24,19 @@ constexpr int TCH_W3 = TCH_B2 + TCH_H2;                // [4]
 constexpr int TCH_B3 = TCH_W3 + TCH_H2;                // [1] (+3 pad)
 constexpr int TCH_FLOATS = TCH_B3 + 4;
 constexpr int TCH_SMEM_BYTES = TCH_FLOATS * 4 + 16;   // + alignment slack
+// The same block in CONSTANT memory (one slot per engine of the device): a warp-uniform constant operand reaches the
+// FFMA2 through a uniform register (LDCU.128 -> FFMA2 R, R.F32, UR.F32x2, R), per scheduler, while a shared-memory
+// broadcast costs 4 cycles of the SM-wide LSU per LDS.128 -- the shared-memory version of this kernel spent 0.39 of
+// its 0.43 ms delivering weights.  The slot is refreshed from the parameters by a copy on the stream
+// before every scoring call (tch_weights_kernel -> staging -> cudaMemcpyToSymbolAsync), so training between calls is fine.
+constexpr int TCH_SLOTS = 8;
+constexpr int TCH_SLOT_FLOATS = 768;   // >= TCH_FLOATS, 3 KB
+static_assert(TCH_SLOT_FLOATS >= TCH_FLOATS, "slot too small");
+__constant__ __align__(16) float c_tch_w[TCH_SLOTS * TCH_SLOT_FLOATS];
 
 struct TcHeadEpi {
   const float* sW;                 // shared-memory weight block
+  int slot;                        // constant-memory slot (CONSTW)
   int act_ntn, act0, act1, act2, act3, final_act;
   float yeta;
   float* sim;
@@ -36,6 +46,27 @@ struct TcHeadEpi {
   const int32_t* node_off_q;
   const int32_t* node_off_db;
 };
+
+// element i of the head weight block: U folded into the NTN rows of layer 0, missing biases = 0
+__device__ __forceinline__ float tch_weight(const ModelDev& M, const float* __restrict__ params, int i) {
+  float w = 0.f;
+  if (i < TCH_B0) {
+    const int r = i / TCH_H0, j = i - r * TCH_H0;
+    if (r < M.Hd[0].din) w = params[M.Hd[0].w_off + r * TCH_H0 + j] * (r < TCH_K ? params[M.u_off + r] : 1.f);
+  } else if (i < TCH_W1) { if (M.Hd[0].bias) w = params[M.Hd[0].b_off + (i - TCH_B0)]; }
+  else if (i < TCH_B1) w = params[M.Hd[1].w_off + (i - TCH_W1)];
+  else if (i < TCH_W2) { if (M.Hd[1].bias) w = params[M.Hd[1].b_off + (i - TCH_B1)]; }
+  else if (i < TCH_B2) w = params[M.Hd[2].w_off + (i - TCH_W2)];
+  else if (i < TCH_W3) { if (M.Hd[2].bias) w = params[M.Hd[2].b_off + (i - TCH_B2)]; }
+  else if (i < TCH_B3) w = params[M.Hd[3].w_off + (i - TCH_W3)];
+  else if (i == TCH_B3) { if (M.Hd[3].bias) w = params[M.Hd[3].b_off]; }
+  return w;
+}
+__global__ void __launch_bounds__(256)
+tch_weights_kernel(const __grid_constant__ ModelDev M, const float* __restrict__ params, float* __restrict__ staging) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < TCH_SLOT_FLOATS) staging[i] = i < TCH_FLOATS ? tch_weight(M, params, i) : 0.f;
+}
 
 // Packed pairs of floats live in 64-bit registers (fma.rn.f32x2 operands): with float2 the compiler keeps the halves
 // as separate scalars and shuffles them into aligned pairs around every FFMA2 (300 MOVs per pass).
@@ -131,7 +162,7 @@ __device__ __forceinline__ void tch_tail2(const TcHeadEpi& E, const float* sW, t
 // [qrow0 + 4 part, + 4) of the tile, processed as two passes of two queries.  The code is kept SMALL on purpose (part
 // is a run-time value, the k loops are rolled in chunks): 16 epilogue warps at different places of a fully unrolled
 // 50 KB epilogue starved on instruction fetch (ncu r2d: stall_no_instruction 5.7 per issue).
-template <bool HIST>
+template <bool HIST, bool CONSTW>
 __device__ __forceinline__ void tc_head_epilogue_part(const TcHeadEpi& E, uint32_t taddr, int qrow0, int part, int g,
                                                       uint64_t* t_empty, int lane) {
   const bool gv = g < E.n;
@@ -141,7 +172,8 @@ __device__ __forceinline__ void tc_head_epilogue_part(const TcHeadEpi& E, uint32
   for (int qp = 0; qp < 2; ++qp) {
     int opaque = 0;
     asm volatile("" : "+r"(opaque));   // per pass: the weight reads must not be hoisted out of the loop (register pressure)
-    const float* sW = E.sW + opaque;   // (an offset, so that the pointer stays a shared-memory pointer: LDS, not LD)
+    // (an offset, so that the pointer keeps its address space: LDS / LDCU, not a generic LD)
+    const float* sW = CONSTW ? c_tch_w + E.slot * TCH_SLOT_FLOATS : E.sW + opaque;
     const int qa = qrow0 + 4 * part + 2 * qp, qb = qa + 1;
     const bool va = qa < E.m, vb = qb < E.m;
     uint4 ca = make_uint4(0u, 0u, 0u, 0u), cb = ca;
@@ -253,9 +285,9 @@ __device__ __forceinline__ void tch_producer_mma_roles(const TcGeom& G, const Tc
   }
 }
 
-template <bool HIST>
+template <bool HIST, bool CONSTW>
 __global__ void __launch_bounds__(TCH_THREADS, 1)
-allpairs_tc_head_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const float* __restrict__ params,
+allpairs_tc_head_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const float* __restrict__ params, int slot,
                         const __nv_bfloat16* __restrict__ Ag, const __nv_bfloat16* __restrict__ Bg,
                         float* __restrict__ sim, int64_t ld, const uint8_t* __restrict__ cnt,
                         const int32_t* __restrict__ node_off_q, const int32_t* __restrict__ node_off_db) {
@@ -274,7 +306,9 @@ allpairs_tc_head_kernel(const __grid_constant__ ModelDev M, const TcGeom G, cons
   // TCH_FLOATS, 16-byte aligned (pointer arithmetic, not an integer round trip: the pointer stays a shared-memory pointer)
   float* sW = reinterpret_cast<float*>(tmem_slot + 4) + (((16u - (tc::smem_u32(tmem_slot + 4) & 15u)) & 15u) >> 2);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // warp index through a shuffle: provably warp-uniform, so that the role branches are uniform control flow and the
+  // epilogue's constant operands can go through the uniform datapath (LDCU -> UR operands of FFMA2)
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const int gg = blockIdx.x / G.q_groups, qg = blockIdx.x - gg * G.q_groups;
   const int gt0 = gg * G.GA;
   const int ga_count = min(G.GA, G.n_gtiles - gt0);
@@ -288,20 +322,8 @@ allpairs_tc_head_kernel(const __grid_constant__ ModelDev M, const TcGeom G, cons
     tc::fence_barrier_init();
   }
   // ---- head weights: U folded into the NTN rows of layer 0, missing biases = 0 ----
-  for (int i = threadIdx.x; i < TCH_FLOATS; i += blockDim.x) {
-    float w = 0.f;
-    if (i < TCH_B0) {
-      const int r = i / TCH_H0, j = i - r * TCH_H0;
-      if (r < M.Hd[0].din) w = params[M.Hd[0].w_off + r * TCH_H0 + j] * (r < TCH_K ? params[M.u_off + r] : 1.f);
-    } else if (i < TCH_W1) { if (M.Hd[0].bias) w = params[M.Hd[0].b_off + (i - TCH_B0)]; }
-    else if (i < TCH_B1) w = params[M.Hd[1].w_off + (i - TCH_W1)];
-    else if (i < TCH_W2) { if (M.Hd[1].bias) w = params[M.Hd[1].b_off + (i - TCH_B1)]; }
-    else if (i < TCH_B2) w = params[M.Hd[2].w_off + (i - TCH_W2)];
-    else if (i < TCH_W3) { if (M.Hd[2].bias) w = params[M.Hd[2].b_off + (i - TCH_B2)]; }
-    else if (i < TCH_B3) w = params[M.Hd[3].w_off + (i - TCH_W3)];
-    else if (i == TCH_B3) { if (M.Hd[3].bias) w = params[M.Hd[3].b_off]; }
-    sW[i] = w;
-  }
+  if (!CONSTW)
+    for (int i = threadIdx.x; i < TCH_FLOATS; i += blockDim.x) sW[i] = tch_weight(M, params, i);
   if (warp == TC_PROD_WARP) tc::tmem_alloc(tmem_slot, 512);
   tc::tc_fence_before();
   __syncthreads();
@@ -314,7 +336,7 @@ allpairs_tc_head_kernel(const __grid_constant__ ModelDev M, const TcGeom G, cons
     tch_producer_mma_roles(G, Wk, S, Ag, Bg, tmem_base, warp, lane);
   } else {
     TcHeadEpi E;
-    E.sW = sW; E.act_ntn = M.pair_act; E.act0 = M.Hd[0].act; E.act1 = M.Hd[1].act; E.act2 = M.Hd[2].act;
+    E.sW = sW; E.slot = slot; E.act_ntn = M.pair_act; E.act0 = M.Hd[0].act; E.act1 = M.Hd[1].act; E.act2 = M.Hd[2].act;
     E.act3 = M.Hd[3].act; E.final_act = M.final_act; E.yeta = M.yeta;
     E.sim = sim; E.ld = ld; E.m = G.m; E.n = G.n; E.cnt = cnt; E.node_off_q = node_off_q; E.node_off_db = node_off_db;
     const int lg = warp & 3, part = (warp >> 2) & 1, grp = warp >> 3;
@@ -326,7 +348,7 @@ allpairs_tc_head_kernel(const __grid_constant__ ModelDev M, const TcGeom G, cons
       tc::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + buf * TC_NPAD;
       const int g = (gt0 + ga) * 128 + lg * 32 + lane;
-      tc_head_epilogue_part<HIST>(E, taddr, (qb0 + i) * G.QH, part, g, t_empty + buf, lane);
+      tc_head_epilogue_part<HIST, CONSTW>(E, taddr, (qb0 + i) * G.QH, part, g, t_empty + buf, lane);
       ga += TC_EPI_GROUPS;
       while (ga >= ga_count) { ga -= ga_count; ++i; }
     }

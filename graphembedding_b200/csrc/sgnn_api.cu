@@ -2,6 +2,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -97,6 +98,8 @@ struct SgnnHandle_t {
   unsigned long long* d_smax = nullptr;                          // [queries][32-graph slices] slice maxima (top-k hints)
   int64_t cap_smax = 0;
   HistTcWs ht;                            // tensor-core node-node histogram: operand tiles, tile tables, count matrix
+  int head_slot = -1;                     // constant-memory slot of the head weights (sgnn_allpairs_tc_head.cuh); -1: none free
+  float* d_head_staging = nullptr;        // the block the slot is refreshed from
   int dep = 16;                           // padded embedding width of the all-pairs scorer
   cudaStream_t stream = nullptr;          // used by *_host entry points
   cudaStream_t copy_stream = nullptr;     // host -> device uploads that overlap compute (sgnn_rank_host)
@@ -110,6 +113,21 @@ struct SgnnHandle_t {
 };
 
 namespace {
+
+// constant-memory slots of the head weights: one per engine and device (a bit mask per device)
+std::mutex g_slot_mu;
+unsigned g_slot_mask[64] = {};
+int acquire_head_slot(int device) {
+  std::lock_guard<std::mutex> lock(g_slot_mu);
+  if (device < 0 || device >= 64) return -1;
+  for (int s = 0; s < sgnn_tc_head_slots(); ++s)
+    if (!(g_slot_mask[device] & (1u << s))) { g_slot_mask[device] |= 1u << s; return s; }
+  return -1;
+}
+void release_head_slot(int device, int slot) {
+  std::lock_guard<std::mutex> lock(g_slot_mu);
+  if (device >= 0 && device < 64 && slot >= 0) g_slot_mask[device] &= ~(1u << slot);
+}
 
 int fail(SgnnHandle h, const std::string& msg) {
   if (h) h->err = msg; else g_create_error = msg;
@@ -384,12 +402,15 @@ int score_all_pairs_tc(SgnnHandle h, const float* emb_q, int m, const float* emb
   smem = std::max<size_t>(smem, 120 * 1024);  // one CTA per SM: each CTA owns all 512 TMEM columns
   const int grid = g_groups * q_groups;
   cudaError_t e = cudaSuccess;
-  if (stages & SCORE_COEF_ONLY) e = sgnn_tc_prep_q(M, G, h->d_params, emb_q, h->d_Btc, h->d_coef, 1, st);
+  if (head && h->head_slot >= 0 &&   // the head weights' constant slot is refreshed wherever the coefficient matrix is (parameters only)
+      ((stages & SCORE_COEF_ONLY) || ((stages & SCORE_PREP_Q) && !(stages & SCORE_COEF_READY))))
+    e = sgnn_tc_head_weights(M, h->d_params, h->d_head_staging, h->head_slot, st);
+  if (e == cudaSuccess && (stages & SCORE_COEF_ONLY)) e = sgnn_tc_prep_q(M, G, h->d_params, emb_q, h->d_Btc, h->d_coef, 1, st);
   if (e == cudaSuccess && (stages & SCORE_PREP_Q))
     e = sgnn_tc_prep_q(M, G, h->d_params, emb_q, h->d_Btc, h->d_coef, (stages & SCORE_COEF_READY) ? 2 : 0, st);
   if (e == cudaSuccess && (stages & SCORE_PREP_DB)) e = sgnn_tc_prep_db(M, G, emb_db, h->d_Atc, st);
   if (e == cudaSuccess && (stages & SCORE_MAIN))
-    e = head ? sgnn_tc_score_head(M, G, grid, smem, h->d_params, h->d_Atc, h->d_Btc, sim, ld, cnt, node_off_q, node_off_db, st)
+    e = head ? sgnn_tc_score_head(M, G, grid, smem, h->d_params, h->head_slot, h->d_Atc, h->d_Btc, sim, ld, cnt, node_off_q, node_off_db, st)
              : sgnn_tc_score(M, G, relu, ref, simk, grid, smem, h->d_params, h->d_Atc, h->d_Btc, sim, ld, smax, st);
   if (e != cudaSuccess) return fail(h, std::string("tensor-core all-pairs launch: ") + cudaGetErrorString(e));
   return 0;
@@ -708,6 +729,14 @@ int sgnn_create(const SgnnConfig* cfg, SgnnHandle* out) {
       h->d_coef = nullptr;   // the staged single-kernel query prep is used instead
   }
   if (plan_launches(h)) return bail("planning launches");
+  if (cfg->precision != SGNN_PREC_FP32 && sgnn_tc_head_supported(h->M)) {
+    h->head_slot = acquire_head_slot(h->device);
+    if (h->head_slot >= 0 &&
+        cudaMalloc(reinterpret_cast<void**>(&h->d_head_staging), (size_t)sgnn_tc_head_staging_floats() * sizeof(float)) != cudaSuccess) {
+      release_head_slot(h->device, h->head_slot);
+      h->head_slot = -1; h->d_head_staging = nullptr;
+    }
+  }
   *out = h;
   return 0;
 }
@@ -718,6 +747,9 @@ int sgnn_destroy(SgnnHandle h) {
   cudaFree(h->d_params); cudaFree(h->d_grads); cudaFree(h->d_m); cudaFree(h->d_v); cudaFree(h->d_loss);
   cudaFree(h->d_coef); cudaFree(h->d_P); cudaFree(h->d_C); cudaFree(h->d_Atc); cudaFree(h->d_Btc); cudaFree(h->d_smax);
   cudaFree(h->d_rowsA); cudaFree(h->d_rowsB); cudaFree(h->d_hnodes[0]); cudaFree(h->d_hnodes[1]);
+  release_head_slot(h->device, h->head_slot);
+  h->head_slot = -1;
+  cudaFree(h->d_head_staging);
   cudaFree(h->ht.At); cudaFree(h->ht.Bt); cudaFree(h->ht.qmeta); cudaFree(h->ht.ameta); cudaFree(h->ht.status);
   cudaFree(h->ht.cnt);
   HostWs& w = h->ws;

@@ -88,17 +88,33 @@ bool sgnn_tc_head_supported(const ModelDev& M) {
 }
 int sgnn_tc_head_smem_bytes() { return TCH_SMEM_BYTES; }
 
-cudaError_t sgnn_tc_score_head(const ModelDev& M, const TcGeom& G, int grid, size_t smem, const float* params,
+// refresh constant slot `slot` from the parameters (stream-ordered: kernel -> staging -> copy into the symbol)
+cudaError_t sgnn_tc_head_weights(const ModelDev& M, const float* params, float* staging, int slot, cudaStream_t st) {
+  if (slot < 0 || slot >= TCH_SLOTS || !staging) return cudaErrorInvalidValue;
+  tch_weights_kernel<<<(TCH_SLOT_FLOATS + 255) / 256, 256, 0, st>>>(M, params, staging);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  return cudaMemcpyToSymbolAsync(c_tch_w, staging, TCH_SLOT_FLOATS * sizeof(float),
+                                 (size_t)slot * TCH_SLOT_FLOATS * sizeof(float), cudaMemcpyDeviceToDevice, st);
+}
+int sgnn_tc_head_slots() { return TCH_SLOTS; }
+int sgnn_tc_head_staging_floats() { return TCH_SLOT_FLOATS; }
+
+// slot >= 0: head weights from constant memory (sgnn_tc_head_weights must have run on the stream); < 0: staged in
+// shared memory by the kernel itself
+cudaError_t sgnn_tc_score_head(const ModelDev& M, const TcGeom& G, int grid, size_t smem, const float* params, int slot,
                                const void* A_ws, const void* B_ws, float* sim, int64_t ld, const uint8_t* cnt,
                                const int32_t* node_off_q, const int32_t* node_off_db, cudaStream_t st) {
-  if (!sgnn_tc_head_supported(M) || G.KC != TCH_K || G.QH != 8) return cudaErrorInvalidValue;
+  if (!sgnn_tc_head_supported(M) || G.KC != TCH_K || G.QH != 8 || slot >= TCH_SLOTS) return cudaErrorInvalidValue;
   const __nv_bfloat16* A = static_cast<const __nv_bfloat16*>(A_ws);
   const __nv_bfloat16* B = static_cast<const __nv_bfloat16*>(B_ws);
   auto launch_it = [&](auto kern) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    kern<<<grid, TCH_THREADS, smem, st>>>(M, G, params, A, B, sim, ld, cnt, node_off_q, node_off_db);
+    kern<<<grid, TCH_THREADS, smem, st>>>(M, G, params, slot, A, B, sim, ld, cnt, node_off_q, node_off_db);
     return cudaGetLastError();
   };
-  return M.hist_bins > 0 ? launch_it(allpairs_tc_head_kernel<true>) : launch_it(allpairs_tc_head_kernel<false>);
+  const bool hist = M.hist_bins > 0;
+  if (slot >= 0) return hist ? launch_it(allpairs_tc_head_kernel<true, true>) : launch_it(allpairs_tc_head_kernel<false, true>);
+  return hist ? launch_it(allpairs_tc_head_kernel<true, false>) : launch_it(allpairs_tc_head_kernel<false, false>);
 }

@@ -26,7 +26,7 @@ cudaError_t sgnn_hist_tc_prep_db(const HistTcGeom& G, const float* nodes_db, con
 cudaError_t sgnn_hist_tc_run(const HistTcGeom& G, const HistTcWs& ws, const int32_t* node_off_db, int sm_count,
                              cudaStream_t st) {
   static const bool unpaired = getenv("SGNN_HIST_UNPAIRED") != nullptr;   // one reciprocal per cell (cross-check)
-  const size_t smem = (size_t)(HT_GA + HT_STAGES) * ht_tile_bytes(G) + (size_t)4 * HT_SEGB * 128 * 8 +
+  const size_t smem = (size_t)(HT_GA + HT_STAGES) * ht_tile_bytes(G) + (size_t)HT_GROUPS * 2 * HT_SEGB * 128 * 8 +
                       (2 + 2 * HT_STAGES + 2 * HT_BUFS) * 8 + 16;
   auto launch = [&](auto kern) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

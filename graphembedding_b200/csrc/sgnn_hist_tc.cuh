@@ -26,8 +26,8 @@
 //     of pair (graph, query), widens them to bytes and writes the pair's 16 counts as one 16-byte store.
 //
 // Roles (576 threads, 1 CTA per SM, persistent over a contiguous range of (A block, B tile) units): warps
-// 0-15 = four epilogue groups of four warps (group e owns TMEM buffer e: lanes 32 (w % 4)..), warp 16 =
-// bulk-copy producer, warp 17 = MMA issuer.
+// 0-15 = four epilogue groups of four warps (group e owns TMEM buffer e: lanes 32 (w % 4)..; the counter words are
+// double-buffered, one barrier per batch), warp 16 = bulk-copy producer, warp 17 = MMA issuer.
 #pragma once
 #include "sgnn_common.cuh"
 #include "sgnn_tc.cuh"
@@ -250,13 +250,17 @@ struct HtTileCtx {
   int n;
 };
 
+// One tile for one epilogue group (HT_GROUP_WARPS warps: 4 TMEM lane quadrants x 1 or 2 halves; the warps of a quadrant
+// split the tile's segments).  row = this thread's TMEM lane (0..127), tid = its index in the group, half = 0 / 1.
+// batch: the group's running batch counter -- the counter words are double-buffered on it, so ONE barrier per batch
+// is enough (the words of batch b are rewritten in batch b + 2, behind the barrier of batch b + 1).
 template <int N, bool PAIRED>
-__device__ __forceinline__ void ht_tile(const HtTileCtx& C, int tid128, int lane) {
+__device__ __forceinline__ void ht_tile(const HtTileCtx& C, int row, int tid, int half, int lane, int& batch) {
   // the first pair this thread reduces: its lane range is fetched now, long before it is needed
   int pre_l0 = 0, pre_l1 = 0;
-  if (tid128 < C.ng) {
-    pre_l0 = C.node_off_db[C.g0 + tid128] - C.row0;
-    pre_l1 = C.node_off_db[C.g0 + tid128 + 1] - C.row0;
+  if (tid < C.ng) {
+    pre_l0 = C.node_off_db[C.g0 + tid] - C.row0;
+    pre_l1 = C.node_off_db[C.g0 + tid + 1] - C.row0;
   }
   const uint32_t ng = (uint32_t)C.ng;
   if (C.n_seg == 0) {   // (never produced by the tile table; keeps the barrier protocol whole)
@@ -264,34 +268,65 @@ __device__ __forceinline__ void ht_tile(const HtTileCtx& C, int tid128, int lane
     __syncwarp();
     if (lane == 0) tc::mbar_arrive(C.t_empty);
   }
-  for (int s0 = 0; s0 < C.n_seg; s0 += HT_SEGB) {
+  for (int s0 = 0; s0 < C.n_seg; s0 += HT_SEGB, ++batch) {
     const int ns = min(HT_SEGB, C.n_seg - s0);
-    for (int sg = 0; sg < ns; ++sg) {
-      float v[N];
-      tc::tmem_ld_n<N>(C.taddr + (uint32_t)((s0 + sg) * N), v);
-      tc::tmem_ld_wait();
+    unsigned long long* const cnt = C.s_cnt + (batch & 1) * (HT_SEGB * 128);
+    // two segments per iteration (one TMEM wait and one loop overhead for 2 N cells); iterations alternate
+    // between the two halves of the quadrant
+    const bool last_batch = s0 + ns == C.n_seg;
+    bool released = false;
+    constexpr int STEP = 2 * (HT_GROUP_WARPS / 4);
+#pragma unroll 1
+    for (int sg = 2 * half; sg < ns; sg += STEP) {
+      const bool last_read = last_batch && sg + STEP >= ns;   // this warp's last TMEM read of the tile
+      if (sg + 1 < ns) {
+        float v[2 * N];
+        tc::tmem_ld_n<2 * N>(C.taddr + (uint32_t)((s0 + sg) * N), v);
+        tc::tmem_ld_wait();
 #pragma unroll
-      for (int i = 0; i < N; ++i) asm volatile("" : "+f"(v[i]));   // uses stay behind the wait
-      if (s0 + ns == C.n_seg && sg == ns - 1) {   // last TMEM read of the tile: hand the buffer back to the MMA issuer
-        tc::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) tc::mbar_arrive(C.t_empty);
+        for (int i = 0; i < 2 * N; ++i) asm volatile("" : "+f"(v[i]));   // uses stay behind the wait
+        if (last_read) {   // hand the buffer back to the MMA issuer before binning the last cells: the ~1 500 cycles of
+          tc::tc_fence_before();   // the next tile's six chained MMAs overlap them and the pair phase
+          __syncwarp();
+          if (lane == 0) tc::mbar_arrive(C.t_empty);
+          released = true;
+        }
+        const unsigned long long w0 = ht_segment<N, PAIRED>(v, C.fb), w1 = ht_segment<N, PAIRED>(v + N, C.fb);
+        cnt[sg * 128 + row] = w0;
+        cnt[(sg + 1) * 128 + row] = w1;
+      } else {
+        float v[N];
+        tc::tmem_ld_n<N>(C.taddr + (uint32_t)((s0 + sg) * N), v);
+        tc::tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < N; ++i) asm volatile("" : "+f"(v[i]));
+        if (last_read) {
+          tc::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) tc::mbar_arrive(C.t_empty);
+          released = true;
+        }
+        cnt[sg * 128 + row] = ht_segment<N, PAIRED>(v, C.fb);
       }
-      C.s_cnt[sg * 128 + tid128] = ht_segment<N, PAIRED>(v, C.fb);
     }
-    asm volatile("bar.sync %0, 128;" ::"r"(C.bar_id) : "memory");
+    if (last_batch && !released) {   // (a warp without segments in the last batch)
+      tc::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(C.t_empty);
+    }
+    asm volatile("bar.sync %0, %1;" ::"r"(C.bar_id), "n"(32 * HT_GROUP_WARPS) : "memory");
     // ---- pair-parallel: thread p owns (graph gi, segment sg) of this batch ----
     const uint32_t n_pairs = ng * (uint32_t)ns;
-    for (uint32_t p = (uint32_t)tid128; p < n_pairs; p += 128u) {
+    for (uint32_t p = (uint32_t)tid; p < n_pairs; p += 32u * HT_GROUP_WARPS) {
       const uint32_t sg = p / ng, gi = p - sg * ng;
       int l0, l1;
-      if (p == (uint32_t)tid128 && p < ng) { l0 = pre_l0; l1 = pre_l1; }
+      if (p < ng) { l0 = pre_l0; l1 = pre_l1; }   // (p < ng implies p == tid: the prefetched range)
       else {
         l0 = C.node_off_db[C.g0 + (int)gi] - C.row0;
         l1 = C.node_off_db[C.g0 + (int)gi + 1] - C.row0;
       }
       unsigned long long ev = 0ull, od = 0ull;
-      const unsigned long long* col = C.s_cnt + sg * 128;
+      const unsigned long long* col = cnt + sg * 128;
       for (int l = l0; l < l1; ++l) {
         const unsigned long long w = col[l];
         ev += w & 0x0F0F0F0F0F0F0F0Full;
@@ -323,28 +358,27 @@ __device__ __forceinline__ void ht_tile(const HtTileCtx& C, int tid128, int lane
       const int q = C.q_sorted[C.bt_first + s0 + (int)sg];
       *reinterpret_cast<uint4*>(C.cnt_out + ((size_t)q * C.n + (size_t)(C.g0 + (int)gi)) * HT_CNT_BYTES) = o;
     }
-    asm volatile("bar.sync %0, 128;" ::"r"(C.bar_id) : "memory");
   }
 }
 
 template <bool PAIRED>
-__device__ __forceinline__ void ht_tile_dispatch(int N, const HtTileCtx& C, int tid128, int lane) {
+__device__ __forceinline__ void ht_tile_dispatch(int N, const HtTileCtx& C, int row, int tid, int half, int lane, int& batch) {
   switch (N) {
-    case 1: ht_tile<1, PAIRED>(C, tid128, lane); break;
-    case 2: ht_tile<2, PAIRED>(C, tid128, lane); break;
-    case 3: ht_tile<3, PAIRED>(C, tid128, lane); break;
-    case 4: ht_tile<4, PAIRED>(C, tid128, lane); break;
-    case 5: ht_tile<5, PAIRED>(C, tid128, lane); break;
-    case 6: ht_tile<6, PAIRED>(C, tid128, lane); break;
-    case 7: ht_tile<7, PAIRED>(C, tid128, lane); break;
-    case 8: ht_tile<8, PAIRED>(C, tid128, lane); break;
-    case 9: ht_tile<9, PAIRED>(C, tid128, lane); break;
-    case 10: ht_tile<10, PAIRED>(C, tid128, lane); break;
-    case 11: ht_tile<11, PAIRED>(C, tid128, lane); break;
-    case 12: ht_tile<12, PAIRED>(C, tid128, lane); break;
-    case 13: ht_tile<13, PAIRED>(C, tid128, lane); break;
-    case 14: ht_tile<14, PAIRED>(C, tid128, lane); break;
-    default: ht_tile<15, PAIRED>(C, tid128, lane); break;
+    case 1: ht_tile<1, PAIRED>(C, row, tid, half, lane, batch); break;
+    case 2: ht_tile<2, PAIRED>(C, row, tid, half, lane, batch); break;
+    case 3: ht_tile<3, PAIRED>(C, row, tid, half, lane, batch); break;
+    case 4: ht_tile<4, PAIRED>(C, row, tid, half, lane, batch); break;
+    case 5: ht_tile<5, PAIRED>(C, row, tid, half, lane, batch); break;
+    case 6: ht_tile<6, PAIRED>(C, row, tid, half, lane, batch); break;
+    case 7: ht_tile<7, PAIRED>(C, row, tid, half, lane, batch); break;
+    case 8: ht_tile<8, PAIRED>(C, row, tid, half, lane, batch); break;
+    case 9: ht_tile<9, PAIRED>(C, row, tid, half, lane, batch); break;
+    case 10: ht_tile<10, PAIRED>(C, row, tid, half, lane, batch); break;
+    case 11: ht_tile<11, PAIRED>(C, row, tid, half, lane, batch); break;
+    case 12: ht_tile<12, PAIRED>(C, row, tid, half, lane, batch); break;
+    case 13: ht_tile<13, PAIRED>(C, row, tid, half, lane, batch); break;
+    case 14: ht_tile<14, PAIRED>(C, row, tid, half, lane, batch); break;
+    default: ht_tile<15, PAIRED>(C, row, tid, half, lane, batch); break;
   }
 }
 
@@ -358,8 +392,8 @@ hist_tc_kernel(const HistTcGeom G, const __nv_bfloat16* __restrict__ At, const _
   const int tile_bytes = ht_tile_bytes(G);
   uint8_t* sA = ht_smem;
   uint8_t* sB = sA + HT_GA * tile_bytes;
-  unsigned long long* s_cnt = reinterpret_cast<unsigned long long*>(sB + HT_STAGES * tile_bytes);   // [4][HT_SEGB][128]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_cnt + 4 * HT_SEGB * 128);
+  unsigned long long* s_cnt = reinterpret_cast<unsigned long long*>(sB + HT_STAGES * tile_bytes);   // [HT_GROUPS][2][HT_SEGB][128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_cnt + HT_GROUPS * 2 * HT_SEGB * 128);
   uint64_t* a_full = bars;                    // [1]
   uint64_t* a_free = bars + 1;                // [1]
   uint64_t* b_full = bars + 2;                // [HT_STAGES]
@@ -378,7 +412,7 @@ hist_tc_kernel(const HistTcGeom G, const __nv_bfloat16* __restrict__ At, const _
     tc::mbar_init(a_full, 1);
     tc::mbar_init(a_free, 1);
     for (int s = 0; s < HT_STAGES; ++s) { tc::mbar_init(b_full + s, 1); tc::mbar_init(b_empty + s, 1); }
-    for (int b = 0; b < HT_BUFS; ++b) { tc::mbar_init(t_full + b, 1); tc::mbar_init(t_empty + b, 4); }
+    for (int b = 0; b < HT_BUFS; ++b) { tc::mbar_init(t_full + b, 1); tc::mbar_init(t_empty + b, HT_GROUP_WARPS); }
     tc::fence_barrier_init();
   }
   if (warp == HT_PROD_WARP) tc::tmem_alloc(tmem_slot, 512);
@@ -461,31 +495,36 @@ hist_tc_kernel(const HistTcGeom G, const __nv_bfloat16* __restrict__ At, const _
         }
       }
     } else {
-      // ===== epilogue groups =====
-      const int e = warp >> 2, quad = warp & 3, tid128 = (warp & 3) * 32 + lane;
+      // ===== epilogue: HT_GROUPS groups of HT_GROUP_WARPS warps; group g takes the tiles it = g, g + HT_GROUPS, ...
+      // (TMEM buffer it % 4).  Measured (r2j): two groups of eight warps, each alternating between two TMEM buffers so
+      // that the MMA of its next tile is hidden, LOSE to four groups of four (0.76 vs 0.65 ms): the 256-thread barrier
+      // and the 8-warp pair phase cost more than the ~9 % of the time a group waits for its accumulator. =====
+      const int grp = warp / HT_GROUP_WARPS, quad = warp & 3, half = (warp % HT_GROUP_WARPS) >> 2;
+      const int row = quad * 32 + lane, tid = (warp % HT_GROUP_WARPS) * 32 + lane;
       const int32_t* bt_n = qmeta + 4;
       const int32_t* bt_cnt = bt_n + G.max_btiles;
       const int32_t* bt_first = bt_cnt + G.max_btiles;
       HtTileCtx C;
-      C.s_cnt = s_cnt + e * (HT_SEGB * 128);
-      C.bar_id = 1 + e;
+      C.s_cnt = s_cnt + grp * (2 * HT_SEGB * 128);   // two batches deep
+      C.bar_id = 1 + grp;
       C.fb = (float)G.bins; C.bins = G.bins;
       C.q_sorted = bt_first + G.max_btiles;
       C.node_off_db = node_off_db;
       C.cnt_out = cnt_out; C.n = G.n;
-      int ab = ab0, b = b0, it = 0;
+      int ab = ab0, b = b0, it = 0, batch = 0;
       for (long long u = u0; u < u1; ++u) {
         const int ga = min(HT_GA, n_at - ab * HT_GA);
         for (int a = 0; a < ga; ++a, ++it) {
-          if ((it & (HT_BUFS - 1)) != e) continue;
+          if ((it % HT_GROUPS) != grp) continue;
+          const int buf = it & (HT_BUFS - 1);
           const int t = ab * HT_GA + a;
           C.g0 = ameta[t]; C.ng = ameta[t + 1] - C.g0; C.row0 = node_off_db[C.g0];
           C.n_seg = bt_cnt[b]; C.bt_first = bt_first[b];
-          C.taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)e * 128u;
-          C.t_empty = t_empty + e;
-          tc::mbar_wait(t_full + e, (it / HT_BUFS) & 1);
+          C.taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)buf * 128u;
+          C.t_empty = t_empty + buf;
+          tc::mbar_wait(t_full + buf, (it / HT_BUFS) & 1);
           tc::tc_fence_after();
-          ht_tile_dispatch<PAIRED>(bt_n[b], C, tid128, lane);
+          ht_tile_dispatch<PAIRED>(bt_n[b], C, row, tid, half, lane, batch);
         }
         if (++b == n_b) { b = 0; ++ab; }
       }

@@ -12,6 +12,8 @@ constexpr int HT_GA = 4;           // database tiles resident per A block
 constexpr int HT_STAGES = 3;       // B-tile ring depth
 constexpr int HT_SEGB = 16;        // segments (queries) per shared-memory counter batch
 constexpr int HT_EPI_WARPS = 16;
+constexpr int HT_GROUP_WARPS = 4;  // warps per epilogue group (4: one warp per TMEM lane quadrant; 8: two that split a tile's segments)
+constexpr int HT_GROUPS = HT_EPI_WARPS / HT_GROUP_WARPS;
 constexpr int HT_PROD_WARP = 16, HT_MMA_WARP = 17;
 constexpr int HT_THREADS = 18 * 32;
 constexpr int HT_CNT_BYTES = 16;   // bytes per pair in the count matrix (one byte per bin)

@@ -221,11 +221,23 @@ __device__ __forceinline__ unsigned long long ht_segment(const float* v, float f
     constexpr float BIAS = 2.4e-7f;
 #pragma unroll
     for (int i = 0; i + 1 < N; i += 2) {
-      const float v1 = 1.f + ht_ex2(fminf(v[i], 60.f));
-      const float v2 = 1.f + ht_ex2(fminf(v[i + 1], 60.f));
+      // the two cells as one packed pair (add / fma / fma.rm .f32x2: three instructions instead of six); which
+      // sigma belongs to which cell does not matter, both go into the same histogram
+      unsigned long long u12, v12, s12, y12;
+      asm("mov.b64 %0, {%1, %2};" : "=l"(u12) : "f"(ht_ex2(fminf(v[i], 60.f))), "f"(ht_ex2(fminf(v[i + 1], 60.f))));
+      asm("add.rn.f32x2 %0, %1, %2;" : "=l"(v12) : "l"(u12), "l"(0x3F8000003F800000ull));
+      float v1, v2;
+      asm("mov.b64 {%0, %1}, %2;" : "=f"(v1), "=f"(v2) : "l"(v12));
       const float r = ht_rcp(v1 * v2);
-      ht_count(nib, ht_bin_bits(fmaf(r, v2, BIAS), fb));
-      ht_count(nib, ht_bin_bits(fmaf(r, v1, BIAS), fb));
+      unsigned long long r2, b2, f2, m2;
+      asm("mov.b64 %0, {%1, %1};" : "=l"(r2) : "f"(r));
+      asm("mov.b64 %0, {%1, %1};" : "=l"(b2) : "f"(BIAS));
+      asm("mov.b64 %0, {%1, %1};" : "=l"(f2) : "f"(fb));
+      asm("mov.b64 %0, {%1, %1};" : "=l"(m2) : "f"(8388608.f));
+      asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(s12) : "l"(r2), "l"(v12), "l"(b2));     // (r v1, r v2) = (sigma2, sigma1)
+      asm("fma.rm.f32x2 %0, %1, %2, %3;" : "=l"(y12) : "l"(s12), "l"(f2), "l"(m2));     // low mantissa bits = floor(sigma fb)
+      ht_count(nib, (uint32_t)y12);
+      ht_count(nib, (uint32_t)(y12 >> 32));
     }
     if constexpr (N & 1) {
       const float u = ht_ex2(v[N - 1]);

@@ -127,6 +127,7 @@ class SynData(Data):
 
 class AIDSData(Data):
     folder = None
+    strip_valence = False   # the *nef variants drop the edge attribute (no edge features)
     synthetic_shape = None  # (train_num, test_num, n_lo, n_hi)
 
     def __init__(self, train):
@@ -146,8 +147,11 @@ class AIDSData(Data):
                     raise RuntimeError('{} not connected'.format(g.graph['gid']))
                 self.graphs.append(g)
         else:
+            import warnings
+            warnings.warn('{}: no .gexf files under {} -- using the SYNTHETIC {}-shaped corpus (set GEB200_DATA_ROOT to '
+                          'the reference data/ directory for real graphs)'.format(type(self).__name__, d, self.folder))
             self.graphs = self._synthesize()
-        if 'nef' in self.folder:  # data.py:80-83
+        if self.strip_valence or 'nef' in self.folder:  # data.py:80-83, 119-121
             for g in self.graphs:
                 for _, _, ed in g.edges(data=True):
                     ed.pop('valence', None)
@@ -190,7 +194,9 @@ class AIDS10kData(AIDSData):
 
 
 class AIDS10kNEFData(AIDS10kData):
-    folder = 'AIDS10knef'
+    """Loads AIDS10k and strips the valence edge attribute (reference ``data.py:95-109``: there is no separate folder)."""
+    folder = 'AIDS10k'
+    strip_valence = True
 
 
 class RankingData(AIDSData):

@@ -30,8 +30,21 @@ def _score_rows_f32(r, norm):
     return np.ascontiguousarray(s, np.float32)
 
 
+_HOST_NOTED = False
+
+
 def _on_device(true_r, pred_r, norm):
+    global _HOST_NOTED
     if _ENGINE is None:
+        # Explicit, not silent: these are the reference's HOST functions (src/metrics.py is numpy / Python), so a
+        # caller that never registered an engine gets the host mirror -- and is told so once.  The training /
+        # evaluation entry points (train.main, tuning) register the engine; the product's scoring path never comes here.
+        if not _HOST_NOTED:
+            _HOST_NOTED = True
+            import warnings
+            warnings.warn('graphembedding_b200.metrics: no engine registered (metrics.use_engine(engine)): '
+                          'precision@k / Kendall tau are evaluated by the host mirror of src/metrics.py, not by the '
+                          'device kernels', stacklevel=3)
         return None
     m, n = true_r.m_n()
     if n > DEVICE_MAX_N or n < 2:

@@ -64,8 +64,8 @@ class Result(object):
 
 class DistanceModelResult(Result):
     """Ground-truth style result from an m x n distance matrix.  The reference loads the
-    matrix from ``result/<dataset>/<metric>/*.npy`` (:182-189); here matrices and node counts
-    are passed in (the on-disk format is SURVEY 8f N2)."""
+    matrix from ``result/<dataset>/<metric>/*.npy`` (:182-189): ``from_disk`` does the same; the
+    constructor takes matrices and node counts directly (synthetic ground truth)."""
 
     def __init__(self, dataset, model, dist_mat, q_nodes, db_nodes, time_mat=None):
         self.dataset, self.model_ = dataset, model
@@ -107,6 +107,42 @@ class DistanceModelResult(Result):
         if metric == 'time':
             return self.time_mat_
         raise RuntimeError('Unknown metric {} for model {}'.format(metric, self.model_))
+
+
+    # ---- the reference's on-disk format ----
+    @classmethod
+    def result_root(cls):
+        import os
+        return os.environ.get('GEB200_RESULT_ROOT', os.path.join(os.path.dirname(os.path.dirname(
+            os.path.abspath(__file__))), 'result'))
+
+    @classmethod
+    def load_result_mat(cls, dataset, model, dist_metric, metric, root=None):
+        """``_load_result_mat`` (src/results.py:182-189): result/<dataset>/<metric>/<dist_metric>_<metric>_mat_
+        <dataset>_<model>_*.npy; the first match wins (``_choose_result_file`` :191-192)."""
+        from glob import glob
+        file_p = (root or cls.result_root()) + '/{}/{}/{}_{}_mat_{}_{}_*.npy'.format(
+            dataset, metric, dist_metric, metric, dataset, model)
+        li = sorted(glob(file_p))
+        if not li:
+            raise RuntimeError('No results found {}'.format(file_p))
+        return np.load(li[0])
+
+    @classmethod
+    def from_disk(cls, dataset, model, root=None):
+        """What the reference's constructor does (src/results.py:130-145): distance and time matrices from .npy
+        files, node counts for the normalisation (distance.py:59-60) from ``load_data(dataset, True / False)``."""
+        from .data import load_data
+        probe = cls.__new__(cls)
+        dist = cls.load_result_mat(dataset, model, probe.dist_metric(), probe.dist_metric(), root)
+        time_mat = cls.load_result_mat(dataset, model, probe.dist_metric(), 'time', root)
+        train, test = load_data(dataset, True), load_data(dataset, False)
+        m, n = dist.shape
+        if m != len(test.graphs) or n != len(train.graphs):
+            raise RuntimeError('result matrix {} x {} does not match the dataset ({} test, {} train graphs)'.format(
+                m, n, len(test.graphs), len(train.graphs)))
+        return cls(dataset, model, dist, [g.number_of_nodes() for g in test.graphs],
+                   [g.number_of_nodes() for g in train.graphs], time_mat=time_mat)
 
 
 class PairwiseGEDModelResult(DistanceModelResult):

@@ -138,12 +138,35 @@ class ClockSampler(object):
                 'window': 'pre-load + timed steps + per-stage timings (GPU continuously busy), 5 ms NVML polling'}
 
 
-def make_rank_data(rank):
+def slice_batch(b, lo, hi):
+    """Contiguous sub-batch [lo, hi) of a host PackedBatch (offsets rebased; no per-graph loop)."""
+    from graphembedding_b200.native import PackedBatch
+    no, rp = np.asarray(b.node_off), np.asarray(b.rowptr)
+    n0, n1 = int(no[lo]), int(no[hi])
+    e0, e1 = int(rp[n0]), int(rp[n1])
+    counts = np.diff(no[lo:hi + 1])
+    return PackedBatch((no[lo:hi + 1] - n0).astype(np.int32), np.asarray(b.labels)[n0:n1], (rp[n0:n1 + 1] - e0).astype(np.int32),
+                       np.asarray(b.col)[e0:e1], np.asarray(b.val)[e0:e1], int(counts.max()) if hi > lo else 0)
+
+
+def make_rank_data(rank, world=1, scaling='weak', db_scale=1):
+    """-> (encoder, queries, this rank's database shard, id offset of the shard, database graphs over all ranks).
+    weak: every rank owns its own N_DB * db_scale graphs; strong (BASELINE configs[3] as written): ONE database of
+    N_DB * db_scale graphs split into contiguous shards (distributed.shard_range).  db_scale > 1 tiles the corpus."""
     from graphembedding_b200 import data as D
+    from graphembedding_b200 import distributed as DS
     from graphembedding_b200.graphs import NodeFeatureOneHotEncoder, pack_nx_graphs
+    from graphembedding_b200.native import PackedBatch
     enc = NodeFeatureOneHotEncoder([], 'type', feat_idx_dic={l: i for i, l in enumerate(D.AIDS_LABELS)})
-    q_gs, db_gs = rank_corpora(rank)
-    return enc, pack_nx_graphs(q_gs, enc), pack_nx_graphs(db_gs, enc)
+    q_gs, db_gs = rank_corpora(rank if scaling == 'weak' else 0)
+    q, db = pack_nx_graphs(q_gs, enc), pack_nx_graphs(db_gs, enc)
+    if db_scale > 1:
+        db = PackedBatch.concat([db] * db_scale)
+    if scaling == 'weak':
+        return enc, q, db, rank * db.n_graphs, world * db.n_graphs
+    total = db.n_graphs
+    lo, hi = DS.shard_range(total, rank, world)
+    return enc, q, slice_batch(db, lo, hi), lo, total
 
 
 def make_train_data(rank, world, n_batches=8):
@@ -290,14 +313,21 @@ def run_reference(args):
         'e2e': {'value': value, 'unit': 'pairs/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}))
 
 
-def workload_config(model=None):
+def workload_config(model=None, scaling='weak', db_total=None, world=1):
     model = model or HEADLINE
-    return {'workload': 'all-pairs ranking, BASELINE configs[3] on the configs[0]/[1] model: {} queries x {} database '
-                        'graphs per GPU, AIDS-shaped (2..10 nodes, 29 labels), {}, top-{}'
-                        .format(M_QUERIES, N_DB, MODELS[model][2], TOPK),
-            'model': model, 'queries': M_QUERIES, 'db_per_gpu': N_DB, 'topk': TOPK,
-            'l2': 'flushed between timed steps (256 MiB write; N > 1: followed by a device-side barrier, both untimed)',
-            'ntn_mode': 'reference', 'dropout': 0.0}
+    cfg = {'workload': 'all-pairs ranking, BASELINE configs[3] on the configs[0]/[1] model: {} queries x {} database '
+                       'graphs per GPU, AIDS-shaped (2..10 nodes, 29 labels), {}, top-{}'
+                       .format(M_QUERIES, N_DB, MODELS[model][2], TOPK),
+           'model': model, 'queries': M_QUERIES, 'db_per_gpu': N_DB, 'topk': TOPK,
+           'l2': 'flushed between timed steps (256 MiB write; N > 1: followed by a device-side barrier, both untimed)',
+           'ntn_mode': 'reference', 'dropout': 0.0}
+    if scaling != 'weak' or (db_total is not None and db_total != N_DB * world):
+        cfg['workload'] = cfg['workload'].replace('{} database graphs per GPU'.format(N_DB),
+                                                  '{} database graphs in total ({} scaling: contiguous shards)'.format(db_total, scaling)
+                                                  if scaling != 'weak' else '{} database graphs per GPU'.format(db_total // world))
+        cfg['db_total'] = db_total
+        cfg['db_per_gpu'] = db_total // world
+    return cfg
 
 
 def timed_steps(torch, fn, steps, flush, align=None):
@@ -345,22 +375,25 @@ def pair_stage_flops(layers, q, db):
 
 
 def rank_bench(model, torch, dist, dev, rank, world, local, args, barrier, max_over_ranks, q, db, flush, clocks=None,
-               exchange_ok=True):
+               id_offset=None, n_total=None):
     """The ranking step of one model: device-timed value, per-stage kernel times, roofline of the dominant kernel,
     end-to-end through the host entry points, parity sample against the fp32 oracle port."""
     from graphembedding_b200 import distributed as DS
     from graphembedding_b200.engine import SgnnEngine
     from graphembedding_b200.layers_factory import parse_layers
     spec, kw, desc = MODELS[model]
+    n_loc = db.n_graphs
+    id_offset = rank * n_loc if id_offset is None else id_offset
+    n_total = world * n_loc if n_total is None else n_total
     layers = parse_layers(spec, 29)
     eng = SgnnEngine(layers, 29, device=local, precision=args.precision, **kw)
     eng.init_params(123)
-    eng.reserve(max_graphs=N_DB, max_nodes=max(q.total_nodes, db.total_nodes), max_nnz=db.nnz, max_queries=M_QUERIES,
-                max_db=N_DB)
+    eng.reserve(max_graphs=max(n_loc, M_QUERIES), max_nodes=max(q.total_nodes, db.total_nodes), max_nnz=db.nnz, max_queries=M_QUERIES,
+                max_db=n_loc)
     qd, dbd = q.to(dev), db.to(dev)
     E = eng.emb_dim
-    emb_q, emb_db = torch.empty((M_QUERIES, E), device=dev), torch.empty((N_DB, E), device=dev)
-    sim = torch.empty((M_QUERIES, N_DB), dtype=torch.float32, device=dev)
+    emb_q, emb_db = torch.empty((M_QUERIES, E), device=dev), torch.empty((n_loc, E), device=dev)
+    sim = torch.empty((M_QUERIES, n_loc), dtype=torch.float32, device=dev)
     ids_d = torch.empty((M_QUERIES, TOPK), dtype=torch.int32, device=dev)
     vals_d = torch.empty((M_QUERIES, TOPK), dtype=torch.float32, device=dev)
     gids_d, gvals_d = torch.empty_like(ids_d), torch.empty_like(vals_d)   # global top-k after the exchange (N > 1)
@@ -381,7 +414,7 @@ def rank_bench(model, torch, dist, dev, rank, world, local, args, barrier, max_o
             peer, exchange = None, 'nccl all-gather + merge kernel'
 
     def step():
-        out['ids'], out['vals'] = DS.sharded_rank(eng, qd, dbd, rank * N_DB, TOPK, dist if world > 1 else None,
+        out['ids'], out['vals'] = DS.sharded_rank(eng, qd, dbd, id_offset, TOPK, dist if world > 1 else None,
                                                   emb_q=emb_q, emb_db=emb_db, sim=sim, peer=peer, ids=ids_d, vals=vals_d,
                                                   out_ids=gids_d, out_vals=gvals_d)
 
@@ -394,7 +427,7 @@ def rank_bench(model, torch, dist, dev, rank, world, local, args, barrier, max_o
         torch.cuda.synchronize()
         got_i, got_v = out['ids'].clone(), out['vals'].clone()
         li, lv, _ = eng.rank_device(qd, dbd, TOPK, emb_q=emb_q, emb_db=emb_db, sim=sim)
-        cv, ci = DS.gather_topk_candidates(lv, li, rank * N_DB, dist)
+        cv, ci = DS.gather_topk_candidates(lv, li, id_offset, dist)
         wi, wv = eng.topk_merge(cv, ci, TOPK)
         torch.cuda.synchronize()
         ok = torch.tensor([1 if (torch.equal(got_i, wi) and torch.equal(got_v, wv)) else 0], device=dev)
@@ -418,14 +451,14 @@ def rank_bench(model, torch, dist, dev, rank, world, local, args, barrier, max_o
         clocks.mark('timed_end')
     launches = eng.launches - launches0
     ms_per_step = max_over_ranks(total_ms) / args.steps
-    res = {'model': model, 'value': M_QUERIES * N_DB * world / (ms_per_step * 1e-3), 'unit': 'pairs/s',
+    res = {'model': model, 'value': M_QUERIES * n_total / (ms_per_step * 1e-3), 'unit': 'pairs/s',
            'ms_per_step': ms_per_step, 'gpu_launches': launches, 'exchange': exchange}
     if verified is not None:
         res['exchange_verified'] = verified
     res.update(rank_stages(model, torch, eng, layers, q, db, qd, dbd, emb_q, emb_db, sim, args, flush))
     if clocks is not None:
         clocks.mark('load_end')
-    res['e2e'] = rank_e2e(torch, eng, q, db, dev, world, args, barrier, max_over_ranks, out.get('ids'))
+    res['e2e'] = rank_e2e(torch, eng, q, db, dev, world, args, barrier, max_over_ranks, out.get('ids'), n_total)
     if world == 1:
         res['parity'] = rank_parity(model, torch, eng, layers, q, db, qd, dbd)
     if peer is not None:
@@ -497,7 +530,7 @@ def rank_stages(model, torch, eng, layers, q, db, qd, dbd, emb_q, emb_db, sim, a
                                                                  eng.STAGE_PREP_DATABASE), K, flush) / K
     e_ms = timed_steps(torch, lambda: (eng.embed(qd, out=emb_q), eng.embed(dbd, out=emb_db)), K, flush) / K
     peak, peak_src = peaks()
-    alg_bytes = 4.0 * M_QUERIES * N_DB + 4.0 * (M_QUERIES + N_DB) * eng.emb_dim
+    alg_bytes = 4.0 * M_QUERIES * db.n_graphs + 4.0 * (M_QUERIES + db.n_graphs) * eng.emb_dim
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
     tc = args.precision != 'fp32'
     return {'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
@@ -507,7 +540,7 @@ def rank_stages(model, torch, eng, layers, q, db, qd, dbd, emb_q, emb_db, sim, a
                          'stage_ms': {'embed_q_plus_db': e_ms, 'operand_prep_q_plus_db': p_ms, 'scorer': k_ms, 'topk': t_ms}}}
 
 
-def rank_e2e(torch, eng, q, db, dev, world, args, barrier, max_over_ranks, dev_ids):
+def rank_e2e(torch, eng, q, db, dev, world, args, barrier, max_over_ranks, dev_ids, n_total):
     """The same step through the host C-ABI entry points: pinned HOST buffers in, top-k out, wall clock."""
     def timed(fn):
         t_w, n_w = time.perf_counter(), 0
@@ -527,7 +560,7 @@ def rank_e2e(torch, eng, q, db, dev, world, args, barrier, max_over_ranks, dev_i
     if world == 1 and dev_ids is not None:
         assert torch.equal(ids_h.to(dev), dev_ids), 'host entry point and device path disagree'
     d2h = 2 * 4 * M_QUERIES * TOPK
-    csr = {'value': M_QUERIES * N_DB * world / (e2e_ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': e2e_ms,
+    csr = {'value': M_QUERIES * n_total / (e2e_ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': e2e_ms,
            'h2d_bytes_per_step': q.nbytes() + db.nbytes(), 'd2h_bytes_per_step': d2h,
            'entry_point': 'sgnn_rank_host (int32 / float CSR arrays from pinned host memory)'}
     # the same step with the batches in the compact wire format (sgnn_compact_batch: byte-wide fields + value
@@ -539,7 +572,7 @@ def rank_e2e(torch, eng, q, db, dev, world, args, barrier, max_over_ranks, dev_i
         ids_c, vals_c = both[0], both[1].view(torch.float32)
         c_ms = timed(lambda: eng.rank_host_compact(qc, dbc, TOPK, ids=ids_c, vals=vals_c))
         assert torch.equal(ids_c, ids_h), 'compact and plain host entry points disagree'
-        e2e = {'value': M_QUERIES * N_DB * world / (c_ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': c_ms,
+        e2e = {'value': M_QUERIES * n_total / (c_ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': c_ms,
                'h2d_bytes_per_step': int(qc.numel() + dbc.numel()), 'd2h_bytes_per_step': d2h,
                'entry_point': 'sgnn_rank_host_compact (compact wire blobs from pinned host memory, expanded on the device)',
                'plain_csr': csr}
@@ -603,16 +636,16 @@ def run_cuda(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    enc, q, db = make_rank_data(rank)
+    enc, q, db, id_offset, n_total = make_rank_data(rank, world, args.scaling, args.db_scale)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     clocks = ClockSampler(local)
     clocks.start()
     common = (torch, dist, dev, rank, world, local, args, barrier, max_over_ranks)
-    head = rank_bench(HEADLINE, *common, q, db, flush, clocks=clocks)
+    head = rank_bench(HEADLINE, *common, q, db, flush, clocks=clocks, id_offset=id_offset, n_total=n_total)
     clk = clocks.stop()
     extra = {}
     if not args.headline_only:
-        other = rank_bench('default', *common, q, db, flush)
+        other = rank_bench('default', *common, q, db, flush, id_offset=id_offset, n_total=n_total)
         extra['default_model'] = {k: other[k] for k in ('value', 'unit', 'ms_per_step', 'gpu_launches', 'roofline', 'e2e', 'parity')
                                   if k in other}
         extra['default_model']['workload'] = MODELS['default'][2]
@@ -626,10 +659,10 @@ def run_cuda(args):
         dist.destroy_process_group()
     if rank != 0:
         return
-    cfg = workload_config()
+    cfg = workload_config(scaling=args.scaling, db_total=n_total, world=world)
     line = {'metric': 'graph-pairs/sec (all-pairs ranking inference)', 'value': head['value'], 'unit': 'pairs/s',
             'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': head['ms_per_step'],
-            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+            'higher_is_better': True, 'scaling': args.scaling, 'vs_baseline': None,
             'dtype': 'f32' if args.precision == 'fp32' else args.precision, 'data': 'synthetic',
             'config': cfg, 'clocks': clk, 'e2e': head['e2e'], 'gpu_launches': head['gpu_launches'],
             'roofline': head['roofline'], 'exchange': head['exchange']}
@@ -638,7 +671,8 @@ def run_cuda(args):
             line[k] = head[k]
     if world == 1 and not args.no_cpu_baseline:
         from oracle import batched as OB
-        v, cores, sample = cpu_rank_baseline(HEADLINE, OB.pad_from_packed(q), OB.pad_from_packed(db), q_sample=64)
+        v, cores, sample = cpu_rank_baseline(HEADLINE, OB.pad_from_packed(q),
+                                             OB.pad_from_packed(slice_batch(db, 0, min(db.n_graphs, N_DB))), q_sample=64)
         q_gs, db_gs = rank_corpora(0)
         line['cpu_baseline'] = {'value': v, 'unit': 'pairs/s', 'cores': cores, 'kind': 'port', 'sample': sample,
                                 'per_pair_reference_structure_pairs_per_s': cpu_per_pair_rate(HEADLINE, q_gs, db_gs)}
@@ -859,7 +893,7 @@ def rank_parity(model, torch, eng, layers, q, db, qd, dbd, nq=64, nd=1000):
     got = sim[:nq, :nd].cpu().numpy().astype(np.float64)
     eng.set_params(eng2_params)
     pq = tuple(t[:nq] for t in OB.pad_from_packed(q))
-    pd = tuple(t[:nd] for t in OB.pad_from_packed(db))
+    pd = OB.pad_from_packed(slice_batch(db, 0, min(nd, db.n_graphs)))
     if eng.has_head:
         xq, hq = OB.embed(ol, P, *pq, with_nodes=True)
         xd, hd = OB.embed(ol, P, *pd, with_nodes=True)
@@ -885,6 +919,9 @@ def main():
     ap.add_argument('--steps', type=int, default=20)
     ap.add_argument('--warmup', type=int, default=5)
     ap.add_argument('--impl', default='cuda', choices=['cuda', 'reference'])
+    ap.add_argument('--scaling', default='weak', choices=['weak', 'strong'],
+                    help='weak: N_DB database graphs PER GPU (default); strong: one database split into contiguous shards')
+    ap.add_argument('--db-scale', type=int, default=1, help='tile the 10 000-graph database corpus this many times')
     ap.add_argument('--headline-only', action='store_true', help='skip the sub-benchmarks (default model, train, web, metrics)')
     ap.add_argument('--precision', default='bf16x3', choices=['fp32', 'bf16x3', 'bf16'],
                     help='all-pairs scorer: bf16x3 = tcgen05 with split-bf16 operands and fp32 accumulation (fp32-grade, '

@@ -5,7 +5,7 @@ import torch
 import bench
 from graphembedding_b200.engine import SgnnEngine
 from graphembedding_b200.layers_factory import parse_layers
-enc, q, db = bench.make_rank_data(0)
+enc, q, db = bench.make_rank_data(0)[:3]
 eng = SgnnEngine(parse_layers(bench.DEFAULT_LAYERS, 29), 29, precision='bf16x3')
 eng.init_params(123)
 eng.reserve(max_graphs=bench.N_DB, max_nodes=db.total_nodes, max_nnz=db.nnz, max_queries=bench.M_QUERIES, max_db=bench.N_DB)

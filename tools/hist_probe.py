@@ -12,7 +12,7 @@ from graphembedding_b200.layers_factory import parse_layers
 
 M, N = int(os.environ.get('PROBE_M', bench.M_QUERIES)), int(os.environ.get('PROBE_N', bench.N_DB))
 bench.M_QUERIES, bench.N_DB = M, N
-enc, q, db = bench.make_rank_data(0)
+enc, q, db = bench.make_rank_data(0)[:3]
 
 
 def engine(precision):

@@ -16,7 +16,7 @@ rank, world, local = int(os.environ['RANK']), int(os.environ['WORLD_SIZE']), int
 torch.cuda.set_device(local)
 dist.init_process_group('nccl', device_id=torch.device('cuda', local))
 torch.cuda.set_stream(torch.cuda.Stream())
-enc, q, db = bench.make_rank_data(rank)
+enc, q, db = bench.make_rank_data(rank)[:3]
 eng = SgnnEngine(parse_layers(bench.DEFAULT_LAYERS, 29), 29, device=local, precision='bf16x3')
 eng.init_params(123)
 eng.reserve(max_graphs=bench.N_DB, max_nodes=db.total_nodes, max_nnz=db.nnz, max_queries=bench.M_QUERIES, max_db=bench.N_DB)

@@ -484,9 +484,15 @@ int score_all_pairs_stages(SgnnHandle h, const float* emb_q, int32_t m, const fl
           (tc_db && (h->hside[1].total_rows >= 0 ? h->hside[1].total_rows : (int64_t)n * mx_db) / HG.S + 1 > t.cap_a_tiles))
         return fail(h, "histogram workspace too small: call sgnn_reserve(max_nodes >= total_nodes, max_queries, max_db) first");
     }
+    // the per-query P' / C tables feed the CUDA-core head kernels only: with the tensor-core head they are built
+    // lazily by the scorer stage, in the rare case that the database side turns out not to fit (22 us off the
+    // query branch of the ranking step)
+    const bool lazy_tables = head_tc && (M.hist_bins == 0 || tc_q);
     if (stages & SCORE_PREP_Q) {
-      allpairs_prep_kernel<<<(m + 3) / 4, 128, 0, st>>>(M, h->d_params, emb_q, m, h->dep, h->d_P, h->d_C);
-      CUDA_OK(h, cudaGetLastError());
+      if (!lazy_tables) {
+        allpairs_prep_kernel<<<(m + 3) / 4, 128, 0, st>>>(M, h->d_params, emb_q, m, h->dep, h->d_P, h->d_C);
+        CUDA_OK(h, cudaGetLastError());
+      }
       if (tc_q) CUDA_OK(h, sgnn_hist_tc_prep_q(HG, h->hside[0].rows, h->hside[0].node_off, h->ht, st));
     }
     if ((stages & SCORE_PREP_DB) && tc_db)
@@ -497,6 +503,10 @@ int score_all_pairs_stages(SgnnHandle h, const float* emb_q, int32_t m, const fl
       if (tc_hist) CUDA_OK(h, sgnn_hist_tc_run(HG, h->ht, h->hside[1].node_off, h->sm_count, st));
       return score_all_pairs_tc(h, emb_q, m, emb_db, n, sim_dev, ld, st, SCORE_MAIN, nullptr, true,
                                 tc_hist ? h->ht.cnt : nullptr, h->hside[0].node_off, h->hside[1].node_off);
+    }
+    if (lazy_tables) {   // the tensor-core head was planned but this database does not fit it
+      allpairs_prep_kernel<<<(m + 3) / 4, 128, 0, st>>>(M, h->d_params, emb_q, m, h->dep, h->d_P, h->d_C);
+      CUDA_OK(h, cudaGetLastError());
     }
     if (tc_hist) {
       CUDA_OK(h, sgnn_hist_tc_run(HG, h->ht, h->hside[1].node_off, h->sm_count, st));

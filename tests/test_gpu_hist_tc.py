@@ -144,3 +144,27 @@ def test_all_pairs_with_tensor_core_histogram_matches_oracle_and_cuda_core_path(
     assert np.max(np.abs(sims[0] - ref)[ok]) <= RTOL
     assert np.max(np.abs(sims[1] - ref)[ok]) <= RTOL
     assert np.max(np.abs(sims[0] - sims[1])[ok]) <= RTOL
+
+
+def test_tensor_core_engine_falls_back_when_the_database_graphs_are_too_large():
+    """Queries fit the tensor-core histogram (<= 10 nodes) but the database does not (30-node graphs: 10 x 30 cells do
+    not fit a count byte): the scorer stage takes the CUDA-core kernels, building the per-query tables it skipped on the
+    query branch.  Same scores as the fp32 engine, through the staged ranking entry point too."""
+    from graphembedding_b200.graphs import pack_nx_graphs
+    eng, layers, flat = _engine('simgnn', precision='bf16x3', final_act='sigmoid')
+    eng32, _, _ = _engine('simgnn', precision='fp32', final_act='sigmoid')
+    qs, dbs = corpus(20, 2, 10, 5), corpus(90, 12, 30, 6)
+    enc = encoder_for(qs + dbs)
+    qb, db = pack_nx_graphs(qs, enc), pack_nx_graphs(dbs, enc)
+    assert db.max_nodes > 25
+    out = []
+    for e in (eng, eng32):
+        e.reserve(max_graphs=90, max_nodes=qb.total_nodes + db.total_nodes, max_nnz=db.nnz, max_queries=20, max_db=90)
+        qd, dd = qb.to(e.device), db.to(e.device)
+        eq, rq = e.embed_nodes(qd)
+        ed, rd = e.embed_nodes(dd)
+        a = e.score_all_pairs_nodes(eq, rq, qd, ed, rd, dd).cpu().numpy()
+        ids, vals, sim = e.rank_device(qd, dd, 5)
+        assert np.array_equal(sim.cpu().numpy(), a)
+        out.append(a)
+    assert np.array_equal(out[0], out[1])          # both engines ran the same CUDA-core kernels

@@ -10,6 +10,7 @@
 // exactly rounded.  Shapes served: K = 16 feature maps, head widths 16 / 8 / 4 / 1, 16 bins or no histogram;
 // everything else stays on the CUDA-core kernel (sgnn_head.cu).
 #pragma once
+#include <cuda_fp16.h>
 #include "sgnn_allpairs_tc.cuh"
 
 constexpr int TCH_K = 16, TCH_H0 = 16, TCH_H1 = 8, TCH_H2 = 4;
@@ -42,6 +43,7 @@ struct TcHeadEpi {
   float* sim;
   int64_t ld;
   int m, n;
+  float hscale;                    // HMMA: inverse of the power-of-two scale of the fp16 weight parts
   const uint8_t* cnt;              // [m][n][16] bin counts (HIST)
   const int32_t* node_off_q;
   const int32_t* node_off_db;
@@ -162,9 +164,11 @@ __device__ __forceinline__ void tch_tail2(const TcHeadEpi& E, const float* sW, t
 // [qrow0 + 4 part, + 4) of the tile, processed as two passes of two queries.  The code is kept SMALL on purpose (part
 // is a run-time value, the k loops are rolled in chunks): 16 epilogue warps at different places of a fully unrolled
 // 50 KB epilogue starved on instruction fetch (ncu r2d: stall_no_instruction 5.7 per issue).
-template <bool HIST, bool CONSTW>
-__device__ __forceinline__ void tc_head_epilogue_part(const TcHeadEpi& E, uint32_t taddr, int qrow0, int part, int g,
-                                                      uint64_t* t_empty, int lane) {
+// HMMA: the histogram half of layer 0 was done by the tensor core (second accumulator at taddr2: 16 columns per
+// query = sum_b count_b W0[16 + b][:]); the epilogue only scales it by 1 / (N_q N_g) into the layer-0 accumulators.
+template <bool HIST, bool CONSTW, bool HMMA>
+__device__ __forceinline__ void tc_head_epilogue_part(const TcHeadEpi& E, uint32_t taddr, uint32_t taddr2, int qrow0,
+                                                      int part, int g, uint64_t* t_empty, int lane) {
   const bool gv = g < E.n;
   int n_g = 1;
   if (HIST && gv) n_g = E.node_off_db[g + 1] - E.node_off_db[g];
@@ -178,9 +182,11 @@ __device__ __forceinline__ void tc_head_epilogue_part(const TcHeadEpi& E, uint32
     const bool va = qa < E.m, vb = qb < E.m;
     uint4 ca = make_uint4(0u, 0u, 0u, 0u), cb = ca;
     int nqa = 0, nqb = 0;
-    if (HIST) {   // issued first: the loads are in flight while the NTN half runs
+    if (HIST && !HMMA) {   // issued first: the loads are in flight while the NTN half runs
       if (gv && va) ca = __ldg(reinterpret_cast<const uint4*>(E.cnt + ((size_t)qa * E.n + g) * 16));
       if (gv && vb) cb = __ldg(reinterpret_cast<const uint4*>(E.cnt + ((size_t)qb * E.n + g) * 16));
+    }
+    if (HIST) {
       if (va) nqa = E.node_off_q[qa + 1] - E.node_off_q[qa];
       if (vb) nqb = E.node_off_q[qb + 1] - E.node_off_q[qb];
     }
@@ -195,7 +201,7 @@ __device__ __forceinline__ void tc_head_epilogue_part(const TcHeadEpi& E, uint32
       tc::tmem_ld8(t0 + kc, va8);
       tc::tmem_ld8(t0 + kc + TCH_K, vb8);
       tc::tmem_ld_wait();
-      if (qp == 1 && kc == TCH_K - 8) {   // last TMEM read of this part: hand the buffer back to its MMA issuer
+      if (!HMMA && qp == 1 && kc == TCH_K - 8) {   // last TMEM read of this part: hand the buffer back to its MMA issuer
         tc::tc_fence_before();
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(t_empty);
@@ -209,9 +215,28 @@ __device__ __forceinline__ void tc_head_epilogue_part(const TcHeadEpi& E, uint32
     if (HIST) {
       const float sa = nqa * n_g > 0 ? 1.f / (float)(nqa * n_g) : 0.f;
       const float sb = nqb * n_g > 0 ? 1.f / (float)(nqb * n_g) : 0.f;
+      if (HMMA) {
+        float ha[TCH_H0], hb[TCH_H0];
+        const uint32_t t2 = taddr2 + (uint32_t)((4 * part + 2 * qp) * TCH_H0);
+        tc::tmem_ld16(t2, ha);
+        tc::tmem_ld16(t2 + TCH_H0, hb);
+        tc::tmem_ld_wait();
+        if (qp == 1) {   // last TMEM read of this part (both accumulators of the tile go back together)
+          tc::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) tc::mbar_arrive(t_empty);
+        }
+        const float sah = sa * E.hscale, sbh = sb * E.hscale;
+        const tch_f2 sa2 = tch_pack(sah, sah), sb2 = tch_pack(sbh, sbh);
+#pragma unroll
+        for (int j = 0; j < TCH_H0 / 2; ++j) {
+          tch_fma2(A[j], sa2, tch_pack(ha[2 * j], ha[2 * j + 1]));
+          tch_fma2(B[j], sb2, tch_pack(hb[2 * j], hb[2 * j + 1]));
+        }
+      }
       const float msa = -8388608.f * sa, msb = -8388608.f * sb;
 #pragma unroll 1
-      for (int wd = 0; wd < 4; ++wd) {   // four bins per count word; the words rotate through .x
+      for (int wd = 0; wd < (HMMA ? 0 : 4); ++wd) {   // four bins per count word; the words rotate through .x
         const float4* w = reinterpret_cast<const float4*>(sW + TCH_W0 + (TCH_K + 4 * wd) * TCH_H0);
 #pragma unroll
         for (int b = 0; b < 4; ++b)
@@ -227,15 +252,37 @@ __device__ __forceinline__ void tc_head_epilogue_part(const TcHeadEpi& E, uint32
   }
 }
 
-// Producer and MMA roles of the head kernel: ONE issuer warp for all four TMEM buffers (a tile's epilogue runs for
+// Producer and MMA roles of the head kernel: ONE issuer warp for all TMEM buffers (a tile's epilogue runs for
 // ~20 us, the issue rate does not matter), so the CTA has 18 warps and the epilogue gets 96 registers per thread
 // instead of the 80 that the 21-warp scorer leaves (register allocation is per 4 warps).
+// HMMA (second MMA per tile): TMEM holds two NTN accumulators (columns 0..255) and two histogram accumulators
+// (256..511), one of each per epilogue group.  The bin counts arrive as fp16 K-major operand tiles written by the
+// histogram kernel (ht_cnt_tiled_bytes: one 4 KB block per (database tile, query), the 8 queries of a query block
+// contiguous), one 32 KB bulk copy per tile into a two-slot ring; the layer-0 rows of the histogram bins are a
+// three-way fp16 split staged in shared memory once per CTA.  Per query: D2[128 graphs][16] (+)= counts
+// [128][16 bins] x W_part[16 bins][16] for the three parts -- integers <= 255 times fp16 parts, accumulated in fp32.
 constexpr int TCH_THREADS = 32 * (TC_EPI_WARPS + 2);
 constexpr int TCH_MMA_WARP = TC_EPI_WARPS + 1;
+constexpr int TCH_A2_BYTES = 8 * 4096;          // one tile's count blocks (8 queries)
+constexpr int TCH_WH_BYTES = 3 * 512;           // three fp16 parts of W0[16 + b][j], K-major 16 x 16
+constexpr int TCH_HMMA_SMEM = 2 * TCH_A2_BYTES + TCH_WH_BYTES + 64;
+struct TchHmma {
+  uint8_t* sA2;          // [2][TCH_A2_BYTES]
+  uint8_t* sWh;          // [3][512]
+  uint64_t* a2_full;     // [2]
+  uint64_t* a2_empty;    // [2]
+  const uint8_t* cnt;    // operand tiles in global memory
+  int m_pad;
+};
+__device__ __forceinline__ uint32_t tch_idesc_f16(int M, int N) {   // A fp16, B fp16, D fp32, both K-major
+  return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);   // (fp16 x bf16 is an illegal instruction)
+}
+template <bool HMMA>
 __device__ __forceinline__ void tch_producer_mma_roles(const TcGeom& G, const TcCtaWork& Wk, const TcSmem& S,
-                                                       const __nv_bfloat16* __restrict__ Ag,
+                                                       const TchHmma& H, const __nv_bfloat16* __restrict__ Ag,
                                                        const __nv_bfloat16* __restrict__ Bg, uint32_t tmem_base, int warp,
                                                        int lane) {
+  constexpr int NB = HMMA ? 2 : TC_BUFS;
   const int ga_count = Wk.ga_count, nq = Wk.nq;
   if (lane != 0 || nq <= 0) return;
   if (warp == TC_PROD_WARP) {
@@ -243,12 +290,23 @@ __device__ __forceinline__ void tch_producer_mma_roles(const TcGeom& G, const Tc
     for (int ga = 0; ga < ga_count; ++ga)
       tc::bulk_g2s(S.sA + ga * S.a_bytes, reinterpret_cast<const uint8_t*>(Ag) + (size_t)(Wk.gt0 + ga) * S.a_bytes,
                    S.a_bytes, S.a_full);
+    int it = 0;
     for (int i = 0; i < nq; ++i) {
       const int s = i % G.stages;
       if (i >= G.stages) tc::mbar_wait(S.b_empty + s, ((i / G.stages) - 1) & 1);
       tc::mbar_arrive_expect_tx(S.b_full + s, S.b_bytes);
       tc::bulk_g2s(S.sB + s * S.b_bytes, reinterpret_cast<const uint8_t*>(Bg) + (size_t)(Wk.qb0 + i) * S.b_bytes,
                    S.b_bytes, S.b_full + s);
+      if (HMMA) {
+        for (int ga = 0; ga < ga_count; ++ga, ++it) {
+          const int sl = it & 1;
+          if (it >= 2) tc::mbar_wait(H.a2_empty + sl, ((it >> 1) - 1) & 1);
+          tc::mbar_arrive_expect_tx(H.a2_full + sl, TCH_A2_BYTES);
+          tc::bulk_g2s(H.sA2 + sl * TCH_A2_BYTES,
+                       H.cnt + ((size_t)(Wk.gt0 + ga) * H.m_pad + (size_t)(Wk.qb0 + i) * 8) * 4096, TCH_A2_BYTES,
+                       H.a2_full + sl);
+        }
+      }
     }
     return;
   }
@@ -259,6 +317,12 @@ __device__ __forceinline__ void tch_producer_mma_roles(const TcGeom& G, const Tc
   const uint64_t b_desc0 = tc::umma_desc(tc::smem_u32(S.sB), TC_NPAD * 16, 128);
   const uint32_t a_tile = (uint32_t)S.a_bytes >> 4, b_tile = (uint32_t)S.b_bytes >> 4;
   const int combos = G.parts == 2 ? 3 : 1, ksteps = G.KCH / 2;
+  const uint32_t idesc2 = tch_idesc_f16(128, TCH_H0);
+  uint64_t a2_desc0 = 0, wh_desc0 = 0;
+  if (HMMA) {
+    a2_desc0 = tc::umma_desc(tc::smem_u32(H.sA2), 128 * 16, 128);
+    wh_desc0 = tc::umma_desc(tc::smem_u32(H.sWh), TCH_H0 * 16, 128);
+  }
   tc::mbar_wait(S.a_full, 0);
   int it = 0;
   for (int i = 0; i < nq; ++i) {   // tile order: query block i outer, database tile ga inner (as the epilogue walks it)
@@ -266,8 +330,8 @@ __device__ __forceinline__ void tch_producer_mma_roles(const TcGeom& G, const Tc
     tc::mbar_wait(S.b_full + s, (i / G.stages) & 1);
     const uint64_t bd0 = b_desc0 + (uint64_t)((uint32_t)s * b_tile);
     for (int ga = 0; ga < ga_count; ++ga, ++it) {
-      const int buf = it & (TC_BUFS - 1);
-      if (it >= TC_BUFS) tc::mbar_wait(S.t_empty + buf, ((it / TC_BUFS) - 1) & 1);
+      const int buf = it & (NB - 1);
+      if (it >= NB) tc::mbar_wait(S.t_empty + buf, ((it / NB) - 1) & 1);
       tc::tc_fence_after();
       const uint64_t ad0 = a_desc0 + (uint64_t)((uint32_t)ga * a_tile);
       const uint32_t d_addr = tmem_base + (uint32_t)buf * TC_NPAD;
@@ -279,30 +343,47 @@ __device__ __forceinline__ void tch_producer_mma_roles(const TcGeom& G, const Tc
           acc = 1;
         }
       }
+      if (HMMA) {
+        const int sl = it & 1;
+        tc::mbar_wait(H.a2_full + sl, (it >> 1) & 1);
+        const uint64_t a2d = a2_desc0 + (uint64_t)((uint32_t)sl * (TCH_A2_BYTES >> 4));
+        const uint32_t d2 = tmem_base + 2u * TC_NPAD + (uint32_t)buf * TC_NPAD;
+        for (int q = 0; q < 8; ++q)
+          for (int sp = 0; sp < 3; ++sp)
+            tc::umma_bf16(d2 + (uint32_t)(q * TCH_H0), a2d + (uint64_t)(q * (4096 >> 4)), wh_desc0 + (uint64_t)(sp * (512 >> 4)),
+                          idesc2, sp > 0 ? 1u : 0u);
+      }
       tc::umma_commit(S.t_full + buf);
+      if (HMMA) tc::umma_commit(H.a2_empty + (it & 1));
     }
     if (nq > G.stages) tc::umma_commit(S.b_empty + s);   // the stage is free once this block's MMAs have completed
   }
 }
 
-template <bool HIST, bool CONSTW>
+template <bool HIST, bool CONSTW, bool HMMA>
 __global__ void __launch_bounds__(TCH_THREADS, 1)
 allpairs_tc_head_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const float* __restrict__ params, int slot,
                         const __nv_bfloat16* __restrict__ Ag, const __nv_bfloat16* __restrict__ Bg,
                         float* __restrict__ sim, int64_t ld, const uint8_t* __restrict__ cnt,
                         const int32_t* __restrict__ node_off_q, const int32_t* __restrict__ node_off_db) {
+  static_assert(!HMMA || HIST, "the second MMA is the histogram half of layer 0");
+  constexpr int NB = HMMA ? 2 : TC_BUFS;
   extern __shared__ __align__(1024) uint8_t tc_smem[];
   uint8_t* smem = tc_smem;
   const int a_bytes = tc_a_bytes(G), b_bytes = tc_b_bytes(G);
   uint8_t* sA = smem;
   uint8_t* sB = sA + TC_GA_MAX * a_bytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + G.stages * b_bytes);
+  uint8_t* sA2 = sB + G.stages * b_bytes;
+  uint8_t* sWh = sA2 + (HMMA ? 2 * TCH_A2_BYTES : 0);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sWh + (HMMA ? TCH_WH_BYTES : 0));
   uint64_t* a_full = bars;
   uint64_t* b_full = bars + 1;
   uint64_t* b_empty = b_full + G.stages;
   uint64_t* t_full = b_empty + G.stages;
   uint64_t* t_empty = t_full + TC_BUFS;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + TC_BUFS);
+  uint64_t* a2_full = t_empty + TC_BUFS;
+  uint64_t* a2_empty = a2_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(a2_empty + 2);
   // TCH_FLOATS, 16-byte aligned (pointer arithmetic, not an integer round trip: the pointer stays a shared-memory pointer)
   float* sW = reinterpret_cast<float*>(tmem_slot + 4) + (((16u - (tc::smem_u32(tmem_slot + 4) & 15u)) & 15u) >> 2);
 
@@ -318,12 +399,41 @@ allpairs_tc_head_kernel(const __grid_constant__ ModelDev M, const TcGeom G, cons
   if (threadIdx.x == 0) {
     tc::mbar_init(a_full, 1);
     for (int s = 0; s < G.stages; ++s) { tc::mbar_init(b_full + s, 1); tc::mbar_init(b_empty + s, 1); }
-    for (int b = 0; b < TC_BUFS; ++b) { tc::mbar_init(t_full + b, 1); tc::mbar_init(t_empty + b, 8); }
+    for (int b = 0; b < NB; ++b) { tc::mbar_init(t_full + b, 1); tc::mbar_init(t_empty + b, 8); }
+    if (HMMA)
+      for (int b = 0; b < 2; ++b) { tc::mbar_init(a2_full + b, 1); tc::mbar_init(a2_empty + b, 1); }
+    tmem_slot[1] = 0u;
     tc::fence_barrier_init();
   }
   // ---- head weights: U folded into the NTN rows of layer 0, missing biases = 0 ----
   if (!CONSTW)
     for (int i = threadIdx.x; i < TCH_FLOATS; i += blockDim.x) sW[i] = tch_weight(M, params, i);
+  if (HMMA) {
+    // layer-0 rows of the 16 bins as three fp16 parts, K-major.  The rows are scaled by a power of two that puts
+    // the largest |w| in [2^14, 2^15): hi + mid + lo then equals the scaled fp32 weight up to 2^-25 (fp16 subnormal
+    // grid), i.e. every weight is exact to 2^-39 of the largest one; the epilogue multiplies the inverse back in.
+    uint32_t* s_wmax = tmem_slot + 1;
+    float w = 0.f;
+    const int b = threadIdx.x >> 4, j = threadIdx.x & 15;
+    if (threadIdx.x < 16 * TCH_H0) w = tch_weight(M, params, TCH_W0 + (TCH_K + b) * TCH_H0 + j);
+    __syncthreads();   // s_wmax = 0 (thread 0, above)
+    if (threadIdx.x < 16 * TCH_H0) atomicMax(s_wmax, __float_as_uint(fabsf(w)));
+    __syncthreads();
+    const int e = (int)(*s_wmax >> 23) - 127;
+    const int S = *s_wmax == 0u ? 0 : max(-100, min(100, 14 - e));
+    if (threadIdx.x < 16 * TCH_H0) {
+      w *= __uint_as_float((uint32_t)(S + 127) << 23);
+      __half* dst = reinterpret_cast<__half*>(sWh + (b >> 3) * 256 + j * 16) + (b & 7);
+#pragma unroll
+      for (int sp = 0; sp < 3; ++sp) {
+        const __half hv = __float2half_rn(w);
+        dst[sp * 256] = hv;
+        w -= __half2float(hv);
+      }
+    }
+    if (threadIdx.x == 0) *reinterpret_cast<float*>(tmem_slot + 2) = __uint_as_float((uint32_t)(127 - S) << 23);
+    tc::fence_proxy_async_smem();
+  }
   if (warp == TC_PROD_WARP) tc::tmem_alloc(tmem_slot, 512);
   tc::tc_fence_before();
   __syncthreads();
@@ -333,22 +443,24 @@ allpairs_tc_head_kernel(const __grid_constant__ ModelDev M, const TcGeom G, cons
   if (warp >= TC_PROD_WARP) {
     TcCtaWork Wk{gt0, ga_count, qb0, nq};
     TcSmem S{sA, sB, a_full, b_full, b_empty, t_full, t_empty, a_bytes, b_bytes};
-    tch_producer_mma_roles(G, Wk, S, Ag, Bg, tmem_base, warp, lane);
+    TchHmma H{sA2, sWh, a2_full, a2_empty, cnt, G.n_qblocks * 8};
+    tch_producer_mma_roles<HMMA>(G, Wk, S, H, Ag, Bg, tmem_base, warp, lane);
   } else {
     TcHeadEpi E;
     E.sW = sW; E.slot = slot; E.act_ntn = M.pair_act; E.act0 = M.Hd[0].act; E.act1 = M.Hd[1].act; E.act2 = M.Hd[2].act;
     E.act3 = M.Hd[3].act; E.final_act = M.final_act; E.yeta = M.yeta;
+    E.hscale = HMMA ? *reinterpret_cast<const float*>(tmem_slot + 2) : 1.f;
     E.sim = sim; E.ld = ld; E.m = G.m; E.n = G.n; E.cnt = cnt; E.node_off_q = node_off_q; E.node_off_db = node_off_db;
     const int lg = warp & 3, part = (warp >> 2) & 1, grp = warp >> 3;
     const int total = nq * ga_count;
     int i = grp / ga_count, ga = grp - i * ga_count;
     for (int it = grp; it < total; it += TC_EPI_GROUPS) {
-      const int buf = it & (TC_BUFS - 1);
-      tc::mbar_wait(t_full + buf, (it / TC_BUFS) & 1);
+      const int buf = it & (NB - 1);
+      tc::mbar_wait(t_full + buf, (it / NB) & 1);
       tc::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + buf * TC_NPAD;
       const int g = (gt0 + ga) * 128 + lg * 32 + lane;
-      tc_head_epilogue_part<HIST, CONSTW>(E, taddr, (qb0 + i) * G.QH, part, g, t_empty + buf, lane);
+      tc_head_epilogue_part<HIST, CONSTW, HMMA>(E, taddr, taddr + 2 * TC_NPAD, (qb0 + i) * G.QH, part, g, t_empty + buf, lane);
       ga += TC_EPI_GROUPS;
       while (ga >= ga_count) { ga -= ga_count; ++i; }
     }

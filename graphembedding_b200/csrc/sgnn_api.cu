@@ -348,6 +348,12 @@ bool head_tc_enabled(SgnnHandle h) {
          (h->M.hist_bins == 0 || hist_tc_enabled(h));
 }
 
+// histogram half of head layer 0 as a second MMA of the head kernel (SGNN_HEAD_HMMA=0: multiplied by the epilogue threads)
+bool head_hmma_enabled() {
+  static const bool off = [] { const char* e = getenv("SGNN_HEAD_HMMA"); return e && e[0] == '0'; }();
+  return !off;
+}
+
 int ensure_query_tables(SgnnHandle h, int64_t m) {
   if (m <= h->cap_P) return 0;
   return fail(h, "query table workspace too small: call sgnn_reserve(max_queries >= m) first");
@@ -368,7 +374,7 @@ enum { SCORE_PREP_Q = 1, SCORE_PREP_DB = 2, SCORE_MAIN = 4, SCORE_ALL = 7,
 int score_all_pairs_tc(SgnnHandle h, const float* emb_q, int m, const float* emb_db, int n, float* sim,
                        int64_t ld, cudaStream_t st, int stages, unsigned long long* smax, bool head = false,
                        const uint8_t* cnt = nullptr, const int32_t* node_off_q = nullptr,
-                       const int32_t* node_off_db = nullptr) {
+                       const int32_t* node_off_db = nullptr, bool cnt_tiled = false) {
   const ModelDev& M = h->M;
   const bool ntn = M.pair_kind == SGNN_LAYER_NTN;
   TcGeom G;
@@ -394,7 +400,7 @@ int score_all_pairs_tc(SgnnHandle h, const float* emb_q, int m, const float* emb
   const int64_t need_b = (int64_t)G.n_qblocks * G.parts * G.KCH * (TC_NPAD * 8);
   if (need_a > h->cap_Atc || need_b > h->cap_Btc)
     return fail(h, "tensor-core operand workspace too small: call sgnn_reserve(max_queries, max_db) first");
-  const size_t fixed = (size_t)TC_GA_MAX * tc_a_bytes(G) + TC_TAIL_BYTES + 1024 + (head ? sgnn_tc_head_smem_bytes() : 0);
+  const size_t fixed = (size_t)TC_GA_MAX * tc_a_bytes(G) + TC_TAIL_BYTES + 1024 + (head ? sgnn_tc_head_smem_bytes(cnt_tiled) : 0);
   if (fixed + 2 * (size_t)tc_b_bytes(G) > (size_t)h->smem_optin)
     return fail(h, "embedding too wide for the tensor-core all-pairs tiles");
   G.stages = (int)std::min<size_t>(std::min(G.qb_per_group, TC_MAX_STAGES), ((size_t)h->smem_optin - fixed) / tc_b_bytes(G));
@@ -410,7 +416,7 @@ int score_all_pairs_tc(SgnnHandle h, const float* emb_q, int m, const float* emb
     e = sgnn_tc_prep_q(M, G, h->d_params, emb_q, h->d_Btc, h->d_coef, (stages & SCORE_COEF_READY) ? 2 : 0, st);
   if (e == cudaSuccess && (stages & SCORE_PREP_DB)) e = sgnn_tc_prep_db(M, G, emb_db, h->d_Atc, st);
   if (e == cudaSuccess && (stages & SCORE_MAIN))
-    e = head ? sgnn_tc_score_head(M, G, grid, smem, h->d_params, h->head_slot, h->d_Atc, h->d_Btc, sim, ld, cnt, node_off_q, node_off_db, st)
+    e = head ? sgnn_tc_score_head(M, G, grid, smem, h->d_params, h->head_slot, h->d_Atc, h->d_Btc, sim, ld, cnt, cnt_tiled, node_off_q, node_off_db, st)
              : sgnn_tc_score(M, G, relu, ref, simk, grid, smem, h->d_params, h->d_Atc, h->d_Btc, sim, ld, smax, st);
   if (e != cudaSuccess) return fail(h, std::string("tensor-core all-pairs launch: ") + cudaGetErrorString(e));
   return 0;
@@ -500,9 +506,13 @@ int score_all_pairs_stages(SgnnHandle h, const float* emb_q, int32_t m, const fl
     if (!(stages & SCORE_MAIN)) return 0;
     cudaError_t e;
     if (head_tc && (M.hist_bins == 0 || tc_hist)) {
+      // the counts leave the histogram kernel as fp16 operand tiles: the head kernel multiplies them with the layer-0
+      // rows of the bins on the tensor core (SGNN_HEAD_HMMA=0: bytes, multiplied by the epilogue threads)
+      const bool tiled = tc_hist && head_hmma_enabled() && ht_cnt_tiled_bytes(m, n) <= h->ht.cap_cnt;
+      if (tiled) HG.cnt_m_pad = (m + 7) / 8 * 8;
       if (tc_hist) CUDA_OK(h, sgnn_hist_tc_run(HG, h->ht, h->hside[1].node_off, h->sm_count, st));
       return score_all_pairs_tc(h, emb_q, m, emb_db, n, sim_dev, ld, st, SCORE_MAIN, nullptr, true,
-                                tc_hist ? h->ht.cnt : nullptr, h->hside[0].node_off, h->hside[1].node_off);
+                                tc_hist ? h->ht.cnt : nullptr, h->hside[0].node_off, h->hside[1].node_off, tiled);
     }
     if (lazy_tables) {   // the tensor-core head was planned but this database does not fit it
       allpairs_prep_kernel<<<(m + 3) / 4, 128, 0, st>>>(M, h->d_params, emb_q, m, h->dep, h->d_P, h->d_C);
@@ -894,7 +904,7 @@ int sgnn_reserve(SgnnHandle h, int64_t max_graphs, int64_t max_nodes, int64_t ma
       if (dev_alloc(h, &t.status, 4)) return 1;
       CUDA_OK(h, cudaMemset(t.status, 0, 16));
     }
-    const int64_t need_cnt = max_queries * max_db * HT_CNT_BYTES;
+    const int64_t need_cnt = std::max<int64_t>(max_queries * max_db * HT_CNT_BYTES, ht_cnt_tiled_bytes(max_queries, max_db));
     if (need_cnt > t.cap_cnt) {
       if (dev_alloc(h, &t.cnt, need_cnt)) return 1;
       t.cap_cnt = need_cnt;

@@ -247,6 +247,13 @@ __device__ __forceinline__ unsigned long long ht_segment(const float* v, float f
   return nib;
 }
 
+// two count bytes of `word` (PRMT selector sel) as a packed pair of exact fp16 values
+__device__ __forceinline__ uint32_t ht_half2(uint32_t word, uint32_t sel) {
+  uint32_t r = __byte_perm(word, 0x64646464u, sel);
+  asm("sub.rn.f16x2 %0, %0, %1;" : "+r"(r) : "r"(0x64006400u));
+  return r;
+}
+
 struct HtTileCtx {
   uint32_t taddr;                 // this warp's lanes, this tile's TMEM buffer
   int n_seg, bt_first;            // B tile: segments, first sorted query
@@ -258,8 +265,9 @@ struct HtTileCtx {
   int bins;
   const int32_t* q_sorted;
   const int32_t* node_off_db;
-  uint8_t* cnt_out;               // [m][n][16]
+  uint8_t* cnt_out;               // [m][n][16] bytes, or fp16 operand tiles (m_pad > 0)
   int n;
+  int m_pad;                      // > 0: counts leave as the A operand of the head kernel's second MMA (ht_cnt_tiled_bytes)
 };
 
 // One tile for one epilogue group (HT_GROUP_WARPS warps: 4 TMEM lane quadrants x 1 or 2 halves; the warps of a quadrant
@@ -368,7 +376,16 @@ __device__ __forceinline__ void ht_tile(const HtTileCtx& C, int row, int tid, in
       }
       add_field(C.bins - 1, extra);
       const int q = C.q_sorted[C.bt_first + s0 + (int)sg];
-      *reinterpret_cast<uint4*>(C.cnt_out + ((size_t)q * C.n + (size_t)(C.g0 + (int)gi)) * HT_CNT_BYTES) = o;
+      if (C.m_pad > 0) {
+        // fp16 K-major operand tiles [g / 128][q][k chunk][g % 128][8 bins]: half(1024 + c) has the bits 0x6400 | c, so
+        // a count byte becomes an exact fp16 with one PRMT and half a packed subtraction
+        const int g = C.g0 + (int)gi;
+        uint4* dst = reinterpret_cast<uint4*>(C.cnt_out) + ((size_t)(g >> 7) * C.m_pad + q) * 256 + (g & 127);
+        dst[0] = make_uint4(ht_half2(o.x, 0x4140), ht_half2(o.x, 0x4342), ht_half2(o.y, 0x4140), ht_half2(o.y, 0x4342));
+        dst[128] = make_uint4(ht_half2(o.z, 0x4140), ht_half2(o.z, 0x4342), ht_half2(o.w, 0x4140), ht_half2(o.w, 0x4342));
+      } else {
+        *reinterpret_cast<uint4*>(C.cnt_out + ((size_t)q * C.n + (size_t)(C.g0 + (int)gi)) * HT_CNT_BYTES) = o;
+      }
     }
   }
 }
@@ -522,7 +539,7 @@ hist_tc_kernel(const HistTcGeom G, const __nv_bfloat16* __restrict__ At, const _
       C.fb = (float)G.bins; C.bins = G.bins;
       C.q_sorted = bt_first + G.max_btiles;
       C.node_off_db = node_off_db;
-      C.cnt_out = cnt_out; C.n = G.n;
+      C.cnt_out = cnt_out; C.n = G.n; C.m_pad = G.cnt_m_pad;
       int ab = ab0, b = b0, it = 0, batch = 0;
       for (long long u = u0; u < u1; ++u) {
         const int ga = min(HT_GA, n_at - ab * HT_GA);

@@ -28,6 +28,7 @@ struct HistTcGeom {
   int bins;
   int S;               // database tile stride in node rows (129 - max_nodes_db)
   int max_atiles, max_btiles;
+  int cnt_m_pad = 0;   // 0: counts as bytes [m][n][16]; > 0 (= round_up(m, 8)): fp16 operand tiles of the head kernel
 };
 
 __host__ __device__ inline int ht_tile_bytes(const HistTcGeom& G) { return G.parts * G.ksteps * 4096; }
@@ -46,6 +47,9 @@ struct HistTcWs {
   int parts = 0, ksteps = 0;
 };
 
+// count matrix as fp16 K-major operand tiles [ceil(n / 128)][round_up(m, 8)][2 k chunks][128 graphs][8 bins]: the A
+// operand of the head kernel's second MMA (sgnn_allpairs_tc_head.cuh), one 4 KB block per (database tile, query)
+inline int64_t ht_cnt_tiled_bytes(int64_t m, int64_t n) { return ((n + 127) / 128) * ((m + 7) / 8 * 8) * 4096; }
 inline int ht_max_btiles(int64_t m) { return (int)(m / 8 + 16); }                 // worst case: 15-node queries, 8 per tile
 inline int64_t ht_max_atiles(int64_t rows) { return rows / (129 - HT_MAXN_DB) + 2; }
 

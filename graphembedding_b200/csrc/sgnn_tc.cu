@@ -86,7 +86,7 @@ bool sgnn_tc_head_supported(const ModelDev& M) {
          M.Hd[2].din == TCH_H1 && M.Hd[2].dout == TCH_H2 && M.Hd[3].din == TCH_H2 && M.Hd[3].dout == 1 &&
          !M.Hd[0].drop && !M.Hd[1].drop && !M.Hd[2].drop && !M.Hd[3].drop;
 }
-int sgnn_tc_head_smem_bytes() { return TCH_SMEM_BYTES; }
+int sgnn_tc_head_smem_bytes(bool hmma) { return TCH_SMEM_BYTES + (hmma ? TCH_HMMA_SMEM : 0); }
 
 // refresh constant slot `slot` from the parameters (stream-ordered: kernel -> staging -> copy into the symbol)
 cudaError_t sgnn_tc_head_weights(const ModelDev& M, const float* params, float* staging, int slot, cudaStream_t st) {
@@ -104,7 +104,7 @@ int sgnn_tc_head_staging_floats() { return TCH_SLOT_FLOATS; }
 // shared memory by the kernel itself
 cudaError_t sgnn_tc_score_head(const ModelDev& M, const TcGeom& G, int grid, size_t smem, const float* params, int slot,
                                const void* A_ws, const void* B_ws, float* sim, int64_t ld, const uint8_t* cnt,
-                               const int32_t* node_off_q, const int32_t* node_off_db, cudaStream_t st) {
+                               bool cnt_tiled, const int32_t* node_off_q, const int32_t* node_off_db, cudaStream_t st) {
   if (!sgnn_tc_head_supported(M) || G.KC != TCH_K || G.QH != 8 || slot >= TCH_SLOTS) return cudaErrorInvalidValue;
   const __nv_bfloat16* A = static_cast<const __nv_bfloat16*>(A_ws);
   const __nv_bfloat16* B = static_cast<const __nv_bfloat16*>(B_ws);
@@ -115,6 +115,8 @@ cudaError_t sgnn_tc_score_head(const ModelDev& M, const TcGeom& G, int grid, siz
     return cudaGetLastError();
   };
   const bool hist = M.hist_bins > 0;
-  if (slot >= 0) return hist ? launch_it(allpairs_tc_head_kernel<true, true>) : launch_it(allpairs_tc_head_kernel<false, true>);
-  return hist ? launch_it(allpairs_tc_head_kernel<true, false>) : launch_it(allpairs_tc_head_kernel<false, false>);
+  if (cnt_tiled && !hist) return cudaErrorInvalidValue;
+  if (cnt_tiled) return slot >= 0 ? launch_it(allpairs_tc_head_kernel<true, true, true>) : launch_it(allpairs_tc_head_kernel<true, false, true>);
+  if (slot >= 0) return hist ? launch_it(allpairs_tc_head_kernel<true, true, false>) : launch_it(allpairs_tc_head_kernel<false, true, false>);
+  return hist ? launch_it(allpairs_tc_head_kernel<true, false, false>) : launch_it(allpairs_tc_head_kernel<false, false, false>);
 }

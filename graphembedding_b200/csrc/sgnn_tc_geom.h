@@ -68,7 +68,7 @@ cudaError_t sgnn_tc_score(const ModelDev& M, const TcGeom& G, bool relu, bool re
 // SimGNN-style head on the scorer's epilogue (sgnn_allpairs_tc_head.cuh): K = 16, head widths 16 / 8 / 4 / 1, no head
 // dropout, 16 bins (cnt = the tensor-core histogram's count matrix) or no histogram; G must be built with KC == K
 bool sgnn_tc_head_supported(const ModelDev& M);
-int sgnn_tc_head_smem_bytes();
+int sgnn_tc_head_smem_bytes(bool hmma);   // hmma: the histogram half of layer 0 as a second MMA (counts as fp16 operand tiles)
 // head weights in constant memory: TCH slots per device (one per engine); sgnn_tc_head_weights refreshes a slot from
 // the parameters on the stream (staging: sgnn_tc_head_staging_floats() device floats owned by the engine)
 int sgnn_tc_head_slots();
@@ -76,5 +76,6 @@ int sgnn_tc_head_staging_floats();
 cudaError_t sgnn_tc_head_weights(const ModelDev& M, const float* params, float* staging, int slot, cudaStream_t st);
 cudaError_t sgnn_tc_score_head(const ModelDev& M, const TcGeom& G, int grid, size_t smem, const float* params, int slot,
                                const void* A_ws, const void* B_ws, float* sim, int64_t ld, const uint8_t* cnt,
-                               const int32_t* node_off_q, const int32_t* node_off_db, cudaStream_t st);
+                               bool cnt_tiled, const int32_t* node_off_q, const int32_t* node_off_db, cudaStream_t st);
+// cnt_tiled: cnt holds the fp16 operand tiles of ht_cnt_tiled_bytes (HistTcGeom::cnt_m_pad), not [m][n][16] bytes
 inline int tc_n_slices(int n) { return ((n + 127) / 128) * 4; }

@@ -27,7 +27,7 @@ cudaError_t sgnn_hist_tc_run(const HistTcGeom& G, const HistTcWs& ws, const int3
                              cudaStream_t st) {
   static const bool unpaired = getenv("SGNN_HIST_UNPAIRED") != nullptr;   // one reciprocal per cell (cross-check)
   const size_t smem = (size_t)(HT_GA + HT_STAGES) * ht_tile_bytes(G) + (size_t)HT_GROUPS * 2 * HT_SEGB * 128 * 8 +
-                      (2 + 2 * HT_STAGES + 2 * HT_BUFS) * 8 + 16;
+                      (2 + 2 * HT_STAGES + 2 * HT_BUFS) * 8 + 16 + 32 * 8;
   auto launch = [&](auto kern) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;

@@ -196,52 +196,55 @@ __device__ __forceinline__ uint32_t ht_bin_bits(float sigma, float fb) {
   asm("fma.rm.f32 %0, %1, %2, 0f4B000000;" : "=f"(y) : "f"(sigma), "f"(fb));
   return __float_as_uint(y);
 }
-// nib += 16^bin: bin in the low 5 bits of `bits`; bin 16 (sigma == 1) gives t2 == 0 and adds nothing
-__device__ __forceinline__ void ht_count(unsigned long long& nib, uint32_t bits) {
-  uint32_t t;
-  asm("shf.l.wrap.b32 %0, 0, 1, %1;" : "=r"(t) : "r"(bits));   // upper word of (1 << 32) << (bits & 31) = 1 << (bits & 31)
-  const uint32_t t2 = t * t;                                    // 1 << 2 bin (0 for bin >= 16)
-  asm("mad.wide.u32 %0, %1, %1, %0;" : "+l"(nib) : "r"(t2));
+// nib += 16^bin: bin in the low 5 bits of `bits` (= 0x4B000000 + bin).  The one-hot nibble word comes from a 32-entry
+// table in shared memory (entries >= 16 are 0: sigma == 1 adds nothing): one address computation + one LDS.64
+// instead of a shift and two multiplies, and it moves the work from the ALU / FMA pipes to the idle LSU.  lutc = table
+// address - ((0x4B000000 << 3) mod 2^32), so that bits * 8 + lutc is the entry's address (32-bit wrap-around).
+__device__ __forceinline__ void ht_count(unsigned long long& nib, uint32_t bits, uint32_t lutc) {
+  unsigned long long one;
+  asm("ld.shared.u64 %0, [%1];" : "=l"(one) : "r"(bits * 8u + lutc));
+  nib += one;
 }
 
 // the n cells of one (lane, query) segment -> 16 nibble counters
+// fb = number of bins, ci = 1 / (fb (1 + eps)), eps = 4 ulp: the paired form's operand scale
 template <int N, bool PAIRED>
-__device__ __forceinline__ unsigned long long ht_segment(const float* v, float fb) {
+__device__ __forceinline__ unsigned long long ht_segment(const float* v, float fb, float ci, uint32_t lutc) {
   unsigned long long nib = 0ull;
+  constexpr float BIAS = 2.4e-7f;
   if constexpr (!PAIRED) {
 #pragma unroll
     for (int i = 0; i < N; ++i) {
       const float u = ht_ex2(v[i]);                 // exp(-s)
       const float sg = ht_rcp(1.f + u);             // sigmoid(s); 1 / inf = 0
-      ht_count(nib, ht_bin_bits(sg, fb));
+      ht_count(nib, ht_bin_bits(sg, fb), lutc);
     }
   } else {
-    // one reciprocal per two cells: 1 / (v1 v2) = r, sigma1 = r v2, sigma2 = r v1.  The arguments are clamped so
-    // that the product stays finite; the tiny positive bias keeps sigmoid(0) = 1/2 on the upper side of its edge.
-    constexpr float BIAS = 2.4e-7f;
+    // one reciprocal per two cells.  With v = (1 + u) ci:  r = 1 / (v1 v2),  r v2 = 1 / v1 = fb (1 + eps) sigma1 and
+    // r v1 = fb (1 + eps) sigma2 -- the bin is the round-down fma of that onto 2^23 (one ulp = 1), so a pair costs
+    // fma.f32x2, mul, rcp, fma.rm.f32x2.  The arguments are clamped so that the product stays finite; eps (4 ulp,
+    // above the error of the approximate reciprocal and the two roundings) keeps sigmoid(0) = 1/2 on the upper side
+    // of its edge.  Which sigma belongs to which cell does not matter, both go into the same histogram.
 #pragma unroll
     for (int i = 0; i + 1 < N; i += 2) {
-      // the two cells as one packed pair (add / fma / fma.rm .f32x2: three instructions instead of six); which
-      // sigma belongs to which cell does not matter, both go into the same histogram
-      unsigned long long u12, v12, s12, y12;
+      unsigned long long u12, v12, y12, c2, r2, m2;
       asm("mov.b64 %0, {%1, %2};" : "=l"(u12) : "f"(ht_ex2(fminf(v[i], 60.f))), "f"(ht_ex2(fminf(v[i + 1], 60.f))));
-      asm("add.rn.f32x2 %0, %1, %2;" : "=l"(v12) : "l"(u12), "l"(0x3F8000003F800000ull));
+      asm("mov.b64 %0, {%1, %1};" : "=l"(c2) : "f"(ci));
+      asm("fma.rn.f32x2 %0, %1, %2, %2;" : "=l"(v12) : "l"(u12), "l"(c2));
       float v1, v2;
       asm("mov.b64 {%0, %1}, %2;" : "=f"(v1), "=f"(v2) : "l"(v12));
       const float r = ht_rcp(v1 * v2);
-      unsigned long long r2, b2, f2, m2;
       asm("mov.b64 %0, {%1, %1};" : "=l"(r2) : "f"(r));
-      asm("mov.b64 %0, {%1, %1};" : "=l"(b2) : "f"(BIAS));
-      asm("mov.b64 %0, {%1, %1};" : "=l"(f2) : "f"(fb));
       asm("mov.b64 %0, {%1, %1};" : "=l"(m2) : "f"(8388608.f));
-      asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(s12) : "l"(r2), "l"(v12), "l"(b2));     // (r v1, r v2) = (sigma2, sigma1)
-      asm("fma.rm.f32x2 %0, %1, %2, %3;" : "=l"(y12) : "l"(s12), "l"(f2), "l"(m2));     // low mantissa bits = floor(sigma fb)
-      ht_count(nib, (uint32_t)y12);
-      ht_count(nib, (uint32_t)(y12 >> 32));
+      asm("fma.rm.f32x2 %0, %1, %2, %3;" : "=l"(y12) : "l"(r2), "l"(v12), "l"(m2));
+      uint32_t y1, y2;
+      asm("mov.b64 {%0, %1}, %2;" : "=r"(y1), "=r"(y2) : "l"(y12));
+      ht_count(nib, y1, lutc);
+      ht_count(nib, y2, lutc);
     }
     if constexpr (N & 1) {
       const float u = ht_ex2(v[N - 1]);
-      ht_count(nib, ht_bin_bits(ht_rcp(1.f + u) + BIAS, fb));
+      ht_count(nib, ht_bin_bits(ht_rcp(1.f + u) + BIAS, fb), lutc);
     }
   }
   return nib;
@@ -261,7 +264,8 @@ struct HtTileCtx {
   unsigned long long* s_cnt;      // [HT_SEGB][128] of this epilogue group
   uint64_t* t_empty;
   int bar_id;
-  float fb;
+  float fb, ci;                   // bins; 1 / (bins (1 + 4 ulp))
+  uint32_t lutc;                  // one-hot table (ht_count)
   int bins;
   const int32_t* q_sorted;
   const int32_t* node_off_db;
@@ -311,7 +315,7 @@ __device__ __forceinline__ void ht_tile(const HtTileCtx& C, int row, int tid, in
           if (lane == 0) tc::mbar_arrive(C.t_empty);
           released = true;
         }
-        const unsigned long long w0 = ht_segment<N, PAIRED>(v, C.fb), w1 = ht_segment<N, PAIRED>(v + N, C.fb);
+        const unsigned long long w0 = ht_segment<N, PAIRED>(v, C.fb, C.ci, C.lutc), w1 = ht_segment<N, PAIRED>(v + N, C.fb, C.ci, C.lutc);
         cnt[sg * 128 + row] = w0;
         cnt[(sg + 1) * 128 + row] = w1;
       } else {
@@ -326,7 +330,7 @@ __device__ __forceinline__ void ht_tile(const HtTileCtx& C, int row, int tid, in
           if (lane == 0) tc::mbar_arrive(C.t_empty);
           released = true;
         }
-        cnt[sg * 128 + row] = ht_segment<N, PAIRED>(v, C.fb);
+        cnt[sg * 128 + row] = ht_segment<N, PAIRED>(v, C.fb, C.ci, C.lutc);
       }
     }
     if (last_batch && !released) {   // (a warp without segments in the last batch)
@@ -430,8 +434,10 @@ hist_tc_kernel(const HistTcGeom G, const __nv_bfloat16* __restrict__ At, const _
   uint64_t* t_full = b_empty + HT_STAGES;     // [HT_BUFS]
   uint64_t* t_empty = t_full + HT_BUFS;       // [HT_BUFS]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + HT_BUFS);
+  unsigned long long* s_lut = reinterpret_cast<unsigned long long*>(tmem_slot + 2);   // [32] one-hot nibble words
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x < 32) s_lut[threadIdx.x] = threadIdx.x < 16 ? 1ull << (4 * threadIdx.x) : 0ull;
   const int n_b = qmeta[0], n_at = qmeta[1];
   const int n_ab = (n_at + HT_GA - 1) / HT_GA;
   const long long total_units = (long long)n_ab * n_b;
@@ -537,6 +543,8 @@ hist_tc_kernel(const HistTcGeom G, const __nv_bfloat16* __restrict__ At, const _
       C.s_cnt = s_cnt + grp * (2 * HT_SEGB * 128);   // two batches deep
       C.bar_id = 1 + grp;
       C.fb = (float)G.bins; C.bins = G.bins;
+      C.ci = 1.f / (C.fb * (1.f + 4.8e-7f));
+      C.lutc = tc::smem_u32(s_lut) - G.lut_bias;   // (a kernel argument: ptxas must not split it into base + offset + immediate)
       C.q_sorted = bt_first + G.max_btiles;
       C.node_off_db = node_off_db;
       C.cnt_out = cnt_out; C.n = G.n; C.m_pad = G.cnt_m_pad;

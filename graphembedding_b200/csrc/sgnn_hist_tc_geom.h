@@ -28,6 +28,7 @@ struct HistTcGeom {
   int bins;
   int S;               // database tile stride in node rows (129 - max_nodes_db)
   int max_atiles, max_btiles;
+  uint32_t lut_bias = 0x58000000u;   // (0x4B000000 << 3) mod 2^32: see ht_count
   int cnt_m_pad = 0;   // 0: counts as bytes [m][n][16]; > 0 (= round_up(m, 8)): fp16 operand tiles of the head kernel
 };
 

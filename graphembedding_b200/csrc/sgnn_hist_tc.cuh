@@ -551,8 +551,13 @@ hist_tc_kernel(const HistTcGeom G, const __nv_bfloat16* __restrict__ At, const _
       int ab = ab0, b = b0, it = 0, batch = 0;
       for (long long u = u0; u < u1; ++u) {
         const int ga = min(HT_GA, n_at - ab * HT_GA);
-        for (int a = 0; a < ga; ++a, ++it) {
-          if ((it % HT_GROUPS) != grp) continue;
+        // (ga <= HT_GROUPS: at most one tile of a unit belongs to this group -- no walk over the other groups' tiles)
+        static_assert(HT_GA <= HT_GROUPS && (HT_GROUPS & (HT_GROUPS - 1)) == 0, "one tile per unit and group");
+        const int a = (grp - it) & (HT_GROUPS - 1);
+        const int it_unit = it;
+        it += ga;
+        if (a < ga) {
+          const int it = it_unit + a;
           const int buf = it & (HT_BUFS - 1);
           const int t = ab * HT_GA + a;
           C.g0 = ameta[t]; C.ng = ameta[t + 1] - C.g0; C.row0 = node_off_db[C.g0];

@@ -3,7 +3,8 @@
 #include "sgnn_hist_tc.cuh"
 
 bool sgnn_hist_tc_supported(int node_dim, int bins, int max_nodes_q, int max_nodes_db) {
-  return node_dim >= 1 && node_dim <= 32 && bins >= 1 && bins <= HT_MAX_BINS && max_nodes_q >= 1 &&
+  // node rows of at most 16 values: one K step; the 7 operand tiles (3 parts x 4 KB) + counter batches fill shared memory
+  return node_dim >= 1 && node_dim <= 16 && bins >= 1 && bins <= HT_MAX_BINS && max_nodes_q >= 1 &&
          max_nodes_q <= HT_MAXN && max_nodes_db >= 1 && max_nodes_db <= HT_MAXN_DB &&
          max_nodes_q * max_nodes_db <= 255;   // one byte per bin in the count matrix
 }
@@ -26,7 +27,7 @@ cudaError_t sgnn_hist_tc_prep_db(const HistTcGeom& G, const float* nodes_db, con
 cudaError_t sgnn_hist_tc_run(const HistTcGeom& G, const HistTcWs& ws, const int32_t* node_off_db, int sm_count,
                              cudaStream_t st) {
   static const bool unpaired = getenv("SGNN_HIST_UNPAIRED") != nullptr;   // one reciprocal per cell (cross-check)
-  const size_t smem = (size_t)(HT_GA + HT_STAGES) * ht_tile_bytes(G) + (size_t)HT_GROUPS * 2 * HT_SEGB * 128 * 8 +
+  const size_t smem = (size_t)(HT_GA + HT_STAGES) * ht_tile_bytes(G) + (size_t)HT_GROUPS * 2 * HT_SEGB * HT_CSTRIDE * 8 +
                       (2 + 2 * HT_STAGES + 2 * HT_BUFS) * 8 + 16 + 32 * 8;
   auto launch = [&](auto kern) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -282,9 +282,10 @@ template <int N, bool PAIRED>
 __device__ __forceinline__ void ht_tile(const HtTileCtx& C, int row, int tid, int half, int lane, int& batch) {
   // the first pair this thread reduces: its lane range is fetched now, long before it is needed
   int pre_l0 = 0, pre_l1 = 0;
-  if (tid < C.ng) {
-    pre_l0 = C.node_off_db[C.g0 + tid] - C.row0;
-    pre_l1 = C.node_off_db[C.g0 + tid + 1] - C.row0;
+  const int pre_gi = tid / max(1, min(HT_SEGB, C.n_seg));   // graph of this thread's first pair (first batch)
+  if (pre_gi < C.ng) {
+    pre_l0 = C.node_off_db[C.g0 + pre_gi] - C.row0;
+    pre_l1 = C.node_off_db[C.g0 + pre_gi + 1] - C.row0;
   }
   const uint32_t ng = (uint32_t)C.ng;
   if (C.n_seg == 0) {   // (never produced by the tile table; keeps the barrier protocol whole)
@@ -294,7 +295,7 @@ __device__ __forceinline__ void ht_tile(const HtTileCtx& C, int row, int tid, in
   }
   for (int s0 = 0; s0 < C.n_seg; s0 += HT_SEGB, ++batch) {
     const int ns = min(HT_SEGB, C.n_seg - s0);
-    unsigned long long* const cnt = C.s_cnt + (batch & 1) * (HT_SEGB * 128);
+    unsigned long long* const cnt = C.s_cnt + (batch & 1) * (HT_SEGB * HT_CSTRIDE);
     // two segments per iteration (one TMEM wait and one loop overhead for 2 N cells); iterations alternate
     // between the two halves of the quadrant
     const bool last_batch = s0 + ns == C.n_seg;
@@ -316,8 +317,8 @@ __device__ __forceinline__ void ht_tile(const HtTileCtx& C, int row, int tid, in
           released = true;
         }
         const unsigned long long w0 = ht_segment<N, PAIRED>(v, C.fb, C.ci, C.lutc), w1 = ht_segment<N, PAIRED>(v + N, C.fb, C.ci, C.lutc);
-        cnt[sg * 128 + row] = w0;
-        cnt[(sg + 1) * 128 + row] = w1;
+        cnt[sg * HT_CSTRIDE + row] = w0;
+        cnt[(sg + 1) * HT_CSTRIDE + row] = w1;
       } else {
         float v[N];
         tc::tmem_ld_n<N>(C.taddr + (uint32_t)((s0 + sg) * N), v);
@@ -330,7 +331,7 @@ __device__ __forceinline__ void ht_tile(const HtTileCtx& C, int row, int tid, in
           if (lane == 0) tc::mbar_arrive(C.t_empty);
           released = true;
         }
-        cnt[sg * 128 + row] = ht_segment<N, PAIRED>(v, C.fb, C.ci, C.lutc);
+        cnt[sg * HT_CSTRIDE + row] = ht_segment<N, PAIRED>(v, C.fb, C.ci, C.lutc);
       }
     }
     if (last_batch && !released) {   // (a warp without segments in the last batch)
@@ -340,17 +341,21 @@ __device__ __forceinline__ void ht_tile(const HtTileCtx& C, int row, int tid, in
     }
     asm volatile("bar.sync %0, %1;" ::"r"(C.bar_id), "n"(32 * HT_GROUP_WARPS) : "memory");
     // ---- pair-parallel: thread p owns (graph gi, segment sg) of this batch ----
+    // pair p = (graph p / ns, segment p % ns): the threads of a warp share two or three graphs, so their lane loops
+    // have (nearly) the same length -- with the graph index fastest every warp ran for its longest graph (avg 13 of
+    // 32 threads active in the loop).  The counter rows are HT_CSTRIDE = 129 words apart: 32 segments of one lane
+    // sit in different banks.
     const uint32_t n_pairs = ng * (uint32_t)ns;
     for (uint32_t p = (uint32_t)tid; p < n_pairs; p += 32u * HT_GROUP_WARPS) {
-      const uint32_t sg = p / ng, gi = p - sg * ng;
+      const uint32_t gi = p / (uint32_t)ns, sg = p - gi * (uint32_t)ns;
       int l0, l1;
-      if (p < ng) { l0 = pre_l0; l1 = pre_l1; }   // (p < ng implies p == tid: the prefetched range)
+      if (s0 == 0 && p == (uint32_t)tid) { l0 = pre_l0; l1 = pre_l1; }   // the prefetched range
       else {
         l0 = C.node_off_db[C.g0 + (int)gi] - C.row0;
         l1 = C.node_off_db[C.g0 + (int)gi + 1] - C.row0;
       }
       unsigned long long ev = 0ull, od = 0ull;
-      const unsigned long long* col = cnt + sg * 128;
+      const unsigned long long* col = cnt + sg * HT_CSTRIDE;
       for (int l = l0; l < l1; ++l) {
         const unsigned long long w = col[l];
         ev += w & 0x0F0F0F0F0F0F0F0Full;
@@ -426,7 +431,7 @@ hist_tc_kernel(const HistTcGeom G, const __nv_bfloat16* __restrict__ At, const _
   uint8_t* sA = ht_smem;
   uint8_t* sB = sA + HT_GA * tile_bytes;
   unsigned long long* s_cnt = reinterpret_cast<unsigned long long*>(sB + HT_STAGES * tile_bytes);   // [HT_GROUPS][2][HT_SEGB][128]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_cnt + HT_GROUPS * 2 * HT_SEGB * 128);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_cnt + HT_GROUPS * 2 * HT_SEGB * HT_CSTRIDE);
   uint64_t* a_full = bars;                    // [1]
   uint64_t* a_free = bars + 1;                // [1]
   uint64_t* b_full = bars + 2;                // [HT_STAGES]
@@ -540,7 +545,7 @@ hist_tc_kernel(const HistTcGeom G, const __nv_bfloat16* __restrict__ At, const _
       const int32_t* bt_cnt = bt_n + G.max_btiles;
       const int32_t* bt_first = bt_cnt + G.max_btiles;
       HtTileCtx C;
-      C.s_cnt = s_cnt + grp * (2 * HT_SEGB * 128);   // two batches deep
+      C.s_cnt = s_cnt + grp * (2 * HT_SEGB * HT_CSTRIDE);   // two batches deep
       C.bar_id = 1 + grp;
       C.fb = (float)G.bins; C.bins = G.bins;
       C.ci = 1.f / (C.fb * (1.f + 4.8e-7f));

@@ -11,6 +11,7 @@ constexpr int HT_BUFS = 4;         // TMEM accumulator buffers of 128 columns
 constexpr int HT_GA = 4;           // database tiles resident per A block
 constexpr int HT_STAGES = 3;       // B-tile ring depth
 constexpr int HT_SEGB = 16;        // segments (queries) per shared-memory counter batch
+constexpr int HT_CSTRIDE = 129;    // counter words per segment row in shared memory (128 lanes + 1: the pair phase reads one lane of 32 segments)
 constexpr int HT_EPI_WARPS = 16;
 constexpr int HT_GROUP_WARPS = 4;  // warps per epilogue group (4: one warp per TMEM lane quadrant; 8: two that split a tile's segments)
 constexpr int HT_GROUPS = HT_EPI_WARPS / HT_GROUP_WARPS;

@@ -193,7 +193,7 @@ int sgnn_score_all_pairs_nodes(SgnnHandle h, const float* emb_q_dev, const float
 /* The Histogram layer of every (query, database) pair as ONE tensor-core GEMM with a binning epilogue
  * (csrc/sgnn_hist_tc.cuh; semantics of sgnn_pair_histogram, build-defined): counts_dev
  * [m][n][16] bytes, byte b = number of node-node cells of pair (i, j) in bin b (bytes >= bins are 0).
- * Needs bins <= 16, node width <= 32, max_nodes_q <= 15, max_nodes_db <= 64, max_nodes_q * max_nodes_db <= 255
+ * Needs bins <= 16, node width <= 16, max_nodes_q <= 15, max_nodes_db <= 64, max_nodes_q * max_nodes_db <= 255
  * (return code 4 otherwise: use sgnn_pair_histogram) and an engine created with a tensor-core precision;
  * workspace: sgnn_reserve(max_nodes >= database node rows, max_queries >= m, max_db >= n).  counts_dev may be
  * NULL (the internal count matrix that sgnn_score_all_pairs_nodes reads is filled).  stages: SGNN_STAGE_* flags. */

@@ -705,9 +705,11 @@ def run_web(torch, dev, rank, world, local, args, barrier, max_over_ranks, flush
     gs = W(True).graphs
     enc = NodeFeatureOneHotEncoder(gs, 'type', feat_idx_dic={l: i for i, l in enumerate(D.WebData.labels)})
     batch = pack_nx_graphs(gs, enc)
-    eng = SgnnEngine(parse_layers(TRAIN_LAYERS, 32), 32, device=local)
-    eng.init_params(123)
-    eng.reserve(max_graphs=WEB_GRAPHS, max_nodes=batch.total_nodes, max_nnz=batch.nnz, max_pairs=WEB_PAIRS)
+    eng = SgnnEngine(parse_layers(TRAIN_LAYERS, 32), 32, device=local, precision='bf16x3')   # histogram on the tensor cores
+    eng32 = SgnnEngine(parse_layers(TRAIN_LAYERS, 32), 32, device=local)                      # ... and the CUDA-core kernel beside it
+    for e in (eng, eng32):
+        e.init_params(123)
+        e.reserve(max_graphs=WEB_GRAPHS, max_nodes=batch.total_nodes, max_nnz=batch.nnz, max_pairs=WEB_PAIRS)
     bd = batch.to(dev)
     rng = np.random.default_rng(7 + rank)
     g1 = torch.as_tensor(rng.integers(0, WEB_GRAPHS, WEB_PAIRS).astype(np.int32), device=dev)
@@ -727,6 +729,11 @@ def run_web(torch, dev, rank, world, local, args, barrier, max_over_ranks, flush
     e_ms = timed_steps(torch, lambda: eng.embed_nodes(bd), args.steps, flush) / args.steps
     emb, rows = eng.embed_nodes(bd)
     h_ms = timed_steps(torch, lambda: eng.pair_histogram(rows, bd.node_off, g1, g2, bins=16), args.steps, flush) / args.steps
+    _, c_tc = eng.pair_histogram(rows, bd.node_off, g1, g2, bins=16)
+    _, c_32 = eng32.pair_histogram(rows, bd.node_off, g1, g2, bins=16)
+    h32_ms = timed_steps(torch, lambda: eng32.pair_histogram(rows, bd.node_off, g1, g2, bins=16), args.steps, flush) / args.steps
+    moved = int((c_tc - c_32).abs().sum().item()) // 2     # cells that the two kernels put into different bins (bin-edge band)
+    tpeak, tpeak_src = peak_tflops()
     no = batch.node_off
     n1 = np.diff(no)[g1.cpu().numpy()].astype(np.float64)
     n2 = np.diff(no)[g2.cpu().numpy()].astype(np.float64)
@@ -738,7 +745,13 @@ def run_web(torch, dev, rank, world, local, args, barrier, max_over_ranks, flush
                         .format(WEB_GRAPHS, batch.total_nodes / WEB_GRAPHS, batch.nnz, WEB_PAIRS),
             'value': WEB_PAIRS * world / (ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': ms,
             'graphs_per_s': WEB_GRAPHS * world / (ms * 1e-3),
-            'stage_ms': {'embed_large_with_node_rows': e_ms, 'pair_histogram': h_ms},
+            'stage_ms': {'embed_large_with_node_rows': e_ms, 'pair_histogram': h_ms, 'pair_histogram_cuda_core': h32_ms},
+            'roofline': {'bound': 'tensor', 'kernel': 'hist_pairs_tc_kernel (+ tile prep, 2 scans, finalize)',
+                         'achieved': 2.0 * 16 * cells / (h_ms * 1e-3) / 1e12, 'peak': tpeak, 'unit': 'TFLOP/s',
+                         'frac': 2.0 * 16 * cells / (h_ms * 1e-3) / 1e12 / tpeak, 'traffic': None, 'peak_source': tpeak_src,
+                         'note': 'algorithmic FLOPs 2 d per node-node cell (SURVEY 8(d)); the kernel is bound by the '
+                                 'sigmoid / bin epilogue (7.75 instructions per cell), not by the six bf16 products'},
+            'parity': {'cells_binned_differently_than_cuda_core_kernel': moved, 'cells': cells},
             'embed_gather': {'algorithmic_bytes': gather_bytes, 'achieved_GBps': gather_bytes / (e_ms * 1e-3) / 1e9,
                              'hbm_peak_GBps': peak},
             'histogram': {'node_node_cells': cells, 'cells_per_s': cells / (h_ms * 1e-3),

@@ -98,6 +98,7 @@ struct SgnnHandle_t {
   unsigned long long* d_smax = nullptr;                          // [queries][32-graph slices] slice maxima (top-k hints)
   int64_t cap_smax = 0;
   HistTcWs ht;                            // tensor-core node-node histogram: operand tiles, tile tables, count matrix
+  HistPairsWs hp;                         // the same layer on listed pairs of large graphs (grown by the call itself)
   int head_slot = -1;                     // constant-memory slot of the head weights (sgnn_allpairs_tc_head.cuh); -1: none free
   float* d_head_staging = nullptr;        // the block the slot is refreshed from
   int dep = 16;                           // padded embedding width of the all-pairs scorer
@@ -772,6 +773,7 @@ int sgnn_destroy(SgnnHandle h) {
   cudaFree(h->d_head_staging);
   cudaFree(h->ht.At); cudaFree(h->ht.Bt); cudaFree(h->ht.qmeta); cudaFree(h->ht.ameta); cudaFree(h->ht.status);
   cudaFree(h->ht.cnt);
+  cudaFree(h->hp.At); cudaFree(h->hp.Bt); cudaFree(h->hp.tile_off); cudaFree(h->hp.unit_off); cudaFree(h->hp.cnt);
   HostWs& w = h->ws;
   for (int s = 0; s < 2; ++s) {
     cudaFree(w.node_off[s]); cudaFree(w.labels[s]); cudaFree(w.rowptr[s]); cudaFree(w.col[s]); cudaFree(w.val[s]);
@@ -1019,6 +1021,39 @@ int sgnn_pair_histogram(SgnnHandle h, const float* node_emb_dev, const int32_t* 
                                    counts_dev, h->sm_count, (cudaStream_t)stream);
   }
   if (e != cudaSuccess) return fail(h, std::string("sgnn_pair_histogram: ") + cudaGetErrorString(e));
+  return 0;
+}
+
+int sgnn_pair_histogram_tc(SgnnHandle h, const float* node_emb_dev, const int32_t* node_off_dev, int32_t n_graphs,
+                           int64_t total_nodes, const int32_t* g1_dev, const int32_t* g2_dev, int32_t n_pairs,
+                           int32_t bins, float* hist_dev, int32_t* counts_dev, void* stream) {
+  if (!h || !node_emb_dev || !node_off_dev || !g1_dev || !g2_dev) return fail(h, "sgnn_pair_histogram_tc: null argument");
+  if (n_graphs < 1 || total_nodes < 0 || n_pairs < 0) return fail(h, "sgnn_pair_histogram_tc: bad sizes");
+  if (h->cfg.precision == SGNN_PREC_FP32 || !sgnn_hist_pairs_tc_supported(h->M.node_dim, bins)) {
+    h->err = "sgnn_pair_histogram_tc: needs a tensor-core precision, node rows of <= 16 values and <= 16 bins "
+             "(use sgnn_pair_histogram)";
+    return 4;
+  }
+  if (n_pairs == 0) return 0;
+  HistPairsWs& w = h->hp;
+  const int64_t tiles = hp_max_tiles(n_graphs, total_nodes);
+  if (tiles * (int64_t)n_pairs >= (int64_t)1 << 31) return fail(h, "sgnn_pair_histogram_tc: too many (pair, tile) units");
+  // workspace grown by the call (the first call of a size allocates; steady-state calls do not)
+  if (tiles > w.cap_tiles) {
+    uint8_t* p8 = static_cast<uint8_t*>(w.At); if (dev_alloc(h, &p8, tiles * 12288)) return 1; w.At = p8;
+    p8 = static_cast<uint8_t*>(w.Bt); if (dev_alloc(h, &p8, tiles * 12288)) return 1; w.Bt = p8;
+    w.cap_tiles = tiles;
+  }
+  if (n_graphs > w.cap_graphs) { if (dev_alloc(h, &w.tile_off, (int64_t)n_graphs + 1)) return 1; w.cap_graphs = n_graphs; }
+  if (n_pairs > w.cap_pairs) { if (dev_alloc(h, &w.unit_off, (int64_t)n_pairs + 1)) return 1; w.cap_pairs = n_pairs; }
+  int32_t* counts = counts_dev;
+  if (!counts) {
+    if ((int64_t)n_pairs * bins > w.cap_cnt) { if (dev_alloc(h, &w.cnt, (int64_t)n_pairs * bins)) return 1; w.cap_cnt = (int64_t)n_pairs * bins; }
+    counts = w.cnt;
+  }
+  cudaError_t e = sgnn_hist_pairs_tc_run(h->M.node_dim, bins, node_emb_dev, node_off_dev, n_graphs, tiles, g1_dev, g2_dev,
+                                         n_pairs, w, hist_dev, counts, h->sm_count, (cudaStream_t)stream);
+  if (e != cudaSuccess) return fail(h, std::string("sgnn_pair_histogram_tc: ") + cudaGetErrorString(e));
   return 0;
 }
 

@@ -1,6 +1,8 @@
 // Launchers of the tensor-core node-node histogram (sgnn_hist_tc.cuh).
 #include <cstdlib>
+#include <algorithm>
 #include "sgnn_hist_tc.cuh"
+#include "sgnn_hist_pairs_tc.cuh"
 
 bool sgnn_hist_tc_supported(int node_dim, int bins, int max_nodes_q, int max_nodes_db) {
   // node rows of at most 16 values: one K step; the 7 operand tiles (3 parts x 4 KB) + counter batches fill shared memory
@@ -132,4 +134,32 @@ extern "C" int sgnn_hist_all_pairs_static(int32_t node_dim, int32_t bins, const 
   if (e == cudaSuccess) e = sgnn_hist_tc_run(G, ws, node_off_db, sms, st);
   if (e != cudaSuccess) return ht_static_fail(err, err_cap, cudaGetErrorString(e));
   return 0;
+}
+
+// ---- listed pairs of large graphs (sgnn_hist_pairs_tc.cuh) -----------------------------------------------------------
+bool sgnn_hist_pairs_tc_supported(int node_dim, int bins) {
+  return node_dim >= 1 && node_dim <= 16 && bins >= 1 && bins <= HT_MAX_BINS;
+}
+
+// ws: At / Bt hold max_tiles operand tiles each, tile_off n_graphs + 1 ints, unit_off n_pairs + 1 ints.
+// counts [n_pairs][bins] (required), hist [n_pairs][bins] or NULL.
+cudaError_t sgnn_hist_pairs_tc_run(int node_dim, int bins, const float* nodes, const int32_t* node_off, int n_graphs,
+                                   int64_t max_tiles, const int32_t* g1, const int32_t* g2, int n_pairs,
+                                   const HistPairsWs& ws, float* hist, int32_t* counts, int sm_count, cudaStream_t st) {
+  if (!sgnn_hist_pairs_tc_supported(node_dim, bins) || !counts) return cudaErrorInvalidValue;
+  HpGeom G;
+  G.n_graphs = n_graphs; G.n_pairs = n_pairs; G.d = node_dim; G.bins = bins; G.lut_bias = 0x58000000u;
+  cudaError_t e = cudaMemsetAsync(counts, 0, (size_t)n_pairs * bins * sizeof(int32_t), st);
+  if (e != cudaSuccess) return e;
+  hp_scan_kernel<0><<<1, 1024, 0, st>>>(node_off, nullptr, nullptr, n_graphs, ws.tile_off);
+  hp_prep_kernel<<<(int)std::min<int64_t>(max_tiles, (int64_t)sm_count * 16), 128, 0, st>>>(
+      G, nodes, node_off, ws.tile_off, reinterpret_cast<__nv_bfloat16*>(ws.At), reinterpret_cast<__nv_bfloat16*>(ws.Bt));
+  hp_scan_kernel<1><<<1, 1024, 0, st>>>(g1, g2, ws.tile_off, n_pairs, ws.unit_off);
+  e = cudaFuncSetAttribute(hist_pairs_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HP_SMEM_BYTES);
+  if (e != cudaSuccess) return e;
+  hist_pairs_tc_kernel<<<sm_count, HP_THREADS, HP_SMEM_BYTES, st>>>(
+      G, reinterpret_cast<const __nv_bfloat16*>(ws.At), reinterpret_cast<const __nv_bfloat16*>(ws.Bt), ws.tile_off,
+      ws.unit_off, node_off, g1, g2, counts);
+  hp_finalize_kernel<<<(n_pairs + 255) / 256, 256, 0, st>>>(G, node_off, g1, g2, counts, hist);
+  return cudaGetLastError();
 }

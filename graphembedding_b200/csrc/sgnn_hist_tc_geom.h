@@ -63,3 +63,18 @@ cudaError_t sgnn_hist_tc_prep_db(const HistTcGeom& G, const float* nodes_db, con
                                  const HistTcWs& ws, cudaStream_t st);
 cudaError_t sgnn_hist_tc_run(const HistTcGeom& G, const HistTcWs& ws, const int32_t* node_off_db, int sm_count,
                              cudaStream_t st);
+
+// ---- listed pairs of large graphs (sgnn_hist_pairs_tc.cuh) ----
+struct HistPairsWs {
+  void* At = nullptr;            // plain operand tiles of every graph (12 KB each)
+  void* Bt = nullptr;            // the same rows scaled by -log2(e)
+  int32_t* tile_off = nullptr;   // [n_graphs + 1] first tile of every graph
+  int32_t* unit_off = nullptr;   // [n_pairs + 1] first (row tile, column tile) unit of every pair
+  int32_t* cnt = nullptr;        // [n_pairs][bins] when the caller wants only the normalised histogram
+  int64_t cap_tiles = 0, cap_graphs = 0, cap_pairs = 0, cap_cnt = 0;
+};
+inline int64_t hp_max_tiles(int64_t n_graphs, int64_t total_nodes) { return total_nodes / 128 + n_graphs; }
+bool sgnn_hist_pairs_tc_supported(int node_dim, int bins);
+cudaError_t sgnn_hist_pairs_tc_run(int node_dim, int bins, const float* nodes, const int32_t* node_off, int n_graphs,
+                                   int64_t max_tiles, const int32_t* g1, const int32_t* g2, int n_pairs,
+                                   const HistPairsWs& ws, float* hist, int32_t* counts, int sm_count, cudaStream_t st);

@@ -113,6 +113,16 @@ class SgnnEngine(object):
         n = int(g1.numel())
         hist = torch.empty((n, bins), dtype=torch.float32, device=self.device)
         counts = torch.empty((n, bins), dtype=torch.int32, device=self.device)
+        n_graphs, total_nodes = int(node_off.numel()) - 1, int(node_emb.shape[0])
+        # large graphs on a tensor-core engine: tiles of 128 node rows per graph (sgnn_hist_pairs_tc.cuh); small graphs
+        # would leave most of a tile empty and stay on the CUDA-core kernel
+        if (self.precision != 'fp32' and self.node_dim <= 16 and bins <= 16 and n_graphs > 0
+                and total_nodes >= 48 * n_graphs):
+            check(self.h, lib().sgnn_pair_histogram_tc(self.h, _ptr(node_emb), _ptr(node_off), n_graphs, total_nodes,
+                                                       _ptr(g1), _ptr(g2), n, int(bins), _ptr(hist), _ptr(counts),
+                                                       _stream_ptr(stream)))
+            self.launches += 6
+            return hist, counts
         check(self.h, lib().sgnn_pair_histogram(self.h, _ptr(node_emb), _ptr(node_off), _ptr(g1), _ptr(g2), n,
                                                 int(bins), _ptr(hist), _ptr(counts), _stream_ptr(stream)))
         self.launches += 1

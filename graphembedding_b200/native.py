@@ -73,6 +73,7 @@ SIGNATURES = {
     'sgnn_hist_all_pairs': (C.c_int, [_P, _P, _P, _I32, _I32, _P, _P, _I32, _I32, _P, _I32, _P]),
     'sgnn_hist_all_pairs_static': (C.c_int, [_I32, _I32, _P, _P, _I32, _I32, _P, _P, _I32, _I32, _P, _P, C.c_char_p, _I32]),
     'sgnn_pair_histogram': (C.c_int, [_P, _P, _P, _P, _P, _I32, _I32, _P, _P, _P]),
+    'sgnn_pair_histogram_tc': (C.c_int, [_P, _P, _P, _I32, _I64, _P, _P, _I32, _I32, _P, _P, _P]),
     'sgnn_score_pairs': (C.c_int, [_P, _P, _P, _P, _I32, _P, _P, _P]),
     'sgnn_forward_pairs': (C.c_int, [_P, _BP, _P, _P, _I32, _P, _P, _P, _P]),
     'sgnn_score_all_pairs': (C.c_int, [_P, _P, _I32, _P, _I32, _P, _I64, _P]),

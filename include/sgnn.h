@@ -164,6 +164,16 @@ int sgnn_embed_graphs_nodes(SgnnHandle h, const SgnnGraphBatch* batch_dev, float
 int sgnn_pair_histogram(SgnnHandle h, const float* node_emb_dev, const int32_t* node_off_dev, const int32_t* g1_dev,
                         const int32_t* g2_dev, int32_t n_pairs, int32_t bins, float* hist_dev, int32_t* counts_dev,
                         void* stream);
+/* sgnn_pair_histogram for LARGE graphs on the tensor cores (csrc/sgnn_hist_pairs_tc.cuh; Web-shaped workloads,
+ * BASELINE configs[4]): same layer, same outputs (integer counts equal outside the bin-edge band of the 6-product bf16
+ * split).  Every graph is cut into tiles of 128 node rows; a work unit is one (row tile, column tile) of one pair, so
+ * graphs far below 128 nodes waste most of a tile -- use it from ~50 nodes per graph up (the Python engine routes by
+ * that).  n_graphs / total_nodes describe node_off_dev / node_emb_dev.  Needs a tensor-core precision, node width
+ * <= 16, bins <= 16 (return code 4 otherwise: use sgnn_pair_histogram).  Build-defined like the layer itself (SURVEY
+ * a24); the first call of a size grows an internal workspace (24 KB per 128 node rows), later calls allocate nothing. */
+int sgnn_pair_histogram_tc(SgnnHandle h, const float* node_emb_dev, const int32_t* node_off_dev, int32_t n_graphs,
+                           int64_t total_nodes, const int32_t* g1_dev, const int32_t* g2_dev, int32_t n_pairs,
+                           int32_t bins, float* hist_dev, int32_t* counts_dev, void* stream);
 /* NTN/Dot + final_act on listed pairs (layers.py:249-252, 282-310; model_mse.py:39-45).
  * raw_dev / sim_dev may be NULL. */
 int sgnn_score_pairs(SgnnHandle h, const float* emb_dev, const int32_t* g1_dev, const int32_t* g2_dev,

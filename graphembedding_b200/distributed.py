@@ -129,7 +129,11 @@ def sharded_rank(engine, queries_dev, db_shard_dev, id_offset, k, dist=None, gro
 def data_parallel_step(engine, batch_dev, g1, g2, target_sim, global_batch, target_sum, target_sqsum, loss,
                        dist=None, group=None, grads=None, peer=None):
     """One DP optimiser step: local fwd+bwd, gradient all-reduce, identical Adam on every rank.
-    ``peer`` (a PeerTopk of this engine): the all-reduce is the peer-memory push fused into Adam."""
+    ``peer`` (a PeerTopk of this engine): the all-reduce is the peer-memory push fused into Adam.
+    The dropout masks are keyed on the pair's index in the GLOBAL batch (rank r owns pairs [r n, (r + 1) n)): with the
+    same seed on every rank, R = 1 and R = 8 draw the same masks for the same global batch."""
+    if dist is not None and dist.is_initialized():
+        engine.set_pair_offset(dist.get_rank(group) * int(g1.numel()))
     engine.train_step(batch_dev, g1, g2, target_sim, global_batch, target_sum, target_sqsum, loss=loss)
     if peer is not None:
         peer.adam_allreduce(1.0, loss)

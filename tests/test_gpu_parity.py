@@ -318,6 +318,48 @@ def test_dropout_forward_and_gradients_match_oracle_with_same_masks(cfg):
         assert np.max(np.abs(no_drop - ref_raw)) == 0
 
 
+@pytest.mark.parametrize('cfg', ['avg_ntn', 'head_drop'])
+def test_dropout_masks_are_keyed_on_the_global_pair_index(cfg):
+    """Data-parallel training (sgnn_set_pair_offset): two 'ranks' that own the halves of a batch, share seed and counter
+    and set offset = rank * pairs_per_rank draw the masks one GPU draws for the whole batch -- their gradients add up
+    to the single-GPU gradient and their predictions are its halves (the masks were keyed on the LOCAL index,
+    so every rank's pair p shared one mask)."""
+    rate = 0.3
+    eng, layers, flat, gs, enc, batch = _setup(cfg, 40, loss_mode='paired', dropout=rate)
+    B = 20
+    tgt = torch.as_tensor(np.random.default_rng(3).uniform(0.05, 1.0, size=B).astype(np.float32), device=eng.device)
+    dev = batch.to(eng.device)
+    g1 = torch.arange(0, B, dtype=torch.int32, device=eng.device)
+    g2 = torch.arange(B, 2 * B, dtype=torch.int32, device=eng.device)
+    eng.set_dropout_stream(99, 5)
+    eng.zero_grads()
+    eng.train_step(dev, g1, g2, tgt, global_batch=B)
+    whole = eng.device_buffers()[1].cpu().numpy().astype(np.float64)
+    eng.set_dropout_stream(99, 6)
+    _, raw_whole, _ = eng.eval_pairs(dev, g1, g2)
+    raw_whole = raw_whole.cpu().numpy()
+    h = B // 2
+    parts, raws = [], []
+    for r in range(2):
+        sl = slice(r * h, (r + 1) * h)
+        eng.set_pair_offset(r * h)
+        eng.set_dropout_stream(99, 5)
+        eng.zero_grads()
+        eng.train_step(dev, g1[sl].contiguous(), g2[sl].contiguous(), tgt[sl].contiguous(), global_batch=B)
+        parts.append(eng.device_buffers()[1].cpu().numpy().astype(np.float64))
+        eng.set_dropout_stream(99, 6)
+        _, raw_r, _ = eng.eval_pairs(dev, g1[sl].contiguous(), g2[sl].contiguous())
+        raws.append(raw_r.cpu().numpy())
+    eng.set_pair_offset(0)
+    assert np.array_equal(np.concatenate(raws), raw_whole)          # same masks: the same numbers, bit for bit
+    g = parts[0] + parts[1]
+    assert np.max(np.abs(g - whole)) <= 1e-5 * max(1e-12, np.max(np.abs(whole)))   # (fp32 atomics in another order)
+    # without the offset the second half draws the FIRST half's masks: different predictions
+    eng.set_dropout_stream(99, 6)
+    _, raw_local, _ = eng.eval_pairs(dev, g1[h:].contiguous(), g2[h:].contiguous())
+    assert not np.array_equal(raw_local.cpu().numpy(), raw_whole[h:])
+
+
 @pytest.mark.parametrize('cfg', ['avg_ntn', 'att3', 'dense_dot'])
 def test_web_shaped_large_graphs_match_oracle(cfg):
     """BASELINE configs[4]: Web-shaped graphs (100..500 nodes, E ~ 2N) go through the CTA-per-graph

@@ -223,9 +223,12 @@ struct TcEpi {
 #define TC_ESTAMP(slot) do { } while (0)
 #endif
 
-__device__ __forceinline__ float tc_warp_max(float x) {   // CREDUX.MAX.F32: one instruction, uniform result
+// CREDUX.MAX.F32: one instruction, uniform result.  .NaN: a NaN score (a diverged model) makes the slice maximum NaN, whose
+// rank key sorts above every number -- as it does in rank_key() / numpy's order -- so the hinted top-k never skips the
+// slice; the callers mark the holders with !(mine < w), which is mine == w for numbers and every lane for a NaN maximum
+__device__ __forceinline__ float tc_warp_max(float x) {
   float y;
-  asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(y) : "f"(x));
+  asm volatile("redux.sync.max.NaN.f32 %0, %1, 0xffffffff;" : "=f"(y) : "f"(x));
   return y;
 }
 
@@ -234,6 +237,7 @@ __device__ __forceinline__ unsigned long long tc_rank_key(float f, int idx) {
   f += 0.f;
   unsigned int u = __float_as_uint(f);
   u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+  if (f != f) u = 0xFFFFFFFFu;
   return ((unsigned long long)u << 32) | (unsigned int)idx;
 }
 
@@ -310,7 +314,7 @@ __device__ __forceinline__ void tc_epilogue_part(const TcEpi& E, uint32_t taddr,
       if (hint) {   // slice maximum and which lanes hold it (ties -> highest graph id, the reference's order)
         const float mine = sv + off_row;
         const float w = tc_warp_max(mine);
-        const unsigned who = __ballot_sync(0xffffffffu, mine == w);
+        const unsigned who = __ballot_sync(0xffffffffu, !(mine < w));
         if (lane == q) { keep = w; keep_mask = who; }
       }
     }
@@ -350,7 +354,7 @@ __device__ __forceinline__ void tc_epilogue_part(const TcEpi& E, uint32_t taddr,
             if (hint) {   // lane (qq mod 32) keeps query qq's slice maximum; flushed every 32 queries
               const float mine = g < E.n ? sv : -INFINITY;
               const float w = tc_warp_max(mine);
-              const int top = 31 - __clz(__ballot_sync(0xffffffffu, mine == w));
+              const int top = 31 - __clz(__ballot_sync(0xffffffffu, !(mine < w)));
               if (lane == (qq & 31)) { keep = w; keep_lane = top; }
               if ((qq & 31) == 31 || qq == nq - 1) {
                 const int qrow = (qq & ~31) + lane;

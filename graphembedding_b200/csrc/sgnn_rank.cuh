@@ -10,6 +10,7 @@ __device__ __forceinline__ unsigned long long rank_key(float f, int idx) {
   f += 0.f;  // -0.0 -> +0.0 (numpy compares them equal)
   unsigned int u = __float_as_uint(f);
   u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+  if (f != f) u = 0xFFFFFFFFu;   // NaN of either sign sorts above every number (np.argsort puts NaN last, the ranking reverses it)
   return ((unsigned long long)u << 32) | (unsigned int)idx;
 }
 
@@ -84,6 +85,7 @@ constexpr int TOPK_CAND = 1024;
 __device__ __forceinline__ unsigned int orderable_u32(float f) {
   f += 0.f;   // -0.0 -> +0.0 (numpy compares them equal)
   const unsigned int u = __float_as_uint(f);
+  if (f != f) return 0xFFFFFFFFu;   // NaN of either sign sorts above every number, as in numpy's order reversed
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 

@@ -173,3 +173,34 @@ def test_attention_pooling_on_device_matches_the_reference_class_fixture():
             eng.reserve(max_nodes=n)
         emb = eng.embed(pack_nx_graphs([nxg], enc).to(eng.device)).cpu().numpy()[0]
         assert close_fp32(emb, out, np.max(np.abs(out))), (rec['d'], n)
+
+
+def test_hinted_topk_agrees_with_the_plain_topk_when_scores_are_nan():
+    """A diverged model: one first-layer weight row is NaN, so every graph that carries that label embeds to NaN and
+    its similarities are NaN.  rank_key() / numpy's order put NaN first; the scorer's slice hints (redux.sync.max.NaN)
+    must say so too, or the hinted top-k of the fused ranking entry point skips those slices and returns other ids
+    than sgnn_topk on the same matrix."""
+    from graphembedding_b200.graphs import pack_nx_graphs
+    from graphembedding_b200.engine import SgnnEngine
+    from graphembedding_b200.layers_factory import parse_layers
+    # tanh everywhere: the device relu is fmaxf(x, 0), which turns NaN into 0
+    spec = ['GraphConvolution:output_dim=16,act=tanh,dropout=False,bias=True,sparse_inputs=True', 'Average',
+            'NTN:input_dim=16,feature_map_dim=10,inneract=tanh,dropout=False,bias=True']
+    eng = SgnnEngine(parse_layers(spec, 29), 29, precision='bf16x3', final_act='sim_kernel')
+    bad = O.init_params(O.parse_layer_specs(spec, 29), seed=21)
+    bad[5 * 16: 5 * 16 + 16] = np.nan            # W0 row of label 5 (GraphConvolution 29 -> 16)
+    eng.set_params(bad)
+    gs = corpus(16 + 4000, 2, 10, 31)
+    enc = encoder_for(gs)
+    q, db = pack_nx_graphs(gs[:16], enc), pack_nx_graphs(gs[16:], enc)
+    ids, vals, sim = _rank(eng, q, db, 10)
+    assert np.isnan(sim).any() and not np.isnan(sim).all()               # some graphs (whole rows for the queries among them)
+    ids2, vals2 = eng.topk(torch.as_tensor(sim, device=eng.device), 10)
+    torch.cuda.synchronize()
+    assert np.array_equal(ids, ids2.cpu().numpy())
+    assert np.array_equal(np.isnan(vals), np.isnan(vals2.cpu().numpy()))
+    rows = ~np.isnan(sim[:, :]).all(1)
+    nan_cols = np.isnan(sim)
+    for i in np.nonzero(rows)[0]:
+        if nan_cols[i].sum() >= 10:
+            assert np.isnan(vals[i]).all()        # NaN ranks first, like np.argsort(...)[::-1]

@@ -17,6 +17,7 @@
 // (it needs the receiver's flag of epoch e before it finishes epoch e), so the slot it overwrites at
 // epoch e + 2 has been merged by then.
 #pragma once
+#include <cstdio>
 #include "sgnn_rank.cuh"
 
 constexpr int PEER_MAX_WORLD = 16;
@@ -35,6 +36,29 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
   return v;
 }
 
+// Wait for a peer's flag to reach `epoch`.  Bounded: a rank that died or diverged (unequal call counts -- every rank must
+// make the same sequence of collective calls, include/sgnn.h) would otherwise hang its peers inside a kernel for ever.
+// After 30 s of waiting the kernel traps: the stream fails with a launch error that the next
+// synchronising call reports, instead of a silent hang.
+__device__ unsigned long long g_peer_spin_limit_ns = 30ull * 1000000000ull;
+__device__ __forceinline__ unsigned long long peer_now_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ void peer_wait_flag(const unsigned long long* f, unsigned long long epoch, unsigned ns) {
+  if (ld_acquire_sys(f) >= epoch) return;
+  const unsigned long long t0 = peer_now_ns(), limit = g_peer_spin_limit_ns;
+  while (ld_acquire_sys(f) < epoch) {
+    __nanosleep(ns);
+    if (peer_now_ns() - t0 > limit) {
+      printf("sgnn peer exchange: waited %llu s for a peer's flag (epoch %llu) -- a rank died or the ranks made different "
+             "sequences of collective calls\n", limit / 1000000000ull, epoch);
+      __trap();
+    }
+  }
+}
+
 // Stream-ordered barrier between the ranks, no host involvement: arrive at every peer, wait for every peer.
 // Epochs live in DEVICE memory (epoch_ctr[0] candidates, [1] gradients, [2] barrier) and are advanced by the
 // kernels themselves, so the launches carry no per-step host argument and can sit inside a CUDA graph.
@@ -46,7 +70,7 @@ __global__ void peer_barrier_kernel(int rank, int world, PeerPtrs P, unsigned lo
     __threadfence_system();
     st_release_sys(P.base[threadIdx.x] + 2 * PEER_MAX_WORLD + rank, epoch);
     const unsigned long long* f = P.base[rank] + 2 * PEER_MAX_WORLD + threadIdx.x;
-    while (ld_acquire_sys(f) < epoch) __nanosleep(32);
+    peer_wait_flag(f, epoch, 32);
   }
 }
 
@@ -87,7 +111,7 @@ peer_merge_kernel(const unsigned long long* __restrict__ mine, int m, int k, int
   const int parity = (int)(epoch & 1ull);
   if (threadIdx.x < world) {
     const unsigned long long* f = mine + parity * PEER_MAX_WORLD + threadIdx.x;
-    while (ld_acquire_sys(f) < epoch) __nanosleep(64);
+    peer_wait_flag(f, epoch, 64);
   }
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -154,7 +178,7 @@ adam_peer_kernel(int n, int n_pad, int world, const unsigned long long* __restri
   const int parity = (int)(epoch & 1ull);
   if (threadIdx.x < world) {
     const unsigned long long* f = mine + goff + parity * PEER_MAX_WORLD + threadIdx.x;
-    while (ld_acquire_sys(f) < epoch) __nanosleep(64);
+    peer_wait_flag(f, epoch, 64);
   }
   __syncthreads();
   const float* slots = reinterpret_cast<const float*>(mine + goff + 2 * PEER_MAX_WORLD) + (size_t)parity * world * n_pad;

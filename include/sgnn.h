@@ -299,7 +299,11 @@ int sgnn_rank_device(SgnnHandle h, const SgnnGraphBatch* q_dev, const SgnnGraphB
  *   2. all-gather the handles on the host (torch.distributed / MPI / files)
  *   3. every rank: sgnn_peer_connect(all_handles [world][64])
  *   4. per step, on EVERY rank, the same number of times: sgnn_topk_exchange(...)
- *   5. host barrier, then sgnn_peer_destroy (also done by sgnn_destroy). */
+ *   5. host barrier, then sgnn_peer_destroy (also done by sgnn_destroy).
+ * Every rank must make the SAME sequence of collective calls (sgnn_topk_exchange, sgnn_rank_sharded,
+ * sgnn_apply_adam_allreduce, sgnn_peer_barrier): the kernels wait for the peers' epoch flags on the device.  The wait
+ * is bounded: after 30 s without a peer's flag (a rank died, or the call counts differ) the kernel prints a message
+ * and traps, so the stream reports a launch failure at the next synchronising call instead of hanging. */
 #define SGNN_IPC_HANDLE_BYTES 64
 int sgnn_peer_create(SgnnHandle h, int32_t world, int32_t rank, int32_t m_cap, int32_t k_cap,
                      uint8_t* ipc_handle_out);

@@ -84,7 +84,7 @@ struct SgnnHandle_t {
   float *d_params = nullptr, *d_grads = nullptr, *d_m = nullptr, *d_v = nullptr, *d_loss = nullptr;
   int64_t adam_t = 0;
   uint64_t drop_seed = 0, drop_counter = 0;   // dropout stream: one counter value per train/eval call
-  int pair_offset = 0;                        // index of a call's first pair in the global batch (sgnn_set_pair_offset)
+  int pair_offset = 0, pair_stride = 1;       // local pair p = pair offset + p * stride of the global batch (sgnn_set_pair_offset)
   float *d_rowsA = nullptr, *d_rowsB = nullptr;   // large-graph path: node-row activations (global workspace)
   int64_t cap_rows = 0;                           // in node rows
   // histogram head: last node-level rows of the query / database side of the ranking entry points
@@ -1225,18 +1225,18 @@ static int launch_pairs(SgnnHandle h, bool bwd, const SgnnGraphBatch* b, const i
     if (bwd)
       train_team_kernel<true><<<tblocks, TEAM_CTA, smem, st>>>(h->M, to_dev(b), nmax, h->d_params, g1, g2, target_sim,
                                                                n_pairs, invB, s1, s2, h->d_grads, loss, raw, sim,
-                                                               dropping, dbase, h->pair_offset);
+                                                               dropping, dbase, h->pair_offset, h->pair_stride);
     else
       train_team_kernel<false><<<tblocks, TEAM_CTA, smem, st>>>(h->M, to_dev(b), nmax, h->d_params, g1, g2, target_sim,
                                                                 n_pairs, invB, s1, s2, h->d_grads, loss, raw, sim,
-                                                                dropping, dbase, h->pair_offset);
+                                                                dropping, dbase, h->pair_offset, h->pair_stride);
     CUDA_OK(h, cudaGetLastError());
     return 0;
   }
 #define SGNN_LAUNCH_PAIRS(NM, BW)                                                                        \
   train_pairs_kernel<NM, BW><<<blocks, wpb * 32, h->train_smem[v], st>>>(                                \
       h->M, to_dev(b), h->d_params, g1, g2, target_sim, n_pairs, invB, s1, s2, h->d_grads, loss, raw, sim,      \
-      dropping, dbase, h->pair_offset)
+      dropping, dbase, h->pair_offset, h->pair_stride)
   if (v == 0) { if (bwd) SGNN_LAUNCH_PAIRS(16, true); else SGNN_LAUNCH_PAIRS(16, false); }
   else { if (bwd) SGNN_LAUNCH_PAIRS(32, true); else SGNN_LAUNCH_PAIRS(32, false); }
 #undef SGNN_LAUNCH_PAIRS
@@ -1312,9 +1312,9 @@ int sgnn_set_dropout_stream(SgnnHandle h, uint64_t seed, uint64_t counter) {
   return 0;
 }
 
-int sgnn_set_pair_offset(SgnnHandle h, int32_t offset) {
-  if (!h || offset < 0) return 1;
-  h->pair_offset = offset;
+int sgnn_set_pair_offset(SgnnHandle h, int32_t offset, int32_t stride) {
+  if (!h || offset < 0 || stride < 1) return 1;
+  h->pair_offset = offset; h->pair_stride = stride;
   return 0;
 }
 

@@ -530,7 +530,7 @@ train_pairs_kernel(const __grid_constant__ ModelDev M, const BatchDev B,
                    const int32_t* __restrict__ g2, const float* __restrict__ target_sim, int n_pairs,
                    float inv_global_batch, float tsum, float tsqsum, float* __restrict__ grads,
                    float* __restrict__ loss, float* __restrict__ raw_out,
-                   float* __restrict__ sim_out, int dropping, uint32_t dbase, int p0) {
+                   float* __restrict__ sim_out, int dropping, uint32_t dbase, int p0, int pstride) {
   extern __shared__ __align__(16) float smem[];
   using Geo = SmallGeom<NMAX>;
   const int wfl = (M.n_params + 3) / 4 * 4;
@@ -565,9 +565,9 @@ train_pairs_kernel(const __grid_constant__ ModelDev M, const BatchDev B,
       saves[s] = my + TL.save + s * savep;
       nmask[s] = dropping ? my + TL.nmask + s * NMAX : nullptr;
       Gs[s] = load_graph<NMAX>(B, gid[s], my + TL.csr + s * Geo::CSR_WORDS, lane);
-      graph_fwd<NMAX>(M, Gs[s], s_w, my + TL.gbuf, acts[s], embs[s], saves[s], lane, dbase, 2 * (p + p0) + s, nmask[s]);
+      graph_fwd<NMAX>(M, Gs[s], s_w, my + TL.gbuf, acts[s], embs[s], saves[s], lane, dbase, 2 * (p0 + p * pstride) + s, nmask[s]);
       if (dropping && M.pair_drop) {   // dropout on the pair layer's inputs (layers.py:287-288)
-        const uint32_t key = drop_layer_key(dbase, 2 * (p + p0) + s, M.pair_ref);
+        const uint32_t key = drop_layer_key(dbase, 2 * (p0 + p * pstride) + s, M.pair_ref);
         for (int a = lane; a < M.emb_dim; a += 32) embs[s][a] *= drop_mask(key, 0, a, M.keep, M.inv_keep);
         __syncwarp();
       }
@@ -640,7 +640,7 @@ train_pairs_kernel(const __grid_constant__ ModelDev M, const BatchDev B,
     if (dropping && M.pair_drop) {   // gradient w.r.t. the un-dropped representations
 #pragma unroll
       for (int s = 0; s < 2; ++s) {
-        const uint32_t key = drop_layer_key(dbase, 2 * (p + p0) + s, M.pair_ref);
+        const uint32_t key = drop_layer_key(dbase, 2 * (p0 + p * pstride) + s, M.pair_ref);
         float* dx = s == 0 ? dx1 : dx2;
         for (int a = lane; a < M.emb_dim; a += 32) dx[a] *= drop_mask(key, 0, a, M.keep, M.inv_keep);
       }
@@ -654,7 +654,7 @@ train_pairs_kernel(const __grid_constant__ ModelDev M, const BatchDev B,
       const float* Hlast = acts[s] + M.L[M.n_node - 1].out_off;
       pool_bwd<NMAX>(M, Gs[s], s_w, s_aux + M.pool_wt_off, Hlast, M.act_ld, s == 0 ? dx1 : dx2,
                      saves[s], Gcur, M.ld, T, s_g, lane);
-      graph_bwd<NMAX>(M, Gs[s], s_w, s_aux, acts[s], Gcur, Gnxt, T, s_g, lane, dropping != 0, dbase, 2 * (p + p0) + s,
+      graph_bwd<NMAX>(M, Gs[s], s_w, s_aux, acts[s], Gcur, Gnxt, T, s_g, lane, dropping != 0, dbase, 2 * (p0 + p * pstride) + s,
                       nmask[s]);
     }
     __syncwarp();

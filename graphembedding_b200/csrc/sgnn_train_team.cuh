@@ -458,8 +458,8 @@ train_team_kernel(const __grid_constant__ ModelDev M, const BatchDev B, int nmax
                   const int32_t* __restrict__ g1, const int32_t* __restrict__ g2,
                   const float* __restrict__ target_sim, int n_pairs, float inv_global_batch, float tsum, float tsqsum,
                   float* __restrict__ grads, float* __restrict__ loss, float* __restrict__ raw_out,
-                  float* __restrict__ sim_out, int dropping, uint32_t dbase, int p0) {
-  // p0: index of this call's first pair in the GLOBAL batch (data-parallel ranks: the dropout masks are keyed on it)
+                  float* __restrict__ sim_out, int dropping, uint32_t dbase, int p0, int pstride) {
+  // local pair p is pair p0 + p * pstride of the GLOBAL batch (data-parallel ranks: the dropout masks are keyed on it)
   extern __shared__ __align__(16) float smem[];
   const TeamLayout TL = team_layout(M, nmax);
   const int wfl = round_up4(M.n_params);
@@ -497,7 +497,7 @@ train_team_kernel(const __grid_constant__ ModelDev M, const BatchDev B, int nmax
 
   for (int p = blockIdx.x; p < n_pairs; p += gridDim.x) {
     const int gid = arm_id == 0 ? g1[p] : g2[p];
-    const int slot = 2 * (p + p0) + arm_id;
+    const int slot = 2 * (p0 + p * pstride) + arm_id;
     const GraphS G = team_load_graph(B, gid, arm + TL.csr, TL, tm);
     team_graph_fwd(M, G, s_w, arm, TL, tm, dropping != 0, dbase, slot);
     __syncthreads();
@@ -540,7 +540,7 @@ train_team_kernel(const __grid_constant__ ModelDev M, const BatchDev B, int nmax
       }
       if (M.n_head > 0) {
         __syncthreads();
-        team_head_fwd(M, s_w, arms, TL, G.n, hf, hg, hcnt, scal, dropping != 0, dbase, p + p0);
+        team_head_fwd(M, s_w, arms, TL, G.n, hf, hg, hcnt, scal, dropping != 0, dbase, p0 + p * pstride);
       }
     }
     __syncthreads();
@@ -569,7 +569,7 @@ train_team_kernel(const __grid_constant__ ModelDev M, const BatchDev B, int nmax
       for (int a = tid; a < D; a += TEAM_CTA) { dx1[a] = graw * x2[a]; dx2[a] = graw * x1[a]; }
     } else {
       if (M.n_head > 0) {   // head backward: leaves dL/d(f_k) in hg[0..K)
-        team_head_bwd(M, s_w, s_g, hf, hg, graw, dropping != 0, dbase, p + p0);
+        team_head_bwd(M, s_w, s_g, hf, hg, graw, dropping != 0, dbase, p0 + p * pstride);
         __syncthreads();
       }
       for (int k = tid; k < K; k += TEAM_CTA) {

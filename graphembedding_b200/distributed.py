@@ -130,10 +130,10 @@ def data_parallel_step(engine, batch_dev, g1, g2, target_sim, global_batch, targ
                        dist=None, group=None, grads=None, peer=None):
     """One DP optimiser step: local fwd+bwd, gradient all-reduce, identical Adam on every rank.
     ``peer`` (a PeerTopk of this engine): the all-reduce is the peer-memory push fused into Adam.
-    The dropout masks are keyed on the pair's index in the GLOBAL batch (rank r owns pairs [r n, (r + 1) n)): with the
-    same seed on every rank, R = 1 and R = 8 draw the same masks for the same global batch."""
+    The dropout masks are keyed on the pair's index in the GLOBAL batch (rank r owns the pairs t = r (mod R),
+    ``pair_slice``): with the same seed on every rank, R = 1 and R = 8 draw the same masks for the same global batch."""
     if dist is not None and dist.is_initialized():
-        engine.set_pair_offset(dist.get_rank(group) * int(g1.numel()))
+        engine.set_pair_offset(dist.get_rank(group), dist.get_world_size(group))
     engine.train_step(batch_dev, g1, g2, target_sim, global_batch, target_sum, target_sqsum, loss=loss)
     if peer is not None:
         peer.adam_allreduce(1.0, loss)
@@ -143,3 +143,66 @@ def data_parallel_step(engine, batch_dev, g1, g2, target_sim, global_batch, targ
     allreduce_gradients(grads, dist, group)
     engine.apply_adam(1.0, loss)
     return loss
+
+
+def redistribute_rows(local_cols, dist=None, group=None):
+    """Database-sharded [m, n_r] column blocks -> this rank's full rows [m_r, n] (the ranking metrics
+    that need WHOLE rows -- Kendall tau, precision@k beyond the merged top-k, MRR -- run on m / R rows per rank).
+    Rank r receives rows ``shard_range(m, r, R)`` of every rank's block (one all-to-all; column order = rank order,
+    i.e. the global database order of a ``shard_range`` split).  Returns (rows [m_r, n], (row_lo, row_hi))."""
+    import torch
+    world = dist.get_world_size(group) if dist is not None and dist.is_initialized() else 1
+    m = int(local_cols.shape[0])
+    if world == 1:
+        return local_cols.contiguous(), (0, m)
+    rank = dist.get_rank(group)
+    n_local = torch.tensor([int(local_cols.shape[1])], dtype=torch.int64, device=local_cols.device)
+    widths = [torch.zeros_like(n_local) for _ in range(world)]
+    dist.all_gather(widths, n_local, group=group)
+    widths = [int(w.item()) for w in widths]
+    lo, hi = shard_range(m, rank, world)
+    send = [local_cols[slice(*shard_range(m, r, world))].contiguous() for r in range(world)]
+    recv = [torch.empty((hi - lo, widths[r]), dtype=local_cols.dtype, device=local_cols.device) for r in range(world)]
+    if dist.get_backend(group) == 'nccl':
+        dist.all_to_all(recv, send, group=group)
+    else:   # gloo has no all_to_all: point-to-point (the CPU tests)
+        ranks = list(range(world)) if group is None else dist.get_process_group_ranks(group)
+        reqs = []
+        for r in range(world):
+            if r == rank:
+                recv[r].copy_(send[r])
+            else:
+                reqs.append(dist.isend(send[r], dst=ranks[r], group=group))
+                reqs.append(dist.irecv(recv[r], src=ranks[r], group=group))
+        for q in reqs:
+            q.wait()
+    return torch.cat(recv, dim=1), (lo, hi)
+
+
+def sharded_full_row_metrics(engine, true_local, pred_local, ks, dist=None, group=None):
+    """precision@k (all k in ks) and Kendall tau-b of a database-sharded similarity matrix: the [m, n_r] blocks of the
+    true and the predicted similarities are redistributed to m / R full rows per rank (``redistribute_rows``), the
+    metric kernels (sgnn_precision_at_k, sgnn_kendall_tau) run on the local rows, and the per-row results are
+    combined: tau gathered in row order, precision averaged with the row counts as weights (metrics.py:14-35 takes
+    the mean over queries).  Returns (precision [len(ks)] float64 numpy, tau [m] float64 numpy), identical on every rank."""
+    import torch
+    world = dist.get_world_size(group) if dist is not None and dist.is_initialized() else 1
+    t_rows, (lo, hi) = redistribute_rows(true_local, dist, group)
+    p_rows, _ = redistribute_rows(pred_local, dist, group)
+    m = int(true_local.shape[0])
+    if hi > lo:
+        prec = engine.precision_at_ks(t_rows, p_rows, ks).to(torch.float64) * float(hi - lo)
+        tau, _ = engine.kendall_tau(t_rows, p_rows)
+    else:
+        prec = torch.zeros(len(ks), dtype=torch.float64, device=true_local.device)
+        tau = torch.zeros(0, dtype=torch.float64, device=true_local.device)
+    if world == 1:
+        return (prec / m).cpu().numpy(), tau.cpu().numpy()
+    dist.all_reduce(prec, group=group)
+    most = (m + world - 1) // world          # shard_range gives the first ranks one row more: pad to a common length
+    pad = torch.full((most,), float('nan'), dtype=torch.float64, device=tau.device)
+    pad[: hi - lo] = tau
+    parts = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(parts, pad, group=group)
+    taus = torch.cat([parts[r][: shard_range(m, r, world)[1] - shard_range(m, r, world)[0]] for r in range(world)])
+    return (prec / m).cpu().numpy(), taus.cpu().numpy()

@@ -349,9 +349,9 @@ class SgnnEngine(object):
         check(self.h, lib().sgnn_apply_adam_allreduce(self.h, float(grad_scale), _ptr(loss), _stream_ptr(stream)))
         self.launches += 2
 
-    def set_pair_offset(self, offset):
-        """Data-parallel training: index of this rank's first pair in the global batch (keys the dropout masks)."""
-        check(self.h, lib().sgnn_set_pair_offset(self.h, int(offset)))
+    def set_pair_offset(self, offset, stride=1):
+        """Data-parallel training: local pair p is pair offset + p * stride of the global batch (keys the dropout masks)."""
+        check(self.h, lib().sgnn_set_pair_offset(self.h, int(offset), int(stride)))
 
     def set_dropout_stream(self, seed, counter=0):
         """Seed / position of the dropout mask stream (one counter value per train/eval call)."""

@@ -263,10 +263,11 @@ int sgnn_zero_grads(SgnnHandle h, void* stream);
  * floor(keep_prob + u) == 1, scale 1/keep_prob, one draw per node for the sparse first layer) are the
  * reference's. */
 int sgnn_set_dropout_stream(SgnnHandle h, uint64_t seed, uint64_t counter);
-/* Data-parallel training: index of this rank's first pair in the GLOBAL batch (default 0).  The masks are keyed on
- * (seed, counter, global pair index, arm, layer, element), so R ranks that share seed and counter and set
- * offset = rank * pairs_per_rank draw exactly the masks one GPU draws for the concatenated batch. */
-int sgnn_set_pair_offset(SgnnHandle h, int32_t offset);
+/* Data-parallel training: local pair p of a call is pair offset + p * stride of the GLOBAL batch (default 0, 1).  The
+ * masks are keyed on (seed, counter, global pair index, arm, layer, element), so R ranks that share seed and counter
+ * draw exactly the masks one GPU draws for the whole batch -- offset = rank, stride = R for the interleaved split of
+ * distributed.pair_slice, offset = rank * pairs_per_rank, stride = 1 for contiguous blocks. */
+int sgnn_set_pair_offset(SgnnHandle h, int32_t offset, int32_t stride);
 
 /* ranking metrics on device (src/metrics.py:14-82, results.py:51-109; Kendall tau-b is
  * build-defined, pinned to scipy.stats.kendalltau).  true_sim/pred_sim are m x n. */

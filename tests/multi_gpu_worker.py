@@ -60,8 +60,19 @@ for cfg, kw in (('default', {}), ('simgnn', dict(final_act='sigmoid'))):
     torch.cuda.synchronize()
     assert torch.equal(ids_p, ids_f) and torch.equal(vals_p, vals_f), (cfg, rank, 'last')
     peer.close()
+    # ranking metrics that need WHOLE rows (Kendall tau, precision@k) under database sharding: all-to-all of the local
+    # [M, N] tiles into M / world full rows per rank, the metric kernels on those, results combined
+    full = torch.cat(tiles, 1).contiguous()
+    g = torch.Generator(device='cpu').manual_seed(5)
+    true_full = (full.cpu() + 0.05 * torch.randn(full.shape, generator=g)).to(dev).contiguous()   # same on every rank
+    prec, tau = DS.sharded_full_row_metrics(eng, true_full[:, rank * N:(rank + 1) * N].contiguous(), sim.contiguous(),
+                                            [1, 10, 100], dist)
+    ref_p = eng.precision_at_ks(true_full, full, [1, 10, 100]).cpu().numpy()
+    ref_t = eng.kendall_tau(true_full, full)[0].cpu().numpy()
+    assert np.array_equal(prec, ref_p) or np.allclose(prec, ref_p, rtol=0, atol=1e-12), (cfg, rank, prec, ref_p)
+    assert np.array_equal(tau, ref_t), (cfg, rank, 'tau')
     if rank == 0:
-        print('ranking ok:', cfg, 'world', world, 'epochs', EPOCHS, flush=True)
+        print('ranking ok:', cfg, 'world', world, 'epochs', EPOCHS, '+ sharded full-row metrics', flush=True)
 
 
 def train_run(cfg, use_peer, steps=12):

@@ -95,3 +95,52 @@ def test_merge_host_statement_is_reference_tie_order():
     ids = np.broadcast_to(np.arange(64, dtype=np.int32), sim.shape)
     got, _ = D.merge_topk_host(sim, ids, 9)
     assert np.array_equal(got, O.sort_id_mat_sim(sim)[:, :9])
+
+
+class _HostMetricEngine(object):
+    """Host statements of sgnn_precision_at_k / sgnn_kendall_tau (the oracle's precision, scipy's tau-b: what the
+    -m gpu tests hold the kernels to) behind the two engine methods sharded_full_row_metrics calls; the 2-GPU test
+    (tests/multi_gpu_worker.py) plugs the kernels in."""
+
+    def precision_at_ks(self, true_sim, pred_sim, ks):
+        t, p = true_sim.numpy(), pred_sim.numpy()
+        return torch.as_tensor(np.asarray(O.precision_at_ks(O.sort_id_mat_sim(t), t, O.sort_id_mat_sim(p), p, list(ks)), np.float64))
+
+    def kendall_tau(self, true_sim, pred_sim):
+        from scipy.stats import kendalltau
+        tau = [kendalltau(a, b).statistic for a, b in zip(true_sim.numpy(), pred_sim.numpy())]
+        return torch.as_tensor(np.asarray(tau, np.float64)), None
+
+
+def _metric_worker(rank, world, port, out):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        m, n = 9, 203                                   # rows and columns that do not divide by the world size
+        rng = np.random.default_rng(23)
+        true = rng.random((m, n)).astype(np.float32)
+        pred = (true + 0.3 * rng.standard_normal((m, n))).astype(np.float32)
+        lo, hi = D.shard_range(n, rank, world)
+        rows, (rlo, rhi) = D.redistribute_rows(torch.as_tensor(pred[:, lo:hi].copy()), dist)
+        ok_rows = bool(np.array_equal(rows.numpy(), pred[rlo:rhi])) and (rlo, rhi) == D.shard_range(m, rank, world)
+        eng = _HostMetricEngine()
+        prec, tau = D.sharded_full_row_metrics(eng, torch.as_tensor(true[:, lo:hi].copy()), torch.as_tensor(pred[:, lo:hi].copy()),
+                                               [1, 10, 50], dist)
+        ref_p = eng.precision_at_ks(torch.as_tensor(true), torch.as_tensor(pred), [1, 10, 50]).numpy()
+        ref_t, _ = eng.kendall_tau(torch.as_tensor(true), torch.as_tensor(pred))
+        out[rank] = (ok_rows, bool(np.allclose(prec, ref_p, rtol=0, atol=1e-12)),
+                     bool(np.allclose(tau, ref_t.numpy(), rtol=0, atol=1e-12)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_row_redistribution_and_full_row_metrics():
+    """Kendall tau / precision@k of a database-sharded matrix = the single-process values after the
+    all-to-all that gives every rank m / R whole rows."""
+    world = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_metric_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    for r in range(world):
+        assert out[r] == (True, True, True), (r, out[r])

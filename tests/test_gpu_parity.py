@@ -342,7 +342,7 @@ def test_dropout_masks_are_keyed_on_the_global_pair_index(cfg):
     parts, raws = [], []
     for r in range(2):
         sl = slice(r * h, (r + 1) * h)
-        eng.set_pair_offset(r * h)
+        eng.set_pair_offset(r * h, 1)
         eng.set_dropout_stream(99, 5)
         eng.zero_grads()
         eng.train_step(dev, g1[sl].contiguous(), g2[sl].contiguous(), tgt[sl].contiguous(), global_batch=B)
@@ -350,7 +350,14 @@ def test_dropout_masks_are_keyed_on_the_global_pair_index(cfg):
         eng.set_dropout_stream(99, 6)
         _, raw_r, _ = eng.eval_pairs(dev, g1[sl].contiguous(), g2[sl].contiguous())
         raws.append(raw_r.cpu().numpy())
-    eng.set_pair_offset(0)
+    # the interleaved split of distributed.pair_slice: rank r owns the pairs t = r (mod 2)
+    for r in range(2):
+        sl = slice(r, None, 2)
+        eng.set_pair_offset(r, 2)
+        eng.set_dropout_stream(99, 6)
+        _, raw_r, _ = eng.eval_pairs(dev, g1[sl].contiguous(), g2[sl].contiguous())
+        assert np.array_equal(raw_r.cpu().numpy(), raw_whole[sl])
+    eng.set_pair_offset(0, 1)
     assert np.array_equal(np.concatenate(raws), raw_whole)          # same masks: the same numbers, bit for bit
     g = parts[0] + parts[1]
     assert np.max(np.abs(g - whole)) <= 1e-5 * max(1e-12, np.max(np.abs(whole)))   # (fp32 atomics in another order)

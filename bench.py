@@ -869,6 +869,19 @@ def run_train(name, torch, dist, dev, rank, world, local, args, barrier, max_ove
     res = {'allreduce': allreduce, 'model': desc, 'value': TRAIN_BATCH * world / (ms * 1e-3), 'unit': 'pairs/s',
            'ms_per_step': ms, 'steps': n, 'gpu_launches': launches, 'final_loss': final_loss, 'dtype': 'f32',
            'roofline': roof(batches[0][0], batches[0][1], ms)}
+    if world == 1:
+        # the same optimiser steps as ONE CUDA graph of len(feeds) steps (engine.capture_train_steps: Adam's step count on
+        # the device): the eager 128-pair step above is bound by the launch path (three launches per step)
+        gfeeds = [(f[0], f[1], f[2], gb, f[3], f[4]) for f in feeds]
+        graph = eng.capture_train_steps(bd, gfeeds, loss)
+        reps = max(2, n // len(gfeeds))
+        gms = timed(lambda i: graph.replay(), reps) / len(gfeeds)
+        eng.adam_device_step(False)
+        res['eager_ms_per_step'] = ms
+        res['ms_per_step'] = gms
+        res['value'] = TRAIN_BATCH / (gms * 1e-3)
+        res['graph'] = '{} optimiser steps per CUDA-graph launch'.format(len(gfeeds))
+        res['roofline'] = roof(batches[0][0], batches[0][1], gms)
     # ---- throughput point: BIG pairs per step (random pairs of the same graphs, random targets), no exchange ----
     BIG = 16384
     rng = np.random.default_rng(5 + rank)

@@ -83,6 +83,9 @@ struct SgnnHandle_t {
   std::vector<SgnnParamInfo> table;
   float *d_params = nullptr, *d_grads = nullptr, *d_m = nullptr, *d_v = nullptr, *d_loss = nullptr;
   int64_t adam_t = 0;
+  long long* d_adam_t = nullptr;              // sgnn_adam_device_step: the step count (and the step size behind it) on the device
+  float* d_adam_lr = nullptr;
+  bool adam_on_device = false;
   uint64_t drop_seed = 0, drop_counter = 0;   // dropout stream: one counter value per train/eval call
   int pair_offset = 0, pair_stride = 1;       // local pair p = pair offset + p * stride of the global batch (sgnn_set_pair_offset)
   float *d_rowsA = nullptr, *d_rowsB = nullptr;   // large-graph path: node-row activations (global workspace)
@@ -774,6 +777,7 @@ int sgnn_destroy(SgnnHandle h) {
   cudaFree(h->d_head_staging);
   cudaFree(h->ht.At); cudaFree(h->ht.Bt); cudaFree(h->ht.qmeta); cudaFree(h->ht.ameta); cudaFree(h->ht.status);
   cudaFree(h->ht.cnt);
+  cudaFree(h->d_adam_t);
   cudaFree(h->hp.At); cudaFree(h->hp.Bt); cudaFree(h->hp.tile_off); cudaFree(h->hp.unit_off); cudaFree(h->hp.cnt);
   HostWs& w = h->ws;
   for (int s = 0; s < 2; ++s) {
@@ -814,6 +818,7 @@ int sgnn_set_params(SgnnHandle h, const float* host_params) {
   CUDA_OK(h, cudaMemset(h->d_v, 0, bytes));
   CUDA_OK(h, cudaMemset(h->d_grads, 0, bytes));
   h->adam_t = 0;
+  if (h->d_adam_t) CUDA_OK(h, cudaMemset(h->d_adam_t, 0, sizeof(long long)));
   return 0;
 }
 
@@ -1261,8 +1266,38 @@ int sgnn_eval_pairs(SgnnHandle h, const SgnnGraphBatch* b, const int32_t* g1, co
                       target_sim ? loss_dev : nullptr, raw_dev, sim_dev, stream);
 }
 
+int sgnn_adam_device_step(SgnnHandle h, int32_t enable) {
+  if (!h) return 1;
+  if (enable && !h->d_adam_t) {
+    CUDA_OK(h, cudaMalloc(reinterpret_cast<void**>(&h->d_adam_t), 16));
+    h->d_adam_lr = reinterpret_cast<float*>(h->d_adam_t + 1);
+  }
+  if (enable && !h->adam_on_device) {
+    const long long t = h->adam_t;
+    CUDA_OK(h, cudaMemcpy(h->d_adam_t, &t, sizeof(t), cudaMemcpyHostToDevice));
+  } else if (!enable && h->adam_on_device) {
+    long long t = 0;
+    CUDA_OK(h, cudaMemcpy(&t, h->d_adam_t, sizeof(t), cudaMemcpyDeviceToHost));   // (synchronises)
+    h->adam_t = t;
+  }
+  h->adam_on_device = enable != 0;
+  return 0;
+}
+
 int sgnn_apply_adam(SgnnHandle h, float grad_scale, float* loss_dev, void* stream) {
   if (!h) return 1;
+  if (h->adam_on_device) {   // step count and step size on the device: nothing in the launch changes from step to step
+    const SgnnConfig& c = h->cfg;
+    const int n = h->M.n_params;
+    const int blocks = std::min((n + 255) / 256, h->sm_count);
+    adam_lr_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(h->d_adam_t, h->d_adam_lr, (double)c.learning_rate, (double)c.beta1,
+                                                      (double)c.beta2);
+    adam_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(n, h->d_params, h->d_grads, h->d_m, h->d_v, grad_scale,
+                                                         c.weight_decay, 0.f, c.beta1, c.beta2, c.epsilon, loss_dev,
+                                                         h->d_adam_lr);
+    CUDA_OK(h, cudaGetLastError());
+    return 0;
+  }
   h->adam_t += 1;
   const SgnnConfig& c = h->cfg;
   const double t = (double)h->adam_t;

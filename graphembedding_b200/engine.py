@@ -349,6 +349,28 @@ class SgnnEngine(object):
         check(self.h, lib().sgnn_apply_adam_allreduce(self.h, float(grad_scale), _ptr(loss), _stream_ptr(stream)))
         self.launches += 2
 
+    def adam_device_step(self, enable=True):
+        """Adam's step count on the device (sgnn_adam_device_step): train_step + apply_adam become capturable."""
+        check(self.h, lib().sgnn_adam_device_step(self.h, 1 if enable else 0))
+
+    def capture_train_steps(self, batch, feeds, loss, grad_scale=1.0):
+        """K optimiser steps as ONE CUDA graph: for every (g1, g2, target_sim, global_batch, target_sum, target_sqsum)
+        in ``feeds`` (device tensors that stay alive): zero ``loss``, sgnn_train_step, sgnn_apply_adam.  Returns the
+        torch.cuda.CUDAGraph; every ``replay()`` runs the K steps (the Adam step count advances on the device)."""
+        import torch
+        self.adam_device_step(True)
+        g = torch.cuda.CUDAGraph()
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(g, stream=side):
+                for g1, g2, t, gb, s1, s2 in feeds:
+                    loss.zero_()
+                    self.train_step(batch, g1, g2, t, gb, s1, s2, loss=loss)
+                    self.apply_adam(grad_scale, loss)
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        return g
+
     def set_pair_offset(self, offset, stride=1):
         """Data-parallel training: local pair p is pair offset + p * stride of the global batch (keys the dropout masks)."""
         check(self.h, lib().sgnn_set_pair_offset(self.h, int(offset), int(stride)))

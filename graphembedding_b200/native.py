@@ -84,6 +84,7 @@ SIGNATURES = {
     'sgnn_train_step': (C.c_int, [_P, _BP, _P, _P, _P, _I32, _I32, _D, _D, _P, _P]),
     'sgnn_eval_pairs': (C.c_int, [_P, _BP, _P, _P, _P, _I32, _I32, _D, _D, _P, _P, _P, _P]),
     'sgnn_apply_adam': (C.c_int, [_P, _F, _P, _P]),
+    'sgnn_adam_device_step': (C.c_int, [_P, _I32]),
     'sgnn_zero_grads': (C.c_int, [_P, _P]),
     'sgnn_set_dropout_stream': (C.c_int, [_P, C.c_uint64, C.c_uint64]),
     'sgnn_set_pair_offset': (C.c_int, [_P, _I32, _I32]),

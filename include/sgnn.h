@@ -256,6 +256,12 @@ int sgnn_eval_pairs(SgnnHandle h, const SgnnGraphBatch* batch_dev, const int32_t
  * then zeroes the grad buffer.  grad_scale multiplies the summed gradient first.
  * loss_dev[1] = weight-decay loss term if loss_dev != NULL. */
 int sgnn_apply_adam(SgnnHandle h, float grad_scale, float* loss_dev, void* stream);
+/* enable = 1: Adam's step count t and the step size lr sqrt(1 - b2^t) / (1 - b1^t) live on the DEVICE (a one-thread
+ * kernel in front of the update advances them, same double arithmetic as the host form), so that a sequence of
+ * sgnn_train_step + sgnn_apply_adam calls can be captured once into a CUDA graph and replayed: one launch for K optimiser
+ * steps instead of 2 K (the 128-pair step of configs[2] is otherwise bound by launch overhead).  enable = 0 copies the
+ * count back to the host (synchronises).  The parameters after N steps are bit-identical in both modes. */
+int sgnn_adam_device_step(SgnnHandle h, int32_t enable);
 int sgnn_zero_grads(SgnnHandle h, void* stream);
 /* Dropout masks (layers.py:45-49, 98-100, 196, 287-288, 332-338) come from a counter-based hash of
  * (seed, counter, pair slot, layer, element): each sgnn_train_step / sgnn_eval_pairs call consumes one

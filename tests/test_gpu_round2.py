@@ -204,3 +204,59 @@ def test_hinted_topk_agrees_with_the_plain_topk_when_scores_are_nan():
     for i in np.nonzero(rows)[0]:
         if nan_cols[i].sum() >= 10:
             assert np.isnan(vals[i]).all()        # NaN ranks first, like np.argsort(...)[::-1]
+
+
+@pytest.mark.parametrize('cfg', ['avg_ntn', 'simgnn'])
+def test_k_optimiser_steps_as_one_cuda_graph_equal_the_eager_steps(cfg):
+    """engine.capture_train_steps (sgnn_adam_device_step): K x (train_step + apply_adam) captured once and replayed --
+    Adam's step count and step size advance on the device -- leaves the parameters of the eager loop (TF-1 Adam,
+    models.py:28-29, 67-74).  Gradients are accumulated with unordered fp32 atomics, so two runs of the SAME path differ
+    at rounding level too: the gate is the spread of two eager runs (+ 1e-7), not bit equality."""
+    from graphembedding_b200.engine import SgnnEngine
+    from graphembedding_b200.graphs import pack_nx_graphs
+    from graphembedding_b200.layers_factory import parse_layers
+    gs = corpus(64, 2, 10, 41)
+    batch = pack_nx_graphs(gs, encoder_for(gs))
+    kw = dict(final_act='sigmoid') if cfg == 'simgnn' else {}
+    rng = np.random.default_rng(2)
+    K, B, reps = 5, 32, 3
+
+    def run(mode):
+        eng = SgnnEngine(parse_layers(CONFIGS[cfg], 29), 29, loss_mode='paired', **kw)
+        eng.init_params(7)
+        dev = eng.device
+        bd = batch.to(dev)
+        r = np.random.default_rng(2)
+        feeds = []
+        for _ in range(K):
+            p = r.integers(0, 64, size=(B, 2)).astype(np.int32)
+            t = r.uniform(0.1, 1.0, B).astype(np.float32)
+            feeds.append((torch.as_tensor(p[:, 0].copy(), device=dev), torch.as_tensor(p[:, 1].copy(), device=dev),
+                          torch.as_tensor(t, device=dev), B, float(t.astype(np.float64).sum()),
+                          float((t.astype(np.float64) ** 2).sum())))
+        loss = torch.zeros(4, device=dev)
+        if mode == 'graph':
+            g = eng.capture_train_steps(bd, feeds, loss)
+            for _ in range(reps):
+                g.replay()
+            torch.cuda.synchronize()
+            eng.adam_device_step(False)
+        else:
+            for _ in range(reps):
+                for g1, g2, t, gb, s1, s2 in feeds:
+                    loss.zero_()
+                    eng.train_step(bd, g1, g2, t, gb, s1, s2, loss=loss)
+                    eng.apply_adam(1.0, loss)
+            torch.cuda.synchronize()
+        # one more EAGER step in both modes: the host step count must have followed the device's
+        g1, g2, t, gb, s1, s2 = feeds[0]
+        eng.train_step(bd, g1, g2, t, gb, s1, s2, loss=loss)
+        eng.apply_adam(1.0, loss)
+        return eng.get_params(), loss.cpu().numpy()
+
+    pe, le = run('eager')
+    pe2, _ = run('eager')
+    pg, lg = run('graph')
+    spread = float(np.max(np.abs(pe - pe2)))
+    assert float(np.max(np.abs(pg - pe))) <= 4 * spread + 1e-7
+    assert float(np.max(np.abs(lg - le))) <= 1e-5 * max(1.0, float(np.max(np.abs(le))))

@@ -317,8 +317,10 @@ int plan_launches(SgnnHandle h) {
   if (h->use_team) {
     // opt in to all of the SM's shared memory: the per-arm buffers grow with the batch's largest graph, and
     // graphs well beyond 32 nodes still fit for the usual layer widths (launch_pairs checks per call)
-    if (set_smem(h, train_team_kernel<true>, (size_t)h->smem_optin)) return 1;
-    if (set_smem(h, train_team_kernel<false>, (size_t)h->smem_optin)) return 1;
+    if (set_smem(h, train_team_kernel<true, 1>, (size_t)h->smem_optin)) return 1;
+    if (set_smem(h, train_team_kernel<false, 1>, (size_t)h->smem_optin)) return 1;
+    if (set_smem(h, train_team_kernel<true, 2>, (size_t)h->smem_optin)) return 1;
+    if (set_smem(h, train_team_kernel<false, 2>, (size_t)h->smem_optin)) return 1;
   }
   return 0;
 }
@@ -1225,16 +1227,16 @@ static int launch_pairs(SgnnHandle h, bool bwd, const SgnnGraphBatch* b, const i
   if (h->use_team) {
     const int nmax = std::max(4, (int)b->max_nodes);
     const size_t smem = team_smem_floats(h->M, nmax) * sizeof(float);
-    const int per_sm = std::max<size_t>(1, std::min<size_t>(TEAM_CTA <= 256 ? 2 : 1, (size_t)h->smem_optin / (smem + 1024)));
-    const int tblocks = std::min(n_pairs, h->sm_count * per_sm);
-    if (bwd)
-      train_team_kernel<true><<<tblocks, TEAM_CTA, smem, st>>>(h->M, to_dev(b), nmax, h->d_params, g1, g2, target_sim,
-                                                               n_pairs, invB, s1, s2, h->d_grads, loss, raw, sim,
-                                                               dropping, dbase, h->pair_offset, h->pair_stride);
-    else
-      train_team_kernel<false><<<tblocks, TEAM_CTA, smem, st>>>(h->M, to_dev(b), nmax, h->d_params, g1, g2, target_sim,
-                                                                n_pairs, invB, s1, s2, h->d_grads, loss, raw, sim,
-                                                                dropping, dbase, h->pair_offset, h->pair_stride);
+    // more pairs than SMs: two CTAs per SM (the 64-register variant) when shared memory holds them
+    const bool two = n_pairs > h->sm_count && 2 * (smem + 1024) <= (size_t)h->smem_optin + 1024;   // (228 KB per SM, 1 KB reserved per CTA)
+    const int tblocks = std::min(n_pairs, h->sm_count * (two ? 2 : 1));
+#define SGNN_LAUNCH_TEAM(BW, MB)                                                                                     \
+  train_team_kernel<BW, MB><<<tblocks, TEAM_CTA, smem, st>>>(h->M, to_dev(b), nmax, h->d_params, g1, g2, target_sim, \
+                                                             n_pairs, invB, s1, s2, h->d_grads, loss, raw, sim,      \
+                                                             dropping, dbase, h->pair_offset, h->pair_stride)
+    if (bwd) { if (two) SGNN_LAUNCH_TEAM(true, 2); else SGNN_LAUNCH_TEAM(true, 1); }
+    else { if (two) SGNN_LAUNCH_TEAM(false, 2); else SGNN_LAUNCH_TEAM(false, 1); }
+#undef SGNN_LAUNCH_TEAM
     CUDA_OK(h, cudaGetLastError());
     return 0;
   }

@@ -452,8 +452,11 @@ __device__ __forceinline__ void team_head_bwd(const ModelDev& M, const float* W,
   }
 }
 
-template <bool BWD>
-__global__ void __launch_bounds__(TEAM_CTA, TEAM_CTA <= 256 ? 2 : 1)
+// MINB: CTAs per SM the register budget is cut for -- 1 (128 registers) for batches of at most one pair per SM, where
+// only the latency of a pair counts; 2 (64 registers, no spills) for larger batches, where two pairs per SM overlap
+// their barrier-separated phases
+template <bool BWD, int MINB>
+__global__ void __launch_bounds__(TEAM_CTA, MINB)
 train_team_kernel(const __grid_constant__ ModelDev M, const BatchDev B, int nmax, const float* __restrict__ params,
                   const int32_t* __restrict__ g1, const int32_t* __restrict__ g2,
                   const float* __restrict__ target_sim, int n_pairs, float inv_global_batch, float tsum, float tsqsum,

@@ -83,6 +83,7 @@ struct SgnnHandle_t {
   std::vector<SgnnParamInfo> table;
   float *d_params = nullptr, *d_grads = nullptr, *d_m = nullptr, *d_v = nullptr, *d_loss = nullptr;
   int64_t adam_t = 0;
+  bool embed_tc = false;                      // sgnn_set_embed_tc
   long long* d_adam_t = nullptr;              // sgnn_adam_device_step: the step count (and the step size behind it) on the device
   float* d_adam_lr = nullptr;
   bool adam_on_device = false;
@@ -638,6 +639,16 @@ int padding_guard(SgnnHandle h, const SgnnGraphBatch* b) {
 int embed_nodes(SgnnHandle h, const SgnnGraphBatch* b, float* emb_dev, float* node_out, cudaStream_t st) {
   if (b->n_graphs == 0) return 0;
   if (padding_guard(h, b)) return 1;
+  // opt-in (sgnn_set_embed_tc / SGNN_EMBED_TC=1): the dense GCN layers as tcgen05 GEMMs over tiles of packed graphs.
+  // Parity-green, but for graphs of ~10 nodes SLOWER than the CUDA-core tile kernel, hence not the default.
+  static const bool etc_env = [] { const char* e = getenv("SGNN_EMBED_TC"); return e && e[0] == '1'; }();
+  if ((etc_env || h->embed_tc) && h->cfg.precision != SGNN_PREC_FP32 && sgnn_embed_tc_supported(h->M, b->max_nodes)) {
+    const cudaError_t e = sgnn_launch_embed_tc(h->M, to_dev(b), b->max_nodes, b->total_nodes, h->d_params, emb_dev, node_out,
+                                               h->ht.status, h->sm_count, h->smem_optin, st);
+    if (e == cudaSuccess) return 0;
+    if (e != cudaErrorInvalidValue) return fail(h, std::string("embedding (tensor-core kernel): ") + cudaGetErrorString(e));
+    cudaGetLastError();
+  }
   if (b->max_nodes <= 32) {
     const cudaError_t e = sgnn_launch_embed_tile(h->M, to_dev(b), b->max_nodes, h->d_params, emb_dev, node_out, nullptr,
                                                  0, 0, nullptr, 0, 0, 0, 0, h->sm_count, h->smem_optin, st);
@@ -1346,6 +1357,13 @@ int sgnn_apply_adam_allreduce(SgnnHandle h, float grad_scale, float* loss_dev, v
 int sgnn_set_dropout_stream(SgnnHandle h, uint64_t seed, uint64_t counter) {
   if (!h) return 1;
   h->drop_seed = seed; h->drop_counter = counter;
+  return 0;
+}
+
+int sgnn_set_embed_tc(SgnnHandle h, int32_t enable) {
+  if (!h) return 1;
+  if (enable && h->cfg.precision == SGNN_PREC_FP32) return fail(h, "sgnn_set_embed_tc: the engine was created with the fp32 (CUDA-core) precision");
+  h->embed_tc = enable != 0;
   return 0;
 }
 

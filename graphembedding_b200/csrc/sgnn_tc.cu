@@ -2,6 +2,7 @@
 #include <cstdlib>
 #include "sgnn_allpairs_tc.cuh"
 #include "sgnn_allpairs_tc_head.cuh"
+#include "sgnn_embed_tc.cuh"
 
 namespace {
 
@@ -119,4 +120,20 @@ cudaError_t sgnn_tc_score_head(const ModelDev& M, const TcGeom& G, int grid, siz
   if (cnt_tiled) return slot >= 0 ? launch_it(allpairs_tc_head_kernel<true, true, true>) : launch_it(allpairs_tc_head_kernel<true, false, true>);
   if (slot >= 0) return hist ? launch_it(allpairs_tc_head_kernel<true, true, false>) : launch_it(allpairs_tc_head_kernel<false, true, false>);
   return hist ? launch_it(allpairs_tc_head_kernel<true, false, false>) : launch_it(allpairs_tc_head_kernel<false, false, false>);
+}
+
+// ---- graph embedding with the dense GCN layers on the tensor cores (sgnn_embed_tc.cuh) ----
+bool sgnn_embed_tc_supported(const ModelDev& M, int max_nodes) { return etc_supported(M, max_nodes); }
+
+cudaError_t sgnn_launch_embed_tc(const ModelDev& M, const BatchDev& B, int max_nodes, int64_t total_rows, const float* params,
+                                 float* emb, float* node_out, int32_t* status, int sm_count, int smem_optin, cudaStream_t st) {
+  if (!etc_supported(M, max_nodes) || total_rows <= 0) return cudaErrorInvalidValue;
+  const EtcPlan P = etc_plan(M, max_nodes, total_rows);
+  if (P.total_bytes > smem_optin) return cudaErrorInvalidValue;
+  cudaError_t e = cudaFuncSetAttribute(embed_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P.total_bytes);
+  if (e != cudaSuccess) return e;
+  const int per_sm = 2 * (P.total_bytes + 1024) <= smem_optin + 1024 ? 2 : 1;
+  const int blocks = std::min(P.n_tiles, sm_count * per_sm);
+  embed_tc_kernel<<<blocks, ETC_THREADS, P.total_bytes, st>>>(M, P, B, (int)total_rows, params, emb, node_out, status);
+  return cudaGetLastError();
 }

@@ -79,3 +79,10 @@ cudaError_t sgnn_tc_score_head(const ModelDev& M, const TcGeom& G, int grid, siz
                                bool cnt_tiled, const int32_t* node_off_q, const int32_t* node_off_db, cudaStream_t st);
 // cnt_tiled: cnt holds the fp16 operand tiles of ht_cnt_tiled_bytes (HistTcGeom::cnt_m_pad), not [m][n][16] bytes
 inline int tc_n_slices(int n) { return ((n + 127) / 128) * 4; }
+
+// graph embedding with the dense GCN layers as tcgen05 GEMMs over tiles of packed graphs (sgnn_embed_tc.cuh);
+// cudaErrorInvalidValue: shape not served (the caller keeps embed_tile_kernel / embed_large_kernel)
+struct BatchDev;
+bool sgnn_embed_tc_supported(const ModelDev& M, int max_nodes);
+cudaError_t sgnn_launch_embed_tc(const ModelDev& M, const BatchDev& B, int max_nodes, int64_t total_rows, const float* params,
+                                 float* emb, float* node_out, int32_t* status, int sm_count, int smem_optin, cudaStream_t st);

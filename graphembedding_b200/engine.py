@@ -349,6 +349,10 @@ class SgnnEngine(object):
         check(self.h, lib().sgnn_apply_adam_allreduce(self.h, float(grad_scale), _ptr(loss), _stream_ptr(stream)))
         self.launches += 2
 
+    def set_embed_tc(self, enable=True):
+        """Opt in to the tcgen05 embedding kernel (sgnn_set_embed_tc) for embed_nodes / the head models' ranking paths."""
+        check(self.h, lib().sgnn_set_embed_tc(self.h, 1 if enable else 0))
+
     def adam_device_step(self, enable=True):
         """Adam's step count on the device (sgnn_adam_device_step): train_step + apply_adam become capturable."""
         check(self.h, lib().sgnn_adam_device_step(self.h, 1 if enable else 0))

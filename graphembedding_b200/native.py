@@ -88,6 +88,7 @@ SIGNATURES = {
     'sgnn_zero_grads': (C.c_int, [_P, _P]),
     'sgnn_set_dropout_stream': (C.c_int, [_P, C.c_uint64, C.c_uint64]),
     'sgnn_set_pair_offset': (C.c_int, [_P, _I32, _I32]),
+    'sgnn_set_embed_tc': (C.c_int, [_P, _I32]),
     'sgnn_precision_at_k': (C.c_int, [_P, _P, _P, _I32, _I32, _P, _I32, _P, _P]),
     'sgnn_kendall_tau': (C.c_int, [_P, _P, _P, _I32, _I32, _P, _P, _P]),
     'sgnn_forward_pairs_host': (C.c_int, [_P, _BP, _P, _P, _I32, _P, _P]),

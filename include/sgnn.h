@@ -164,6 +164,12 @@ int sgnn_embed_graphs_nodes(SgnnHandle h, const SgnnGraphBatch* batch_dev, float
 int sgnn_pair_histogram(SgnnHandle h, const float* node_emb_dev, const int32_t* node_off_dev, const int32_t* g1_dev,
                         const int32_t* g2_dev, int32_t n_pairs, int32_t bins, float* hist_dev, int32_t* counts_dev,
                         void* stream);
+/* enable = 1: sgnn_embed_graphs_nodes (and the ranking entry points of models with a Histogram head) run the dense GCN
+ * layers H W of layers.py:96-118 as tcgen05 GEMMs over 128-row tiles of packed graphs (csrc/sgnn_embed_tc.cuh: 6-product
+ * bf16 split, fp32 in TMEM, A_hat applied outside the MMA through the tile's CSR) whenever the model fits: GCN-only node
+ * stacks of widths 16..64 (multiples of 16), graphs of <= 64 nodes, no dropout, Average / Attention / Padding pooling.
+ * Same results to fp32 rounding.  OFF by default: measured slower than the CUDA-core tile kernel on ~10-node graphs. */
+int sgnn_set_embed_tc(SgnnHandle h, int32_t enable);
 /* sgnn_pair_histogram for LARGE graphs on the tensor cores (csrc/sgnn_hist_pairs_tc.cuh; Web-shaped workloads,
  * BASELINE configs[4]): same layer, same outputs (integer counts equal outside the bin-edge band of the 6-product bf16
  * split).  Every graph is cut into tiles of 128 node rows; a work unit is one (row tile, column tile) of one pair, so

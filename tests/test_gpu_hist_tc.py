@@ -167,4 +167,6 @@ def test_tensor_core_engine_falls_back_when_the_database_graphs_are_too_large():
         ids, vals, sim = e.rank_device(qd, dd, 5)
         assert np.array_equal(sim.cpu().numpy(), a)
         out.append(a)
-    assert np.array_equal(out[0], out[1])          # both engines ran the same CUDA-core kernels
+    # both engines scored with the same CUDA-core kernels; the embeddings differ at rounding level (the tensor-core engine
+    # runs its dense GCN layers as 6-product bf16 GEMMs)
+    assert np.max(np.abs(out[0] - out[1])) <= 1e-6

@@ -277,34 +277,54 @@ struct TchHmma {
 __device__ __forceinline__ uint32_t tch_idesc_f16(int M, int N) {   // A fp16, B fp16, D fp32, both K-major
   return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);   // (fp16 x bf16 is an illegal instruction)
 }
+// Work of a CTA: a contiguous range [u0, u1) of units u = (A block ab, query block qb), ab-major -- an even split of ALL
+// units over the grid (the 2-D split of the scorer, g-groups x q-groups, left 10 % of this kernel's time to imbalance:
+// 79 database tiles in blocks of 4 and 128 query blocks over <= 148 CTAs gave 76 tile-units to most CTAs against a
+// mean of 68).  A range that crosses into the next A block reloads the resident database tiles once (a_free).
+struct TchRange {
+  int u0, u1, n_qb, GA, n_gtiles;
+  __device__ __forceinline__ int ab_first() const { return u0 / n_qb; }
+  __device__ __forceinline__ int ab_last() const { return (u1 - 1) / n_qb; }
+  __device__ __forceinline__ void segment(int ab, int& gt0, int& ga_count, int& qb0, int& nq) const {
+    gt0 = ab * GA; ga_count = min(GA, n_gtiles - gt0);
+    const int lo = max(u0, ab * n_qb), hi = min(u1, (ab + 1) * n_qb);
+    qb0 = lo - ab * n_qb; nq = hi - lo;
+  }
+};
+
 template <bool HMMA>
-__device__ __forceinline__ void tch_producer_mma_roles(const TcGeom& G, const TcCtaWork& Wk, const TcSmem& S,
-                                                       const TchHmma& H, const __nv_bfloat16* __restrict__ Ag,
+__device__ __forceinline__ void tch_producer_mma_roles(const TcGeom& G, const TchRange& R, const TcSmem& S,
+                                                       const TchHmma& H, uint64_t* a_free,
+                                                       const __nv_bfloat16* __restrict__ Ag,
                                                        const __nv_bfloat16* __restrict__ Bg, uint32_t tmem_base, int warp,
                                                        int lane) {
   constexpr int NB = HMMA ? 2 : TC_BUFS;
-  const int ga_count = Wk.ga_count, nq = Wk.nq;
-  if (lane != 0 || nq <= 0) return;
+  if (lane != 0 || R.u1 <= R.u0) return;
   if (warp == TC_PROD_WARP) {
-    tc::mbar_arrive_expect_tx(S.a_full, ga_count * S.a_bytes);
-    for (int ga = 0; ga < ga_count; ++ga)
-      tc::bulk_g2s(S.sA + ga * S.a_bytes, reinterpret_cast<const uint8_t*>(Ag) + (size_t)(Wk.gt0 + ga) * S.a_bytes,
-                   S.a_bytes, S.a_full);
-    int it = 0;
-    for (int i = 0; i < nq; ++i) {
-      const int s = i % G.stages;
-      if (i >= G.stages) tc::mbar_wait(S.b_empty + s, ((i / G.stages) - 1) & 1);
-      tc::mbar_arrive_expect_tx(S.b_full + s, S.b_bytes);
-      tc::bulk_g2s(S.sB + s * S.b_bytes, reinterpret_cast<const uint8_t*>(Bg) + (size_t)(Wk.qb0 + i) * S.b_bytes,
-                   S.b_bytes, S.b_full + s);
-      if (HMMA) {
-        for (int ga = 0; ga < ga_count; ++ga, ++it) {
-          const int sl = it & 1;
-          if (it >= 2) tc::mbar_wait(H.a2_empty + sl, ((it >> 1) - 1) & 1);
-          tc::mbar_arrive_expect_tx(H.a2_full + sl, TCH_A2_BYTES);
-          tc::bulk_g2s(H.sA2 + sl * TCH_A2_BYTES,
-                       H.cnt + ((size_t)(Wk.gt0 + ga) * H.m_pad + (size_t)(Wk.qb0 + i) * 8) * 4096, TCH_A2_BYTES,
-                       H.a2_full + sl);
+    int it = 0, qi = 0, seg = 0;
+    for (int ab = R.ab_first(); ab <= R.ab_last(); ++ab, ++seg) {
+      int gt0, ga_count, qb0, nq;
+      R.segment(ab, gt0, ga_count, qb0, nq);
+      if (seg > 0) tc::mbar_wait(a_free, (seg - 1) & 1);   // every MMA on the previous A block has completed
+      tc::mbar_arrive_expect_tx(S.a_full, ga_count * S.a_bytes);
+      for (int ga = 0; ga < ga_count; ++ga)
+        tc::bulk_g2s(S.sA + ga * S.a_bytes, reinterpret_cast<const uint8_t*>(Ag) + (size_t)(gt0 + ga) * S.a_bytes,
+                     S.a_bytes, S.a_full);
+      for (int i = 0; i < nq; ++i, ++qi) {
+        const int s = qi % G.stages;
+        if (qi >= G.stages) tc::mbar_wait(S.b_empty + s, ((qi / G.stages) - 1) & 1);
+        tc::mbar_arrive_expect_tx(S.b_full + s, S.b_bytes);
+        tc::bulk_g2s(S.sB + s * S.b_bytes, reinterpret_cast<const uint8_t*>(Bg) + (size_t)(qb0 + i) * S.b_bytes,
+                     S.b_bytes, S.b_full + s);
+        if (HMMA) {
+          for (int ga = 0; ga < ga_count; ++ga, ++it) {
+            const int sl = it & 1;
+            if (it >= 2) tc::mbar_wait(H.a2_empty + sl, ((it >> 1) - 1) & 1);
+            tc::mbar_arrive_expect_tx(H.a2_full + sl, TCH_A2_BYTES);
+            tc::bulk_g2s(H.sA2 + sl * TCH_A2_BYTES,
+                         H.cnt + ((size_t)(gt0 + ga) * H.m_pad + (size_t)(qb0 + i) * 8) * 4096, TCH_A2_BYTES,
+                         H.a2_full + sl);
+          }
         }
       }
     }
@@ -323,40 +343,45 @@ __device__ __forceinline__ void tch_producer_mma_roles(const TcGeom& G, const Tc
     a2_desc0 = tc::umma_desc(tc::smem_u32(H.sA2), 128 * 16, 128);
     wh_desc0 = tc::umma_desc(tc::smem_u32(H.sWh), TCH_H0 * 16, 128);
   }
-  tc::mbar_wait(S.a_full, 0);
-  int it = 0;
-  for (int i = 0; i < nq; ++i) {   // tile order: query block i outer, database tile ga inner (as the epilogue walks it)
-    const int s = i % G.stages;
-    tc::mbar_wait(S.b_full + s, (i / G.stages) & 1);
-    const uint64_t bd0 = b_desc0 + (uint64_t)((uint32_t)s * b_tile);
-    for (int ga = 0; ga < ga_count; ++ga, ++it) {
-      const int buf = it & (NB - 1);
-      if (it >= NB) tc::mbar_wait(S.t_empty + buf, ((it / NB) - 1) & 1);
-      tc::tc_fence_after();
-      const uint64_t ad0 = a_desc0 + (uint64_t)((uint32_t)ga * a_tile);
-      const uint32_t d_addr = tmem_base + (uint32_t)buf * TC_NPAD;
-      uint32_t acc = 0;
-      for (int c = 0; c < combos; ++c) {   // (hi,hi) (hi,lo) (lo,hi)
-        const uint32_t ao = c == 2 ? a_part : 0u, bo = c == 1 ? b_part : 0u;
-        for (int ks = 0; ks < ksteps; ++ks) {
-          tc::umma_bf16(d_addr, ad0 + ao + (uint64_t)(ks * a_ks), bd0 + bo + (uint64_t)(ks * b_ks), idesc, acc);
-          acc = 1;
+  int it = 0, qi = 0, seg = 0;
+  for (int ab = R.ab_first(); ab <= R.ab_last(); ++ab, ++seg) {
+    int gt0, ga_count, qb0, nq;
+    R.segment(ab, gt0, ga_count, qb0, nq);
+    tc::mbar_wait(S.a_full, seg & 1);
+    for (int i = 0; i < nq; ++i, ++qi) {   // tile order: query block outer, database tile inner (as the epilogue walks it)
+      const int s = qi % G.stages;
+      tc::mbar_wait(S.b_full + s, (qi / G.stages) & 1);
+      const uint64_t bd0 = b_desc0 + (uint64_t)((uint32_t)s * b_tile);
+      for (int ga = 0; ga < ga_count; ++ga, ++it) {
+        const int buf = it & (NB - 1);
+        if (it >= NB) tc::mbar_wait(S.t_empty + buf, ((it / NB) - 1) & 1);
+        tc::tc_fence_after();
+        const uint64_t ad0 = a_desc0 + (uint64_t)((uint32_t)ga * a_tile);
+        const uint32_t d_addr = tmem_base + (uint32_t)buf * TC_NPAD;
+        uint32_t acc = 0;
+        for (int c = 0; c < combos; ++c) {   // (hi,hi) (hi,lo) (lo,hi)
+          const uint32_t ao = c == 2 ? a_part : 0u, bo = c == 1 ? b_part : 0u;
+          for (int ks = 0; ks < ksteps; ++ks) {
+            tc::umma_bf16(d_addr, ad0 + ao + (uint64_t)(ks * a_ks), bd0 + bo + (uint64_t)(ks * b_ks), idesc, acc);
+            acc = 1;
+          }
         }
+        if (HMMA) {
+          const int sl = it & 1;
+          tc::mbar_wait(H.a2_full + sl, (it >> 1) & 1);
+          const uint64_t a2d = a2_desc0 + (uint64_t)((uint32_t)sl * (TCH_A2_BYTES >> 4));
+          const uint32_t d2 = tmem_base + 2u * TC_NPAD + (uint32_t)buf * TC_NPAD;
+          for (int q = 0; q < 8; ++q)
+            for (int sp = 0; sp < 3; ++sp)
+              tc::umma_bf16(d2 + (uint32_t)(q * TCH_H0), a2d + (uint64_t)(q * (4096 >> 4)), wh_desc0 + (uint64_t)(sp * (512 >> 4)),
+                            idesc2, sp > 0 ? 1u : 0u);
+        }
+        tc::umma_commit(S.t_full + buf);
+        if (HMMA) tc::umma_commit(H.a2_empty + (it & 1));
       }
-      if (HMMA) {
-        const int sl = it & 1;
-        tc::mbar_wait(H.a2_full + sl, (it >> 1) & 1);
-        const uint64_t a2d = a2_desc0 + (uint64_t)((uint32_t)sl * (TCH_A2_BYTES >> 4));
-        const uint32_t d2 = tmem_base + 2u * TC_NPAD + (uint32_t)buf * TC_NPAD;
-        for (int q = 0; q < 8; ++q)
-          for (int sp = 0; sp < 3; ++sp)
-            tc::umma_bf16(d2 + (uint32_t)(q * TCH_H0), a2d + (uint64_t)(q * (4096 >> 4)), wh_desc0 + (uint64_t)(sp * (512 >> 4)),
-                          idesc2, sp > 0 ? 1u : 0u);
-      }
-      tc::umma_commit(S.t_full + buf);
-      if (HMMA) tc::umma_commit(H.a2_empty + (it & 1));
+      tc::umma_commit(S.b_empty + s);   // the stage is free once this block's MMAs have completed
     }
-    if (nq > G.stages) tc::umma_commit(S.b_empty + s);   // the stage is free once this block's MMAs have completed
+    tc::umma_commit(a_free);
   }
 }
 
@@ -383,21 +408,23 @@ allpairs_tc_head_kernel(const __grid_constant__ ModelDev M, const TcGeom G, cons
   uint64_t* t_empty = t_full + TC_BUFS;
   uint64_t* a2_full = t_empty + TC_BUFS;
   uint64_t* a2_empty = a2_full + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(a2_empty + 2);
+  uint64_t* a_free = a2_empty + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(a_free + 1);
   // TCH_FLOATS, 16-byte aligned (pointer arithmetic, not an integer round trip: the pointer stays a shared-memory pointer)
   float* sW = reinterpret_cast<float*>(tmem_slot + 4) + (((16u - (tc::smem_u32(tmem_slot + 4) & 15u)) & 15u) >> 2);
 
   // warp index through a shuffle: provably warp-uniform, so that the role branches are uniform control flow and the
   // epilogue's constant operands can go through the uniform datapath (LDCU -> UR operands of FFMA2)
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
-  const int gg = blockIdx.x / G.q_groups, qg = blockIdx.x - gg * G.q_groups;
-  const int gt0 = gg * G.GA;
-  const int ga_count = min(G.GA, G.n_gtiles - gt0);
-  const int qb0 = qg * G.qb_per_group;
-  const int nq = max(0, min(G.qb_per_group, G.n_qblocks - qb0));
+  const int n_ab = (G.n_gtiles + G.GA - 1) / G.GA;
+  const long long total_units = (long long)n_ab * G.n_qblocks;
+  TchRange R;
+  R.u0 = (int)(total_units * blockIdx.x / gridDim.x); R.u1 = (int)(total_units * (blockIdx.x + 1) / gridDim.x);
+  R.n_qb = G.n_qblocks; R.GA = G.GA; R.n_gtiles = G.n_gtiles;
 
   if (threadIdx.x == 0) {
     tc::mbar_init(a_full, 1);
+    tc::mbar_init(a_free, 1);
     for (int s = 0; s < G.stages; ++s) { tc::mbar_init(b_full + s, 1); tc::mbar_init(b_empty + s, 1); }
     for (int b = 0; b < NB; ++b) { tc::mbar_init(t_full + b, 1); tc::mbar_init(t_empty + b, 8); }
     if (HMMA)
@@ -441,28 +468,32 @@ allpairs_tc_head_kernel(const __grid_constant__ ModelDev M, const TcGeom G, cons
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp >= TC_PROD_WARP) {
-    TcCtaWork Wk{gt0, ga_count, qb0, nq};
     TcSmem S{sA, sB, a_full, b_full, b_empty, t_full, t_empty, a_bytes, b_bytes};
     TchHmma H{sA2, sWh, a2_full, a2_empty, cnt, G.n_qblocks * 8};
-    tch_producer_mma_roles<HMMA>(G, Wk, S, H, Ag, Bg, tmem_base, warp, lane);
-  } else {
+    tch_producer_mma_roles<HMMA>(G, R, S, H, a_free, Ag, Bg, tmem_base, warp, lane);
+  } else if (R.u1 > R.u0) {
     TcHeadEpi E;
     E.sW = sW; E.slot = slot; E.act_ntn = M.pair_act; E.act0 = M.Hd[0].act; E.act1 = M.Hd[1].act; E.act2 = M.Hd[2].act;
     E.act3 = M.Hd[3].act; E.final_act = M.final_act; E.yeta = M.yeta;
     E.hscale = HMMA ? *reinterpret_cast<const float*>(tmem_slot + 2) : 1.f;
     E.sim = sim; E.ld = ld; E.m = G.m; E.n = G.n; E.cnt = cnt; E.node_off_q = node_off_q; E.node_off_db = node_off_db;
     const int lg = warp & 3, part = (warp >> 2) & 1, grp = warp >> 3;
-    const int total = nq * ga_count;
-    int i = grp / ga_count, ga = grp - i * ga_count;
-    for (int it = grp; it < total; it += TC_EPI_GROUPS) {
-      const int buf = it & (NB - 1);
-      tc::mbar_wait(t_full + buf, (it / NB) & 1);
-      tc::tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + buf * TC_NPAD;
-      const int g = (gt0 + ga) * 128 + lg * 32 + lane;
-      tc_head_epilogue_part<HIST, CONSTW, HMMA>(E, taddr, taddr + 2 * TC_NPAD, (qb0 + i) * G.QH, part, g, t_empty + buf, lane);
-      ga += TC_EPI_GROUPS;
-      while (ga >= ga_count) { ga -= ga_count; ++i; }
+    int it_base = 0;
+    for (int ab = R.ab_first(); ab <= R.ab_last(); ++ab) {
+      int gt0, ga_count, qb0, nq;
+      R.segment(ab, gt0, ga_count, qb0, nq);
+      const int total = nq * ga_count;
+      for (int lt = (grp - it_base) & (TC_EPI_GROUPS - 1); lt < total; lt += TC_EPI_GROUPS) {
+        const int it = it_base + lt;
+        const int i = lt / ga_count, ga = lt - i * ga_count;
+        const int buf = it & (NB - 1);
+        tc::mbar_wait(t_full + buf, (it / NB) & 1);
+        tc::tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + buf * TC_NPAD;
+        const int g = (gt0 + ga) * 128 + lg * 32 + lane;
+        tc_head_epilogue_part<HIST, CONSTW, HMMA>(E, taddr, taddr + 2 * TC_NPAD, (qb0 + i) * G.QH, part, g, t_empty + buf, lane);
+      }
+      it_base += total;
     }
   }
   tc::tc_fence_before();

@@ -411,10 +411,14 @@ int score_all_pairs_tc(SgnnHandle h, const float* emb_q, int m, const float* emb
   const size_t fixed = (size_t)TC_GA_MAX * tc_a_bytes(G) + TC_TAIL_BYTES + 1024 + (head ? sgnn_tc_head_smem_bytes(cnt_tiled) : 0);
   if (fixed + 2 * (size_t)tc_b_bytes(G) > (size_t)h->smem_optin)
     return fail(h, "embedding too wide for the tensor-core all-pairs tiles");
-  G.stages = (int)std::min<size_t>(std::min(G.qb_per_group, TC_MAX_STAGES), ((size_t)h->smem_optin - fixed) / tc_b_bytes(G));
+  // the head kernel splits ALL (A block, query block) units evenly over the grid (sgnn_allpairs_tc_head.cuh: TchRange)
+  const int64_t head_units = (int64_t)g_groups * G.n_qblocks;
+  const int head_grid = (int)std::min<int64_t>(h->sm_count, head_units);
+  const int per_cta = head ? (int)((head_units + head_grid - 1) / head_grid) : G.qb_per_group;
+  G.stages = (int)std::min<size_t>(std::min(per_cta, TC_MAX_STAGES), ((size_t)h->smem_optin - fixed) / tc_b_bytes(G));
   size_t smem = fixed + (size_t)G.stages * tc_b_bytes(G);
   smem = std::max<size_t>(smem, 120 * 1024);  // one CTA per SM: each CTA owns all 512 TMEM columns
-  const int grid = g_groups * q_groups;
+  const int grid = head ? head_grid : g_groups * q_groups;
   cudaError_t e = cudaSuccess;
   if (head && h->head_slot >= 0 &&   // the head weights' constant slot is refreshed wherever the coefficient matrix is (parameters only)
       ((stages & SCORE_COEF_ONLY) || ((stages & SCORE_PREP_Q) && !(stages & SCORE_COEF_READY))))

@@ -470,7 +470,7 @@ int score_all_pairs_stages(SgnnHandle h, const float* emb_q, int32_t m, const fl
   if (M.n_head > 0) {   // SimGNN-style head
     // each stage needs the node rows of ITS side (the ranking entry points prepare the query side before the
     // database has been embedded)
-    const bool need_q = M.hist_bins > 0 && (stages & (SCORE_PREP_Q | SCORE_MAIN));
+    const bool need_q = M.hist_bins > 0 && (stages & (SCORE_PREP_Q | SCORE_MAIN | SCORE_COEF_ONLY));
     const bool need_db = M.hist_bins > 0 && (stages & (SCORE_PREP_DB | SCORE_MAIN));
     if ((need_q && !h->hside[0].rows) || (need_db && !h->hside[1].rows))
       return fail(h, "the model has a Histogram layer: all-pairs scoring needs the node rows of both sides "
@@ -511,8 +511,12 @@ int score_all_pairs_stages(SgnnHandle h, const float* emb_q, int32_t m, const fl
         allpairs_prep_kernel<<<(m + 3) / 4, 128, 0, st>>>(M, h->d_params, emb_q, m, h->dep, h->d_P, h->d_C);
         CUDA_OK(h, cudaGetLastError());
       }
-      if (tc_q) CUDA_OK(h, sgnn_hist_tc_prep_q(HG, h->hside[0].rows, h->hside[0].node_off, h->ht, st));
+      // (with SCORE_COEF_READY the bucket sort has run in the SCORE_COEF_ONLY stage, beside the query embedding)
+      if (tc_q) CUDA_OK(h, sgnn_hist_tc_prep_q(HG, h->hside[0].rows, h->hside[0].node_off, h->ht, st,
+                                                (stages & SCORE_COEF_READY) ? 2 : 0));
     }
+    if ((stages & SCORE_COEF_ONLY) && tc_q)
+      CUDA_OK(h, sgnn_hist_tc_prep_q(HG, nullptr, h->hside[0].node_off, h->ht, st, 1));
     if ((stages & SCORE_PREP_DB) && tc_db)
       CUDA_OK(h, sgnn_hist_tc_prep_db(HG, h->hside[1].rows, h->hside[1].node_off, h->ht, st));
     if (!(stages & SCORE_MAIN)) return 0;

@@ -11,11 +11,14 @@ bool sgnn_hist_tc_supported(int node_dim, int bins, int max_nodes_q, int max_nod
          max_nodes_q * max_nodes_db <= 255;   // one byte per bin in the count matrix
 }
 
+// mode 0: bucket sort of the queries + operand tiles; 1: sort only (needs the node offsets, not the node rows: a
+// caller may run it beside the query embedding); 2: operand tiles only (the sort has run)
 cudaError_t sgnn_hist_tc_prep_q(const HistTcGeom& G, const float* nodes_q, const int32_t* node_off_q, const HistTcWs& ws,
-                                cudaStream_t st) {
-  ht_sort_q_kernel<<<1, 1024, 0, st>>>(node_off_q, G.m, G.max_btiles, ws.qmeta, ws.status);
-  ht_prep_q_kernel<<<G.max_btiles, 128, 0, st>>>(G, nodes_q, node_off_q, ws.qmeta,
-                                                 reinterpret_cast<__nv_bfloat16*>(ws.Bt));
+                                cudaStream_t st, int mode) {
+  if (mode != 2) ht_sort_q_kernel<<<1, 1024, 0, st>>>(node_off_q, G.m, G.max_btiles, ws.qmeta, ws.status);
+  if (mode != 1)
+    ht_prep_q_kernel<<<G.max_btiles, 128, 0, st>>>(G, nodes_q, node_off_q, ws.qmeta,
+                                                   reinterpret_cast<__nv_bfloat16*>(ws.Bt));
   return cudaGetLastError();
 }
 

@@ -156,14 +156,22 @@ ht_prep_db_kernel(const HistTcGeom G, const float* __restrict__ nodes_db, const 
   const int n_at = min(G.max_atiles, total / G.S + 1);
   if (t == 0 && threadIdx.x == 0) qmeta[1] = n_at;
   if (t >= n_at) return;
-  if (threadIdx.x < 2) {   // lower_bound over the graph start offsets
-    const int key = (t + (int)threadIdx.x) * G.S;
-    int lo = 0, hi = G.n;
+  if (threadIdx.x < 64) {   // lower_bound over the graph start offsets: warp w searches key (t + w) S, 32 probes per step
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;   // (3 dependent loads for 10 000 graphs instead of 14)
+    const int key = (t + w) * G.S;
+    int lo = 0, hi = G.n;   // answer in [lo, hi]
     while (lo < hi) {
-      const int mid = (lo + hi) >> 1;
-      if (node_off_db[mid] < key) lo = mid + 1; else hi = mid;
+      const int span = hi - lo;
+      const int step = (span + 32) / 33;                     // probes at lo + step (lane + 1) - 1 ...
+      const int pos = min(hi - 1, lo + step * (lane + 1) - 1);
+      const bool less = node_off_db[pos] < key;              // monotone in pos
+      const unsigned bal = __ballot_sync(0xffffffffu, less);
+      const int nless = __popc(bal);                         // probes 0 .. nless - 1 are < key
+      const int new_lo = nless == 0 ? lo : min(hi - 1, lo + step * nless - 1) + 1;
+      const int new_hi = nless == 32 ? hi : min(hi - 1, lo + step * (nless + 1) - 1);
+      lo = new_lo; hi = max(new_lo, new_hi);
     }
-    s_g[threadIdx.x] = lo;
+    if (lane == 0) s_g[w] = lo;
   }
   __syncthreads();
   const int g0 = s_g[0], g1 = s_g[1];

@@ -58,7 +58,7 @@ inline int64_t ht_max_atiles(int64_t rows) { return rows / (129 - HT_MAXN_DB) + 
 // false: shape outside the tensor-core kernel (the caller keeps the CUDA-core kernel)
 bool sgnn_hist_tc_supported(int node_dim, int bins, int max_nodes_q, int max_nodes_db);
 cudaError_t sgnn_hist_tc_prep_q(const HistTcGeom& G, const float* nodes_q, const int32_t* node_off_q, const HistTcWs& ws,
-                                cudaStream_t st);
+                                cudaStream_t st, int mode = 0);
 cudaError_t sgnn_hist_tc_prep_db(const HistTcGeom& G, const float* nodes_db, const int32_t* node_off_db,
                                  const HistTcWs& ws, cudaStream_t st);
 cudaError_t sgnn_hist_tc_run(const HistTcGeom& G, const HistTcWs& ws, const int32_t* node_off_db, int sm_count,

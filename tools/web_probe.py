@@ -13,7 +13,7 @@ W = type('WebBench', (D.WebData,), {'num_train': 256})
 gs = W(True).graphs
 enc = NodeFeatureOneHotEncoder(gs, 'type', feat_idx_dic={l: i for i, l in enumerate(D.WebData.labels)})
 batch = pack_nx_graphs(gs, enc)
-eng = SgnnEngine(parse_layers(bench.TRAIN_LAYERS, 32), 32)
+eng = SgnnEngine(parse_layers(bench.TRAIN_LAYERS, 32), 32, precision=os.environ.get('WEB_PRECISION', 'bf16x3'))
 eng.init_params(123)
 eng.reserve(max_graphs=256, max_nodes=batch.total_nodes, max_nnz=batch.nnz, max_pairs=4096)
 bd = batch.to(eng.device)

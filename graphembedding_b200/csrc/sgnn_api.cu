@@ -1349,6 +1349,9 @@ int sgnn_apply_adam_allreduce(SgnnHandle h, float grad_scale, float* loss_dev, v
   if (h->peer_world == 0) return fail(h, "sgnn_apply_adam_allreduce: no peer exchange set up (sgnn_peer_create/connect)");
   for (int r = 0; r < h->peer_world; ++r)
     if (!h->peer_bufs[r]) return fail(h, "sgnn_apply_adam_allreduce: peers not connected");
+  if (h->adam_on_device)
+    return fail(h, "sgnn_apply_adam_allreduce: the Adam step count lives on the device (sgnn_adam_device_step); the peer "
+                   "all-reduce form keeps it on the host -- disable the device step count first");
   h->adam_t += 1;
   const SgnnConfig& c = h->cfg;
   const double t = (double)h->adam_t;

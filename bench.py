@@ -734,6 +734,18 @@ def run_web(torch, dev, rank, world, local, args, barrier, max_over_ranks, flush
     h32_ms = timed_steps(torch, lambda: eng32.pair_histogram(rows, bd.node_off, g1, g2, bins=16), args.steps, flush) / args.steps
     moved = int((c_tc - c_32).abs().sum().item()) // 2     # cells that the two kernels put into different bins (bin-edge band)
     tpeak, tpeak_src = peak_tflops()
+    # listed-pair TRAINING on the same graphs (the arms' buffers of the per-pair kernel in a global workspace): 128 pairs
+    TB = 128
+    tt = torch.as_tensor(np.random.default_rng(3).uniform(0.05, 1.0, TB).astype(np.float32), device=dev)
+    tl = torch.zeros(4, device=dev)
+
+    def tstep():
+        tl.zero_()
+        eng32.train_step(bd, g1[:TB], g2[:TB], tt, TB, 1.0, 1.0, loss=tl)
+        eng32.apply_adam(1.0, tl)
+    for _ in range(3):
+        tstep()
+    t_ms = timed_steps(torch, tstep, max(3, args.steps // 2), flush) / max(3, args.steps // 2)
     no = batch.node_off
     n1 = np.diff(no)[g1.cpu().numpy()].astype(np.float64)
     n2 = np.diff(no)[g2.cpu().numpy()].astype(np.float64)
@@ -752,6 +764,9 @@ def run_web(torch, dev, rank, world, local, args, barrier, max_over_ranks, flush
                          'note': 'algorithmic FLOPs 2 d per node-node cell (SURVEY 8(d)); the kernel is bound by the '
                                  'sigmoid / bin epilogue (7.75 instructions per cell), not by the six bf16 products'},
             'parity': {'cells_binned_differently_than_cuda_core_kernel': moved, 'cells': cells},
+            'train': {'pairs_per_step': TB, 'ms_per_step': t_ms, 'value': TB * world / (t_ms * 1e-3), 'unit': 'pairs/s',
+                      'note': 'fwd + bwd + Adam on 128 listed pairs of the Web-shaped graphs (train_team_kernel, arm '
+                              'buffers in a global workspace), fp32'},
             'embed_gather': {'algorithmic_bytes': gather_bytes, 'achieved_GBps': gather_bytes / (e_ms * 1e-3) / 1e9,
                              'hbm_peak_GBps': peak},
             'histogram': {'node_node_cells': cells, 'cells_per_s': cells / (h_ms * 1e-3),

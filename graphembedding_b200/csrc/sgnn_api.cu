@@ -84,6 +84,8 @@ struct SgnnHandle_t {
   float *d_params = nullptr, *d_grads = nullptr, *d_m = nullptr, *d_v = nullptr, *d_loss = nullptr;
   int64_t adam_t = 0;
   bool embed_tc = false;                      // sgnn_set_embed_tc
+  float* d_arm_ws = nullptr;                  // per-CTA arm buffers of the per-pair training kernel for graphs beyond shared memory
+  int64_t cap_arm_ws = 0;
   long long* d_adam_t = nullptr;              // sgnn_adam_device_step: the step count (and the step size behind it) on the device
   float* d_adam_lr = nullptr;
   bool adam_on_device = false;
@@ -322,6 +324,8 @@ int plan_launches(SgnnHandle h) {
     if (set_smem(h, train_team_kernel<false, 1>, (size_t)h->smem_optin)) return 1;
     if (set_smem(h, train_team_kernel<true, 2>, (size_t)h->smem_optin)) return 1;
     if (set_smem(h, train_team_kernel<false, 2>, (size_t)h->smem_optin)) return 1;
+    if (set_smem(h, train_team_kernel<true, 1, true>, (size_t)h->smem_optin)) return 1;
+    if (set_smem(h, train_team_kernel<false, 1, true>, (size_t)h->smem_optin)) return 1;
   }
   return 0;
 }
@@ -799,6 +803,7 @@ int sgnn_destroy(SgnnHandle h) {
   cudaFree(h->ht.At); cudaFree(h->ht.Bt); cudaFree(h->ht.qmeta); cudaFree(h->ht.ameta); cudaFree(h->ht.status);
   cudaFree(h->ht.cnt);
   cudaFree(h->d_adam_t);
+  cudaFree(h->d_arm_ws);
   cudaFree(h->hp.At); cudaFree(h->hp.Bt); cudaFree(h->hp.tile_off); cudaFree(h->hp.unit_off); cudaFree(h->hp.cnt);
   HostWs& w = h->ws;
   for (int s = 0; s < 2; ++s) {
@@ -1222,12 +1227,24 @@ static int launch_pairs(SgnnHandle h, bool bwd, const SgnnGraphBatch* b, const i
   if (n_pairs == 0) return 0;
   if (global_batch < n_pairs) return fail(h, "global_batch < n_pairs");
   if (padding_guard(h, b)) return 1;
-  if (b->max_nodes > 32) {   // beyond the warp-per-pair kernel; the CTA-per-pair kernel takes what fits shared memory
+  bool garms = false;   // the arms' buffers in a global workspace: graphs beyond what shared memory holds (Web-shaped)
+  if (b->max_nodes > 32) {   // beyond the warp-per-pair kernel; the CTA-per-pair kernel takes any size
     const size_t need = h->use_team ? team_smem_floats(h->M, (int)b->max_nodes) * sizeof(float) : 0;
-    if (!h->use_team || need > (size_t)h->smem_optin)
-      return fail(h, "graphs of up to " + std::to_string(b->max_nodes) + " nodes do not fit the per-pair kernel's shared memory (" +
-                         std::to_string(need / 1024) + " KB needed): listed-pair training / evaluation of graphs this large "
-                         "is not built yet (embedding, all-pairs scoring and the histogram op handle them)");
+    if (!h->use_team)
+      return fail(h, "graphs of up to " + std::to_string(b->max_nodes) + " nodes need the CTA-per-pair training kernel "
+                     "(SGNN_TRAIN_KERNEL=warp serves graphs of <= 32 nodes)");
+    if (need > (size_t)h->smem_optin) {
+      garms = true;
+      const size_t need_g = team_smem_floats_garms(h->M, (int)b->max_nodes) * sizeof(float);
+      if (need_g > (size_t)h->smem_optin)
+        return fail(h, "the model's weights do not fit the per-pair kernel's shared memory (" + std::to_string(need_g / 1024) +
+                           " KB needed)");
+      const int64_t ws = (int64_t)team_arm_ws_floats(h->M, (int)b->max_nodes) * std::min(n_pairs, h->sm_count);
+      if (ws > h->cap_arm_ws) {   // grown by the call (the first call of a size allocates; steady-state calls do not)
+        if (dev_alloc(h, &h->d_arm_ws, ws)) return 1;
+        h->cap_arm_ws = ws;
+      }
+    }
   }
   const int v = b->max_nodes <= 16 ? 0 : 1;
   const int wpb = h->train_wpb[v];
@@ -1245,6 +1262,20 @@ static int launch_pairs(SgnnHandle h, bool bwd, const SgnnGraphBatch* b, const i
   }
   if (h->use_team) {
     const int nmax = std::max(4, (int)b->max_nodes);
+    if (garms) {
+      const size_t gsmem = team_smem_floats_garms(h->M, nmax) * sizeof(float);
+      const int gblocks = std::min(n_pairs, h->sm_count);
+      if (bwd)
+        train_team_kernel<true, 1, true><<<gblocks, TEAM_CTA, gsmem, st>>>(
+            h->M, to_dev(b), nmax, h->d_params, g1, g2, target_sim, n_pairs, invB, s1, s2, h->d_grads, loss, raw, sim,
+            dropping, dbase, h->pair_offset, h->pair_stride, h->d_arm_ws);
+      else
+        train_team_kernel<false, 1, true><<<gblocks, TEAM_CTA, gsmem, st>>>(
+            h->M, to_dev(b), nmax, h->d_params, g1, g2, target_sim, n_pairs, invB, s1, s2, h->d_grads, loss, raw, sim,
+            dropping, dbase, h->pair_offset, h->pair_stride, h->d_arm_ws);
+      CUDA_OK(h, cudaGetLastError());
+      return 0;
+    }
     const size_t smem = team_smem_floats(h->M, nmax) * sizeof(float);
     // more pairs than SMs: two CTAs per SM (the 64-register variant) when shared memory holds them
     const bool two = n_pairs > h->sm_count && 2 * (smem + 1024) <= (size_t)h->smem_optin + 1024;   // (228 KB per SM, 1 KB reserved per CTA)

@@ -73,6 +73,13 @@ __host__ __device__ inline size_t team_smem_floats(const ModelDev& M, int nmax) 
   const int wpfl = M.pair_kind == SGNN_LAYER_NTN ? round_up4(M.D * M.D * M.K) : 0;
   return (size_t)2 * wfl + wpfl + round_up4(M.aux_floats) + 2 * (size_t)t.arm_total + t.pair_total;
 }
+// shared memory of the GARMS variant (arms in the global workspace) and the workspace floats per CTA
+__host__ __device__ inline size_t team_smem_floats_garms(const ModelDev& M, int nmax) {
+  return team_smem_floats(M, nmax) - 2 * (size_t)team_layout(M, nmax).arm_total;
+}
+__host__ __device__ inline size_t team_arm_ws_floats(const ModelDev& M, int nmax) {
+  return 2 * (size_t)team_layout(M, nmax).arm_total;
+}
 
 __device__ __forceinline__ GraphS team_load_graph(const BatchDev& B, int g, float* scratch, const TeamLayout& TL,
                                                   const Team& tm) {
@@ -455,13 +462,18 @@ __device__ __forceinline__ void team_head_bwd(const ModelDev& M, const float* W,
 // MINB: CTAs per SM the register budget is cut for -- 1 (128 registers) for batches of at most one pair per SM, where
 // only the latency of a pair counts; 2 (64 registers, no spills) for larger batches, where two pairs per SM overlap
 // their barrier-separated phases
-template <bool BWD, int MINB>
+// GARMS: the two arms' buffers (CSR slice, saved activations, gradient rows: ~160 floats per node for GCN32-GCN16) live
+// in a GLOBAL workspace slice of this CTA instead of shared memory -- Web-shaped graphs of hundreds of nodes
+// (configs[4]) do not fit next to the weights.  Same code, same barriers (bar.sync orders global accesses of the CTA's
+// threads as well); the slice stays in L1 / L2.
+template <bool BWD, int MINB, bool GARMS = false>
 __global__ void __launch_bounds__(TEAM_CTA, MINB)
 train_team_kernel(const __grid_constant__ ModelDev M, const BatchDev B, int nmax, const float* __restrict__ params,
                   const int32_t* __restrict__ g1, const int32_t* __restrict__ g2,
                   const float* __restrict__ target_sim, int n_pairs, float inv_global_batch, float tsum, float tsqsum,
                   float* __restrict__ grads, float* __restrict__ loss, float* __restrict__ raw_out,
-                  float* __restrict__ sim_out, int dropping, uint32_t dbase, int p0, int pstride) {
+                  float* __restrict__ sim_out, int dropping, uint32_t dbase, int p0, int pstride,
+                  float* __restrict__ arm_ws = nullptr) {
   // local pair p is pair p0 + p * pstride of the GLOBAL batch (data-parallel ranks: the dropout masks are keyed on it)
   extern __shared__ __align__(16) float smem[];
   const TeamLayout TL = team_layout(M, nmax);
@@ -472,8 +484,8 @@ train_team_kernel(const __grid_constant__ ModelDev M, const BatchDev B, int nmax
   float* s_wp = s_g + wfl;
   const int wpfl = M.pair_kind == SGNN_LAYER_NTN ? round_up4(D * DK) : 0;
   float* s_aux = s_wp + wpfl;
-  float* arms = s_aux + round_up4(M.aux_floats);
-  float* pairb = arms + 2 * TL.arm_total;
+  float* arms = GARMS ? arm_ws + (size_t)blockIdx.x * 2 * TL.arm_total : s_aux + round_up4(M.aux_floats);
+  float* pairb = s_aux + round_up4(M.aux_floats) + (GARMS ? 0 : 2 * TL.arm_total);
   stage_weights(M, params, s_w, s_wp);
   if (BWD)
     for (int i = threadIdx.x; i < wfl; i += blockDim.x) s_g[i] = 0.f;

@@ -265,6 +265,11 @@ __device__ __forceinline__ uint32_t ht_half2(uint32_t word, uint32_t sel) {
   return r;
 }
 
+// ceil(65536 / n) for n = 1..16 by table: (p * ht_rcp16(n)) >> 16 == p / n for p < 4096 (an integer division by a run-time
+// value costs ~25 instructions, and the pair phase needs one per round)
+__constant__ uint32_t c_ht_rcp16[17] = {0, 65536, 32768, 21846, 16384, 13108, 10923, 9363, 8192, 7282, 6554, 5958, 5462, 5042, 4682, 4370, 4096};
+__device__ __forceinline__ uint32_t ht_rcp16(int n) { return c_ht_rcp16[n]; }
+
 struct HtTileCtx {
   uint32_t taddr;                 // this warp's lanes, this tile's TMEM buffer
   int n_seg, bt_first;            // B tile: segments, first sorted query
@@ -290,7 +295,7 @@ template <int N, bool PAIRED>
 __device__ __forceinline__ void ht_tile(const HtTileCtx& C, int row, int tid, int half, int lane, int& batch) {
   // the first pair this thread reduces: its lane range is fetched now, long before it is needed
   int pre_l0 = 0, pre_l1 = 0;
-  const int pre_gi = tid / max(1, min(HT_SEGB, C.n_seg));   // graph of this thread's first pair (first batch)
+  const int pre_gi = (int)(((uint32_t)tid * ht_rcp16(max(1, min(HT_SEGB, C.n_seg)))) >> 16);   // graph of this thread's first pair (first batch)
   if (pre_gi < C.ng) {
     pre_l0 = C.node_off_db[C.g0 + pre_gi] - C.row0;
     pre_l1 = C.node_off_db[C.g0 + pre_gi + 1] - C.row0;
@@ -354,8 +359,9 @@ __device__ __forceinline__ void ht_tile(const HtTileCtx& C, int row, int tid, in
     // 32 threads active in the loop).  The counter rows are HT_CSTRIDE = 129 words apart: 32 segments of one lane
     // sit in different banks.
     const uint32_t n_pairs = ng * (uint32_t)ns;
+    const uint32_t rcp_ns = ht_rcp16(ns);
     for (uint32_t p = (uint32_t)tid; p < n_pairs; p += 32u * HT_GROUP_WARPS) {
-      const uint32_t gi = p / (uint32_t)ns, sg = p - gi * (uint32_t)ns;
+      const uint32_t gi = (p * rcp_ns) >> 16, sg = p - gi * (uint32_t)ns;   // p / ns, p % ns (exact: p < 4096, ns <= 16)
       int l0, l1;
       if (s0 == 0 && p == (uint32_t)tid) { l0 = pre_l0; l1 = pre_l1; }   // the prefetched range
       else {
@@ -391,7 +397,7 @@ __device__ __forceinline__ void ht_tile(const HtTileCtx& C, int row, int tid, in
         add_field(C.bins, 0u - over);
         extra += over;
       }
-      add_field(C.bins - 1, extra);
+      if (extra) add_field(C.bins - 1, extra);   // (rare: only cells whose sigmoid rounds to 1)
       const int q = C.q_sorted[C.bt_first + s0 + (int)sg];
       if (C.m_pad > 0) {
         // fp16 K-major operand tiles [g / 128][q][k chunk][g % 128][8 bins]: half(1024 + c) has the bits 0x6400 | c, so

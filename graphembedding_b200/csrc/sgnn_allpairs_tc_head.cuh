@@ -47,6 +47,8 @@ struct TcHeadEpi {
   const uint8_t* cnt;              // [m][n][16] bin counts (HIST)
   const int32_t* node_off_q;
   const int32_t* node_off_db;
+  unsigned long long* smax;        // optional [m][n_slices] slice maxima (rank keys) for the hinted top-k, as TcEpi::smax
+  int n_slices;
 };
 
 // element i of the head weight block: U folded into the NTN rows of layer 0, missing biases = 0
@@ -249,6 +251,16 @@ __device__ __forceinline__ void tc_head_epilogue_part(const TcHeadEpi& E, uint32
     tch_tail2(E, sW, A, B, oa, ob);
     if (gv && va) E.sim[(size_t)qa * E.ld + g] = oa;
     if (gv && vb) E.sim[(size_t)qb * E.ld + g] = ob;
+    if (E.smax) {   // largest rank key of this warp's 32-graph slice, per query (ties -> highest graph id)
+      const float ma = gv ? oa : -INFINITY, mb = gv ? ob : -INFINITY;
+      const float wa = tc_warp_max(ma), wb = tc_warp_max(mb);
+      const unsigned ha = __ballot_sync(0xffffffffu, !(ma < wa)), hb = __ballot_sync(0xffffffffu, !(mb < wb));
+      if (lane == 0) {
+        const size_t sl = (size_t)(g >> 5);
+        if (va) E.smax[(size_t)qa * E.n_slices + sl] = tc_rank_key(wa, (g & ~31) + 31 - __clz(ha | 1u));
+        if (vb) E.smax[(size_t)qb * E.n_slices + sl] = tc_rank_key(wb, (g & ~31) + 31 - __clz(hb | 1u));
+      }
+    }
   }
 }
 
@@ -390,7 +402,8 @@ __global__ void __launch_bounds__(TCH_THREADS, 1)
 allpairs_tc_head_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const float* __restrict__ params, int slot,
                         const __nv_bfloat16* __restrict__ Ag, const __nv_bfloat16* __restrict__ Bg,
                         float* __restrict__ sim, int64_t ld, const uint8_t* __restrict__ cnt,
-                        const int32_t* __restrict__ node_off_q, const int32_t* __restrict__ node_off_db) {
+                        const int32_t* __restrict__ node_off_q, const int32_t* __restrict__ node_off_db,
+                        unsigned long long* __restrict__ smax) {
   static_assert(!HMMA || HIST, "the second MMA is the histogram half of layer 0");
   constexpr int NB = HMMA ? 2 : TC_BUFS;
   extern __shared__ __align__(1024) uint8_t tc_smem[];
@@ -477,6 +490,7 @@ allpairs_tc_head_kernel(const __grid_constant__ ModelDev M, const TcGeom G, cons
     E.act3 = M.Hd[3].act; E.final_act = M.final_act; E.yeta = M.yeta;
     E.hscale = HMMA ? *reinterpret_cast<const float*>(tmem_slot + 2) : 1.f;
     E.sim = sim; E.ld = ld; E.m = G.m; E.n = G.n; E.cnt = cnt; E.node_off_q = node_off_q; E.node_off_db = node_off_db;
+    E.smax = smax; E.n_slices = G.n_gtiles * 4;
     const int lg = warp & 3, part = (warp >> 2) & 1, grp = warp >> 3;
     int it_base = 0;
     for (int ab = R.ab_first(); ab <= R.ab_last(); ++ab) {

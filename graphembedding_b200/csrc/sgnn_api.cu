@@ -366,6 +366,15 @@ bool head_hmma_enabled() {
   return !off;
 }
 
+// the scorer stage of a head model will run on the tensor-core head kernel (same predicate as score_all_pairs_stages)
+bool head_tc_will_run(SgnnHandle h) {
+  const ModelDev& M = h->M;
+  if (M.n_head == 0 || !head_tc_enabled(h)) return false;
+  if (M.hist_bins == 0) return true;
+  return hist_tc_enabled(h) && h->hside[0].rows && h->hside[1].rows &&
+         sgnn_hist_tc_supported(M.node_dim, M.hist_bins, h->hside[0].max_nodes, h->hside[1].max_nodes);
+}
+
 int ensure_query_tables(SgnnHandle h, int64_t m) {
   if (m <= h->cap_P) return 0;
   return fail(h, "query table workspace too small: call sgnn_reserve(max_queries >= m) first");
@@ -432,7 +441,7 @@ int score_all_pairs_tc(SgnnHandle h, const float* emb_q, int m, const float* emb
     e = sgnn_tc_prep_q(M, G, h->d_params, emb_q, h->d_Btc, h->d_coef, (stages & SCORE_COEF_READY) ? 2 : 0, st);
   if (e == cudaSuccess && (stages & SCORE_PREP_DB)) e = sgnn_tc_prep_db(M, G, emb_db, h->d_Atc, st);
   if (e == cudaSuccess && (stages & SCORE_MAIN))
-    e = head ? sgnn_tc_score_head(M, G, grid, smem, h->d_params, h->head_slot, h->d_Atc, h->d_Btc, sim, ld, cnt, cnt_tiled, node_off_q, node_off_db, st)
+    e = head ? sgnn_tc_score_head(M, G, grid, smem, h->d_params, h->head_slot, h->d_Atc, h->d_Btc, sim, ld, cnt, cnt_tiled, node_off_q, node_off_db, smax, st)
              : sgnn_tc_score(M, G, relu, ref, simk, grid, smem, h->d_params, h->d_Atc, h->d_Btc, sim, ld, smax, st);
   if (e != cudaSuccess) return fail(h, std::string("tensor-core all-pairs launch: ") + cudaGetErrorString(e));
   return 0;
@@ -454,7 +463,8 @@ int score_and_topk(SgnnHandle h, const float* emb_q, int m, const float* emb_db,
   const int n_slices = tc_n_slices(n);
   const bool want_topk = k > 0 && ids;
   // hinted kernels: warp per row for k <= 32 and 1024..32768 columns, CTA per row for k <= 256 and >= 8192
-  const bool hint = want_topk && h->cfg.precision != SGNN_PREC_FP32 && h->M.n_head == 0 && (int64_t)m * n_slices <= h->cap_smax &&
+  const bool hint = want_topk && h->cfg.precision != SGNN_PREC_FP32 && (h->M.n_head == 0 || head_tc_will_run(h)) &&
+                    (int64_t)m * n_slices <= h->cap_smax &&
                     ((k <= 32 && n_slices >= 32 && n_slices <= 1024) || (k <= 256 && n_slices >= 256));
   if (score_all_pairs_stages(h, emb_q, m, emb_db, n, sim, ld, st, stages, hint ? h->d_smax : nullptr)) return 1;
   if (!want_topk) return 0;
@@ -531,7 +541,7 @@ int score_all_pairs_stages(SgnnHandle h, const float* emb_q, int32_t m, const fl
       const bool tiled = tc_hist && head_hmma_enabled() && ht_cnt_tiled_bytes(m, n) <= h->ht.cap_cnt;
       if (tiled) HG.cnt_m_pad = (m + 7) / 8 * 8;
       if (tc_hist) CUDA_OK(h, sgnn_hist_tc_run(HG, h->ht, h->hside[1].node_off, h->sm_count, st));
-      return score_all_pairs_tc(h, emb_q, m, emb_db, n, sim_dev, ld, st, SCORE_MAIN, nullptr, true,
+      return score_all_pairs_tc(h, emb_q, m, emb_db, n, sim_dev, ld, st, SCORE_MAIN, smax, true,
                                 tc_hist ? h->ht.cnt : nullptr, h->hside[0].node_off, h->hside[1].node_off, tiled);
     }
     if (lazy_tables) {   // the tensor-core head was planned but this database does not fit it

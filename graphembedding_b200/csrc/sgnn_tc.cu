@@ -105,14 +105,15 @@ int sgnn_tc_head_staging_floats() { return TCH_SLOT_FLOATS; }
 // shared memory by the kernel itself
 cudaError_t sgnn_tc_score_head(const ModelDev& M, const TcGeom& G, int grid, size_t smem, const float* params, int slot,
                                const void* A_ws, const void* B_ws, float* sim, int64_t ld, const uint8_t* cnt,
-                               bool cnt_tiled, const int32_t* node_off_q, const int32_t* node_off_db, cudaStream_t st) {
+                               bool cnt_tiled, const int32_t* node_off_q, const int32_t* node_off_db, unsigned long long* smax,
+                               cudaStream_t st) {
   if (!sgnn_tc_head_supported(M) || G.KC != TCH_K || G.QH != 8 || slot >= TCH_SLOTS) return cudaErrorInvalidValue;
   const __nv_bfloat16* A = static_cast<const __nv_bfloat16*>(A_ws);
   const __nv_bfloat16* B = static_cast<const __nv_bfloat16*>(B_ws);
   auto launch_it = [&](auto kern) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    kern<<<grid, TCH_THREADS, smem, st>>>(M, G, params, slot, A, B, sim, ld, cnt, node_off_q, node_off_db);
+    kern<<<grid, TCH_THREADS, smem, st>>>(M, G, params, slot, A, B, sim, ld, cnt, node_off_q, node_off_db, smax);
     return cudaGetLastError();
   };
   const bool hist = M.hist_bins > 0;

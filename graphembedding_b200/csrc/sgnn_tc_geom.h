@@ -76,7 +76,9 @@ int sgnn_tc_head_staging_floats();
 cudaError_t sgnn_tc_head_weights(const ModelDev& M, const float* params, float* staging, int slot, cudaStream_t st);
 cudaError_t sgnn_tc_score_head(const ModelDev& M, const TcGeom& G, int grid, size_t smem, const float* params, int slot,
                                const void* A_ws, const void* B_ws, float* sim, int64_t ld, const uint8_t* cnt,
-                               bool cnt_tiled, const int32_t* node_off_q, const int32_t* node_off_db, cudaStream_t st);
+                               bool cnt_tiled, const int32_t* node_off_q, const int32_t* node_off_db, unsigned long long* smax,
+                               cudaStream_t st);
+// smax (optional): slice maxima for the hinted top-k, as sgnn_tc_score
 // cnt_tiled: cnt holds the fp16 operand tiles of ht_cnt_tiled_bytes (HistTcGeom::cnt_m_pad), not [m][n][16] bytes
 inline int tc_n_slices(int n) { return ((n + 127) / 128) * 4; }
 

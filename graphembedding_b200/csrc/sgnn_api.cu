@@ -87,7 +87,6 @@ struct SgnnHandle_t {
   float* d_arm_ws = nullptr;                  // per-CTA arm buffers of the per-pair training kernel for graphs beyond shared memory
   int64_t cap_arm_ws = 0;
   long long* d_adam_t = nullptr;              // sgnn_adam_device_step: the step count (and the step size behind it) on the device
-  float* d_adam_lr = nullptr;
   bool adam_on_device = false;
   uint64_t drop_seed = 0, drop_counter = 0;   // dropout stream: one counter value per train/eval call
   int pair_offset = 0, pair_stride = 1;       // local pair p = pair offset + p * stride of the global batch (sgnn_set_pair_offset)
@@ -1331,8 +1330,8 @@ int sgnn_eval_pairs(SgnnHandle h, const SgnnGraphBatch* b, const int32_t* g1, co
 int sgnn_adam_device_step(SgnnHandle h, int32_t enable) {
   if (!h) return 1;
   if (enable && !h->d_adam_t) {
-    CUDA_OK(h, cudaMalloc(reinterpret_cast<void**>(&h->d_adam_t), 16));
-    h->d_adam_lr = reinterpret_cast<float*>(h->d_adam_t + 1);
+    CUDA_OK(h, cudaMalloc(reinterpret_cast<void**>(&h->d_adam_t), 16));   // [0] step count, [1] finished CTAs of the running update
+    CUDA_OK(h, cudaMemset(h->d_adam_t, 0, 16));
   }
   if (enable && !h->adam_on_device) {
     const long long t = h->adam_t;
@@ -1352,11 +1351,9 @@ int sgnn_apply_adam(SgnnHandle h, float grad_scale, float* loss_dev, void* strea
     const SgnnConfig& c = h->cfg;
     const int n = h->M.n_params;
     const int blocks = std::min((n + 255) / 256, h->sm_count);
-    adam_lr_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(h->d_adam_t, h->d_adam_lr, (double)c.learning_rate, (double)c.beta1,
-                                                      (double)c.beta2);
     adam_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(n, h->d_params, h->d_grads, h->d_m, h->d_v, grad_scale,
                                                          c.weight_decay, 0.f, c.beta1, c.beta2, c.epsilon, loss_dev,
-                                                         h->d_adam_lr);
+                                                         h->d_adam_t, (double)c.learning_rate);
     CUDA_OK(h, cudaGetLastError());
     return 0;
   }

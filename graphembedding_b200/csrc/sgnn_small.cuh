@@ -668,19 +668,23 @@ train_pairs_kernel(const __grid_constant__ ModelDev M, const BatchDev B,
   }
 }
 
-// TF-1 Adam's step size lr * sqrt(1 - b2^t) / (1 - b1^t) for the NEXT step, from a step count that lives on the device
-// (same double arithmetic as the host form in sgnn_apply_adam)
-__global__ void adam_lr_kernel(long long* __restrict__ t_dev, float* __restrict__ lr_dev, double lr, double b1, double b2) {
-  const double t = (double)(++(*t_dev));
-  *lr_dev = (float)(lr * sqrt(1.0 - pow(b2, t)) / (1.0 - pow(b1, t)));
-}
-
 // weight decay gradient + TF-1 Adam (models.py:28-29, 67-74; F14), grads zeroed afterwards
 __global__ void adam_kernel(int n, float* __restrict__ params, float* __restrict__ grads,
                             float* __restrict__ m, float* __restrict__ v, float grad_scale, float wd,
                             float lr_t, float b1, float b2, float eps, float* __restrict__ loss,
-                            const float* __restrict__ lr_dev = nullptr) {
-  if (lr_dev) lr_t = *lr_dev;   // device-side step count (adam_lr_kernel): the launch can sit in a replayed CUDA graph
+                            long long* __restrict__ t_dev = nullptr, double lr = 0.0) {
+  // t_dev: the step count lives on the device (sgnn_adam_device_step), so that the launch can sit in a replayed CUDA
+  // graph: every CTA derives this step's size lr sqrt(1 - b2^t) / (1 - b1^t), t = *t_dev + 1, in the host form's double
+  // arithmetic; the LAST CTA to finish advances the count (t_dev[1] counts finished CTAs: all of them have read t by then)
+  __shared__ float s_lr;
+  if (t_dev) {
+    if (threadIdx.x == 0) {
+      const double t = (double)(t_dev[0] + 1);
+      s_lr = (float)(lr * sqrt(1.0 - pow((double)b2, t)) / (1.0 - pow((double)b1, t)));
+    }
+    __syncthreads();
+    lr_t = s_lr;
+  }
   float wdl = 0.f;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const float p = params[i];
@@ -695,5 +699,15 @@ __global__ void adam_kernel(int n, float* __restrict__ params, float* __restrict
   if (loss) {
     wdl = warp_sum(wdl);
     if ((threadIdx.x & 31) == 0 && wdl != 0.f) atomicAdd(loss + 1, 0.5f * wd * wdl);
+  }
+  if (t_dev) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      if (atomicAdd(reinterpret_cast<unsigned long long*>(t_dev + 1), 1ull) == (unsigned long long)gridDim.x - 1ull) {
+        t_dev[1] = 0;
+        t_dev[0] += 1;
+      }
+    }
   }
 }

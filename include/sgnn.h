@@ -262,8 +262,8 @@ int sgnn_eval_pairs(SgnnHandle h, const SgnnGraphBatch* batch_dev, const int32_t
  * then zeroes the grad buffer.  grad_scale multiplies the summed gradient first.
  * loss_dev[1] = weight-decay loss term if loss_dev != NULL. */
 int sgnn_apply_adam(SgnnHandle h, float grad_scale, float* loss_dev, void* stream);
-/* enable = 1: Adam's step count t and the step size lr sqrt(1 - b2^t) / (1 - b1^t) live on the DEVICE (a one-thread
- * kernel in front of the update advances them, same double arithmetic as the host form), so that a sequence of
+/* enable = 1: Adam's step count t and the step size lr sqrt(1 - b2^t) / (1 - b1^t) live on the DEVICE (the update
+ * kernel derives and advances them itself, same double arithmetic as the host form), so that a sequence of
  * sgnn_train_step + sgnn_apply_adam calls can be captured once into a CUDA graph and replayed: one launch for K optimiser
  * steps instead of 2 K (the 128-pair step of configs[2] is otherwise bound by launch overhead).  enable = 0 copies the
  * count back to the host (synchronises).  The parameters after N steps are bit-identical in both modes. */

@@ -30,7 +30,7 @@ for case in range(int(os.environ.get('FUZZ_CASES', '40'))):
     sums = np.array_equal(got[:, :, :bins].sum(-1), np.outer(sq, sd)) and np.all(got[:, :, bins:] == 0)
     eq = np.array_equal(got[:, :, :bins][ok], want[ok])
     dmax = int(np.abs(got[:, :, :bins] - want).sum(-1).max())
-    good = sums and eq and dmax <= 4 and ok.mean() > 0.9
+    good = sums and eq and dmax <= 4 and (ok.mean() > 0.9 or m * n < 100)
     bad += not good
     print('all-pairs', case, cfg, 'm', m, 'n', n, 'qmax', qmax, 'dbmax', dbmax, 'scale', scale, 'ok' if good else 'FAIL', dmax, round(float(ok.mean()), 3), flush=True)
 for case in range(int(os.environ.get('FUZZ_PAIR_CASES', '12'))):

@@ -1437,6 +1437,17 @@ int sgnn_precision_at_k(SgnnHandle h, const float* true_sim_dev, const float* pr
   return 0;
 }
 
+int sgnn_precision_from_topk(SgnnHandle h, const float* true_sim_dev, int64_t ld, const float* true_topk_vals_dev,
+                             const int32_t* pred_topk_ids_dev, int32_t m, int32_t kmax, const int32_t* ks_dev,
+                             int32_t n_ks, double* prec_dev, void* stream) {
+  if (!h || !true_sim_dev || !true_topk_vals_dev || !pred_topk_ids_dev || !ks_dev || !prec_dev)
+    return fail(h, "sgnn_precision_from_topk: null argument");
+  if (m <= 0 || kmax <= 0 || n_ks <= 0) return fail(h, "sgnn_precision_from_topk: empty problem");
+  LAUNCH_OK(h, "sgnn_precision_from_topk", sgnn_launch_prec_from_topk(true_sim_dev, ld, true_topk_vals_dev, pred_topk_ids_dev,
+                                                                      m, kmax, ks_dev, n_ks, prec_dev, (cudaStream_t)stream));
+  return 0;
+}
+
 int sgnn_kendall_tau(SgnnHandle h, const float* true_sim_dev, const float* pred_sim_dev, int32_t m, int32_t n,
                      int64_t* counts_dev, double* tau_dev, void* stream) {
   if (!h || !true_sim_dev || !pred_sim_dev || !counts_dev) return fail(h, "sgnn_kendall_tau: null argument");

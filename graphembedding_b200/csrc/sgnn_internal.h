@@ -26,6 +26,8 @@ cudaError_t sgnn_launch_peer_adam(int n, int rank, int world, int64_t slot_elems
                                   float eps, float* loss, int sm_count, cudaStream_t st);
 cudaError_t sgnn_launch_sort_rows(const float* sim, int m, int n, int64_t ld, int32_t* ids, int smem_optin,
                                   cudaStream_t st);
+cudaError_t sgnn_launch_prec_from_topk(const float* true_sim, int64_t ld, const float* true_vals, const int32_t* pred_ids,
+                                       int m, int kmax, const int32_t* ks, int n_ks, double* prec, cudaStream_t st);
 cudaError_t sgnn_launch_prec_at_k(const float* true_sim, const float* pred_sim, int m, int n, const int32_t* ks,
                                   int n_ks, double* prec, int smem_optin, cudaStream_t st);
 cudaError_t sgnn_launch_kendall(const float* true_sim, const float* pred_sim, int m, int n, long long* counts,

@@ -46,6 +46,12 @@ cudaError_t sgnn_launch_sort_rows(const float* sim, int m, int n, int64_t ld, in
   return cudaGetLastError();
 }
 
+cudaError_t sgnn_launch_prec_from_topk(const float* true_sim, int64_t ld, const float* true_vals, const int32_t* pred_ids,
+                                       int m, int kmax, const int32_t* ks, int n_ks, double* prec, cudaStream_t st) {
+  prec_from_topk_kernel<<<n_ks, 256, 0, st>>>(true_sim, ld, true_vals, pred_ids, m, kmax, ks, n_ks, prec);
+  return cudaGetLastError();
+}
+
 cudaError_t sgnn_launch_prec_at_k(const float* true_sim, const float* pred_sim, int m, int n, const int32_t* ks,
                                   int n_ks, double* prec, int smem_optin, cudaStream_t st) {
   const int n_pad = pad_pow2(n);

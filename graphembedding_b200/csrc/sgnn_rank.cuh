@@ -656,3 +656,37 @@ kendall_tau_kernel(const float* __restrict__ true_sim, const float* __restrict__
     }
   }
 }
+
+
+// precision@k for SMALL k from two top-k lists (src/metrics.py:14-35): the tie-inclusive true top-k set of a row is
+// { j : true[j] >= k-th largest true value }, the predicted top-k the first k ids of the predicted order, so
+//   prec@k = mean_rows |{ i < k : true[row][pred_ids[row][i]] >= true_vals[row][k - 1] }| / k.
+// One CTA per k of the list; the hit counts are integers, so the result is exact and deterministic (no sort of the
+// 10 000-wide rows: 2 top-k launches + this kernel instead of two full row sorts).
+__global__ void __launch_bounds__(256)
+prec_from_topk_kernel(const float* __restrict__ true_sim, int64_t ld, const float* __restrict__ true_vals,
+                      const int32_t* __restrict__ pred_ids, int m, int kmax, const int32_t* __restrict__ ks, int n_ks,
+                      double* __restrict__ prec) {
+  __shared__ long long s_sum[8];
+  const int ki = blockIdx.x;
+  if (ki >= n_ks) return;
+  const int k = ks[ki];
+  long long hits = 0;
+  if (k >= 1 && k <= kmax)
+    for (int r = threadIdx.x; r < m; r += blockDim.x) {
+      const float thr = true_vals[(size_t)r * kmax + (k - 1)];
+      const int32_t* ids = pred_ids + (size_t)r * kmax;
+      const float* row = true_sim + (size_t)r * ld;
+      int c = 0;
+      for (int i = 0; i < k; ++i) c += row[ids[i]] >= thr ? 1 : 0;
+      hits += c;
+    }
+  for (int o = 16; o > 0; o >>= 1) hits += __shfl_down_sync(0xffffffffu, hits, o);
+  if ((threadIdx.x & 31) == 0) s_sum[threadIdx.x >> 5] = hits;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    long long t = 0;
+    for (int w = 0; w < 8; ++w) t += s_sum[w];
+    prec[ki] = (k >= 1 && k <= kmax) ? (double)t / ((double)k * (double)m) : 0.0 / 0.0;
+  }
+}

@@ -285,6 +285,15 @@ class SgnnEngine(object):
         assert tuple(true_sim.shape) == (m, n) and true_sim.is_contiguous() and pred_sim.is_contiguous()
         ks_d = torch.as_tensor(np.asarray(ks, np.int32), device=self.device)
         out = torch.empty(len(ks), dtype=torch.float64, device=self.device)
+        kmax = int(max(ks))
+        if kmax <= 64 and n >= 4 * kmax and min(ks) >= 1:
+            # small k: two top-k launches + a count kernel instead of two full row sorts (sgnn_precision_from_topk)
+            _, tv = self.topk(true_sim, kmax, stream=stream)
+            pi, _ = self.topk(pred_sim, kmax, stream=stream)
+            check(self.h, lib().sgnn_precision_from_topk(self.h, _ptr(true_sim), true_sim.stride(0), _ptr(tv), _ptr(pi), m,
+                                                         kmax, _ptr(ks_d), len(ks), _ptr(out), _stream_ptr(stream)))
+            self.launches += 1
+            return out
         check(self.h, lib().sgnn_precision_at_k(self.h, _ptr(true_sim), _ptr(pred_sim), m, n, _ptr(ks_d),
                                                 len(ks), _ptr(out), _stream_ptr(stream)))
         self.launches += 2

@@ -90,6 +90,7 @@ SIGNATURES = {
     'sgnn_set_pair_offset': (C.c_int, [_P, _I32, _I32]),
     'sgnn_set_embed_tc': (C.c_int, [_P, _I32]),
     'sgnn_precision_at_k': (C.c_int, [_P, _P, _P, _I32, _I32, _P, _I32, _P, _P]),
+    'sgnn_precision_from_topk': (C.c_int, [_P, _P, _I64, _P, _P, _I32, _I32, _P, _I32, _P, _P]),
     'sgnn_kendall_tau': (C.c_int, [_P, _P, _P, _I32, _I32, _P, _P, _P]),
     'sgnn_forward_pairs_host': (C.c_int, [_P, _BP, _P, _P, _I32, _P, _P]),
     'sgnn_rank_device': (C.c_int, [_P, _BP, _BP, _I32, _P, _P, _P, _I64, _P, _P, _P]),

@@ -260,3 +260,29 @@ def test_k_optimiser_steps_as_one_cuda_graph_equal_the_eager_steps(cfg):
     spread = float(np.max(np.abs(pe - pe2)))
     assert float(np.max(np.abs(pg - pe))) <= 4 * spread + 1e-7
     assert float(np.max(np.abs(lg - le))) <= 1e-5 * max(1.0, float(np.max(np.abs(le))))
+
+
+@pytest.mark.parametrize('n', [40, 1000, 10000])
+def test_precision_at_small_k_from_topk_equals_the_sorting_kernel_and_the_oracle(n):
+    """src/metrics.py:14-35 for k <= 64 without sorting the rows (sgnn_precision_from_topk): tie-inclusive true top-k
+    (heavy ties, fully tied rows), predicted top-k in the ranking's tie order -- equal to the oracle and to
+    sgnn_precision_at_k."""
+    from graphembedding_b200.native import lib
+    eng, layers, flat = _engine('default')
+    rng = np.random.default_rng(n)
+    m = 9
+    true = (rng.integers(0, max(2, n // 5), size=(m, n)) / 7.0).astype(np.float32)     # many ties
+    pred = np.round(rng.random((m, n)), 2).astype(np.float32)                          # ties in the prediction too
+    true[2, :] = 0.5
+    pred[3, :] = pred[3, 0]
+    true[4, : n // 2] = true[4, 0]
+    ks = [1, 2, 5, 10]
+    td, pd_ = torch.as_tensor(true, device=eng.device), torch.as_tensor(pred, device=eng.device)
+    got = eng.precision_at_ks(td, pd_, ks).cpu().numpy()                               # the top-k form (k <= 64, n >= 4 k)
+    ref = O.precision_at_ks(O.sort_id_mat_sim(true), true, O.sort_id_mat_sim(pred), pred, ks)
+    assert np.allclose(got, ref, rtol=0, atol=1e-12), (got, ref)
+    ks_d = torch.as_tensor(np.asarray(ks, np.int32), device=eng.device)
+    old = torch.empty(len(ks), dtype=torch.float64, device=eng.device)
+    assert lib().sgnn_precision_at_k(eng.h, td.data_ptr(), pd_.data_ptr(), m, n, ks_d.data_ptr(), len(ks), old.data_ptr(), None) == 0
+    torch.cuda.synchronize()
+    assert np.allclose(got, old.cpu().numpy(), rtol=0, atol=1e-12)

@@ -3,8 +3,9 @@
 #include "sgnn_internal.h"
 #include <algorithm>
 
+// power of two >= max(n, 16): block_bitonic_u64 works on 16-key blocks
 static int pad_pow2(int n) {
-  int p = 2;
+  int p = 16;
   while (p < n) p <<= 1;
   return p;
 }

@@ -438,50 +438,99 @@ topk_hint_warp_kernel(const float* __restrict__ sim, const unsigned long long* _
   }
 }
 
-// Full descending ranking of one row per CTA: bitonic sort of 64-bit keys in shared memory.
+// ---------------------------------------------------------------------------------------
+// Bitonic sort of n_pad (power of two, 16 <= n_pad <= 16 * blockDim.x) 64-bit keys in shared memory; DESC selects the
+// direction.  Register-blocked: a thread takes 2^NB keys whose indices differ in NB consecutive index bits, runs the NB
+// compare-exchange steps of those strides in registers and writes them back, so a merge phase of log2(size) steps costs
+// ceil(log2(size) / 4) trips through shared memory (32 for 16 384 keys instead of 105), and the phases of size <= 16
+// are one trip.  While sorting, logical key i lives in slot bitonic_slot(i): a rotation inside its 16-key block by the
+// block number, so both a thread's 16 CONTIGUOUS keys (stride-1 trip) and 16 lanes' consecutive keys (all other trips)
+// fall into 16 different 8-byte banks.  The caller FILLS s_keys[bitonic_slot(i)]; the result is in linear order.
+__device__ __forceinline__ int bitonic_slot(int i) { return (i & ~15) | ((i + (i >> 4)) & 15); }
+
+template <bool DESC>
+__device__ __forceinline__ void bitonic_cex(unsigned long long& a, unsigned long long& b, bool first) {
+  if (((a < b) == first) == DESC) { const unsigned long long t = a; a = b; b = t; }
+}
+
+// the NB steps of strides 2^(ls+NB-1) ... 2^ls of the merge phase `size`
+template <bool DESC, int NB>
+__device__ __forceinline__ void bitonic_trip(unsigned long long* s_keys, int n_pad, int size, int ls) {
+  constexpr int E = 1 << NB;
+  for (int g = threadIdx.x; g < (n_pad >> NB); g += blockDim.x) {
+    const int base = ((g >> ls) << (ls + NB)) | (g & ((1 << ls) - 1));
+    const bool first = (base & size) == 0;   // the bit `size` lies above every stride bit: one direction per thread
+    unsigned long long v[E];
+#pragma unroll
+    for (int j = 0; j < E; ++j) v[j] = s_keys[bitonic_slot(base + (j << ls))];
+#pragma unroll
+    for (int k = NB - 1; k >= 0; --k)
+#pragma unroll
+      for (int j = 0; j < E; ++j)
+        if (!(j & (1 << k))) bitonic_cex<DESC>(v[j], v[j | (1 << k)], first);
+#pragma unroll
+    for (int j = 0; j < E; ++j) s_keys[bitonic_slot(base + (j << ls))] = v[j];
+  }
+  __syncthreads();
+}
+
+template <bool DESC>
+__device__ __forceinline__ void block_bitonic_u64(unsigned long long* s_keys, int n_pad) {
+  // merge phases of size 2, 4, 8, 16: a thread sorts 16 contiguous keys in registers
+  for (int g = threadIdx.x; g < (n_pad >> 4); g += blockDim.x) {
+    const int base = g << 4;
+    unsigned long long v[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) v[j] = s_keys[bitonic_slot(base + j)];
+#pragma unroll
+    for (int size = 2; size <= 16; size <<= 1)
+#pragma unroll
+      for (int stride = size >> 1; stride > 0; stride >>= 1)
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          if (!(j & stride)) bitonic_cex<DESC>(v[j], v[j | stride], ((base + j) & size) == 0);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) s_keys[bitonic_slot(base + j)] = v[j];
+  }
+  __syncthreads();
+  for (int L = 5; (1 << L) <= n_pad; ++L) {
+    const int size = 1 << L, r = L & 3;
+    if (r == 1) bitonic_trip<DESC, 1>(s_keys, n_pad, size, L - 1);
+    else if (r == 2) bitonic_trip<DESC, 2>(s_keys, n_pad, size, L - 2);
+    else if (r == 3) bitonic_trip<DESC, 3>(s_keys, n_pad, size, L - 3);
+    for (int ls = L - r - 4; ls >= 0; ls -= 4) bitonic_trip<DESC, 4>(s_keys, n_pad, size, ls);
+  }
+  // back to linear order (a permutation inside every 16-key block)
+  unsigned long long v[16];
+#pragma unroll
+  for (int c = 0; c < 16; ++c) {
+    const int i = threadIdx.x + c * blockDim.x;
+    if (i < n_pad) v[c] = s_keys[bitonic_slot(i)];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int c = 0; c < 16; ++c) {
+    const int i = threadIdx.x + c * blockDim.x;
+    if (i < n_pad) s_keys[i] = v[c];
+  }
+  __syncthreads();
+}
+
+// Full descending ranking of one row per CTA: bitonic sort of 64-bit keys in shared memory (block_bitonic_u64).
 __global__ void __launch_bounds__(1024)
 sort_rows_kernel(const float* __restrict__ sim, int n, int n_pad, int64_t ld,
                  int32_t* __restrict__ ids) {
   extern __shared__ __align__(16) unsigned long long s_keys[];
   const float* r = sim + (size_t)blockIdx.x * ld;
-  for (int i = threadIdx.x; i < n_pad; i += blockDim.x) s_keys[i] = i < n ? rank_key(r[i], i) : 0ull;
+  for (int i = threadIdx.x; i < n_pad; i += blockDim.x) s_keys[bitonic_slot(i)] = i < n ? rank_key(r[i], i) : 0ull;
   __syncthreads();
-  for (int size = 2; size <= n_pad; size <<= 1) {
-    for (int stride = size >> 1; stride > 0; stride >>= 1) {
-      for (int t = threadIdx.x; t < (n_pad >> 1); t += blockDim.x) {
-        const int lo = 2 * t - (t & (stride - 1));
-        const int hi = lo + stride;
-        const bool desc = (lo & size) == 0;  // descending blocks first -> overall descending
-        const unsigned long long a = s_keys[lo], b = s_keys[hi];
-        if ((a < b) == desc) { s_keys[lo] = b; s_keys[hi] = a; }
-      }
-      __syncthreads();
-    }
-  }
+  block_bitonic_u64<true>(s_keys, n_pad);
   for (int i = threadIdx.x; i < n; i += blockDim.x)
     ids[(size_t)blockIdx.x * n + i] = (int)(s_keys[i] & 0xffffffffull);
 }
 
 // ---------------------------------------------------------------------------------------
 // Ranking metrics, one CTA (1024 threads) per query row, everything in shared memory.
-// ---------------------------------------------------------------------------------------
-// in-place bitonic sort of n_pad (power of two) 64-bit keys; DESC selects the direction
-template <bool DESC>
-__device__ __forceinline__ void block_bitonic_u64(unsigned long long* s_keys, int n_pad) {
-  for (int size = 2; size <= n_pad; size <<= 1) {
-    for (int stride = size >> 1; stride > 0; stride >>= 1) {
-      for (int t = threadIdx.x; t < (n_pad >> 1); t += blockDim.x) {
-        const int lo = 2 * t - (t & (stride - 1));
-        const int hi = lo + stride;
-        const bool first = (lo & size) == 0;
-        const unsigned long long a = s_keys[lo], b = s_keys[hi];
-        if (((a < b) == first) == DESC) { s_keys[lo] = b; s_keys[hi] = a; }
-      }
-      __syncthreads();
-    }
-  }
-}
-
 // precision@k (src/metrics.py:14-35 with results.py:51-82 top-k semantics): the true top-k is
 // tie-inclusive, the predicted top-k is the first k of the descending ranking.  Item j is in
 // both sets iff k >= need_j = max(tie-inclusive true position, predicted position), so ONE pass
@@ -497,7 +546,7 @@ prec_at_k_kernel(const float* __restrict__ true_sim, const float* __restrict__ p
   const float* t = true_sim + (size_t)blockIdx.x * n;
   const float* p = pred_sim + (size_t)blockIdx.x * n;
   const int tid = threadIdx.x;
-  for (int i = tid; i < n_pad; i += blockDim.x) s_keys[i] = i < n ? rank_key(t[i], i) : 0ull;
+  for (int i = tid; i < n_pad; i += blockDim.x) s_keys[bitonic_slot(i)] = i < n ? rank_key(t[i], i) : 0ull;
   for (int i = tid; i < n + 2; i += blockDim.x) s_hist[i] = 0;
   __syncthreads();
   block_bitonic_u64<true>(s_keys, n_pad);
@@ -512,7 +561,7 @@ prec_at_k_kernel(const float* __restrict__ true_sim, const float* __restrict__ p
     s_pos[(int)(s_keys[i] & 0xffffffffull)] = lo + 1;
   }
   __syncthreads();
-  for (int i = tid; i < n_pad; i += blockDim.x) s_keys[i] = i < n ? rank_key(p[i], i) : 0ull;
+  for (int i = tid; i < n_pad; i += blockDim.x) s_keys[bitonic_slot(i)] = i < n ? rank_key(p[i], i) : 0ull;
   __syncthreads();
   block_bitonic_u64<true>(s_keys, n_pad);
   for (int i = tid; i < n; i += blockDim.x) {
@@ -585,7 +634,7 @@ kendall_tau_kernel(const float* __restrict__ true_sim, const float* __restrict__
   const float* y = pred_sim + (size_t)blockIdx.x * n;
   const int tid = threadIdx.x;
   for (int i = tid; i < n_pad; i += blockDim.x)
-    s_keys[i] = i < n ? (((unsigned long long)orderable_u32(x[i]) << 32) | orderable_u32(y[i])) : ~0ull;
+    s_keys[bitonic_slot(i)] = i < n ? (((unsigned long long)orderable_u32(x[i]) << 32) | orderable_u32(y[i])) : ~0ull;
   __syncthreads();
   block_bitonic_u64<false>(s_keys, n_pad);   // ascending; padding (all ones) goes last
   // tie pairs: sum_i (#elements after i inside i's run) = sum_i (upper_bound(key_i) - 1 - i)

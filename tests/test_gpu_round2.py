@@ -286,3 +286,18 @@ def test_precision_at_small_k_from_topk_equals_the_sorting_kernel_and_the_oracle
     assert lib().sgnn_precision_at_k(eng.h, td.data_ptr(), pd_.data_ptr(), m, n, ks_d.data_ptr(), len(ks), old.data_ptr(), None) == 0
     torch.cuda.synchronize()
     assert np.allclose(got, old.cpu().numpy(), rtol=0, atol=1e-12)
+
+
+@pytest.mark.parametrize('n', [1, 3, 16, 17, 31, 100, 513, 4097, 10000, 16384])
+def test_full_ranking_of_rows_of_any_length_is_the_reference_order(n):
+    """results.py:221-224 (sort_id_mat): the register-blocked bitonic sort of sgnn_rank.cuh on row lengths either side
+    of its 16-key blocks and of the powers of two, with heavy ties (ties keep the reference's order) -- bit-exact."""
+    eng, layers, flat = _engine('default')
+    rng = np.random.default_rng(n)
+    m = 5
+    sim = (rng.integers(0, max(2, n // 4), size=(m, n)) / 9.0).astype(np.float32)
+    sim[1] = rng.random(n).astype(np.float32)
+    sim[2] = 0.5
+    sim[3] = np.sort(sim[3])
+    full = eng.sort_rows(torch.as_tensor(sim, device=eng.device)).cpu().numpy()
+    assert np.array_equal(full, O.sort_id_mat_sim(sim))

@@ -135,31 +135,39 @@ __device__ __forceinline__ float tch_count(unsigned word, int byte, float s, flo
 }
 
 // layers 1.. of the head on two pairs' layer-0 outputs (weight rows read once for both); final similarities in oa / ob
+// FAST: the activations are the SimGNN-style chain's (relu, relu, relu, identity, final sigmoid) at compile time -- no
+// run-time dispatch, no out-of-line call sites (they cost register moves around every call), the sigmoid in line
+template <bool FAST>
 __device__ __forceinline__ void tch_tail2(const TcHeadEpi& E, const float* sW, tch_f2* a0, tch_f2* b0, float& oa, float& ob) {
-  tch_act<TCH_H0 / 2>(a0, E.act0, E.yeta);
-  tch_act<TCH_H0 / 2>(b0, E.act0, E.yeta);
+  tch_act<TCH_H0 / 2>(a0, FAST ? (int)SGNN_ACT_RELU : E.act0, E.yeta);
+  tch_act<TCH_H0 / 2>(b0, FAST ? (int)SGNN_ACT_RELU : E.act0, E.yeta);
   tch_f2 a1[TCH_H1 / 2], b1[TCH_H1 / 2];
   tch_bias2<TCH_H1 / 4>(a1, b1, sW + TCH_B1);
 #pragma unroll
   for (int k = 0; k < TCH_H0; ++k)
     tch_row2<TCH_H1 / 4>(a1, b1, tch_half(a0[k >> 1], k & 1), tch_half(b0[k >> 1], k & 1),
                          reinterpret_cast<const float4*>(sW + TCH_W1 + k * TCH_H1));
-  tch_act<TCH_H1 / 2>(a1, E.act1, E.yeta);
-  tch_act<TCH_H1 / 2>(b1, E.act1, E.yeta);
+  tch_act<TCH_H1 / 2>(a1, FAST ? (int)SGNN_ACT_RELU : E.act1, E.yeta);
+  tch_act<TCH_H1 / 2>(b1, FAST ? (int)SGNN_ACT_RELU : E.act1, E.yeta);
   tch_f2 a2[TCH_H2 / 2], b2[TCH_H2 / 2];
   tch_bias2<TCH_H2 / 4>(a2, b2, sW + TCH_B2);
 #pragma unroll
   for (int k = 0; k < TCH_H1; ++k)
     tch_row2<TCH_H2 / 4>(a2, b2, tch_half(a1[k >> 1], k & 1), tch_half(b1[k >> 1], k & 1),
                          reinterpret_cast<const float4*>(sW + TCH_W2 + k * TCH_H2));
-  tch_act<TCH_H2 / 2>(a2, E.act2, E.yeta);
-  tch_act<TCH_H2 / 2>(b2, E.act2, E.yeta);
+  tch_act<TCH_H2 / 2>(a2, FAST ? (int)SGNN_ACT_RELU : E.act2, E.yeta);
+  tch_act<TCH_H2 / 2>(b2, FAST ? (int)SGNN_ACT_RELU : E.act2, E.yeta);
   const float4 w3 = *reinterpret_cast<const float4*>(sW + TCH_W3);
   const float c3 = sW[TCH_B3];
   oa = fmaf(tch_half(a2[1], 1), w3.w, fmaf(tch_half(a2[1], 0), w3.z, fmaf(tch_half(a2[0], 1), w3.y, fmaf(tch_half(a2[0], 0), w3.x, c3))));
   ob = fmaf(tch_half(b2[1], 1), w3.w, fmaf(tch_half(b2[1], 0), w3.z, fmaf(tch_half(b2[0], 1), w3.y, fmaf(tch_half(b2[0], 0), w3.x, c3))));
-  oa = tch_slow_act(tch_act1(oa, E.act3, E.yeta), E.final_act, E.yeta);
-  ob = tch_slow_act(tch_act1(ob, E.act3, E.yeta), E.final_act, E.yeta);
+  if (FAST) {   // the expression of sgnn_act(SGNN_ACT_SIGMOID): the same bits as the generic kernel
+    oa = 1.f / (1.f + expf(-oa));
+    ob = 1.f / (1.f + expf(-ob));
+  } else {
+    oa = tch_slow_act(tch_act1(oa, E.act3, E.yeta), E.final_act, E.yeta);
+    ob = tch_slow_act(tch_act1(ob, E.act3, E.yeta), E.final_act, E.yeta);
+  }
 }
 
 // Epilogue of one tile part: this thread owns TMEM lane (database graph) g and the accumulator columns of queries
@@ -168,7 +176,10 @@ __device__ __forceinline__ void tch_tail2(const TcHeadEpi& E, const float* sW, t
 // 50 KB epilogue starved on instruction fetch (ncu r2d: stall_no_instruction 5.7 per issue).
 // HMMA: the histogram half of layer 0 was done by the tensor core (second accumulator at taddr2: 16 columns per
 // query = sum_b count_b W0[16 + b][:]); the epilogue only scales it by 1 / (N_q N_g) into the layer-0 accumulators.
-template <bool HIST, bool CONSTW, bool HMMA>
+// FAST: the specialised activations of tch_tail2 (measured: 0.923 -> 0.901 ms per ranking step; reading the weights
+// from a compile-time constant slot on top of it, which turns half of the LDCU.64 into LDCU.128, gave 0.900, and
+// unrolling the k chunks for the other half spilled: 0.912 -- both dropped)
+template <bool HIST, bool CONSTW, bool HMMA, bool FAST>
 __device__ __forceinline__ void tc_head_epilogue_part(const TcHeadEpi& E, uint32_t taddr, uint32_t taddr2, int qrow0,
                                                       int part, int g, uint64_t* t_empty, int lane) {
   const bool gv = g < E.n;
@@ -180,6 +191,7 @@ __device__ __forceinline__ void tc_head_epilogue_part(const TcHeadEpi& E, uint32
     asm volatile("" : "+r"(opaque));   // per pass: the weight reads must not be hoisted out of the loop (register pressure)
     // (an offset, so that the pointer keeps its address space: LDS / LDCU, not a generic LD)
     const float* sW = CONSTW ? c_tch_w + E.slot * TCH_SLOT_FLOATS : E.sW + opaque;
+    const int act_ntn = FAST ? (int)SGNN_ACT_RELU : E.act_ntn;
     const int qa = qrow0 + 4 * part + 2 * qp, qb = qa + 1;
     const bool va = qa < E.m, vb = qb < E.m;
     uint4 ca = make_uint4(0u, 0u, 0u, 0u), cb = ca;
@@ -211,7 +223,7 @@ __device__ __forceinline__ void tc_head_epilogue_part(const TcHeadEpi& E, uint32
       const float4* w = reinterpret_cast<const float4*>(sW + TCH_W0 + kc * TCH_H0);
 #pragma unroll
       for (int k = 0; k < 8; ++k)
-        tch_row2<TCH_H0 / 4>(A, B, tch_act1(va8[k], E.act_ntn, E.yeta), tch_act1(vb8[k], E.act_ntn, E.yeta),
+        tch_row2<TCH_H0 / 4>(A, B, tch_act1(va8[k], act_ntn, E.yeta), tch_act1(vb8[k], act_ntn, E.yeta),
                              w + k * (TCH_H0 / 4));
     }
     if (HIST) {
@@ -248,7 +260,7 @@ __device__ __forceinline__ void tc_head_epilogue_part(const TcHeadEpi& E, uint32
       }
     }
     float oa, ob;
-    tch_tail2(E, sW, A, B, oa, ob);
+    tch_tail2<FAST>(E, sW, A, B, oa, ob);
     if (gv && va) E.sim[(size_t)qa * E.ld + g] = oa;
     if (gv && vb) E.sim[(size_t)qb * E.ld + g] = ob;
     if (E.smax) {   // largest rank key of this warp's 32-graph slice, per query (ties -> highest graph id)
@@ -397,7 +409,7 @@ __device__ __forceinline__ void tch_producer_mma_roles(const TcGeom& G, const Tc
   }
 }
 
-template <bool HIST, bool CONSTW, bool HMMA>
+template <bool HIST, bool CONSTW, bool HMMA, bool FAST = false>
 __global__ void __launch_bounds__(TCH_THREADS, 1)
 allpairs_tc_head_kernel(const __grid_constant__ ModelDev M, const TcGeom G, const float* __restrict__ params, int slot,
                         const __nv_bfloat16* __restrict__ Ag, const __nv_bfloat16* __restrict__ Bg,
@@ -505,7 +517,7 @@ allpairs_tc_head_kernel(const __grid_constant__ ModelDev M, const TcGeom G, cons
         tc::tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + buf * TC_NPAD;
         const int g = (gt0 + ga) * 128 + lg * 32 + lane;
-        tc_head_epilogue_part<HIST, CONSTW, HMMA>(E, taddr, taddr + 2 * TC_NPAD, (qb0 + i) * G.QH, part, g, t_empty + buf, lane);
+        tc_head_epilogue_part<HIST, CONSTW, HMMA, FAST>(E, taddr, taddr + 2 * TC_NPAD, (qb0 + i) * G.QH, part, g, t_empty + buf, lane);
       }
       it_base += total;
     }

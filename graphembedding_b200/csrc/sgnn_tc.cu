@@ -118,7 +118,14 @@ cudaError_t sgnn_tc_score_head(const ModelDev& M, const TcGeom& G, int grid, siz
   };
   const bool hist = M.hist_bins > 0;
   if (cnt_tiled && !hist) return cudaErrorInvalidValue;
-  if (cnt_tiled) return slot >= 0 ? launch_it(allpairs_tc_head_kernel<true, true, true>) : launch_it(allpairs_tc_head_kernel<true, false, true>);
+  if (cnt_tiled && slot >= 0) {
+    // the SimGNN-style chain's activations get the specialised epilogue (FAST of tc_head_epilogue_part)
+    const bool fast = M.pair_act == SGNN_ACT_RELU && M.Hd[0].act == SGNN_ACT_RELU && M.Hd[1].act == SGNN_ACT_RELU &&
+                      M.Hd[2].act == SGNN_ACT_RELU && M.Hd[3].act == SGNN_ACT_IDENTITY && M.final_act == SGNN_ACT_SIGMOID;
+    if (fast) return launch_it(allpairs_tc_head_kernel<true, true, true, true>);
+    return launch_it(allpairs_tc_head_kernel<true, true, true>);
+  }
+  if (cnt_tiled) return launch_it(allpairs_tc_head_kernel<true, false, true>);
   if (slot >= 0) return hist ? launch_it(allpairs_tc_head_kernel<true, true, false>) : launch_it(allpairs_tc_head_kernel<false, true, false>);
   return hist ? launch_it(allpairs_tc_head_kernel<true, false, false>) : launch_it(allpairs_tc_head_kernel<false, false, false>);
 }

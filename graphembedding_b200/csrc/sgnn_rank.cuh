@@ -620,6 +620,31 @@ __device__ __forceinline__ long long block_sum_i64(long long v, long long* s_red
   return v;
 }
 
+// tie pairs contributed by the elements of mask word t (kendall_tau_kernel): every set bit i adds the number of
+// consecutive set bits ending at i, counted across word boundaries
+__device__ __forceinline__ long long tie_pairs_of_word(const unsigned int* mask, int t) {
+  unsigned int w = mask[t];
+  if (w == 0u) return 0ll;
+  long long carry = 0;
+  if (w & 1u)   // the run at bit 0 continues the set bits at the top of the words before
+    for (int j = t - 1; j >= 0; --j) {
+      const int lead = __clz(~mask[j]);   // set bits from bit 31 downward (32 for an all-ones word)
+      carry += lead;
+      if (lead < 32) break;
+    }
+  long long sum = 0;
+  int consumed = 0;
+  while (w != 0u) {
+    const int tz = __ffs(w) - 1;
+    w >>= tz; consumed += tz;
+    const int r = w == 0xffffffffu ? 32 : __ffs(~w) - 1;   // run length (the shifted-in top bits are zero)
+    sum += (long long)r * (consumed == 0 ? carry : 0ll) + (long long)r * (r + 1) / 2;
+    w = r == 32 ? 0u : w >> r;
+    consumed += r;
+  }
+  return sum;
+}
+
 // Kendall tau-b of (true row, predicted row), exact integer pair counts (Knight's algorithm):
 // sort by (x, y); tie pairs from run lengths; discordant pairs = strict inversions of the y
 // sequence, counted by a bottom-up merge sort whose merges are rank computations by binary
@@ -637,18 +662,24 @@ kendall_tau_kernel(const float* __restrict__ true_sim, const float* __restrict__
     s_keys[bitonic_slot(i)] = i < n ? (((unsigned long long)orderable_u32(x[i]) << 32) | orderable_u32(y[i])) : ~0ull;
   __syncthreads();
   block_bitonic_u64<false>(s_keys, n_pad);   // ascending; padding (all ones) goes last
-  // tie pairs: sum_i (#elements after i inside i's run) = sum_i (upper_bound(key_i) - 1 - i)
-  long long nx = 0, nxy = 0;
-  for (int i = tid; i < n; i += blockDim.x) {
-    const unsigned long long k = s_keys[i];
-    const unsigned int kx = (unsigned int)(k >> 32);
-    int lo = i + 1, hi = n;
-    while (lo < hi) { const int mid = (lo + hi) >> 1; if ((unsigned int)(s_keys[mid] >> 32) > kx) hi = mid; else lo = mid + 1; }
-    nx += lo - 1 - i;
-    lo = i + 1; hi = n;
-    while (lo < hi) { const int mid = (lo + hi) >> 1; if (s_keys[mid] > k) hi = mid; else lo = mid + 1; }
-    nxy += lo - 1 - i;
+  // tie pairs of a sorted sequence = sum_i (#elements before i inside i's run of equal keys): bit i of a mask says
+  // "element i equals element i - 1" (one ballot per 32 consecutive elements), and the sum over a run of r set bits
+  // that continues c set bits of the words before it is r c + r (r + 1) / 2 -- no binary searches
+  __shared__ unsigned int s_mx[512], s_mxy[512];   // n_pad <= 16384
+  const int n_words = (n + 31) >> 5;
+  for (int i = tid; i < n_words * 32; i += blockDim.x) {   // (whole warps: i / 32 is warp-uniform)
+    bool ex = false, exy = false;
+    if (i >= 1 && i < n) {
+      const unsigned long long k = s_keys[i], kp = s_keys[i - 1];
+      ex = (unsigned int)(k >> 32) == (unsigned int)(kp >> 32);
+      exy = k == kp;
+    }
+    const unsigned int bx = __ballot_sync(0xffffffffu, ex), bxy = __ballot_sync(0xffffffffu, exy);
+    if ((tid & 31) == 0) { s_mx[i >> 5] = bx; s_mxy[i >> 5] = bxy; }
   }
+  __syncthreads();
+  long long nx = tid < n_words ? tie_pairs_of_word(s_mx, tid) : 0ll;
+  long long nxy = tid < n_words ? tie_pairs_of_word(s_mxy, tid) : 0ll;
   nx = block_sum_i64(nx, s_red);
   nxy = block_sum_i64(nxy, s_red);
   // compact the y keys (low words) of the sorted sequence into a u32 array over the same memory
@@ -686,13 +717,13 @@ kendall_tau_kernel(const float* __restrict__ true_sim, const float* __restrict__
     unsigned int* sw = src; src = dst; dst = sw;
   }
   dis = block_sum_i64(dis, s_red);
-  long long ny = 0;
-  for (int i = tid; i < n; i += blockDim.x) {
-    const unsigned int v = src[i];
-    int lo = i + 1, hi = n;
-    while (lo < hi) { const int md = (lo + hi) >> 1; if (src[md] > v) hi = md; else lo = md + 1; }
-    ny += lo - 1 - i;
+  for (int i = tid; i < n_words * 32; i += blockDim.x) {
+    const bool ey = i >= 1 && i < n && src[i] == src[i - 1];
+    const unsigned int by = __ballot_sync(0xffffffffu, ey);
+    if ((tid & 31) == 0) s_mx[i >> 5] = by;
   }
+  __syncthreads();
+  long long ny = tid < n_words ? tie_pairs_of_word(s_mx, tid) : 0ll;
   ny = block_sum_i64(ny, s_red);
   if (tid == 0) {
     const long long tot = (long long)n * (n - 1) / 2;
